@@ -1,0 +1,264 @@
+/*
+ * mgb200.h -- C ABI of libmgb200.so: the B200 (sm_100a) engine for the
+ * sample-and-evaluate hot path of dfki-asr/morphablegraphs.
+ *
+ * The reference has no FFI of its own (it is pure Python); the boundary it
+ * already exercises is the duck-typed batched API towards the absent `mgrd`
+ * package (reference morphablegraphs/motion_generator/mgrd_sample_filter.py:62-75,
+ * motion_primitive_generator.py:167-177).  Every entry point below names the
+ * reference function(s) it replaces.  INTEGRATION.md shows the ctypes stub a
+ * maintainer adds on the reference side.
+ *
+ * Conventions
+ *  - return 0 on success, a negative MGB_E_* code otherwise; the message is
+ *    available from mgb_last_error() (thread-local).  No C++ exception
+ *    crosses the ABI.
+ *  - `d_*` pointers are CALLER-OWNED DEVICE memory on the handle's device
+ *    (e.g. torch tensor data_ptr()), fp32 row-major unless stated otherwise.
+ *    `h_*` pointers are host memory.
+ *  - calls taking `stream` are asynchronous on that cudaStream_t (passed as
+ *    void*); NULL is the legacy default stream.
+ *  - a model / constraints handle is immutable after creation and may be used
+ *    from several host threads; workspace is per call.
+ *  - there is no CPU fallback: every compute entry fails with MGB_E_CUDA when
+ *    no sm_100-class device is usable.
+ */
+#ifndef MGB200_H
+#define MGB200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MGB_OK 0
+#define MGB_E_INVALID (-1)     /* bad argument / unsupported shape            */
+#define MGB_E_CUDA (-2)        /* CUDA runtime error (message has the detail) */
+#define MGB_E_UNSUPPORTED (-3) /* constraint type outside the device path     */
+#define MGB_E_WORKSPACE (-4)   /* workspace too small                         */
+
+typedef struct mgb_model mgb_model;
+typedef struct mgb_constraints mgb_constraints;
+
+/* Skeleton node types (anim_utils SKELETON_NODE_TYPE_*). */
+#define MGB_NODE_ROOT 0
+#define MGB_NODE_JOINT 1
+#define MGB_NODE_END_SITE 2
+
+/* One motion primitive: spatial fPCA basis + GMM + skeleton.  All arrays are
+ * host float64, exactly the numbers of the model JSON.
+ * Replaces: MotionPrimitive._initialize_from_json
+ *   (reference motion_model/motion_primitive.py:93-180) and the skeleton
+ *   fields the reference reads (utilities/__init__.py:13-16). */
+typedef struct {
+    int32_t n_frames;   /* F   n_canonical_frames                            */
+    int32_t n_basis;    /* Nb  n_basis_spatial                               */
+    int32_t n_dim;      /* P   n_dim_spatial = 3 + 4 * animated joints       */
+    int32_t n_spatial;  /* K   spatial latent dims                           */
+    int32_t n_latent;   /* D   GMM dimension (K + K_t)                       */
+    int32_t n_gmm;      /* G   mixture components                            */
+    const double* eigen;              /* [K, Nb*P]  eigen_vectors_spatial    */
+    const double* mean;               /* [Nb*P]     mean_spatial_vector      */
+    const double* knots;              /* [Nb+4]     b_spline_knots_spatial   */
+    const double* translation_maxima; /* [3]                                 */
+    const double* gmm_weights;        /* [G]                                 */
+    const double* gmm_means;          /* [G, D]                              */
+    const double* gmm_covars;         /* [G, D, D]                           */
+    int32_t n_nodes;
+    const int32_t* node_parent;  /* [n_nodes] parent index, -1 for the root; parents precede children */
+    const int32_t* node_type;    /* [n_nodes] MGB_NODE_*                     */
+    const int32_t* node_channel; /* [n_nodes] quaternion_frame_index, -1 if fixed */
+    const double* node_offset;   /* [n_nodes, 3]                             */
+    const double* node_rotation; /* [n_nodes, 4] (w,x,y,z), used for fixed joints */
+    int32_t aligning_node;       /* skeleton.aligning_root_node              */
+    double aligning_dir[3];      /* skeleton.aligning_root_dir               */
+} mgb_model_desc;
+
+/* Constraint term types (reference constraints/spatial_constraints/__init__.py:23-32). */
+#define MGB_CT_POSITION 0   /* keyframe_position: GlobalTransformConstraint          */
+#define MGB_CT_RELATIVE 1   /* keyframe_relative_position                            */
+#define MGB_CT_DIR2D 2      /* keyframe_2d_direction                                 */
+#define MGB_CT_POSE 3       /* keyframe_pose: PoseConstraint (transition continuity) */
+#define MGB_CT_TWO_HANDS 4  /* keyframe_two_hands                                    */
+#define MGB_CT_FEET 5       /* keyframe_feet                                         */
+#define MGB_CT_LOOK_AT 6    /* keyframe_look_at                                      */
+#define MGB_CT_CA 7         /* ca_constraint: min over frames                        */
+
+#define MGB_MAX_POSE_POINTS 32
+
+/* One constraint of a MotionPrimitiveConstraints list, flattened.
+ * Fields used per type:
+ *  POSITION : node[0], time_slot, has_position, axis_mask (bit i set = axis i constrained),
+ *             target, has_orientation, orient_q   (global_transform_constraint.py:71-143)
+ *  RELATIVE : as POSITION (all axes) + offset[4]  (relative_transform_constraint.py:46-50)
+ *  DIR2D    : time_slot, dir[2] = normalised (x,z) target (direction_2d_constraint.py:42-52)
+ *  POSE     : time_slot (t), time_slot2 (t+1), points_offset/n_points into the pose point
+ *             array, has_velocity, velocity[3]    (pose_constraint.py:48-67)
+ *  TWO_HANDS: node[0]=left, node[1]=right, target, target2, center (two_hand_constraint.py:68-93)
+ *  FEET     : node[0]=LeftFoot, node[1]=RightFoot, target=left, target2=right; the term is
+ *             multiplied by `weight` once more (quirk Q6, feet_constraint.py:49-50)
+ *  LOOK_AT  : node[0]=head joint, target          (look_at_constraint.py:58-68)
+ *  CA       : node[0], time_slot = first of n_slots consecutive slots, axis_mask, target
+ *             (global_transform_ca_constraint.py:34-40)
+ */
+typedef struct {
+    int32_t type;
+    int32_t node[2];
+    int32_t time_slot;
+    int32_t time_slot2;
+    int32_t n_slots;
+    int32_t points_offset;
+    int32_t n_points;
+    int32_t has_position;
+    int32_t has_orientation;
+    int32_t has_velocity;
+    uint32_t axis_mask;
+    double weight; /* weight_factor */
+    double target[3];
+    double target2[3];
+    double center[3];
+    double orient_q[4]; /* target orientation quaternion (w,x,y,z) */
+    double offset[4];
+    double dir[2];
+    double velocity[3];
+} mgb_constraint_desc;
+
+typedef struct {
+    int32_t node;
+    double target[3];
+    double weight;
+} mgb_pose_point;
+
+/* Optional frame alignment to the previous motion (non-local path,
+ * reference motion_primitive_constraints.py:111-114 with prev_frames given):
+ * heading (degrees, from +z towards +x) and root translation of the last
+ * previous frame. mode 0 = none (is_local), 1 = align to prev frame. */
+typedef struct {
+    int32_t mode;
+    double prev_heading_deg;
+    double prev_root[3];
+} mgb_align_desc;
+
+/* ---- handles ---------------------------------------------------------- */
+
+/* Copies bases, GMM (precision Cholesky computed here in fp64, as
+ * _compute_precision_cholesky at motion_primitive.py:141-142) and skeleton to
+ * `device`. */
+int mgb_model_create(const mgb_model_desc* desc, int device, mgb_model** out);
+void mgb_model_destroy(mgb_model* m);
+
+/* Cubic B-spline basis at `t`, FITPACK splev semantics incl. extrapolation
+ * (what motion_spline.py:89-92 evaluates per channel): value = sum_i w[i]*c[span+i]. */
+int mgb_spline_basis(const double* knots, int32_t n_knots, double t, int32_t* span, double w[4]);
+
+/* Compile a constraint list into a device program.
+ * times[n_times]: the distinct evaluation times; if spans/weights are given
+ * (4 weights per time, from the caller's own splev) they are used verbatim,
+ * otherwise computed with mgb_spline_basis.
+ * Replaces the per-candidate body of MotionPrimitiveConstraints.evaluate
+ * (motion_primitive_constraints.py:100-122). */
+int mgb_constraints_pack(const mgb_model* m, const mgb_constraint_desc* c, int32_t n,
+                         const mgb_pose_point* points, int32_t n_points,
+                         const double* times, int32_t n_times,
+                         const int32_t* spans /*[n_times] or NULL*/,
+                         const double* weights /*[n_times,4] or NULL*/,
+                         const mgb_align_desc* align /* or NULL */,
+                         mgb_constraints** out);
+void mgb_constraints_destroy(mgb_constraints* c);
+int32_t mgb_constraints_n_terms(const mgb_constraints* c);
+
+/* ---- kernels ---------------------------------------------------------- */
+
+/* K1: GMM sampling, s = mu_g + L_g z, samples stacked in component order as
+ * sklearn GaussianMixture.sample does (motion_primitive.py:182-189).
+ * h_counts[G]: samples per component over the WHOLE job (host multinomial
+ * draw); this call fills global indices [index_base, index_base + n).
+ * Philox4x32-10 keyed by (seed, global index): invariant to sharding. */
+int mgb_sample(const mgb_model* m, int64_t n, int64_t index_base, const int64_t* h_counts,
+               uint64_t seed, float* d_s /*[n,D]*/, void* stream);
+
+/* K6: fused score.  cost[i] = err_scale * sum_j w_j c_j(s_i)
+ *        + quality_scale * (-log p(s_i)) + magnitude_scale * |s_i|
+ * Replaces evaluate_samples_using_constraints' loop body
+ * (motion_primitive_generator.py:251-257 -> objective_functions.py:142-160 ->
+ * motion_primitive_constraints.py:100-122), the naturalness term
+ * (objective_functions.py:256) and `+ 2|s|` (mg_state_planner.py:110-129).
+ * s_is_f64 != 0: d_s holds float64 (what the reference's sampler returns).
+ * d_cost [n] and d_terms [n_terms, n] (unweighted per-constraint errors) may be
+ * NULL.  d_best_cost[k] / d_best_idx[k] (global index = index_base + i)
+ * receive the k smallest costs, ties -> lowest index (first-minimum rule,
+ * motion_primitive_generator.py:253-257); k == 0 skips selection.
+ * k > 1 requires d_cost.  Workspace: mgb_score_workspace_bytes(). */
+size_t mgb_score_workspace_bytes(int64_t n, int32_t k);
+int mgb_score(const mgb_model* m, const mgb_constraints* c, const void* d_s, int32_t s_is_f64,
+              int64_t n, int64_t index_base, float err_scale, float quality_scale,
+              float magnitude_scale, float* d_cost, float* d_terms, int32_t k,
+              float* d_best_cost, int64_t* d_best_idx, void* d_workspace,
+              size_t workspace_bytes, void* stream);
+
+/* Same through HOST buffers (pageable or pinned): chunked H2D on a copy stream
+ * overlapped with scoring, D2H of the k results; synchronous.  This is the
+ * call the reference-side shim makes with the numpy array it already holds. */
+int mgb_score_host(const mgb_model* m, const mgb_constraints* c, const void* h_s, int32_t s_is_f64,
+                   int64_t n, int64_t index_base, float err_scale, float quality_scale,
+                   float magnitude_scale, float* h_cost /*[n] or NULL*/, int32_t k,
+                   float* h_best_cost, int64_t* h_best_idx);
+
+/* K2: back-projection  coeffs[n, Nb*P] = s[:, :K] . E' + m'  (translation
+ * maxima folded in), motion_primitive.py:236-256.
+ * impl: 0 = auto, 1 = fp32 SIMT, 2 = tcgen05 TF32x3 tensor-core path. */
+int mgb_backproject(const mgb_model* m, const float* d_s, int64_t n, float* d_coeffs,
+                    int32_t impl, void* stream);
+
+/* K3: spline evaluation  frames[n, T, P] = B[T, Nb] . coeffs[n, Nb, P]
+ * (motion_spline.py:71-92).  spans/weights as in mgb_constraints_pack; device
+ * copies are made internally (T small). */
+int mgb_eval_frames(const mgb_model* m, const float* d_coeffs, int64_t n, const double* times,
+                    int32_t n_times, const int32_t* spans, const double* weights,
+                    float* d_frames, void* stream);
+
+/* K4: forward kinematics  pos[nT, nj, 3] of the listed nodes for frames[nT, P]
+ * (anim_utils SkeletonNode.get_global_position; call sites
+ * global_transform_constraint.py:103, pose_constraint.py:51, features.py:146). */
+int mgb_fk(const mgb_model* m, const float* d_frames, int64_t n_frames, const int32_t* h_nodes,
+           int32_t n_nodes, float* d_pos, void* stream);
+
+/* K5a: scoring from materialised frames (staged pipeline): d_frames is
+ * [n, n_times, P] at the constraint set's own times, in pack order. */
+int mgb_score_frames(const mgb_model* m, const mgb_constraints* c, const float* d_frames,
+                     const float* d_s /* [n,D] for logpdf / magnitude, may be NULL if unused */,
+                     int64_t n, int64_t index_base, float err_scale, float quality_scale,
+                     float magnitude_scale, float* d_cost, float* d_terms, int32_t k,
+                     float* d_best_cost, int64_t* d_best_idx, void* d_workspace,
+                     size_t workspace_bytes, void* stream);
+
+/* K5b: GMM log-density  logpdf[i] = logsumexp_g(log w_g + log N(s_i; mu_g, Sigma_g))
+ * (sklearn score_samples via precisions_cholesky_, objective_functions.py:110,198,256). */
+int mgb_logpdf(const mgb_model* m, const float* d_s, int64_t n, float* d_logpdf, void* stream);
+
+/* K5c: k smallest of a cost array, ties -> lowest index. */
+int mgb_topk(const float* d_cost, int64_t n, int64_t index_base, int32_t k, float* d_best_cost,
+             int64_t* d_best_idx, void* d_workspace, size_t workspace_bytes, void* stream);
+
+/* K7: one Lloyd iteration for every node of a cluster-tree level at once.
+ * x[n, dim] (row stride ld), node[n] = tree node of each sample in this level,
+ * centroids[n_nodes, 4, dim].  Assign writes label[n]; update accumulates
+ * sums[n_nodes,4,dim] / counts[n_nodes,4] (zeroed by the caller).
+ * Replaces sklearn KMeans(n_clusters=4).fit_predict per node
+ * (space_partitioning/cluster_tree_node_builder.py:83-103). */
+int mgb_kmeans_assign_update(const float* d_x, int64_t n, int32_t dim, int32_t ld,
+                             const int32_t* d_node, const float* d_centroids, int32_t n_sub,
+                             int32_t* d_label, float* d_sums, int32_t* d_counts,
+                             float* d_inertia /* [1], accumulated */, void* stream);
+
+/* number of kernels this library has launched in this process (bench.py's gpu_launches) */
+int64_t mgb_launch_count(void);
+const char* mgb_last_error(void);
+const char* mgb_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MGB200_H */

@@ -1,0 +1,128 @@
+"""ctypes binding of libmgb200.so (include/mgb200.h).
+
+The library is built in-tree by `__graft_entry__.build()` (explicit nvcc,
+sm_100a) so that the .so travels with the repository snapshot.  Loading fails
+loudly: there is no fallback implementation of any entry point.
+"""
+import ctypes as C
+import glob
+import os
+import subprocess
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+CSRC = os.path.join(_HERE, "csrc")
+LIB_PATH = os.path.join(CSRC, "libmgb200.so")
+INCLUDE = os.path.join(os.path.dirname(_HERE), "include", "mgb200.h")
+
+NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
+              "-Xcompiler", "-fPIC", "-shared"]
+
+
+def sources():
+    return sorted(glob.glob(os.path.join(CSRC, "*.cu")))
+
+
+def build(force=False, verbose=False):
+    """Compile csrc/*.cu into csrc/libmgb200.so for sm_100a (cross-compiles without a GPU)."""
+    srcs = sources()
+    deps = srcs + glob.glob(os.path.join(CSRC, "*.cuh")) + [INCLUDE]
+    if not force and os.path.exists(LIB_PATH):
+        if os.path.getmtime(LIB_PATH) >= max(os.path.getmtime(p) for p in deps):
+            return LIB_PATH
+    nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+    defines = ["-DMGB_HAVE_TC"] if any(os.path.basename(s) == "mgb_gemm_tc.cu" for s in srcs) else []
+    cmd = [nvcc] + NVCC_FLAGS + defines + ["-o", LIB_PATH] + srcs
+    if verbose:
+        print(" ".join(cmd))
+    subprocess.run(cmd, check=True)
+    return LIB_PATH
+
+
+class ModelDesc(C.Structure):
+    _fields_ = [("n_frames", C.c_int32), ("n_basis", C.c_int32), ("n_dim", C.c_int32), ("n_spatial", C.c_int32),
+                ("n_latent", C.c_int32), ("n_gmm", C.c_int32),
+                ("eigen", C.POINTER(C.c_double)), ("mean", C.POINTER(C.c_double)), ("knots", C.POINTER(C.c_double)),
+                ("translation_maxima", C.POINTER(C.c_double)), ("gmm_weights", C.POINTER(C.c_double)),
+                ("gmm_means", C.POINTER(C.c_double)), ("gmm_covars", C.POINTER(C.c_double)),
+                ("n_nodes", C.c_int32),
+                ("node_parent", C.POINTER(C.c_int32)), ("node_type", C.POINTER(C.c_int32)),
+                ("node_channel", C.POINTER(C.c_int32)), ("node_offset", C.POINTER(C.c_double)),
+                ("node_rotation", C.POINTER(C.c_double)),
+                ("aligning_node", C.c_int32), ("aligning_dir", C.c_double * 3)]
+
+
+class ConstraintDesc(C.Structure):
+    _fields_ = [("type", C.c_int32), ("node", C.c_int32 * 2), ("time_slot", C.c_int32), ("time_slot2", C.c_int32),
+                ("n_slots", C.c_int32), ("points_offset", C.c_int32), ("n_points", C.c_int32),
+                ("has_position", C.c_int32), ("has_orientation", C.c_int32), ("has_velocity", C.c_int32),
+                ("axis_mask", C.c_uint32), ("weight", C.c_double),
+                ("target", C.c_double * 3), ("target2", C.c_double * 3), ("center", C.c_double * 3),
+                ("orient_q", C.c_double * 4), ("offset", C.c_double * 4), ("dir", C.c_double * 2),
+                ("velocity", C.c_double * 3)]
+
+
+class PosePoint(C.Structure):
+    _fields_ = [("node", C.c_int32), ("target", C.c_double * 3), ("weight", C.c_double)]
+
+
+class AlignDesc(C.Structure):
+    _fields_ = [("mode", C.c_int32), ("prev_heading_deg", C.c_double), ("prev_root", C.c_double * 3)]
+
+
+CT_POSITION, CT_RELATIVE, CT_DIR2D, CT_POSE, CT_TWO_HANDS, CT_FEET, CT_LOOK_AT, CT_CA = range(8)
+MAX_POSE_POINTS = 32
+
+# every symbol include/mgb200.h declares: (restype, argtypes)
+_vp, _i32, _i64, _f, _sz = C.c_void_p, C.c_int32, C.c_int64, C.c_float, C.c_size_t
+_pd, _pi32 = C.POINTER(C.c_double), C.POINTER(C.c_int32)
+SYMBOLS = {
+    "mgb_model_create": (C.c_int, [C.POINTER(ModelDesc), C.c_int, C.POINTER(_vp)]),
+    "mgb_model_destroy": (None, [_vp]),
+    "mgb_spline_basis": (C.c_int, [_pd, _i32, C.c_double, _pi32, _pd]),
+    "mgb_constraints_pack": (C.c_int, [_vp, C.POINTER(ConstraintDesc), _i32, C.POINTER(PosePoint), _i32, _pd, _i32,
+                                       _pi32, _pd, C.POINTER(AlignDesc), C.POINTER(_vp)]),
+    "mgb_constraints_destroy": (None, [_vp]),
+    "mgb_constraints_n_terms": (_i32, [_vp]),
+    "mgb_sample": (C.c_int, [_vp, _i64, _i64, C.POINTER(C.c_int64), C.c_uint64, _vp, _vp]),
+    "mgb_score_workspace_bytes": (_sz, [_i64, _i32]),
+    "mgb_score": (C.c_int, [_vp, _vp, _vp, _i32, _i64, _i64, _f, _f, _f, _vp, _vp, _i32, _vp, _vp, _vp, _sz, _vp]),
+    "mgb_score_host": (C.c_int, [_vp, _vp, _vp, _i32, _i64, _i64, _f, _f, _f, _vp, _i32, _vp, _vp]),
+    "mgb_backproject": (C.c_int, [_vp, _vp, _i64, _vp, _i32, _vp]),
+    "mgb_eval_frames": (C.c_int, [_vp, _vp, _i64, _pd, _i32, _pi32, _pd, _vp, _vp]),
+    "mgb_fk": (C.c_int, [_vp, _vp, _i64, _pi32, _i32, _vp, _vp]),
+    "mgb_score_frames": (C.c_int, [_vp, _vp, _vp, _vp, _i64, _i64, _f, _f, _f, _vp, _vp, _i32, _vp, _vp, _vp, _sz, _vp]),
+    "mgb_logpdf": (C.c_int, [_vp, _vp, _i64, _vp, _vp]),
+    "mgb_topk": (C.c_int, [_vp, _i64, _i64, _i32, _vp, _vp, _vp, _sz, _vp]),
+    "mgb_kmeans_assign_update": (C.c_int, [_vp, _i64, _i32, _i32, _vp, _vp, _i32, _vp, _vp, _vp, _vp, _vp]),
+    "mgb_launch_count": (C.c_int64, []),
+    "mgb_last_error": (C.c_char_p, []),
+    "mgb_version": (C.c_char_p, []),
+}
+
+_lib = None
+
+
+class MgbError(RuntimeError):
+    pass
+
+
+def load():
+    """dlopen libmgb200.so and bind every declared symbol; raises if the library is absent."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise MgbError("libmgb200.so not built (%s missing): run `python -c 'import __graft_entry__ as g; g.build()'`; "
+                       "there is no CPU fallback" % LIB_PATH)
+    lib = C.CDLL(LIB_PATH)
+    for name, (res, args) in SYMBOLS.items():
+        fn = getattr(lib, name)     # AttributeError if the symbol is missing
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def check(rc):
+    if rc != 0:
+        raise MgbError("libmgb200: %s (code %d)" % (load().mgb_last_error().decode("utf-8", "replace"), rc))

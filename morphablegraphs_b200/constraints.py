@@ -1,0 +1,241 @@
+"""Host-side mirror of the reference's constraint containers for the hot path.
+
+Same class names, constructor signatures `(skeleton, constraint_desc, precision,
+weight_factor)` and attribute names as reference
+`morphablegraphs/constraints/spatial_constraints/keyframe_constraints/*.py` and
+`constraints/motion_primitive_constraints.py:56-77`, so that (a) the parity
+tests read like reference code and (b) `engine.pack_constraints` works on either
+these or the reference's own objects.  They are data holders: evaluation of a
+whole candidate batch happens on the GPU (`engine.DeviceConstraints`).
+"""
+import numpy as np
+
+SPATIAL_CONSTRAINT_TYPE_TRAJECTORY = "trajectory"
+SPATIAL_CONSTRAINT_TYPE_KEYFRAME_POSITION = "keyframe_position"
+SPATIAL_CONSTRAINT_TYPE_KEYFRAME_DIR_2D = "keyframe_2d_direction"
+SPATIAL_CONSTRAINT_TYPE_KEYFRAME_POSE = "keyframe_pose"
+SPATIAL_CONSTRAINT_TYPE_TWO_HAND_POSITION = "keyframe_two_hands"
+SPATIAL_CONSTRAINT_TYPE_TRAJECTORY_SET = "trajectory_set"
+SPATIAL_CONSTRAINT_TYPE_KEYFRAME_LOOK_AT = "keyframe_look_at"
+SPATIAL_CONSTRAINT_TYPE_KEYFRAME_FEET = "keyframe_feet"
+SPATIAL_CONSTRAINT_TYPE_CA_CONSTRAINT = "ca_constraint"
+SPATIAL_CONSTRAINT_TYPE_KEYFRAME_RELATIVE_POSITION = "keyframe_relative_position"
+
+
+class SpatialConstraintBase(object):
+    """reference spatial_constraint_base.py:29-35"""
+
+    def __init__(self, precision, weight_factor=1.0):
+        self.precision = precision
+        self.weight_factor = weight_factor
+        self.constraint_type = None
+
+
+class KeyframeConstraintBase(SpatialConstraintBase):
+    """reference keyframe_constraint_base.py:28-40"""
+
+    def __init__(self, constraint_desc, precision, weight_factor=1.0):
+        assert "canonical_keyframe" in list(constraint_desc.keys())
+        super(KeyframeConstraintBase, self).__init__(precision, weight_factor)
+        self.semantic_annotation = constraint_desc["semanticAnnotation"]
+        self.keyframe_label = constraint_desc["semanticAnnotation"]["keyframeLabel"]
+        self.canonical_keyframe = constraint_desc["canonical_keyframe"]
+
+
+class GlobalTransformConstraint(KeyframeConstraintBase):
+    """reference global_transform_constraint.py:38-64; orientation given as
+    `qOrientation` (w,x,y,z).  Euler `orientation` input needs anim_utils'
+    euler_to_quaternion and is converted by the caller."""
+
+    def __init__(self, skeleton, constraint_desc, precision, weight_factor=1.0):
+        super(GlobalTransformConstraint, self).__init__(constraint_desc, precision, weight_factor)
+        self.constraint_type = SPATIAL_CONSTRAINT_TYPE_KEYFRAME_POSITION
+        self.skeleton = skeleton
+        self.joint_name = constraint_desc["joint"]
+        self.position = constraint_desc["position"] if "position" in constraint_desc else None
+        if "qOrientation" in constraint_desc:
+            self.orientation = constraint_desc["qOrientation"]
+        else:
+            self.orientation = None
+        self.n_canonical_frames = constraint_desc["n_canonical_frames"]
+
+
+class RelativeTransformConstraint(GlobalTransformConstraint):
+    """reference relative_transform_constraint.py:33-44"""
+
+    def __init__(self, skeleton, constraint_desc, precision, weight_factor=1.0):
+        super(RelativeTransformConstraint, self).__init__(skeleton, constraint_desc, precision, weight_factor)
+        self.constraint_type = SPATIAL_CONSTRAINT_TYPE_KEYFRAME_RELATIVE_POSITION
+        self.offset = constraint_desc["offset"]
+
+
+class GlobalTransformCAConstraint(GlobalTransformConstraint):
+    """reference global_transform_ca_constraint.py:28-32"""
+
+    def __init__(self, skeleton, constraint_desc, precision, weight_factor=1.0, step_idx=-1):
+        super(GlobalTransformCAConstraint, self).__init__(skeleton, constraint_desc, precision, weight_factor)
+        self.constraint_type = SPATIAL_CONSTRAINT_TYPE_CA_CONSTRAINT
+        self.step_idx = step_idx
+
+
+class Direction2DConstraint(KeyframeConstraintBase):
+    """reference direction_2d_constraint.py:32-40"""
+
+    def __init__(self, skeleton, constraint_desc, precision, weight_factor=1.0):
+        super(Direction2DConstraint, self).__init__(constraint_desc, precision, weight_factor)
+        self.skeleton = skeleton
+        self.constraint_type = SPATIAL_CONSTRAINT_TYPE_KEYFRAME_DIR_2D
+        self.direction_constraint = constraint_desc["dir_vector"]
+        self.target_dir = np.array([self.direction_constraint[0], self.direction_constraint[2]], dtype=np.float64)
+        self.target_dir /= np.linalg.norm(self.target_dir)
+        self.target_dir_len = np.linalg.norm(self.target_dir)
+
+
+class PoseConstraint(KeyframeConstraintBase):
+    """reference pose_constraint.py:34-46"""
+
+    def __init__(self, skeleton, constraint_desc, precision, weight_factor=1.0):
+        super(PoseConstraint, self).__init__(constraint_desc, precision, weight_factor)
+        self.skeleton = skeleton
+        self.pose_constraint = constraint_desc["frame_constraint"]
+        self.velocity_constraint = constraint_desc.get("velocity_constraint", None)
+        self.constraint_type = SPATIAL_CONSTRAINT_TYPE_KEYFRAME_POSE
+        self.node_names = constraint_desc["node_names"]
+        self.weights = constraint_desc["weights"]
+
+
+class TwoHandConstraintSet(KeyframeConstraintBase):
+    """reference two_hand_constraint.py:40-54"""
+
+    def __init__(self, skeleton, constraint_desc, precision, weight_factor=1.0):
+        super(TwoHandConstraintSet, self).__init__(constraint_desc, precision, weight_factor)
+        self.skeleton = skeleton
+        self.constraint_type = SPATIAL_CONSTRAINT_TYPE_TWO_HAND_POSITION
+        self.positions = constraint_desc["positions"]
+        self.orientations = constraint_desc["orientations"]
+        self.joint_names = constraint_desc["joint"]
+        self.target_direction = np.array(self.positions[1], dtype=np.float64) - np.array(self.positions[0], dtype=np.float64)
+        self.target_delta = np.linalg.norm(self.target_direction)
+        self.target_center = np.array(self.positions[0], dtype=np.float64) + 0.5 * self.target_direction
+        self.target_direction /= self.target_delta
+        self.n_canonical_frames = constraint_desc["n_canonical_frames"]
+
+
+class FeetConstraint(KeyframeConstraintBase):
+    """reference feet_constraint.py:30-37"""
+
+    def __init__(self, skeleton, constraint_desc, precision, weight_factor=1.0):
+        super(FeetConstraint, self).__init__(constraint_desc, precision, weight_factor)
+        self.skeleton = skeleton
+        self.constraint_type = SPATIAL_CONSTRAINT_TYPE_KEYFRAME_FEET
+        self.left = constraint_desc["left"]
+        self.right = constraint_desc["right"]
+
+
+class LookAtConstraint(KeyframeConstraintBase):
+    """reference look_at_constraint.py:36-44"""
+
+    def __init__(self, skeleton, constraint_desc, precision, weight_factor=1.0):
+        super(LookAtConstraint, self).__init__(constraint_desc, precision, weight_factor)
+        self.skeleton = skeleton
+        self.constraint_type = SPATIAL_CONSTRAINT_TYPE_KEYFRAME_LOOK_AT
+        self.joint_name = "Head"
+        self.target_position = constraint_desc["position"]
+
+
+CONSTRAINT_FACTORY = {
+    "GlobalTransformConstraint": GlobalTransformConstraint,
+    "RelativeTransformConstraint": RelativeTransformConstraint,
+    "Direction2DConstraint": Direction2DConstraint,
+    "PoseConstraint": PoseConstraint,
+    "TwoHandConstraintSet": TwoHandConstraintSet,
+    "FeetConstraint": FeetConstraint,
+    "LookAtConstraint": LookAtConstraint,
+    "GlobalTransformCAConstraint": GlobalTransformCAConstraint,
+}
+
+
+class MotionPrimitiveConstraints(object):
+    """reference motion_primitive_constraints.py:47-77 (fields the hot path reads
+    and writes: constraints, is_local, skeleton, start_pose, aligning_transform,
+    min_error, evaluations, time, use_local_optimization)."""
+
+    def __init__(self):
+        self.action_name = None
+        self.motion_primitive_name = None
+        self.settings = None
+        self.constraints = list()
+        self.use_local_optimization = False
+        self.start_pose = None
+        self.skeleton = None
+        self.precision = {"pos": 1.0, "rot": 1.0, "smooth": 1.0}
+        self.verbose = False
+        self.min_error = 0.0
+        self.best_parameters = None
+        self.evaluations = 0
+        self.aligning_transform = None
+        self.is_local = False
+        self.is_last_step = False
+        self.time = 0.0
+
+    def transform_constraints_to_local_cos(self):
+        """reference motion_primitive_constraints.py:268-378 (host, once per step):
+        targets x inv(aligning_transform); position / relative / CA constraints are
+        rebuilt with weight 1.0 (quirk Q5), the others keep their weight."""
+        if self.is_local or self.aligning_transform is None:
+            return self
+        inv = np.linalg.inv(np.asarray(self.aligning_transform, dtype=np.float64))
+        out = MotionPrimitiveConstraints()
+        out.start_pose = {"orientation": [0, 0, 0], "position": [0, 0, 0]}
+        out.skeleton = self.skeleton
+        out.is_local = True
+        out.use_local_optimization = self.use_local_optimization
+
+        def tp(p, w=1.0):
+            return np.dot(inv, [p[0], p[1], p[2], w])[:3]
+
+        def tp_masked(position):
+            pos = [position[0], position[1], position[2], 1]
+            idx = [i for i in range(3) if pos[i] is None]
+            for i in idx:
+                pos[i] = 0
+            pos = np.dot(inv, pos)[:3].tolist()
+            for i in idx:
+                pos[i] = None
+            return pos
+
+        for c in self.constraints:
+            ct = c.constraint_type
+            base = {"canonical_keyframe": c.canonical_keyframe, "semanticAnnotation": c.semantic_annotation}
+            if ct == SPATIAL_CONSTRAINT_TYPE_KEYFRAME_POSITION:
+                if c.position is not None:
+                    d = dict(base, joint=c.joint_name, position=tp_masked(c.position), n_canonical_frames=c.n_canonical_frames)
+                    out.constraints.append(GlobalTransformConstraint(self.skeleton, d, 1.0))
+            elif ct == SPATIAL_CONSTRAINT_TYPE_KEYFRAME_RELATIVE_POSITION:
+                if c.position is not None:
+                    d = dict(base, joint=c.joint_name, position=tp_masked(c.position), n_canonical_frames=c.n_canonical_frames,
+                             offset=c.offset)
+                    out.constraints.append(RelativeTransformConstraint(self.skeleton, d, 1.0))
+            elif ct == SPATIAL_CONSTRAINT_TYPE_CA_CONSTRAINT:
+                d = dict(base, joint=c.joint_name, position=tp(c.position).tolist(), n_canonical_frames=c.n_canonical_frames,
+                         ca_constraint=True)
+                out.constraints.append(GlobalTransformCAConstraint(self.skeleton, d, 1.0))
+            elif ct == SPATIAL_CONSTRAINT_TYPE_TWO_HAND_POSITION:
+                d = dict(base, joint=c.joint_names, positions=[tp(p) for p in c.positions], orientations=c.orientations,
+                         n_canonical_frames=c.n_canonical_frames)
+                out.constraints.append(TwoHandConstraintSet(self.skeleton, d, c.precision, c.weight_factor))
+            elif ct == SPATIAL_CONSTRAINT_TYPE_KEYFRAME_POSE:
+                d = dict(base, keyframeLabel="start", frame_constraint=[tp(p) for p in c.pose_constraint],
+                         velocity_constraint=c.velocity_constraint, node_names=c.node_names, weights=c.weights)
+                out.constraints.append(PoseConstraint(self.skeleton, d, c.precision, c.weight_factor))
+            elif ct == SPATIAL_CONSTRAINT_TYPE_KEYFRAME_DIR_2D:
+                dv = c.direction_constraint
+                d = dict(base, dir_vector=tp(dv, 0.0))
+                out.constraints.append(Direction2DConstraint(self.skeleton, d, c.precision, c.weight_factor))
+            elif ct == SPATIAL_CONSTRAINT_TYPE_KEYFRAME_LOOK_AT:
+                d = dict(base, position=tp(c.target_position))
+                out.constraints.append(LookAtConstraint(self.skeleton, d, c.precision, c.weight_factor))
+            elif ct == SPATIAL_CONSTRAINT_TYPE_KEYFRAME_FEET:
+                d = dict(base, left=tp(c.left), right=tp(c.right))
+                out.constraints.append(FeetConstraint(self.skeleton, d, c.precision, c.weight_factor))
+        return out

@@ -1,0 +1,730 @@
+// Host side of libmgb200.so: handles, model packing, the constraint-program
+// compiler, FITPACK-compatible B-spline basis, and the host-buffer entry point.
+#include <math.h>
+#include <stdarg.h>
+#include <string.h>
+
+#include <algorithm>
+#include <atomic>
+#include <map>
+#include <mutex>
+
+#include "mgb_internal.cuh"
+
+// ---------------------------------------------------------------------------
+// errors / counters
+// ---------------------------------------------------------------------------
+static thread_local char g_err[1024] = "";
+static std::atomic<long long> g_launches{0};
+
+void mgb_set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+void mgb_count_launch(int n) { g_launches += n; }
+
+extern "C" const char* mgb_last_error(void) { return g_err; }
+extern "C" int64_t mgb_launch_count(void) { return g_launches.load(); }
+extern "C" const char* mgb_version(void) { return "mgb200 0.1 (sm_100a)"; }
+
+// ---------------------------------------------------------------------------
+// B-spline basis: FITPACK splev / fpbspl semantics (cubic), including the
+// clamp of the interval index that makes evaluation outside the knot range an
+// extrapolation of the end polynomial piece (reference quirk Q1:
+// motion_primitive.py:233 samples t = F, one past the last knot).
+// ---------------------------------------------------------------------------
+extern "C" int mgb_spline_basis(const double* knots, int32_t n_knots, double t, int32_t* span, double w[4]) {
+    MGB_REQUIRE(knots && span && w, "null argument");
+    const int k = 3;
+    MGB_REQUIRE(n_knots >= 2 * (k + 1), "need at least %d knots", 2 * (k + 1));
+    const int nk1 = n_knots - k - 1;
+    int l = k;  // knots[l] <= t < knots[l+1], clamped to [k, nk1-1]
+    while (l + 1 < nk1 && t >= knots[l + 1]) ++l;
+    double h[4] = {1.0, 0.0, 0.0, 0.0}, hh[3];
+    for (int j = 1; j <= k; ++j) {
+        for (int i = 0; i < j; ++i) hh[i] = h[i];
+        h[0] = 0.0;
+        for (int i = 0; i < j; ++i) {
+            const int li = l + i + 1, lj = li - j;
+            const double den = knots[li] - knots[lj];
+            const double f = den != 0.0 ? hh[i] / den : 0.0;
+            h[i] += f * (knots[li] - t);
+            h[i + 1] = f * (t - knots[lj]);
+        }
+    }
+    *span = l - k;
+    for (int i = 0; i < 4; ++i) w[i] = h[i];
+    return MGB_OK;
+}
+
+// ---------------------------------------------------------------------------
+// small fp64 helpers
+// ---------------------------------------------------------------------------
+static void quat_matrix_d(const double* q, double* R) {
+    // transformations.quaternion_matrix
+    const double n = q[0] * q[0] + q[1] * q[1] + q[2] * q[2] + q[3] * q[3];
+    if (n < 8.881784197001252e-16) {
+        for (int i = 0; i < 9; ++i) R[i] = (i % 4 == 0) ? 1.0 : 0.0;
+        return;
+    }
+    const double s = 2.0 / n;
+    const double w = q[0], x = q[1], y = q[2], z = q[3];
+    R[0] = 1.0 - s * (y * y + z * z); R[1] = s * (x * y - z * w);       R[2] = s * (x * z + y * w);
+    R[3] = s * (x * y + z * w);       R[4] = 1.0 - s * (x * x + z * z); R[5] = s * (y * z - x * w);
+    R[6] = s * (x * z - y * w);       R[7] = s * (y * z + x * w);       R[8] = 1.0 - s * (x * x + y * y);
+}
+
+static bool cholesky_lower(const double* A, int D, std::vector<double>& L) {
+    L.assign((size_t)D * D, 0.0);
+    for (int i = 0; i < D; ++i) {
+        for (int j = 0; j <= i; ++j) {
+            double s = A[(size_t)i * D + j];
+            for (int k = 0; k < j; ++k) s -= L[(size_t)i * D + k] * L[(size_t)j * D + k];
+            if (i == j) {
+                if (s <= 0.0) return false;
+                L[(size_t)i * D + i] = sqrt(s);
+            } else {
+                L[(size_t)i * D + j] = s / L[(size_t)j * D + j];
+            }
+        }
+    }
+    return true;
+}
+
+template <typename T>
+static int upload(T** dst, const std::vector<T>& src) {
+    *dst = nullptr;
+    if (src.empty()) return MGB_OK;
+    MGB_CUDA(cudaMalloc((void**)dst, sizeof(T) * src.size()));
+    MGB_CUDA(cudaMemcpy(*dst, src.data(), sizeof(T) * src.size(), cudaMemcpyHostToDevice));
+    return MGB_OK;
+}
+
+// ---------------------------------------------------------------------------
+// model
+// ---------------------------------------------------------------------------
+extern "C" int mgb_model_create(const mgb_model_desc* d, int device, mgb_model** out) {
+    MGB_REQUIRE(d && out, "null argument");
+    *out = nullptr;
+    MGB_REQUIRE(d->n_frames > 0 && d->n_basis >= 4 && d->n_dim >= 7 && d->n_spatial > 0, "bad model shape");
+    MGB_REQUIRE(d->n_latent >= d->n_spatial && d->n_gmm > 0, "bad GMM shape");
+    MGB_REQUIRE((d->n_dim - 3) % 4 == 0, "n_dim must be 3 + 4 * joints");
+    MGB_REQUIRE(d->eigen && d->mean && d->knots && d->translation_maxima && d->gmm_weights && d->gmm_means && d->gmm_covars,
+                "null model array");
+    MGB_REQUIRE(d->n_nodes > 0 && d->node_parent && d->node_type && d->node_channel && d->node_offset && d->node_rotation,
+                "null skeleton array");
+    int ndev = 0;
+    cudaError_t ce = cudaGetDeviceCount(&ndev);
+    if (ce != cudaSuccess || ndev <= 0) {
+        mgb_set_error("no CUDA device available (%s); libmgb200 has no CPU fallback", cudaGetErrorString(ce));
+        return MGB_E_CUDA;
+    }
+    MGB_REQUIRE(device >= 0 && device < ndev, "device %d out of range (%d devices)", device, ndev);
+    MGB_CUDA(cudaSetDevice(device));
+
+    mgb_model* m = new mgb_model();
+    m->device = device;
+    m->F = d->n_frames; m->Nb = d->n_basis; m->P = d->n_dim; m->K = d->n_spatial; m->D = d->n_latent; m->G = d->n_gmm;
+    m->M = m->Nb * m->P;
+    const int K = m->K, M = m->M, P = m->P, D = m->D, G = m->G;
+    m->E.resize((size_t)K * M);
+    m->mean.resize(M);
+    for (int j = 0; j < M; ++j) {
+        const int pch = j % P;
+        const double sc = pch < 3 ? d->translation_maxima[pch] : 1.0;  // motion_primitive.py:255
+        m->mean[j] = d->mean[j] * sc;
+        for (int k = 0; k < K; ++k) m->E[(size_t)k * M + j] = d->eigen[(size_t)k * M + j] * sc;
+    }
+    m->knots.assign(d->knots, d->knots + m->Nb + 4);
+    // skeleton
+    m->n_nodes = d->n_nodes;
+    m->parent.assign(d->node_parent, d->node_parent + d->n_nodes);
+    m->type.assign(d->node_type, d->node_type + d->n_nodes);
+    m->channel.assign(d->node_channel, d->node_channel + d->n_nodes);
+    m->offset.assign(d->node_offset, d->node_offset + 3 * d->n_nodes);
+    m->fixed_rot.resize((size_t)9 * d->n_nodes);
+    m->children.assign(d->n_nodes, std::vector<int>());
+    int n_root = 0;
+    for (int i = 0; i < d->n_nodes; ++i) {
+        const int pa = m->parent[i];
+        if (pa < 0) {
+            ++n_root;
+        } else if (pa >= i) {
+            mgb_set_error("skeleton nodes must be ordered parents first (node %d has parent %d)", i, pa);
+            delete m;
+            return MGB_E_INVALID;
+        } else {
+            m->children[pa].push_back(i);
+        }
+        if (m->channel[i] >= 0 && 3 + 4 * m->channel[i] + 4 > P) {
+            mgb_set_error("node %d: channel %d outside the %d pose channels", i, m->channel[i], P);
+            delete m;
+            return MGB_E_INVALID;
+        }
+        quat_matrix_d(d->node_rotation + 4 * i, &m->fixed_rot[(size_t)9 * i]);
+    }
+    if (n_root != 1 || m->parent[0] >= 0 || m->type[0] != MGB_NODE_ROOT) {
+        mgb_set_error("skeleton must have exactly one root, at index 0, of type MGB_NODE_ROOT");
+        delete m;
+        return MGB_E_INVALID;
+    }
+    m->aligning_node = d->aligning_node;
+    for (int i = 0; i < 3; ++i) m->aligning_dir[i] = d->aligning_dir[i];
+
+    // GMM: precision Cholesky (sklearn _compute_precision_cholesky, 'full'), per-component constant
+    m->NQ = (D + 3) / 4;
+    std::vector<float4> gtab((size_t)G * m->NQ * (D + 1));
+    std::vector<float> gc(G), chol((size_t)G * D * D), means((size_t)G * D);
+    std::vector<double> L, Pc((size_t)D * D);
+    for (int g = 0; g < G; ++g) {
+        if (!cholesky_lower(d->gmm_covars + (size_t)g * D * D, D, L)) {
+            mgb_set_error("covariance of GMM component %d is not positive definite", g);
+            delete m;
+            return MGB_E_INVALID;
+        }
+        // X = L^-1 (lower), precision_chol = X^T (upper): y = (s - mu) . Pc
+        std::fill(Pc.begin(), Pc.end(), 0.0);
+        for (int c = 0; c < D; ++c) {  // solve L x = e_c
+            for (int i = c; i < D; ++i) {
+                double s = (i == c) ? 1.0 : 0.0;
+                for (int k = c; k < i; ++k) s -= L[(size_t)i * D + k] * Pc[(size_t)c * D + k];  // Pc[c][k] = X[k][c]
+                Pc[(size_t)c * D + i] = s / L[(size_t)i * D + i];                               // X[i][c] stored transposed
+            }
+        }
+        double logdet = 0.0;
+        for (int i = 0; i < D; ++i) logdet += log(Pc[(size_t)i * D + i]);
+        gc[g] = (float)(log(d->gmm_weights[g]) + logdet - 0.5 * D * log(2.0 * M_PI));
+        const double* mu = d->gmm_means + (size_t)g * D;
+        for (int q = 0; q < m->NQ; ++q) {
+            float4* row = &gtab[(size_t)(g * m->NQ + q) * (D + 1)];
+            double bias[4] = {0, 0, 0, 0};
+            for (int k = 0; k <= D; ++k) {
+                float v[4] = {0, 0, 0, 0};
+                for (int c = 0; c < 4; ++c) {
+                    const int j = 4 * q + c;
+                    if (j >= D) continue;
+                    if (k < D) {
+                        v[c] = (float)Pc[(size_t)k * D + j];
+                        bias[c] -= mu[k] * Pc[(size_t)k * D + j];
+                    } else {
+                        v[c] = (float)bias[c];
+                    }
+                }
+                row[k] = make_float4(v[0], v[1], v[2], v[3]);
+            }
+        }
+        for (int i = 0; i < D * D; ++i) chol[(size_t)g * D * D + i] = (float)L[i];
+        for (int i = 0; i < D; ++i) means[(size_t)g * D + i] = (float)mu[i];
+    }
+    m->gmm_tab_bytes = gtab.size() * sizeof(float4);
+
+    std::vector<float> Ef(m->E.begin(), m->E.end()), meanf(m->mean.begin(), m->mean.end());
+    std::vector<float> offf(m->offset.begin(), m->offset.end()), rotf(m->fixed_rot.begin(), m->fixed_rot.end());
+    int rc = MGB_OK;
+    if ((rc = upload(&m->d_E, Ef)) || (rc = upload(&m->d_mean, meanf)) || (rc = upload(&m->d_gmm_tab, gtab)) ||
+        (rc = upload(&m->d_gmm_c, gc)) || (rc = upload(&m->d_chol, chol)) || (rc = upload(&m->d_means, means)) ||
+        (rc = upload(&m->d_parent, m->parent)) || (rc = upload(&m->d_type, m->type)) || (rc = upload(&m->d_channel, m->channel)) ||
+        (rc = upload(&m->d_offset, offf)) || (rc = upload(&m->d_fixed_rot, rotf))) {
+        mgb_model_destroy(m);
+        return rc;
+    }
+    *out = m;
+    return MGB_OK;
+}
+
+extern "C" void mgb_model_destroy(mgb_model* m) {
+    if (!m) return;
+    cudaSetDevice(m->device);
+    cudaFree(m->d_E); cudaFree(m->d_mean); cudaFree(m->d_gmm_tab); cudaFree(m->d_gmm_c); cudaFree(m->d_chol);
+    cudaFree(m->d_means); cudaFree(m->d_parent); cudaFree(m->d_type); cudaFree(m->d_channel); cudaFree(m->d_offset);
+    cudaFree(m->d_fixed_rot); cudaFree(m->d_Bsplit); cudaFree(m->d_ws);
+    for (int b = 0; b < 2; ++b) {
+        if (m->pinned[b]) cudaFreeHost(m->pinned[b]);
+        cudaFree(m->d_stage[b]);
+        if (m->ev_copied[b]) cudaEventDestroy(m->ev_copied[b]);
+        if (m->ev_done[b]) cudaEventDestroy(m->ev_done[b]);
+    }
+    if (m->copy_stream) cudaStreamDestroy(m->copy_stream);
+    if (m->compute_stream) cudaStreamDestroy(m->compute_stream);
+    delete m;
+}
+
+// ---------------------------------------------------------------------------
+// constraint program compiler
+// ---------------------------------------------------------------------------
+namespace {
+
+struct Action {
+    int code;
+    int a, b;
+    std::vector<float> cst;
+};
+
+struct Compiler {
+    const mgb_model* m;
+    int n_times;
+    std::vector<int> spans;
+    std::vector<double> weights;  // [n_times + 1][4]; the extra slot is control point 0 (alignment)
+    std::map<std::pair<int, int>, int> quad_of;  // (slot, group) -> quad; group -1 = translation, j = joint channel j
+    std::vector<std::pair<int, int>> quads;
+    std::vector<MgbOp> ops;
+    std::vector<float> cst;
+    std::vector<std::map<int, std::vector<Action>>> attach;  // [slot][node] -> actions
+    int scratch_used = 0;
+    int max_depth = 0;
+
+    int quad(int slot, int group) {
+        auto key = std::make_pair(slot, group);
+        auto it = quad_of.find(key);
+        if (it != quad_of.end()) return it->second;
+        int q = (int)quads.size();
+        quads.push_back(key);
+        quad_of[key] = q;
+        return q;
+    }
+    int push_cst(const std::vector<float>& v) {
+        int off = (int)cst.size();
+        cst.insert(cst.end(), v.begin(), v.end());
+        return off;
+    }
+    void op(int code, int a, int b, const std::vector<float>& v) {
+        MgbOp o;
+        o.code = code; o.a = a; o.b = b; o.c = push_cst(v);
+        ops.push_back(o);
+    }
+    int alloc_scratch(int n) {
+        int off = scratch_used;
+        scratch_used += n;
+        return off;
+    }
+    void add(int slot, int node, Action a) { attach[slot][node].push_back(std::move(a)); }
+
+    bool subtree_needed(int node, const std::vector<char>& need) const { return need[node] != 0; }
+
+    void emit_node(int slot, int node, const std::vector<char>& need, int depth) {
+        const int type = m->type[node];
+        const double* off = &m->offset[(size_t)3 * node];
+        if (type == MGB_NODE_ROOT) {
+            op(OP_ROOT, quad(slot, -1), quad(slot, m->channel[node] >= 0 ? m->channel[node] : 0),
+               {(float)off[0], (float)off[1], (float)off[2]});
+        } else if (type == MGB_NODE_JOINT && m->channel[node] >= 0) {
+            op(OP_JOINT, quad(slot, m->channel[node]), 0, {(float)off[0], (float)off[1], (float)off[2]});
+        } else {
+            std::vector<float> v(12);
+            bool ident = true;
+            for (int i = 0; i < 9; ++i) {
+                double r = (type == MGB_NODE_END_SITE) ? ((i % 4 == 0) ? 1.0 : 0.0) : m->fixed_rot[(size_t)9 * node + i];
+                v[i] = (float)r;
+                if (fabs(r - ((i % 4 == 0) ? 1.0 : 0.0)) > 0.0) ident = false;
+            }
+            for (int i = 0; i < 3; ++i) v[9 + i] = (float)off[i];
+            op(OP_CONST, ident ? 1 : 0, 0, v);
+        }
+        auto it = attach[slot].find(node);
+        if (it != attach[slot].end())
+            for (const Action& a : it->second) op(a.code, a.a, a.b, a.cst);
+        std::vector<int> kids;
+        for (int c : m->children[node])
+            if (need[c]) kids.push_back(c);
+        for (size_t i = 0; i < kids.size(); ++i) {
+            const bool last = (i + 1 == kids.size());
+            if (!last) {
+                op(OP_PUSH, 0, 0, {});
+                max_depth = std::max(max_depth, depth + 1);
+            }
+            emit_node(slot, kids[i], need, last ? depth : depth + 1);
+            if (!last) op(OP_POP, 0, 0, {});
+        }
+    }
+
+    void emit_slot(int slot) {
+        if (attach[slot].empty()) return;
+        std::vector<char> need(m->n_nodes, 0);
+        for (auto& kv : attach[slot]) {
+            int nd = kv.first;
+            while (nd >= 0 && !need[nd]) {
+                need[nd] = 1;
+                nd = m->parent[nd];
+            }
+        }
+        emit_node(slot, 0, need, 0);
+    }
+};
+
+}  // namespace
+
+extern "C" int mgb_constraints_pack(const mgb_model* m, const mgb_constraint_desc* cd, int32_t n, const mgb_pose_point* points,
+                                    int32_t n_points, const double* times, int32_t n_times, const int32_t* spans_in,
+                                    const double* weights_in, const mgb_align_desc* align, mgb_constraints** out) {
+    MGB_REQUIRE(m && out, "null argument");
+    *out = nullptr;
+    MGB_REQUIRE(n >= 0 && (n == 0 || cd), "bad constraint list");
+    MGB_REQUIRE(n_times >= 0 && (n_times == 0 || times), "bad time list");
+    MGB_REQUIRE((spans_in == nullptr) == (weights_in == nullptr), "spans and weights must be given together");
+    Compiler C;
+    C.m = m;
+    C.n_times = n_times;
+    C.spans.resize(n_times + 1);
+    C.weights.resize((size_t)4 * (n_times + 1));
+    for (int t = 0; t < n_times; ++t) {
+        if (spans_in) {
+            C.spans[t] = spans_in[t];
+            for (int q = 0; q < 4; ++q) C.weights[4 * t + q] = weights_in[4 * t + q];
+        } else {
+            int rc = mgb_spline_basis(m->knots.data(), (int)m->knots.size(), times[t], &C.spans[t], &C.weights[4 * t]);
+            if (rc != MGB_OK) return rc;
+        }
+        MGB_REQUIRE(C.spans[t] >= 0 && C.spans[t] + 4 <= m->Nb, "time %d: span %d out of range", t, C.spans[t]);
+    }
+    const int CP0 = n_times;  // pseudo slot: control point 0
+    C.spans[CP0] = 0;
+    C.weights[4 * CP0] = 1.0;
+    C.weights[4 * CP0 + 1] = C.weights[4 * CP0 + 2] = C.weights[4 * CP0 + 3] = 0.0;
+    C.attach.resize(n_times + 1);
+
+    auto check_node = [&](int nd) { return nd >= 0 && nd < m->n_nodes; };
+    auto check_slot = [&](int s) { return s >= 0 && s < n_times; };
+    struct Final { int code, a, b; std::vector<float> cst; };
+    std::vector<Final> finals;
+    std::vector<MgbOp> begins;
+
+    for (int j = 0; j < n; ++j) {
+        const mgb_constraint_desc& c = cd[j];
+        const float w = (float)c.weight;
+        switch (c.type) {
+            case MGB_CT_POSITION:
+            case MGB_CT_RELATIVE: {
+                MGB_REQUIRE(check_node(c.node[0]) && check_slot(c.time_slot), "constraint %d: bad node / time slot", j);
+                if (c.has_position) {
+                    if (c.type == MGB_CT_POSITION) {
+                        C.add(c.time_slot, c.node[0],
+                              {OP_POS, j, (int)(c.axis_mask & 7u), {w, (float)c.target[0], (float)c.target[1], (float)c.target[2]}});
+                    } else {
+                        C.add(c.time_slot, c.node[0],
+                              {OP_REL, j, 0, {w, (float)c.offset[0], (float)c.offset[1], (float)c.offset[2], (float)c.offset[3],
+                                              (float)c.target[0], (float)c.target[1], (float)c.target[2]}});
+                    }
+                }
+                if (c.has_orientation) {
+                    // anim_utils quaternion_rotate_vector(q, [0,0,0,1]) for a general q, then unit length
+                    const double qw = c.orient_q[0], qx = c.orient_q[1], qy = c.orient_q[2], qz = c.orient_q[3];
+                    double v[3] = {2 * (qx * qz + qw * qy), 2 * (qy * qz - qw * qx), qw * qw - qx * qx - qy * qy + qz * qz};
+                    double nv = sqrt(v[0] * v[0] + v[1] * v[1] + v[2] * v[2]);
+                    MGB_REQUIRE(nv > 0, "constraint %d: zero orientation quaternion", j);
+                    C.add(c.time_slot, c.node[0], {OP_ORIENT, j, 0, {w, (float)(v[0] / nv), (float)(v[1] / nv), (float)(v[2] / nv)}});
+                }
+                break;
+            }
+            case MGB_CT_DIR2D: {
+                MGB_REQUIRE(check_slot(c.time_slot) && check_node(m->aligning_node), "constraint %d: bad time slot", j);
+                const double len = sqrt(c.dir[0] * c.dir[0] + c.dir[1] * c.dir[1]);
+                C.add(c.time_slot, m->aligning_node,
+                      {OP_DIR2D, j, 0, {w, (float)m->aligning_dir[0], (float)m->aligning_dir[1], (float)m->aligning_dir[2],
+                                        (float)c.dir[0], (float)c.dir[1], (float)len}});
+                break;
+            }
+            case MGB_CT_LOOK_AT: {
+                MGB_REQUIRE(check_node(c.node[0]) && check_slot(c.time_slot), "constraint %d: bad node / time slot", j);
+                C.add(c.time_slot, c.node[0], {OP_LOOKAT, j, 0, {w, (float)c.target[0], (float)c.target[1], (float)c.target[2]}});
+                break;
+            }
+            case MGB_CT_TWO_HANDS:
+            case MGB_CT_FEET: {
+                MGB_REQUIRE(check_node(c.node[0]) && check_node(c.node[1]) && check_slot(c.time_slot), "constraint %d: bad node / time slot", j);
+                const int base = C.alloc_scratch(6);
+                C.add(c.time_slot, c.node[0], {OP_STORE, base, 0, {}});
+                C.add(c.time_slot, c.node[1], {OP_STORE, base + 3, 0, {}});
+                if (c.type == MGB_CT_TWO_HANDS) {
+                    finals.push_back({OP_TWOHANDS, j, base,
+                                      {w, (float)c.center[0], (float)c.center[1], (float)c.center[2], (float)c.target[0], (float)c.target[1],
+                                       (float)c.target[2], (float)c.target2[0], (float)c.target2[1], (float)c.target2[2]}});
+                } else {
+                    finals.push_back({OP_FEET, j, base,
+                                      {w, (float)c.target[0], (float)c.target[1], (float)c.target[2], (float)c.target2[0], (float)c.target2[1],
+                                       (float)c.target2[2], w}});
+                }
+                break;
+            }
+            case MGB_CT_POSE: {
+                MGB_REQUIRE(check_slot(c.time_slot), "constraint %d: bad time slot", j);
+                MGB_REQUIRE(c.n_points > 0 && c.n_points <= MGB_MAX_POSE_POINTS, "constraint %d: %d pose points (max %d)", j, c.n_points,
+                            MGB_MAX_POSE_POINTS);
+                MGB_REQUIRE(points && c.points_offset >= 0 && c.points_offset + c.n_points <= n_points, "constraint %d: pose points out of range", j);
+                if (c.has_velocity) MGB_REQUIRE(check_slot(c.time_slot2), "constraint %d: bad second time slot", j);
+                const int base = C.alloc_scratch(3 * c.n_points + 3);
+                double W = 0, sax = 0, saz = 0;
+                std::vector<float> v = {w, (float)c.n_points, c.has_velocity ? 1.f : 0.f, (float)c.velocity[0], (float)c.velocity[1],
+                                        (float)c.velocity[2], 0.f, 0.f, 0.f};
+                for (int q = 0; q < c.n_points; ++q) {
+                    const mgb_pose_point& pp = points[c.points_offset + q];
+                    MGB_REQUIRE(check_node(pp.node), "constraint %d: pose point %d has a bad node", j, q);
+                    C.add(c.time_slot, pp.node, {OP_STORE, base + 3 * q, 0, {}});
+                    W += pp.weight;
+                    sax += pp.weight * pp.target[0];
+                    saz += pp.weight * pp.target[2];
+                    v.push_back((float)pp.target[0]);
+                    v.push_back((float)pp.target[1]);
+                    v.push_back((float)pp.target[2]);
+                    v.push_back((float)pp.weight);
+                }
+                v[6] = (float)W; v[7] = (float)sax; v[8] = (float)saz;
+                if (c.has_velocity) C.add(c.time_slot2, points[c.points_offset].node, {OP_STORE, base + 3 * c.n_points, 0, {}});
+                finals.push_back({OP_POSE, j, base, v});
+                break;
+            }
+            case MGB_CT_CA: {
+                MGB_REQUIRE(check_node(c.node[0]) && c.n_slots > 0 && check_slot(c.time_slot) && check_slot(c.time_slot + c.n_slots - 1),
+                            "constraint %d: bad node / slot range", j);
+                const int sc = C.alloc_scratch(1);
+                MgbOp b;
+                b.code = OP_CA_BEGIN; b.a = sc; b.b = 0; b.c = 0;
+                begins.push_back(b);
+                for (int f = 0; f < c.n_slots; ++f)
+                    C.add(c.time_slot + f, c.node[0],
+                          {OP_CA_ACC, sc, (int)(c.axis_mask & 7u), {(float)c.target[0], (float)c.target[1], (float)c.target[2]}});
+                finals.push_back({OP_CA_END, j, sc, {w}});
+                break;
+            }
+            default:
+                mgb_set_error("constraint %d: type %d is outside the device path", j, c.type);
+                return MGB_E_UNSUPPORTED;
+        }
+    }
+    MGB_REQUIRE(C.scratch_used <= MGB_SCRATCH_FLOATS, "constraint set needs %d scratch floats (max %d)", C.scratch_used, MGB_SCRATCH_FLOATS);
+
+    // ---- program: [CA begins] [alignment prelude] [slots ...] [finals] -------
+    C.cst.push_back(0.f);  // offset 0 is a valid dummy for ops without constants
+    for (const MgbOp& b : begins) C.ops.push_back(b);
+    const bool do_align = align && align->mode == 1;
+    if (do_align) {
+        MGB_REQUIRE(check_node(m->aligning_node), "bad aligning node");
+        const double PI = M_PI;
+        C.add(CP0, m->aligning_node,
+              {OP_ALIGN, C.quad(CP0, -1), 0,
+               {(float)m->aligning_dir[0], (float)m->aligning_dir[1], (float)m->aligning_dir[2], (float)(align->prev_heading_deg * PI / 180.0),
+                (float)align->prev_root[0], (float)align->prev_root[2]}});
+        C.emit_slot(CP0);
+    }
+    for (int t = 0; t < n_times; ++t) C.emit_slot(t);
+    for (const Final& f : finals) C.op(f.code, f.a, f.b, f.cst);
+    MGB_REQUIRE(C.max_depth <= MGB_STACK_DEPTH, "skeleton walk needs a transform stack of %d (max %d)", C.max_depth, MGB_STACK_DEPTH);
+
+    // ---- contracted quad table (fp64 accumulate, fp32 store) ------------------
+    const int K = m->K, P = m->P, M = m->M;
+    mgb_constraints* c = new mgb_constraints();
+    c->model = m;
+    c->n_terms = n;
+    c->n_times = n_times;
+    c->n_quads = (int)C.quads.size();
+    c->tab.assign((size_t)c->n_quads * (K + 1) * 4, 0.f);
+    for (int q = 0; q < c->n_quads; ++q) {
+        const int slot = C.quads[q].first, group = C.quads[q].second;
+        const int ch0 = group < 0 ? 0 : 3 + 4 * group;
+        const int nch = group < 0 ? 3 : 4;
+        for (int ch = 0; ch < nch; ++ch) {
+            for (int k = 0; k <= K; ++k) {
+                double acc = 0.0;
+                for (int i = 0; i < 4; ++i) {
+                    const int col = (C.spans[slot] + i) * P + ch0 + ch;
+                    const double basis = (k < K) ? m->E[(size_t)k * M + col] : m->mean[col];
+                    acc += C.weights[4 * slot + i] * basis;
+                }
+                c->tab[((size_t)q * (K + 1) + k) * 4 + ch] = (float)acc;
+            }
+        }
+    }
+    c->ops_fused = C.ops;
+    // frames-mode program: quads index channels of the materialised frames
+    int cp0_slot = -1;
+    for (int t = 0; t < n_times; ++t)
+        if (C.spans[t] == 0 && C.weights[4 * t] == 1.0 && C.weights[4 * t + 1] == 0.0 && C.weights[4 * t + 2] == 0.0 && C.weights[4 * t + 3] == 0.0)
+            cp0_slot = t;
+    bool frames_ok = true;
+    c->ops_frames = C.ops;
+    for (MgbOp& o : c->ops_frames) {
+        auto remap = [&](int q) -> int {
+            int slot = C.quads[q].first, group = C.quads[q].second;
+            if (slot == CP0) {
+                if (cp0_slot < 0) { frames_ok = false; return 0; }
+                slot = cp0_slot;
+            }
+            return slot * P + (group < 0 ? 0 : 3 + 4 * group);
+        };
+        if (o.code == OP_ROOT) { o.a = remap(o.a); o.b = remap(o.b); }
+        else if (o.code == OP_JOINT || o.code == OP_ALIGN) { o.a = remap(o.a); }
+    }
+    if (!frames_ok) c->ops_frames.clear();
+    c->cst = C.cst;
+    c->n_ops = (int)C.ops.size();
+    c->n_cst = (int)C.cst.size();
+    c->times.assign(times, times + n_times);
+    c->spans.assign(C.spans.begin(), C.spans.begin() + n_times);
+    c->weights.assign(C.weights.begin(), C.weights.begin() + (size_t)4 * n_times);
+
+    MGB_CUDA(cudaSetDevice(m->device));
+    int rc = MGB_OK;
+    std::vector<float4> tab4((size_t)c->n_quads * (K + 1));
+    for (size_t i = 0; i < tab4.size(); ++i) tab4[i] = make_float4(c->tab[4 * i], c->tab[4 * i + 1], c->tab[4 * i + 2], c->tab[4 * i + 3]);
+    if ((rc = upload(&c->d_tab, tab4)) || (rc = upload(&c->d_ops_fused, c->ops_fused)) || (rc = upload(&c->d_ops_frames, c->ops_frames)) ||
+        (rc = upload(&c->d_cst, c->cst))) {
+        mgb_constraints_destroy(c);
+        return rc;
+    }
+    *out = c;
+    return MGB_OK;
+}
+
+extern "C" void mgb_constraints_destroy(mgb_constraints* c) {
+    if (!c) return;
+    cudaFree(c->d_tab); cudaFree(c->d_ops_fused); cudaFree(c->d_ops_frames); cudaFree(c->d_cst);
+    delete c;
+}
+
+extern "C" int32_t mgb_constraints_n_terms(const mgb_constraints* c) { return c ? c->n_terms : 0; }
+
+// ---------------------------------------------------------------------------
+// scoring entry points
+// ---------------------------------------------------------------------------
+extern "C" int mgb_score(const mgb_model* m, const mgb_constraints* c, const void* d_s, int32_t s_is_f64, int64_t n, int64_t index_base,
+                         float err_scale, float quality_scale, float magnitude_scale, float* d_cost, float* d_terms, int32_t k,
+                         float* d_best_cost, int64_t* d_best_idx, void* d_workspace, size_t workspace_bytes, void* stream) {
+    return mgb_launch_score(m, c, d_s, s_is_f64, nullptr, n, index_base, err_scale, quality_scale, magnitude_scale, d_cost, d_terms, k,
+                            d_best_cost, d_best_idx, d_workspace, workspace_bytes, (cudaStream_t)stream);
+}
+
+extern "C" int mgb_score_frames(const mgb_model* m, const mgb_constraints* c, const float* d_frames, const float* d_s, int64_t n,
+                                int64_t index_base, float err_scale, float quality_scale, float magnitude_scale, float* d_cost,
+                                float* d_terms, int32_t k, float* d_best_cost, int64_t* d_best_idx, void* d_workspace,
+                                size_t workspace_bytes, void* stream) {
+    MGB_REQUIRE(d_frames, "d_frames is NULL");
+    MGB_REQUIRE(c && (c->n_ops == 0 || !c->ops_frames.empty()),
+                "this constraint set needs control point 0 (alignment): include time 0 in the packed times to score from frames");
+    return mgb_launch_score(m, c, d_s, 0, d_frames, n, index_base, err_scale, quality_scale, magnitude_scale, d_cost, d_terms, k,
+                            d_best_cost, d_best_idx, d_workspace, workspace_bytes, (cudaStream_t)stream);
+}
+
+static std::mutex g_host_mutex;
+
+extern "C" int mgb_score_host(const mgb_model* m_, const mgb_constraints* c, const void* h_s, int32_t s_is_f64, int64_t n,
+                              int64_t index_base, float err_scale, float quality_scale, float magnitude_scale, float* h_cost, int32_t k,
+                              float* h_best_cost, int64_t* h_best_idx) {
+    MGB_REQUIRE(m_ && c && (h_s || n == 0), "null argument");
+    MGB_REQUIRE(k >= 0 && k <= 64, "k must be in [0, 64]");
+    MGB_REQUIRE(k == 0 || (h_best_cost && h_best_idx), "k > 0 needs h_best_cost / h_best_idx");
+    std::lock_guard<std::mutex> lock(g_host_mutex);
+    mgb_model* m = const_cast<mgb_model*>(m_);  // staging buffers are lazily created caches
+    MGB_CUDA(cudaSetDevice(m->device));
+    const size_t elt = s_is_f64 ? sizeof(double) : sizeof(float);
+    const size_t row = (size_t)m->D * elt;
+    const int64_t CH = 1 << 18;
+    const size_t chunk_bytes = (size_t)CH * row;
+    if (!m->copy_stream) {
+        MGB_CUDA(cudaStreamCreateWithFlags(&m->copy_stream, cudaStreamNonBlocking));
+        MGB_CUDA(cudaStreamCreateWithFlags(&m->compute_stream, cudaStreamNonBlocking));
+        for (int b = 0; b < 2; ++b) {
+            MGB_CUDA(cudaEventCreateWithFlags(&m->ev_copied[b], cudaEventDisableTiming));
+            MGB_CUDA(cudaEventCreateWithFlags(&m->ev_done[b], cudaEventDisableTiming));
+        }
+    }
+    if (m->stage_bytes < chunk_bytes) {
+        for (int b = 0; b < 2; ++b) {
+            if (m->pinned[b]) cudaFreeHost(m->pinned[b]);
+            cudaFree(m->d_stage[b]);
+            m->pinned[b] = nullptr;
+            m->d_stage[b] = nullptr;
+            MGB_CUDA(cudaMalloc(&m->d_stage[b], chunk_bytes));
+        }
+        m->stage_bytes = chunk_bytes;
+    }
+    const int64_t n_chunks = n > 0 ? (n + CH - 1) / CH : 0;
+    const bool need_all_costs = (h_cost != nullptr) || (k > 1);
+    // workspace layout: [score ws][chunk best cost][chunk best idx][costs (optional)]
+    const size_t ws_score = mgb_score_workspace_bytes(n, 1);
+    const size_t best_off = (ws_score + 255) & ~(size_t)255;
+    const size_t n_best = (size_t)std::max<int64_t>(n_chunks, 64);
+    const size_t idx_off = (best_off + n_best * sizeof(float) + 255) & ~(size_t)255;
+    const size_t cost_off = (idx_off + n_best * sizeof(int64_t) + 255) & ~(size_t)255;
+    const size_t need = cost_off + (need_all_costs ? (size_t)n * sizeof(float) : 0);
+    if (m->ws_bytes < need) {
+        cudaFree(m->d_ws);
+        m->d_ws = nullptr;
+        m->ws_bytes = 0;
+        MGB_CUDA(cudaMalloc(&m->d_ws, need));
+        m->ws_bytes = need;
+    }
+    unsigned char* ws = reinterpret_cast<unsigned char*>(m->d_ws);
+    float* d_bc = reinterpret_cast<float*>(ws + best_off);
+    int64_t* d_bi = reinterpret_cast<int64_t*>(ws + idx_off);
+    float* d_cost = need_all_costs ? reinterpret_cast<float*>(ws + cost_off) : nullptr;
+
+    cudaPointerAttributes attr;
+    bool host_pinned = false;
+    if (n > 0 && cudaPointerGetAttributes(&attr, h_s) == cudaSuccess) host_pinned = (attr.type == cudaMemoryTypeHost);
+    cudaGetLastError();  // pageable memory reports an error on old drivers; clear it
+    if (!host_pinned && n > 0 && !m->pinned[0]) {
+        for (int b = 0; b < 2; ++b) MGB_CUDA(cudaMallocHost(&m->pinned[b], chunk_bytes));
+    }
+    for (int64_t ch = 0; ch < n_chunks; ++ch) {
+        const int b = (int)(ch & 1);
+        const int64_t lo = ch * CH, cnt = std::min<int64_t>(CH, n - lo);
+        const unsigned char* src = reinterpret_cast<const unsigned char*>(h_s) + (size_t)lo * row;
+        if (ch >= 2) MGB_CUDA(cudaEventSynchronize(m->ev_done[b]));
+        if (host_pinned) {
+            MGB_CUDA(cudaMemcpyAsync(m->d_stage[b], src, (size_t)cnt * row, cudaMemcpyHostToDevice, m->copy_stream));
+        } else {
+            memcpy(m->pinned[b], src, (size_t)cnt * row);
+            MGB_CUDA(cudaMemcpyAsync(m->d_stage[b], m->pinned[b], (size_t)cnt * row, cudaMemcpyHostToDevice, m->copy_stream));
+        }
+        MGB_CUDA(cudaEventRecord(m->ev_copied[b], m->copy_stream));
+        MGB_CUDA(cudaStreamWaitEvent(m->compute_stream, m->ev_copied[b], 0));
+        int rc = mgb_launch_score(m, c, m->d_stage[b], s_is_f64, nullptr, cnt, index_base + lo, err_scale, quality_scale, magnitude_scale,
+                                  d_cost ? d_cost + lo : nullptr, nullptr, (k >= 1) ? 1 : 0, d_bc + ch, d_bi + ch, ws, ws_score,
+                                  m->compute_stream);
+        if (rc != MGB_OK) return rc;
+        MGB_CUDA(cudaEventRecord(m->ev_done[b], m->compute_stream));
+    }
+    if (h_cost && n > 0) MGB_CUDA(cudaMemcpyAsync(h_cost, d_cost, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, m->compute_stream));
+    if (k == 1) {
+        std::vector<float> bc(std::max<int64_t>(n_chunks, 1));
+        std::vector<int64_t> bi(std::max<int64_t>(n_chunks, 1));
+        if (n_chunks > 0) {
+            MGB_CUDA(cudaMemcpyAsync(bc.data(), d_bc, n_chunks * sizeof(float), cudaMemcpyDeviceToHost, m->compute_stream));
+            MGB_CUDA(cudaMemcpyAsync(bi.data(), d_bi, n_chunks * sizeof(int64_t), cudaMemcpyDeviceToHost, m->compute_stream));
+        }
+        MGB_CUDA(cudaStreamSynchronize(m->compute_stream));
+        float best = INFINITY;
+        int64_t besti = index_base;
+        bool have = false;
+        for (int64_t ch = 0; ch < n_chunks; ++ch) {
+            const float cc = bc[ch];
+            if (cc != cc) continue;  // NaN never wins (reference: `min_error > error`)
+            if (!have || cc < best || (cc == best && bi[ch] < besti)) {
+                best = cc;
+                besti = bi[ch];
+                have = true;
+            }
+        }
+        h_best_cost[0] = best;
+        h_best_idx[0] = besti;
+    } else if (k > 1) {
+        int rc = mgb_topk(d_cost, n, index_base, k, d_bc, d_bi, ws, ws_score, m->compute_stream);
+        if (rc != MGB_OK) return rc;
+        MGB_CUDA(cudaMemcpyAsync(h_best_cost, d_bc, k * sizeof(float), cudaMemcpyDeviceToHost, m->compute_stream));
+        MGB_CUDA(cudaMemcpyAsync(h_best_idx, d_bi, k * sizeof(int64_t), cudaMemcpyDeviceToHost, m->compute_stream));
+        MGB_CUDA(cudaStreamSynchronize(m->compute_stream));
+    } else {
+        MGB_CUDA(cudaStreamSynchronize(m->compute_stream));
+    }
+    return MGB_OK;
+}
+
+// placeholders until the tensor-core translation unit is linked in
+#ifndef MGB_HAVE_TC
+int mgb_backproject_tc(const mgb_model*, const float*, int64_t, float*, cudaStream_t) {
+    mgb_set_error("tensor-core back-projection not built");
+    return MGB_E_UNSUPPORTED;
+}
+int mgb_backproject_tc_prepare(mgb_model*) { return MGB_E_UNSUPPORTED; }
+#endif

@@ -1,0 +1,172 @@
+// Internal declarations shared by the translation units of libmgb200.so.
+// Not part of the ABI (include/mgb200.h is).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string>
+#include <vector>
+
+#include "../../include/mgb200.h"
+
+// ---------------------------------------------------------------------------
+// error handling: thread-local message, no exceptions across the ABI
+// ---------------------------------------------------------------------------
+void mgb_set_error(const char* fmt, ...);
+void mgb_count_launch(int n = 1);
+
+#define MGB_CUDA(expr)                                                                  \
+    do {                                                                                \
+        cudaError_t _e = (expr);                                                        \
+        if (_e != cudaSuccess) {                                                        \
+            mgb_set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, __LINE__); \
+            return MGB_E_CUDA;                                                          \
+        }                                                                               \
+    } while (0)
+
+#define MGB_REQUIRE(cond, ...)            \
+    do {                                  \
+        if (!(cond)) {                    \
+            mgb_set_error(__VA_ARGS__);   \
+            return MGB_E_INVALID;         \
+        }                                 \
+    } while (0)
+
+// ---------------------------------------------------------------------------
+// scoring program (built by mgb_constraints_pack, interpreted by the score kernels)
+// ---------------------------------------------------------------------------
+struct MgbOp {
+    int32_t code;
+    int32_t a;  // quad index / term index / scratch slot (see op list)
+    int32_t b;  // second quad index / mask / count
+    int32_t c;  // offset into the float constant pool
+};
+
+enum MgbOpCode : int32_t {
+    OP_ROOT = 0,      // a = translation quad, b = rotation quad, c -> root offset[3]
+    OP_JOINT = 1,     // a = rotation quad, c -> offset[3]
+    OP_CONST = 2,     // a = 1 if rotation is identity, c -> R[9], t[3]
+    OP_PUSH = 3,
+    OP_POP = 4,
+    OP_ALIGN = 5,     // a = translation quad of control point 0, c -> ref_dir[3], prev heading(rad), prev x, prev z
+    OP_POS = 6,       // a = term, b = axis mask, c -> weight, target[3]
+    OP_ORIENT = 7,    // a = term, c -> weight, v2[3] (unit)
+    OP_REL = 8,       // a = term, c -> weight, offset[4], target[3]
+    OP_DIR2D = 9,     // a = term, c -> weight, ref_dir[3], target_dir[2], target_len
+    OP_LOOKAT = 10,   // a = term, c -> weight, target[3]
+    OP_STORE = 11,    // a = scratch float offset: scratch[a..a+2] = position
+    OP_TWOHANDS = 12, // a = term, b = scratch offset (left, right), c -> weight, center[3], p0[3], p1[3]
+    OP_FEET = 13,     // a = term, b = scratch offset (left, right), c -> weight, left[3], right[3], inner weight
+    OP_POSE = 14,     // a = term, b = scratch offset: points [n*3] then root2[3]; c -> weight, n, has_vel, vel[3], W, sax, saz, (target[3], w) * n
+    OP_CA_BEGIN = 15, // a = scratch offset (1 float)
+    OP_CA_ACC = 16,   // a = scratch offset, b = axis mask, c -> target[3]
+    OP_CA_END = 17,   // a = term, b = scratch offset, c -> weight
+    OP_RESET = 18,    // G = identity (between slots; not required, kept for clarity)
+};
+
+#define MGB_SCRATCH_FLOATS 160
+#define MGB_STACK_DEPTH 8
+
+struct mgb_model {
+    int device = 0;
+    int F = 0, Nb = 0, P = 0, K = 0, D = 0, G = 0, M = 0;  // M = Nb * P
+    int n_nodes = 0;
+    int aligning_node = 0;
+    double aligning_dir[3] = {0, 0, 1};
+    // host fp64 (translation maxima already folded into E / mean)
+    std::vector<double> E;     // [K][M]
+    std::vector<double> mean;  // [M]
+    std::vector<double> knots; // [Nb+4]
+    std::vector<int> parent, type, channel;
+    std::vector<double> offset;    // [n_nodes][3]
+    std::vector<double> fixed_rot; // [n_nodes][9] rotation matrix of fixed joints (identity otherwise)
+    std::vector<std::vector<int>> children;
+    // device fp32
+    float* d_E = nullptr;     // [K][M]
+    float* d_mean = nullptr;  // [M]
+    // GMM
+    int NQ = 0;               // quads per component = ceil(D/4)
+    float4* d_gmm_tab = nullptr;  // [(g*NQ + q) * (D+1) + k]: k<D -> P_g[k][4q..4q+3], k==D -> -(mu_g P_g)[4q..]
+    float* d_gmm_c = nullptr;     // [G]  log w_g + log det - D/2 log 2 pi
+    float* d_chol = nullptr;      // [G][D][D] lower Cholesky of the covariances (sampling)
+    float* d_means = nullptr;     // [G][D]
+    size_t gmm_tab_bytes = 0;
+    // skeleton on device for the FK kernel
+    int* d_parent = nullptr;
+    int* d_type = nullptr;
+    int* d_channel = nullptr;
+    float* d_offset = nullptr;     // [n_nodes][3]
+    float* d_fixed_rot = nullptr;  // [n_nodes][9]
+    // tensor-core back-projection operands (TF32 hi/lo split), built lazily
+    float* d_Bsplit = nullptr;
+    int Ksplit = 0;
+    // private streams / staging for the host-buffer entry
+    cudaStream_t copy_stream = nullptr, compute_stream = nullptr;
+    void* pinned[2] = {nullptr, nullptr};
+    void* d_stage[2] = {nullptr, nullptr};
+    size_t stage_bytes = 0;
+    void* d_ws = nullptr;
+    size_t ws_bytes = 0;
+    cudaEvent_t ev_copied[2] = {nullptr, nullptr}, ev_done[2] = {nullptr, nullptr};
+};
+
+struct mgb_constraints {
+    const mgb_model* model = nullptr;
+    int n_terms = 0;
+    int n_times = 0;
+    int n_quads = 0;
+    int n_ops = 0;
+    int n_cst = 0;
+    bool needs_s = false;  // program itself never needs s beyond K; logpdf/magnitude decided per call
+    std::vector<MgbOp> ops_fused;   // quads index the contracted table
+    std::vector<MgbOp> ops_frames;  // quads index channels of materialised frames: slot * P + channel
+    std::vector<float> cst;
+    std::vector<float> tab;  // [n_quads][K+1][4]
+    std::vector<double> times;
+    std::vector<int> spans;
+    std::vector<double> weights;
+    float4* d_tab = nullptr;
+    MgbOp* d_ops_fused = nullptr;
+    MgbOp* d_ops_frames = nullptr;
+    float* d_cst = nullptr;
+};
+
+// device-side view handed to the score kernels by value
+struct ScoreParams {
+    const float4* tab;  // fused: contracted quads
+    const MgbOp* ops;
+    const float* cst;
+    int n_ops, n_cst, n_quads;
+    int K, D, P, n_times;
+    int n_terms;
+    // GMM
+    const float4* gmm_tab;
+    const float* gmm_c;
+    int G, NQ;
+    int gmm_in_smem;
+    // inputs
+    const void* s;        // [n, D] float or double
+    const float* frames;  // frames mode: [n, n_times, P]
+    long long n;
+    long long index_base;
+    float err_scale, quality_scale, magnitude_scale;
+    float* cost;
+    float* terms;
+    // selection
+    int want_best;
+    float* part_cost;          // [grid]
+    long long* part_idx;       // [grid]
+    unsigned int* done_count;  // [1]
+    float* best_cost;
+    long long* best_idx;
+    int tab_in_smem;
+};
+
+// launchers implemented in the kernel translation units
+int mgb_launch_score(const mgb_model* m, const mgb_constraints* c, const void* d_s, int s_is_f64,
+                     const float* d_frames, int64_t n, int64_t index_base, float err_scale,
+                     float quality_scale, float magnitude_scale, float* d_cost, float* d_terms, int k,
+                     float* d_best_cost, int64_t* d_best_idx, void* d_ws, size_t ws_bytes,
+                     cudaStream_t stream);
+int mgb_backproject_tc(const mgb_model* m, const float* d_s, int64_t n, float* d_coeffs, cudaStream_t stream);
+int mgb_backproject_tc_prepare(mgb_model* m);

@@ -1,0 +1,624 @@
+// K1 (GMM sampler), K2 (fp32 SIMT back-projection), K3 (spline evaluation),
+// K4 (forward kinematics), K5b (GMM log-density), K7 (k-means level step).
+// These are the HBM-bound staged kernels: each stages its tile through shared
+// memory so that every global access is a coalesced 128-bit (or 32-bit
+// unit-stride) transaction, and sizes its grid from the SM count.
+#include <float.h>
+#include <math.h>
+
+#include "mgb_internal.cuh"
+
+namespace {
+
+int sm_count() {
+    static int n = 0;
+    if (n == 0) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+        if (n <= 0) n = 148;
+    }
+    return n;
+}
+
+// ---------------------------------------------------------------------------
+// Philox4x32-10 (Salmon et al.), counter = (global index, block), key = seed
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ uint4 philox4x32_10(uint4 ctr, uint2 key) {
+    const unsigned int M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
+#pragma unroll
+    for (int r = 0; r < 10; ++r) {
+        unsigned int hi0 = __umulhi(M0, ctr.x), lo0 = M0 * ctr.x;
+        unsigned int hi1 = __umulhi(M1, ctr.z), lo1 = M1 * ctr.z;
+        ctr = make_uint4(hi1 ^ ctr.y ^ key.x, lo1, hi0 ^ ctr.w ^ key.y, lo0);
+        key.x += W0;
+        key.y += W1;
+    }
+    return ctr;
+}
+
+__device__ __forceinline__ float u01(unsigned int x) {  // (0, 1]
+    return (float)(x >> 8) * (1.0f / 16777216.0f) + (0.5f / 16777216.0f);
+}
+
+#define SAMPLE_BLOCK 128
+
+// K1.  One thread per candidate; z and then s live in the thread's shared-memory
+// row (odd stride), the tile is written out with unit-stride stores.
+__global__ void __launch_bounds__(SAMPLE_BLOCK) mgb_sample_kernel(const float* __restrict__ means, const float* __restrict__ chol,
+                                                                 const long long* __restrict__ prefix, int G, int D, long long n,
+                                                                 long long index_base, unsigned long long seed, float* __restrict__ out) {
+    extern __shared__ float sm[];
+    const int SROW = D | 1;
+    float* row = sm + threadIdx.x * SROW;
+    const long long n_tiles = (n + SAMPLE_BLOCK - 1) / SAMPLE_BLOCK;
+    for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const long long i = tile * SAMPLE_BLOCK + threadIdx.x;
+        const long long gi = index_base + i;
+        __syncthreads();
+        if (i < n) {
+            // component of global index gi in the component-ordered stacking
+            int g = 0;
+            while (g + 1 < G && gi >= prefix[g + 1]) ++g;
+            uint2 key = make_uint2((unsigned int)seed, (unsigned int)(seed >> 32));
+            for (int d0 = 0; d0 < D; d0 += 4) {
+                uint4 r = philox4x32_10(make_uint4((unsigned int)gi, (unsigned int)((unsigned long long)gi >> 32), (unsigned int)(d0 >> 2), 0x6d67u), key);
+                float r0 = sqrtf(-2.f * __logf(u01(r.x))), r1 = sqrtf(-2.f * __logf(u01(r.z)));
+                float s0, c0, s1, c1;
+                __sincosf(6.283185307179586f * u01(r.y), &s0, &c0);
+                __sincosf(6.283185307179586f * u01(r.w), &s1, &c1);
+                float z[4] = {r0 * c0, r0 * s0, r1 * c1, r1 * s1};
+                for (int q = 0; q < 4 && d0 + q < D; ++q) row[d0 + q] = z[q];
+            }
+            // s = mu + L z, in place from the last row up (row d only needs z[0..d])
+            const float* L = chol + (size_t)g * D * D;
+            const float* mu = means + (size_t)g * D;
+            for (int d = D - 1; d >= 0; --d) {
+                float acc = __ldg(mu + d);
+                const float* Lr = L + (size_t)d * D;
+                for (int j = 0; j <= d; ++j) acc = fmaf(__ldg(Lr + j), row[j], acc);
+                row[d] = acc;
+            }
+        }
+        __syncthreads();
+        // coalesced write-out of the tile
+        const long long base = tile * SAMPLE_BLOCK;
+        const long long remaining = (n - base) * (long long)D;
+        const int total = SAMPLE_BLOCK * D;
+        const int step_r = SAMPLE_BLOCK / D, step_c = SAMPLE_BLOCK % D;
+        int r = threadIdx.x / D, c = threadIdx.x % D;
+        float* dst = out + base * D;
+        for (int e = threadIdx.x; e < total; e += SAMPLE_BLOCK) {
+            if (e < remaining) dst[e] = sm[r * SROW + c];
+            r += step_r;
+            c += step_c;
+            if (c >= D) { c -= D; r += 1; }
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------
+// K2 (SIMT fp32): coeffs[n, M] = alpha[n, K] . E'[K, M] + mean'[M]
+// CTA = 256 threads = 256 consecutive columns x BP_ROWS candidates; alpha tile
+// transposed in shared memory so one 128-bit broadcast load feeds 4 FMAs;
+// every store instruction of a warp writes 128 contiguous bytes.
+// ---------------------------------------------------------------------------
+#define BP_ROWS 32
+#define BP_COLS 256
+__global__ void __launch_bounds__(BP_COLS) mgb_backproject_simt(const float* __restrict__ s, int D, int K, const float* __restrict__ E,
+                                                                const float* __restrict__ mean, int M, long long n, float* __restrict__ out) {
+    extern __shared__ __align__(16) float sm_a[];  // [K][BP_ROWS]
+    const int col = blockIdx.x * BP_COLS + threadIdx.x;
+    const bool col_ok = col < M;
+    const float mu = col_ok ? __ldg(mean + col) : 0.f;
+    const long long n_row_tiles = (n + BP_ROWS - 1) / BP_ROWS;
+    for (long long rt = blockIdx.y; rt < n_row_tiles; rt += gridDim.y) {
+        const long long r0 = rt * BP_ROWS;
+        __syncthreads();
+        for (int e = threadIdx.x; e < BP_ROWS * K; e += BP_COLS) {
+            int r = e / K, k = e - r * K;
+            long long gr = r0 + r;
+            sm_a[k * BP_ROWS + r] = (gr < n) ? __ldg(s + gr * D + k) : 0.f;
+        }
+        __syncthreads();
+        float acc[BP_ROWS];
+#pragma unroll
+        for (int r = 0; r < BP_ROWS; ++r) acc[r] = mu;
+        for (int k = 0; k < K; ++k) {
+            const float e = col_ok ? __ldg(E + (size_t)k * M + col) : 0.f;
+            const float4* a4 = reinterpret_cast<const float4*>(sm_a + k * BP_ROWS);
+#pragma unroll
+            for (int r4 = 0; r4 < BP_ROWS / 4; ++r4) {
+                float4 a = a4[r4];
+                acc[4 * r4 + 0] = fmaf(a.x, e, acc[4 * r4 + 0]);
+                acc[4 * r4 + 1] = fmaf(a.y, e, acc[4 * r4 + 1]);
+                acc[4 * r4 + 2] = fmaf(a.z, e, acc[4 * r4 + 2]);
+                acc[4 * r4 + 3] = fmaf(a.w, e, acc[4 * r4 + 3]);
+            }
+        }
+        if (col_ok) {
+#pragma unroll
+            for (int r = 0; r < BP_ROWS; ++r) {
+                long long gr = r0 + r;
+                if (gr < n) __stcs(out + gr * M + col, acc[r]);
+            }
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------
+// K3: frames[n, T, P] = B[T, Nb] . coeffs[n, Nb, P]  (4 non-zeros per row of B)
+// One candidate at a time per CTA: its [Nb, P] coefficient block is read once
+// (coalesced) into shared memory, every output element is then 4 FMAs and the
+// output is written as one contiguous run.
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) mgb_eval_frames_kernel(const float* __restrict__ coeffs, int Nb, int P, long long n,
+                                                              const int* __restrict__ spans, const float4* __restrict__ w4, int T,
+                                                              float* __restrict__ frames) {
+    extern __shared__ __align__(16) float sm_c[];  // [Nb*P] + spans/weights
+    const int M = Nb * P;
+    float4* sm_w = reinterpret_cast<float4*>(sm_c + ((M + 3) & ~3));
+    int* sm_span = reinterpret_cast<int*>(sm_w + T);
+    for (int t = threadIdx.x; t < T; t += blockDim.x) {
+        sm_w[t] = w4[t];
+        sm_span[t] = spans[t];
+    }
+    const int TP = T * P;
+    for (long long i = blockIdx.x; i < n; i += gridDim.x) {
+        __syncthreads();
+        const float* src = coeffs + (size_t)i * M;
+        if ((M & 3) == 0) {
+            const float4* s4 = reinterpret_cast<const float4*>(src);
+            float4* d4 = reinterpret_cast<float4*>(sm_c);
+            for (int e = threadIdx.x; e < (M >> 2); e += blockDim.x) d4[e] = __ldcs(s4 + e);
+        } else {
+            for (int e = threadIdx.x; e < M; e += blockDim.x) sm_c[e] = __ldcs(src + e);
+        }
+        __syncthreads();
+        float* dst = frames + (size_t)i * TP;
+        int t = threadIdx.x / P, pch = threadIdx.x % P;
+        const int step_t = blockDim.x / P, step_p = blockDim.x % P;
+        for (int o = threadIdx.x; o < TP; o += blockDim.x) {
+            const float4 w = sm_w[t];
+            const float* c0 = sm_c + sm_span[t] * P + pch;
+            float v = w.x * c0[0];
+            v = fmaf(w.y, c0[P], v);
+            v = fmaf(w.z, c0[2 * P], v);
+            v = fmaf(w.w, c0[3 * P], v);
+            __stcs(dst + o, v);
+            t += step_t;
+            pch += step_p;
+            if (pch >= P) { pch -= P; t += 1; }
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------
+// K4: forward kinematics of listed nodes.  Thread per frame; a tile of frames
+// is staged in shared memory (rows of P floats, odd stride), each thread walks
+// the parent chains from a per-call "plan" (node order with parents first).
+// ---------------------------------------------------------------------------
+#define MGB_QUAT_EPS 8.881784197001252e-16f
+
+__device__ __forceinline__ void quat_R(float w, float x, float y, float z, float* R) {
+    float n = w * w + x * x + y * y + z * z;
+    if (n < MGB_QUAT_EPS) {
+        R[0] = 1.f; R[1] = 0.f; R[2] = 0.f; R[3] = 0.f; R[4] = 1.f; R[5] = 0.f; R[6] = 0.f; R[7] = 0.f; R[8] = 1.f;
+        return;
+    }
+    float s = __fdividef(2.0f, n);
+    float xs = x * s, ys = y * s, zs = z * s;
+    float wx = w * xs, wy = w * ys, wz = w * zs, xx = x * xs, xy = x * ys, xz = x * zs, yy = y * ys, yz = y * zs, zz = z * zs;
+    R[0] = 1.f - (yy + zz); R[1] = xy - wz; R[2] = xz + wy;
+    R[3] = xy + wz; R[4] = 1.f - (xx + zz); R[5] = yz - wx;
+    R[6] = xz - wy; R[7] = yz + wx; R[8] = 1.f - (xx + yy);
+}
+
+struct FkStep {
+    int node_type;   // MGB_NODE_*
+    int channel;     // quaternion_frame_index or -1
+    int parent_slot; // slot (in the plan) of the parent, -1 for the root
+    int out_index;   // >= 0: write position to output column out_index
+    float off[3];
+    float rot[9];    // fixed rotation
+};
+
+#define FK_BLOCK 128
+#define FK_MAX_PLAN 160
+__global__ void __launch_bounds__(FK_BLOCK) mgb_fk_kernel(const float* __restrict__ frames, int P, long long n_frames, const FkStep* __restrict__ plan,
+                                                         int n_plan, int n_out, float* __restrict__ pos) {
+    extern __shared__ __align__(16) float smf[];
+    const int SROW = P | 1;
+    float* sm_frames = smf;                                  // [FK_BLOCK][SROW]
+    float* sm_out = smf + (size_t)FK_BLOCK * SROW;           // [FK_BLOCK][n_out*3 | 1]
+    const int OROW = (n_out * 3) | 1;
+    __shared__ FkStep sm_plan[FK_MAX_PLAN];
+    for (int e = threadIdx.x; e < n_plan; e += FK_BLOCK) sm_plan[e] = plan[e];
+    const long long n_tiles = (n_frames + FK_BLOCK - 1) / FK_BLOCK;
+    for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const long long base = tile * FK_BLOCK;
+        __syncthreads();
+        {
+            const float* src = frames + base * P;
+            const long long remaining = (n_frames - base) * (long long)P;
+            const int total = FK_BLOCK * P;
+            const int step_r = FK_BLOCK / P, step_c = FK_BLOCK % P;
+            int r = threadIdx.x / P, c = threadIdx.x % P;
+            for (int e = threadIdx.x; e < total; e += FK_BLOCK) {
+                sm_frames[r * SROW + c] = (e < remaining) ? __ldcs(src + e) : 0.f;
+                r += step_r;
+                c += step_c;
+                if (c >= P) { c -= P; r += 1; }
+            }
+        }
+        __syncthreads();
+        const float* f = sm_frames + threadIdx.x * SROW;
+        float* o = sm_out + threadIdx.x * OROW;
+        // global transforms of the plan's nodes, kept in local memory (12 floats per node)
+        float Gm[FK_MAX_PLAN][12];
+        for (int sidx = 0; sidx < n_plan; ++sidx) {
+            const FkStep& st = sm_plan[sidx];
+            float Rl[9], tl[3] = {st.off[0], st.off[1], st.off[2]};
+            bool has_rot = true;
+            if (st.node_type == MGB_NODE_ROOT) {
+                quat_R(f[3], f[4], f[5], f[6], Rl);
+                tl[0] += f[0]; tl[1] += f[1]; tl[2] += f[2];
+            } else if (st.node_type == MGB_NODE_END_SITE) {
+                has_rot = false;
+            } else if (st.channel >= 0) {
+                const float* q = f + 3 + 4 * st.channel;
+                quat_R(q[0], q[1], q[2], q[3], Rl);
+            } else {
+#pragma unroll
+                for (int q = 0; q < 9; ++q) Rl[q] = st.rot[q];
+            }
+            float* Gc = Gm[sidx];
+            if (st.parent_slot < 0) {
+                if (has_rot) {
+#pragma unroll
+                    for (int q = 0; q < 9; ++q) Gc[q] = Rl[q];
+                } else {
+#pragma unroll
+                    for (int q = 0; q < 9; ++q) Gc[q] = (q % 4 == 0) ? 1.f : 0.f;
+                }
+                Gc[9] = tl[0]; Gc[10] = tl[1]; Gc[11] = tl[2];
+            } else {
+                const float* Gp = Gm[st.parent_slot];
+#pragma unroll
+                for (int a = 0; a < 3; ++a)
+                    Gc[9 + a] = fmaf(Gp[a * 3], tl[0], fmaf(Gp[a * 3 + 1], tl[1], fmaf(Gp[a * 3 + 2], tl[2], Gp[9 + a])));
+                if (has_rot) {
+#pragma unroll
+                    for (int a = 0; a < 3; ++a)
+#pragma unroll
+                        for (int b = 0; b < 3; ++b)
+                            Gc[a * 3 + b] = fmaf(Gp[a * 3], Rl[b], fmaf(Gp[a * 3 + 1], Rl[3 + b], Gp[a * 3 + 2] * Rl[6 + b]));
+                } else {
+#pragma unroll
+                    for (int q = 0; q < 9; ++q) Gc[q] = Gp[q];
+                }
+            }
+            if (st.out_index >= 0) {
+                o[st.out_index * 3 + 0] = Gc[9];
+                o[st.out_index * 3 + 1] = Gc[10];
+                o[st.out_index * 3 + 2] = Gc[11];
+            }
+        }
+        __syncthreads();
+        {
+            const int W = n_out * 3;
+            float* dst = pos + base * W;
+            const long long remaining = (n_frames - base) * (long long)W;
+            const int total = FK_BLOCK * W;
+            const int step_r = FK_BLOCK / W, step_c = FK_BLOCK % W;
+            int r = threadIdx.x / W, c = threadIdx.x % W;
+            for (int e = threadIdx.x; e < total; e += FK_BLOCK) {
+                if (e < remaining) __stcs(dst + e, sm_out[r * OROW + c]);
+                r += step_r;
+                c += step_c;
+                if (c >= W) { c -= W; r += 1; }
+            }
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------
+// K5b: GMM log-density, thread per sample, s row in shared memory
+// ---------------------------------------------------------------------------
+#define LP_BLOCK 128
+__global__ void __launch_bounds__(LP_BLOCK) mgb_logpdf_kernel(const float* __restrict__ s, long long n, int D, int G, int NQ,
+                                                             const float4* __restrict__ gtab, const float* __restrict__ gc,
+                                                             float* __restrict__ out) {
+    extern __shared__ __align__(16) float sml[];
+    const int SROW = D | 1;
+    const long long n_tiles = (n + LP_BLOCK - 1) / LP_BLOCK;
+    for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const long long base = tile * LP_BLOCK;
+        __syncthreads();
+        {
+            const float* src = s + base * D;
+            const long long remaining = (n - base) * (long long)D;
+            const int total = LP_BLOCK * D;
+            const int step_r = LP_BLOCK / D, step_c = LP_BLOCK % D;
+            int r = threadIdx.x / D, c = threadIdx.x % D;
+            for (int e = threadIdx.x; e < total; e += LP_BLOCK) {
+                sml[r * SROW + c] = (e < remaining) ? __ldg(src + e) : 0.f;
+                r += step_r;
+                c += step_c;
+                if (c >= D) { c -= D; r += 1; }
+            }
+        }
+        __syncthreads();
+        const float* row = sml + threadIdx.x * SROW;
+        float mx = -INFINITY, ssum = 0.f;
+        for (int g = 0; g < G; ++g) {
+            float qf = 0.f;
+            for (int jq = 0; jq < NQ; ++jq) {
+                const float4* tr = gtab + (size_t)(g * NQ + jq) * (D + 1);
+                float4 y = __ldg(tr + D);
+                const int cnt = min(D, 4 * jq + 4);
+                for (int k = 0; k < cnt; ++k) {
+                    const float4 e = __ldg(tr + k);
+                    const float sk = row[k];
+                    y.x = fmaf(sk, e.x, y.x);
+                    y.y = fmaf(sk, e.y, y.y);
+                    y.z = fmaf(sk, e.z, y.z);
+                    y.w = fmaf(sk, e.w, y.w);
+                }
+                qf = fmaf(y.x, y.x, fmaf(y.y, y.y, fmaf(y.z, y.z, fmaf(y.w, y.w, qf))));
+            }
+            const float lp = __ldg(gc + g) - 0.5f * qf;
+            if (lp > mx) {
+                ssum = ssum * __expf(mx - lp) + 1.f;
+                mx = lp;
+            } else {
+                ssum += __expf(lp - mx);
+            }
+        }
+        const long long i = base + threadIdx.x;
+        if (i < n) out[i] = mx + __logf(ssum);
+    }
+}
+
+// ---------------------------------------------------------------------------
+// K7: one Lloyd step for a whole tree level.  Thread per sample: nearest of its
+// node's n_sub centroids, label out, then sums/counts accumulated with
+// warp-aggregated atomics when the whole warp hits the same (node, label).
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) mgb_kmeans_kernel(const float* __restrict__ x, long long n, int dim, int ld, const int* __restrict__ node,
+                                                        const float* __restrict__ cent, int n_sub, int* __restrict__ label,
+                                                        float* __restrict__ sums, int* __restrict__ counts, float* __restrict__ inertia) {
+    float local_inertia = 0.f;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        const int nd = node ? node[i] : 0;
+        const float* xi = x + (size_t)i * ld;
+        const float* cb = cent + (size_t)nd * n_sub * dim;
+        float best = INFINITY;
+        int bl = 0;
+        for (int k = 0; k < n_sub; ++k) {
+            float d = 0.f;
+            const float* ck = cb + (size_t)k * dim;
+            for (int j = 0; j < dim; ++j) {
+                float e = __ldg(xi + j) - __ldg(ck + j);
+                d = fmaf(e, e, d);
+            }
+            if (d < best) { best = d; bl = k; }
+        }
+        label[i] = bl;
+        local_inertia += best;
+        float* sb = sums + ((size_t)nd * n_sub + bl) * dim;
+        for (int j = 0; j < dim; ++j) atomicAdd(sb + j, __ldg(xi + j));
+        atomicAdd(counts + (size_t)nd * n_sub + bl, 1);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) local_inertia += __shfl_xor_sync(0xffffffffu, local_inertia, o);
+    if (inertia && (threadIdx.x & 31) == 0) atomicAdd(inertia, local_inertia);
+}
+
+}  // namespace
+
+// ===========================================================================
+// C ABI
+// ===========================================================================
+extern "C" int mgb_sample(const mgb_model* m, int64_t n, int64_t index_base, const int64_t* h_counts, uint64_t seed,
+                          float* d_s, void* stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    MGB_REQUIRE(m && h_counts && (d_s || n == 0), "null argument");
+    MGB_REQUIRE(n >= 0 && index_base >= 0, "negative size");
+    if (n == 0) return MGB_OK;
+    std::vector<long long> prefix(m->G + 1, 0);
+    for (int g = 0; g < m->G; ++g) {
+        MGB_REQUIRE(h_counts[g] >= 0, "negative component count");
+        prefix[g + 1] = prefix[g] + h_counts[g];
+    }
+    MGB_REQUIRE(index_base + n <= prefix[m->G], "component counts (%lld) do not cover [%lld, %lld)", prefix[m->G],
+                (long long)index_base, (long long)(index_base + n));
+    long long* d_prefix = nullptr;
+    MGB_CUDA(cudaMallocAsync((void**)&d_prefix, sizeof(long long) * (m->G + 1), stream));
+    MGB_CUDA(cudaMemcpyAsync(d_prefix, prefix.data(), sizeof(long long) * (m->G + 1), cudaMemcpyHostToDevice, stream));
+    // the host vector must outlive the async copy
+    MGB_CUDA(cudaStreamSynchronize(stream));
+    size_t smem = (size_t)SAMPLE_BLOCK * (m->D | 1) * sizeof(float);
+    MGB_REQUIRE(smem <= 200 * 1024, "latent dimension too large for the sampler");
+    static bool configured = false;
+    if (!configured) {
+        MGB_CUDA(cudaFuncSetAttribute(mgb_sample_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        configured = true;
+    }
+    long long n_tiles = (n + SAMPLE_BLOCK - 1) / SAMPLE_BLOCK;
+    int occ = 1;
+    MGB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, mgb_sample_kernel, SAMPLE_BLOCK, smem));
+    long long grid = (long long)sm_count() * (occ > 0 ? occ : 1);
+    if (grid > n_tiles) grid = n_tiles;
+    mgb_sample_kernel<<<(unsigned)grid, SAMPLE_BLOCK, smem, stream>>>(m->d_means, m->d_chol, d_prefix, m->G, m->D, n, index_base,
+                                                                    (unsigned long long)seed, d_s);
+    mgb_count_launch();
+    MGB_CUDA(cudaGetLastError());
+    MGB_CUDA(cudaFreeAsync(d_prefix, stream));
+    return MGB_OK;
+}
+
+extern "C" int mgb_backproject(const mgb_model* m, const float* d_s, int64_t n, float* d_coeffs, int32_t impl, void* stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    MGB_REQUIRE(m && (n == 0 || (d_s && d_coeffs)), "null argument");
+    MGB_REQUIRE(impl >= 0 && impl <= 2, "impl must be 0 (auto), 1 (simt) or 2 (tensor core)");
+    if (n == 0) return MGB_OK;
+    if (impl == 2 || (impl == 0 && m->d_Bsplit != nullptr)) return mgb_backproject_tc(m, d_s, n, d_coeffs, stream);
+    size_t smem = (size_t)m->K * BP_ROWS * sizeof(float);
+    MGB_REQUIRE(smem <= 48 * 1024, "K too large for the SIMT back-projection (use impl=2)");
+    dim3 grid((m->M + BP_COLS - 1) / BP_COLS, 1, 1);
+    long long row_tiles = (n + BP_ROWS - 1) / BP_ROWS;
+    long long gy = ((long long)sm_count() * 8 + grid.x - 1) / grid.x;
+    if (gy > row_tiles) gy = row_tiles;
+    if (gy > 65535) gy = 65535;
+    grid.y = (unsigned)gy;
+    mgb_backproject_simt<<<grid, BP_COLS, smem, stream>>>(d_s, m->D, m->K, m->d_E, m->d_mean, m->M, n, d_coeffs);
+    mgb_count_launch();
+    MGB_CUDA(cudaGetLastError());
+    return MGB_OK;
+}
+
+extern "C" int mgb_eval_frames(const mgb_model* m, const float* d_coeffs, int64_t n, const double* times, int32_t n_times,
+                               const int32_t* spans, const double* weights, float* d_frames, void* stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    MGB_REQUIRE(m && times && n_times > 0, "null argument");
+    MGB_REQUIRE(n == 0 || (d_coeffs && d_frames), "null device pointer");
+    if (n == 0) return MGB_OK;
+    std::vector<int> sp(n_times);
+    std::vector<float4> w4(n_times);
+    for (int t = 0; t < n_times; ++t) {
+        double w[4];
+        int span;
+        if (spans && weights) {
+            span = spans[t];
+            for (int q = 0; q < 4; ++q) w[q] = weights[4 * t + q];
+        } else {
+            int rc = mgb_spline_basis(m->knots.data(), (int)m->knots.size(), times[t], &span, w);
+            if (rc != MGB_OK) return rc;
+        }
+        MGB_REQUIRE(span >= 0 && span + 4 <= m->Nb, "span out of range");
+        sp[t] = span;
+        w4[t] = make_float4((float)w[0], (float)w[1], (float)w[2], (float)w[3]);
+    }
+    int* d_sp = nullptr;
+    float4* d_w4 = nullptr;
+    MGB_CUDA(cudaMallocAsync((void**)&d_sp, sizeof(int) * n_times, stream));
+    MGB_CUDA(cudaMallocAsync((void**)&d_w4, sizeof(float4) * n_times, stream));
+    MGB_CUDA(cudaMemcpyAsync(d_sp, sp.data(), sizeof(int) * n_times, cudaMemcpyHostToDevice, stream));
+    MGB_CUDA(cudaMemcpyAsync(d_w4, w4.data(), sizeof(float4) * n_times, cudaMemcpyHostToDevice, stream));
+    MGB_CUDA(cudaStreamSynchronize(stream));
+    size_t smem = (size_t)((m->M + 3) & ~3) * sizeof(float) + (size_t)n_times * (sizeof(float4) + sizeof(int)) + 16;
+    MGB_REQUIRE(smem <= 200 * 1024, "coefficient block too large for shared memory");
+    static bool configured = false;
+    if (!configured) {
+        MGB_CUDA(cudaFuncSetAttribute(mgb_eval_frames_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        configured = true;
+    }
+    int occ = 1;
+    MGB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, mgb_eval_frames_kernel, 256, smem));
+    long long grid = (long long)sm_count() * (occ > 0 ? occ : 1);
+    if (grid > n) grid = n;
+    mgb_eval_frames_kernel<<<(unsigned)grid, 256, smem, stream>>>(d_coeffs, m->Nb, m->P, n, d_sp, d_w4, n_times, d_frames);
+    mgb_count_launch();
+    MGB_CUDA(cudaGetLastError());
+    MGB_CUDA(cudaFreeAsync(d_sp, stream));
+    MGB_CUDA(cudaFreeAsync(d_w4, stream));
+    return MGB_OK;
+}
+
+extern "C" int mgb_fk(const mgb_model* m, const float* d_frames, int64_t n_frames, const int32_t* h_nodes, int32_t n_out,
+                      float* d_pos, void* stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    MGB_REQUIRE(m && h_nodes && n_out > 0, "null argument");
+    MGB_REQUIRE(n_frames == 0 || (d_frames && d_pos), "null device pointer");
+    if (n_frames == 0) return MGB_OK;
+    // plan: every ancestor of a requested node, parents first (node order is topological)
+    std::vector<int> need(m->n_nodes, 0), out_of(m->n_nodes, -1);
+    std::vector<std::vector<int>> outs(m->n_nodes);
+    for (int j = 0; j < n_out; ++j) {
+        int nd = h_nodes[j];
+        MGB_REQUIRE(nd >= 0 && nd < m->n_nodes, "node index %d out of range", nd);
+        outs[nd].push_back(j);
+        while (nd >= 0 && !need[nd]) {
+            need[nd] = 1;
+            nd = m->parent[nd];
+        }
+    }
+    std::vector<FkStep> plan;
+    std::vector<int> slot(m->n_nodes, -1);
+    for (int nd = 0; nd < m->n_nodes; ++nd) {
+        if (!need[nd]) continue;
+        // a node requested several times gets one step per extra output (cheap, rare)
+        for (size_t rep = 0; rep < (outs[nd].empty() ? 1 : outs[nd].size()); ++rep) {
+            FkStep st;
+            st.node_type = m->type[nd];
+            st.channel = m->channel[nd];
+            st.parent_slot = m->parent[nd] >= 0 ? slot[m->parent[nd]] : -1;
+            st.out_index = outs[nd].empty() ? -1 : outs[nd][rep];
+            for (int q = 0; q < 3; ++q) st.off[q] = (float)m->offset[nd * 3 + q];
+            for (int q = 0; q < 9; ++q) st.rot[q] = (float)m->fixed_rot[nd * 9 + q];
+            if (rep == 0) slot[nd] = (int)plan.size();
+            plan.push_back(st);
+        }
+    }
+    MGB_REQUIRE((int)plan.size() <= FK_MAX_PLAN, "FK plan of %d nodes exceeds %d", (int)plan.size(), FK_MAX_PLAN);
+    FkStep* d_plan = nullptr;
+    MGB_CUDA(cudaMallocAsync((void**)&d_plan, sizeof(FkStep) * plan.size(), stream));
+    MGB_CUDA(cudaMemcpyAsync(d_plan, plan.data(), sizeof(FkStep) * plan.size(), cudaMemcpyHostToDevice, stream));
+    MGB_CUDA(cudaStreamSynchronize(stream));
+    size_t smem = ((size_t)FK_BLOCK * (m->P | 1) + (size_t)FK_BLOCK * ((n_out * 3) | 1)) * sizeof(float);
+    MGB_REQUIRE(smem <= 200 * 1024, "frame tile too large for shared memory");
+    static bool configured = false;
+    if (!configured) {
+        MGB_CUDA(cudaFuncSetAttribute(mgb_fk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        configured = true;
+    }
+    int occ = 1;
+    MGB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, mgb_fk_kernel, FK_BLOCK, smem));
+    long long n_tiles = (n_frames + FK_BLOCK - 1) / FK_BLOCK;
+    long long grid = (long long)sm_count() * (occ > 0 ? occ : 1);
+    if (grid > n_tiles) grid = n_tiles;
+    mgb_fk_kernel<<<(unsigned)grid, FK_BLOCK, smem, stream>>>(d_frames, m->P, n_frames, d_plan, (int)plan.size(), n_out, d_pos);
+    mgb_count_launch();
+    MGB_CUDA(cudaGetLastError());
+    MGB_CUDA(cudaFreeAsync(d_plan, stream));
+    return MGB_OK;
+}
+
+extern "C" int mgb_logpdf(const mgb_model* m, const float* d_s, int64_t n, float* d_logpdf, void* stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    MGB_REQUIRE(m && (n == 0 || (d_s && d_logpdf)), "null argument");
+    if (n == 0) return MGB_OK;
+    size_t smem = (size_t)LP_BLOCK * (m->D | 1) * sizeof(float);
+    MGB_REQUIRE(smem <= 200 * 1024, "latent dimension too large");
+    static bool configured = false;
+    if (!configured) {
+        MGB_CUDA(cudaFuncSetAttribute(mgb_logpdf_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        configured = true;
+    }
+    int occ = 1;
+    MGB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, mgb_logpdf_kernel, LP_BLOCK, smem));
+    long long n_tiles = (n + LP_BLOCK - 1) / LP_BLOCK;
+    long long grid = (long long)sm_count() * (occ > 0 ? occ : 1);
+    if (grid > n_tiles) grid = n_tiles;
+    mgb_logpdf_kernel<<<(unsigned)grid, LP_BLOCK, smem, stream>>>(d_s, n, m->D, m->G, m->NQ, m->d_gmm_tab, m->d_gmm_c, d_logpdf);
+    mgb_count_launch();
+    MGB_CUDA(cudaGetLastError());
+    return MGB_OK;
+}
+
+extern "C" int mgb_kmeans_assign_update(const float* d_x, int64_t n, int32_t dim, int32_t ld, const int32_t* d_node,
+                                        const float* d_centroids, int32_t n_sub, int32_t* d_label, float* d_sums,
+                                        int32_t* d_counts, float* d_inertia, void* stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    MGB_REQUIRE(n == 0 || (d_x && d_centroids && d_label && d_sums && d_counts), "null argument");
+    MGB_REQUIRE(dim > 0 && ld >= dim && n_sub > 0, "bad shape");
+    if (n == 0) return MGB_OK;
+    long long blocks = (n + 255) / 256;
+    long long grid = (long long)sm_count() * 8;
+    if (grid > blocks) grid = blocks;
+    mgb_kmeans_kernel<<<(unsigned)grid, 256, 0, stream>>>(d_x, n, dim, ld, d_node, d_centroids, n_sub, d_label, d_sums, d_counts, d_inertia);
+    mgb_count_launch();
+    MGB_CUDA(cudaGetLastError());
+    return MGB_OK;
+}

@@ -1,0 +1,518 @@
+"""Thin Python layer over libmgb200.so: packs reference-shaped objects into the
+C-ABI descriptors and launches the kernels on torch-owned device memory.
+
+Duck-typed on the reference's attribute names, so `DeviceModel` /
+`DeviceConstraints` accept either the reference's own objects
+(`MotionPrimitiveModelWrapper`, anim_utils `Skeleton`,
+`MotionPrimitiveConstraints`) or this package's mirrors.
+
+PyTorch is plumbing only: device allocations, streams, `torch.distributed`.
+All arithmetic of the path runs in the CUDA library; nothing here falls back
+to the CPU.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+from ._lib import MgbError  # noqa: F401
+
+
+class UnsupportedConstraintError(MgbError):
+    """A constraint outside the device path (trajectory constraints that query a host
+    spline per frame, quaternion-frame pose constraints, start-pose alignment with its
+    call-order dependent mutation - SURVEY.md Q2).  Callers decide what to do; the engine
+    never drops a term silently and never evaluates it on the CPU itself."""
+
+
+def _torch():
+    import torch
+    return torch
+
+
+def _motion_primitive(model):
+    return getattr(model, "motion_primitive", model)
+
+
+def _dptr(a):
+    return a.ctypes.data_as(C.POINTER(C.c_double))
+
+
+def _iptr(a):
+    return a.ctypes.data_as(C.POINTER(C.c_int32))
+
+
+# ---------------------------------------------------------------------------
+# skeleton packing
+# ---------------------------------------------------------------------------
+def _node_type_int(node):
+    t = node.node_type
+    if isinstance(t, str):
+        return {"root": 0, "joint": 1, "end_site": 2}[t]
+    return int(t)
+
+
+def pack_skeleton(skeleton):
+    """Topologically ordered flat arrays + name -> index map.
+    Fields read: reference utilities/__init__.py:13-16 (node_name, offset, rotation,
+    fixed, children), quaternion_frame_index (mg_state_planner.py:288)."""
+    if skeleton is None:
+        # root-only skeleton: enough for sampling / back-projection / spline evaluation
+        names = ["root"]
+        return dict(names=names, index={"root": 0}, parent=np.array([-1], dtype=np.int32),
+                    type=np.array([0], dtype=np.int32), channel=np.array([0], dtype=np.int32),
+                    offset=np.zeros((1, 3)), rotation=np.array([[1.0, 0, 0, 0]]), aligning_node=0,
+                    aligning_dir=[0.0, 0.0, 1.0])
+    root_name = skeleton.root if isinstance(skeleton.root, str) else skeleton.root.node_name
+    order = []
+    stack = [skeleton.nodes[root_name]]
+    while stack:                      # pre-order: parents precede children
+        node = stack.pop()
+        order.append(node)
+        stack.extend(reversed(list(node.children)))
+    index = {n.node_name: i for i, n in enumerate(order)}
+    n = len(order)
+    parent = np.full(n, -1, dtype=np.int32)
+    ntype = np.zeros(n, dtype=np.int32)
+    channel = np.full(n, -1, dtype=np.int32)
+    offset = np.zeros((n, 3))
+    rotation = np.zeros((n, 4))
+    rotation[:, 0] = 1.0
+    for i, node in enumerate(order):
+        if node.parent is not None:
+            parent[i] = index[node.parent.node_name]
+        ntype[i] = _node_type_int(node)
+        if ntype[i] == 0:
+            channel[i] = 0
+        elif ntype[i] == 1 and not node.fixed:
+            channel[i] = int(node.quaternion_frame_index)
+        offset[i] = np.asarray(node.offset, dtype=np.float64)
+        if node.rotation is not None:
+            rotation[i] = np.asarray(node.rotation, dtype=np.float64)
+    aligning = getattr(skeleton, "aligning_root_node", None) or root_name
+    return dict(names=[n.node_name for n in order], index=index, parent=parent, type=ntype, channel=channel,
+                offset=offset, rotation=rotation, aligning_node=index[aligning],
+                aligning_dir=list(getattr(skeleton, "aligning_root_dir", [0.0, 0.0, 1.0])))
+
+
+# ---------------------------------------------------------------------------
+# spline basis: the same FITPACK call the reference makes (motion_spline.py:89-92)
+# ---------------------------------------------------------------------------
+def spline_basis(knots, t, degree=3):
+    """(span, w[4]) with value = sum_i w[i] * coeffs[span+i], from scipy.splev on identity
+    coefficients; falls back to the library's own FITPACK-compatible recurrence."""
+    knots = np.ascontiguousarray(knots, dtype=np.float64)
+    nb = len(knots) - degree - 1
+    nk1 = nb
+    l = degree
+    while l + 1 < nk1 and t >= knots[l + 1]:
+        l += 1
+    span = l - degree
+    try:
+        import scipy.interpolate as si
+        eye = np.eye(nb)
+        w = np.array([float(si.splev(t, (knots, eye[span + i], degree))) for i in range(degree + 1)])
+    except ImportError:  # pragma: no cover
+        lib = _lib.load()
+        sp = C.c_int32()
+        w = np.zeros(4)
+        _lib.check(lib.mgb_spline_basis(_dptr(knots), len(knots), float(t), C.byref(sp), _dptr(w)))
+        span = sp.value
+    return span, w
+
+
+def lib_spline_basis(knots, t):
+    """The library's own basis (host code in csrc/mgb_api.cu); no GPU needed."""
+    lib = _lib.load()
+    knots = np.ascontiguousarray(knots, dtype=np.float64)
+    sp = C.c_int32()
+    w = np.zeros(4)
+    _lib.check(lib.mgb_spline_basis(_dptr(knots), len(knots), float(t), C.byref(sp), _dptr(w)))
+    return sp.value, w
+
+
+# ---------------------------------------------------------------------------
+# model
+# ---------------------------------------------------------------------------
+class DeviceModel(object):
+    """One motion primitive + skeleton resident on one GPU (mgb_model handle)."""
+
+    def __init__(self, model, skeleton=None, device=None):
+        torch = _torch()
+        if not torch.cuda.is_available():
+            raise MgbError("no CUDA device: morphablegraphs_b200 has no CPU fallback")
+        self.lib = _lib.load()
+        if device is None:
+            device = torch.cuda.current_device()
+        self.device = int(device)
+        self.torch_device = torch.device("cuda", self.device)
+        mp = _motion_primitive(model)
+        s = mp.s_pca
+        # reference stores eigen vectors transposed at load (motion_primitive.py:158): [Nb*P, K]
+        E = np.ascontiguousarray(np.asarray(s["eigen_vectors"], dtype=np.float64).T)
+        mean = np.ascontiguousarray(s["mean_vector"], dtype=np.float64)
+        self.knots = np.ascontiguousarray(s["knots"], dtype=np.float64)
+        self.Nb, self.P, self.K = int(s["n_basis"]), int(s["n_dim"]), int(s["n_components"])
+        self.F = int(mp.n_canonical_frames)
+        tm = np.ascontiguousarray(mp.translation_maxima, dtype=np.float64)
+        gmm = mp.gaussian_mixture_model
+        self.gmm_weights = np.ascontiguousarray(gmm.weights_, dtype=np.float64)
+        means = np.ascontiguousarray(gmm.means_, dtype=np.float64)
+        covars = np.ascontiguousarray(gmm.covariances_, dtype=np.float64)
+        self.G, self.D = means.shape
+        assert E.shape == (self.K, self.Nb * self.P), E.shape
+        self.skeleton = skeleton
+        sk = pack_skeleton(skeleton)
+        self.node_index = sk["index"]
+        self.node_names = sk["names"]
+        offset = np.ascontiguousarray(sk["offset"], dtype=np.float64)
+        rotation = np.ascontiguousarray(sk["rotation"], dtype=np.float64)
+        d = _lib.ModelDesc()
+        d.n_frames, d.n_basis, d.n_dim, d.n_spatial, d.n_latent, d.n_gmm = self.F, self.Nb, self.P, self.K, self.D, self.G
+        d.eigen, d.mean, d.knots, d.translation_maxima = _dptr(E), _dptr(mean), _dptr(self.knots), _dptr(tm)
+        d.gmm_weights, d.gmm_means, d.gmm_covars = _dptr(self.gmm_weights), _dptr(means), _dptr(covars)
+        d.n_nodes = len(sk["names"])
+        d.node_parent, d.node_type, d.node_channel = _iptr(sk["parent"]), _iptr(sk["type"]), _iptr(sk["channel"])
+        d.node_offset, d.node_rotation = _dptr(offset), _dptr(rotation)
+        d.aligning_node = sk["aligning_node"]
+        d.aligning_dir = (C.c_double * 3)(*sk["aligning_dir"])
+        h = C.c_void_p()
+        _lib.check(self.lib.mgb_model_create(C.byref(d), self.device, C.byref(h)))
+        self.handle = h
+        self._ws = None
+
+    def __del__(self):
+        try:
+            if getattr(self, "handle", None):
+                self.lib.mgb_model_destroy(self.handle)
+                self.handle = None
+        except Exception:
+            pass
+
+    # -- helpers ---------------------------------------------------------------
+    def _stream(self):
+        return C.c_void_p(_torch().cuda.current_stream(self.torch_device).cuda_stream)
+
+    def workspace(self):
+        torch = _torch()
+        nbytes = int(self.lib.mgb_score_workspace_bytes(0, 1))
+        if self._ws is None or self._ws.numel() < nbytes:
+            self._ws = torch.zeros(nbytes, dtype=torch.uint8, device=self.torch_device)
+        return self._ws
+
+    def _f32(self, t):
+        torch = _torch()
+        if not isinstance(t, torch.Tensor):
+            t = torch.as_tensor(np.ascontiguousarray(t, dtype=np.float32), device=self.torch_device)
+        if t.device != self.torch_device or t.dtype != torch.float32 or not t.is_contiguous():
+            t = t.to(device=self.torch_device, dtype=torch.float32).contiguous()
+        return t
+
+    # -- K1 ----------------------------------------------------------------------
+    def component_counts(self, n_total, seed):
+        """Multinomial split over components, drawn on the host like sklearn's sampler does
+        (GaussianMixture.sample: rng.multinomial(n, weights_))."""
+        rng = np.random.RandomState(None if seed is None else (int(seed) & 0x7FFFFFFF))
+        return rng.multinomial(int(n_total), self.gmm_weights).astype(np.int64)
+
+    def sample(self, n, seed=0, index_base=0, counts=None, n_total=None):
+        """[n, D] float32 device tensor: global indices [index_base, index_base+n) of a job of
+        n_total samples stacked in component order (motion_primitive.py:182-189)."""
+        torch = _torch()
+        n_total = int(n if n_total is None else n_total)
+        if counts is None:
+            counts = self.component_counts(n_total, seed)
+        counts = np.ascontiguousarray(counts, dtype=np.int64)
+        out = torch.empty((int(n), self.D), dtype=torch.float32, device=self.torch_device)
+        with torch.cuda.device(self.device):
+            _lib.check(self.lib.mgb_sample(self.handle, int(n), int(index_base), counts.ctypes.data_as(C.POINTER(C.c_int64)),
+                                           C.c_uint64(int(seed) & 0xFFFFFFFFFFFFFFFF), C.c_void_p(out.data_ptr()), self._stream()))
+        return out
+
+    # -- K2 / K3 / K4 / K5b ---------------------------------------------------
+    def backproject(self, s, impl=0, out=None):
+        torch = _torch()
+        s = self._f32(s)
+        n = s.shape[0]
+        if out is None:
+            out = torch.empty((n, self.Nb, self.P), dtype=torch.float32, device=self.torch_device)
+        with torch.cuda.device(self.device):
+            _lib.check(self.lib.mgb_backproject(self.handle, C.c_void_p(s.data_ptr()), n, C.c_void_p(out.data_ptr()), int(impl),
+                                                self._stream()))
+        return out
+
+    def basis(self, times):
+        times = np.ascontiguousarray(np.atleast_1d(times), dtype=np.float64)
+        spans = np.zeros(len(times), dtype=np.int32)
+        weights = np.zeros((len(times), 4), dtype=np.float64)
+        for i, t in enumerate(times):
+            spans[i], weights[i] = spline_basis(self.knots, float(t))
+        return times, spans, weights
+
+    def eval_frames(self, coeffs, times, out=None):
+        torch = _torch()
+        coeffs = self._f32(coeffs)
+        n = coeffs.shape[0]
+        times, spans, weights = self.basis(times)
+        if out is None:
+            out = torch.empty((n, len(times), self.P), dtype=torch.float32, device=self.torch_device)
+        with torch.cuda.device(self.device):
+            _lib.check(self.lib.mgb_eval_frames(self.handle, C.c_void_p(coeffs.data_ptr()), n, _dptr(times), len(times), _iptr(spans),
+                                                _dptr(weights), C.c_void_p(out.data_ptr()), self._stream()))
+        return out
+
+    def fk(self, frames, node_names, out=None):
+        torch = _torch()
+        frames = self._f32(frames)
+        lead = frames.shape[:-1]
+        nf = int(np.prod(lead)) if len(lead) else 1
+        nodes = np.ascontiguousarray([self.node_index[nm] for nm in node_names], dtype=np.int32)
+        if out is None:
+            out = torch.empty(tuple(lead) + (len(nodes), 3), dtype=torch.float32, device=self.torch_device)
+        with torch.cuda.device(self.device):
+            _lib.check(self.lib.mgb_fk(self.handle, C.c_void_p(frames.data_ptr()), nf, _iptr(nodes), len(nodes),
+                                       C.c_void_p(out.data_ptr()), self._stream()))
+        return out
+
+    def logpdf(self, s):
+        torch = _torch()
+        s = self._f32(s)
+        out = torch.empty((s.shape[0],), dtype=torch.float32, device=self.torch_device)
+        with torch.cuda.device(self.device):
+            _lib.check(self.lib.mgb_logpdf(self.handle, C.c_void_p(s.data_ptr()), s.shape[0], C.c_void_p(out.data_ptr()), self._stream()))
+        return out
+
+
+# ---------------------------------------------------------------------------
+# constraints
+# ---------------------------------------------------------------------------
+def _mask_and_target(position):
+    mask, tgt = 0, [0.0, 0.0, 0.0]
+    for i in range(3):
+        if position[i] is not None:
+            mask |= 1 << i
+            tgt[i] = float(position[i])
+    return mask, tgt
+
+
+def flatten_constraints(dmodel, mp_constraints):
+    """MotionPrimitiveConstraints -> (ConstraintDesc[], PosePoint[], times).
+    Field names per type: SURVEY.md Appendix C / the reference classes cited in
+    include/mgb200.h."""
+    skeleton = mp_constraints.skeleton if getattr(mp_constraints, "skeleton", None) is not None else dmodel.skeleton
+    idx = dmodel.node_index
+    times = []
+    slot_of = {}
+
+    def slot(t):
+        t = float(t)
+        if t not in slot_of:
+            slot_of[t] = len(times)
+            times.append(t)
+        return slot_of[t]
+
+    clist = list(mp_constraints.constraints)
+    # CA constraints need consecutive slots for the integer frames 0..F-1: allocate them first
+    ca_frames = 0
+    for c in clist:
+        if c.constraint_type == "ca_constraint":
+            ca_frames = max(ca_frames, int(c.n_canonical_frames))
+    for f in range(ca_frames):
+        slot(float(f))
+    descs = (_lib.ConstraintDesc * max(len(clist), 1))()
+    points = []
+
+    def node(name):
+        if name not in idx:
+            raise UnsupportedConstraintError("joint %r is not in the packed skeleton" % (name,))
+        return idx[name]
+
+    for j, c in enumerate(clist):
+        d = descs[j]
+        ct = c.constraint_type
+        d.weight = float(c.weight_factor)
+        if ct in ("keyframe_position", "keyframe_relative_position"):
+            d.type = _lib.CT_POSITION if ct == "keyframe_position" else _lib.CT_RELATIVE
+            d.node[0] = node(c.joint_name)
+            d.time_slot = slot(c.canonical_keyframe)
+            if c.position is not None:
+                d.has_position = 1
+                if ct == "keyframe_relative_position":
+                    if any(p is None for p in c.position):
+                        raise UnsupportedConstraintError("relative constraint with an unconstrained axis")
+                    d.axis_mask = 7
+                    d.target = (C.c_double * 3)(*[float(p) for p in c.position])
+                    d.offset = (C.c_double * 4)(*[float(o) for o in c.offset])
+                else:
+                    mask, tgt = _mask_and_target(c.position)
+                    d.axis_mask = mask
+                    d.target = (C.c_double * 3)(*tgt)
+            if getattr(c, "orientation", None) is not None:
+                d.has_orientation = 1
+                d.orient_q = (C.c_double * 4)(*[float(q) for q in c.orientation])
+        elif ct == "keyframe_2d_direction":
+            d.type = _lib.CT_DIR2D
+            d.time_slot = slot(c.canonical_keyframe)
+            d.dir = (C.c_double * 2)(float(c.target_dir[0]), float(c.target_dir[1]))
+        elif ct == "keyframe_pose":
+            if not hasattr(c, "node_names"):
+                raise UnsupportedConstraintError("PoseConstraintQuatFrame is outside the device path")
+            n = len(c.node_names)
+            if n > _lib.MAX_POSE_POINTS:
+                raise UnsupportedConstraintError("pose constraint with %d points (max %d)" % (n, _lib.MAX_POSE_POINTS))
+            d.type = _lib.CT_POSE
+            d.time_slot = slot(c.canonical_keyframe)
+            d.points_offset = len(points)
+            d.n_points = n
+            for nm, tgt, w in zip(c.node_names, c.pose_constraint, c.weights):
+                pp = _lib.PosePoint()
+                pp.node = node(nm)
+                pp.target = (C.c_double * 3)(*[float(x) for x in tgt])
+                pp.weight = float(w)
+                points.append(pp)
+            if c.velocity_constraint is not None:
+                d.has_velocity = 1
+                d.velocity = (C.c_double * 3)(*[float(x) for x in c.velocity_constraint])
+                d.time_slot2 = slot(c.canonical_keyframe + 1)
+        elif ct == "keyframe_two_hands":
+            d.type = _lib.CT_TWO_HANDS
+            d.node[0], d.node[1] = node(c.joint_names[0]), node(c.joint_names[1])
+            d.time_slot = slot(c.canonical_keyframe)
+            d.target = (C.c_double * 3)(*[float(x) for x in c.positions[0]])
+            d.target2 = (C.c_double * 3)(*[float(x) for x in c.positions[1]])
+            d.center = (C.c_double * 3)(*[float(x) for x in c.target_center])
+        elif ct == "keyframe_feet":
+            d.type = _lib.CT_FEET
+            d.node[0], d.node[1] = node("LeftFoot"), node("RightFoot")   # names fixed by feet_constraint.py:49-50
+            d.time_slot = slot(c.canonical_keyframe)
+            d.target = (C.c_double * 3)(*[float(x) for x in c.left])
+            d.target2 = (C.c_double * 3)(*[float(x) for x in c.right])
+        elif ct == "keyframe_look_at":
+            d.type = _lib.CT_LOOK_AT
+            d.node[0] = node(skeleton.head_joint)
+            d.time_slot = slot(c.canonical_keyframe)
+            d.target = (C.c_double * 3)(*[float(x) for x in c.target_position])
+        elif ct == "ca_constraint":
+            d.type = _lib.CT_CA
+            d.node[0] = node(c.joint_name)
+            d.time_slot = 0
+            d.n_slots = int(c.n_canonical_frames)
+            mask, tgt = _mask_and_target(c.position)
+            d.axis_mask = mask
+            d.target = (C.c_double * 3)(*tgt)
+        else:
+            raise UnsupportedConstraintError("constraint type %r is outside the device path" % (ct,))
+    parr = (_lib.PosePoint * max(len(points), 1))(*points)
+    return descs, len(clist), parr, len(points), np.asarray(times, dtype=np.float64)
+
+
+class DeviceConstraints(object):
+    """A MotionPrimitiveConstraints list compiled for the GPU (mgb_constraints handle)."""
+
+    def __init__(self, dmodel, mp_constraints, prev_frames=None):
+        self.dmodel = dmodel
+        self.lib = dmodel.lib
+        descs, n, parr, n_points, times = flatten_constraints(dmodel, mp_constraints)
+        align = _lib.AlignDesc()
+        align.mode = 0
+        is_local = bool(getattr(mp_constraints, "is_local", False))
+        if not is_local:
+            if prev_frames is not None:
+                from .skeleton import heading_degrees
+                skeleton = mp_constraints.skeleton if getattr(mp_constraints, "skeleton", None) is not None else dmodel.skeleton
+                last = np.asarray(prev_frames[-1], dtype=np.float64)
+                align.mode = 1
+                align.prev_heading_deg = heading_degrees(skeleton, last)
+                align.prev_root = (C.c_double * 3)(*last[:3])
+                if 0.0 not in times:            # control point 0 == frame at t = 0 (clamped spline)
+                    times = np.concatenate([times, [0.0]])
+            elif getattr(mp_constraints, "start_pose", None) is not None:
+                raise UnsupportedConstraintError("start-pose alignment mutates start_pose per call (SURVEY.md Q2)")
+        self.times, self.spans, self.weights = dmodel.basis(times) if len(times) else (np.zeros(0), np.zeros(0, np.int32), np.zeros((0, 4)))
+        self.n_terms = n
+        h = C.c_void_p()
+        _lib.check(self.lib.mgb_constraints_pack(dmodel.handle, descs, n, parr, n_points, _dptr(self.times), len(self.times),
+                                                 _iptr(self.spans), _dptr(self.weights), C.byref(align), C.byref(h)))
+        self.handle = h
+
+    def __del__(self):
+        try:
+            if getattr(self, "handle", None):
+                self.lib.mgb_constraints_destroy(self.handle)
+                self.handle = None
+        except Exception:
+            pass
+
+    def score(self, s, k=1, error_scale=1.0, quality_scale=0.0, magnitude_scale=0.0, return_cost=False,
+              return_terms=False, index_base=0, frames=None):
+        """Score device-resident candidates.  s: [n, D] float32 or float64 CUDA tensor.
+        Returns dict(best_cost[k], best_idx[k] (device tensors), cost[n]?, terms[n_terms, n]?)."""
+        torch = _torch()
+        dm = self.dmodel
+        if not isinstance(s, torch.Tensor):
+            s = torch.as_tensor(np.ascontiguousarray(s), device=dm.torch_device)
+        if s.device != dm.torch_device:
+            s = s.to(dm.torch_device)
+        if s.dtype not in (torch.float32, torch.float64):
+            s = s.float()
+        s = s.contiguous()
+        n = int(s.shape[0])
+        assert s.dim() == 2 and s.shape[1] == dm.D, "samples must be [n, %d]" % dm.D
+        need_cost = return_cost or k > 1
+        cost = torch.empty((n,), dtype=torch.float32, device=dm.torch_device) if need_cost else None
+        terms = torch.empty((self.n_terms, n), dtype=torch.float32, device=dm.torch_device) if return_terms else None
+        best_cost = torch.empty((max(k, 1),), dtype=torch.float32, device=dm.torch_device)
+        best_idx = torch.empty((max(k, 1),), dtype=torch.int64, device=dm.torch_device)
+        ws = dm.workspace()
+        ptr = lambda t: C.c_void_p(t.data_ptr()) if t is not None else C.c_void_p(0)
+        with torch.cuda.device(dm.device):
+            if frames is None:
+                _lib.check(self.lib.mgb_score(dm.handle, self.handle, ptr(s), 1 if s.dtype == torch.float64 else 0, n, int(index_base),
+                                              float(error_scale), float(quality_scale), float(magnitude_scale), ptr(cost), ptr(terms),
+                                              int(k), ptr(best_cost), ptr(best_idx), ptr(ws), ws.numel(), dm._stream()))
+            else:
+                frames = dm._f32(frames)
+                s32 = s if s.dtype == torch.float32 else s.float()
+                _lib.check(self.lib.mgb_score_frames(dm.handle, self.handle, ptr(frames), ptr(s32), n, int(index_base),
+                                                     float(error_scale), float(quality_scale), float(magnitude_scale), ptr(cost),
+                                                     ptr(terms), int(k), ptr(best_cost), ptr(best_idx), ptr(ws), ws.numel(), dm._stream()))
+        out = {"best_cost": best_cost[:k], "best_idx": best_idx[:k]}
+        if return_cost:
+            out["cost"] = cost
+        if return_terms:
+            out["terms"] = terms
+        return out
+
+    def score_host(self, samples, k=1, error_scale=1.0, quality_scale=0.0, magnitude_scale=0.0, return_cost=False,
+                   index_base=0):
+        """Score HOST candidates (numpy float32/float64 [n, D], or a pinned CPU torch tensor):
+        chunked H2D overlapped with scoring, only the k results come back."""
+        torch = _torch()
+        if isinstance(samples, torch.Tensor):
+            assert samples.device.type == "cpu" and samples.is_contiguous()
+            is64 = samples.dtype == torch.float64
+            assert is64 or samples.dtype == torch.float32
+            n, D = samples.shape
+            sptr = samples.data_ptr()
+        else:
+            if samples.dtype not in (np.float32, np.float64) or not samples.flags["C_CONTIGUOUS"]:
+                samples = np.ascontiguousarray(samples, dtype=np.float64)
+            is64 = samples.dtype == np.float64
+            n, D = samples.shape
+            sptr = samples.ctypes.data
+        assert D == self.dmodel.D
+        cost = np.empty(n, dtype=np.float32) if return_cost else None
+        bc = np.empty(max(k, 1), dtype=np.float32)
+        bi = np.empty(max(k, 1), dtype=np.int64)
+        _lib.check(self.lib.mgb_score_host(self.dmodel.handle, self.handle, C.c_void_p(sptr), 1 if is64 else 0, int(n), int(index_base),
+                                           float(error_scale), float(quality_scale), float(magnitude_scale),
+                                           C.c_void_p(cost.ctypes.data if cost is not None else 0), int(k),
+                                           C.c_void_p(bc.ctypes.data), C.c_void_p(bi.ctypes.data)))
+        out = {"best_cost": bc[:k], "best_idx": bi[:k]}
+        if return_cost:
+            out["cost"] = cost
+        return out
+
+
+def launch_count():
+    return int(_lib.load().mgb_launch_count())

@@ -1,0 +1,282 @@
+"""Generate tests/golden/*.npz by running the REFERENCE's own modules.
+
+TEST INFRASTRUCTURE ONLY; runs only in the build container (needs
+/root/reference).  Usage:  python -m oracle.make_golden
+
+What runs unmodified from /root/reference (through oracle/refload.py):
+  MotionStateGraphNode/MotionPrimitiveModelWrapper -> MotionPrimitive.back_project,
+  MotionSpline.evaluate / get_motion_vector, sklearn GMM sample / score_samples,
+  MotionPrimitiveConstraints.evaluate + every spatial constraint class,
+  obj_spatial_error_sum, MotionPrimitiveGenerator.evaluate_samples_using_constraints,
+  ClusterTree / FeatureClusterTree search.
+What they call into and is NOT the reference (oracle/standin): anim_utils FK,
+alignment, point clouds; transformations.  PARITY UNPINNED for those.
+
+Each fixture stores the inputs that cannot be regenerated from seeds (the
+sklearn-drawn samples, the constraint specs as JSON) and the reference outputs.
+"""
+import io
+import json
+import os
+import sys
+import contextlib
+
+import numpy as np
+
+from oracle import refload
+from morphablegraphs_b200 import synthetic as syn
+
+GOLDEN_DIR = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests", "golden")
+
+
+def _quiet():
+    return contextlib.redirect_stdout(io.StringIO())
+
+
+def reference_factory(ns):
+    sc = ns.spatial_constraints
+    return {
+        "GlobalTransformConstraint": sc.GlobalTransformConstraint,
+        "RelativeTransformConstraint": sc.RelativeTransformConstraint,
+        "Direction2DConstraint": sc.Direction2DConstraint,
+        "PoseConstraint": sc.PoseConstraint,
+        "TwoHandConstraintSet": sc.TwoHandConstraintSet,
+        "FeetConstraint": sc.FeetConstraint,
+        "LookAtConstraint": sc.LookAtConstraint,
+        "GlobalTransformCAConstraint": ns.ca_constraint.GlobalTransformCAConstraint,
+    }
+
+
+def build_mp_constraints(ns, skeleton, specs, is_local=True):
+    mpc = ns.motion_primitive_constraints.MotionPrimitiveConstraints()
+    mpc.skeleton = skeleton
+    mpc.is_local = is_local
+    mpc.constraints = syn.build_constraints(reference_factory(ns), skeleton, specs)
+    return mpc
+
+
+def make_specs(ns, node, skeleton, F, rng, which):
+    """Constraint specs with targets taken from held-out draws of the same model
+    (so errors are in a realistic range), SURVEY.md section 8(d)."""
+    held = node.sample_low_dimensional_vectors(3)
+    spl = [node.back_project(h, use_time_parameters=False) for h in held]
+
+    def pos(k, joint, t):
+        return skeleton.nodes[joint].get_global_position(spl[k].evaluate(t)).tolist()
+
+    specs = []
+    if which == "config1":
+        specs.append(syn.spec("GlobalTransformConstraint",
+                              syn.position_constraint_desc("RightFoot", pos(0, "RightFoot", F - 1), F - 1, F), 1.0, 1.0))
+        return specs
+    # mixed set: every keyframe constraint type of SURVEY.md Appendix C
+    p = pos(0, "RightHand", F - 1)
+    q = skeleton.nodes["RightHand"].get_global_orientation_quaternion(spl[1].evaluate(F - 1)).tolist()
+    specs.append(syn.spec("GlobalTransformConstraint",
+                          syn.position_constraint_desc("RightHand", p, F - 1, F, orientation_q=q), 1.0, 1.0))
+    p = pos(1, "Hips", (F - 1) / 2.0)
+    p[1] = None   # height unconstrained; fractional keyframe (graph_walk_planner.py:203)
+    specs.append(syn.spec("GlobalTransformConstraint",
+                          syn.position_constraint_desc("Hips", p, (F - 1) / 2.0, F), 1.0, 0.5))
+    d = syn.position_constraint_desc("LeftHand", pos(2, "Bip01_L_Finger2", F - 1), F - 1, F)
+    d["offset"] = [3.0, -1.0, 2.0, 1.0]
+    specs.append(syn.spec("RelativeTransformConstraint", d, 1.0, 0.8))
+    specs.append(syn.spec("Direction2DConstraint",
+                          {"canonical_keyframe": F - 1, "dir_vector": [0.3, 0.0, 1.0],
+                           "semanticAnnotation": syn.sem()}, 1.0, 0.02))
+    names = ["Hips", "LeftHand", "RightHand", "LeftFoot", "RightFoot"]
+    f0 = spl[2].evaluate(0)
+    f1 = spl[2].evaluate(1)
+    cloud = [skeleton.nodes[n].get_global_position(f0).tolist() for n in names]
+    vel = (skeleton.nodes["Hips"].get_global_position(f1) - np.array(cloud[0])).tolist()
+    specs.append(syn.spec("PoseConstraint",
+                          {"canonical_keyframe": 0, "frame_constraint": cloud, "velocity_constraint": vel,
+                           "semanticAnnotation": syn.sem("start"), "node_names": names,
+                           "weights": [skeleton.joint_weight_map[n] for n in names]}, 1.0, 1.5))
+    specs.append(syn.spec("TwoHandConstraintSet",
+                          {"joint": ["LeftHand", "RightHand"],
+                           "positions": [pos(0, "LeftHand", F // 2), pos(0, "RightHand", F // 2)],
+                           "orientations": [None, None], "n_canonical_frames": F,
+                           "canonical_keyframe": F // 2, "semanticAnnotation": syn.sem("mid")}, 1.0, 1.0))
+    specs.append(syn.spec("FeetConstraint",
+                          {"canonical_keyframe": F - 1, "left": pos(1, "LeftFoot", F - 1),
+                           "right": pos(1, "RightFoot", F - 1), "semanticAnnotation": syn.sem()}, 1.0, 0.7))
+    specs.append(syn.spec("LookAtConstraint",
+                          {"canonical_keyframe": F // 3, "position": [40.0, 150.0, 200.0],
+                           "semanticAnnotation": syn.sem("look")}, 1.0, 2.0))
+    d = syn.position_constraint_desc("LeftFoot", pos(2, "LeftFoot", F // 2), None, F)
+    d["ca_constraint"] = True
+    specs.append(syn.spec("GlobalTransformCAConstraint", d, 1.0, 1.0))
+    return specs
+
+
+def run_case(ns, shape, which, n_samples, seed, translation_maxima=(1.0, 1.0, 1.0), non_local=False, n_joints=None):
+    cfg = syn.SHAPES[shape]
+    F = cfg["n_frames"]
+    mj = syn.make_model_json(shape, translation_maxima=translation_maxima)
+    skel_desc = syn.make_skeleton_desc(cfg["n_joints"])
+    skeleton = refload.make_skeleton(skel_desc)
+    node = refload.make_graph_node(ns, mj)
+    np.random.seed(seed)          # sklearn's GaussianMixture.sample uses the global state
+    rng = np.random.RandomState(syn.SEED_CONSTRAINTS)
+    specs = make_specs(ns, node, skeleton, F, rng, which)
+    S = node.sample_low_dimensional_vectors(n_samples)
+    mpc = build_mp_constraints(ns, skeleton, specs, is_local=not non_local)
+    prev_frames = None
+    if non_local:
+        prev = node.back_project(node.sample_low_dimensional_vectors(1)[0], use_time_parameters=False)
+        with _quiet():
+            pf = prev.get_motion_vector()
+        # turn and shift the previous motion so that alignment has something to do
+        from anim_utils.animation_data.motion_concatenation import transform_quaternion_frames
+        from transformations import quaternion_matrix, quaternion_about_axis
+        m = quaternion_matrix(quaternion_about_axis(0.7, [0, 1, 0]))
+        m[:3, 3] = [120.0, 0.0, -40.0]
+        prev_frames = transform_quaternion_frames(pf, m)[-3:]
+    out = {}
+    out["samples"] = S
+    out["specs_json"] = np.array(json.dumps(specs))
+    out["shape"] = np.array(shape)
+    out["translation_maxima"] = np.array(translation_maxima, dtype=np.float64)
+    out["is_local"] = np.array(not non_local)
+    if prev_frames is not None:
+        out["prev_frames"] = np.asarray(prev_frames)
+    # --- reference outputs -------------------------------------------------
+    splines = [node.back_project(s, use_time_parameters=False) for s in S]
+    out["coeffs"] = np.array([sp.coeffs.copy() for sp in splines])
+    key_times = sorted({float(sp_["desc"]["canonical_keyframe"]) for sp_ in specs
+                        if sp_["desc"].get("canonical_keyframe") is not None})
+    out["key_times"] = np.array(key_times)
+    out["key_frames"] = np.array([[sp.evaluate(t) for t in key_times] for sp in splines])
+    n_mv = min(4, n_samples)
+    with _quiet():
+        out["motion_vectors"] = np.array([splines[i].get_motion_vector() for i in range(n_mv)])
+    fk_names = list(skel_desc["nodes"].keys())
+    out["fk_names_json"] = np.array(json.dumps(fk_names))
+    out["fk_positions"] = np.array([[skeleton.nodes[n].get_global_position(out["key_frames"][i, -1])
+                                     for n in fk_names] for i in range(n_samples)])
+    # per-term errors and total cost through the reference's own loop
+    terms = np.zeros((len(mpc.constraints), n_samples))
+    costs = np.zeros(n_samples)
+    obj = ns.objective_functions.obj_spatial_error_sum
+    with _quiet():
+        for i, s in enumerate(S):
+            sp = node.back_project(s, use_time_parameters=False)
+            if non_local:
+                from anim_utils.animation_data.motion_concatenation import align_quaternion_frames
+                sp.coeffs = align_quaternion_frames(skeleton, skeleton.aligning_root_node, sp.coeffs,
+                                                    prev_frames, None)
+            for j, c in enumerate(mpc.constraints):
+                terms[j, i] = c.evaluate_motion_spline(sp)
+            costs[i] = obj(s, (node, mpc, prev_frames))
+    out["terms"] = terms
+    out["costs"] = costs
+    out["evaluations"] = np.array(mpc.evaluations)
+    # the reference's own arg-min loop
+    gen = ns.motion_primitive_generator.MotionPrimitiveGenerator.__new__(
+        ns.motion_primitive_generator.MotionPrimitiveGenerator)
+    gen.objective = obj
+    with _quiet():
+        best, min_error = gen.evaluate_samples_using_constraints(S, node, mpc, prev_frames)
+    out["best_idx"] = np.array(int(np.where((S == best).all(axis=1))[0][0]))
+    out["min_error"] = np.array(min_error)
+    gmm = node.get_gaussian_mixture_model()
+    out["logpdf"] = gmm.score_samples(S)
+    out["naturalness_cost"] = costs * 1.0 + 0.1 * (-out["logpdf"])   # error_scale 1, quality_scale 0.1
+    out["magnitude_cost"] = costs + 2.0 * np.linalg.norm(S, axis=1)   # mg_state_planner.py:129
+    return out, (node, skeleton, mpc, S, prev_frames)
+
+
+def run_tree_case(ns, n_data=400, n_candidates_list=(1, 2, 5), seed=11):
+    """ClusterTree (k-means + kd leaves) and FeatureClusterTree built by the
+    reference (KMeans seeded through numpy's global state) and searched with
+    the config-1 objective.  Stores the tree topology so the device-side search
+    can be checked on the *same* tree."""
+    shape = "S"
+    cfg = syn.SHAPES[shape]
+    F = cfg["n_frames"]
+    mj = syn.make_model_json(shape)
+    skeleton = refload.make_skeleton(syn.make_skeleton_desc(cfg["n_joints"]))
+    node = refload.make_graph_node(ns, mj)
+    np.random.seed(seed)
+    specs = make_specs(ns, node, skeleton, F, None, "config1")
+    mpc = build_mp_constraints(ns, skeleton, specs)
+    data = node.sample_low_dimensional_vectors(n_data)
+    K = node.get_n_spatial_components()
+    obj = ns.objective_functions.obj_spatial_error_sum
+    out = {"data": data, "specs_json": np.array(json.dumps(specs))}
+    with _quiet():
+        # max_level 6: a node that still holds > n_subdivisions samples at depth == max_level gets
+        # kd-tree children but leaf=False and the reference's own search then dies on
+        # `KDTreeWrapper.mean` (cluster_tree_node_builder.py:139-154 vs cluster_tree_node.py:133-134);
+        # deep enough that every branch ends in a proper leaf
+        tree = ns.cluster_tree.ClusterTree(4, 6, K, store_indices=True, use_kd_tree=True)
+        tree.construct(data)
+    out["cluster_tree_json"] = np.array(json.dumps(serialize_cluster_tree(tree.root)))
+    res = []
+    for nc in n_candidates_list:
+        with _quiet():
+            v, s = tree.find_best_example_excluding_search_candidates(obj, (node, mpc, None), nc)
+        res.append(np.concatenate([[v], np.asarray(s, dtype=np.float64)]))
+    out["cluster_tree_results"] = np.array(res)
+    out["n_candidates"] = np.array(n_candidates_list)
+    with _quiet():
+        opts = {"n_subdivisions": 4, "clustering_method": 0, "use_feature_mean": False}
+        ftree = ns.feature_cluster_tree.FeatureClusterTree(data[:, :K], data, None, opts, [])
+    out["feature_tree_json"] = np.array(json.dumps(serialize_feature_tree(ftree)))
+    res = []
+    for nc in n_candidates_list:
+        with _quiet():
+            v, s = ftree.find_best_example_excluding_search_candidates(obj, (node, mpc, None), nc)
+        res.append(np.concatenate([[v], np.asarray(s, dtype=np.float64)]))
+    out["feature_tree_results"] = np.array(res)
+    return out
+
+
+def serialize_kd(n):
+    if n is None:
+        return None
+    return {"point": list(map(float, n.point)), "type": n.type, "left": serialize_kd(n.left),
+            "right": serialize_kd(n.right)}
+
+
+def serialize_cluster_tree(node):
+    d = {"mean": node.mean.tolist(), "leaf": bool(node.leaf), "children": []}
+    for c in node.clusters:
+        if c.type == "kdtree":
+            d["children"].append({"kdtree": serialize_kd(c.kdtree.root)})
+        else:
+            d["children"].append(serialize_cluster_tree(c))
+    return d
+
+
+def serialize_feature_tree(node):
+    return {"mean": np.asarray(node._mean).tolist(),
+            "indices": None if node._indices is None else [int(i) for i in node._indices],
+            "children": [serialize_feature_tree(c) for c in node._children]}
+
+
+def main():
+    ns = refload.load()
+    os.makedirs(GOLDEN_DIR, exist_ok=True)
+    cases = [
+        ("s_config1", dict(shape="S", which="config1", n_samples=96, seed=2024)),
+        ("s_mixed", dict(shape="S", which="mixed", n_samples=64, seed=2025)),
+        ("s_mixed_tm", dict(shape="S", which="mixed", n_samples=32, seed=2026, translation_maxima=(50.0, 10.0, 80.0))),
+        ("s_nonlocal", dict(shape="S", which="mixed", n_samples=32, seed=2027, non_local=True)),
+        ("xs_mixed", dict(shape="XS", which="mixed", n_samples=32, seed=2028)),
+        ("l_mixed", dict(shape="L", which="mixed", n_samples=12, seed=2029)),
+    ]
+    for name, kw in cases:
+        out, _ = run_case(ns, **kw)
+        # keep fixtures small: coefficients only for the first 8 candidates
+        out["coeffs"] = out["coeffs"][:8]
+        np.savez_compressed(os.path.join(GOLDEN_DIR, name + ".npz"), **out)
+        print(name, "costs[:3]", out["costs"][:3], "best", int(out["best_idx"]), float(out["min_error"]))
+    out = run_tree_case(ns)
+    np.savez_compressed(os.path.join(GOLDEN_DIR, "s_tree.npz"), **out)
+    print("s_tree", out["cluster_tree_results"][:, 0], out["feature_tree_results"][:, 0])
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -1,0 +1,89 @@
+"""Pins oracle/np_oracle.py against the golden vectors produced by the
+reference's own modules (oracle/make_golden.py).  CPU only."""
+import json
+
+import numpy as np
+import pytest
+
+from oracle import np_oracle as O
+from tests.common import Case, CASES, rel_err
+
+TOL = 1e-9   # float64 restatement vs float64 reference
+
+
+@pytest.fixture(scope="module", params=CASES)
+def case(request):
+    return Case(request.param)
+
+
+def test_coeffs_and_frames(case):
+    g = case.g
+    ma = O.ModelArrays(case.node)
+    coeffs = O.back_project_coeffs(ma, case.samples)
+    assert rel_err(coeffs[:8], g["coeffs"]).max() < TOL
+    frames = O.eval_frames(ma, coeffs, g["key_times"])
+    assert rel_err(frames, g["key_frames"]).max() < TOL
+    # full motion vector incl. the extrapolated last sample at t = F (quirk Q1)
+    mv = O.eval_frames(ma, coeffs[:g["motion_vectors"].shape[0]], O.motion_vector_times(ma.F))
+    assert mv.shape == g["motion_vectors"].shape
+    assert rel_err(mv, g["motion_vectors"]).max() < TOL
+
+
+def test_basis_restatements_agree(case):
+    ma = O.ModelArrays(case.node)
+    for t in list(case.g["key_times"]) + [0.0, 0.5, ma.F - 1.0, float(ma.F), ma.F * 1.02, -0.25]:
+        s1, w1 = O.spline_basis_fitpack(ma.knots, t)
+        s2, w2 = O.spline_basis_deboor(ma.knots, t)
+        assert s1 == s2
+        assert np.abs(w1 - w2).max() < 1e-12
+        assert abs(w1.sum() - 1.0) < 1e-12
+
+
+def test_fk_positions(case):
+    g = case.g
+    names = json.loads(str(g["fk_names_json"]))
+    pos = O.fk_positions(case.skeleton, g["key_frames"][:, -1, :], names)
+    assert rel_err(pos, g["fk_positions"]).max() < TOL
+
+
+def test_terms_costs_argmin(case):
+    g = case.g
+    cost, terms = O.candidate_costs(case.node, case.skeleton, case.constraints, case.samples, case.prev_frames,
+                                    return_terms=True)
+    assert rel_err(terms, g["terms"]).max() < 1e-8
+    assert rel_err(cost, g["costs"]).max() < 1e-8
+    idx, err = O.first_argmin(cost)
+    assert idx == int(g["best_idx"])
+    assert abs(err - float(g["min_error"])) < 1e-8 * max(1.0, abs(err))
+    bi, be = O.evaluate_samples_using_constraints(case.node, case.skeleton, case.constraints, case.samples,
+                                                  case.prev_frames, chunk=7)
+    assert bi == idx and abs(be - err) < 1e-12
+
+
+def test_gmm_logpdf_and_objectives(case):
+    g = case.g
+    ma = O.ModelArrays(case.node)
+    lp = O.gmm_logpdf(ma, case.samples)
+    assert rel_err(lp, g["logpdf"]).max() < 1e-9
+    c_nat = O.candidate_costs(case.node, case.skeleton, case.constraints, case.samples, case.prev_frames,
+                              error_scale=1.0, quality_scale=0.1)
+    assert rel_err(c_nat, g["naturalness_cost"]).max() < 1e-8
+    c_mag = O.candidate_costs(case.node, case.skeleton, case.constraints, case.samples, case.prev_frames,
+                              magnitude_scale=2.0)
+    assert rel_err(c_mag, g["magnitude_cost"]).max() < 1e-8
+
+
+def test_precision_cholesky_matches_mirror(case):
+    ma = O.ModelArrays(case.node)
+    pc = O.precision_cholesky(ma.covars)
+    assert np.abs(pc - ma.prec_chol).max() < 1e-9
+
+
+def test_loop_port_matches_vectorised():
+    case = Case("s_config1")
+    ma = O.ModelArrays(case.node)
+    c = case.constraints.constraints[0]
+    i, e = O.loop_evaluate_one_position(ma, case.skeleton, c, case.samples[:24])
+    cost = O.candidate_costs(case.node, case.skeleton, case.constraints, case.samples[:24])
+    j, f = O.first_argmin(cost)
+    assert i == j and abs(e - f) < 1e-9
