@@ -652,6 +652,7 @@ extern "C" int mgb_score_host(const mgb_model* m_, const mgb_constraints* c, con
         m->d_ws = nullptr;
         m->ws_bytes = 0;
         MGB_CUDA(cudaMalloc(&m->d_ws, need));
+        MGB_CUDA(cudaMemset(m->d_ws, 0, need));
         m->ws_bytes = need;
     }
     unsigned char* ws = reinterpret_cast<unsigned char*>(m->d_ws);

@@ -321,10 +321,12 @@ __global__ void __launch_bounds__(MGB_BLOCK) mgb_score_kernel(ScoreParams p) {
                     break;
                 }
                 case OP_ORIENT: {
+                    // angle_between_vectors(v1, v2) = acos(v1.v2 / |v1||v2|), evaluated as
+                    // atan2(|v1 x v2|, v1.v2): same value, but well conditioned near 0 and pi in fp32
                     float vx = G.R[2], vy = G.R[5], vz = G.R[8];
-                    float d = (vx * cs[1] + vy * cs[2] + vz * cs[3]) * rsqrtf(vx * vx + vy * vy + vz * vz);
-                    d = fminf(1.f, fmaxf(-1.f, d));
-                    emit(op.a, cs[0], acosf(d));
+                    float cx = vy * cs[3] - vz * cs[2], cy = vz * cs[1] - vx * cs[3], cz = vx * cs[2] - vy * cs[1];
+                    float d = vx * cs[1] + vy * cs[2] + vz * cs[3];
+                    emit(op.a, cs[0], atan2f(sqrtf(cx * cx + cy * cy + cz * cz), d));
                     break;
                 }
                 case OP_REL: {
@@ -337,14 +339,13 @@ __global__ void __launch_bounds__(MGB_BLOCK) mgb_score_kernel(ScoreParams p) {
                     break;
                 }
                 case OP_DIR2D: {
+                    // degrees(acos(clamp(t.d / (|t||d|)))) evaluated as atan2(|t x d|, t.d) (same value,
+                    // well conditioned for small angles in fp32); d = (x, z) of R_global * ref_dir
                     float px = G.R[0] * cs[1] + G.R[1] * cs[2] + G.R[2] * cs[3];
                     float pz = G.R[6] * cs[1] + G.R[7] * cs[2] + G.R[8] * cs[3];
-                    float inv = rsqrtf(px * px + pz * pz);
-                    float dx = px * inv, dz = pz * inv;
-                    float mag = cs[6] * sqrtf(dx * dx + dz * dz);
-                    float cosang = (cs[4] * dx + cs[5] * dz) / mag;
-                    cosang = fminf(1.f, fmaxf(-1.f, cosang));
-                    emit(op.a, cs[0], fabsf(acosf(cosang) * 57.29577951308232f));
+                    float cr = cs[4] * pz - cs[5] * px;
+                    float dt = cs[4] * px + cs[5] * pz;
+                    emit(op.a, cs[0], atan2f(fabsf(cr), dt) * 57.29577951308232f);
                     break;
                 }
                 case OP_LOOKAT: {
@@ -721,11 +722,8 @@ int mgb_launch_score(const mgb_model* m, const mgb_constraints* c, const void* d
     smem += (size_t)MGB_BLOCK * (m->D | 1) * sizeof(float);
     smem += 16 + 32 * sizeof(float) + 8 + 32 * sizeof(long long);
     MGB_REQUIRE(smem <= 200 * 1024, "constraint program too large for shared memory (%zu bytes)", smem);
-    if (k == 1) {
-        // the completion counter must start at zero; it is reset by the kernel itself afterwards,
-        // so only the very first use of a workspace needs this (cheap, stream-ordered)
-        MGB_CUDA(cudaMemsetAsync(p.done_count, 0, sizeof(unsigned int), stream));
-    }
+    // the completion counter in the workspace must be zero on entry: the caller zero-fills a
+    // fresh workspace once (include/mgb200.h) and the kernel re-arms it at the end of every launch
     if (d_terms) MGB_CUDA(cudaMemsetAsync(d_terms, 0, (size_t)c->n_terms * n * sizeof(float), stream));
 
     int rc;

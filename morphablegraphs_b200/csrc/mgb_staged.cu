@@ -45,9 +45,15 @@ __device__ __forceinline__ float u01(unsigned int x) {  // (0, 1]
 
 // K1.  One thread per candidate; z and then s live in the thread's shared-memory
 // row (odd stride), the tile is written out with unit-stride stores.
+#define MGB_MAX_GMM 64
+struct GmmPrefix {
+    long long v[MGB_MAX_GMM + 1];
+};
+
 __global__ void __launch_bounds__(SAMPLE_BLOCK) mgb_sample_kernel(const float* __restrict__ means, const float* __restrict__ chol,
-                                                                 const long long* __restrict__ prefix, int G, int D, long long n,
+                                                                 const GmmPrefix pre, int G, int D, long long n,
                                                                  long long index_base, unsigned long long seed, float* __restrict__ out) {
+    const long long* prefix = pre.v;
     extern __shared__ float sm[];
     const int SROW = D | 1;
     float* row = sm + threadIdx.x * SROW;
@@ -426,18 +432,16 @@ extern "C" int mgb_sample(const mgb_model* m, int64_t n, int64_t index_base, con
     MGB_REQUIRE(m && h_counts && (d_s || n == 0), "null argument");
     MGB_REQUIRE(n >= 0 && index_base >= 0, "negative size");
     if (n == 0) return MGB_OK;
-    std::vector<long long> prefix(m->G + 1, 0);
+    MGB_REQUIRE(m->G <= MGB_MAX_GMM, "at most %d mixture components are supported by the sampler", MGB_MAX_GMM);
+    GmmPrefix prefix;  // passed by value as a kernel argument: no allocation, copy or sync per call
+    prefix.v[0] = 0;
     for (int g = 0; g < m->G; ++g) {
         MGB_REQUIRE(h_counts[g] >= 0, "negative component count");
-        prefix[g + 1] = prefix[g] + h_counts[g];
+        prefix.v[g + 1] = prefix.v[g] + h_counts[g];
     }
-    MGB_REQUIRE(index_base + n <= prefix[m->G], "component counts (%lld) do not cover [%lld, %lld)", prefix[m->G],
+    for (int g = m->G + 1; g <= MGB_MAX_GMM; ++g) prefix.v[g] = prefix.v[m->G];
+    MGB_REQUIRE(index_base + n <= prefix.v[m->G], "component counts (%lld) do not cover [%lld, %lld)", prefix.v[m->G],
                 (long long)index_base, (long long)(index_base + n));
-    long long* d_prefix = nullptr;
-    MGB_CUDA(cudaMallocAsync((void**)&d_prefix, sizeof(long long) * (m->G + 1), stream));
-    MGB_CUDA(cudaMemcpyAsync(d_prefix, prefix.data(), sizeof(long long) * (m->G + 1), cudaMemcpyHostToDevice, stream));
-    // the host vector must outlive the async copy
-    MGB_CUDA(cudaStreamSynchronize(stream));
     size_t smem = (size_t)SAMPLE_BLOCK * (m->D | 1) * sizeof(float);
     MGB_REQUIRE(smem <= 200 * 1024, "latent dimension too large for the sampler");
     static bool configured = false;
@@ -450,11 +454,10 @@ extern "C" int mgb_sample(const mgb_model* m, int64_t n, int64_t index_base, con
     MGB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, mgb_sample_kernel, SAMPLE_BLOCK, smem));
     long long grid = (long long)sm_count() * (occ > 0 ? occ : 1);
     if (grid > n_tiles) grid = n_tiles;
-    mgb_sample_kernel<<<(unsigned)grid, SAMPLE_BLOCK, smem, stream>>>(m->d_means, m->d_chol, d_prefix, m->G, m->D, n, index_base,
+    mgb_sample_kernel<<<(unsigned)grid, SAMPLE_BLOCK, smem, stream>>>(m->d_means, m->d_chol, prefix, m->G, m->D, n, index_base,
                                                                     (unsigned long long)seed, d_s);
     mgb_count_launch();
     MGB_CUDA(cudaGetLastError());
-    MGB_CUDA(cudaFreeAsync(d_prefix, stream));
     return MGB_OK;
 }
 

@@ -1,0 +1,112 @@
+"""Timed CPU baseline for bench.py (`cpu_baseline` leg and `--impl reference`).
+
+TEST INFRASTRUCTURE ONLY.  Times the oracle port (oracle/np_oracle.py: the
+vectorised float64 numpy restatement of the reference's sample -> back-project
+-> spline -> FK -> cost -> arg-min path) on the host cores, one worker process
+per core, each drawing its own GMM samples exactly like the reference's sampler
+(sklearn GaussianMixture.sample algorithm, np_oracle.gmm_sample) and scoring
+them in chunks.  Also times the per-candidate loop port
+(np_oracle.loop_evaluate_one_position), which has the reference's own call
+structure (one Python iteration, P splev calls and a chain of 4x4 products per
+candidate - reference motion_primitive_generator.py:253-257) and therefore its
+single-core speed.
+
+The reference itself cannot run on the GPU box (/root/reference is absent there
+and its third-party dependencies are not installed), so kind = "port".
+Nothing in here imports torch or touches CUDA (workers are spawned).
+"""
+import multiprocessing as mp
+import os
+import time
+
+import numpy as np
+
+_STATE = {}
+
+
+def build_case(shape="S"):
+    from morphablegraphs_b200 import synthetic as syn
+    from morphablegraphs_b200 import Skeleton, MotionStateGraphNode, MotionPrimitiveConstraints, CONSTRAINT_FACTORY
+    from oracle import np_oracle as O
+    cfg = syn.SHAPES[shape]
+    F = cfg["n_frames"]
+    skeleton = Skeleton.from_desc(syn.make_skeleton_desc(cfg["n_joints"]))
+    node = MotionStateGraphNode()
+    node._initialize_from_json(None, syn.make_model_json(shape))
+    ma = O.ModelArrays(node)
+    rng = np.random.RandomState(syn.SEED_CONSTRAINTS)
+    held, _ = O.gmm_sample(ma, 1, rng)
+    frame = O.eval_frames(ma, O.back_project_coeffs(ma, held), [F - 1.0])[:, 0, :]
+    target = O.fk_positions(skeleton, frame, ["RightFoot"])[0, 0].tolist()
+    mpc = MotionPrimitiveConstraints()
+    mpc.skeleton = skeleton
+    mpc.is_local = True
+    specs = [syn.spec("GlobalTransformConstraint", syn.position_constraint_desc("RightFoot", target, F - 1, F))]
+    mpc.constraints = syn.build_constraints(CONSTRAINT_FACTORY, skeleton, specs)
+    return node, skeleton, mpc, ma
+
+
+def _init(shape):
+    os.environ.setdefault("OMP_NUM_THREADS", "1")
+    os.environ.setdefault("OPENBLAS_NUM_THREADS", "1")
+    _STATE["case"] = build_case(shape)
+
+
+def _work(args):
+    from oracle import np_oracle as O
+    seed, n, chunk = args
+    node, skeleton, mpc, ma = _STATE["case"]
+    rng = np.random.RandomState(seed)
+    best = (np.inf, -1)
+    done = 0
+    while done < n:
+        m = min(chunk, n - done)
+        S, _ = O.gmm_sample(ma, m, rng)
+        cost = O.candidate_costs(ma, skeleton, mpc, S)
+        i, e = O.first_argmin(cost)
+        if e < best[0]:
+            best = (e, done + i)
+        done += m
+    return best[0], n
+
+
+class Pool(object):
+    """Persistent worker pool so that process start-up is outside the timed region."""
+
+    def __init__(self, shape="S", workers=None):
+        self.workers = workers or os.cpu_count() or 1
+        ctx = mp.get_context("spawn")
+        self.pool = ctx.Pool(self.workers, initializer=_init, initargs=(shape,))
+        # make sure every worker has finished its initialiser
+        self.pool.map(_work, [(i, 64, 64) for i in range(self.workers * 2)])
+
+    def run(self, n_total, seed=0, chunk=16384):
+        """Sample and score n_total candidates across the workers; returns seconds."""
+        per = int(np.ceil(n_total / float(self.workers * 4)))
+        jobs = []
+        left = n_total
+        j = 0
+        while left > 0:
+            m = min(per, left)
+            jobs.append((seed * 100003 + j, m, chunk))
+            left -= m
+            j += 1
+        t0 = time.perf_counter()
+        res = self.pool.map(_work, jobs)
+        dt = time.perf_counter() - t0
+        assert sum(r[1] for r in res) == n_total
+        return dt
+
+    def close(self):
+        self.pool.close()
+        self.pool.join()
+
+
+def loop_port_rate(shape="S", n=1500, seed=3):
+    """candidates/s of the per-candidate loop port on one core."""
+    from oracle import np_oracle as O
+    node, skeleton, mpc, ma = build_case(shape)
+    S, _ = O.gmm_sample(ma, n, np.random.RandomState(seed))
+    t0 = time.perf_counter()
+    O.loop_evaluate_one_position(ma, skeleton, mpc.constraints[0], S)
+    return n / (time.perf_counter() - t0)
