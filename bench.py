@@ -1,0 +1,428 @@
+#!/usr/bin/env python
+"""bench.py -- motion candidates evaluated / second (sample -> back-project -> FK -> cost -> arg-min).
+
+Contract (driver): `python bench.py --gpus N --steps K --warmup W` prints ONE JSON line on rank 0;
+N > 1 is launched by torchrun (one rank per GPU, NCCL).  `--impl reference` times the CPU port of
+the reference's path (oracle/, all host cores) on the same workload instead.
+
+Workloads (BASELINE.json `configs`):
+  S1M (default, configs[1]): synthetic walk-leftStance primitive (J=19, P=79, F=50, Nb=10, K=10, D=13,
+       G=8), 1,000,000 GMM samples per step PER GPU, one joint-position constraint (the exact
+       constraint of tests/golden/s_config1.npz), arg-min.
+  L4M  (configs[3]): large model (J=70, K=100, D=103, G=32), 4,000,000 candidates per step per GPU,
+       mixed constraints (tests/golden/l_mixed.npz) + naturalness.
+
+A step (device arm, `value`): K1 GMM sampling on the device + K6 fused score + arg-min (+ for N > 1
+the exchange of every rank's best (cost, index)); model and constraint tables resident in HBM.
+`e2e`: the reference-facing call with HOST samples (float64, pinned) -> mgb_score_host -> best
+(cost, index) back on the host; H2D and D2H inside the timed region.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+METRIC = "motion candidates evaluated/sec (backproject+FK+cost)"
+UNIT = "candidates/s"
+WORKLOADS = {
+    "S1M": dict(golden="s_config1", shape="S", n_per_gpu=1_000_000, quality_scale=0.0,
+                desc="S primitive (J=19,P=79,F=50,Nb=10,K=10,D=13,G=8), 1M GMM samples/step/GPU, "
+                     "one joint-position constraint, arg-min"),
+    "L4M": dict(golden="l_mixed", shape="L", n_per_gpu=4_000_000, quality_scale=0.1,
+                desc="L primitive (J=70,P=283,F=100,Nb=20,K=100,D=103,G=32), 4M samples/step/GPU, "
+                     "mixed constraints + naturalness, arg-min"),
+}
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="S1M", choices=sorted(WORKLOADS))
+    ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the cpu_baseline leg")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-staged", action="store_true", help="skip the staged-pipeline kernel rooflines")
+    return ap.parse_args()
+
+
+def build_case(workload):
+    """Model, skeleton and constraint list of the workload, rebuilt from seeds + the committed
+    golden fixture's constraint specs (product host classes only; no oracle, no reference)."""
+    from morphablegraphs_b200 import synthetic as syn
+    from morphablegraphs_b200 import Skeleton, MotionStateGraphNode, MotionPrimitiveConstraints, CONSTRAINT_FACTORY
+    w = WORKLOADS[workload]
+    g = np.load(os.path.join(ROOT, "tests", "golden", w["golden"] + ".npz"), allow_pickle=False)
+    cfg = syn.SHAPES[w["shape"]]
+    skeleton = Skeleton.from_desc(syn.make_skeleton_desc(cfg["n_joints"]))
+    node = MotionStateGraphNode()
+    node._initialize_from_json(None, syn.make_model_json(w["shape"], translation_maxima=tuple(g["translation_maxima"])))
+    node.set_skeleton(skeleton)
+    mpc = MotionPrimitiveConstraints()
+    mpc.skeleton = skeleton
+    mpc.is_local = bool(g["is_local"])
+    mpc.constraints = syn.build_constraints(CONSTRAINT_FACTORY, skeleton, json.loads(str(g["specs_json"])))
+    prev = g["prev_frames"] if "prev_frames" in g.files else None
+    return node, skeleton, mpc, prev
+
+
+class ClockSampler(object):
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index = index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append((time.perf_counter(), line.strip()))
+
+    def stop(self):
+        if self.proc is not None:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=5)
+            except Exception:
+                self.proc.kill()
+
+    def summary(self, t0=None, t1=None):
+        sm, mx, reasons, pw = [], 0.0, set(), 0.0
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ts, line in self.lines:
+            if t0 is not None and not (t0 - 0.05 <= ts <= t1 + 0.15):
+                continue
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0]))
+                mx = max(mx, float(f[1]))
+                pw = max(pw, float(f[2]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": mx, "reasons": sorted(reasons), "samples": len(sm),
+                "power_w_max": pw}
+
+
+# ---------------------------------------------------------------------------
+# CPU arm: the oracle port on the host cores (the ONLY place bench.py executes oracle/)
+# ---------------------------------------------------------------------------
+def cpu_pool(workload):
+    from oracle import cpu_baseline as cb
+    w = WORKLOADS[workload]
+    return cb.Pool(w["golden"], w["shape"], w["quality_scale"])
+
+
+def calibrate_cpu(pool, seconds):
+    """Candidates per sample so that one sample takes about `seconds` on this host."""
+    n0 = 20000 * pool.workers // 8 + 8000
+    dt = pool.run(n0, seed=11)
+    rate = n0 / dt
+    return max(n0, int(rate * seconds)), rate
+
+
+def run_reference(args):
+    """`--impl reference`: the reference's CPU path (numpy port, oracle/np_oracle.py; the reference
+    itself is not installable on the GPU box: anim_utils/transformations are absent) on
+    all host cores; each step = a bounded sample of the workload (sample -> score -> arg-min)."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    w = WORKLOADS[args.workload]
+    pool = cpu_pool(args.workload)
+    per_step, _ = calibrate_cpu(pool, min(4.0, 120.0 / max(1, args.steps + args.warmup // 4)))
+    per_step = min(per_step, w["n_per_gpu"])
+    for i in range(args.warmup):
+        pool.run(per_step // 4, seed=100 + i)
+    t = 0.0
+    for i in range(args.steps):
+        t += pool.run(per_step, seed=200 + i)
+    pool.close()
+    value = per_step * args.steps / t
+    sample = "%d candidates per step (of the %d-candidate workload), sampled + scored + arg-min" % (per_step, w["n_per_gpu"])
+    out = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+           "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t / args.steps,
+           "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+           "config": {"workload": args.workload, "description": w["desc"], "sample": sample},
+           "cpu_baseline": {"value": value, "unit": UNIT, "cores": pool.workers, "kind": "port", "sample": sample},
+           "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+           "gpu_launches": 0}
+    print(json.dumps(out))
+    return 0
+
+
+def cpu_baseline_leg(args):
+    from oracle import cpu_baseline as cb
+    w = WORKLOADS[args.workload]
+    pool = cpu_pool(args.workload)
+    n, _ = calibrate_cpu(pool, max(2.0, args.cpu_seconds * 0.6))
+    n = min(n, w["n_per_gpu"])
+    dt = pool.run(n, seed=5)
+    pool.close()
+    out = {"value": n / dt, "unit": UNIT, "cores": pool.workers, "kind": "port",
+           "sample": "%d of %d candidates, sampled + scored + arg-min by oracle/np_oracle.py (vectorised float64 numpy), "
+                     "one process per core" % (n, w["n_per_gpu"])}
+    if args.workload == "S1M":
+        n_loop = 1500
+        out["loop_port"] = {"value": cb.loop_port_rate(w["golden"], w["shape"], n=n_loop), "unit": UNIT, "cores": 1,
+                            "sample": "%d candidates through the per-candidate loop port (the reference's own call structure)" % n_loop}
+    return out
+
+
+# ---------------------------------------------------------------------------
+# GPU arm
+# ---------------------------------------------------------------------------
+class L2Flusher(object):
+    """Between timed iterations: overwrite a buffer larger than the 126 MB L2 (untimed)."""
+
+    def __init__(self, torch, device, nbytes=384 << 20):
+        self.buf = torch.empty(nbytes // 4, dtype=torch.float32, device=device)
+        self.v = 0.0
+
+    def __call__(self):
+        self.v += 1.0
+        self.buf.fill_(self.v)
+
+
+def timed(torch, fn, reps, flush, warmup=3):
+    """Mean device time (ms) of fn() over reps, CUDA events on the current stream, L2 flushed
+    (untimed) before every repetition."""
+    for _ in range(warmup):
+        fn()
+    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(reps)]
+    torch.cuda.synchronize()
+    for e0, e1 in evs:
+        flush()
+        e0.record()
+        fn()
+        e1.record()
+    torch.cuda.synchronize()
+    return float(np.mean([e0.elapsed_time(e1) for e0, e1 in evs]))
+
+
+def algorithmic_work(dm, dc, n, quality_scale):
+    """Per-launch algorithmic bytes / flop of each kernel (SURVEY.md section 8(d) x n candidates)."""
+    D, K, P, Nb, G = dm.D, dm.K, dm.P, dm.Nb, dm.G
+    T = len(dc.times)
+    nq = dc.n_quads
+    fk_flop = 100.0 * nq                      # ~100 flop per joint on a walked chain (a14)
+    gmm_flop = 2.0 * G * D * D if quality_scale != 0.0 else 0.0
+    return {
+        "K1_gmm_sample": dict(bound="hbm", bytes=4.0 * D * n, flop=2.0 * D * D * n),
+        "K6_fused_score": dict(bound="fp32", bytes=(4.0 * D + 4.0) * n, flop=(2.0 * K * 4 * nq + fk_flop + gmm_flop) * n),
+        "K2_backproject": dict(bound="tensor", bytes=(4.0 * K + 4.0 * Nb * P) * n, flop=2.0 * K * Nb * P * n),
+        "K3_spline_eval": dict(bound="hbm", bytes=(4.0 * P * min(Nb, 4 * T) + 4.0 * T * P) * n, flop=8.0 * T * P * n),
+        "K5a_score_frames": dict(bound="hbm", bytes=(4.0 * 4 * nq + 4.0) * n, flop=(fk_flop + gmm_flop) * n),
+    }
+
+
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+    from morphablegraphs_b200 import engine, _lib
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the B200 arm has no CPU fallback (use --impl reference for the CPU port)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    w = WORKLOADS[args.workload]
+    n = w["n_per_gpu"]
+    qs = w["quality_scale"]
+    node, skeleton, mpc, prev = build_case(args.workload)
+    dm = engine.DeviceModel(node, skeleton, local)
+    dc = engine.DeviceConstraints(dm, mpc, prev)
+    lib = _lib.load()
+    flush = L2Flusher(torch, dev)
+    counts = dm.component_counts(n * world, seed=2024)       # one multinomial split for the whole job
+    S = torch.empty((n, dm.D), dtype=torch.float32, device=dev)
+    gathered = torch.empty((world, 2), dtype=torch.float64, device=dev) if world > 1 else None
+    state = {"seed": 0}
+
+    def step():
+        """one pass of the hot path over this rank's shard: K1 sample -> K6 score + arg-min (-> exchange)"""
+        state["seed"] += 1
+        dm.sample(n, seed=state["seed"], index_base=rank * n, counts=counts, n_total=n * world, out=S)
+        res = dc.score(S, k=1, quality_scale=qs, index_base=rank * n)
+        if world > 1:
+            mine = torch.stack([res["best_cost"][0].double(), res["best_idx"][0].double()])
+            dist.all_gather_into_tensor(gathered.view(-1), mine)
+            c = gathered[:, 0]
+            best = torch.argmin(c)          # first minimum: ranks hold ascending global index ranges
+            return gathered[best]
+        return res
+
+    clocks = ClockSampler(local)
+    if rank == 0:
+        clocks.start()
+    for _ in range(max(args.warmup, 3)):
+        step()
+    launches0 = engine.launch_count()
+    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    t_wall0 = time.perf_counter()
+    for e0, e1 in evs:
+        flush()
+        e0.record()
+        step()
+        e1.record()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    t_wall1 = time.perf_counter()
+    launches = engine.launch_count() - launches0
+    total_ms = float(sum(e0.elapsed_time(e1) for e0, e1 in evs))
+    if world > 1:
+        t = torch.tensor([total_ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        total_ms = float(t.item())
+    value = n * world * args.steps / (total_ms * 1e-3)
+
+    # ---- e2e: host samples (float64, pinned) through the reference-facing call ----------
+    host = torch.empty((n, dm.D), dtype=torch.float64).pin_memory()
+    host.copy_(S.double().cpu())
+    e2e_steps = max(3, min(args.steps, 10))
+    for _ in range(2):
+        dc.score_host(host, k=1, quality_scale=qs, index_base=rank * n)
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        r = dc.score_host(host, k=1, quality_scale=qs, index_base=rank * n)
+        if world > 1:
+            mine = torch.tensor([float(r["best_cost"][0]), float(r["best_idx"][0])], dtype=torch.float64, device=dev)
+            dist.all_gather_into_tensor(gathered.view(-1), mine)
+            gathered.cpu()
+    torch.cuda.synchronize()
+    e2e_t = time.perf_counter() - t0
+    if world > 1:
+        t = torch.tensor([e2e_t], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_t = float(t.item())
+    t_clock1 = time.perf_counter()
+    e2e = {"value": n * world * e2e_steps / e2e_t, "unit": UNIT, "h2d_bytes_per_step": int(n * dm.D * 8) * world,
+           "d2h_bytes_per_step": 12 * world, "steps": e2e_steps, "ms_per_step": 1e3 * e2e_t / e2e_steps,
+           "call": "MotionPrimitiveGenerator.evaluate_samples_using_constraints -> mgb_score_host, float64 pinned host samples"}
+    if rank == 0:
+        clocks.stop()
+    clk = clocks.summary(t_wall0, t_clock1) if rank == 0 else None
+    return dict(torch=torch, dist=dist, dm=dm, dc=dc, lib=lib, flush=flush, S=S, counts=counts, n=n, qs=qs, rank=rank,
+                world=world, local=local, value=value, total_ms=total_ms, launches=launches, e2e=e2e, clocks=clk, w=w)
+
+
+def kernel_rooflines(ctx, args):
+    """Per-kernel device times (CUDA events, L2 flushed before each launch) against the measured
+    peaks: HBM copy bandwidth from MEASURED_PEAKS.json, fp32 FMA rate measured live by the library."""
+    import ctypes as C
+    torch, dm, dc, flush, S, n, qs = ctx["torch"], ctx["dm"], ctx["dc"], ctx["flush"], ctx["S"], ctx["n"], ctx["qs"]
+    peaks = {}
+    pk_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(pk_path):
+        peaks = json.load(open(pk_path))
+    hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
+    peak_src = "measured (MEASURED_PEAKS.json)" if "hbm_gbs" in peaks else "fallback (B200_PROFILING.md)"
+    tf = C.c_double()
+    _ = ctx["lib"].mgb_fp32_fma_peak(ctx["local"], C.byref(tf))
+    fp32_peak = float(tf.value)
+    work = algorithmic_work(dm, dc, n, qs)
+    reps = 10
+    times = {}
+    times["K1_gmm_sample"] = timed(torch, lambda: dm.sample(n, seed=7, counts=ctx["counts"], n_total=n * ctx["world"], out=S), reps, flush)
+    times["K6_fused_score"] = timed(torch, lambda: dc.score(S, k=1, quality_scale=qs), reps, flush)
+    if not args.no_staged:
+        ns = min(n, 1_000_000 if dm.K <= 16 else 250_000)     # staged intermediates: n * Nb * P * 4 bytes
+        Ss = S[:ns]
+        coeffs = torch.empty((ns, dm.Nb, dm.P), dtype=torch.float32, device=S.device)
+        frames = torch.empty((ns, len(dc.times), dm.P), dtype=torch.float32, device=S.device)
+        sw = algorithmic_work(dm, dc, ns, qs)
+        for k in ("K2_backproject", "K3_spline_eval", "K5a_score_frames"):
+            work[k] = sw[k]
+            work[k]["n"] = ns
+        times["K2_backproject"] = timed(torch, lambda: dm.backproject(Ss, impl=1, out=coeffs), 5, flush)
+        times["K3_spline_eval"] = timed(torch, lambda: dm.eval_frames(coeffs, dc.times, out=frames), 5, flush)
+        times["K5a_score_frames"] = timed(torch, lambda: dc.score(Ss, k=1, quality_scale=qs, frames=frames), 5, flush)
+    out = {}
+    for k, ms in times.items():
+        wk = work[k]
+        gbs = wk["bytes"] / (ms * 1e-3) * 1e-9
+        tfs = wk["flop"] / (ms * 1e-3) * 1e-12
+        ent = {"ms": ms, "n": wk.get("n", n), "bound": wk["bound"], "algorithmic_bytes": wk["bytes"], "algorithmic_flop": wk["flop"],
+               "achieved_gbs": gbs, "achieved_tflops": tfs, "hbm_frac": gbs / hbm_peak, "fp32_frac": tfs / fp32_peak if fp32_peak else None}
+        out[k] = ent
+    return out, hbm_peak, fp32_peak, peak_src
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+    ctx = run_b200(args)
+    rank, world = ctx["rank"], ctx["world"]
+    kr, hbm_peak, fp32_peak, peak_src = kernel_rooflines(ctx, args)
+    if world > 1:
+        ctx["dist"].barrier()
+    if rank != 0:
+        if world > 1:
+            ctx["dist"].destroy_process_group()
+        return 0
+    dom = "K6_fused_score" if kr["K6_fused_score"]["ms"] >= kr["K1_gmm_sample"]["ms"] else "K1_gmm_sample"
+    d = kr[dom]
+    if d["bound"] == "hbm":
+        roof = {"kernel": dom, "bound": "hbm", "achieved": d["achieved_gbs"], "peak": hbm_peak, "unit": "GB/s",
+                "frac": d["hbm_frac"], "traffic": None, "peak_source": peak_src}
+    else:
+        roof = {"kernel": dom, "bound": "fp32", "achieved": d["achieved_tflops"], "peak": fp32_peak, "unit": "TFLOP/s",
+                "frac": d["fp32_frac"], "traffic": None,
+                "peak_source": "fp32 FMA rate measured live (mgb_fp32_fma_peak); SURVEY.md 8(d): K6 is compute-bound, "
+                               "its HBM fraction (%.3f of %s) is not the limiter" % (d["hbm_frac"], peak_src)}
+    out = {"metric": METRIC, "value": ctx["value"], "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+           "ms_per_step": ctx["total_ms"] / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+           "dtype": "f32", "data": "synthetic",
+           "config": {"workload": args.workload, "description": ctx["w"]["desc"], "candidates_per_gpu_per_step": ctx["n"],
+                      "l2": "flushed (384 MB fill, untimed) before every timed step", "parallelism": "candidates sharded x%d" % world},
+           "roofline": roof, "kernels": kr, "e2e": ctx["e2e"], "gpu_launches": ctx["launches"], "clocks": ctx["clocks"]}
+    if world == 1 and not args.no_cpu_baseline:
+        out["cpu_baseline"] = cpu_baseline_leg(args)
+    print(json.dumps(out))
+    if world > 1:
+        ctx["dist"].destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -168,6 +168,9 @@ int mgb_constraints_pack(const mgb_model* m, const mgb_constraint_desc* c, int32
                          mgb_constraints** out);
 void mgb_constraints_destroy(mgb_constraints* c);
 int32_t mgb_constraints_n_terms(const mgb_constraints* c);
+/* size of the compiled program: contracted channel quads, interpreter ops, evaluation times
+ * (used by bench.py to state the algorithmic flop of a launch) */
+int mgb_constraints_info(const mgb_constraints* c, int32_t* n_quads, int32_t* n_ops, int32_t* n_times);
 
 /* ---- kernels ---------------------------------------------------------- */
 
@@ -254,6 +257,10 @@ int mgb_kmeans_assign_update(const float* d_x, int64_t n, int32_t dim, int32_t l
                              const int32_t* d_node, const float* d_centroids, int32_t n_sub,
                              int32_t* d_label, float* d_sums, int32_t* d_counts,
                              float* d_inertia /* [1], accumulated */, void* stream);
+
+/* Diagnostic: measured fp32 FMA throughput (TFLOP/s) of `device`; the denominator of the
+ * compute-bound fused score kernel's roofline in bench.py (no reference counterpart). */
+int mgb_fp32_fma_peak(int32_t device, double* tflops);
 
 /* number of kernels this library has launched in this process (bench.py's gpu_launches) */
 int64_t mgb_launch_count(void);

@@ -83,6 +83,7 @@ SYMBOLS = {
                                        _pi32, _pd, C.POINTER(AlignDesc), C.POINTER(_vp)]),
     "mgb_constraints_destroy": (None, [_vp]),
     "mgb_constraints_n_terms": (_i32, [_vp]),
+    "mgb_constraints_info": (C.c_int, [_vp, _pi32, _pi32, _pi32]),
     "mgb_sample": (C.c_int, [_vp, _i64, _i64, C.POINTER(C.c_int64), C.c_uint64, _vp, _vp]),
     "mgb_score_workspace_bytes": (_sz, [_i64, _i32]),
     "mgb_score": (C.c_int, [_vp, _vp, _vp, _i32, _i64, _i64, _f, _f, _f, _vp, _vp, _i32, _vp, _vp, _vp, _sz, _vp]),
@@ -94,6 +95,7 @@ SYMBOLS = {
     "mgb_logpdf": (C.c_int, [_vp, _vp, _i64, _vp, _vp]),
     "mgb_topk": (C.c_int, [_vp, _i64, _i64, _i32, _vp, _vp, _vp, _sz, _vp]),
     "mgb_kmeans_assign_update": (C.c_int, [_vp, _i64, _i32, _i32, _vp, _vp, _i32, _vp, _vp, _vp, _vp, _vp]),
+    "mgb_fp32_fma_peak": (C.c_int, [_i32, _pd]),
     "mgb_launch_count": (C.c_int64, []),
     "mgb_last_error": (C.c_char_p, []),
     "mgb_version": (C.c_char_p, []),

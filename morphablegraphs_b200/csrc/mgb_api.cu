@@ -584,6 +584,14 @@ extern "C" void mgb_constraints_destroy(mgb_constraints* c) {
 
 extern "C" int32_t mgb_constraints_n_terms(const mgb_constraints* c) { return c ? c->n_terms : 0; }
 
+extern "C" int mgb_constraints_info(const mgb_constraints* c, int32_t* n_quads, int32_t* n_ops, int32_t* n_times) {
+    MGB_REQUIRE(c, "null handle");
+    if (n_quads) *n_quads = c->n_quads;
+    if (n_ops) *n_ops = c->n_ops;
+    if (n_times) *n_times = c->n_times;
+    return MGB_OK;
+}
+
 // ---------------------------------------------------------------------------
 // scoring entry points
 // ---------------------------------------------------------------------------

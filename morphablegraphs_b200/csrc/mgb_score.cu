@@ -656,7 +656,7 @@ int mgb_launch_score(const mgb_model* m, const mgb_constraints* c, const void* d
     MGB_REQUIRE(n >= 0, "negative n");
     MGB_REQUIRE(k >= 0 && k <= 64, "k must be in [0, 64]");
     const bool frames = d_frames != nullptr;
-    MGB_REQUIRE(frames || d_s, "d_s is NULL");
+    MGB_REQUIRE(frames || d_s || n == 0, "d_s is NULL");
     MGB_REQUIRE(!(frames && s_is_f64), "frames mode takes float32 s");
     if ((quality_scale != 0.f || magnitude_scale != 0.f) && frames) MGB_REQUIRE(d_s, "logpdf / magnitude need d_s");
     if (k > 0) {

@@ -6,6 +6,8 @@
 #include <float.h>
 #include <math.h>
 
+#include <algorithm>
+
 #include "mgb_internal.cuh"
 
 namespace {
@@ -234,23 +236,24 @@ struct FkStep {
 __global__ void __launch_bounds__(FK_BLOCK) mgb_fk_kernel(const float* __restrict__ frames, int P, long long n_frames, const FkStep* __restrict__ plan,
                                                          int n_plan, int n_out, float* __restrict__ pos) {
     extern __shared__ __align__(16) float smf[];
+    const int FKB = blockDim.x;  // frames per tile (<= FKB, chosen by the launcher to fit shared memory)
     const int SROW = P | 1;
-    float* sm_frames = smf;                                  // [FK_BLOCK][SROW]
-    float* sm_out = smf + (size_t)FK_BLOCK * SROW;           // [FK_BLOCK][n_out*3 | 1]
+    float* sm_frames = smf;                                  // [FKB][SROW]
+    float* sm_out = smf + (size_t)FKB * SROW;           // [FKB][n_out*3 | 1]
     const int OROW = (n_out * 3) | 1;
     __shared__ FkStep sm_plan[FK_MAX_PLAN];
-    for (int e = threadIdx.x; e < n_plan; e += FK_BLOCK) sm_plan[e] = plan[e];
-    const long long n_tiles = (n_frames + FK_BLOCK - 1) / FK_BLOCK;
+    for (int e = threadIdx.x; e < n_plan; e += FKB) sm_plan[e] = plan[e];
+    const long long n_tiles = (n_frames + FKB - 1) / FKB;
     for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-        const long long base = tile * FK_BLOCK;
+        const long long base = tile * FKB;
         __syncthreads();
         {
             const float* src = frames + base * P;
             const long long remaining = (n_frames - base) * (long long)P;
-            const int total = FK_BLOCK * P;
-            const int step_r = FK_BLOCK / P, step_c = FK_BLOCK % P;
+            const int total = FKB * P;
+            const int step_r = FKB / P, step_c = FKB % P;
             int r = threadIdx.x / P, c = threadIdx.x % P;
-            for (int e = threadIdx.x; e < total; e += FK_BLOCK) {
+            for (int e = threadIdx.x; e < total; e += FKB) {
                 sm_frames[r * SROW + c] = (e < remaining) ? __ldcs(src + e) : 0.f;
                 r += step_r;
                 c += step_c;
@@ -315,10 +318,10 @@ __global__ void __launch_bounds__(FK_BLOCK) mgb_fk_kernel(const float* __restric
             const int W = n_out * 3;
             float* dst = pos + base * W;
             const long long remaining = (n_frames - base) * (long long)W;
-            const int total = FK_BLOCK * W;
-            const int step_r = FK_BLOCK / W, step_c = FK_BLOCK % W;
+            const int total = FKB * W;
+            const int step_r = FKB / W, step_c = FKB % W;
             int r = threadIdx.x / W, c = threadIdx.x % W;
-            for (int e = threadIdx.x; e < total; e += FK_BLOCK) {
+            for (int e = threadIdx.x; e < total; e += FKB) {
                 if (e < remaining) __stcs(dst + e, sm_out[r * OROW + c]);
                 r += step_r;
                 c += step_c;
@@ -569,7 +572,12 @@ extern "C" int mgb_fk(const mgb_model* m, const float* d_frames, int64_t n_frame
     MGB_CUDA(cudaMallocAsync((void**)&d_plan, sizeof(FkStep) * plan.size(), stream));
     MGB_CUDA(cudaMemcpyAsync(d_plan, plan.data(), sizeof(FkStep) * plan.size(), cudaMemcpyHostToDevice, stream));
     MGB_CUDA(cudaStreamSynchronize(stream));
-    size_t smem = ((size_t)FK_BLOCK * (m->P | 1) + (size_t)FK_BLOCK * ((n_out * 3) | 1)) * sizeof(float);
+    int fkb = FK_BLOCK;
+    size_t smem = 0;
+    for (;; fkb >>= 1) {
+        smem = ((size_t)fkb * (m->P | 1) + (size_t)fkb * ((n_out * 3) | 1)) * sizeof(float);
+        if (smem <= 100 * 1024 || fkb == 32) break;
+    }
     MGB_REQUIRE(smem <= 200 * 1024, "frame tile too large for shared memory");
     static bool configured = false;
     if (!configured) {
@@ -577,11 +585,11 @@ extern "C" int mgb_fk(const mgb_model* m, const float* d_frames, int64_t n_frame
         configured = true;
     }
     int occ = 1;
-    MGB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, mgb_fk_kernel, FK_BLOCK, smem));
-    long long n_tiles = (n_frames + FK_BLOCK - 1) / FK_BLOCK;
+    MGB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, mgb_fk_kernel, fkb, smem));
+    long long n_tiles = (n_frames + fkb - 1) / fkb;
     long long grid = (long long)sm_count() * (occ > 0 ? occ : 1);
     if (grid > n_tiles) grid = n_tiles;
-    mgb_fk_kernel<<<(unsigned)grid, FK_BLOCK, smem, stream>>>(d_frames, m->P, n_frames, d_plan, (int)plan.size(), n_out, d_pos);
+    mgb_fk_kernel<<<(unsigned)grid, fkb, smem, stream>>>(d_frames, m->P, n_frames, d_plan, (int)plan.size(), n_out, d_pos);
     mgb_count_launch();
     MGB_CUDA(cudaGetLastError());
     MGB_CUDA(cudaFreeAsync(d_plan, stream));
@@ -623,5 +631,53 @@ extern "C" int mgb_kmeans_assign_update(const float* d_x, int64_t n, int32_t dim
     mgb_kmeans_kernel<<<(unsigned)grid, 256, 0, stream>>>(d_x, n, dim, ld, d_node, d_centroids, n_sub, d_label, d_sums, d_counts, d_inertia);
     mgb_count_launch();
     MGB_CUDA(cudaGetLastError());
+    return MGB_OK;
+}
+
+// ---------------------------------------------------------------------------
+// diagnostic: achievable fp32 FMA rate of this device (denominator of the
+// compute-bound fused score kernel's roofline)
+// ---------------------------------------------------------------------------
+namespace {
+__global__ void __launch_bounds__(256) mgb_fma_peak_kernel(float* out, int iters, float a, float b) {
+    float x[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) x[i] = (float)(threadIdx.x + i) * 1e-3f;
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int i = 0; i < 16; ++i) x[i] = fmaf(x[i], a, b);
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) s += x[i];
+    if (s == 123.456f) out[0] = s;  // never true in practice; keeps the chain alive
+}
+}  // namespace
+
+extern "C" int mgb_fp32_fma_peak(int32_t device, double* tflops) {
+    MGB_REQUIRE(tflops, "null argument");
+    MGB_CUDA(cudaSetDevice(device));
+    float* d = nullptr;
+    MGB_CUDA(cudaMalloc((void**)&d, sizeof(float)));
+    cudaEvent_t e0, e1;
+    MGB_CUDA(cudaEventCreate(&e0));
+    MGB_CUDA(cudaEventCreate(&e1));
+    const int iters = 4096, blocks = sm_count() * 8;
+    double best = 0.0;
+    for (int rep = 0; rep < 6; ++rep) {
+        MGB_CUDA(cudaEventRecord(e0, 0));
+        mgb_fma_peak_kernel<<<blocks, 256>>>(d, iters, 0.999f, 1e-3f);
+        MGB_CUDA(cudaEventRecord(e1, 0));
+        MGB_CUDA(cudaEventSynchronize(e1));
+        float ms = 0.f;
+        MGB_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+        const double fl = 2.0 * 16.0 * iters * 256.0 * blocks;
+        if (rep > 0 && ms > 0.f) best = std::max(best, fl / (ms * 1e-3) * 1e-12);
+    }
+    mgb_count_launch(6);
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    cudaFree(d);
+    *tflops = best;
     return MGB_OK;
 }

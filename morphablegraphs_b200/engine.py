@@ -215,7 +215,7 @@ class DeviceModel(object):
         rng = np.random.RandomState(None if seed is None else (int(seed) & 0x7FFFFFFF))
         return rng.multinomial(int(n_total), self.gmm_weights).astype(np.int64)
 
-    def sample(self, n, seed=0, index_base=0, counts=None, n_total=None):
+    def sample(self, n, seed=0, index_base=0, counts=None, n_total=None, out=None):
         """[n, D] float32 device tensor: global indices [index_base, index_base+n) of a job of
         n_total samples stacked in component order (motion_primitive.py:182-189)."""
         torch = _torch()
@@ -223,7 +223,8 @@ class DeviceModel(object):
         if counts is None:
             counts = self.component_counts(n_total, seed)
         counts = np.ascontiguousarray(counts, dtype=np.int64)
-        out = torch.empty((int(n), self.D), dtype=torch.float32, device=self.torch_device)
+        if out is None:
+            out = torch.empty((int(n), self.D), dtype=torch.float32, device=self.torch_device)
         with torch.cuda.device(self.device):
             _lib.check(self.lib.mgb_sample(self.handle, int(n), int(index_base), counts.ctypes.data_as(C.POINTER(C.c_int64)),
                                            C.c_uint64(int(seed) & 0xFFFFFFFFFFFFFFFF), C.c_void_p(out.data_ptr()), self._stream()))
@@ -434,6 +435,9 @@ class DeviceConstraints(object):
         _lib.check(self.lib.mgb_constraints_pack(dmodel.handle, descs, n, parr, n_points, _dptr(self.times), len(self.times),
                                                  _iptr(self.spans), _dptr(self.weights), C.byref(align), C.byref(h)))
         self.handle = h
+        nq, no, nt = C.c_int32(), C.c_int32(), C.c_int32()
+        _lib.check(self.lib.mgb_constraints_info(h, C.byref(nq), C.byref(no), C.byref(nt)))
+        self.n_quads, self.n_ops = nq.value, no.value
 
     def __del__(self):
         try:

@@ -24,45 +24,46 @@ import numpy as np
 _STATE = {}
 
 
-def build_case(shape="S"):
+def build_case(golden="s_config1", shape="S"):
+    """Same workload as bench.py's GPU arm: model from seeds, constraint list from the committed
+    golden fixture's specs."""
+    import json
     from morphablegraphs_b200 import synthetic as syn
     from morphablegraphs_b200 import Skeleton, MotionStateGraphNode, MotionPrimitiveConstraints, CONSTRAINT_FACTORY
     from oracle import np_oracle as O
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    g = np.load(os.path.join(root, "tests", "golden", golden + ".npz"), allow_pickle=False)
     cfg = syn.SHAPES[shape]
-    F = cfg["n_frames"]
     skeleton = Skeleton.from_desc(syn.make_skeleton_desc(cfg["n_joints"]))
     node = MotionStateGraphNode()
-    node._initialize_from_json(None, syn.make_model_json(shape))
+    node._initialize_from_json(None, syn.make_model_json(shape, translation_maxima=tuple(g["translation_maxima"])))
     ma = O.ModelArrays(node)
-    rng = np.random.RandomState(syn.SEED_CONSTRAINTS)
-    held, _ = O.gmm_sample(ma, 1, rng)
-    frame = O.eval_frames(ma, O.back_project_coeffs(ma, held), [F - 1.0])[:, 0, :]
-    target = O.fk_positions(skeleton, frame, ["RightFoot"])[0, 0].tolist()
     mpc = MotionPrimitiveConstraints()
     mpc.skeleton = skeleton
-    mpc.is_local = True
-    specs = [syn.spec("GlobalTransformConstraint", syn.position_constraint_desc("RightFoot", target, F - 1, F))]
-    mpc.constraints = syn.build_constraints(CONSTRAINT_FACTORY, skeleton, specs)
-    return node, skeleton, mpc, ma
+    mpc.is_local = bool(g["is_local"])
+    mpc.constraints = syn.build_constraints(CONSTRAINT_FACTORY, skeleton, json.loads(str(g["specs_json"])))
+    prev = g["prev_frames"] if "prev_frames" in g.files else None
+    return node, skeleton, mpc, ma, prev
 
 
-def _init(shape):
+def _init(golden, shape, quality_scale):
     os.environ.setdefault("OMP_NUM_THREADS", "1")
     os.environ.setdefault("OPENBLAS_NUM_THREADS", "1")
-    _STATE["case"] = build_case(shape)
+    _STATE["case"] = build_case(golden, shape)
+    _STATE["quality_scale"] = quality_scale
 
 
 def _work(args):
     from oracle import np_oracle as O
     seed, n, chunk = args
-    node, skeleton, mpc, ma = _STATE["case"]
+    node, skeleton, mpc, ma, prev = _STATE["case"]
     rng = np.random.RandomState(seed)
     best = (np.inf, -1)
     done = 0
     while done < n:
         m = min(chunk, n - done)
         S, _ = O.gmm_sample(ma, m, rng)
-        cost = O.candidate_costs(ma, skeleton, mpc, S)
+        cost = O.candidate_costs(ma, skeleton, mpc, S, prev, quality_scale=_STATE["quality_scale"])
         i, e = O.first_argmin(cost)
         if e < best[0]:
             best = (e, done + i)
@@ -73,10 +74,10 @@ def _work(args):
 class Pool(object):
     """Persistent worker pool so that process start-up is outside the timed region."""
 
-    def __init__(self, shape="S", workers=None):
+    def __init__(self, golden="s_config1", shape="S", quality_scale=0.0, workers=None):
         self.workers = workers or os.cpu_count() or 1
         ctx = mp.get_context("spawn")
-        self.pool = ctx.Pool(self.workers, initializer=_init, initargs=(shape,))
+        self.pool = ctx.Pool(self.workers, initializer=_init, initargs=(golden, shape, quality_scale))
         # make sure every worker has finished its initialiser
         self.pool.map(_work, [(i, 64, 64) for i in range(self.workers * 2)])
 
@@ -102,10 +103,10 @@ class Pool(object):
         self.pool.join()
 
 
-def loop_port_rate(shape="S", n=1500, seed=3):
-    """candidates/s of the per-candidate loop port on one core."""
+def loop_port_rate(golden="s_config1", shape="S", n=1500, seed=3):
+    """candidates/s of the per-candidate loop port on one core (one position constraint)."""
     from oracle import np_oracle as O
-    node, skeleton, mpc, ma = build_case(shape)
+    node, skeleton, mpc, ma, _ = build_case(golden, shape)
     S, _ = O.gmm_sample(ma, n, np.random.RandomState(seed))
     t0 = time.perf_counter()
     O.loop_evaluate_one_position(ma, skeleton, mpc.constraints[0], S)
