@@ -203,6 +203,15 @@ int mgb_score(const mgb_model* m, const mgb_constraints* c, const void* d_s, int
               float* d_best_cost, int64_t* d_best_idx, void* d_workspace,
               size_t workspace_bytes, void* stream);
 
+/* Fused K1 + K6: candidates [index_base, index_base + n) of a job drawn in-kernel (exactly the
+ * rows mgb_sample writes for the same h_counts / seed) and scored without ever being stored:
+ * _get_best_fit_sample_using_gmm (motion_primitive_generator.py:192-206) in one launch.  The
+ * caller regenerates the winning row with mgb_sample(n = 1, index_base = best_idx). */
+int mgb_sample_score(const mgb_model* m, const mgb_constraints* c, int64_t n, int64_t index_base,
+                     const int64_t* h_counts, uint64_t seed, float err_scale, float quality_scale,
+                     float magnitude_scale, float* d_cost /*[n] or NULL*/, int32_t k, float* d_best_cost,
+                     int64_t* d_best_idx, void* d_workspace, size_t workspace_bytes, void* stream);
+
 /* Same through HOST buffers (pageable or pinned): chunked H2D on a copy stream
  * overlapped with scoring, D2H of the k results; synchronous.  This is the
  * call the reference-side shim makes with the numpy array it already holds. */

@@ -87,6 +87,7 @@ SYMBOLS = {
     "mgb_sample": (C.c_int, [_vp, _i64, _i64, C.POINTER(C.c_int64), C.c_uint64, _vp, _vp]),
     "mgb_score_workspace_bytes": (_sz, [_i64, _i32]),
     "mgb_score": (C.c_int, [_vp, _vp, _vp, _i32, _i64, _i64, _f, _f, _f, _vp, _vp, _i32, _vp, _vp, _vp, _sz, _vp]),
+    "mgb_sample_score": (C.c_int, [_vp, _vp, _i64, _i64, C.POINTER(C.c_int64), C.c_uint64, _f, _f, _f, _vp, _i32, _vp, _vp, _vp, _sz, _vp]),
     "mgb_score_host": (C.c_int, [_vp, _vp, _vp, _i32, _i64, _i64, _f, _f, _f, _vp, _i32, _vp, _vp]),
     "mgb_backproject": (C.c_int, [_vp, _vp, _i64, _vp, _i32, _vp]),
     "mgb_eval_frames": (C.c_int, [_vp, _vp, _i64, _pd, _i32, _pi32, _pd, _vp, _vp]),

@@ -145,6 +145,7 @@ extern "C" int mgb_model_create(const mgb_model_desc* d, int device, mgb_model**
     m->channel.assign(d->node_channel, d->node_channel + d->n_nodes);
     m->offset.assign(d->node_offset, d->node_offset + 3 * d->n_nodes);
     m->fixed_rot.resize((size_t)9 * d->n_nodes);
+    m->fixed_quat.resize((size_t)4 * d->n_nodes);
     m->children.assign(d->n_nodes, std::vector<int>());
     int n_root = 0;
     for (int i = 0; i < d->n_nodes; ++i) {
@@ -164,6 +165,13 @@ extern "C" int mgb_model_create(const mgb_model_desc* d, int device, mgb_model**
             return MGB_E_INVALID;
         }
         quat_matrix_d(d->node_rotation + 4 * i, &m->fixed_rot[(size_t)9 * i]);
+        {
+            const double* q = d->node_rotation + 4 * i;
+            const double nq = q[0] * q[0] + q[1] * q[1] + q[2] * q[2] + q[3] * q[3];
+            const double inv = nq < 8.881784197001252e-16 ? 0.0 : 1.0 / sqrt(nq);
+            m->fixed_quat[(size_t)4 * i + 0] = inv == 0.0 ? 1.0 : q[0] * inv;
+            for (int c = 1; c < 4; ++c) m->fixed_quat[(size_t)4 * i + c] = inv == 0.0 ? 0.0 : q[c] * inv;
+        }
     }
     if (n_root != 1 || m->parent[0] >= 0 || m->type[0] != MGB_NODE_ROOT) {
         mgb_set_error("skeleton must have exactly one root, at index 0, of type MGB_NODE_ROOT");
@@ -175,8 +183,12 @@ extern "C" int mgb_model_create(const mgb_model_desc* d, int device, mgb_model**
 
     // GMM: precision Cholesky (sklearn _compute_precision_cholesky, 'full'), per-component constant
     m->NQ = (D + 3) / 4;
-    std::vector<float4> gtab((size_t)G * m->NQ * (D + 1));
-    std::vector<float> gc(G), chol((size_t)G * D * D), means((size_t)G * D);
+    m->DP = (D + 3) & ~3;
+    const int DP = m->DP;
+    std::vector<float4> gtab((size_t)G * m->NQ * (DP + 1), make_float4(0.f, 0.f, 0.f, 0.f));
+    m->LS = (D + 3) & ~3;
+    const int LS = m->LS;
+    std::vector<float> gc(G), chol((size_t)G * D * LS, 0.f), means((size_t)G * D);
     std::vector<double> L, Pc((size_t)D * D);
     for (int g = 0; g < G; ++g) {
         if (!cholesky_lower(d->gmm_covars + (size_t)g * D * D, D, L)) {
@@ -198,24 +210,22 @@ extern "C" int mgb_model_create(const mgb_model_desc* d, int device, mgb_model**
         gc[g] = (float)(log(d->gmm_weights[g]) + logdet - 0.5 * D * log(2.0 * M_PI));
         const double* mu = d->gmm_means + (size_t)g * D;
         for (int q = 0; q < m->NQ; ++q) {
-            float4* row = &gtab[(size_t)(g * m->NQ + q) * (D + 1)];
+            float4* row = &gtab[(size_t)(g * m->NQ + q) * (DP + 1)];
             double bias[4] = {0, 0, 0, 0};
-            for (int k = 0; k <= D; ++k) {
+            for (int k = 0; k < D; ++k) {
                 float v[4] = {0, 0, 0, 0};
                 for (int c = 0; c < 4; ++c) {
                     const int j = 4 * q + c;
                     if (j >= D) continue;
-                    if (k < D) {
-                        v[c] = (float)Pc[(size_t)k * D + j];
-                        bias[c] -= mu[k] * Pc[(size_t)k * D + j];
-                    } else {
-                        v[c] = (float)bias[c];
-                    }
+                    v[c] = (float)Pc[(size_t)k * D + j];
+                    bias[c] -= mu[k] * Pc[(size_t)k * D + j];
                 }
-                row[k] = make_float4(v[0], v[1], v[2], v[3]);
+                row[1 + k] = make_float4(v[0], v[1], v[2], v[3]);
             }
+            row[0] = make_float4((float)bias[0], (float)bias[1], (float)bias[2], (float)bias[3]);
         }
-        for (int i = 0; i < D * D; ++i) chol[(size_t)g * D * D + i] = (float)L[i];
+        for (int i = 0; i < D; ++i)
+            for (int j = 0; j <= i; ++j) chol[((size_t)g * D + i) * LS + j] = (float)L[(size_t)i * D + j];
         for (int i = 0; i < D; ++i) means[(size_t)g * D + i] = (float)mu[i];
     }
     m->gmm_tab_bytes = gtab.size() * sizeof(float4);
@@ -312,14 +322,14 @@ struct Compiler {
         } else if (type == MGB_NODE_JOINT && m->channel[node] >= 0) {
             op(OP_JOINT, quad(slot, m->channel[node]), 0, {(float)off[0], (float)off[1], (float)off[2]});
         } else {
-            std::vector<float> v(12);
+            std::vector<float> v(7);
             bool ident = true;
-            for (int i = 0; i < 9; ++i) {
-                double r = (type == MGB_NODE_END_SITE) ? ((i % 4 == 0) ? 1.0 : 0.0) : m->fixed_rot[(size_t)9 * node + i];
+            for (int i = 0; i < 4; ++i) {
+                const double r = (type == MGB_NODE_END_SITE) ? (i == 0 ? 1.0 : 0.0) : m->fixed_quat[(size_t)4 * node + i];
                 v[i] = (float)r;
-                if (fabs(r - ((i % 4 == 0) ? 1.0 : 0.0)) > 0.0) ident = false;
+                if (fabs(fabs(r) - (i == 0 ? 1.0 : 0.0)) > 0.0) ident = false;
             }
-            for (int i = 0; i < 3; ++i) v[9 + i] = (float)off[i];
+            for (int i = 0; i < 3; ++i) v[4 + i] = (float)off[i];
             op(OP_CONST, ident ? 1 : 0, 0, v);
         }
         auto it = attach[slot].find(node);
@@ -518,7 +528,9 @@ extern "C" int mgb_constraints_pack(const mgb_model* m, const mgb_constraint_des
     c->n_terms = n;
     c->n_times = n_times;
     c->n_quads = (int)C.quads.size();
-    c->tab.assign((size_t)c->n_quads * (K + 1) * 4, 0.f);
+    const int KP = (K + 3) & ~3;  // rows padded with zeros to a multiple of 4; entry 0 of a quad is the bias (mean) row
+    c->KP = KP;
+    c->tab.assign((size_t)c->n_quads * (KP + 1) * 4, 0.f);
     for (int q = 0; q < c->n_quads; ++q) {
         const int slot = C.quads[q].first, group = C.quads[q].second;
         const int ch0 = group < 0 ? 0 : 3 + 4 * group;
@@ -531,7 +543,8 @@ extern "C" int mgb_constraints_pack(const mgb_model* m, const mgb_constraint_des
                     const double basis = (k < K) ? m->E[(size_t)k * M + col] : m->mean[col];
                     acc += C.weights[4 * slot + i] * basis;
                 }
-                c->tab[((size_t)q * (K + 1) + k) * 4 + ch] = (float)acc;
+                const int row = (k < K) ? 1 + k : 0;
+                c->tab[((size_t)q * (KP + 1) + row) * 4 + ch] = (float)acc;
             }
         }
     }
@@ -565,7 +578,7 @@ extern "C" int mgb_constraints_pack(const mgb_model* m, const mgb_constraint_des
 
     MGB_CUDA(cudaSetDevice(m->device));
     int rc = MGB_OK;
-    std::vector<float4> tab4((size_t)c->n_quads * (K + 1));
+    std::vector<float4> tab4((size_t)c->n_quads * (KP + 1));
     for (size_t i = 0; i < tab4.size(); ++i) tab4[i] = make_float4(c->tab[4 * i], c->tab[4 * i + 1], c->tab[4 * i + 2], c->tab[4 * i + 3]);
     if ((rc = upload(&c->d_tab, tab4)) || (rc = upload(&c->d_ops_fused, c->ops_fused)) || (rc = upload(&c->d_ops_frames, c->ops_frames)) ||
         (rc = upload(&c->d_cst, c->cst))) {
@@ -598,8 +611,24 @@ extern "C" int mgb_constraints_info(const mgb_constraints* c, int32_t* n_quads, 
 extern "C" int mgb_score(const mgb_model* m, const mgb_constraints* c, const void* d_s, int32_t s_is_f64, int64_t n, int64_t index_base,
                          float err_scale, float quality_scale, float magnitude_scale, float* d_cost, float* d_terms, int32_t k,
                          float* d_best_cost, int64_t* d_best_idx, void* d_workspace, size_t workspace_bytes, void* stream) {
-    return mgb_launch_score(m, c, d_s, s_is_f64, nullptr, n, index_base, err_scale, quality_scale, magnitude_scale, d_cost, d_terms, k,
-                            d_best_cost, d_best_idx, d_workspace, workspace_bytes, (cudaStream_t)stream);
+    MGB_REQUIRE(c, "null constraints handle");
+    return mgb_launch_score(m, c, 0, d_s, s_is_f64, nullptr, nullptr, 0, n, index_base, err_scale, quality_scale, magnitude_scale, d_cost,
+                            d_terms, k, d_best_cost, d_best_idx, d_workspace, workspace_bytes, (cudaStream_t)stream);
+}
+
+extern "C" int mgb_sample_score(const mgb_model* m, const mgb_constraints* c, int64_t n, int64_t index_base, const int64_t* h_counts,
+                                uint64_t seed, float err_scale, float quality_scale, float magnitude_scale, float* d_cost, int32_t k,
+                                float* d_best_cost, int64_t* d_best_idx, void* d_workspace, size_t workspace_bytes, void* stream) {
+    MGB_REQUIRE(c, "null constraints handle");
+    return mgb_launch_score(m, c, 2, nullptr, 0, nullptr, h_counts, seed, n, index_base, err_scale, quality_scale, magnitude_scale, d_cost,
+                            nullptr, k, d_best_cost, d_best_idx, d_workspace, workspace_bytes, (cudaStream_t)stream);
+}
+
+extern "C" int mgb_logpdf(const mgb_model* m, const float* d_s, int64_t n, float* d_logpdf, void* stream) {
+    MGB_REQUIRE(m && (n == 0 || (d_s && d_logpdf)), "null argument");
+    // the score kernel with an empty program: cost = quality_scale * (-log p(s)) with quality_scale = -1
+    return mgb_launch_score(m, nullptr, 0, d_s, 0, nullptr, nullptr, 0, n, 0, 0.f, -1.f, 0.f, d_logpdf, nullptr, 0, nullptr, nullptr, nullptr, 0,
+                            (cudaStream_t)stream);
 }
 
 extern "C" int mgb_score_frames(const mgb_model* m, const mgb_constraints* c, const float* d_frames, const float* d_s, int64_t n,
@@ -609,8 +638,8 @@ extern "C" int mgb_score_frames(const mgb_model* m, const mgb_constraints* c, co
     MGB_REQUIRE(d_frames, "d_frames is NULL");
     MGB_REQUIRE(c && (c->n_ops == 0 || !c->ops_frames.empty()),
                 "this constraint set needs control point 0 (alignment): include time 0 in the packed times to score from frames");
-    return mgb_launch_score(m, c, d_s, 0, d_frames, n, index_base, err_scale, quality_scale, magnitude_scale, d_cost, d_terms, k,
-                            d_best_cost, d_best_idx, d_workspace, workspace_bytes, (cudaStream_t)stream);
+    return mgb_launch_score(m, c, 1, d_s, 0, d_frames, nullptr, 0, n, index_base, err_scale, quality_scale, magnitude_scale, d_cost, d_terms,
+                            k, d_best_cost, d_best_idx, d_workspace, workspace_bytes, (cudaStream_t)stream);
 }
 
 static std::mutex g_host_mutex;
@@ -688,9 +717,9 @@ extern "C" int mgb_score_host(const mgb_model* m_, const mgb_constraints* c, con
         }
         MGB_CUDA(cudaEventRecord(m->ev_copied[b], m->copy_stream));
         MGB_CUDA(cudaStreamWaitEvent(m->compute_stream, m->ev_copied[b], 0));
-        int rc = mgb_launch_score(m, c, m->d_stage[b], s_is_f64, nullptr, cnt, index_base + lo, err_scale, quality_scale, magnitude_scale,
-                                  d_cost ? d_cost + lo : nullptr, nullptr, (k >= 1) ? 1 : 0, d_bc + ch, d_bi + ch, ws, ws_score,
-                                  m->compute_stream);
+        int rc = mgb_launch_score(m, c, 0, m->d_stage[b], s_is_f64, nullptr, nullptr, 0, cnt, index_base + lo, err_scale, quality_scale,
+                                  magnitude_scale, d_cost ? d_cost + lo : nullptr, nullptr, (k >= 1) ? 1 : 0, d_bc + ch, d_bi + ch, ws,
+                                  ws_score, m->compute_stream);
         if (rc != MGB_OK) return rc;
         MGB_CUDA(cudaEventRecord(m->ev_done[b], m->compute_stream));
     }

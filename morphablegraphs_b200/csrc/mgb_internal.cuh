@@ -45,7 +45,7 @@ struct MgbOp {
 enum MgbOpCode : int32_t {
     OP_ROOT = 0,      // a = translation quad, b = rotation quad, c -> root offset[3]
     OP_JOINT = 1,     // a = rotation quad, c -> offset[3]
-    OP_CONST = 2,     // a = 1 if rotation is identity, c -> R[9], t[3]
+    OP_CONST = 2,     // a = 1 if rotation is identity, c -> unit quaternion[4], offset[3]
     OP_PUSH = 3,
     OP_POP = 4,
     OP_ALIGN = 5,     // a = translation quad of control point 0, c -> ref_dir[3], prev heading(rad), prev x, prev z
@@ -80,15 +80,18 @@ struct mgb_model {
     std::vector<int> parent, type, channel;
     std::vector<double> offset;    // [n_nodes][3]
     std::vector<double> fixed_rot; // [n_nodes][9] rotation matrix of fixed joints (identity otherwise)
+    std::vector<double> fixed_quat; // [n_nodes][4] the same as a unit quaternion (identity below eps)
     std::vector<std::vector<int>> children;
     // device fp32
     float* d_E = nullptr;     // [K][M]
     float* d_mean = nullptr;  // [M]
     // GMM
     int NQ = 0;               // quads per component = ceil(D/4)
-    float4* d_gmm_tab = nullptr;  // [(g*NQ + q) * (D+1) + k]: k<D -> P_g[k][4q..4q+3], k==D -> -(mu_g P_g)[4q..]
+    int DP = 0;               // D rounded up to a multiple of 4
+    float4* d_gmm_tab = nullptr;  // [(g*NQ + q) * (DP+1) + r]: r = 0 -> -(mu_g P_g)[4q..4q+3], r = 1+k -> P_g[k][4q..4q+3] (zero for k >= D)
     float* d_gmm_c = nullptr;     // [G]  log w_g + log det - D/2 log 2 pi
-    float* d_chol = nullptr;      // [G][D][D] lower Cholesky of the covariances (sampling)
+    int LS = 0;                   // row stride of d_chol = D rounded up to a multiple of 4
+    float* d_chol = nullptr;      // [G][D][LS] lower Cholesky of the covariances (sampling), rows 16-byte aligned
     float* d_means = nullptr;     // [G][D]
     size_t gmm_tab_bytes = 0;
     // skeleton on device for the FK kernel
@@ -117,11 +120,12 @@ struct mgb_constraints {
     int n_quads = 0;
     int n_ops = 0;
     int n_cst = 0;
+    int KP = 0;  // K rounded up to a multiple of 4: quad q occupies tab[q * (KP + 1) ...], bias first
     bool needs_s = false;  // program itself never needs s beyond K; logpdf/magnitude decided per call
     std::vector<MgbOp> ops_fused;   // quads index the contracted table
     std::vector<MgbOp> ops_frames;  // quads index channels of materialised frames: slot * P + channel
     std::vector<float> cst;
-    std::vector<float> tab;  // [n_quads][K+1][4]
+    std::vector<float> tab;  // [n_quads][KP+1][4]
     std::vector<double> times;
     std::vector<int> spans;
     std::vector<double> weights;
@@ -131,24 +135,39 @@ struct mgb_constraints {
     float* d_cst = nullptr;
 };
 
+#define MGB_MAX_GMM 64
+struct MgbGmmPrefix {  // job-wide prefix sums of the per-component sample counts (component-ordered stacking)
+    long long v[MGB_MAX_GMM + 1];
+};
+
 // device-side view handed to the score kernels by value
 struct ScoreParams {
-    const float4* tab;  // fused: contracted quads
+    const float4* tab;  // contracted quads [n_quads][1 + KP]
     const MgbOp* ops;
     const float* cst;
     int n_ops, n_cst, n_quads;
-    int K, D, P, n_times;
+    int K, KP, D, DP, P, n_times;
     int n_terms;
-    // GMM
-    const float4* gmm_tab;
+    // GMM log-density
+    const float4* gmm_tab;  // [(g * NQ + q)][1 + DP]
     const float* gmm_c;
     int G, NQ;
     int gmm_in_smem;
+    int tab_in_smem;
+    // GMM sampling (MODE_SAMPLE)
+    const float* chol;   // [G][D][LS]
+    const float* means;  // [G][D]
+    int LS;
+    int chol_in_smem;
+    unsigned long long seed;
+    MgbGmmPrefix prefix;
     // inputs
     const void* s;        // [n, D] float or double
     const float* frames;  // frames mode: [n, n_times, P]
     long long n;
     long long index_base;
+    int s_aligned;        // s is 16-byte aligned: full tiles travel by TMA bulk copy
+    int nbuf;             // tile buffers in shared memory (2 = double-buffered)
     float err_scale, quality_scale, magnitude_scale;
     float* cost;
     float* terms;
@@ -159,12 +178,12 @@ struct ScoreParams {
     unsigned int* done_count;  // [1]
     float* best_cost;
     long long* best_idx;
-    int tab_in_smem;
 };
 
 // launchers implemented in the kernel translation units
-int mgb_launch_score(const mgb_model* m, const mgb_constraints* c, const void* d_s, int s_is_f64,
-                     const float* d_frames, int64_t n, int64_t index_base, float err_scale,
+// mode: 0 = candidates from d_s, 1 = from materialised frames, 2 = sampled in-kernel (h_counts, seed)
+int mgb_launch_score(const mgb_model* m, const mgb_constraints* c, int mode, const void* d_s, int s_is_f64,
+                     const float* d_frames, const int64_t* h_counts, uint64_t seed, int64_t n, int64_t index_base, float err_scale,
                      float quality_scale, float magnitude_scale, float* d_cost, float* d_terms, int k,
                      float* d_best_cost, int64_t* d_best_idx, void* d_ws, size_t ws_bytes,
                      cudaStream_t stream);

@@ -1,15 +1,17 @@
-// K6 / K5a: fused keyframe score kernels (sm_100a).
+// K6 / K5a / fused K1+K6: keyframe score kernels (sm_100a).
 //
-// One thread scores one candidate.  The constraint list was compiled by
+// One thread scores CPT candidates.  The constraint list was compiled by
 // mgb_constraints_pack into (a) a table of "quads": for every constrained time
 // slot and every needed group of 4 pose channels (root translation, one joint
 // quaternion) the spatial basis pre-contracted with that slot's 4 B-spline
-// weights, laid out [quad][k][4] so one 16-byte broadcast load feeds 4 FMAs, and
+// weights, laid out [quad][1 + KP] float4 (bias row first, K rows zero-padded to
+// a multiple of 4) so one 16-byte broadcast load feeds 4 FMAs per candidate, and
 // (b) a small op program: a depth-first walk over the needed part of the
-// skeleton (forward kinematics with a 3x4 transform held in registers) with the
+// skeleton (forward kinematics in quaternion form, 8 floats of state) with the
 // constraint terms attached to the nodes they read.
 //
 // What it replaces in the reference, per candidate:
+//   GaussianMixture.sample (MODE_SAMPLE)          motion_primitive.py:182-189
 //   MotionPrimitive.back_project_spatial_coeffs   motion_primitive.py:236-256
 //   MotionSpline.evaluate (P splev calls)         motion_spline.py:89-92
 //   anim_utils SkeletonNode.get_global_matrix     (call sites global_transform_constraint.py:103 ...)
@@ -18,113 +20,33 @@
 //   + 2|s|                                        mg_state_planner.py:110-129
 //   first-minimum arg-min                         motion_primitive_generator.py:251-257
 //
-// Memory: s tile staged through shared memory with coalesced 128-bit loads
-// (rows are D floats = 52 B at the small shape, so a thread-per-row global read
-// would touch 13 lines per request); quad table, op program and constants are
-// copied to shared memory once per CTA (persistent, grid-stride over tiles);
-// block arg-min by warp shuffles, last-arriving CTA folds the per-CTA partials.
+// Memory: MODE_S reads the candidate tile (a contiguous run of TILE*D elements)
+// with ONE 1-D TMA bulk copy per tile into shared memory, double-buffered on
+// mbarriers so the next tile lands while the current one is scored; MODE_SAMPLE
+// draws the latent vector in registers (Philox keyed by the global index) and
+// touches no HBM at all; quad table, GMM table, op program and constants are
+// staged in shared memory once per persistent CTA; block arg-min by warp
+// shuffles, last-arriving CTA folds the per-CTA partials.
 #include <float.h>
 #include <math.h>
+#include <stdlib.h>
 
+#include <type_traits>
+
+#include "mgb_device.cuh"
 #include "mgb_internal.cuh"
 
 #define MGB_BLOCK 256
-#define MGB_QUAT_EPS 8.881784197001252e-16f /* 4 * DBL_EPSILON, transformations.quaternion_matrix */
+
+enum { MODE_S = 0, MODE_FRAMES = 1, MODE_SAMPLE = 2 };
 
 namespace {
 
-struct Xf {
-    float R[9];
-    float t[3];
-};
-
-__device__ __forceinline__ void quat_to_R(float w, float x, float y, float z, float* R) {
-    float n = w * w + x * x + y * y + z * z;
-    if (n < MGB_QUAT_EPS) {
-        R[0] = 1.f; R[1] = 0.f; R[2] = 0.f;
-        R[3] = 0.f; R[4] = 1.f; R[5] = 0.f;
-        R[6] = 0.f; R[7] = 0.f; R[8] = 1.f;
-        return;
-    }
-    float s = __fdividef(2.0f, n);
-    float xs = x * s, ys = y * s, zs = z * s;
-    float wx = w * xs, wy = w * ys, wz = w * zs;
-    float xx = x * xs, xy = x * ys, xz = x * zs;
-    float yy = y * ys, yz = y * zs, zz = z * zs;
-    R[0] = 1.f - (yy + zz); R[1] = xy - wz;         R[2] = xz + wy;
-    R[3] = xy + wz;         R[4] = 1.f - (xx + zz); R[5] = yz - wx;
-    R[6] = xz - wy;         R[7] = yz + wx;         R[8] = 1.f - (xx + yy);
-}
-
-// G = G * [Rl | tl]
-__device__ __forceinline__ void xf_mul(Xf& G, const float* Rl, float tx, float ty, float tz) {
-    G.t[0] = fmaf(G.R[0], tx, fmaf(G.R[1], ty, fmaf(G.R[2], tz, G.t[0])));
-    G.t[1] = fmaf(G.R[3], tx, fmaf(G.R[4], ty, fmaf(G.R[5], tz, G.t[1])));
-    G.t[2] = fmaf(G.R[6], tx, fmaf(G.R[7], ty, fmaf(G.R[8], tz, G.t[2])));
-    float N[9];
-#pragma unroll
-    for (int i = 0; i < 3; ++i) {
-#pragma unroll
-        for (int j = 0; j < 3; ++j) {
-            N[i * 3 + j] = fmaf(G.R[i * 3 + 0], Rl[0 + j], fmaf(G.R[i * 3 + 1], Rl[3 + j], G.R[i * 3 + 2] * Rl[6 + j]));
-        }
-    }
-#pragma unroll
-    for (int i = 0; i < 9; ++i) G.R[i] = N[i];
-}
-
-__device__ __forceinline__ void xf_translate(Xf& G, float tx, float ty, float tz) {
-    G.t[0] = fmaf(G.R[0], tx, fmaf(G.R[1], ty, fmaf(G.R[2], tz, G.t[0])));
-    G.t[1] = fmaf(G.R[3], tx, fmaf(G.R[4], ty, fmaf(G.R[5], tz, G.t[1])));
-    G.t[2] = fmaf(G.R[6], tx, fmaf(G.R[7], ty, fmaf(G.R[8], tz, G.t[2])));
-}
-
-#define MGB_FMA4(k)                                  \
-    {                                                \
-        float4 e = row[k];                           \
-        acc.x = fmaf(s[k], e.x, acc.x);              \
-        acc.y = fmaf(s[k], e.y, acc.y);              \
-        acc.z = fmaf(s[k], e.z, acc.z);              \
-        acc.w = fmaf(s[k], e.w, acc.w);              \
-    }
-#define MGB_CASE(k) \
-    case (k) + 1:   \
-        if ((k) < NREG) MGB_FMA4((k) < NREG ? (k) : 0)
-
-// acc = row[bias] + sum_{k < cnt} s[k] * row[k]; s lives in registers, the
-// runtime count is dispatched once through a fall-through switch
-template <int NREG>
-__device__ __forceinline__ float4 dotquad_reg(const float4* __restrict__ row, int bias, int cnt, const float (&s)[NREG > 0 ? NREG : 1]) {
-    float4 acc = row[bias];
-    switch (cnt) {
-        MGB_CASE(31) MGB_CASE(30) MGB_CASE(29) MGB_CASE(28) MGB_CASE(27) MGB_CASE(26) MGB_CASE(25) MGB_CASE(24)
-        MGB_CASE(23) MGB_CASE(22) MGB_CASE(21) MGB_CASE(20) MGB_CASE(19) MGB_CASE(18) MGB_CASE(17) MGB_CASE(16)
-        MGB_CASE(15) MGB_CASE(14) MGB_CASE(13) MGB_CASE(12) MGB_CASE(11) MGB_CASE(10) MGB_CASE(9) MGB_CASE(8)
-        MGB_CASE(7) MGB_CASE(6) MGB_CASE(5) MGB_CASE(4) MGB_CASE(3) MGB_CASE(2) MGB_CASE(1) MGB_CASE(0)
-        default: break;
-    }
-    return acc;
-}
-
-// same with s read from the thread's shared-memory row (large D)
-__device__ __forceinline__ float4 dotquad_smem(const float4* __restrict__ row, int bias, int cnt, const float* __restrict__ s) {
-    float4 acc = row[bias];
-    for (int k = 0; k < cnt; ++k) {
-        float4 e = row[k];
-        float sk = s[k];
-        acc.x = fmaf(sk, e.x, acc.x);
-        acc.y = fmaf(sk, e.y, acc.y);
-        acc.z = fmaf(sk, e.z, acc.z);
-        acc.w = fmaf(sk, e.w, acc.w);
-    }
-    return acc;
-}
-
-__device__ __forceinline__ float masked_dist(unsigned mask, const float* tgt, const float* p) {
+__device__ __forceinline__ float masked_dist(unsigned mask, const float* tgt, float px, float py, float pz) {
     float d = 0.f;
-    if (mask & 1u) { float e = tgt[0] - p[0]; d = fmaf(e, e, d); }
-    if (mask & 2u) { float e = tgt[1] - p[1]; d = fmaf(e, e, d); }
-    if (mask & 4u) { float e = tgt[2] - p[2]; d = fmaf(e, e, d); }
+    if (mask & 1u) { float e = tgt[0] - px; d = fmaf(e, e, d); }
+    if (mask & 2u) { float e = tgt[1] - py; d = fmaf(e, e, d); }
+    if (mask & 4u) { float e = tgt[2] - pz; d = fmaf(e, e, d); }
     return sqrtf(d);
 }
 
@@ -137,113 +59,225 @@ __device__ __forceinline__ bool better(float c1, long long i1, float c2, long lo
     return (c1 < c2) || (c1 == c2 && i1 < i2);
 }
 
+// acc[c] = row[0] + sum_{k < 4 * chunks} s[c][k] * row[1 + k]; s in registers
+template <int NREG, int CPT>
+__device__ __forceinline__ void dot_rows_reg(const float4* __restrict__ row, int chunks, const float (&s)[CPT][NREG > 0 ? NREG : 1],
+                                             float4 (&acc)[CPT]) {
+    const float4 b = row[0];
+#pragma unroll
+    for (int c = 0; c < CPT; ++c) acc[c] = b;
+#pragma unroll
+    for (int j = 0; j < NREG / 4; ++j) {
+        if (j >= chunks) break;
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk) {
+            const float4 e = row[1 + 4 * j + kk];
+#pragma unroll
+            for (int c = 0; c < CPT; ++c) {
+                const float sk = s[c][4 * j + kk];
+                acc[c].x = fmaf(sk, e.x, acc[c].x);
+                acc[c].y = fmaf(sk, e.y, acc[c].y);
+                acc[c].z = fmaf(sk, e.z, acc[c].z);
+                acc[c].w = fmaf(sk, e.w, acc[c].w);
+            }
+        }
+    }
+}
+
+// same with s read from memory (candidate row pointers), any D; rows beyond D are zero in the table
+template <int CPT, typename ST>
+__device__ __forceinline__ void dot_rows_mem(const float4* __restrict__ row, int cnt, const ST* (&srow)[CPT], float4 (&acc)[CPT]) {
+    const float4 b = row[0];
+#pragma unroll
+    for (int c = 0; c < CPT; ++c) acc[c] = b;
+    for (int k = 0; k < cnt; ++k) {
+        const float4 e = row[1 + k];
+#pragma unroll
+        for (int c = 0; c < CPT; ++c) {
+            const float sk = (float)srow[c][k];
+            acc[c].x = fmaf(sk, e.x, acc[c].x);
+            acc[c].y = fmaf(sk, e.y, acc[c].y);
+            acc[c].z = fmaf(sk, e.z, acc[c].z);
+            acc[c].w = fmaf(sk, e.w, acc[c].w);
+        }
+    }
+}
+
 // ---------------------------------------------------------------------------
-// NREG > 0 : the whole latent vector s lives in registers (D <= NREG)
-// NREG == 0: s stays in the shared-memory tile (any D)
-// FRAMES   : pose channels come from materialised frames instead of the
-//            contracted basis (staged pipeline, K5a)
+// NREG > 0 : the whole latent vector lives in registers (D <= NREG)
+// NREG == 0: s is read from the shared-memory tile (any D)
+// CPT      : candidates per thread (rows tid, tid + MGB_BLOCK, ... of the tile)
+// MODE     : MODE_S (candidates from global memory), MODE_FRAMES (pose channels from
+//            materialised frames, staged pipeline K5a), MODE_SAMPLE (fused K1: candidates drawn in-kernel)
 // ---------------------------------------------------------------------------
-template <int NREG, bool FRAMES, bool TERMS, typename SIn>
-__global__ void __launch_bounds__(MGB_BLOCK) mgb_score_kernel(ScoreParams p) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
+template <int NREG, int CPT, int MODE, typename SIn>
+__global__ void __launch_bounds__(MGB_BLOCK) mgb_score_kernel(const __grid_constant__ ScoreParams p) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    constexpr int TILE = MGB_BLOCK * CPT;
+    constexpr int NR = NREG > 0 ? NREG : 1;
+    // element type of the shared-memory tile: large latent vectors (NREG == 0) are kept as float
+    // (float64 input is converted while it is staged), small ones stay raw and are converted on the way to registers
+    using TIn = typename std::conditional<NREG == 0, float, SIn>::type;
+    constexpr bool RAW = sizeof(TIn) == sizeof(SIn);
     const int tid = threadIdx.x;
-    const int D = p.D, K = p.K;
-    const int SROW = D | 1;  // odd row stride: conflict-free per-thread rows
+    const int D = p.D, KP = p.KP, DP = p.DP;
+    const int SROW = D | 1;  // MODE_SAMPLE with NREG == 0: per-thread rows, odd stride
 
     // ---- carve shared memory ------------------------------------------------
     size_t off = 0;
     float4* sm_tab = reinterpret_cast<float4*>(smem_raw + off);
-    if (p.tab_in_smem) off += (size_t)p.n_quads * (K + 1) * sizeof(float4);
+    if (p.tab_in_smem) off += (size_t)p.n_quads * (KP + 1) * sizeof(float4);
     float4* sm_gmm = reinterpret_cast<float4*>(smem_raw + off);
-    if (p.gmm_in_smem) off += (size_t)p.G * p.NQ * (D + 1) * sizeof(float4);
+    if (p.gmm_in_smem) off += (size_t)p.G * p.NQ * (DP + 1) * sizeof(float4);
+    float* sm_chol = reinterpret_cast<float*>(smem_raw + off);
+    if (MODE == MODE_SAMPLE && p.chol_in_smem) off += ((size_t)p.G * D * p.LS + (((size_t)p.G * D + 3) & ~(size_t)3)) * sizeof(float);
+    float* sm_mu = sm_chol + (size_t)p.G * D * p.LS;
     MgbOp* sm_ops = reinterpret_cast<MgbOp*>(smem_raw + off);
     off += (size_t)p.n_ops * sizeof(MgbOp);
     float* sm_cst = reinterpret_cast<float*>(smem_raw + off);
     off += (size_t)((p.n_cst + 3) & ~3) * sizeof(float);
-    float* sm_s = reinterpret_cast<float*>(smem_raw + off);
-    off += (size_t)MGB_BLOCK * SROW * sizeof(float);
-    off = (off + 15) & ~(size_t)15;
     float* sm_redc = reinterpret_cast<float*>(smem_raw + off);
     off += 32 * sizeof(float);
-    long long* sm_redi = reinterpret_cast<long long*>(smem_raw + ((off + 7) & ~(size_t)7));
+    long long* sm_redi = reinterpret_cast<long long*>(smem_raw + off);
+    off += 32 * sizeof(long long);
+    unsigned long long* sm_bar = reinterpret_cast<unsigned long long*>(smem_raw + off);
+    off += 2 * sizeof(unsigned long long);
+    off = (off + 127) & ~(size_t)127;
+    unsigned char* sm_tile = smem_raw + off;  // nbuf raw tiles [TILE][D] of SIn (MODE_S / MODE_FRAMES), or [TILE][SROW] floats (MODE_SAMPLE, NREG == 0)
+    const size_t tile_bytes = (MODE == MODE_SAMPLE) ? (size_t)TILE * SROW * sizeof(float) : (size_t)TILE * D * sizeof(TIn);
 
     // ---- one-time staging of program + tables -------------------------------
     if (p.tab_in_smem) {
-        const int n4 = p.n_quads * (K + 1);
+        const int n4 = p.n_quads * (KP + 1);
         for (int i = tid; i < n4; i += MGB_BLOCK) sm_tab[i] = p.tab[i];
     }
     if (p.gmm_in_smem) {
-        const int n4 = p.G * p.NQ * (D + 1);
+        const int n4 = p.G * p.NQ * (DP + 1);
         for (int i = tid; i < n4; i += MGB_BLOCK) sm_gmm[i] = p.gmm_tab[i];
+    }
+    if (MODE == MODE_SAMPLE && p.chol_in_smem) {
+        const int nl = p.G * D * p.LS;
+        for (int i = tid; i < nl; i += MGB_BLOCK) sm_chol[i] = p.chol[i];
+        for (int i = tid; i < p.G * D; i += MGB_BLOCK) sm_mu[i] = p.means[i];
     }
     for (int i = tid; i < p.n_ops; i += MGB_BLOCK) sm_ops[i] = p.ops[i];
     for (int i = tid; i < p.n_cst; i += MGB_BLOCK) sm_cst[i] = p.cst[i];
     const float4* tab = p.tab_in_smem ? sm_tab : p.tab;
     const float4* gtab = p.gmm_in_smem ? sm_gmm : p.gmm_tab;
-    const bool use_s = (!FRAMES) || (p.s != nullptr);
+    const float* chol = (MODE == MODE_SAMPLE && p.chol_in_smem) ? sm_chol : p.chol;
+    const float* mus = (MODE == MODE_SAMPLE && p.chol_in_smem) ? sm_mu : p.means;
+    const bool load_s = (MODE == MODE_S) || (MODE == MODE_FRAMES && p.s != nullptr);
+    const bool use_s = load_s || MODE == MODE_SAMPLE;
+    const bool use_tma = RAW && load_s && p.s_aligned;
+    if (use_tma && tid == 0) {
+        mgb_mbar_init(&sm_bar[0], 1);
+        mgb_mbar_init(&sm_bar[1], 1);
+        mgb_fence_barrier_init();
+    }
+    __syncthreads();
 
     float best_c = INFINITY;
     long long best_i = LLONG_MAX;
+    const long long n_tiles = (p.n + TILE - 1) / TILE;
+    const SIn* __restrict__ s_glob = reinterpret_cast<const SIn*>(p.s);
+    auto tile_by_tma = [&](long long tile) -> bool { return use_tma && (tile + 1) * TILE <= p.n; };
+    unsigned int phase[2] = {0u, 0u};
+    if (use_tma && tid == 0 && blockIdx.x < n_tiles && tile_by_tma(blockIdx.x))
+        mgb_tma_load_1d(sm_tile, s_glob + (size_t)blockIdx.x * TILE * D, (unsigned int)tile_bytes, &sm_bar[0]);
 
-    const long long n_tiles = (p.n + MGB_BLOCK - 1) / MGB_BLOCK;
-    for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-        const long long base = tile * MGB_BLOCK;
-        __syncthreads();
-        if (use_s) {
-            // coalesced tile load: element e of the tile -> row e / D, column e % D,
-            // tracked incrementally (no per-element division)
-            const SIn* __restrict__ src = reinterpret_cast<const SIn*>(p.s) + base * D;
-            long long remaining = (p.n - base) * (long long)D;
-            const int total = MGB_BLOCK * D;
-            const int step_r = MGB_BLOCK / D, step_c = MGB_BLOCK % D;
-            int r = tid / D, c = tid % D;
-            for (int e = tid; e < total; e += MGB_BLOCK) {
-                float v = 0.f;
-                if (e < remaining) v = (float)__ldg(src + e);
-                sm_s[r * SROW + c] = v;
-                r += step_r;
-                c += step_c;
-                if (c >= D) { c -= D; r += 1; }
+    int it = 0;
+    for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
+        const long long base = tile * TILE;
+        const int buf = (p.nbuf == 2) ? (it & 1) : 0;
+        const TIn* sm_s = reinterpret_cast<const TIn*>(sm_tile + (size_t)buf * tile_bytes);
+        if (load_s) {
+            if (p.nbuf == 2) {
+                const long long next = tile + gridDim.x;
+                if (tid == 0 && next < n_tiles && tile_by_tma(next))
+                    mgb_tma_load_1d(sm_tile + (size_t)(buf ^ 1) * tile_bytes, s_glob + (size_t)next * TILE * D, (unsigned int)tile_bytes,
+                                    &sm_bar[buf ^ 1]);
+            } else if (it > 0 && tid == 0 && tile_by_tma(tile)) {
+                mgb_tma_load_1d(sm_tile, s_glob + (size_t)tile * TILE * D, (unsigned int)tile_bytes, &sm_bar[0]);
+            }
+            if (tile_by_tma(tile)) {
+                mgb_mbar_wait(&sm_bar[buf], phase[buf]);
+                phase[buf] ^= 1u;
+            } else {
+                // ragged / unaligned tile: cooperative coalesced copy, zero fill past the end
+                TIn* dst = const_cast<TIn*>(sm_s);
+                const SIn* src = s_glob + (size_t)base * D;
+                const long long remaining = (p.n - base) * (long long)D;
+                for (int e = tid; e < TILE * D; e += MGB_BLOCK) dst[e] = (e < remaining) ? (TIn)__ldg(src + e) : (TIn)0;
+                __syncthreads();
             }
         }
-        __syncthreads();
 
-        const long long i = base + tid;
-        const bool valid = i < p.n;
-        const float* srow = sm_s + tid * SROW;
-        float s[NREG > 0 ? NREG : 1];
-        if (NREG > 0) {
+        // ---- candidates of this thread ------------------------------------------
+        long long idx[CPT];
+        bool valid[CPT];
+        float s[CPT][NR];
+        const TIn* srow[CPT];
+        const float* frow[CPT];
+        float* myrow[CPT];
 #pragma unroll
-            for (int k = 0; k < NREG; ++k) s[k] = (k < D && use_s) ? srow[k] : 0.f;
+        for (int c = 0; c < CPT; ++c) {
+            const int r = c * MGB_BLOCK + tid;
+            idx[c] = base + r;
+            valid[c] = idx[c] < p.n;
+            srow[c] = sm_s + (size_t)r * D;
+            frow[c] = (MODE == MODE_FRAMES) ? (p.frames + (size_t)(valid[c] ? idx[c] : 0) * p.n_times * p.P) : nullptr;
+            myrow[c] = reinterpret_cast<float*>(sm_tile) + (size_t)r * SROW;
+            if (MODE == MODE_SAMPLE) {
+                const unsigned long long gi = (unsigned long long)(p.index_base + idx[c]);
+                int g = 0;
+                while (g + 1 < p.G && (long long)gi >= p.prefix.v[g + 1]) ++g;
+                const uint2 key = make_uint2((unsigned int)p.seed, (unsigned int)(p.seed >> 32));
+                if (NREG > 0) {
+                    mgb_sample_row_reg<NR>(reinterpret_cast<const float4*>(chol + (size_t)g * D * p.LS), p.LS, mus + (size_t)g * D, D, gi, key, s[c]);
+                } else {
+                    mgb_sample_row_mem(chol + (size_t)g * D * p.LS, p.LS, mus + (size_t)g * D, D, gi, key, myrow[c]);
+                }
+            } else if (NREG > 0) {
+#pragma unroll
+                for (int k = 0; k < NR; ++k) s[c][k] = (k < D && use_s) ? (float)srow[c][k] : 0.f;
+            }
         }
-        const float* frow = FRAMES ? (p.frames + (size_t)(valid ? i : 0) * p.n_times * p.P) : nullptr;
 
         // ---- interpreter state ------------------------------------------------
-        Xf G;
-#pragma unroll
-        for (int q = 0; q < 9; ++q) G.R[q] = (q % 4 == 0) ? 1.f : 0.f;
-        G.t[0] = G.t[1] = G.t[2] = 0.f;
-        float al_c = 1.f, al_s = 0.f, al_dx = 0.f, al_dz = 0.f, al_qw = 1.f, al_qy = 0.f;
-        float total = 0.f;
-        float scratch[MGB_SCRATCH_FLOATS];
-        float stack[MGB_STACK_DEPTH * 12];
+        MgbXf G[CPT];
+        float al_c[CPT], al_s[CPT], al_dx[CPT], al_dz[CPT], al_qw[CPT], al_qy[CPT];
+        float total[CPT];
+        float scratch[CPT][MGB_SCRATCH_FLOATS];
+        float stack[CPT][MGB_STACK_DEPTH * 8];
         int sp = 0;
+#pragma unroll
+        for (int c = 0; c < CPT; ++c) {
+            mgb_xf_identity(G[c]);
+            al_c[c] = 1.f; al_s[c] = 0.f; al_dx[c] = 0.f; al_dz[c] = 0.f; al_qw[c] = 1.f; al_qy[c] = 0.f;
+            total[c] = 0.f;
+        }
 
-        auto quad = [&](int q) -> float4 {
-            if (FRAMES) {
-                const float* f = frow + q;
-                return make_float4(__ldg(f), __ldg(f + 1), __ldg(f + 2), __ldg(f + 3));
-            } else if (NREG > 0) {
-                return dotquad_reg<NREG>(tab + (size_t)q * (K + 1), K, K, s);
+        auto quad = [&](int q, float4 (&out)[CPT]) {
+            if constexpr (MODE == MODE_FRAMES) {
+#pragma unroll
+                for (int c = 0; c < CPT; ++c) {
+                    const float* f = frow[c] + q;
+                    out[c] = make_float4(__ldg(f), __ldg(f + 1), __ldg(f + 2), __ldg(f + 3));
+                }
+            } else if constexpr (NREG > 0) {
+                dot_rows_reg<NREG, CPT>(tab + (size_t)q * (KP + 1), KP >> 2, s, out);
+            } else if constexpr (MODE == MODE_SAMPLE) {
+                const float* rows[CPT];
+#pragma unroll
+                for (int c = 0; c < CPT; ++c) rows[c] = myrow[c];
+                dot_rows_mem<CPT, float>(tab + (size_t)q * (KP + 1), p.K, rows, out);
             } else {
-                return dotquad_smem(tab + (size_t)q * (K + 1), K, K, srow);
+                dot_rows_mem<CPT, TIn>(tab + (size_t)q * (KP + 1), p.K, srow, out);
             }
         };
-        auto emit = [&](int term, float w, float e) {
-            total = fmaf(w, e, total);
-            if (TERMS) {
-                if (valid) p.terms[(size_t)term * p.n + i] += e;
-            }
+        auto emit = [&](int c, int term, float w, float e) {
+            total[c] = fmaf(w, e, total[c]);
+            if (p.terms != nullptr && valid[c]) p.terms[(size_t)term * p.n + idx[c]] += e;
         };
 
         for (int pc = 0; pc < p.n_ops; ++pc) {
@@ -251,188 +285,224 @@ __global__ void __launch_bounds__(MGB_BLOCK) mgb_score_kernel(ScoreParams p) {
             const float* cs = sm_cst + op.c;
             switch (op.code) {
                 case OP_ROOT: {
-                    float4 tr = quad(op.a);
-                    float4 q = quad(op.b);
-                    // optional alignment to the previous motion (identity when local)
-                    float tx = al_c * tr.x + al_s * tr.z + al_dx;
-                    float tz = -al_s * tr.x + al_c * tr.z + al_dz;
-                    float qw = al_qw * q.x - al_qy * q.z;
-                    float qx = al_qw * q.y + al_qy * q.w;
-                    float qy = al_qw * q.z + al_qy * q.x;
-                    float qz = al_qw * q.w - al_qy * q.y;
-                    quat_to_R(qw, qx, qy, qz, G.R);
-                    G.t[0] = tx + cs[0];
-                    G.t[1] = tr.y + cs[1];
-                    G.t[2] = tz + cs[2];
+                    float4 tr[CPT], q[CPT];
+                    quad(op.a, tr);
+                    quad(op.b, q);
+#pragma unroll
+                    for (int c = 0; c < CPT; ++c) {
+                        // optional alignment to the previous motion (identity when local)
+                        const float tx = al_c[c] * tr[c].x + al_s[c] * tr[c].z + al_dx[c];
+                        const float tz = -al_s[c] * tr[c].x + al_c[c] * tr[c].z + al_dz[c];
+                        const float qw = al_qw[c] * q[c].x - al_qy[c] * q[c].z;
+                        const float qx = al_qw[c] * q[c].y + al_qy[c] * q[c].w;
+                        const float qy = al_qw[c] * q[c].z + al_qy[c] * q[c].x;
+                        const float qz = al_qw[c] * q[c].w - al_qy[c] * q[c].y;
+                        mgb_xf_set_rot(G[c], qw, qx, qy, qz);
+                        G[c].tx = tx + cs[0];
+                        G[c].ty = tr[c].y + cs[1];
+                        G[c].tz = tz + cs[2];
+                    }
                     break;
                 }
                 case OP_JOINT: {
-                    float4 q = quad(op.a);
-                    float Rl[9];
-                    quat_to_R(q.x, q.y, q.z, q.w, Rl);
-                    xf_mul(G, Rl, cs[0], cs[1], cs[2]);
+                    float4 q[CPT];
+                    quad(op.a, q);
+#pragma unroll
+                    for (int c = 0; c < CPT; ++c) mgb_xf_child(G[c], q[c].x, q[c].y, q[c].z, q[c].w, cs[0], cs[1], cs[2]);
                     break;
                 }
                 case OP_CONST: {
-                    if (op.a) {
-                        xf_translate(G, cs[9], cs[10], cs[11]);
-                    } else {
-                        float Rl[9];
 #pragma unroll
-                        for (int q = 0; q < 9; ++q) Rl[q] = cs[q];
-                        xf_mul(G, Rl, cs[9], cs[10], cs[11]);
+                    for (int c = 0; c < CPT; ++c) {
+                        if (op.a) mgb_xf_translate(G[c], cs[4], cs[5], cs[6]);
+                        else mgb_xf_child(G[c], cs[0], cs[1], cs[2], cs[3], cs[4], cs[5], cs[6]);
                     }
                     break;
                 }
                 case OP_PUSH: {
 #pragma unroll
-                    for (int q = 0; q < 9; ++q) stack[sp * 12 + q] = G.R[q];
-#pragma unroll
-                    for (int q = 0; q < 3; ++q) stack[sp * 12 + 9 + q] = G.t[q];
+                    for (int c = 0; c < CPT; ++c) {
+                        float* st = stack[c] + sp * 8;
+                        st[0] = G[c].w; st[1] = G[c].x; st[2] = G[c].y; st[3] = G[c].z;
+                        st[4] = G[c].s2; st[5] = G[c].tx; st[6] = G[c].ty; st[7] = G[c].tz;
+                    }
                     ++sp;
                     break;
                 }
                 case OP_POP: {
                     --sp;
 #pragma unroll
-                    for (int q = 0; q < 9; ++q) G.R[q] = stack[sp * 12 + q];
-#pragma unroll
-                    for (int q = 0; q < 3; ++q) G.t[q] = stack[sp * 12 + 9 + q];
+                    for (int c = 0; c < CPT; ++c) {
+                        const float* st = stack[c] + sp * 8;
+                        G[c].w = st[0]; G[c].x = st[1]; G[c].y = st[2]; G[c].z = st[3];
+                        G[c].s2 = st[4]; G[c].tx = st[5]; G[c].ty = st[6]; G[c].tz = st[7];
+                    }
                     break;
                 }
                 case OP_ALIGN: {
-                    // heading of the aligning node at control point 0 (G.R), raw root
-                    // translation of control point 0 (quad op.a), previous heading / root
-                    float px = G.R[0] * cs[0] + G.R[1] * cs[1] + G.R[2] * cs[2];
-                    float pz = G.R[6] * cs[0] + G.R[7] * cs[1] + G.R[8] * cs[2];
-                    float ang = cs[3] - atan2f(px, pz);
-                    const float PI = 3.14159265358979323846f;
-                    if (ang > PI) ang -= 2.f * PI;
-                    if (ang <= -PI) ang += 2.f * PI;
-                    sincosf(ang, &al_s, &al_c);
-                    sincosf(0.5f * ang, &al_qy, &al_qw);
-                    float4 tr = quad(op.a);
-                    al_dx = cs[4] - (al_c * tr.x + al_s * tr.z);
-                    al_dz = cs[5] - (-al_s * tr.x + al_c * tr.z);
+                    // heading of the aligning node at control point 0, raw root translation of
+                    // control point 0 (quad op.a), previous heading / root
+                    float4 tr[CPT];
+                    quad(op.a, tr);
+#pragma unroll
+                    for (int c = 0; c < CPT; ++c) {
+                        float px, py, pz;
+                        mgb_xf_rotate(G[c], cs[0], cs[1], cs[2], px, py, pz);
+                        float ang = cs[3] - atan2f(px, pz);
+                        const float PI = 3.14159265358979323846f;
+                        if (ang > PI) ang -= 2.f * PI;
+                        if (ang <= -PI) ang += 2.f * PI;
+                        sincosf(ang, &al_s[c], &al_c[c]);
+                        sincosf(0.5f * ang, &al_qy[c], &al_qw[c]);
+                        al_dx[c] = cs[4] - (al_c[c] * tr[c].x + al_s[c] * tr[c].z);
+                        al_dz[c] = cs[5] - (-al_s[c] * tr[c].x + al_c[c] * tr[c].z);
+                    }
                     break;
                 }
                 case OP_POS: {
-                    emit(op.a, cs[0], masked_dist((unsigned)op.b, cs + 1, G.t));
+#pragma unroll
+                    for (int c = 0; c < CPT; ++c) emit(c, op.a, cs[0], masked_dist((unsigned)op.b, cs + 1, G[c].tx, G[c].ty, G[c].tz));
                     break;
                 }
                 case OP_ORIENT: {
                     // angle_between_vectors(v1, v2) = acos(v1.v2 / |v1||v2|), evaluated as
                     // atan2(|v1 x v2|, v1.v2): same value, but well conditioned near 0 and pi in fp32
-                    float vx = G.R[2], vy = G.R[5], vz = G.R[8];
-                    float cx = vy * cs[3] - vz * cs[2], cy = vz * cs[1] - vx * cs[3], cz = vx * cs[2] - vy * cs[1];
-                    float d = vx * cs[1] + vy * cs[2] + vz * cs[3];
-                    emit(op.a, cs[0], atan2f(sqrtf(cx * cx + cy * cy + cz * cz), d));
+#pragma unroll
+                    for (int c = 0; c < CPT; ++c) {
+                        float vx, vy, vz;
+                        mgb_xf_rotate(G[c], 0.f, 0.f, 1.f, vx, vy, vz);
+                        const float cx = vy * cs[3] - vz * cs[2], cy = vz * cs[1] - vx * cs[3], cz = vx * cs[2] - vy * cs[1];
+                        const float d = vx * cs[1] + vy * cs[2] + vz * cs[3];
+                        emit(c, op.a, cs[0], atan2f(sqrtf(cx * cx + cy * cy + cz * cz), d));
+                    }
                     break;
                 }
                 case OP_REL: {
-                    float ox = cs[1], oy = cs[2], oz = cs[3], ow = cs[4];
-                    float pp[3];
-                    pp[0] = G.R[0] * ox + G.R[1] * oy + G.R[2] * oz + G.t[0] * ow;
-                    pp[1] = G.R[3] * ox + G.R[4] * oy + G.R[5] * oz + G.t[1] * ow;
-                    pp[2] = G.R[6] * ox + G.R[7] * oy + G.R[8] * oz + G.t[2] * ow;
-                    emit(op.a, cs[0], dist3(cs + 5, pp));
+#pragma unroll
+                    for (int c = 0; c < CPT; ++c) {
+                        float pp[3];
+                        mgb_xf_rotate(G[c], cs[1], cs[2], cs[3], pp[0], pp[1], pp[2]);
+                        pp[0] = fmaf(G[c].tx, cs[4], pp[0]);
+                        pp[1] = fmaf(G[c].ty, cs[4], pp[1]);
+                        pp[2] = fmaf(G[c].tz, cs[4], pp[2]);
+                        emit(c, op.a, cs[0], dist3(cs + 5, pp));
+                    }
                     break;
                 }
                 case OP_DIR2D: {
                     // degrees(acos(clamp(t.d / (|t||d|)))) evaluated as atan2(|t x d|, t.d) (same value,
                     // well conditioned for small angles in fp32); d = (x, z) of R_global * ref_dir
-                    float px = G.R[0] * cs[1] + G.R[1] * cs[2] + G.R[2] * cs[3];
-                    float pz = G.R[6] * cs[1] + G.R[7] * cs[2] + G.R[8] * cs[3];
-                    float cr = cs[4] * pz - cs[5] * px;
-                    float dt = cs[4] * px + cs[5] * pz;
-                    emit(op.a, cs[0], atan2f(fabsf(cr), dt) * 57.29577951308232f);
+#pragma unroll
+                    for (int c = 0; c < CPT; ++c) {
+                        float px, py, pz;
+                        mgb_xf_rotate(G[c], cs[1], cs[2], cs[3], px, py, pz);
+                        const float cr = cs[4] * pz - cs[5] * px;
+                        const float dt = cs[4] * px + cs[5] * pz;
+                        emit(c, op.a, cs[0], atan2f(fabsf(cr), dt) * 57.29577951308232f);
+                    }
                     break;
                 }
                 case OP_LOOKAT: {
-                    float tx = cs[1] - G.t[0], ty = cs[2] - G.t[1], tz = cs[3] - G.t[2];
-                    float ti = rsqrtf(tx * tx + ty * ty + tz * tz);
-                    tx *= ti; ty *= ti; tz *= ti;
-                    float hx = G.R[2], hy = G.R[5], hz = G.R[8];
-                    float hi = rsqrtf(hx * hx + hy * hy + hz * hz);
-                    hx *= hi; hy *= hi; hz *= hi;
-                    float cx = hy * tz - hz * ty, cy = hz * tx - hx * tz, cz = hx * ty - hy * tx;
-                    float sn = sqrtf(cx * cx + cy * cy + cz * cz);
-                    float cn = hx * tx + hy * ty + hz * tz;
-                    emit(op.a, cs[0], fabsf(atan2f(sn, cn)));
+#pragma unroll
+                    for (int c = 0; c < CPT; ++c) {
+                        float tx = cs[1] - G[c].tx, ty = cs[2] - G[c].ty, tz = cs[3] - G[c].tz;
+                        const float ti = rsqrtf(tx * tx + ty * ty + tz * tz);
+                        tx *= ti; ty *= ti; tz *= ti;
+                        float hx, hy, hz;
+                        mgb_xf_rotate(G[c], 0.f, 0.f, 1.f, hx, hy, hz);
+                        const float hi = rsqrtf(hx * hx + hy * hy + hz * hz);
+                        hx *= hi; hy *= hi; hz *= hi;
+                        const float cx = hy * tz - hz * ty, cy = hz * tx - hx * tz, cz = hx * ty - hy * tx;
+                        emit(c, op.a, cs[0], fabsf(atan2f(sqrtf(cx * cx + cy * cy + cz * cz), hx * tx + hy * ty + hz * tz)));
+                    }
                     break;
                 }
                 case OP_STORE: {
-                    scratch[op.a] = G.t[0];
-                    scratch[op.a + 1] = G.t[1];
-                    scratch[op.a + 2] = G.t[2];
+#pragma unroll
+                    for (int c = 0; c < CPT; ++c) {
+                        scratch[c][op.a] = G[c].tx;
+                        scratch[c][op.a + 1] = G[c].ty;
+                        scratch[c][op.a + 2] = G[c].tz;
+                    }
                     break;
                 }
                 case OP_TWOHANDS: {
-                    const float* lp = scratch + op.b;
-                    const float* rp = scratch + op.b + 3;
-                    float mid[3] = {lp[0] + 0.5f * (rp[0] - lp[0]), lp[1] + 0.5f * (rp[1] - lp[1]), lp[2] + 0.5f * (rp[2] - lp[2])};
-                    float e = dist3(cs + 1, mid) + dist3(cs + 4, lp) + dist3(cs + 7, rp);
-                    emit(op.a, cs[0], e);
+#pragma unroll
+                    for (int c = 0; c < CPT; ++c) {
+                        const float* lp = scratch[c] + op.b;
+                        const float* rp = scratch[c] + op.b + 3;
+                        const float mid[3] = {lp[0] + 0.5f * (rp[0] - lp[0]), lp[1] + 0.5f * (rp[1] - lp[1]), lp[2] + 0.5f * (rp[2] - lp[2])};
+                        emit(c, op.a, cs[0], dist3(cs + 1, mid) + dist3(cs + 4, lp) + dist3(cs + 7, rp));
+                    }
                     break;
                 }
                 case OP_FEET: {
-                    const float* lp = scratch + op.b;
-                    const float* rp = scratch + op.b + 3;
-                    float e = (dist3(cs + 1, lp) + dist3(cs + 4, rp)) * cs[7];
-                    emit(op.a, cs[0], e);
+#pragma unroll
+                    for (int c = 0; c < CPT; ++c) {
+                        const float* lp = scratch[c] + op.b;
+                        const float* rp = scratch[c] + op.b + 3;
+                        emit(c, op.a, cs[0], (dist3(cs + 1, lp) + dist3(cs + 4, rp)) * cs[7]);
+                    }
                     break;
                 }
                 case OP_POSE: {
                     // weighted 2-D rigid alignment of the candidate's point cloud (b) onto the
                     // target cloud (a), then mean point distance + root velocity error
                     const int np = (int)cs[1];
-                    const float* pts = scratch + op.b;
                     const float W = cs[6], sax = cs[7], saz = cs[8];
                     const float* tg = cs + 9;  // (ax, ay, az, w) * np
-                    float num_l = 0.f, den_l = 0.f, sbx = 0.f, sbz = 0.f;
-                    for (int j = 0; j < np; ++j) {
-                        float ax = tg[4 * j], az = tg[4 * j + 2], w = tg[4 * j + 3];
-                        float bx = pts[3 * j], bz = pts[3 * j + 2];
-                        num_l = fmaf(w, ax * bz - bx * az, num_l);
-                        den_l = fmaf(w, ax * bx + az * bz, den_l);
-                        sbx = fmaf(w, bx, sbx);
-                        sbz = fmaf(w, bz, sbz);
+#pragma unroll
+                    for (int c = 0; c < CPT; ++c) {
+                        const float* pts = scratch[c] + op.b;
+                        float num_l = 0.f, den_l = 0.f, sbx = 0.f, sbz = 0.f;
+                        for (int j = 0; j < np; ++j) {
+                            const float ax = tg[4 * j], az = tg[4 * j + 2], w = tg[4 * j + 3];
+                            const float bx = pts[3 * j], bz = pts[3 * j + 2];
+                            num_l = fmaf(w, ax * bz - bx * az, num_l);
+                            den_l = fmaf(w, ax * bx + az * bz, den_l);
+                            sbx = fmaf(w, bx, sbx);
+                            sbz = fmaf(w, bz, sbz);
+                        }
+                        const float invW = 1.f / W;
+                        const float num = num_l - (sax * sbz - sbx * saz) * invW;
+                        const float den = den_l - (sax * sbx + saz * sbz) * invW;
+                        const float theta = atan2f(num, den);
+                        float st, ct;
+                        sincosf(theta, &st, &ct);
+                        const float ox = (sax - sbx * ct - sbz * st) * invW;
+                        const float oz = (saz + sbx * st - sbz * ct) * invW;
+                        float dsum = 0.f;
+                        for (int j = 0; j < np; ++j) {
+                            const float bx = pts[3 * j], by = pts[3 * j + 1], bz = pts[3 * j + 2];
+                            const float tx = ct * bx + st * bz + ox;
+                            const float tz = -st * bx + ct * bz + oz;
+                            const float ex = tg[4 * j] - tx, ey = tg[4 * j + 1] - by, ez = tg[4 * j + 2] - tz;
+                            dsum += sqrtf(fmaf(ex, ex, fmaf(ey, ey, ez * ez)));
+                        }
+                        float e = dsum / (float)np;
+                        if (cs[2] != 0.f) {
+                            const float* r2 = pts + 3 * np;
+                            const float vx = cs[3] - (r2[0] - pts[0]), vy = cs[4] - (r2[1] - pts[1]), vz = cs[5] - (r2[2] - pts[2]);
+                            e += sqrtf(fmaf(vx, vx, fmaf(vy, vy, vz * vz)));
+                        }
+                        emit(c, op.a, cs[0], e);
                     }
-                    float invW = 1.f / W;
-                    float num = num_l - (sax * sbz - sbx * saz) * invW;
-                    float den = den_l - (sax * sbx + saz * sbz) * invW;
-                    float theta = atan2f(num, den);
-                    float st, ct;
-                    sincosf(theta, &st, &ct);
-                    float ox = (sax - sbx * ct - sbz * st) * invW;
-                    float oz = (saz + sbx * st - sbz * ct) * invW;
-                    float dsum = 0.f;
-                    for (int j = 0; j < np; ++j) {
-                        float bx = pts[3 * j], by = pts[3 * j + 1], bz = pts[3 * j + 2];
-                        float tx = ct * bx + st * bz + ox;
-                        float tz = -st * bx + ct * bz + oz;
-                        float ex = tg[4 * j] - tx, ey = tg[4 * j + 1] - by, ez = tg[4 * j + 2] - tz;
-                        dsum += sqrtf(fmaf(ex, ex, fmaf(ey, ey, ez * ez)));
-                    }
-                    float e = dsum / (float)np;
-                    if (cs[2] != 0.f) {
-                        const float* r2 = pts + 3 * np;
-                        float vx = cs[3] - (r2[0] - pts[0]), vy = cs[4] - (r2[1] - pts[1]), vz = cs[5] - (r2[2] - pts[2]);
-                        e += sqrtf(fmaf(vx, vx, fmaf(vy, vy, vz * vz)));
-                    }
-                    emit(op.a, cs[0], e);
                     break;
                 }
                 case OP_CA_BEGIN: {
-                    scratch[op.a] = INFINITY;
+#pragma unroll
+                    for (int c = 0; c < CPT; ++c) scratch[c][op.a] = INFINITY;
                     break;
                 }
                 case OP_CA_ACC: {
-                    scratch[op.a] = fminf(scratch[op.a], masked_dist((unsigned)op.b, cs, G.t));
+#pragma unroll
+                    for (int c = 0; c < CPT; ++c)
+                        scratch[c][op.a] = fminf(scratch[c][op.a], masked_dist((unsigned)op.b, cs, G[c].tx, G[c].ty, G[c].tz));
                     break;
                 }
                 case OP_CA_END: {
-                    emit(op.a, cs[0], scratch[op.b]);
+#pragma unroll
+                    for (int c = 0; c < CPT; ++c) emit(c, op.a, cs[0], scratch[c][op.b]);
                     break;
                 }
                 default:
@@ -440,43 +510,77 @@ __global__ void __launch_bounds__(MGB_BLOCK) mgb_score_kernel(ScoreParams p) {
             }
         }
 
-        float cost = p.err_scale * total;
+        float cost[CPT];
+#pragma unroll
+        for (int c = 0; c < CPT; ++c) cost[c] = p.err_scale * total[c];
         if (p.quality_scale != 0.f) {
-            // GMM log-density from the precision Cholesky factors; column quads of the
-            // upper-triangular factor only need rows k <= 4q+3
-            float mx = -INFINITY, ssum = 0.f;
+            // GMM log-density from the precision Cholesky factors; column quad jq of the
+            // upper-triangular factor only needs rows k < 4 jq + 4
+            float mx[CPT], ssum[CPT];
+#pragma unroll
+            for (int c = 0; c < CPT; ++c) { mx[c] = -INFINITY; ssum[c] = 0.f; }
             for (int g = 0; g < p.G; ++g) {
-                float qf = 0.f;
+                float qf[CPT];
+#pragma unroll
+                for (int c = 0; c < CPT; ++c) qf[c] = 0.f;
                 for (int jq = 0; jq < p.NQ; ++jq) {
-                    const float4* row = gtab + (size_t)(g * p.NQ + jq) * (D + 1);
-                    int cnt = min(D, 4 * jq + 4);
-                    float4 y = (NREG > 0) ? dotquad_reg<NREG>(row, D, cnt, s) : dotquad_smem(row, D, cnt, srow);
-                    qf = fmaf(y.x, y.x, fmaf(y.y, y.y, fmaf(y.z, y.z, fmaf(y.w, y.w, qf))));
+                    const float4* row = gtab + (size_t)(g * p.NQ + jq) * (DP + 1);
+                    float4 y[CPT];
+                    if constexpr (NREG > 0) {
+                        dot_rows_reg<NREG, CPT>(row, jq + 1, s, y);
+                    } else if constexpr (MODE == MODE_SAMPLE) {
+                        const float* rows[CPT];
+#pragma unroll
+                        for (int c = 0; c < CPT; ++c) rows[c] = myrow[c];
+                        dot_rows_mem<CPT, float>(row, min(D, 4 * jq + 4), rows, y);
+                    } else {
+                        dot_rows_mem<CPT, TIn>(row, min(D, 4 * jq + 4), srow, y);
+                    }
+#pragma unroll
+                    for (int c = 0; c < CPT; ++c)
+                        qf[c] = fmaf(y[c].x, y[c].x, fmaf(y[c].y, y[c].y, fmaf(y[c].z, y[c].z, fmaf(y[c].w, y[c].w, qf[c]))));
                 }
-                float lp = p.gmm_c[g] - 0.5f * qf;
-                if (lp > mx) {
-                    ssum = ssum * __expf(mx - lp) + 1.f;
-                    mx = lp;
-                } else {
-                    ssum += __expf(lp - mx);
+                const float gc = p.gmm_c[g];
+#pragma unroll
+                for (int c = 0; c < CPT; ++c) {
+                    const float lp = gc - 0.5f * qf[c];
+                    if (lp > mx[c]) {
+                        ssum[c] = ssum[c] * __expf(mx[c] - lp) + 1.f;
+                        mx[c] = lp;
+                    } else {
+                        ssum[c] += __expf(lp - mx[c]);
+                    }
                 }
             }
-            cost = fmaf(p.quality_scale, -(mx + __logf(ssum)), cost);
+#pragma unroll
+            for (int c = 0; c < CPT; ++c) cost[c] = fmaf(p.quality_scale, -(mx[c] + __logf(ssum[c])), cost[c]);
         }
         if (p.magnitude_scale != 0.f) {
-            float m2 = 0.f;
-            if (NREG > 0) {
 #pragma unroll
-                for (int k = 0; k < NREG; ++k) m2 = fmaf(s[k], s[k], m2);
-            } else {
-                for (int k = 0; k < D; ++k) m2 = fmaf(srow[k], srow[k], m2);
+            for (int c = 0; c < CPT; ++c) {
+                float m2 = 0.f;
+                if constexpr (NREG > 0) {
+#pragma unroll
+                    for (int k = 0; k < NR; ++k) m2 = fmaf(s[c][k], s[c][k], m2);
+                } else if constexpr (MODE == MODE_SAMPLE) {
+                    for (int k = 0; k < D; ++k) m2 = fmaf(myrow[c][k], myrow[c][k], m2);
+                } else {
+                    for (int k = 0; k < D; ++k) { const float v = (float)srow[c][k]; m2 = fmaf(v, v, m2); }
+                }
+                cost[c] = fmaf(p.magnitude_scale, sqrtf(m2), cost[c]);
             }
-            cost = fmaf(p.magnitude_scale, sqrtf(m2), cost);
         }
-        if (valid) {
-            if (p.cost) p.cost[i] = cost;
-            const long long gi = p.index_base + i;
-            if (better(cost, gi, best_c, best_i)) { best_c = cost; best_i = gi; }
+#pragma unroll
+        for (int c = 0; c < CPT; ++c) {
+            if (valid[c]) {
+                if (p.cost) p.cost[idx[c]] = cost[c];
+                const long long gi = p.index_base + idx[c];
+                if (better(cost[c], gi, best_c, best_i)) { best_c = cost[c]; best_i = gi; }
+            }
+        }
+        if (load_s) {
+            __syncthreads();                       // every thread is done reading this tile buffer ...
+            if (tid == 0) mgb_fence_proxy_async();  // ... before the async proxy (TMA) may overwrite it
         }
     }
 
@@ -604,20 +708,33 @@ int num_sms() {
     return g_num_sms;
 }
 
-template <int NREG, bool FRAMES, bool TERMS, typename SIn>
-int launch_variant(const ScoreParams& p, size_t smem, cudaStream_t stream) {
-    auto kern = mgb_score_kernel<NREG, FRAMES, TERMS, SIn>;
+constexpr size_t MGB_SMEM_MAX = 220 * 1024;
+
+struct SmemPlan {
+    size_t fixed;  // tables + program + reduction scratch (everything before the tile buffers)
+};
+
+template <int NREG, int CPT, int MODE, typename SIn>
+int launch_variant(ScoreParams& p, const SmemPlan& plan, cudaStream_t stream) {
+    auto kern = mgb_score_kernel<NREG, CPT, MODE, SIn>;
     static bool configured = false;
-    static size_t configured_smem = 0;
-    if (!configured || smem > configured_smem) {
-        MGB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(200 * 1024)));
+    if (!configured) {
+        MGB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)MGB_SMEM_MAX));
         configured = true;
-        configured_smem = 200 * 1024;
     }
+    size_t tile = 0;  // bytes of one tile buffer
+    if (MODE == MODE_S || (MODE == MODE_FRAMES && p.s != nullptr)) tile = (size_t)MGB_BLOCK * CPT * p.D * (NREG == 0 ? sizeof(float) : sizeof(SIn));
+    if (MODE == MODE_SAMPLE && NREG == 0) tile = (size_t)MGB_BLOCK * CPT * (p.D | 1) * sizeof(float);
+    tile = (tile + 127) & ~(size_t)127;
+    // two tile buffers (TMA prefetch of the next tile) when they fit comfortably
+    p.nbuf = (MODE != MODE_SAMPLE && tile > 0 && plan.fixed + 2 * tile <= 96 * 1024) ? 2 : 1;
+    if (MODE == MODE_SAMPLE) p.nbuf = 1;
+    const size_t smem = plan.fixed + (size_t)p.nbuf * tile;
+    MGB_REQUIRE(smem <= MGB_SMEM_MAX, "constraint program / candidate tile too large for shared memory (%zu bytes)", smem);
     int occ = 1;
     MGB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, MGB_BLOCK, smem));
     if (occ < 1) occ = 1;
-    long long n_tiles = (p.n + MGB_BLOCK - 1) / MGB_BLOCK;
+    const long long n_tiles = (p.n + MGB_BLOCK * CPT - 1) / (MGB_BLOCK * CPT);
     long long grid = (long long)num_sms() * occ;
     if (grid > n_tiles) grid = n_tiles;
     if (grid < 1) grid = 1;
@@ -627,16 +744,26 @@ int launch_variant(const ScoreParams& p, size_t smem, cudaStream_t stream) {
     return MGB_OK;
 }
 
-template <bool FRAMES, bool TERMS, typename SIn>
-int launch_nreg(int D, const ScoreParams& p, size_t smem, cudaStream_t stream) {
-    if (D <= 16) return launch_variant<16, FRAMES, TERMS, SIn>(p, smem, stream);
-    if (D <= 32) return launch_variant<32, FRAMES, TERMS, SIn>(p, smem, stream);
-    return launch_variant<0, FRAMES, TERMS, SIn>(p, smem, stream);
+int cpt_preference() {
+    static int v = -1;
+    if (v < 0) {
+        const char* e = getenv("MGB_CPT");
+        v = (e && atoi(e) == 1) ? 1 : 2;
+    }
+    return v;
+}
+
+template <int MODE, typename SIn>
+int launch_shape(int D, ScoreParams& p, const SmemPlan& plan, cudaStream_t stream) {
+    if (D <= 16) {
+        if (cpt_preference() == 2 && p.n >= 2LL * MGB_BLOCK * num_sms()) return launch_variant<16, 2, MODE, SIn>(p, plan, stream);
+        return launch_variant<16, 1, MODE, SIn>(p, plan, stream);
+    }
+    if (D <= 32) return launch_variant<32, 1, MODE, SIn>(p, plan, stream);
+    return launch_variant<0, 1, MODE, SIn>(p, plan, stream);
 }
 
 }  // namespace
-
-size_t mgb_score_grid_upper_bound() { return (size_t)num_sms() * 8; }
 
 extern "C" size_t mgb_score_workspace_bytes(int64_t n, int32_t k) {
     (void)n;
@@ -646,18 +773,21 @@ extern "C" size_t mgb_score_workspace_bytes(int64_t n, int32_t k) {
     return parts * (sizeof(float) + sizeof(long long)) + 256;
 }
 
-int mgb_launch_score(const mgb_model* m, const mgb_constraints* c, const void* d_s, int s_is_f64,
-                     const float* d_frames, int64_t n, int64_t index_base, float err_scale,
+int mgb_launch_score(const mgb_model* m, const mgb_constraints* c, int mode, const void* d_s, int s_is_f64,
+                     const float* d_frames, const int64_t* h_counts, uint64_t seed, int64_t n, int64_t index_base, float err_scale,
                      float quality_scale, float magnitude_scale, float* d_cost, float* d_terms, int k,
                      float* d_best_cost, int64_t* d_best_idx, void* d_ws, size_t ws_bytes,
                      cudaStream_t stream) {
-    MGB_REQUIRE(m && c, "null handle");
-    MGB_REQUIRE(c->model == m, "constraints were packed for a different model");
+    MGB_REQUIRE(m, "null model handle");
+    MGB_REQUIRE(!c || c->model == m, "constraints were packed for a different model");
     MGB_REQUIRE(n >= 0, "negative n");
     MGB_REQUIRE(k >= 0 && k <= 64, "k must be in [0, 64]");
-    const bool frames = d_frames != nullptr;
-    MGB_REQUIRE(frames || d_s || n == 0, "d_s is NULL");
+    MGB_REQUIRE(mode >= MODE_S && mode <= MODE_SAMPLE, "bad mode");
+    const bool frames = mode == MODE_FRAMES;
+    MGB_REQUIRE(!frames || d_frames, "d_frames is NULL");
+    MGB_REQUIRE(mode != MODE_S || d_s || n == 0, "d_s is NULL");
     MGB_REQUIRE(!(frames && s_is_f64), "frames mode takes float32 s");
+    MGB_REQUIRE(!d_terms || c, "d_terms needs a constraint set");
     if ((quality_scale != 0.f || magnitude_scale != 0.f) && frames) MGB_REQUIRE(d_s, "logpdf / magnitude need d_s");
     if (k > 0) {
         MGB_REQUIRE(d_best_cost && d_best_idx, "k > 0 needs d_best_cost / d_best_idx");
@@ -677,25 +807,35 @@ int mgb_launch_score(const mgb_model* m, const mgb_constraints* c, const void* d
         return MGB_OK;
     }
     ScoreParams p;
-    p.tab = c->d_tab;
-    p.ops = frames ? c->d_ops_frames : c->d_ops_fused;
-    p.cst = c->d_cst;
-    p.n_ops = c->n_ops;
-    p.n_cst = c->n_cst;
-    p.n_quads = c->n_quads;
+    memset(&p, 0, sizeof(p));
+    if (c) {
+        p.tab = c->d_tab;
+        p.ops = frames ? c->d_ops_frames : c->d_ops_fused;
+        p.cst = c->d_cst;
+        p.n_ops = c->n_ops;
+        p.n_cst = c->n_cst;
+        p.n_quads = c->n_quads;
+        p.n_times = c->n_times;
+        p.n_terms = c->n_terms;
+        p.KP = c->KP;
+    }
     p.K = m->K;
     p.D = m->D;
+    p.DP = m->DP;
     p.P = m->P;
-    p.n_times = c->n_times;
-    p.n_terms = c->n_terms;
     p.gmm_tab = m->d_gmm_tab;
     p.gmm_c = m->d_gmm_c;
     p.G = m->G;
     p.NQ = m->NQ;
+    p.chol = m->d_chol;
+    p.means = m->d_means;
+    p.LS = m->LS;
+    p.seed = seed;
     p.s = d_s;
     p.frames = d_frames;
     p.n = n;
     p.index_base = index_base;
+    p.s_aligned = (d_s != nullptr && (reinterpret_cast<uintptr_t>(d_s) & 15u) == 0) ? 1 : 0;
     p.err_scale = err_scale;
     p.quality_scale = quality_scale;
     p.magnitude_scale = magnitude_scale;
@@ -709,31 +849,50 @@ int mgb_launch_score(const mgb_model* m, const mgb_constraints* c, const void* d
     p.done_count = reinterpret_cast<unsigned int*>(ws + parts * (sizeof(long long) + sizeof(float)));
     p.best_cost = d_best_cost;
     p.best_idx = reinterpret_cast<long long*>(d_best_idx);
+    if (mode == MODE_SAMPLE) {
+        MGB_REQUIRE(h_counts, "sampling needs the per-component counts");
+        MGB_REQUIRE(m->G <= MGB_MAX_GMM, "at most %d mixture components are supported by the sampler", MGB_MAX_GMM);
+        p.prefix.v[0] = 0;
+        for (int g = 0; g < m->G; ++g) {
+            MGB_REQUIRE(h_counts[g] >= 0, "negative component count");
+            p.prefix.v[g + 1] = p.prefix.v[g] + h_counts[g];
+        }
+        for (int g = m->G + 1; g <= MGB_MAX_GMM; ++g) p.prefix.v[g] = p.prefix.v[m->G];
+        MGB_REQUIRE(index_base >= 0 && index_base + n <= p.prefix.v[m->G], "component counts (%lld) do not cover [%lld, %lld)",
+                    p.prefix.v[m->G], (long long)index_base, (long long)(index_base + n));
+    }
 
     // shared-memory budget: tables go to shared memory when they fit
-    size_t tab_bytes = frames ? 0 : (size_t)c->n_quads * (m->K + 1) * sizeof(float4);
-    size_t gmm_bytes = (quality_scale != 0.f) ? (size_t)m->G * m->NQ * (m->D + 1) * sizeof(float4) : 0;
-    p.tab_in_smem = (!frames && tab_bytes <= 96 * 1024) ? 1 : 0;
-    size_t smem = p.tab_in_smem ? tab_bytes : 0;
-    p.gmm_in_smem = (gmm_bytes > 0 && smem + gmm_bytes <= 128 * 1024) ? 1 : 0;
-    if (p.gmm_in_smem) smem += gmm_bytes;
-    smem += (size_t)c->n_ops * sizeof(MgbOp);
-    smem += (size_t)((c->n_cst + 3) & ~3) * sizeof(float);
-    smem += (size_t)MGB_BLOCK * (m->D | 1) * sizeof(float);
-    smem += 16 + 32 * sizeof(float) + 8 + 32 * sizeof(long long);
-    MGB_REQUIRE(smem <= 200 * 1024, "constraint program too large for shared memory (%zu bytes)", smem);
+    const size_t tab_bytes = (frames || !c) ? 0 : (size_t)c->n_quads * (c->KP + 1) * sizeof(float4);
+    const size_t gmm_bytes = (quality_scale != 0.f) ? (size_t)m->G * m->NQ * (m->DP + 1) * sizeof(float4) : 0;
+    const size_t chol_bytes = (mode == MODE_SAMPLE) ? ((size_t)m->G * m->D * m->LS + (((size_t)m->G * m->D + 3) & ~(size_t)3)) * sizeof(float) : 0;
+    size_t fixed = 0;
+    p.tab_in_smem = (tab_bytes > 0 && tab_bytes <= 96 * 1024) ? 1 : 0;
+    if (p.tab_in_smem) fixed += tab_bytes;
+    p.gmm_in_smem = (gmm_bytes > 0 && fixed + gmm_bytes <= 112 * 1024) ? 1 : 0;
+    if (p.gmm_in_smem) fixed += gmm_bytes;
+    p.chol_in_smem = (chol_bytes > 0 && fixed + chol_bytes <= 112 * 1024) ? 1 : 0;
+    if (p.chol_in_smem) fixed += chol_bytes;
+    fixed += (size_t)p.n_ops * sizeof(MgbOp);
+    fixed += (size_t)((p.n_cst + 3) & ~3) * sizeof(float);
+    fixed += 32 * sizeof(float) + 32 * sizeof(long long) + 2 * sizeof(unsigned long long);
+    fixed = (fixed + 127) & ~(size_t)127;
+    SmemPlan plan;
+    plan.fixed = fixed + 128;  // slack for the base alignment of the dynamic segment
     // the completion counter in the workspace must be zero on entry: the caller zero-fills a
     // fresh workspace once (include/mgb200.h) and the kernel re-arms it at the end of every launch
     if (d_terms) MGB_CUDA(cudaMemsetAsync(d_terms, 0, (size_t)c->n_terms * n * sizeof(float), stream));
 
     int rc;
     const int D = m->D;
-    if (frames) {
-        rc = d_terms ? launch_nreg<true, true, float>(D, p, smem, stream) : launch_nreg<true, false, float>(D, p, smem, stream);
+    if (mode == MODE_FRAMES) {
+        rc = launch_variant<0, 1, MODE_FRAMES, float>(p, plan, stream);
+    } else if (mode == MODE_SAMPLE) {
+        rc = launch_shape<MODE_SAMPLE, float>(D, p, plan, stream);
     } else if (s_is_f64) {
-        rc = d_terms ? launch_nreg<false, true, double>(D, p, smem, stream) : launch_nreg<false, false, double>(D, p, smem, stream);
+        rc = launch_shape<MODE_S, double>(D, p, plan, stream);
     } else {
-        rc = d_terms ? launch_nreg<false, true, float>(D, p, smem, stream) : launch_nreg<false, false, float>(D, p, smem, stream);
+        rc = launch_shape<MODE_S, float>(D, p, plan, stream);
     }
     if (rc != MGB_OK) return rc;
     if (k > 1) {
@@ -741,7 +900,6 @@ int mgb_launch_score(const mgb_model* m, const mgb_constraints* c, const void* d
     }
     return MGB_OK;
 }
-
 extern "C" int mgb_topk(const float* d_cost, int64_t n, int64_t index_base, int32_t k, float* d_best_cost,
                         int64_t* d_best_idx, void* d_workspace, size_t workspace_bytes, void* stream_) {
     cudaStream_t stream = (cudaStream_t)stream_;

@@ -8,6 +8,7 @@
 
 #include <algorithm>
 
+#include "mgb_device.cuh"
 #include "mgb_internal.cuh"
 
 namespace {
@@ -23,86 +24,68 @@ int sm_count() {
     return n;
 }
 
-// ---------------------------------------------------------------------------
-// Philox4x32-10 (Salmon et al.), counter = (global index, block), key = seed
-// ---------------------------------------------------------------------------
-__device__ __forceinline__ uint4 philox4x32_10(uint4 ctr, uint2 key) {
-    const unsigned int M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
-#pragma unroll
-    for (int r = 0; r < 10; ++r) {
-        unsigned int hi0 = __umulhi(M0, ctr.x), lo0 = M0 * ctr.x;
-        unsigned int hi1 = __umulhi(M1, ctr.z), lo1 = M1 * ctr.z;
-        ctr = make_uint4(hi1 ^ ctr.y ^ key.x, lo1, hi0 ^ ctr.w ^ key.y, lo0);
-        key.x += W0;
-        key.y += W1;
+#define SAMPLE_BLOCK 256
+
+// K1.  One thread draws one candidate (Philox4x32-10 keyed by the global index, Box-Muller,
+// s = mu_g + L_g z with the Cholesky rows broadcast from shared memory as float4), writes its
+// row into a densely packed shared-memory tile [SAMPLE_BLOCK][D]; the tile (one contiguous
+// run of global memory) leaves with ONE TMA bulk store, double-buffered so the store of
+// tile i overlaps the arithmetic of tile i + 1.
+template <int NREG>
+__global__ void __launch_bounds__(SAMPLE_BLOCK) mgb_sample_kernel(const float* __restrict__ means, const float* __restrict__ chol, int LS,
+                                                                 const __grid_constant__ MgbGmmPrefix pre, int G, int D, long long n,
+                                                                 long long index_base, unsigned long long seed, int in_smem, int aligned,
+                                                                 float* __restrict__ out) {
+    extern __shared__ __align__(128) unsigned char sm_raw1[];
+    constexpr int NR = NREG > 0 ? NREG : 1;
+    const int SB = blockDim.x;  // rows per tile (<= SB; fewer for large D so that two tiles fit)
+    const size_t tile_bytes = ((size_t)SB * D * sizeof(float) + 127) & ~(size_t)127;
+    float* sm_tile = reinterpret_cast<float*>(sm_raw1);
+    float* sm_chol = reinterpret_cast<float*>(sm_raw1 + 2 * tile_bytes);
+    float* sm_mu = sm_chol + (size_t)G * D * LS;
+    if (in_smem) {
+        for (int i = threadIdx.x; i < G * D * LS; i += SB) sm_chol[i] = chol[i];
+        for (int i = threadIdx.x; i < G * D; i += SB) sm_mu[i] = means[i];
     }
-    return ctr;
-}
-
-__device__ __forceinline__ float u01(unsigned int x) {  // (0, 1]
-    return (float)(x >> 8) * (1.0f / 16777216.0f) + (0.5f / 16777216.0f);
-}
-
-#define SAMPLE_BLOCK 128
-
-// K1.  One thread per candidate; z and then s live in the thread's shared-memory
-// row (odd stride), the tile is written out with unit-stride stores.
-#define MGB_MAX_GMM 64
-struct GmmPrefix {
-    long long v[MGB_MAX_GMM + 1];
-};
-
-__global__ void __launch_bounds__(SAMPLE_BLOCK) mgb_sample_kernel(const float* __restrict__ means, const float* __restrict__ chol,
-                                                                 const GmmPrefix pre, int G, int D, long long n,
-                                                                 long long index_base, unsigned long long seed, float* __restrict__ out) {
-    const long long* prefix = pre.v;
-    extern __shared__ float sm[];
-    const int SROW = D | 1;
-    float* row = sm + threadIdx.x * SROW;
-    const long long n_tiles = (n + SAMPLE_BLOCK - 1) / SAMPLE_BLOCK;
-    for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-        const long long i = tile * SAMPLE_BLOCK + threadIdx.x;
-        const long long gi = index_base + i;
+    const float* L = in_smem ? sm_chol : chol;
+    const float* mus = in_smem ? sm_mu : means;
+    const uint2 key = make_uint2((unsigned int)seed, (unsigned int)(seed >> 32));
+    const long long n_tiles = (n + SB - 1) / SB;
+    int it = 0;
+    for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
+        float* buf = reinterpret_cast<float*>(sm_raw1 + (size_t)(it & 1) * tile_bytes);
+        if (threadIdx.x == 0) mgb_tma_store_wait_read<1>();  // the store that last read this buffer (two tiles ago) is done
         __syncthreads();
+        const long long i = tile * SB + threadIdx.x;
+        const unsigned long long gi = (unsigned long long)(index_base + i);
+        float* row = buf + (size_t)threadIdx.x * D;
         if (i < n) {
-            // component of global index gi in the component-ordered stacking
-            int g = 0;
-            while (g + 1 < G && gi >= prefix[g + 1]) ++g;
-            uint2 key = make_uint2((unsigned int)seed, (unsigned int)(seed >> 32));
-            for (int d0 = 0; d0 < D; d0 += 4) {
-                uint4 r = philox4x32_10(make_uint4((unsigned int)gi, (unsigned int)((unsigned long long)gi >> 32), (unsigned int)(d0 >> 2), 0x6d67u), key);
-                float r0 = sqrtf(-2.f * __logf(u01(r.x))), r1 = sqrtf(-2.f * __logf(u01(r.z)));
-                float s0, c0, s1, c1;
-                __sincosf(6.283185307179586f * u01(r.y), &s0, &c0);
-                __sincosf(6.283185307179586f * u01(r.w), &s1, &c1);
-                float z[4] = {r0 * c0, r0 * s0, r1 * c1, r1 * s1};
-                for (int q = 0; q < 4 && d0 + q < D; ++q) row[d0 + q] = z[q];
-            }
-            // s = mu + L z, in place from the last row up (row d only needs z[0..d])
-            const float* L = chol + (size_t)g * D * D;
-            const float* mu = means + (size_t)g * D;
-            for (int d = D - 1; d >= 0; --d) {
-                float acc = __ldg(mu + d);
-                const float* Lr = L + (size_t)d * D;
-                for (int j = 0; j <= d; ++j) acc = fmaf(__ldg(Lr + j), row[j], acc);
-                row[d] = acc;
+            int g = 0;  // component of global index gi in the component-ordered stacking
+            while (g + 1 < G && (long long)gi >= pre.v[g + 1]) ++g;
+            if (NREG > 0) {
+                float s[NR];
+                mgb_sample_row_reg<NR>(reinterpret_cast<const float4*>(L + (size_t)g * D * LS), LS, mus + (size_t)g * D, D, gi, key, s);
+#pragma unroll
+                for (int d = 0; d < NR; ++d)
+                    if (d < D) row[d] = s[d];
+            } else {
+                mgb_sample_row_mem(L + (size_t)g * D * LS, LS, mus + (size_t)g * D, D, gi, key, row);
             }
         }
+        const long long base = tile * SB;
+        const bool full = aligned && base + SB <= n;
+        if (full) mgb_fence_proxy_async();  // generic-proxy writes of the tile visible to the async proxy
         __syncthreads();
-        // coalesced write-out of the tile
-        const long long base = tile * SAMPLE_BLOCK;
-        const long long remaining = (n - base) * (long long)D;
-        const int total = SAMPLE_BLOCK * D;
-        const int step_r = SAMPLE_BLOCK / D, step_c = SAMPLE_BLOCK % D;
-        int r = threadIdx.x / D, c = threadIdx.x % D;
-        float* dst = out + base * D;
-        for (int e = threadIdx.x; e < total; e += SAMPLE_BLOCK) {
-            if (e < remaining) dst[e] = sm[r * SROW + c];
-            r += step_r;
-            c += step_c;
-            if (c >= D) { c -= D; r += 1; }
+        if (full) {
+            if (threadIdx.x == 0) mgb_tma_store_1d(out + base * D, buf, (unsigned int)(SB * D * sizeof(float)));
+        } else {
+            const long long remaining = (n - base) * (long long)D;
+            float* dst = out + base * D;
+            for (int e = threadIdx.x; e < SB * D; e += SB)
+                if (e < remaining) dst[e] = buf[e];
         }
     }
+    if (threadIdx.x == 0) mgb_tma_store_wait_read<0>();
 }
 
 // ---------------------------------------------------------------------------
@@ -156,47 +139,61 @@ __global__ void __launch_bounds__(BP_COLS) mgb_backproject_simt(const float* __r
 
 // ---------------------------------------------------------------------------
 // K3: frames[n, T, P] = B[T, Nb] . coeffs[n, Nb, P]  (4 non-zeros per row of B)
-// One candidate at a time per CTA: its [Nb, P] coefficient block is read once
-// (coalesced) into shared memory, every output element is then 4 FMAs and the
-// output is written as one contiguous run.
+// One thread owns one (candidate, channel) pair and walks the T evaluation
+// times with a sliding window of 4 coefficients in registers: a coefficient is
+// loaded once per window move, not once per output (Nb loads and T stores per
+// thread for a full motion).  Lanes of a warp hold consecutive flat indices
+// i * P + p, so every load and store instruction of a warp covers one
+// contiguous 128-byte run.  Spans / weights are broadcast from shared memory.
 // ---------------------------------------------------------------------------
+#define K3_PARAM_T 96
+struct SplineTimes {  // small time lists travel as a kernel argument: no allocation, copy or sync per call
+    float4 w[K3_PARAM_T];
+    int span[K3_PARAM_T];
+};
+
+template <bool IN_PARAM>
 __global__ void __launch_bounds__(256) mgb_eval_frames_kernel(const float* __restrict__ coeffs, int Nb, int P, long long n,
                                                               const int* __restrict__ spans, const float4* __restrict__ w4, int T,
-                                                              float* __restrict__ frames) {
-    extern __shared__ __align__(16) float sm_c[];  // [Nb*P] + spans/weights
-    const int M = Nb * P;
-    float4* sm_w = reinterpret_cast<float4*>(sm_c + ((M + 3) & ~3));
+                                                              float* __restrict__ frames, const __grid_constant__ SplineTimes st) {
+    extern __shared__ __align__(16) unsigned char sm_raw3[];
+    float4* sm_w = reinterpret_cast<float4*>(sm_raw3);
     int* sm_span = reinterpret_cast<int*>(sm_w + T);
     for (int t = threadIdx.x; t < T; t += blockDim.x) {
-        sm_w[t] = w4[t];
-        sm_span[t] = spans[t];
+        sm_w[t] = IN_PARAM ? st.w[t] : w4[t];
+        sm_span[t] = IN_PARAM ? st.span[t] : spans[t];
     }
-    const int TP = T * P;
-    for (long long i = blockIdx.x; i < n; i += gridDim.x) {
-        __syncthreads();
-        const float* src = coeffs + (size_t)i * M;
-        if ((M & 3) == 0) {
-            const float4* s4 = reinterpret_cast<const float4*>(src);
-            float4* d4 = reinterpret_cast<float4*>(sm_c);
-            for (int e = threadIdx.x; e < (M >> 2); e += blockDim.x) d4[e] = __ldcs(s4 + e);
-        } else {
-            for (int e = threadIdx.x; e < M; e += blockDim.x) sm_c[e] = __ldcs(src + e);
-        }
-        __syncthreads();
-        float* dst = frames + (size_t)i * TP;
-        int t = threadIdx.x / P, pch = threadIdx.x % P;
-        const int step_t = blockDim.x / P, step_p = blockDim.x % P;
-        for (int o = threadIdx.x; o < TP; o += blockDim.x) {
+    __syncthreads();
+    const long long total = n * (long long)P;
+    const size_t M = (size_t)Nb * P;
+    const size_t TP = (size_t)T * P;
+    for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (long long)gridDim.x * blockDim.x) {
+        const long long i = e / P;
+        const int pch = (int)(e - i * P);
+        const float* __restrict__ src = coeffs + (size_t)i * M + pch;
+        float* __restrict__ dst = frames + (size_t)i * TP + pch;
+        int cur = -8;
+        float c0 = 0.f, c1 = 0.f, c2 = 0.f, c3 = 0.f;
+        for (int t = 0; t < T; ++t) {
+            const int sp = sm_span[t];
+            if (sp != cur) {
+                if (sp == cur + 1) {
+                    c0 = c1; c1 = c2; c2 = c3;
+                    c3 = __ldcs(src + (size_t)(sp + 3) * P);
+                } else {
+                    c0 = __ldcs(src + (size_t)sp * P);
+                    c1 = __ldcs(src + (size_t)(sp + 1) * P);
+                    c2 = __ldcs(src + (size_t)(sp + 2) * P);
+                    c3 = __ldcs(src + (size_t)(sp + 3) * P);
+                }
+                cur = sp;
+            }
             const float4 w = sm_w[t];
-            const float* c0 = sm_c + sm_span[t] * P + pch;
-            float v = w.x * c0[0];
-            v = fmaf(w.y, c0[P], v);
-            v = fmaf(w.z, c0[2 * P], v);
-            v = fmaf(w.w, c0[3 * P], v);
-            __stcs(dst + o, v);
-            t += step_t;
-            pch += step_p;
-            if (pch >= P) { pch -= P; t += 1; }
+            float v = w.x * c0;
+            v = fmaf(w.y, c1, v);
+            v = fmaf(w.z, c2, v);
+            v = fmaf(w.w, c3, v);
+            __stcs(dst + (size_t)t * P, v);
         }
     }
 }
@@ -206,7 +203,6 @@ __global__ void __launch_bounds__(256) mgb_eval_frames_kernel(const float* __res
 // is staged in shared memory (rows of P floats, odd stride), each thread walks
 // the parent chains from a per-call "plan" (node order with parents first).
 // ---------------------------------------------------------------------------
-#define MGB_QUAT_EPS 8.881784197001252e-16f
 
 __device__ __forceinline__ void quat_R(float w, float x, float y, float z, float* R) {
     float n = w * w + x * x + y * y + z * z;
@@ -332,64 +328,6 @@ __global__ void __launch_bounds__(FK_BLOCK) mgb_fk_kernel(const float* __restric
 }
 
 // ---------------------------------------------------------------------------
-// K5b: GMM log-density, thread per sample, s row in shared memory
-// ---------------------------------------------------------------------------
-#define LP_BLOCK 128
-__global__ void __launch_bounds__(LP_BLOCK) mgb_logpdf_kernel(const float* __restrict__ s, long long n, int D, int G, int NQ,
-                                                             const float4* __restrict__ gtab, const float* __restrict__ gc,
-                                                             float* __restrict__ out) {
-    extern __shared__ __align__(16) float sml[];
-    const int SROW = D | 1;
-    const long long n_tiles = (n + LP_BLOCK - 1) / LP_BLOCK;
-    for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-        const long long base = tile * LP_BLOCK;
-        __syncthreads();
-        {
-            const float* src = s + base * D;
-            const long long remaining = (n - base) * (long long)D;
-            const int total = LP_BLOCK * D;
-            const int step_r = LP_BLOCK / D, step_c = LP_BLOCK % D;
-            int r = threadIdx.x / D, c = threadIdx.x % D;
-            for (int e = threadIdx.x; e < total; e += LP_BLOCK) {
-                sml[r * SROW + c] = (e < remaining) ? __ldg(src + e) : 0.f;
-                r += step_r;
-                c += step_c;
-                if (c >= D) { c -= D; r += 1; }
-            }
-        }
-        __syncthreads();
-        const float* row = sml + threadIdx.x * SROW;
-        float mx = -INFINITY, ssum = 0.f;
-        for (int g = 0; g < G; ++g) {
-            float qf = 0.f;
-            for (int jq = 0; jq < NQ; ++jq) {
-                const float4* tr = gtab + (size_t)(g * NQ + jq) * (D + 1);
-                float4 y = __ldg(tr + D);
-                const int cnt = min(D, 4 * jq + 4);
-                for (int k = 0; k < cnt; ++k) {
-                    const float4 e = __ldg(tr + k);
-                    const float sk = row[k];
-                    y.x = fmaf(sk, e.x, y.x);
-                    y.y = fmaf(sk, e.y, y.y);
-                    y.z = fmaf(sk, e.z, y.z);
-                    y.w = fmaf(sk, e.w, y.w);
-                }
-                qf = fmaf(y.x, y.x, fmaf(y.y, y.y, fmaf(y.z, y.z, fmaf(y.w, y.w, qf))));
-            }
-            const float lp = __ldg(gc + g) - 0.5f * qf;
-            if (lp > mx) {
-                ssum = ssum * __expf(mx - lp) + 1.f;
-                mx = lp;
-            } else {
-                ssum += __expf(lp - mx);
-            }
-        }
-        const long long i = base + threadIdx.x;
-        if (i < n) out[i] = mx + __logf(ssum);
-    }
-}
-
-// ---------------------------------------------------------------------------
 // K7: one Lloyd step for a whole tree level.  Thread per sample: nearest of its
 // node's n_sub centroids, label out, then sums/counts accumulated with
 // warp-aggregated atomics when the whole warp hits the same (node, label).
@@ -429,6 +367,35 @@ __global__ void __launch_bounds__(256) mgb_kmeans_kernel(const float* __restrict
 // ===========================================================================
 // C ABI
 // ===========================================================================
+template <int NREG>
+static int launch_sample(const mgb_model* m, const MgbGmmPrefix& prefix, int64_t n, int64_t index_base, uint64_t seed, float* d_s,
+                         cudaStream_t stream) {
+    auto kern = mgb_sample_kernel<NREG>;
+    int sb = SAMPLE_BLOCK;
+    while (sb > 32 && 2 * (size_t)sb * m->D * sizeof(float) > 64 * 1024) sb >>= 1;
+    const size_t tile_bytes = ((size_t)sb * m->D * sizeof(float) + 127) & ~(size_t)127;
+    const size_t chol_bytes = ((size_t)m->G * m->D * m->LS + (size_t)m->G * m->D) * sizeof(float);
+    const int in_smem = (2 * tile_bytes + chol_bytes <= 96 * 1024) ? 1 : 0;
+    const size_t smem = 2 * tile_bytes + (in_smem ? chol_bytes : 0) + 128;
+    MGB_REQUIRE(smem <= 200 * 1024, "latent dimension too large for the sampler");
+    static bool configured = false;
+    if (!configured) {
+        MGB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        configured = true;
+    }
+    long long n_tiles = (n + sb - 1) / sb;
+    int occ = 1;
+    MGB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, sb, smem));
+    long long grid = (long long)sm_count() * (occ > 0 ? occ : 1);
+    if (grid > n_tiles) grid = n_tiles;
+    const int aligned = ((reinterpret_cast<uintptr_t>(d_s) & 15u) == 0 && ((size_t)sb * m->D * sizeof(float)) % 16 == 0) ? 1 : 0;
+    kern<<<(unsigned)grid, sb, smem, stream>>>(m->d_means, m->d_chol, m->LS, prefix, m->G, m->D, n, index_base,
+                                                        (unsigned long long)seed, in_smem, aligned, d_s);
+    mgb_count_launch();
+    MGB_CUDA(cudaGetLastError());
+    return MGB_OK;
+}
+
 extern "C" int mgb_sample(const mgb_model* m, int64_t n, int64_t index_base, const int64_t* h_counts, uint64_t seed,
                           float* d_s, void* stream_) {
     cudaStream_t stream = (cudaStream_t)stream_;
@@ -436,7 +403,7 @@ extern "C" int mgb_sample(const mgb_model* m, int64_t n, int64_t index_base, con
     MGB_REQUIRE(n >= 0 && index_base >= 0, "negative size");
     if (n == 0) return MGB_OK;
     MGB_REQUIRE(m->G <= MGB_MAX_GMM, "at most %d mixture components are supported by the sampler", MGB_MAX_GMM);
-    GmmPrefix prefix;  // passed by value as a kernel argument: no allocation, copy or sync per call
+    MgbGmmPrefix prefix;  // passed by value as a kernel argument: no allocation, copy or sync per call
     prefix.v[0] = 0;
     for (int g = 0; g < m->G; ++g) {
         MGB_REQUIRE(h_counts[g] >= 0, "negative component count");
@@ -445,23 +412,9 @@ extern "C" int mgb_sample(const mgb_model* m, int64_t n, int64_t index_base, con
     for (int g = m->G + 1; g <= MGB_MAX_GMM; ++g) prefix.v[g] = prefix.v[m->G];
     MGB_REQUIRE(index_base + n <= prefix.v[m->G], "component counts (%lld) do not cover [%lld, %lld)", prefix.v[m->G],
                 (long long)index_base, (long long)(index_base + n));
-    size_t smem = (size_t)SAMPLE_BLOCK * (m->D | 1) * sizeof(float);
-    MGB_REQUIRE(smem <= 200 * 1024, "latent dimension too large for the sampler");
-    static bool configured = false;
-    if (!configured) {
-        MGB_CUDA(cudaFuncSetAttribute(mgb_sample_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        configured = true;
-    }
-    long long n_tiles = (n + SAMPLE_BLOCK - 1) / SAMPLE_BLOCK;
-    int occ = 1;
-    MGB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, mgb_sample_kernel, SAMPLE_BLOCK, smem));
-    long long grid = (long long)sm_count() * (occ > 0 ? occ : 1);
-    if (grid > n_tiles) grid = n_tiles;
-    mgb_sample_kernel<<<(unsigned)grid, SAMPLE_BLOCK, smem, stream>>>(m->d_means, m->d_chol, prefix, m->G, m->D, n, index_base,
-                                                                    (unsigned long long)seed, d_s);
-    mgb_count_launch();
-    MGB_CUDA(cudaGetLastError());
-    return MGB_OK;
+    if (m->D <= 16) return launch_sample<16>(m, prefix, n, index_base, seed, d_s, stream);
+    if (m->D <= 32) return launch_sample<32>(m, prefix, n, index_base, seed, d_s, stream);
+    return launch_sample<0>(m, prefix, n, index_base, seed, d_s, stream);
 }
 
 extern "C" int mgb_backproject(const mgb_model* m, const float* d_s, int64_t n, float* d_coeffs, int32_t impl, void* stream_) {
@@ -490,6 +443,7 @@ extern "C" int mgb_eval_frames(const mgb_model* m, const float* d_coeffs, int64_
     MGB_REQUIRE(m && times && n_times > 0, "null argument");
     MGB_REQUIRE(n == 0 || (d_coeffs && d_frames), "null device pointer");
     if (n == 0) return MGB_OK;
+    SplineTimes st;
     std::vector<int> sp(n_times);
     std::vector<float4> w4(n_times);
     for (int t = 0; t < n_times; ++t) {
@@ -505,30 +459,37 @@ extern "C" int mgb_eval_frames(const mgb_model* m, const float* d_coeffs, int64_
         MGB_REQUIRE(span >= 0 && span + 4 <= m->Nb, "span out of range");
         sp[t] = span;
         w4[t] = make_float4((float)w[0], (float)w[1], (float)w[2], (float)w[3]);
+        if (t < K3_PARAM_T) {
+            st.span[t] = span;
+            st.w[t] = w4[t];
+        }
     }
+    const bool in_param = n_times <= K3_PARAM_T;
     int* d_sp = nullptr;
     float4* d_w4 = nullptr;
-    MGB_CUDA(cudaMallocAsync((void**)&d_sp, sizeof(int) * n_times, stream));
-    MGB_CUDA(cudaMallocAsync((void**)&d_w4, sizeof(float4) * n_times, stream));
-    MGB_CUDA(cudaMemcpyAsync(d_sp, sp.data(), sizeof(int) * n_times, cudaMemcpyHostToDevice, stream));
-    MGB_CUDA(cudaMemcpyAsync(d_w4, w4.data(), sizeof(float4) * n_times, cudaMemcpyHostToDevice, stream));
-    MGB_CUDA(cudaStreamSynchronize(stream));
-    size_t smem = (size_t)((m->M + 3) & ~3) * sizeof(float) + (size_t)n_times * (sizeof(float4) + sizeof(int)) + 16;
-    MGB_REQUIRE(smem <= 200 * 1024, "coefficient block too large for shared memory");
-    static bool configured = false;
-    if (!configured) {
-        MGB_CUDA(cudaFuncSetAttribute(mgb_eval_frames_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        configured = true;
+    if (!in_param) {
+        MGB_CUDA(cudaMallocAsync((void**)&d_sp, sizeof(int) * n_times, stream));
+        MGB_CUDA(cudaMallocAsync((void**)&d_w4, sizeof(float4) * n_times, stream));
+        MGB_CUDA(cudaMemcpyAsync(d_sp, sp.data(), sizeof(int) * n_times, cudaMemcpyHostToDevice, stream));
+        MGB_CUDA(cudaMemcpyAsync(d_w4, w4.data(), sizeof(float4) * n_times, cudaMemcpyHostToDevice, stream));
+        MGB_CUDA(cudaStreamSynchronize(stream));  // sp / w4 are stack-owned host buffers
     }
+    size_t smem = (size_t)n_times * (sizeof(float4) + sizeof(int)) + 16;
+    MGB_REQUIRE(smem <= 200 * 1024, "too many evaluation times for shared memory");
+    auto kern = in_param ? mgb_eval_frames_kernel<true> : mgb_eval_frames_kernel<false>;
+    if (smem > 48 * 1024) MGB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     int occ = 1;
-    MGB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, mgb_eval_frames_kernel, 256, smem));
+    MGB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, 256, smem));
     long long grid = (long long)sm_count() * (occ > 0 ? occ : 1);
-    if (grid > n) grid = n;
-    mgb_eval_frames_kernel<<<(unsigned)grid, 256, smem, stream>>>(d_coeffs, m->Nb, m->P, n, d_sp, d_w4, n_times, d_frames);
+    const long long blocks = (n * (long long)m->P + 255) / 256;
+    if (grid > blocks) grid = blocks;
+    kern<<<(unsigned)grid, 256, smem, stream>>>(d_coeffs, m->Nb, m->P, n, d_sp, d_w4, n_times, d_frames, st);
     mgb_count_launch();
     MGB_CUDA(cudaGetLastError());
-    MGB_CUDA(cudaFreeAsync(d_sp, stream));
-    MGB_CUDA(cudaFreeAsync(d_w4, stream));
+    if (!in_param) {
+        MGB_CUDA(cudaFreeAsync(d_sp, stream));
+        MGB_CUDA(cudaFreeAsync(d_w4, stream));
+    }
     return MGB_OK;
 }
 
@@ -593,28 +554,6 @@ extern "C" int mgb_fk(const mgb_model* m, const float* d_frames, int64_t n_frame
     mgb_count_launch();
     MGB_CUDA(cudaGetLastError());
     MGB_CUDA(cudaFreeAsync(d_plan, stream));
-    return MGB_OK;
-}
-
-extern "C" int mgb_logpdf(const mgb_model* m, const float* d_s, int64_t n, float* d_logpdf, void* stream_) {
-    cudaStream_t stream = (cudaStream_t)stream_;
-    MGB_REQUIRE(m && (n == 0 || (d_s && d_logpdf)), "null argument");
-    if (n == 0) return MGB_OK;
-    size_t smem = (size_t)LP_BLOCK * (m->D | 1) * sizeof(float);
-    MGB_REQUIRE(smem <= 200 * 1024, "latent dimension too large");
-    static bool configured = false;
-    if (!configured) {
-        MGB_CUDA(cudaFuncSetAttribute(mgb_logpdf_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        configured = true;
-    }
-    int occ = 1;
-    MGB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, mgb_logpdf_kernel, LP_BLOCK, smem));
-    long long n_tiles = (n + LP_BLOCK - 1) / LP_BLOCK;
-    long long grid = (long long)sm_count() * (occ > 0 ? occ : 1);
-    if (grid > n_tiles) grid = n_tiles;
-    mgb_logpdf_kernel<<<(unsigned)grid, LP_BLOCK, smem, stream>>>(d_s, n, m->D, m->G, m->NQ, m->d_gmm_tab, m->d_gmm_c, d_logpdf);
-    mgb_count_launch();
-    MGB_CUDA(cudaGetLastError());
     return MGB_OK;
 }
 

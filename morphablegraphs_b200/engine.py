@@ -487,6 +487,34 @@ class DeviceConstraints(object):
             out["terms"] = terms
         return out
 
+    def sample_score(self, n, seed=0, counts=None, n_total=None, index_base=0, k=1, error_scale=1.0, quality_scale=0.0,
+                     magnitude_scale=0.0, return_cost=False):
+        """Fused K1 + K6 (mgb_sample_score): draw candidates [index_base, index_base + n) of a job of
+        n_total samples in-kernel and score them; nothing but the k best (cost, global index) is
+        written.  `DeviceModel.sample(1, seed, index_base=idx, counts=counts, n_total=n_total)`
+        regenerates a winning row bit-exactly."""
+        torch = _torch()
+        dm = self.dmodel
+        n_total = int(n if n_total is None else n_total)
+        if counts is None:
+            counts = dm.component_counts(n_total, seed)
+        counts = np.ascontiguousarray(counts, dtype=np.int64)
+        need_cost = return_cost or k > 1
+        cost = torch.empty((int(n),), dtype=torch.float32, device=dm.torch_device) if need_cost else None
+        best_cost = torch.empty((max(k, 1),), dtype=torch.float32, device=dm.torch_device)
+        best_idx = torch.empty((max(k, 1),), dtype=torch.int64, device=dm.torch_device)
+        ws = dm.workspace()
+        ptr = lambda t: C.c_void_p(t.data_ptr()) if t is not None else C.c_void_p(0)
+        with torch.cuda.device(dm.device):
+            _lib.check(self.lib.mgb_sample_score(dm.handle, self.handle, int(n), int(index_base),
+                                                 counts.ctypes.data_as(C.POINTER(C.c_int64)), C.c_uint64(int(seed) & 0xFFFFFFFFFFFFFFFF),
+                                                 float(error_scale), float(quality_scale), float(magnitude_scale), ptr(cost), int(k),
+                                                 ptr(best_cost), ptr(best_idx), ptr(ws), ws.numel(), dm._stream()))
+        out = {"best_cost": best_cost[:k], "best_idx": best_idx[:k], "counts": counts}
+        if return_cost:
+            out["cost"] = cost
+        return out
+
     def score_host(self, samples, k=1, error_scale=1.0, quality_scale=0.0, magnitude_scale=0.0, return_cost=False,
                    index_base=0):
         """Score HOST candidates (numpy float32/float64 [n, D], or a pinned CPU torch tensor):

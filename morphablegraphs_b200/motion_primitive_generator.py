@@ -90,22 +90,22 @@ class MotionPrimitiveGenerator(object):
 
     # ------------------------------------------------------------------ :192-206
     def _get_best_fit_sample_using_gmm(self, graph_node, mp_constraints, prev_mp_name="", prev_frames=None, prev_parameters=None):
-        """Sample N on the device (K1), score (K6), arg-min; only the winning row and its cost
-        come back to the host."""
-        mp = graph_node.motion_primitive
+        """Sample N and score them in ONE fused launch (mgb_sample_score: K1 + K6, candidates never
+        leave the registers), arg-min on the device; the winning row is regenerated from its
+        global index (Philox is keyed by it) and only that row and its cost come back to the host."""
         dc = _device_constraints(graph_node, mp_constraints, prev_frames)
         dm = dc.dmodel
         seed = int(self._rng.randint(0, 2 ** 31 - 1))
         n = int(self.n_random_samples)
-        samples = dm.sample(n, seed=seed)
         obj = self.objective
-        res = dc.score(samples, k=1, error_scale=getattr(obj, "error_scale", 1.0),
-                       quality_scale=getattr(obj, "quality_scale", 0.0), magnitude_scale=getattr(obj, "magnitude_scale", 0.0))
+        res = dc.sample_score(n, seed=seed, k=1, error_scale=getattr(obj, "error_scale", 1.0),
+                              quality_scale=getattr(obj, "quality_scale", 0.0), magnitude_scale=getattr(obj, "magnitude_scale", 0.0))
         best_idx = int(res["best_idx"][0].item())
         min_error = float(res["best_cost"][0].item())
         mp_constraints.min_error = min_error
         mp_constraints.evaluations += n
-        return samples[best_idx].cpu().numpy().astype(np.float64)
+        best = dm.sample(1, seed=seed, index_base=best_idx, counts=res["counts"], n_total=n)
+        return best[0].cpu().numpy().astype(np.float64)
 
     # ------------------------------------------------------------------ :220-228
     def _get_best_fit_sample_using_cluster_tree(self, graph_node, constraints, prev_frames, n_candidates=-1):

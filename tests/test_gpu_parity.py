@@ -179,6 +179,27 @@ def test_full_size_properties(big):
     assert rel_err(cost[pick].cpu().numpy(), ref).max() < RTOL
 
 
+def test_fused_sample_score(big):
+    """mgb_sample_score (K1 + K6 in one launch, candidates never stored) == mgb_sample then mgb_score."""
+    dm, dc = big.dm, big.dc
+    for n, base, total in ((70_001, 0, 70_001), (50_000, 123_457, 400_000)):
+        counts = dm.component_counts(total, seed=11)
+        S = dm.sample(n, seed=11, counts=counts, index_base=base, n_total=total)
+        for kw in ({}, {"quality_scale": 0.1}, {"magnitude_scale": 2.0}):
+            a = dc.score(S, k=1, return_cost=True, index_base=base, **kw)
+            b = dc.sample_score(n, seed=11, counts=counts, n_total=total, index_base=base, k=1, return_cost=True, **kw)
+            assert rel_err(b["cost"].cpu().numpy(), a["cost"].cpu().numpy()).max() < 1e-6
+            ia, ib = int(a["best_idx"][0]), int(b["best_idx"][0])
+            assert ia == ib or abs(float(a["cost"][ia - base]) - float(a["cost"][ib - base])) < 1e-6
+            # the winning row regenerated from its global index is the row that was scored
+            row = dm.sample(1, seed=11, counts=counts, index_base=ib, n_total=total)
+            assert torch.equal(row[0], S[ib - base])
+    k = 4
+    r = dc.sample_score(5000, seed=3, k=k, return_cost=True)
+    order = np.lexsort((np.arange(5000), r["cost"].cpu().numpy()))[:k]
+    assert list(r["best_idx"].cpu().numpy()) == list(order)
+
+
 def test_sampler_distribution(big):
     """The reference's RNG stream cannot be reproduced on the device, so K1 is checked
     distributionally: component frequencies, per-component mean and covariance."""
