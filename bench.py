@@ -314,6 +314,7 @@ def run_b200(args):
     value = n * world * args.steps / (total_ms * 1e-3)
 
     # ---- e2e: host samples (float64, pinned) through the reference-facing call ----------
+    dm.sample(n, seed=2024, counts=counts, n_total=n * world, index_base=rank * n, out=S)
     host = torch.empty((n, dm.D), dtype=torch.float64).pin_memory()
     host.copy_(S.double().cpu())
     e2e_steps = max(3, min(args.steps, 10))
@@ -376,7 +377,9 @@ def kernel_rooflines(ctx, args):
         for k in ("K2_backproject", "K3_spline_eval", "K5a_score_frames"):
             work[k] = sw[k]
             work[k]["n"] = ns
-        times["K2_backproject"] = timed(torch, lambda: dm.backproject(Ss, impl=1, out=coeffs), 5, flush)
+        times["K2_backproject"] = timed(torch, lambda: dm.backproject(Ss, impl=2, out=coeffs), 5, flush)      # tcgen05 3xTF32
+        work["K2_backproject_simt"] = dict(work["K2_backproject"], bound="fp32")
+        times["K2_backproject_simt"] = timed(torch, lambda: dm.backproject(Ss, impl=1, out=coeffs), 5, flush)
         times["K3_spline_eval"] = timed(torch, lambda: dm.eval_frames(coeffs, dc.times, out=frames), 5, flush)
         times["K5a_score_frames"] = timed(torch, lambda: dc.score(Ss, k=1, quality_scale=qs, frames=frames), 5, flush)
     out = {}

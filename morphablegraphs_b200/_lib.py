@@ -23,18 +23,35 @@ def sources():
 
 
 def build(force=False, verbose=False):
-    """Compile csrc/*.cu into csrc/libmgb200.so for sm_100a (cross-compiles without a GPU)."""
+    """Compile csrc/*.cu into csrc/libmgb200.so for sm_100a (cross-compiles without a GPU):
+    one object per translation unit (compiled in parallel, only when stale), then one link."""
+    from concurrent.futures import ThreadPoolExecutor
     srcs = sources()
-    deps = srcs + glob.glob(os.path.join(CSRC, "*.cuh")) + [INCLUDE]
-    if not force and os.path.exists(LIB_PATH):
-        if os.path.getmtime(LIB_PATH) >= max(os.path.getmtime(p) for p in deps):
-            return LIB_PATH
+    headers = glob.glob(os.path.join(CSRC, "*.cuh")) + [INCLUDE]
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
-    defines = ["-DMGB_HAVE_TC"] if any(os.path.basename(s) == "mgb_gemm_tc.cu" for s in srcs) else []
-    cmd = [nvcc] + NVCC_FLAGS + defines + ["-o", LIB_PATH] + srcs
-    if verbose:
-        print(" ".join(cmd))
-    subprocess.run(cmd, check=True)
+    objdir = os.path.join(CSRC, "build")
+    os.makedirs(objdir, exist_ok=True)
+    hdr_time = max(os.path.getmtime(p) for p in headers)
+    flags = [f for f in NVCC_FLAGS if f != "-shared"]
+    jobs = []
+    objs = []
+    for src in srcs:
+        obj = os.path.join(objdir, os.path.basename(src)[:-3] + ".o")
+        objs.append(obj)
+        stale = force or not os.path.exists(obj) or os.path.getmtime(obj) < max(os.path.getmtime(src), hdr_time)
+        if stale:
+            jobs.append([nvcc] + flags + ["-c", "-o", obj, src])
+
+    def run(cmd):
+        if verbose:
+            print(" ".join(cmd))
+        subprocess.run(cmd, check=True)
+
+    if jobs:
+        with ThreadPoolExecutor(max_workers=len(jobs)) as ex:
+            list(ex.map(run, jobs))
+    if jobs or not os.path.exists(LIB_PATH):
+        run([nvcc] + NVCC_FLAGS + ["-o", LIB_PATH] + objs)
     return LIB_PATH
 
 

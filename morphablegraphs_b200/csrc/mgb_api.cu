@@ -240,6 +240,12 @@ extern "C" int mgb_model_create(const mgb_model_desc* d, int device, mgb_model**
         mgb_model_destroy(m);
         return rc;
     }
+    // tensor-core back-projection operand (3xTF32 stage images); models too large for the
+    // shared-memory plan simply keep the SIMT path
+    if (mgb_backproject_tc_prepare(m) != MGB_OK) {
+        cudaFree(m->d_Bsplit);
+        m->d_Bsplit = nullptr;
+    }
     *out = m;
     return MGB_OK;
 }
@@ -758,11 +764,3 @@ extern "C" int mgb_score_host(const mgb_model* m_, const mgb_constraints* c, con
     return MGB_OK;
 }
 
-// placeholders until the tensor-core translation unit is linked in
-#ifndef MGB_HAVE_TC
-int mgb_backproject_tc(const mgb_model*, const float*, int64_t, float*, cudaStream_t) {
-    mgb_set_error("tensor-core back-projection not built");
-    return MGB_E_UNSUPPORTED;
-}
-int mgb_backproject_tc_prepare(mgb_model*) { return MGB_E_UNSUPPORTED; }
-#endif

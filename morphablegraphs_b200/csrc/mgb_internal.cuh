@@ -101,8 +101,8 @@ struct mgb_model {
     float* d_offset = nullptr;     // [n_nodes][3]
     float* d_fixed_rot = nullptr;  // [n_nodes][9]
     // tensor-core back-projection operands (TF32 hi/lo split), built lazily
-    float* d_Bsplit = nullptr;
-    int Ksplit = 0;
+    float* d_Bsplit = nullptr;  // packed stage images of E' (see mgb_tc.cu: TcB)
+    int tc_Kp = 0, tc_Np = 0, tc_NC = 0, tc_KC = 0, tc_nst = 0;
     // private streams / staging for the host-buffer entry
     cudaStream_t copy_stream = nullptr, compute_stream = nullptr;
     void* pinned[2] = {nullptr, nullptr};

@@ -1,0 +1,410 @@
+// Tensor-core (tcgen05 / TMEM) kernels of libmgb200.so, sm_100a.
+//
+// K2-TC  mgb_backproject_tc: coeffs[n, M] = s[n, :K] . E'[K, M] + mean'[M]
+//        (MotionPrimitive.back_project_spatial_coeffs, reference motion_primitive.py:236-256)
+//        as a 3xTF32 GEMM: every fp32 operand is split into two TF32 numbers (hi + lo) and
+//        the product is accumulated as a_hi.b_hi + a_lo.b_hi + a_hi.b_lo in the fp32 TMEM
+//        accumulator, which restores ~fp32 accuracy (2^-21 relative per product) - the
+//        north star's 1e-4 parity bound cannot be met by single-pass TF32 (2^-11).
+//
+// Structure of every kernel here (one persistent CTA per SM, 192 threads):
+//   warp 0      B producer: the constant operand (basis / GMM tables) was packed on the host
+//               into per-stage images that already have the UMMA canonical K-major layout,
+//               so a stage is ONE 1-D TMA bulk copy (UBLKCP) from L2 into shared memory,
+//               ring of NST stages on full/empty mbarriers.
+//   warp 1      MMA issuer: one lane issues tcgen05.mma (SASS UTCMMA), 128 x NC x 8 per
+//               instruction, accumulators double-buffered in TMEM (2 x 256 columns) so the
+//               epilogue of N-chunk c overlaps the MMAs of chunk c + 1; tcgen05.commit
+//               releases the B stage / publishes the accumulator.
+//   warps 2-5   A producers + epilogue: thread r owns candidate row r of the 128-row tile
+//               (= TMEM lane r): writes the hi/lo split of its latent vector into the
+//               canonical A layout, later reads its accumulator row with tcgen05.ld (LDTM).
+#include <math.h>
+#include <string.h>
+
+#include <algorithm>
+#include <vector>
+
+#include "mgb_internal.cuh"
+#include "mgb_tc.cuh"
+
+#define MGB_HAVE_TC 1
+
+namespace {
+
+constexpr int TC_THREADS = 192;
+constexpr int TC_M = 128;        // rows (candidates) per tile = TMEM lanes
+constexpr int TC_MAX_STAGES = 4;
+constexpr int TC_TMEM_COLS = 512;
+constexpr int TC_BUF_COLS = 256;  // one accumulator buffer
+
+// packed constant operand (device)
+struct TcB {
+    const float* data;
+    int Kp;  // K padded to a multiple of 8
+    int Np;  // N padded to a multiple of 16
+    int NC;  // N-chunk (multiple of 16, <= 256)
+    int KC;  // K-chunk (multiple of 8)
+    __host__ __device__ int n_nc() const { return (Np + NC - 1) / NC; }
+    __host__ __device__ int n_kc() const { return (Kp + KC - 1) / KC; }
+    __host__ __device__ int wc(int c) const { return min(NC, Np - c * NC); }
+    __host__ __device__ int wk(int kc) const { return min(KC, Kp - kc * KC); }
+    // float offset of stage image (c, kc): [hi block wc x wk][lo block wc x wk]
+    __host__ __device__ size_t off(int c, int kc) const { return 2 * ((size_t)Kp * c * NC + (size_t)wc(c) * kc * KC); }
+    __host__ __device__ size_t total() const { return 2 * (size_t)Kp * Np; }
+};
+
+struct TcBackprojectParams {
+    TcB B;
+    const float* s;     // [n, D]
+    const float* mean;  // [M]
+    float* out;         // [n, M]
+    long long n;
+    int D, K, M;
+    int nst;            // B stages
+};
+
+// shared-memory carve-up, identical on host and device
+struct TcSmem {
+    size_t a_hi, a_lo, b_stage, bars, tmem_ptr, total;
+    size_t stage_bytes;
+};
+__host__ __device__ inline TcSmem tc_smem_plan(int Kp, int NC, int KC, int nst) {
+    TcSmem p;
+    size_t off = 0;
+    p.a_hi = off; off += (size_t)TC_M * Kp * 4;
+    p.a_lo = off; off += (size_t)TC_M * Kp * 4;
+    p.stage_bytes = (size_t)2 * NC * KC * 4;
+    p.b_stage = off; off += p.stage_bytes * nst;
+    p.bars = off; off += 8 * (2 * TC_MAX_STAGES + 2 + 4);
+    p.tmem_ptr = off; off += 16;
+    p.total = off;
+    return p;
+}
+
+struct TcBars {
+    unsigned long long* b_full;   // [TC_MAX_STAGES]
+    unsigned long long* b_empty;  // [TC_MAX_STAGES]
+    unsigned long long* a_full;
+    unsigned long long* a_empty;
+    unsigned long long* t_full;   // [2]
+    unsigned long long* t_empty;  // [2]
+};
+
+__device__ __forceinline__ TcBars tc_bars(unsigned char* base) {
+    TcBars b;
+    unsigned long long* p = reinterpret_cast<unsigned long long*>(base);
+    b.b_full = p;
+    b.b_empty = p + TC_MAX_STAGES;
+    b.a_full = p + 2 * TC_MAX_STAGES;
+    b.a_empty = p + 2 * TC_MAX_STAGES + 1;
+    b.t_full = p + 2 * TC_MAX_STAGES + 2;
+    b.t_empty = p + 2 * TC_MAX_STAGES + 4;
+    return b;
+}
+
+// ---- role bodies shared by the tensor-core kernels ---------------------------------------
+
+// warp 0, one lane: stream every stage image of B once per tile
+__device__ __forceinline__ void tc_b_producer(const TcB& B, unsigned char* sm_stage, size_t stage_bytes, int nst, const TcBars& bars,
+                                              long long my_tiles) {
+    unsigned int it = 0;
+    const int n_nc = B.n_nc(), n_kc = B.n_kc();
+    for (long long t = 0; t < my_tiles; ++t) {
+        for (int c = 0; c < n_nc; ++c) {
+            const int wc = B.wc(c);
+            for (int kc = 0; kc < n_kc; ++kc, ++it) {
+                const int st = it % nst;
+                const unsigned int ph = (it / nst) & 1u;
+                mgb_mbar_wait(&bars.b_empty[st], ph ^ 1u);
+                const unsigned int bytes = (unsigned int)(2 * wc * B.wk(kc) * 4);
+                mgb_mbar_expect_tx(&bars.b_full[st], bytes);
+                mgb_bulk_g2s(sm_stage + (size_t)st * stage_bytes, B.data + B.off(c, kc), bytes, &bars.b_full[st]);
+            }
+        }
+    }
+}
+
+// warp 1, one lane: all MMAs of this CTA
+__device__ __forceinline__ void tc_mma_issuer(const TcB& B, uint32_t a_hi_addr, uint32_t a_lo_addr, uint32_t stage_addr, size_t stage_bytes,
+                                              int nst, const TcBars& bars, uint32_t tmem_base, long long my_tiles) {
+    unsigned int it = 0, cc = 0;
+    const int n_nc = B.n_nc(), n_kc = B.n_kc();
+    const uint32_t A_LBO = TC_M * 16, SBO = 128;
+    for (long long t = 0; t < my_tiles; ++t) {
+        mgb_mbar_wait(bars.a_full, (unsigned int)(t & 1));
+        mgb_tc_fence_after();
+        for (int c = 0; c < n_nc; ++c, ++cc) {
+            const int wc = B.wc(c);
+            const unsigned int buf = cc & 1u;
+            mgb_mbar_wait(&bars.t_empty[buf], ((cc >> 1) & 1u) ^ 1u);
+            mgb_tc_fence_after();
+            const uint32_t d_addr = tmem_base + buf * TC_BUF_COLS;
+            const uint32_t idesc = mgb_umma_idesc_tf32(TC_M, wc);
+            const uint32_t B_LBO = (uint32_t)wc * 16;
+            uint32_t acc = 0;
+            for (int kc = 0; kc < n_kc; ++kc, ++it) {
+                const int st = it % nst;
+                mgb_mbar_wait(&bars.b_full[st], (it / nst) & 1u);
+                mgb_tc_fence_after();
+                const int wk = B.wk(kc);
+                const uint32_t b_hi = stage_addr + (uint32_t)(st * stage_bytes);
+                const uint32_t b_lo = b_hi + (uint32_t)(wc * wk * 4);
+                for (int j = 0; j < wk / 8; ++j) {
+                    const uint32_t a_off = (uint32_t)((kc * B.KC) / 4 + 2 * j) * A_LBO;
+                    const uint32_t b_off = (uint32_t)(2 * j) * B_LBO;
+                    const uint64_t da_hi = mgb_umma_desc(a_hi_addr + a_off, A_LBO, SBO);
+                    const uint64_t da_lo = mgb_umma_desc(a_lo_addr + a_off, A_LBO, SBO);
+                    const uint64_t db_hi = mgb_umma_desc(b_hi + b_off, B_LBO, SBO);
+                    const uint64_t db_lo = mgb_umma_desc(b_lo + b_off, B_LBO, SBO);
+                    mgb_umma_tf32(d_addr, da_lo, db_hi, idesc, acc);  // small terms first
+                    mgb_umma_tf32(d_addr, da_hi, db_lo, idesc, 1u);
+                    mgb_umma_tf32(d_addr, da_hi, db_hi, idesc, 1u);
+                    acc = 1u;
+                }
+                mgb_umma_commit(&bars.b_empty[st]);
+            }
+            mgb_umma_commit(&bars.t_full[buf]);
+        }
+        mgb_umma_commit(bars.a_empty);
+    }
+}
+
+// one row of A: hi / lo split of `cnt` values (zero padded to Kp), written as float4 chunks
+// into the canonical layout (threads of a warp write 512 contiguous bytes per chunk)
+template <typename Load>
+__device__ __forceinline__ void tc_write_a_row(unsigned char* a_hi, unsigned char* a_lo, int row, int Kp, int cnt, Load load) {
+    for (int k0 = 0; k0 < Kp; k0 += 4) {
+        float h[4], l[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const float v = (k0 + q < cnt) ? load(k0 + q) : 0.f;
+            mgb_tf32_split(v, h[q], l[q]);
+        }
+        const uint32_t off = mgb_canon_off((uint32_t)row, (uint32_t)k0, TC_M);
+        *reinterpret_cast<float4*>(a_hi + off) = make_float4(h[0], h[1], h[2], h[3]);
+        *reinterpret_cast<float4*>(a_lo + off) = make_float4(l[0], l[1], l[2], l[3]);
+    }
+}
+
+// ---------------------------------------------------------------------------
+// K2-TC
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(TC_THREADS, 1) mgb_backproject_tc_kernel(const __grid_constant__ TcBackprojectParams p) {
+    extern __shared__ __align__(1024) unsigned char smem[];
+    const TcSmem plan = tc_smem_plan(p.B.Kp, p.B.NC, p.B.KC, p.nst);
+    const TcBars bars = tc_bars(smem + plan.bars);
+    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(smem + plan.tmem_ptr);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const long long n_tiles = (p.n + TC_M - 1) / TC_M;
+    const long long my_tiles = (n_tiles > blockIdx.x) ? (n_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < TC_MAX_STAGES; ++i) {
+            mgb_mbar_init(&bars.b_full[i], 1);
+            mgb_mbar_init(&bars.b_empty[i], 1);
+        }
+        mgb_mbar_init(bars.a_full, 128);
+        mgb_mbar_init(bars.a_empty, 1);
+        for (int i = 0; i < 2; ++i) {
+            mgb_mbar_init(&bars.t_full[i], 1);
+            mgb_mbar_init(&bars.t_empty[i], 128);
+        }
+        mgb_fence_barrier_init();
+    }
+    if (warp == 1) mgb_tmem_alloc(tmem_ptr, TC_TMEM_COLS);
+    mgb_tc_fence_before();
+    __syncthreads();
+    mgb_tc_fence_after();
+    const uint32_t tmem_base = *tmem_ptr;
+
+    if (warp == 0) {
+        if (lane == 0) tc_b_producer(p.B, smem + plan.b_stage, plan.stage_bytes, p.nst, bars, my_tiles);
+    } else if (warp == 1) {
+        if (lane == 0)
+            tc_mma_issuer(p.B, mgb_smem_u32(smem + plan.a_hi), mgb_smem_u32(smem + plan.a_lo), mgb_smem_u32(smem + plan.b_stage),
+                          plan.stage_bytes, p.nst, bars, tmem_base, my_tiles);
+    } else {
+        const int row = 32 * (warp & 3) + lane;  // TMEM lane quarter of this warp
+        const uint32_t lane_addr = tmem_base + ((uint32_t)(32 * (warp & 3)) << 16);
+        const int n_nc = p.B.n_nc();
+        const int vec = (p.M % 4 == 0) ? 4 : (p.M % 2 == 0) ? 2 : 1;
+        unsigned int cc = 0;
+        for (long long t = 0; t < my_tiles; ++t) {
+            const long long g = (blockIdx.x + t * gridDim.x) * TC_M + row;
+            const bool valid = g < p.n;
+            mgb_mbar_wait(bars.a_empty, (unsigned int)(t & 1) ^ 1u);
+            const float* srow = p.s + (size_t)(valid ? g : 0) * p.D;
+            tc_write_a_row(smem + plan.a_hi, smem + plan.a_lo, row, p.B.Kp, valid ? p.K : 0, [&](int k) { return __ldg(srow + k); });
+            mgb_fence_proxy_async();
+            mgb_mbar_arrive(bars.a_full);
+            float* orow = p.out + (size_t)(valid ? g : 0) * p.M;
+            for (int c = 0; c < n_nc; ++c, ++cc) {
+                const unsigned int buf = cc & 1u;
+                mgb_mbar_wait(&bars.t_full[buf], (cc >> 1) & 1u);
+                mgb_tc_fence_after();
+                const int wc = p.B.wc(c);
+                for (int b0 = 0; b0 < wc; b0 += 32) {
+                    float v[32];
+                    mgb_tmem_ld32(lane_addr + buf * TC_BUF_COLS + b0, v);
+                    const int col0 = c * p.B.NC + b0;
+                    if (valid) {
+                        if (vec == 4) {
+#pragma unroll
+                            for (int i = 0; i < 32; i += 4) {
+                                if (col0 + i < p.M) {
+                                    const float4 mu = __ldg(reinterpret_cast<const float4*>(p.mean + col0 + i));
+                                    __stcs(reinterpret_cast<float4*>(orow + col0 + i),
+                                           make_float4(v[i] + mu.x, v[i + 1] + mu.y, v[i + 2] + mu.z, v[i + 3] + mu.w));
+                                }
+                            }
+                        } else if (vec == 2) {
+#pragma unroll
+                            for (int i = 0; i < 32; i += 2) {
+                                if (col0 + i < p.M) {
+                                    const float2 mu = __ldg(reinterpret_cast<const float2*>(p.mean + col0 + i));
+                                    __stcs(reinterpret_cast<float2*>(orow + col0 + i), make_float2(v[i] + mu.x, v[i + 1] + mu.y));
+                                }
+                            }
+                        } else {
+#pragma unroll
+                            for (int i = 0; i < 32; ++i)
+                                if (col0 + i < p.M) __stcs(orow + col0 + i, v[i] + __ldg(p.mean + col0 + i));
+                        }
+                    }
+                }
+                mgb_tc_fence_before();
+                mgb_mbar_arrive(&bars.t_empty[buf]);
+            }
+        }
+    }
+    mgb_tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        mgb_tc_fence_after();
+        mgb_tmem_dealloc(tmem_base, TC_TMEM_COLS);
+    }
+}
+
+}  // namespace
+
+// ===========================================================================
+// host side
+// ===========================================================================
+namespace {
+
+// cvt.rna.tf32.f32 on the host: round to nearest, ties away from zero, 13 bits dropped
+float tf32_rna_host(float x) {
+    uint32_t u;
+    memcpy(&u, &x, 4);
+    if ((u & 0x7F800000u) == 0x7F800000u) return x;
+    u = (u + 0x1000u) & 0xFFFFE000u;
+    float r;
+    memcpy(&r, &u, 4);
+    return r;
+}
+
+// Pack logical B[k][n] (fp64, k < K, n < N; element(k, n) = get(k, n)) into per-stage images
+// in the UMMA canonical K-major layout, hi block then lo block (TcB::off).
+template <typename Get>
+std::vector<float> tc_pack_b(TcB& B, int K, int N, Get get) {
+    std::vector<float> out(B.total(), 0.f);
+    for (int c = 0; c < B.n_nc(); ++c) {
+        const int wc = B.wc(c);
+        for (int kc = 0; kc < B.n_kc(); ++kc) {
+            const int wk = B.wk(kc);
+            float* hi = out.data() + B.off(c, kc);
+            float* lo = hi + (size_t)wc * wk;
+            for (int nn = 0; nn < wc; ++nn) {
+                const int n = c * B.NC + nn;
+                for (int kk = 0; kk < wk; ++kk) {
+                    const int k = kc * B.KC + kk;
+                    const double v = (k < K && n < N) ? get(k, n) : 0.0;
+                    const float h = tf32_rna_host((float)v);
+                    const float l = tf32_rna_host((float)(v - (double)h));
+                    const size_t o = mgb_canon_off((uint32_t)nn, (uint32_t)kk, (uint32_t)wc) / 4;
+                    hi[o] = h;
+                    lo[o] = l;
+                }
+            }
+        }
+    }
+    return out;
+}
+
+constexpr size_t TC_SMEM_BUDGET = 220 * 1024;
+
+// choose the chunking for an operand with K rows / N columns next to a resident A tile
+bool tc_plan_b(TcB& B, int K, int N, int* nst_out) {
+    B.Kp = (K + 7) & ~7;
+    B.Np = (N + 15) & ~15;
+    B.NC = std::min(256, B.Np);
+    B.KC = std::min(16, B.Kp);
+    for (int nst = TC_MAX_STAGES; nst >= 2; --nst) {
+        if (tc_smem_plan(B.Kp, B.NC, B.KC, nst).total + 1024 <= TC_SMEM_BUDGET) {
+            *nst_out = nst;
+            return true;
+        }
+    }
+    B.KC = 8;
+    for (int nst = TC_MAX_STAGES; nst >= 2; --nst) {
+        if (tc_smem_plan(B.Kp, B.NC, B.KC, nst).total + 1024 <= TC_SMEM_BUDGET) {
+            *nst_out = nst;
+            return true;
+        }
+    }
+    return false;
+}
+
+int tc_num_sms() {
+    static int n = 0;
+    if (n == 0) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+        if (n <= 0) n = 148;
+    }
+    return n;
+}
+
+}  // namespace
+
+// Packs E' once per model (hi/lo TF32 stage images); thread-compatible with the rest of the
+// handle: called from mgb_model_create, so the handle stays immutable afterwards.
+int mgb_backproject_tc_prepare(mgb_model* m) {
+    TcB B;
+    int nst = 0;
+    if (!tc_plan_b(B, m->K, m->M, &nst)) {
+        mgb_set_error("tensor-core back-projection: K = %d does not fit shared memory", m->K);
+        return MGB_E_UNSUPPORTED;
+    }
+    const int M = m->M;
+    std::vector<float> packed = tc_pack_b(B, m->K, M, [&](int k, int n) { return m->E[(size_t)k * M + n]; });
+    MGB_CUDA(cudaMalloc((void**)&m->d_Bsplit, packed.size() * sizeof(float)));
+    MGB_CUDA(cudaMemcpy(m->d_Bsplit, packed.data(), packed.size() * sizeof(float), cudaMemcpyHostToDevice));
+    m->tc_Kp = B.Kp; m->tc_Np = B.Np; m->tc_NC = B.NC; m->tc_KC = B.KC; m->tc_nst = nst;
+    return MGB_OK;
+}
+
+int mgb_backproject_tc(const mgb_model* m, const float* d_s, int64_t n, float* d_coeffs, cudaStream_t stream) {
+    MGB_REQUIRE(m->d_Bsplit != nullptr, "tensor-core back-projection operand was not prepared for this model");
+    MGB_REQUIRE((reinterpret_cast<uintptr_t>(d_coeffs) & 15u) == 0, "d_coeffs must be 16-byte aligned");
+    TcBackprojectParams p;
+    p.B.data = m->d_Bsplit;
+    p.B.Kp = m->tc_Kp; p.B.Np = m->tc_Np; p.B.NC = m->tc_NC; p.B.KC = m->tc_KC;
+    p.nst = m->tc_nst;
+    p.s = d_s; p.mean = m->d_mean; p.out = d_coeffs;
+    p.n = n; p.D = m->D; p.K = m->K; p.M = m->M;
+    const size_t smem = tc_smem_plan(p.B.Kp, p.B.NC, p.B.KC, p.nst).total;
+    static bool configured = false;
+    if (!configured) {
+        MGB_CUDA(cudaFuncSetAttribute(mgb_backproject_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM_BUDGET));
+        configured = true;
+    }
+    const long long n_tiles = (n + TC_M - 1) / TC_M;
+    const int grid = (int)std::min<long long>(n_tiles, tc_num_sms());
+    mgb_backproject_tc_kernel<<<grid, TC_THREADS, smem, stream>>>(p);
+    mgb_count_launch();
+    MGB_CUDA(cudaGetLastError());
+    return MGB_OK;
+}

@@ -83,6 +83,13 @@ def test_staged_pipeline(case):
     S = torch.as_tensor(case.samples, device="cuda").float()
     coeffs = case.dm.backproject(S, impl=1)
     assert rel_err(coeffs[:8].cpu().numpy(), g["coeffs"]).max() < RTOL
+    # K2 on the tensor cores (tcgen05, 3xTF32): same parity bound, and ~fp32 agreement with the SIMT kernel
+    coeffs_tc = case.dm.backproject(S, impl=2)
+    assert rel_err(coeffs_tc[:8].cpu().numpy(), g["coeffs"]).max() < RTOL
+    assert rel_err(coeffs_tc.cpu().numpy(), coeffs.cpu().numpy()).max() < 2e-5
+    for n_ragged in (1, 127, 129, 1000):       # ragged last tile / fewer rows than a tile
+        c_r = case.dm.backproject(S[:n_ragged], impl=2)
+        assert rel_err(c_r.cpu().numpy(), coeffs[:n_ragged].cpu().numpy()).max() < 2e-5
     frames = case.dm.eval_frames(coeffs, g["key_times"])
     assert rel_err(frames.cpu().numpy(), g["key_frames"]).max() < RTOL
     n_mv = g["motion_vectors"].shape[0]
