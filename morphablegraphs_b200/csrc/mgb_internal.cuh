@@ -102,7 +102,7 @@ struct mgb_model {
     float* d_fixed_rot = nullptr;  // [n_nodes][9]
     // tensor-core back-projection operands (TF32 hi/lo split), built lazily
     float* d_Bsplit = nullptr;  // packed stage images of E' (see mgb_tc.cu: TcB)
-    int tc_Kp = 0, tc_Np = 0, tc_NC = 0, tc_KC = 0, tc_nst = 0;
+    int tc_Kp = 0, tc_Np = 0, tc_NC = 0, tc_KC = 0, tc_nst = 0, tc_W = 0, tc_nbuf = 1;
     // private streams / staging for the host-buffer entry
     cudaStream_t copy_stream = nullptr, compute_stream = nullptr;
     void* pinned[2] = {nullptr, nullptr};

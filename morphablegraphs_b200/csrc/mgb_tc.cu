@@ -20,6 +20,7 @@
 //               (= TMEM lane r): writes the hi/lo split of its latent vector into the
 //               canonical A layout, later reads its accumulator row with tcgen05.ld (LDTM).
 #include <math.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
@@ -29,10 +30,13 @@
 #include "mgb_tc.cuh"
 
 #define MGB_HAVE_TC 1
+#ifndef MGB_ST
+#define MGB_ST(p, v) (*(p) = (v))
+#endif
 
 namespace {
 
-constexpr int TC_THREADS = 192;
+constexpr int TC_THREADS = 320;    // warp 0 B producer, warp 1 MMA issuer, warps 2-5 / 6-9 epilogue groups of TMEM buffer 0 / 1
 constexpr int TC_M = 128;        // rows (candidates) per tile = TMEM lanes
 constexpr int TC_MAX_STAGES = 4;
 constexpr int TC_TMEM_COLS = 512;
@@ -62,20 +66,25 @@ struct TcBackprojectParams {
     long long n;
     int D, K, M;
     int nst;            // B stages
+    int W;              // epilogue staging width: a warp writes W consecutive floats of a row back to back
+    int nbuf;           // staging buffers (1 or 2)
+    int dbg;            // MGB_TC_DBG bits (timing experiments): 1 = no global stores, 2 = no TMEM reads either
 };
 
 // shared-memory carve-up, identical on host and device
 struct TcSmem {
-    size_t a_hi, a_lo, b_stage, bars, tmem_ptr, total;
+    size_t a_hi, a_lo, b_stage, out_stage, bars, tmem_ptr, total;
     size_t stage_bytes;
 };
-__host__ __device__ inline TcSmem tc_smem_plan(int Kp, int NC, int KC, int nst) {
+// W: columns of the epilogue's row staging (0 = none); a staged row has W + 4 floats (16-byte aligned, conflict-free 128-bit accesses)
+__host__ __device__ inline TcSmem tc_smem_plan(int Kp, int NC, int KC, int nst, int W = 0, int nbuf = 1) {
     TcSmem p;
     size_t off = 0;
     p.a_hi = off; off += (size_t)TC_M * Kp * 4;
     p.a_lo = off; off += (size_t)TC_M * Kp * 4;
     p.stage_bytes = (size_t)2 * NC * KC * 4;
     p.b_stage = off; off += p.stage_bytes * nst;
+    p.out_stage = off; off += (W > 0) ? (size_t)nbuf * TC_M * (W + 4) * 4 : 0;
     p.bars = off; off += 8 * (2 * TC_MAX_STAGES + 2 + 4);
     p.tmem_ptr = off; off += 16;
     p.total = off;
@@ -187,12 +196,38 @@ __device__ __forceinline__ void tc_write_a_row(unsigned char* a_hi, unsigned cha
     }
 }
 
+
+// staging [32][SS] -> global rows: row after row, consecutive instructions cover consecutive bytes of a row;
+// 8 independent shared loads are in flight before their 8 stores issue
+template <typename V>
+__device__ __forceinline__ void tc_store_rows(const float* stg, int SS, float* obase, int M, int n_rows, int ncol, int W, int lane) {
+    constexpr int VW = sizeof(V) / 4;
+    const int steps = max(1, W / (32 * VW));          // store instructions per row (power of two)
+    const int sh = 31 - __clz(steps);
+    const int total = 16 << sh;  // 16 rows per warp
+    for (int i0 = 0; i0 < total; i0 += 8) {
+        V tmp[8];
+        bool ok[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            const int i = i0 + u, r = i >> sh, ci = VW * (lane + 32 * (i & (steps - 1)));
+            ok[u] = r < n_rows && ci < ncol;
+            if (ok[u]) tmp[u] = *reinterpret_cast<const V*>(stg + r * SS + ci);
+        }
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            const int i = i0 + u, r = i >> sh, ci = VW * (lane + 32 * (i & (steps - 1)));
+            if (ok[u]) __stcs(reinterpret_cast<V*>(obase + (size_t)r * M + ci), tmp[u]);
+        }
+    }
+}
+
 // ---------------------------------------------------------------------------
 // K2-TC
 // ---------------------------------------------------------------------------
 __global__ void __launch_bounds__(TC_THREADS, 1) mgb_backproject_tc_kernel(const __grid_constant__ TcBackprojectParams p) {
     extern __shared__ __align__(1024) unsigned char smem[];
-    const TcSmem plan = tc_smem_plan(p.B.Kp, p.B.NC, p.B.KC, p.nst);
+    const TcSmem plan = tc_smem_plan(p.B.Kp, p.B.NC, p.B.KC, p.nst, p.W, p.nbuf);
     const TcBars bars = tc_bars(smem + plan.bars);
     uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(smem + plan.tmem_ptr);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -208,7 +243,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mgb_backproject_tc_kernel(const
         mgb_mbar_init(bars.a_empty, 1);
         for (int i = 0; i < 2; ++i) {
             mgb_mbar_init(&bars.t_full[i], 1);
-            mgb_mbar_init(&bars.t_empty[i], 128);
+            mgb_mbar_init(&bars.t_empty[i], 256);
         }
         mgb_fence_barrier_init();
     }
@@ -225,56 +260,79 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mgb_backproject_tc_kernel(const
             tc_mma_issuer(p.B, mgb_smem_u32(smem + plan.a_hi), mgb_smem_u32(smem + plan.a_lo), mgb_smem_u32(smem + plan.b_stage),
                           plan.stage_bytes, p.nst, bars, tmem_base, my_tiles);
     } else {
-        const int row = 32 * (warp & 3) + lane;  // TMEM lane quarter of this warp
-        const uint32_t lane_addr = tmem_base + ((uint32_t)(32 * (warp & 3)) << 16);
+        const int wq = warp & 3;            // TMEM lane quarter of this warp
+        const int ew = warp - 2;            // epilogue warp 0..7
+        const int h = ew >> 2;              // which half of a column group this warp moves out of TMEM
+        const int row = 32 * wq + lane;
+        const uint32_t lane_addr = tmem_base + ((uint32_t)(32 * wq) << 16);
+        const int W = p.W, SS = W + 4;
+        float* stg0 = reinterpret_cast<float*>(smem + plan.out_stage);  // nbuf x [128][W + 4]
         const int n_nc = p.B.n_nc();
-        const int vec = (p.M % 4 == 0) ? 4 : (p.M % 2 == 0) ? 2 : 1;
-        unsigned int cc = 0;
-        for (long long t = 0; t < my_tiles; ++t) {
+        const int M = p.M;
+        const int vec = (M % 4 == 0) ? 4 : (M % 2 == 0) ? 2 : 1;
+        unsigned int cc = 0, gi = 0;
+        // A row of tile t: [s[:K] | 1] so that row K of the packed operand (the mean) is added by the GEMM itself
+        auto write_a = [&](long long t) {
             const long long g = (blockIdx.x + t * gridDim.x) * TC_M + row;
             const bool valid = g < p.n;
             mgb_mbar_wait(bars.a_empty, (unsigned int)(t & 1) ^ 1u);
             const float* srow = p.s + (size_t)(valid ? g : 0) * p.D;
-            tc_write_a_row(smem + plan.a_hi, smem + plan.a_lo, row, p.B.Kp, valid ? p.K : 0, [&](int k) { return __ldg(srow + k); });
+            const int K = p.K;
+            tc_write_a_row(smem + plan.a_hi, smem + plan.a_lo, row, p.B.Kp, valid ? K + 1 : 0, [&](int k) { return k < K ? __ldg(srow + k) : 1.f; });
             mgb_fence_proxy_async();
             mgb_mbar_arrive(bars.a_full);
-            float* orow = p.out + (size_t)(valid ? g : 0) * p.M;
+        };
+        if (h == 0 && my_tiles > 0) write_a(0);
+        for (long long t = 0; t < my_tiles; ++t) {
+            const long long tile0 = (blockIdx.x + t * gridDim.x) * TC_M;
+            // store phase: this warp writes rows 16 ew .. 16 ew + 15 of the tile, so the CTA's 8 warps cover one
+            // compact run of 128 rows x W columns at a time (what the memory system writes back best)
+            const int n_rows = (int)max((long long)0, min((long long)16, p.n - tile0 - 16 * ew));
             for (int c = 0; c < n_nc; ++c, ++cc) {
+                // refill A for the next tile at this tile's last chunk: its MMAs are all issued by then
+                if (h == 0 && c == n_nc - 1 && t + 1 < my_tiles) write_a(t + 1);
                 const unsigned int buf = cc & 1u;
                 mgb_mbar_wait(&bars.t_full[buf], (cc >> 1) & 1u);
                 mgb_tc_fence_after();
                 const int wc = p.B.wc(c);
-                for (int b0 = 0; b0 < wc; b0 += 32) {
-                    float v[32];
-                    mgb_tmem_ld32(lane_addr + buf * TC_BUF_COLS + b0, v);
-                    const int col0 = c * p.B.NC + b0;
-                    if (valid) {
-                        if (vec == 4) {
+                for (int w0 = 0; w0 < wc; w0 += W, ++gi) {
+                    const int col0 = c * p.B.NC + w0;   // first column of this group
+                    const int ncol = min(W, M - col0);  // valid columns of the group (CTA-uniform)
+                    const bool last = (w0 + W >= wc) || (col0 + W >= M);
+                    float* stg = stg0 + (size_t)(p.nbuf == 2 ? (gi & 1u) : 0u) * TC_M * SS;
+                    if (ncol > 0) {
+                        if (p.nbuf == 1) asm volatile("bar.sync 1, 256;" ::: "memory");  // stores of the previous group have read the staging
+                        // TMEM -> registers -> staging, thread-per-row: this warp moves columns [h W/2, (h+1) W/2) of its 32 rows
+                        for (int b0 = h * (W >> 1); b0 < (h + 1) * (W >> 1) && b0 < ncol && !(p.dbg & 4); b0 += 32) {
+                            float v[32];
+                            mgb_tmem_ld32(lane_addr + buf * TC_BUF_COLS + w0 + b0, v);
 #pragma unroll
-                            for (int i = 0; i < 32; i += 4) {
-                                if (col0 + i < p.M) {
-                                    const float4 mu = __ldg(reinterpret_cast<const float4*>(p.mean + col0 + i));
-                                    __stcs(reinterpret_cast<float4*>(orow + col0 + i),
-                                           make_float4(v[i] + mu.x, v[i + 1] + mu.y, v[i + 2] + mu.z, v[i + 3] + mu.w));
-                                }
-                            }
-                        } else if (vec == 2) {
-#pragma unroll
-                            for (int i = 0; i < 32; i += 2) {
-                                if (col0 + i < p.M) {
-                                    const float2 mu = __ldg(reinterpret_cast<const float2*>(p.mean + col0 + i));
-                                    __stcs(reinterpret_cast<float2*>(orow + col0 + i), make_float2(v[i] + mu.x, v[i + 1] + mu.y));
-                                }
-                            }
-                        } else {
-#pragma unroll
-                            for (int i = 0; i < 32; ++i)
-                                if (col0 + i < p.M) __stcs(orow + col0 + i, v[i] + __ldg(p.mean + col0 + i));
+                            for (int i = 0; i < 32; i += 4) *reinterpret_cast<float4*>(stg + row * SS + b0 + i) = make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]);
                         }
                     }
+                    if (last) {  // accumulator buffer drained: hand it back before the stores
+                        mgb_tc_fence_before();
+                        mgb_mbar_arrive_relaxed(&bars.t_empty[buf]);
+                    }
+                    if (ncol <= 0) break;
+                    asm volatile("bar.sync 1, 256;" ::: "memory");  // staging of this group complete
+                    float* obase = p.out + (size_t)(tile0 + 16 * ew) * M + col0;
+                    const float* srows = stg + (size_t)16 * ew * SS;
+                    if (p.dbg & 1) {
+                        if (srows[lane] == 123.456f) obase[0] = 0.f;
+                    } else if (vec == 4) {
+                        tc_store_rows<float4>(srows, SS, obase, M, n_rows, ncol, W, lane);
+                    } else if (vec == 2) {
+                        tc_store_rows<float2>(srows, SS, obase, M, n_rows, ncol, W, lane);
+                    } else {
+                        for (int r = 0; r < n_rows; ++r)
+                            for (int ci = lane; ci < ncol; ci += 32) __stcs(obase + (size_t)r * M + ci, srows[r * SS + ci]);
+                    }
+                    if (last) {
+                        ++gi;
+                        break;
+                    }
                 }
-                mgb_tc_fence_before();
-                mgb_mbar_arrive(&bars.t_empty[buf]);
             }
         }
     }
@@ -335,22 +393,29 @@ std::vector<float> tc_pack_b(TcB& B, int K, int N, Get get) {
 constexpr size_t TC_SMEM_BUDGET = 220 * 1024;
 
 // choose the chunking for an operand with K rows / N columns next to a resident A tile
-bool tc_plan_b(TcB& B, int K, int N, int* nst_out) {
+bool tc_plan_b(TcB& B, int K, int N, int* nst_out, int* W_out = nullptr, int* nbuf_out = nullptr) {
     B.Kp = (K + 7) & ~7;
     B.Np = (N + 15) & ~15;
     B.NC = std::min(256, B.Np);
-    B.KC = std::min(16, B.Kp);
-    for (int nst = TC_MAX_STAGES; nst >= 2; --nst) {
-        if (tc_smem_plan(B.Kp, B.NC, B.KC, nst).total + 1024 <= TC_SMEM_BUDGET) {
-            *nst_out = nst;
-            return true;
-        }
-    }
-    B.KC = 8;
-    for (int nst = TC_MAX_STAGES; nst >= 2; --nst) {
-        if (tc_smem_plan(B.Kp, B.NC, B.KC, nst).total + 1024 <= TC_SMEM_BUDGET) {
-            *nst_out = nst;
-            return true;
+    // epilogue staging (width, buffers) in order of preference, then B stage depth / size
+    const int cand[5][2] = {{128, 2}, {256, 1}, {128, 1}, {64, 2}, {64, 1}};
+    int forced_w = 0, forced_nb = 0;
+    if (const char* e = getenv("MGB_TC_W")) forced_w = atoi(e);
+    if (const char* e = getenv("MGB_TC_NBUF")) forced_nb = atoi(e);
+    for (int wi = 0; wi < (W_out ? 5 : 1); ++wi) {
+        const int W = W_out ? cand[wi][0] : 0, nbuf = W_out ? cand[wi][1] : 1;
+        if (W_out && ((forced_w && W != forced_w) || (forced_nb && nbuf != forced_nb))) continue;
+        const int KCs[2] = {16, 8};
+        for (int ki = 0; ki < 2; ++ki) {
+            B.KC = std::min(KCs[ki], B.Kp);
+            for (int nst = TC_MAX_STAGES; nst >= 2; --nst) {
+                if (tc_smem_plan(B.Kp, B.NC, B.KC, nst, W, nbuf).total + 1024 <= TC_SMEM_BUDGET) {
+                    *nst_out = nst;
+                    if (W_out) *W_out = W;
+                    if (nbuf_out) *nbuf_out = nbuf;
+                    return true;
+                }
+            }
         }
     }
     return false;
@@ -374,15 +439,17 @@ int tc_num_sms() {
 int mgb_backproject_tc_prepare(mgb_model* m) {
     TcB B;
     int nst = 0;
-    if (!tc_plan_b(B, m->K, m->M, &nst)) {
+    int W = 0, nbuf = 1;
+    if (!tc_plan_b(B, m->K + 1, m->M, &nst, &W, &nbuf)) {
         mgb_set_error("tensor-core back-projection: K = %d does not fit shared memory", m->K);
         return MGB_E_UNSUPPORTED;
     }
     const int M = m->M;
-    std::vector<float> packed = tc_pack_b(B, m->K, M, [&](int k, int n) { return m->E[(size_t)k * M + n]; });
+    const int K = m->K;  // row K of the operand is the mean: the A tile carries a column of ones
+    std::vector<float> packed = tc_pack_b(B, K + 1, M, [&](int k, int n) { return k < K ? m->E[(size_t)k * M + n] : m->mean[n]; });
     MGB_CUDA(cudaMalloc((void**)&m->d_Bsplit, packed.size() * sizeof(float)));
     MGB_CUDA(cudaMemcpy(m->d_Bsplit, packed.data(), packed.size() * sizeof(float), cudaMemcpyHostToDevice));
-    m->tc_Kp = B.Kp; m->tc_Np = B.Np; m->tc_NC = B.NC; m->tc_KC = B.KC; m->tc_nst = nst;
+    m->tc_Kp = B.Kp; m->tc_Np = B.Np; m->tc_NC = B.NC; m->tc_KC = B.KC; m->tc_nst = nst; m->tc_W = W; m->tc_nbuf = nbuf;
     return MGB_OK;
 }
 
@@ -393,9 +460,12 @@ int mgb_backproject_tc(const mgb_model* m, const float* d_s, int64_t n, float* d
     p.B.data = m->d_Bsplit;
     p.B.Kp = m->tc_Kp; p.B.Np = m->tc_Np; p.B.NC = m->tc_NC; p.B.KC = m->tc_KC;
     p.nst = m->tc_nst;
+    p.W = m->tc_W;
+    p.nbuf = m->tc_nbuf;
     p.s = d_s; p.mean = m->d_mean; p.out = d_coeffs;
     p.n = n; p.D = m->D; p.K = m->K; p.M = m->M;
-    const size_t smem = tc_smem_plan(p.B.Kp, p.B.NC, p.B.KC, p.nst).total;
+    { const char* e = getenv("MGB_TC_DBG"); p.dbg = e ? atoi(e) : 0; }
+    const size_t smem = tc_smem_plan(p.B.Kp, p.B.NC, p.B.KC, p.nst, p.W, p.nbuf).total;
     static bool configured = false;
     if (!configured) {
         MGB_CUDA(cudaFuncSetAttribute(mgb_backproject_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM_BUDGET));

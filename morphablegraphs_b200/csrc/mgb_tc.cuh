@@ -27,6 +27,11 @@ __device__ __forceinline__ void mgb_tf32_split(float x, float& hi, float& lo) {
 __device__ __forceinline__ void mgb_mbar_arrive(unsigned long long* bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(mgb_smem_u32(bar)) : "memory");
 }
+// arrival without release semantics: does not order (or wait for) this thread's earlier global stores;
+// TMEM reads are ordered by tcgen05.wait::ld + tcgen05.fence::before_thread_sync instead
+__device__ __forceinline__ void mgb_mbar_arrive_relaxed(unsigned long long* bar) {
+    asm volatile("mbarrier.arrive.relaxed.cta.shared::cta.b64 _, [%0];" ::"r"(mgb_smem_u32(bar)) : "memory");
+}
 __device__ __forceinline__ void mgb_mbar_expect_tx(unsigned long long* bar, unsigned int bytes) {
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(mgb_smem_u32(bar)), "r"(bytes) : "memory");
 }

@@ -1,0 +1,57 @@
+#!/usr/bin/env python
+"""Run ONE kernel of libmgb200.so a few times on cuda:0 (the target of ncu captures).
+usage: python tools/run_kernel.py <k1|k2tc|k2simt|k3|k6|k1k6|k5b> [--shape S|L] [--n N] [--reps R]"""
+import argparse
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import torch  # noqa: E402
+import bench  # noqa: E402
+from morphablegraphs_b200 import engine  # noqa: E402
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("kernel")
+    ap.add_argument("--shape", default="S")
+    ap.add_argument("--n", type=int, default=1_000_000)
+    ap.add_argument("--reps", type=int, default=3)
+    a = ap.parse_args()
+    wl = "S1M" if a.shape == "S" else "L4M"
+    node, skeleton, mpc, prev = bench.build_case(wl)
+    qs = bench.WORKLOADS[wl]["quality_scale"]
+    dm = engine.DeviceModel(node, skeleton, 0)
+    dc = engine.DeviceConstraints(dm, mpc, prev)
+    n = a.n
+    counts = dm.component_counts(n, seed=2024)
+    S = dm.sample(n, seed=1, counts=counts)
+    coeffs = frames = None
+    if a.kernel in ("k2tc", "k2simt", "k3"):
+        coeffs = torch.empty((n, dm.Nb, dm.P), dtype=torch.float32, device="cuda")
+    if a.kernel == "k3":
+        dm.backproject(S, impl=2, out=coeffs)
+        frames = torch.empty((n, len(dc.times), dm.P), dtype=torch.float32, device="cuda")
+    fns = {
+        "k1": lambda: dm.sample(n, seed=7, counts=counts, out=S),
+        "k2tc": lambda: dm.backproject(S, impl=2, out=coeffs),
+        "k2simt": lambda: dm.backproject(S, impl=1, out=coeffs),
+        "k3": lambda: dm.eval_frames(coeffs, dc.times, out=frames),
+        "k6": lambda: dc.score(S, k=1, quality_scale=qs),
+        "k1k6": lambda: dc.sample_score(n, seed=7, counts=counts, k=1, quality_scale=qs),
+        "k5b": lambda: dm.logpdf(S),
+    }
+    fn = fns[a.kernel]
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    for _ in range(a.reps):
+        e0.record()
+        fn()
+        e1.record()
+        torch.cuda.synchronize()
+        print("%s shape=%s n=%d: %.4f ms" % (a.kernel, a.shape, n, e0.elapsed_time(e1)))
+
+
+if __name__ == "__main__":
+    main()
