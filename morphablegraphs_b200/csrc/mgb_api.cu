@@ -190,6 +190,8 @@ extern "C" int mgb_model_create(const mgb_model_desc* d, int device, mgb_model**
     const int LS = m->LS;
     std::vector<float> gc(G), chol((size_t)G * D * LS, 0.f), means((size_t)G * D);
     std::vector<double> L, Pc((size_t)D * D);
+    m->prec_chol.assign((size_t)G * D * D, 0.0);
+    m->gmm_bias.assign((size_t)G * D, 0.0);
     for (int g = 0; g < G; ++g) {
         if (!cholesky_lower(d->gmm_covars + (size_t)g * D * D, D, L)) {
             mgb_set_error("covariance of GMM component %d is not positive definite", g);
@@ -224,6 +226,11 @@ extern "C" int mgb_model_create(const mgb_model_desc* d, int device, mgb_model**
             }
             row[0] = make_float4((float)bias[0], (float)bias[1], (float)bias[2], (float)bias[3]);
         }
+        for (int k = 0; k < D; ++k)
+            for (int j = 0; j < D; ++j) {
+                m->prec_chol[((size_t)g * D + k) * D + j] = Pc[(size_t)k * D + j];
+                m->gmm_bias[(size_t)g * D + j] -= mu[k] * Pc[(size_t)k * D + j];
+            }
         for (int i = 0; i < D; ++i)
             for (int j = 0; j <= i; ++j) chol[((size_t)g * D + i) * LS + j] = (float)L[(size_t)i * D + j];
         for (int i = 0; i < D; ++i) means[(size_t)g * D + i] = (float)mu[i];
@@ -246,6 +253,10 @@ extern "C" int mgb_model_create(const mgb_model_desc* d, int device, mgb_model**
         cudaFree(m->d_Bsplit);
         m->d_Bsplit = nullptr;
     }
+    if (mgb_score_tc_prepare_model(m) != MGB_OK) {
+        cudaFree(m->d_Bgmm);
+        m->d_Bgmm = nullptr;
+    }
     *out = m;
     return MGB_OK;
 }
@@ -255,7 +266,7 @@ extern "C" void mgb_model_destroy(mgb_model* m) {
     cudaSetDevice(m->device);
     cudaFree(m->d_E); cudaFree(m->d_mean); cudaFree(m->d_gmm_tab); cudaFree(m->d_gmm_c); cudaFree(m->d_chol);
     cudaFree(m->d_means); cudaFree(m->d_parent); cudaFree(m->d_type); cudaFree(m->d_channel); cudaFree(m->d_offset);
-    cudaFree(m->d_fixed_rot); cudaFree(m->d_Bsplit); cudaFree(m->d_ws);
+    cudaFree(m->d_fixed_rot); cudaFree(m->d_Bsplit); cudaFree(m->d_Bgmm); cudaFree(m->d_ws);
     for (int b = 0; b < 2; ++b) {
         if (m->pinned[b]) cudaFreeHost(m->pinned[b]);
         cudaFree(m->d_stage[b]);
@@ -537,6 +548,7 @@ extern "C" int mgb_constraints_pack(const mgb_model* m, const mgb_constraint_des
     const int KP = (K + 3) & ~3;  // rows padded with zeros to a multiple of 4; entry 0 of a quad is the bias (mean) row
     c->KP = KP;
     c->tab.assign((size_t)c->n_quads * (KP + 1) * 4, 0.f);
+    c->tab64.assign((size_t)c->n_quads * (KP + 1) * 4, 0.0);
     for (int q = 0; q < c->n_quads; ++q) {
         const int slot = C.quads[q].first, group = C.quads[q].second;
         const int ch0 = group < 0 ? 0 : 3 + 4 * group;
@@ -551,10 +563,13 @@ extern "C" int mgb_constraints_pack(const mgb_model* m, const mgb_constraint_des
                 }
                 const int row = (k < K) ? 1 + k : 0;
                 c->tab[((size_t)q * (KP + 1) + row) * 4 + ch] = (float)acc;
+                c->tab64[((size_t)q * (KP + 1) + row) * 4 + ch] = acc;
             }
         }
     }
     c->ops_fused = C.ops;
+    c->quad_slot.resize(C.quads.size());
+    for (size_t q = 0; q < C.quads.size(); ++q) c->quad_slot[q] = C.quads[q].first;
     // frames-mode program: quads index channels of the materialised frames
     int cp0_slot = -1;
     for (int t = 0; t < n_times; ++t)
@@ -591,12 +606,17 @@ extern "C" int mgb_constraints_pack(const mgb_model* m, const mgb_constraint_des
         mgb_constraints_destroy(c);
         return rc;
     }
+    if (mgb_score_tc_prepare_constraints(m, c) != MGB_OK) {  // e.g. a slot with more quads than one chunk: SIMT path only
+        cudaFree(c->d_Bq); cudaFree(c->d_ops_tc); cudaFree(c->d_phase_tc);
+        c->d_Bq = nullptr; c->d_ops_tc = nullptr; c->d_phase_tc = nullptr;
+    }
     *out = c;
     return MGB_OK;
 }
 
 extern "C" void mgb_constraints_destroy(mgb_constraints* c) {
     if (!c) return;
+    cudaFree(c->d_Bq); cudaFree(c->d_ops_tc); cudaFree(c->d_phase_tc);
     cudaFree(c->d_tab); cudaFree(c->d_ops_fused); cudaFree(c->d_ops_frames); cudaFree(c->d_cst);
     delete c;
 }

@@ -103,6 +103,11 @@ struct mgb_model {
     // tensor-core back-projection operands (TF32 hi/lo split), built lazily
     float* d_Bsplit = nullptr;  // packed stage images of E' (see mgb_tc.cu: TcB)
     int tc_Kp = 0, tc_Np = 0, tc_NC = 0, tc_KC = 0, tc_nst = 0, tc_W = 0, tc_nbuf = 1;
+    // tensor-core score path (D > 32): GMM precision factors as a packed 3xTF32 operand
+    std::vector<double> prec_chol;  // [G][D][D] upper factors P_g (y = (s - mu_g) . P_g), fp64
+    std::vector<double> gmm_bias;   // [G][D]   -mu_g . P_g
+    float* d_Bgmm = nullptr;
+    int tcg_Kp = 0, tcg_Np = 0, tcg_NC = 0, tcg_KC = 0, tcg_CW = 0;
     // private streams / staging for the host-buffer entry
     cudaStream_t copy_stream = nullptr, compute_stream = nullptr;
     void* pinned[2] = {nullptr, nullptr};
@@ -126,6 +131,15 @@ struct mgb_constraints {
     std::vector<MgbOp> ops_frames;  // quads index channels of materialised frames: slot * P + channel
     std::vector<float> cst;
     std::vector<float> tab;  // [n_quads][KP+1][4]
+    std::vector<double> tab64;  // same in fp64 (source of the hi/lo split of the tensor-core operand)
+    std::vector<int> quad_slot;  // evaluation slot of every quad (quads of a slot are contiguous)
+    float* d_Bq = nullptr;      // packed quad operand of the tensor-core score path (models with D > 32): every N-chunk
+                                // holds whole slots, so the program can run chunk by chunk
+    int tcq_Kp = 0, tcq_Np = 0, tcq_NC = 0, tcq_KC = 0;
+    std::vector<MgbOp> ops_tc;   // program with quad fields = position inside their chunk
+    std::vector<int> phase_tc;   // [n_chunks + 1] op index where the ops of chunk c begin
+    MgbOp* d_ops_tc = nullptr;
+    int* d_phase_tc = nullptr;
     std::vector<double> times;
     std::vector<int> spans;
     std::vector<double> weights;
@@ -189,3 +203,9 @@ int mgb_launch_score(const mgb_model* m, const mgb_constraints* c, int mode, con
                      cudaStream_t stream);
 int mgb_backproject_tc(const mgb_model* m, const float* d_s, int64_t n, float* d_coeffs, cudaStream_t stream);
 int mgb_backproject_tc_prepare(mgb_model* m);
+// tensor-core score path (mgb_tc.cu): operands are packed at handle creation for models with D > 32
+int mgb_score_tc_prepare_model(mgb_model* m);
+int mgb_score_tc_prepare_constraints(const mgb_model* m, mgb_constraints* c);
+bool mgb_score_tc_usable(const mgb_model* m, const mgb_constraints* c, float quality_scale);
+int mgb_launch_score_tc(const mgb_model* m, const mgb_constraints* c, const ScoreParams& p, int s_is_f64, float quality_scale,
+                        cudaStream_t stream);

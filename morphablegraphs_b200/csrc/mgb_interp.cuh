@@ -26,247 +26,263 @@ __device__ __forceinline__ float dist3(const float* a, const float* b) {
 }
 
 
-template <int CPT, typename QuadFn, typename EmitFn>
-__device__ __forceinline__ void mgb_run_program(const MgbOp* __restrict__ ops, int n_ops, const float* __restrict__ cst, QuadFn quad, EmitFn emit) {
+// Interpreter state + resumable execution: run(ops, pc0, pc1, ...) executes ops [pc0, pc1) and keeps the
+// kinematic state, so a caller that receives the quad values in pieces can interleave (tensor-core kernel).
+template <int CPT>
+struct MgbInterp {
     MgbXf G[CPT];
     float al_c[CPT], al_s[CPT], al_dx[CPT], al_dz[CPT], al_qw[CPT], al_qy[CPT];
     float scratch[CPT][MGB_SCRATCH_FLOATS];
     float stack[CPT][MGB_STACK_DEPTH * 8];
-    int sp = 0;
-#pragma unroll
-    for (int c = 0; c < CPT; ++c) {
-        mgb_xf_identity(G[c]);
-        al_c[c] = 1.f; al_s[c] = 0.f; al_dx[c] = 0.f; al_dz[c] = 0.f; al_qw[c] = 1.f; al_qy[c] = 0.f;
-    }
+    int sp;
 
-    for (int pc = 0; pc < n_ops; ++pc) {
-        const MgbOp op = ops[pc];
-        const float* cs = cst + op.c;
-        switch (op.code) {
-            case OP_ROOT: {
-                float4 tr[CPT], q[CPT];
-                quad(op.a, tr);
-                quad(op.b, q);
+    __device__ __forceinline__ void init() {
+        sp = 0;
 #pragma unroll
-                for (int c = 0; c < CPT; ++c) {
-                    // optional alignment to the previous motion (identity when local)
-                    const float tx = al_c[c] * tr[c].x + al_s[c] * tr[c].z + al_dx[c];
-                    const float tz = -al_s[c] * tr[c].x + al_c[c] * tr[c].z + al_dz[c];
-                    const float qw = al_qw[c] * q[c].x - al_qy[c] * q[c].z;
-                    const float qx = al_qw[c] * q[c].y + al_qy[c] * q[c].w;
-                    const float qy = al_qw[c] * q[c].z + al_qy[c] * q[c].x;
-                    const float qz = al_qw[c] * q[c].w - al_qy[c] * q[c].y;
-                    mgb_xf_set_rot(G[c], qw, qx, qy, qz);
-                    G[c].tx = tx + cs[0];
-                    G[c].ty = tr[c].y + cs[1];
-                    G[c].tz = tz + cs[2];
-                }
-                break;
-            }
-            case OP_JOINT: {
-                float4 q[CPT];
-                quad(op.a, q);
-#pragma unroll
-                for (int c = 0; c < CPT; ++c) mgb_xf_child(G[c], q[c].x, q[c].y, q[c].z, q[c].w, cs[0], cs[1], cs[2]);
-                break;
-            }
-            case OP_CONST: {
-#pragma unroll
-                for (int c = 0; c < CPT; ++c) {
-                    if (op.a) mgb_xf_translate(G[c], cs[4], cs[5], cs[6]);
-                    else mgb_xf_child(G[c], cs[0], cs[1], cs[2], cs[3], cs[4], cs[5], cs[6]);
-                }
-                break;
-            }
-            case OP_PUSH: {
-#pragma unroll
-                for (int c = 0; c < CPT; ++c) {
-                    float* st = stack[c] + sp * 8;
-                    st[0] = G[c].w; st[1] = G[c].x; st[2] = G[c].y; st[3] = G[c].z;
-                    st[4] = G[c].s2; st[5] = G[c].tx; st[6] = G[c].ty; st[7] = G[c].tz;
-                }
-                ++sp;
-                break;
-            }
-            case OP_POP: {
-                --sp;
-#pragma unroll
-                for (int c = 0; c < CPT; ++c) {
-                    const float* st = stack[c] + sp * 8;
-                    G[c].w = st[0]; G[c].x = st[1]; G[c].y = st[2]; G[c].z = st[3];
-                    G[c].s2 = st[4]; G[c].tx = st[5]; G[c].ty = st[6]; G[c].tz = st[7];
-                }
-                break;
-            }
-            case OP_ALIGN: {
-                // heading of the aligning node at control point 0, raw root translation of
-                // control point 0 (quad op.a), previous heading / root
-                float4 tr[CPT];
-                quad(op.a, tr);
-#pragma unroll
-                for (int c = 0; c < CPT; ++c) {
-                    float px, py, pz;
-                    mgb_xf_rotate(G[c], cs[0], cs[1], cs[2], px, py, pz);
-                    float ang = cs[3] - atan2f(px, pz);
-                    const float PI = 3.14159265358979323846f;
-                    if (ang > PI) ang -= 2.f * PI;
-                    if (ang <= -PI) ang += 2.f * PI;
-                    sincosf(ang, &al_s[c], &al_c[c]);
-                    sincosf(0.5f * ang, &al_qy[c], &al_qw[c]);
-                    al_dx[c] = cs[4] - (al_c[c] * tr[c].x + al_s[c] * tr[c].z);
-                    al_dz[c] = cs[5] - (-al_s[c] * tr[c].x + al_c[c] * tr[c].z);
-                }
-                break;
-            }
-            case OP_POS: {
-#pragma unroll
-                for (int c = 0; c < CPT; ++c) emit(c, op.a, cs[0], masked_dist((unsigned)op.b, cs + 1, G[c].tx, G[c].ty, G[c].tz));
-                break;
-            }
-            case OP_ORIENT: {
-                // angle_between_vectors(v1, v2) = acos(v1.v2 / |v1||v2|), evaluated as
-                // atan2(|v1 x v2|, v1.v2): same value, but well conditioned near 0 and pi in fp32
-#pragma unroll
-                for (int c = 0; c < CPT; ++c) {
-                    float vx, vy, vz;
-                    mgb_xf_rotate(G[c], 0.f, 0.f, 1.f, vx, vy, vz);
-                    const float cx = vy * cs[3] - vz * cs[2], cy = vz * cs[1] - vx * cs[3], cz = vx * cs[2] - vy * cs[1];
-                    const float d = vx * cs[1] + vy * cs[2] + vz * cs[3];
-                    emit(c, op.a, cs[0], atan2f(sqrtf(cx * cx + cy * cy + cz * cz), d));
-                }
-                break;
-            }
-            case OP_REL: {
-#pragma unroll
-                for (int c = 0; c < CPT; ++c) {
-                    float pp[3];
-                    mgb_xf_rotate(G[c], cs[1], cs[2], cs[3], pp[0], pp[1], pp[2]);
-                    pp[0] = fmaf(G[c].tx, cs[4], pp[0]);
-                    pp[1] = fmaf(G[c].ty, cs[4], pp[1]);
-                    pp[2] = fmaf(G[c].tz, cs[4], pp[2]);
-                    emit(c, op.a, cs[0], dist3(cs + 5, pp));
-                }
-                break;
-            }
-            case OP_DIR2D: {
-                // degrees(acos(clamp(t.d / (|t||d|)))) evaluated as atan2(|t x d|, t.d) (same value,
-                // well conditioned for small angles in fp32); d = (x, z) of R_global * ref_dir
-#pragma unroll
-                for (int c = 0; c < CPT; ++c) {
-                    float px, py, pz;
-                    mgb_xf_rotate(G[c], cs[1], cs[2], cs[3], px, py, pz);
-                    const float cr = cs[4] * pz - cs[5] * px;
-                    const float dt = cs[4] * px + cs[5] * pz;
-                    emit(c, op.a, cs[0], atan2f(fabsf(cr), dt) * 57.29577951308232f);
-                }
-                break;
-            }
-            case OP_LOOKAT: {
-#pragma unroll
-                for (int c = 0; c < CPT; ++c) {
-                    float tx = cs[1] - G[c].tx, ty = cs[2] - G[c].ty, tz = cs[3] - G[c].tz;
-                    const float ti = rsqrtf(tx * tx + ty * ty + tz * tz);
-                    tx *= ti; ty *= ti; tz *= ti;
-                    float hx, hy, hz;
-                    mgb_xf_rotate(G[c], 0.f, 0.f, 1.f, hx, hy, hz);
-                    const float hi = rsqrtf(hx * hx + hy * hy + hz * hz);
-                    hx *= hi; hy *= hi; hz *= hi;
-                    const float cx = hy * tz - hz * ty, cy = hz * tx - hx * tz, cz = hx * ty - hy * tx;
-                    emit(c, op.a, cs[0], fabsf(atan2f(sqrtf(cx * cx + cy * cy + cz * cz), hx * tx + hy * ty + hz * tz)));
-                }
-                break;
-            }
-            case OP_STORE: {
-#pragma unroll
-                for (int c = 0; c < CPT; ++c) {
-                    scratch[c][op.a] = G[c].tx;
-                    scratch[c][op.a + 1] = G[c].ty;
-                    scratch[c][op.a + 2] = G[c].tz;
-                }
-                break;
-            }
-            case OP_TWOHANDS: {
-#pragma unroll
-                for (int c = 0; c < CPT; ++c) {
-                    const float* lp = scratch[c] + op.b;
-                    const float* rp = scratch[c] + op.b + 3;
-                    const float mid[3] = {lp[0] + 0.5f * (rp[0] - lp[0]), lp[1] + 0.5f * (rp[1] - lp[1]), lp[2] + 0.5f * (rp[2] - lp[2])};
-                    emit(c, op.a, cs[0], dist3(cs + 1, mid) + dist3(cs + 4, lp) + dist3(cs + 7, rp));
-                }
-                break;
-            }
-            case OP_FEET: {
-#pragma unroll
-                for (int c = 0; c < CPT; ++c) {
-                    const float* lp = scratch[c] + op.b;
-                    const float* rp = scratch[c] + op.b + 3;
-                    emit(c, op.a, cs[0], (dist3(cs + 1, lp) + dist3(cs + 4, rp)) * cs[7]);
-                }
-                break;
-            }
-            case OP_POSE: {
-                // weighted 2-D rigid alignment of the candidate's point cloud (b) onto the
-                // target cloud (a), then mean point distance + root velocity error
-                const int np = (int)cs[1];
-                const float W = cs[6], sax = cs[7], saz = cs[8];
-                const float* tg = cs + 9;  // (ax, ay, az, w) * np
-#pragma unroll
-                for (int c = 0; c < CPT; ++c) {
-                    const float* pts = scratch[c] + op.b;
-                    float num_l = 0.f, den_l = 0.f, sbx = 0.f, sbz = 0.f;
-                    for (int j = 0; j < np; ++j) {
-                        const float ax = tg[4 * j], az = tg[4 * j + 2], w = tg[4 * j + 3];
-                        const float bx = pts[3 * j], bz = pts[3 * j + 2];
-                        num_l = fmaf(w, ax * bz - bx * az, num_l);
-                        den_l = fmaf(w, ax * bx + az * bz, den_l);
-                        sbx = fmaf(w, bx, sbx);
-                        sbz = fmaf(w, bz, sbz);
-                    }
-                    const float invW = 1.f / W;
-                    const float num = num_l - (sax * sbz - sbx * saz) * invW;
-                    const float den = den_l - (sax * sbx + saz * sbz) * invW;
-                    const float theta = atan2f(num, den);
-                    float st, ct;
-                    sincosf(theta, &st, &ct);
-                    const float ox = (sax - sbx * ct - sbz * st) * invW;
-                    const float oz = (saz + sbx * st - sbz * ct) * invW;
-                    float dsum = 0.f;
-                    for (int j = 0; j < np; ++j) {
-                        const float bx = pts[3 * j], by = pts[3 * j + 1], bz = pts[3 * j + 2];
-                        const float tx = ct * bx + st * bz + ox;
-                        const float tz = -st * bx + ct * bz + oz;
-                        const float ex = tg[4 * j] - tx, ey = tg[4 * j + 1] - by, ez = tg[4 * j + 2] - tz;
-                        dsum += sqrtf(fmaf(ex, ex, fmaf(ey, ey, ez * ez)));
-                    }
-                    float e = dsum / (float)np;
-                    if (cs[2] != 0.f) {
-                        const float* r2 = pts + 3 * np;
-                        const float vx = cs[3] - (r2[0] - pts[0]), vy = cs[4] - (r2[1] - pts[1]), vz = cs[5] - (r2[2] - pts[2]);
-                        e += sqrtf(fmaf(vx, vx, fmaf(vy, vy, vz * vz)));
-                    }
-                    emit(c, op.a, cs[0], e);
-                }
-                break;
-            }
-            case OP_CA_BEGIN: {
-#pragma unroll
-                for (int c = 0; c < CPT; ++c) scratch[c][op.a] = INFINITY;
-                break;
-            }
-            case OP_CA_ACC: {
-#pragma unroll
-                for (int c = 0; c < CPT; ++c)
-                    scratch[c][op.a] = fminf(scratch[c][op.a], masked_dist((unsigned)op.b, cs, G[c].tx, G[c].ty, G[c].tz));
-                break;
-            }
-            case OP_CA_END: {
-#pragma unroll
-                for (int c = 0; c < CPT; ++c) emit(c, op.a, cs[0], scratch[c][op.b]);
-                break;
-            }
-            default:
-                break;
+        for (int c = 0; c < CPT; ++c) {
+            mgb_xf_identity(G[c]);
+            al_c[c] = 1.f; al_s[c] = 0.f; al_dx[c] = 0.f; al_dz[c] = 0.f; al_qw[c] = 1.f; al_qy[c] = 0.f;
         }
     }
 
+    template <typename QuadFn, typename EmitFn>
+    __device__ __forceinline__ void run(const MgbOp* __restrict__ ops, int pc0, int pc1, const float* __restrict__ cst, QuadFn quad, EmitFn emit) {
+        for (int pc = pc0; pc < pc1; ++pc) {
+            const MgbOp op = ops[pc];
+            const float* cs = cst + op.c;
+            switch (op.code) {
+                case OP_ROOT: {
+                    float4 tr[CPT], q[CPT];
+                    quad(op.a, tr);
+                    quad(op.b, q);
+#pragma unroll
+                    for (int c = 0; c < CPT; ++c) {
+                        // optional alignment to the previous motion (identity when local)
+                        const float tx = al_c[c] * tr[c].x + al_s[c] * tr[c].z + al_dx[c];
+                        const float tz = -al_s[c] * tr[c].x + al_c[c] * tr[c].z + al_dz[c];
+                        const float qw = al_qw[c] * q[c].x - al_qy[c] * q[c].z;
+                        const float qx = al_qw[c] * q[c].y + al_qy[c] * q[c].w;
+                        const float qy = al_qw[c] * q[c].z + al_qy[c] * q[c].x;
+                        const float qz = al_qw[c] * q[c].w - al_qy[c] * q[c].y;
+                        mgb_xf_set_rot(G[c], qw, qx, qy, qz);
+                        G[c].tx = tx + cs[0];
+                        G[c].ty = tr[c].y + cs[1];
+                        G[c].tz = tz + cs[2];
+                    }
+                    break;
+                }
+                case OP_JOINT: {
+                    float4 q[CPT];
+                    quad(op.a, q);
+#pragma unroll
+                    for (int c = 0; c < CPT; ++c) mgb_xf_child(G[c], q[c].x, q[c].y, q[c].z, q[c].w, cs[0], cs[1], cs[2]);
+                    break;
+                }
+                case OP_CONST: {
+#pragma unroll
+                    for (int c = 0; c < CPT; ++c) {
+                        if (op.a) mgb_xf_translate(G[c], cs[4], cs[5], cs[6]);
+                        else mgb_xf_child(G[c], cs[0], cs[1], cs[2], cs[3], cs[4], cs[5], cs[6]);
+                    }
+                    break;
+                }
+                case OP_PUSH: {
+#pragma unroll
+                    for (int c = 0; c < CPT; ++c) {
+                        float* st = stack[c] + sp * 8;
+                        st[0] = G[c].w; st[1] = G[c].x; st[2] = G[c].y; st[3] = G[c].z;
+                        st[4] = G[c].s2; st[5] = G[c].tx; st[6] = G[c].ty; st[7] = G[c].tz;
+                    }
+                    ++sp;
+                    break;
+                }
+                case OP_POP: {
+                    --sp;
+#pragma unroll
+                    for (int c = 0; c < CPT; ++c) {
+                        const float* st = stack[c] + sp * 8;
+                        G[c].w = st[0]; G[c].x = st[1]; G[c].y = st[2]; G[c].z = st[3];
+                        G[c].s2 = st[4]; G[c].tx = st[5]; G[c].ty = st[6]; G[c].tz = st[7];
+                    }
+                    break;
+                }
+                case OP_ALIGN: {
+                    // heading of the aligning node at control point 0, raw root translation of
+                    // control point 0 (quad op.a), previous heading / root
+                    float4 tr[CPT];
+                    quad(op.a, tr);
+#pragma unroll
+                    for (int c = 0; c < CPT; ++c) {
+                        float px, py, pz;
+                        mgb_xf_rotate(G[c], cs[0], cs[1], cs[2], px, py, pz);
+                        float ang = cs[3] - atan2f(px, pz);
+                        const float PI = 3.14159265358979323846f;
+                        if (ang > PI) ang -= 2.f * PI;
+                        if (ang <= -PI) ang += 2.f * PI;
+                        sincosf(ang, &al_s[c], &al_c[c]);
+                        sincosf(0.5f * ang, &al_qy[c], &al_qw[c]);
+                        al_dx[c] = cs[4] - (al_c[c] * tr[c].x + al_s[c] * tr[c].z);
+                        al_dz[c] = cs[5] - (-al_s[c] * tr[c].x + al_c[c] * tr[c].z);
+                    }
+                    break;
+                }
+                case OP_POS: {
+#pragma unroll
+                    for (int c = 0; c < CPT; ++c) emit(c, op.a, cs[0], masked_dist((unsigned)op.b, cs + 1, G[c].tx, G[c].ty, G[c].tz));
+                    break;
+                }
+                case OP_ORIENT: {
+                    // angle_between_vectors(v1, v2) = acos(v1.v2 / |v1||v2|), evaluated as
+                    // atan2(|v1 x v2|, v1.v2): same value, but well conditioned near 0 and pi in fp32
+#pragma unroll
+                    for (int c = 0; c < CPT; ++c) {
+                        float vx, vy, vz;
+                        mgb_xf_rotate(G[c], 0.f, 0.f, 1.f, vx, vy, vz);
+                        const float cx = vy * cs[3] - vz * cs[2], cy = vz * cs[1] - vx * cs[3], cz = vx * cs[2] - vy * cs[1];
+                        const float d = vx * cs[1] + vy * cs[2] + vz * cs[3];
+                        emit(c, op.a, cs[0], atan2f(sqrtf(cx * cx + cy * cy + cz * cz), d));
+                    }
+                    break;
+                }
+                case OP_REL: {
+#pragma unroll
+                    for (int c = 0; c < CPT; ++c) {
+                        float pp[3];
+                        mgb_xf_rotate(G[c], cs[1], cs[2], cs[3], pp[0], pp[1], pp[2]);
+                        pp[0] = fmaf(G[c].tx, cs[4], pp[0]);
+                        pp[1] = fmaf(G[c].ty, cs[4], pp[1]);
+                        pp[2] = fmaf(G[c].tz, cs[4], pp[2]);
+                        emit(c, op.a, cs[0], dist3(cs + 5, pp));
+                    }
+                    break;
+                }
+                case OP_DIR2D: {
+                    // degrees(acos(clamp(t.d / (|t||d|)))) evaluated as atan2(|t x d|, t.d) (same value,
+                    // well conditioned for small angles in fp32); d = (x, z) of R_global * ref_dir
+#pragma unroll
+                    for (int c = 0; c < CPT; ++c) {
+                        float px, py, pz;
+                        mgb_xf_rotate(G[c], cs[1], cs[2], cs[3], px, py, pz);
+                        const float cr = cs[4] * pz - cs[5] * px;
+                        const float dt = cs[4] * px + cs[5] * pz;
+                        emit(c, op.a, cs[0], atan2f(fabsf(cr), dt) * 57.29577951308232f);
+                    }
+                    break;
+                }
+                case OP_LOOKAT: {
+#pragma unroll
+                    for (int c = 0; c < CPT; ++c) {
+                        float tx = cs[1] - G[c].tx, ty = cs[2] - G[c].ty, tz = cs[3] - G[c].tz;
+                        const float ti = rsqrtf(tx * tx + ty * ty + tz * tz);
+                        tx *= ti; ty *= ti; tz *= ti;
+                        float hx, hy, hz;
+                        mgb_xf_rotate(G[c], 0.f, 0.f, 1.f, hx, hy, hz);
+                        const float hi = rsqrtf(hx * hx + hy * hy + hz * hz);
+                        hx *= hi; hy *= hi; hz *= hi;
+                        const float cx = hy * tz - hz * ty, cy = hz * tx - hx * tz, cz = hx * ty - hy * tx;
+                        emit(c, op.a, cs[0], fabsf(atan2f(sqrtf(cx * cx + cy * cy + cz * cz), hx * tx + hy * ty + hz * tz)));
+                    }
+                    break;
+                }
+                case OP_STORE: {
+#pragma unroll
+                    for (int c = 0; c < CPT; ++c) {
+                        scratch[c][op.a] = G[c].tx;
+                        scratch[c][op.a + 1] = G[c].ty;
+                        scratch[c][op.a + 2] = G[c].tz;
+                    }
+                    break;
+                }
+                case OP_TWOHANDS: {
+#pragma unroll
+                    for (int c = 0; c < CPT; ++c) {
+                        const float* lp = scratch[c] + op.b;
+                        const float* rp = scratch[c] + op.b + 3;
+                        const float mid[3] = {lp[0] + 0.5f * (rp[0] - lp[0]), lp[1] + 0.5f * (rp[1] - lp[1]), lp[2] + 0.5f * (rp[2] - lp[2])};
+                        emit(c, op.a, cs[0], dist3(cs + 1, mid) + dist3(cs + 4, lp) + dist3(cs + 7, rp));
+                    }
+                    break;
+                }
+                case OP_FEET: {
+#pragma unroll
+                    for (int c = 0; c < CPT; ++c) {
+                        const float* lp = scratch[c] + op.b;
+                        const float* rp = scratch[c] + op.b + 3;
+                        emit(c, op.a, cs[0], (dist3(cs + 1, lp) + dist3(cs + 4, rp)) * cs[7]);
+                    }
+                    break;
+                }
+                case OP_POSE: {
+                    // weighted 2-D rigid alignment of the candidate's point cloud (b) onto the
+                    // target cloud (a), then mean point distance + root velocity error
+                    const int np = (int)cs[1];
+                    const float W = cs[6], sax = cs[7], saz = cs[8];
+                    const float* tg = cs + 9;  // (ax, ay, az, w) * np
+#pragma unroll
+                    for (int c = 0; c < CPT; ++c) {
+                        const float* pts = scratch[c] + op.b;
+                        float num_l = 0.f, den_l = 0.f, sbx = 0.f, sbz = 0.f;
+                        for (int j = 0; j < np; ++j) {
+                            const float ax = tg[4 * j], az = tg[4 * j + 2], w = tg[4 * j + 3];
+                            const float bx = pts[3 * j], bz = pts[3 * j + 2];
+                            num_l = fmaf(w, ax * bz - bx * az, num_l);
+                            den_l = fmaf(w, ax * bx + az * bz, den_l);
+                            sbx = fmaf(w, bx, sbx);
+                            sbz = fmaf(w, bz, sbz);
+                        }
+                        const float invW = 1.f / W;
+                        const float num = num_l - (sax * sbz - sbx * saz) * invW;
+                        const float den = den_l - (sax * sbx + saz * sbz) * invW;
+                        const float theta = atan2f(num, den);
+                        float st, ct;
+                        sincosf(theta, &st, &ct);
+                        const float ox = (sax - sbx * ct - sbz * st) * invW;
+                        const float oz = (saz + sbx * st - sbz * ct) * invW;
+                        float dsum = 0.f;
+                        for (int j = 0; j < np; ++j) {
+                            const float bx = pts[3 * j], by = pts[3 * j + 1], bz = pts[3 * j + 2];
+                            const float tx = ct * bx + st * bz + ox;
+                            const float tz = -st * bx + ct * bz + oz;
+                            const float ex = tg[4 * j] - tx, ey = tg[4 * j + 1] - by, ez = tg[4 * j + 2] - tz;
+                            dsum += sqrtf(fmaf(ex, ex, fmaf(ey, ey, ez * ez)));
+                        }
+                        float e = dsum / (float)np;
+                        if (cs[2] != 0.f) {
+                            const float* r2 = pts + 3 * np;
+                            const float vx = cs[3] - (r2[0] - pts[0]), vy = cs[4] - (r2[1] - pts[1]), vz = cs[5] - (r2[2] - pts[2]);
+                            e += sqrtf(fmaf(vx, vx, fmaf(vy, vy, vz * vz)));
+                        }
+                        emit(c, op.a, cs[0], e);
+                    }
+                    break;
+                }
+                case OP_CA_BEGIN: {
+#pragma unroll
+                    for (int c = 0; c < CPT; ++c) scratch[c][op.a] = INFINITY;
+                    break;
+                }
+                case OP_CA_ACC: {
+#pragma unroll
+                    for (int c = 0; c < CPT; ++c)
+                        scratch[c][op.a] = fminf(scratch[c][op.a], masked_dist((unsigned)op.b, cs, G[c].tx, G[c].ty, G[c].tz));
+                    break;
+                }
+                case OP_CA_END: {
+#pragma unroll
+                    for (int c = 0; c < CPT; ++c) emit(c, op.a, cs[0], scratch[c][op.b]);
+                    break;
+                }
+                default:
+                    break;
+            }
+        }
+
+    }
+};
+
+template <int CPT, typename QuadFn, typename EmitFn>
+__device__ __forceinline__ void mgb_run_program(const MgbOp* __restrict__ ops, int n_ops, const float* __restrict__ cst, QuadFn quad, EmitFn emit) {
+    MgbInterp<CPT> it;
+    it.init();
+    it.run(ops, 0, n_ops, cst, quad, emit);
 }

@@ -635,7 +635,10 @@ int mgb_launch_score(const mgb_model* m, const mgb_constraints* c, int mode, con
 
     int rc;
     const int D = m->D;
-    if (mode == MODE_FRAMES) {
+    if (mode == MODE_S && mgb_score_tc_usable(m, c, quality_scale)) {
+        // large latent spaces: contraction + GMM log-density on the tensor cores (mgb_tc.cu)
+        rc = mgb_launch_score_tc(m, c, p, s_is_f64, quality_scale, stream);
+    } else if (mode == MODE_FRAMES) {
         rc = launch_variant<0, 1, MODE_FRAMES, float>(p, plan, stream);
     } else if (mode == MODE_SAMPLE) {
         rc = launch_shape<MODE_SAMPLE, float>(D, p, plan, stream);

@@ -27,6 +27,7 @@
 #include <vector>
 
 #include "mgb_internal.cuh"
+#include "mgb_interp.cuh"
 #include "mgb_tc.cuh"
 
 #define MGB_HAVE_TC 1
@@ -114,66 +115,80 @@ __device__ __forceinline__ TcBars tc_bars(unsigned char* base) {
 
 // ---- role bodies shared by the tensor-core kernels ---------------------------------------
 
-// warp 0, one lane: stream every stage image of B once per tile
-__device__ __forceinline__ void tc_b_producer(const TcB& B, unsigned char* sm_stage, size_t stage_bytes, int nst, const TcBars& bars,
+// The constant operands of one tile pass: up to two packed matrices that share the A tile
+// (e.g. the contracted constraint quads, then the GMM precision factors), streamed in order.
+struct TcSegs {
+    TcB seg[2];
+    int n;
+};
+
+// warp 0, one lane: stream every stage image of every operand once per tile
+__device__ __forceinline__ void tc_b_producer(const TcSegs& S, unsigned char* sm_stage, size_t stage_bytes, int nst, const TcBars& bars,
                                               long long my_tiles) {
     unsigned int it = 0;
-    const int n_nc = B.n_nc(), n_kc = B.n_kc();
     for (long long t = 0; t < my_tiles; ++t) {
-        for (int c = 0; c < n_nc; ++c) {
-            const int wc = B.wc(c);
-            for (int kc = 0; kc < n_kc; ++kc, ++it) {
-                const int st = it % nst;
-                const unsigned int ph = (it / nst) & 1u;
-                mgb_mbar_wait(&bars.b_empty[st], ph ^ 1u);
-                const unsigned int bytes = (unsigned int)(2 * wc * B.wk(kc) * 4);
-                mgb_mbar_expect_tx(&bars.b_full[st], bytes);
-                mgb_bulk_g2s(sm_stage + (size_t)st * stage_bytes, B.data + B.off(c, kc), bytes, &bars.b_full[st]);
+        for (int sg = 0; sg < S.n; ++sg) {
+            const TcB& B = S.seg[sg];
+            const int n_nc = B.n_nc(), n_kc = B.n_kc();
+            for (int c = 0; c < n_nc; ++c) {
+                const int wc = B.wc(c);
+                for (int kc = 0; kc < n_kc; ++kc, ++it) {
+                    const int st = it % nst;
+                    const unsigned int ph = (it / nst) & 1u;
+                    mgb_mbar_wait(&bars.b_empty[st], ph ^ 1u);
+                    const unsigned int bytes = (unsigned int)(2 * wc * B.wk(kc) * 4);
+                    mgb_mbar_expect_tx(&bars.b_full[st], bytes);
+                    mgb_bulk_g2s(sm_stage + (size_t)st * stage_bytes, B.data + B.off(c, kc), bytes, &bars.b_full[st]);
+                }
             }
         }
     }
 }
 
-// warp 1, one lane: all MMAs of this CTA
-__device__ __forceinline__ void tc_mma_issuer(const TcB& B, uint32_t a_hi_addr, uint32_t a_lo_addr, uint32_t stage_addr, size_t stage_bytes,
+// warp 1, one lane: all MMAs of this CTA.  Chunk number cc (counted over all operands and tiles)
+// accumulates into TMEM buffer cc & 1.
+__device__ __forceinline__ void tc_mma_issuer(const TcSegs& S, uint32_t a_hi_addr, uint32_t a_lo_addr, uint32_t stage_addr, size_t stage_bytes,
                                               int nst, const TcBars& bars, uint32_t tmem_base, long long my_tiles) {
     unsigned int it = 0, cc = 0;
-    const int n_nc = B.n_nc(), n_kc = B.n_kc();
     const uint32_t A_LBO = TC_M * 16, SBO = 128;
     for (long long t = 0; t < my_tiles; ++t) {
         mgb_mbar_wait(bars.a_full, (unsigned int)(t & 1));
         mgb_tc_fence_after();
-        for (int c = 0; c < n_nc; ++c, ++cc) {
-            const int wc = B.wc(c);
-            const unsigned int buf = cc & 1u;
-            mgb_mbar_wait(&bars.t_empty[buf], ((cc >> 1) & 1u) ^ 1u);
-            mgb_tc_fence_after();
-            const uint32_t d_addr = tmem_base + buf * TC_BUF_COLS;
-            const uint32_t idesc = mgb_umma_idesc_tf32(TC_M, wc);
-            const uint32_t B_LBO = (uint32_t)wc * 16;
-            uint32_t acc = 0;
-            for (int kc = 0; kc < n_kc; ++kc, ++it) {
-                const int st = it % nst;
-                mgb_mbar_wait(&bars.b_full[st], (it / nst) & 1u);
+        for (int sg = 0; sg < S.n; ++sg) {
+            const TcB& B = S.seg[sg];
+            const int n_nc = B.n_nc(), n_kc = B.n_kc();
+            for (int c = 0; c < n_nc; ++c, ++cc) {
+                const int wc = B.wc(c);
+                const unsigned int buf = cc & 1u;
+                mgb_mbar_wait(&bars.t_empty[buf], ((cc >> 1) & 1u) ^ 1u);
                 mgb_tc_fence_after();
-                const int wk = B.wk(kc);
-                const uint32_t b_hi = stage_addr + (uint32_t)(st * stage_bytes);
-                const uint32_t b_lo = b_hi + (uint32_t)(wc * wk * 4);
-                for (int j = 0; j < wk / 8; ++j) {
-                    const uint32_t a_off = (uint32_t)((kc * B.KC) / 4 + 2 * j) * A_LBO;
-                    const uint32_t b_off = (uint32_t)(2 * j) * B_LBO;
-                    const uint64_t da_hi = mgb_umma_desc(a_hi_addr + a_off, A_LBO, SBO);
-                    const uint64_t da_lo = mgb_umma_desc(a_lo_addr + a_off, A_LBO, SBO);
-                    const uint64_t db_hi = mgb_umma_desc(b_hi + b_off, B_LBO, SBO);
-                    const uint64_t db_lo = mgb_umma_desc(b_lo + b_off, B_LBO, SBO);
-                    mgb_umma_tf32(d_addr, da_lo, db_hi, idesc, acc);  // small terms first
-                    mgb_umma_tf32(d_addr, da_hi, db_lo, idesc, 1u);
-                    mgb_umma_tf32(d_addr, da_hi, db_hi, idesc, 1u);
-                    acc = 1u;
+                const uint32_t d_addr = tmem_base + buf * TC_BUF_COLS;
+                const uint32_t idesc = mgb_umma_idesc_tf32(TC_M, wc);
+                const uint32_t B_LBO = (uint32_t)wc * 16;
+                uint32_t acc = 0;
+                for (int kc = 0; kc < n_kc; ++kc, ++it) {
+                    const int st = it % nst;
+                    mgb_mbar_wait(&bars.b_full[st], (it / nst) & 1u);
+                    mgb_tc_fence_after();
+                    const int wk = B.wk(kc);
+                    const uint32_t b_hi = stage_addr + (uint32_t)(st * stage_bytes);
+                    const uint32_t b_lo = b_hi + (uint32_t)(wc * wk * 4);
+                    for (int j = 0; j < wk / 8; ++j) {
+                        const uint32_t a_off = (uint32_t)((kc * B.KC) / 4 + 2 * j) * A_LBO;
+                        const uint32_t b_off = (uint32_t)(2 * j) * B_LBO;
+                        const uint64_t da_hi = mgb_umma_desc(a_hi_addr + a_off, A_LBO, SBO);
+                        const uint64_t da_lo = mgb_umma_desc(a_lo_addr + a_off, A_LBO, SBO);
+                        const uint64_t db_hi = mgb_umma_desc(b_hi + b_off, B_LBO, SBO);
+                        const uint64_t db_lo = mgb_umma_desc(b_lo + b_off, B_LBO, SBO);
+                        mgb_umma_tf32(d_addr, da_lo, db_hi, idesc, acc);  // small terms first
+                        mgb_umma_tf32(d_addr, da_hi, db_lo, idesc, 1u);
+                        mgb_umma_tf32(d_addr, da_hi, db_hi, idesc, 1u);
+                        acc = 1u;
+                    }
+                    mgb_umma_commit(&bars.b_empty[st]);
                 }
-                mgb_umma_commit(&bars.b_empty[st]);
+                mgb_umma_commit(&bars.t_full[buf]);
             }
-            mgb_umma_commit(&bars.t_full[buf]);
         }
         mgb_umma_commit(bars.a_empty);
     }
@@ -254,11 +269,20 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mgb_backproject_tc_kernel(const
     const uint32_t tmem_base = *tmem_ptr;
 
     if (warp == 0) {
-        if (lane == 0) tc_b_producer(p.B, smem + plan.b_stage, plan.stage_bytes, p.nst, bars, my_tiles);
+        if (lane == 0) {
+            TcSegs S;
+            S.seg[0] = p.B;
+            S.n = 1;
+            tc_b_producer(S, smem + plan.b_stage, plan.stage_bytes, p.nst, bars, my_tiles);
+        }
     } else if (warp == 1) {
-        if (lane == 0)
-            tc_mma_issuer(p.B, mgb_smem_u32(smem + plan.a_hi), mgb_smem_u32(smem + plan.a_lo), mgb_smem_u32(smem + plan.b_stage),
+        if (lane == 0) {
+            TcSegs S;
+            S.seg[0] = p.B;
+            S.n = 1;
+            tc_mma_issuer(S, mgb_smem_u32(smem + plan.a_hi), mgb_smem_u32(smem + plan.a_lo), mgb_smem_u32(smem + plan.b_stage),
                           plan.stage_bytes, p.nst, bars, tmem_base, my_tiles);
+        }
     } else {
         const int wq = warp & 3;            // TMEM lane quarter of this warp
         const int ew = warp - 2;            // epilogue warp 0..7
@@ -474,6 +498,509 @@ int mgb_backproject_tc(const mgb_model* m, const float* d_s, int64_t n, float* d
     const long long n_tiles = (n + TC_M - 1) / TC_M;
     const int grid = (int)std::min<long long>(n_tiles, tc_num_sms());
     mgb_backproject_tc_kernel<<<grid, TC_THREADS, smem, stream>>>(p);
+    mgb_count_launch();
+    MGB_CUDA(cudaGetLastError());
+    return MGB_OK;
+}
+
+// ===========================================================================
+// K6-TC: fused keyframe score for large latent spaces (D > 32) on the tensor cores.
+//
+// Per 128-candidate tile one A operand [s | 1] (hi / lo TF32 split) feeds two packed
+// constant operands in turn:
+//   quads : the spatial basis pre-contracted with the B-spline weights of every constrained
+//           time slot (mgb_constraints_pack), bias (mean) in the row that meets the 1
+//           -> pose channels at the constrained keyframes        (back-projection + spline)
+//   GMM   : the precision Cholesky factors P_g of all components side by side, bias -mu_g.P_g
+//           -> y_g = (s - mu_g) . P_g, log-density by logsumexp   (naturalness term)
+// Epilogue group 0 (warps 2-5) prepares A, drains the quad chunk into shared memory and runs
+// the constraint program (forward kinematics + terms) on it; group 1 (warps 6-9) drains the
+// GMM chunks (sum of squares per component straight from TMEM, thread = candidate) while the
+// next chunk is being multiplied.  Replaces the same reference functions as mgb_score.cu.
+// ===========================================================================
+namespace {
+
+struct TcScoreParams {
+    ScoreParams sp;
+    TcSegs segs;
+    int seg_q, seg_g;  // index of the quad / GMM operand in segs, -1 if absent
+    int nst;
+    int Kp;
+    int QS;            // floats per candidate row of the quad-value area (also the raw-sample staging)
+    const int* phase;  // [quad chunks + 1] first op of every chunk's part of the program
+    int ops_in_smem;   // program + constants staged in shared memory (else read through L1)
+    int CW;            // GMM columns per component
+    int cpc;           // components per N-chunk
+};
+
+struct TcScoreSmem {
+    size_t a_hi, a_lo, b_stage, qv, ops, cst, lp, redc, redi, bars, sbar, tmem_ptr, flag, total;
+    size_t stage_bytes;
+};
+__host__ __device__ inline TcScoreSmem tc_score_smem_plan(int Kp, size_t stage_bytes, int nst, int QS, int n_ops, int n_cst) {
+    TcScoreSmem p;
+    size_t off = 0;
+    p.a_hi = off; off += (size_t)TC_M * Kp * 4;
+    p.a_lo = off; off += (size_t)TC_M * Kp * 4;
+    p.stage_bytes = stage_bytes;
+    p.b_stage = off; off += stage_bytes * nst;
+    p.qv = off; off += ((size_t)TC_M * QS * 4 + 15) & ~(size_t)15;
+    p.ops = off; off += (size_t)n_ops * sizeof(MgbOp);
+    p.cst = off; off += (size_t)((n_cst + 3) & ~3) * 4;
+    p.lp = off; off += TC_M * 4;
+    p.redc = off; off += 16;
+    p.redi = off; off += 32;
+    p.bars = off; off += 8 * (2 * TC_MAX_STAGES + 2 + 4);
+    p.sbar = off; off += 8;
+    p.tmem_ptr = off; off += 8;
+    p.flag = off; off += 8;
+    p.total = off;
+    return p;
+}
+
+__device__ __forceinline__ bool tc_better(float c1, long long i1, float c2, long long i2) { return (c1 < c2) || (c1 == c2 && i1 < i2); }
+
+template <typename SIn>
+__global__ void __launch_bounds__(TC_THREADS, 1) mgb_score_tc_kernel(const __grid_constant__ TcScoreParams p) {
+    extern __shared__ __align__(1024) unsigned char smem[];
+    const ScoreParams& sp = p.sp;
+    size_t stage_bytes = 0;
+    for (int i = 0; i < p.segs.n; ++i) stage_bytes = max(stage_bytes, (size_t)2 * p.segs.seg[i].NC * p.segs.seg[i].KC * 4);
+    const TcScoreSmem L = tc_score_smem_plan(p.Kp, stage_bytes, p.nst, p.QS, p.ops_in_smem ? sp.n_ops : 0, p.ops_in_smem ? sp.n_cst : 0);
+    const TcBars bars = tc_bars(smem + L.bars);
+    unsigned long long* s_full = reinterpret_cast<unsigned long long*>(smem + L.sbar);
+    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(smem + L.tmem_ptr);
+    MgbOp* sm_ops = reinterpret_cast<MgbOp*>(smem + L.ops);
+    float* sm_cst = reinterpret_cast<float*>(smem + L.cst);
+    float* sm_lp = reinterpret_cast<float*>(smem + L.lp);
+    float* qv = reinterpret_cast<float*>(smem + L.qv);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const long long n_tiles = (sp.n + TC_M - 1) / TC_M;
+    const long long my_tiles = (n_tiles > blockIdx.x) ? (n_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+
+    if (p.ops_in_smem) {
+        for (int i = threadIdx.x; i < sp.n_ops; i += TC_THREADS) sm_ops[i] = sp.ops[i];
+        for (int i = threadIdx.x; i < sp.n_cst; i += TC_THREADS) sm_cst[i] = sp.cst[i];
+    }
+    const MgbOp* ops = p.ops_in_smem ? sm_ops : sp.ops;
+    const float* cst = p.ops_in_smem ? sm_cst : sp.cst;
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < TC_MAX_STAGES; ++i) {
+            mgb_mbar_init(&bars.b_full[i], 1);
+            mgb_mbar_init(&bars.b_empty[i], 1);
+        }
+        mgb_mbar_init(bars.a_full, 128);
+        mgb_mbar_init(bars.a_empty, 1);
+        for (int i = 0; i < 2; ++i) {
+            mgb_mbar_init(&bars.t_full[i], 1);
+            mgb_mbar_init(&bars.t_empty[i], 128);
+        }
+        mgb_mbar_init(s_full, 1);
+        mgb_fence_barrier_init();
+    }
+    if (warp == 1) mgb_tmem_alloc(tmem_ptr, TC_TMEM_COLS);
+    mgb_tc_fence_before();
+    __syncthreads();
+    mgb_tc_fence_after();
+    const uint32_t tmem_base = *tmem_ptr;
+    const int n_nc_q = p.seg_q >= 0 ? p.segs.seg[p.seg_q].n_nc() : 0;
+    const int n_nc_g = p.seg_g >= 0 ? p.segs.seg[p.seg_g].n_nc() : 0;
+
+    if (warp == 0) {
+        if (lane == 0) tc_b_producer(p.segs, smem + L.b_stage, L.stage_bytes, p.nst, bars, my_tiles);
+    } else if (warp == 1) {
+        if (lane == 0)
+            tc_mma_issuer(p.segs, mgb_smem_u32(smem + L.a_hi), mgb_smem_u32(smem + L.a_lo), mgb_smem_u32(smem + L.b_stage), L.stage_bytes,
+                          p.nst, bars, tmem_base, my_tiles);
+    } else if (warp < 6) {
+        // ================= group 0: A producer, quad drain, constraint program, selection =================
+        const int wq = warp & 3;
+        const int row = 32 * wq + lane;  // candidate row of the tile = TMEM lane
+        const int tid0 = threadIdx.x - 64;
+        const uint32_t lane_addr = tmem_base + ((uint32_t)(32 * wq) << 16);
+        const int D = sp.D, QS = p.QS;
+        constexpr int NH = sizeof(SIn) / 4;   // the raw tile is staged in NH pieces of RP rows (it must fit the quad-value area)
+        constexpr int RP = TC_M / NH;
+        const SIn* __restrict__ s_glob = reinterpret_cast<const SIn*>(sp.s);
+        SIn* raw = reinterpret_cast<SIn*>(qv);
+        float best_c = INFINITY;
+        long long best_i = LLONG_MAX;
+        unsigned int cc = 0, sload = 0;
+        for (long long t = 0; t < my_tiles; ++t) {
+            const long long g0 = (blockIdx.x + t * gridDim.x) * TC_M;
+            const long long idx = g0 + row;
+            const bool valid = idx < sp.n;
+            // ---- A tile: [s | 1] split into TF32 hi / lo -------------------------------------------
+            float m2 = 0.f;
+            for (int piece = 0; piece < NH; ++piece) {
+                const long long r0 = g0 + (long long)piece * RP;
+                const long long rows_here = max(0LL, min((long long)RP, sp.n - r0));
+                asm volatile("bar.sync 3, 128;" ::: "memory");  // the area is free: program of the previous tile / previous piece done
+                if (sp.s_aligned && rows_here == RP) {
+                    if (tid0 == 0) {
+                        const unsigned int bytes = (unsigned int)(RP * D * sizeof(SIn));
+                        mgb_fence_proxy_async();  // generic-proxy accesses of the area are ordered before the async-proxy write
+                        mgb_mbar_expect_tx(s_full, bytes);
+                        mgb_bulk_g2s(raw, s_glob + (size_t)r0 * D, bytes, s_full);
+                    }
+                    mgb_mbar_wait(s_full, sload & 1u);
+                    ++sload;
+                } else {
+                    const long long remaining = rows_here * D;
+                    for (int e = tid0; e < RP * D; e += 128) raw[e] = (e < remaining) ? s_glob[(size_t)r0 * D + e] : (SIn)0;
+                    asm volatile("bar.sync 3, 128;" ::: "memory");
+                }
+                if (piece == 0) mgb_mbar_wait(bars.a_empty, (unsigned int)(t & 1) ^ 1u);
+                if (row / RP == piece) {
+                    const SIn* mine = raw + (size_t)(row - piece * RP) * D;
+                    tc_write_a_row(smem + L.a_hi, smem + L.a_lo, row, p.Kp, valid ? D + 1 : 0, [&](int k) {
+                        const float v = k < D ? (float)mine[k] : 1.f;
+                        if (k < D) m2 = fmaf(v, v, m2);
+                        return v;
+                    });
+                }
+            }
+            mgb_fence_proxy_async();
+            mgb_mbar_arrive(bars.a_full);
+            // ---- quad chunks: TMEM -> this thread's row of the quad-value area, then the part of the constraint
+            //      program that reads them (every chunk holds whole time slots; kinematic state carries over) -----
+            float total = 0.f;
+            MgbInterp<1> interp;
+            interp.init();
+            const float* myq = qv + (size_t)row * QS;
+            auto quad = [&](int q, float4 (&out)[1]) { out[0] = make_float4(myq[4 * q], myq[4 * q + 1], myq[4 * q + 2], myq[4 * q + 3]); };
+            auto emit = [&](int, int term, float w, float e) {
+                total = fmaf(w, e, total);
+                if (sp.terms != nullptr && valid) sp.terms[(size_t)term * sp.n + idx] += e;
+            };
+            for (int c = 0; c < n_nc_q; ++c, ++cc) {
+                const TcB& B = p.segs.seg[p.seg_q];
+                const unsigned int buf = cc & 1u;
+                mgb_mbar_wait(&bars.t_full[buf], (cc >> 1) & 1u);
+                mgb_tc_fence_after();
+                const int wc = B.wc(c);
+                for (int b0 = 0; b0 < wc; b0 += 32) {
+                    float v[32];
+                    mgb_tmem_ld32(lane_addr + buf * TC_BUF_COLS + b0, v);
+#pragma unroll
+                    for (int i = 0; i < 32; ++i)
+                        if (b0 + i < wc) qv[(size_t)row * QS + b0 + i] = v[i];
+                }
+                mgb_tc_fence_before();
+                mgb_mbar_arrive_relaxed(&bars.t_empty[buf]);
+                interp.run(ops, __ldg(p.phase + c), __ldg(p.phase + c + 1), cst, quad, emit);
+            }
+            cc += n_nc_g;
+            float cost = sp.err_scale * total;
+            if (p.seg_g >= 0) {
+                asm volatile("bar.sync 2, 256;" ::: "memory");  // group 1 has published -log p(s) of this tile
+                cost = fmaf(sp.quality_scale, sm_lp[row], cost);
+            }
+            if (sp.magnitude_scale != 0.f) cost = fmaf(sp.magnitude_scale, sqrtf(m2), cost);
+            if (valid) {
+                if (sp.cost) sp.cost[idx] = cost;
+                const long long gi = sp.index_base + idx;
+                if (tc_better(cost, gi, best_c, best_i)) { best_c = cost; best_i = gi; }
+            }
+        }
+        // ---- selection: group-0 arg-min, per-CTA partial, last CTA folds (first minimum wins) ----------
+        if (sp.want_best) {
+            float* sm_redc = reinterpret_cast<float*>(smem + L.redc);
+            long long* sm_redi = reinterpret_cast<long long*>(smem + L.redi);
+            int* sm_flag = reinterpret_cast<int*>(smem + L.flag);
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                const float oc = __shfl_xor_sync(0xffffffffu, best_c, o);
+                const long long oi = __shfl_xor_sync(0xffffffffu, best_i, o);
+                if (tc_better(oc, oi, best_c, best_i)) { best_c = oc; best_i = oi; }
+            }
+            if (lane == 0) { sm_redc[wq] = best_c; sm_redi[wq] = best_i; }
+            asm volatile("bar.sync 3, 128;" ::: "memory");
+            if (tid0 == 0) {
+                for (int w = 0; w < 4; ++w)
+                    if (tc_better(sm_redc[w], sm_redi[w], best_c, best_i)) { best_c = sm_redc[w]; best_i = sm_redi[w]; }
+                sp.part_cost[blockIdx.x] = best_c;
+                sp.part_idx[blockIdx.x] = best_i;
+                __threadfence();
+                const unsigned int done = atomicAdd(sp.done_count, 1u);
+                *sm_flag = (done == gridDim.x - 1) ? 1 : 0;
+            }
+            asm volatile("bar.sync 3, 128;" ::: "memory");
+            if (*sm_flag) {
+                __threadfence();
+                best_c = INFINITY;
+                best_i = LLONG_MAX;
+                for (int b = tid0; b < (int)gridDim.x; b += 128) {
+                    const float oc = __ldcg(sp.part_cost + b);
+                    const long long oi = __ldcg(sp.part_idx + b);
+                    if (tc_better(oc, oi, best_c, best_i)) { best_c = oc; best_i = oi; }
+                }
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) {
+                    const float oc = __shfl_xor_sync(0xffffffffu, best_c, o);
+                    const long long oi = __shfl_xor_sync(0xffffffffu, best_i, o);
+                    if (tc_better(oc, oi, best_c, best_i)) { best_c = oc; best_i = oi; }
+                }
+                asm volatile("bar.sync 3, 128;" ::: "memory");
+                if (lane == 0) { sm_redc[wq] = best_c; sm_redi[wq] = best_i; }
+                asm volatile("bar.sync 3, 128;" ::: "memory");
+                if (tid0 == 0) {
+                    for (int w = 0; w < 4; ++w)
+                        if (tc_better(sm_redc[w], sm_redi[w], best_c, best_i)) { best_c = sm_redc[w]; best_i = sm_redi[w]; }
+                    if (best_i == LLONG_MAX) best_i = sp.index_base;  // nothing finite: reference keeps index 0
+                    sp.best_cost[0] = best_c;
+                    sp.best_idx[0] = best_i;
+                    *sp.done_count = 0u;  // ready for the next launch
+                }
+            }
+        }
+    } else if (p.seg_g >= 0) {
+        // ================= group 1: GMM log-density straight from TMEM =================
+        const int wq = warp & 3;
+        const int row = 32 * wq + lane;
+        const uint32_t lane_addr = tmem_base + ((uint32_t)(32 * wq) << 16);
+        const int CW = p.CW, G = sp.G;
+        unsigned int cc = 0;
+        for (long long t = 0; t < my_tiles; ++t) {
+            // the quad chunks belong to group 0, but this group still has to OBSERVE every phase of the accumulator
+            // barriers: a parity wait is only meaningful when the waiter is at most one phase ahead of the barrier
+            for (int c = 0; c < n_nc_q; ++c, ++cc) mgb_mbar_wait(&bars.t_full[cc & 1u], (cc >> 1) & 1u);
+            float mx = -INFINITY, ssum = 0.f;
+            int g = 0;
+            for (int c = 0; c < n_nc_g; ++c, ++cc) {
+                const unsigned int buf = cc & 1u;
+                mgb_mbar_wait(&bars.t_full[buf], (cc >> 1) & 1u);
+                mgb_tc_fence_after();
+                const uint32_t base = lane_addr + buf * TC_BUF_COLS;
+                for (int j = 0; j < p.cpc && g < G; ++j, ++g) {
+                    // y = (s - mu_g) . P_g occupies CW columns; padding columns are exact zeros
+                    float qf0 = 0.f, qf1 = 0.f;
+                    int b0 = 0;
+                    for (; b0 + 32 <= CW; b0 += 32) {
+                        float v[32];
+                        mgb_tmem_ld32(base + j * CW + b0, v);
+#pragma unroll
+                        for (int i = 0; i < 32; i += 2) {
+                            qf0 = fmaf(v[i], v[i], qf0);
+                            qf1 = fmaf(v[i + 1], v[i + 1], qf1);
+                        }
+                    }
+                    for (; b0 < CW; b0 += 8) {
+                        float v[8];
+                        mgb_tmem_ld8(base + j * CW + b0, v);
+#pragma unroll
+                        for (int i = 0; i < 8; i += 2) {
+                            qf0 = fmaf(v[i], v[i], qf0);
+                            qf1 = fmaf(v[i + 1], v[i + 1], qf1);
+                        }
+                    }
+                    const float lp = __ldg(sp.gmm_c + g) - 0.5f * (qf0 + qf1);
+                    if (lp > mx) {
+                        ssum = ssum * __expf(mx - lp) + 1.f;
+                        mx = lp;
+                    } else {
+                        ssum += __expf(lp - mx);
+                    }
+                }
+                mgb_tc_fence_before();
+                mgb_mbar_arrive_relaxed(&bars.t_empty[buf]);
+            }
+            sm_lp[row] = -(mx + __logf(ssum));
+            asm volatile("bar.sync 2, 256;" ::: "memory");
+        }
+    }
+    mgb_tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        mgb_tc_fence_after();
+        mgb_tmem_dealloc(tmem_base, TC_TMEM_COLS);
+    }
+}
+
+}  // namespace
+
+// ---- host side of K6-TC -------------------------------------------------------------------
+namespace {
+constexpr int TC_SCORE_MIN_D = 33;  // smaller latent spaces stay on the register-resident SIMT kernel
+constexpr int TC_SCORE_KC = 8;
+constexpr int TC_SCORE_QCHUNK = 128;  // columns of one chunk of the quad operand = 32 quads: what one pass of the program sees
+
+bool tc_disabled() {
+    static int v = -1;
+    if (v < 0) {
+        const char* e = getenv("MGB_NO_TC");
+        v = (e && atoi(e) != 0) ? 1 : 0;
+    }
+    return v == 1;
+}
+}  // namespace
+
+int mgb_score_tc_prepare_model(mgb_model* m) {
+    if (m->D < TC_SCORE_MIN_D) return MGB_OK;
+    const int D = m->D, G = m->G;
+    int CW = (D + 7) & ~7;
+    int cpc = std::max(1, TC_BUF_COLS / CW);
+    if ((cpc * CW) % 16 != 0) {
+        CW = (D + 15) & ~15;
+        cpc = std::max(1, TC_BUF_COLS / CW);
+    }
+    if (CW > TC_BUF_COLS) {
+        mgb_set_error("tensor-core score: D = %d exceeds one accumulator buffer", D);
+        return MGB_E_UNSUPPORTED;
+    }
+    TcB B;
+    B.data = nullptr;
+    B.Kp = (D + 1 + 7) & ~7;
+    B.Np = (G * CW + 15) & ~15;
+    B.NC = cpc * CW;
+    B.KC = TC_SCORE_KC;
+    std::vector<float> packed = tc_pack_b(B, D + 1, G * CW, [&](int k, int n) -> double {
+        const int g = n / CW, j = n % CW;
+        if (j >= D) return 0.0;
+        return k < D ? m->prec_chol[((size_t)g * D + k) * D + j] : m->gmm_bias[(size_t)g * D + j];
+    });
+    MGB_CUDA(cudaMalloc((void**)&m->d_Bgmm, packed.size() * sizeof(float)));
+    MGB_CUDA(cudaMemcpy(m->d_Bgmm, packed.data(), packed.size() * sizeof(float), cudaMemcpyHostToDevice));
+    m->tcg_Kp = B.Kp; m->tcg_Np = B.Np; m->tcg_NC = B.NC; m->tcg_KC = B.KC; m->tcg_CW = CW;
+    return MGB_OK;
+}
+
+int mgb_score_tc_prepare_constraints(const mgb_model* m, mgb_constraints* c) {
+    if (m->D < TC_SCORE_MIN_D || c->n_quads == 0) return MGB_OK;
+    const int D = m->D, K = m->K, KP = c->KP;
+    const int NQC = TC_SCORE_QCHUNK / 4;  // quads per N-chunk
+    // column layout: quads in program order, but a slot never straddles a chunk (the interpreter runs chunk by chunk)
+    std::vector<int> pos(c->n_quads);  // position (in quads) of every quad in the padded layout
+    int cur = 0;
+    for (int q = 0; q < c->n_quads;) {
+        int e = q;
+        while (e < c->n_quads && c->quad_slot[e] == c->quad_slot[q]) ++e;
+        const int cnt = e - q;
+        if (cnt > NQC) {
+            mgb_set_error("tensor-core score: a time slot needs %d quads (max %d per chunk)", cnt, NQC);
+            return MGB_E_UNSUPPORTED;
+        }
+        if (cur / NQC != (cur + cnt - 1) / NQC) cur = (cur / NQC + 1) * NQC;
+        for (int i = q; i < e; ++i) pos[i] = cur++;
+        q = e;
+    }
+    const int n_pos = cur;
+    const int n_chunks = (n_pos + NQC - 1) / NQC;
+    std::vector<int> quad_at(n_pos, -1);
+    for (int q = 0; q < c->n_quads; ++q) quad_at[pos[q]] = q;
+    TcB B;
+    B.data = nullptr;
+    B.Kp = (D + 1 + 7) & ~7;
+    B.Np = (4 * n_pos + 15) & ~15;
+    B.NC = std::min(TC_SCORE_QCHUNK, B.Np);
+    B.KC = TC_SCORE_KC;
+    // row k < K: basis row k of the quad; row D (the one that meets the 1 of the A tile): the mean
+    std::vector<float> packed = tc_pack_b(B, D + 1, 4 * n_pos, [&](int k, int n) -> double {
+        const int q = quad_at[n >> 2], ch = n & 3;
+        if (q < 0) return 0.0;
+        if (k < K) return c->tab64[((size_t)q * (KP + 1) + 1 + k) * 4 + ch];
+        if (k == D) return c->tab64[((size_t)q * (KP + 1)) * 4 + ch];
+        return 0.0;
+    });
+    // program: quad fields -> position inside the chunk; phase table
+    c->ops_tc = c->ops_fused;
+    c->phase_tc.assign(n_chunks + 1, 0);
+    int chunk = 0;
+    for (size_t i = 0; i < c->ops_tc.size(); ++i) {
+        MgbOp& o = c->ops_tc[i];
+        const bool qa = o.code == OP_ROOT || o.code == OP_JOINT || o.code == OP_ALIGN, qb = o.code == OP_ROOT;
+        if (!qa) continue;
+        const int ca = pos[o.a] / NQC, cb = qb ? pos[o.b] / NQC : ca;
+        if (ca != cb || ca < chunk) {
+            mgb_set_error("tensor-core score: program is not monotone in its quads");
+            return MGB_E_UNSUPPORTED;
+        }
+        while (chunk < ca) c->phase_tc[++chunk] = (int)i;
+        o.a = pos[o.a] % NQC;
+        if (qb) o.b = pos[o.b] % NQC;
+    }
+    while (chunk < n_chunks) c->phase_tc[++chunk] = (int)c->ops_tc.size();
+    c->phase_tc[n_chunks] = (int)c->ops_tc.size();  // ops after the last quad (finals) run with the last chunk
+    MGB_CUDA(cudaMalloc((void**)&c->d_Bq, packed.size() * sizeof(float)));
+    MGB_CUDA(cudaMemcpy(c->d_Bq, packed.data(), packed.size() * sizeof(float), cudaMemcpyHostToDevice));
+    MGB_CUDA(cudaMalloc((void**)&c->d_ops_tc, c->ops_tc.size() * sizeof(MgbOp)));
+    MGB_CUDA(cudaMemcpy(c->d_ops_tc, c->ops_tc.data(), c->ops_tc.size() * sizeof(MgbOp), cudaMemcpyHostToDevice));
+    MGB_CUDA(cudaMalloc((void**)&c->d_phase_tc, c->phase_tc.size() * sizeof(int)));
+    MGB_CUDA(cudaMemcpy(c->d_phase_tc, c->phase_tc.data(), c->phase_tc.size() * sizeof(int), cudaMemcpyHostToDevice));
+    c->tcq_Kp = B.Kp; c->tcq_Np = B.Np; c->tcq_NC = B.NC; c->tcq_KC = B.KC;
+    return MGB_OK;
+}
+
+static bool tc_score_plan(const mgb_model* m, const mgb_constraints* c, float quality_scale, TcScoreParams* out, size_t* smem_out) {
+    TcScoreParams p;
+    memset(&p, 0, sizeof(p));
+    p.seg_q = p.seg_g = -1;
+    p.segs.n = 0;
+    p.Kp = (m->D + 1 + 7) & ~7;
+    const bool use_q = c && c->n_quads > 0;
+    const bool use_g = quality_scale != 0.f;
+    if (use_q) {
+        if (!c->d_Bq) return false;
+        TcB& B = p.segs.seg[p.segs.n];
+        B.data = c->d_Bq; B.Kp = c->tcq_Kp; B.Np = c->tcq_Np; B.NC = c->tcq_NC; B.KC = c->tcq_KC;
+        p.seg_q = p.segs.n++;
+        p.phase = c->d_phase_tc;
+    }
+    if (use_g) {
+        if (!m->d_Bgmm) return false;
+        TcB& B = p.segs.seg[p.segs.n];
+        B.data = m->d_Bgmm; B.Kp = m->tcg_Kp; B.Np = m->tcg_Np; B.NC = m->tcg_NC; B.KC = m->tcg_KC;
+        p.seg_g = p.segs.n++;
+        p.CW = m->tcg_CW;
+        p.cpc = m->tcg_NC / m->tcg_CW;
+    }
+    if (p.segs.n == 0) return false;
+    p.QS = std::max(use_q ? std::min(c->tcq_Np, TC_SCORE_QCHUNK) : 0, m->D) | 1;
+    size_t stage_bytes = 0;
+    for (int i = 0; i < p.segs.n; ++i) stage_bytes = std::max(stage_bytes, (size_t)2 * p.segs.seg[i].NC * p.segs.seg[i].KC * 4);
+    const int n_ops = c ? c->n_ops : 0, n_cst = c ? c->n_cst : 0;
+    // preference: program in shared memory with >= 2 stages, else program read through L1
+    for (int in_smem = 1; in_smem >= 0; --in_smem) {
+        for (int nst = TC_MAX_STAGES; nst >= 2; --nst) {
+            const size_t total = tc_score_smem_plan(p.Kp, stage_bytes, nst, p.QS, in_smem ? n_ops : 0, in_smem ? n_cst : 0).total;
+            if (total + 1024 <= TC_SMEM_BUDGET) {
+                p.nst = nst;
+                p.ops_in_smem = in_smem;
+                *out = p;
+                *smem_out = total;
+                return true;
+            }
+        }
+    }
+    return false;
+}
+
+bool mgb_score_tc_usable(const mgb_model* m, const mgb_constraints* c, float quality_scale) {
+    if (tc_disabled() || m->D < TC_SCORE_MIN_D) return false;
+    TcScoreParams p;
+    size_t smem;
+    return tc_score_plan(m, c, quality_scale, &p, &smem);
+}
+
+int mgb_launch_score_tc(const mgb_model* m, const mgb_constraints* c, const ScoreParams& sp, int s_is_f64, float quality_scale,
+                        cudaStream_t stream) {
+    TcScoreParams p;
+    size_t smem = 0;
+    MGB_REQUIRE(tc_score_plan(m, c, quality_scale, &p, &smem), "tensor-core score path is not available for this model / constraint set");
+    p.sp = sp;
+    p.sp.ops = c ? c->d_ops_tc : nullptr;
+    static bool configured = false;
+    if (!configured) {
+        MGB_CUDA(cudaFuncSetAttribute(mgb_score_tc_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM_BUDGET));
+        MGB_CUDA(cudaFuncSetAttribute(mgb_score_tc_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM_BUDGET));
+        configured = true;
+    }
+    const long long n_tiles = (sp.n + TC_M - 1) / TC_M;
+    const int grid = (int)std::min<long long>(n_tiles, tc_num_sms());
+    if (s_is_f64)
+        mgb_score_tc_kernel<double><<<grid, TC_THREADS, smem, stream>>>(p);
+    else
+        mgb_score_tc_kernel<float><<<grid, TC_THREADS, smem, stream>>>(p);
     mgb_count_launch();
     MGB_CUDA(cudaGetLastError());
     return MGB_OK;
