@@ -192,6 +192,8 @@ extern "C" int mgb_model_create(const mgb_model_desc* d, int device, mgb_model**
     std::vector<double> L, Pc((size_t)D * D);
     m->prec_chol.assign((size_t)G * D * D, 0.0);
     m->gmm_bias.assign((size_t)G * D, 0.0);
+    m->chol64.assign((size_t)G * D * D, 0.0);
+    m->means64.assign(d->gmm_means, d->gmm_means + (size_t)G * D);
     for (int g = 0; g < G; ++g) {
         if (!cholesky_lower(d->gmm_covars + (size_t)g * D * D, D, L)) {
             mgb_set_error("covariance of GMM component %d is not positive definite", g);
@@ -232,7 +234,10 @@ extern "C" int mgb_model_create(const mgb_model_desc* d, int device, mgb_model**
                 m->gmm_bias[(size_t)g * D + j] -= mu[k] * Pc[(size_t)k * D + j];
             }
         for (int i = 0; i < D; ++i)
-            for (int j = 0; j <= i; ++j) chol[((size_t)g * D + i) * LS + j] = (float)L[(size_t)i * D + j];
+            for (int j = 0; j <= i; ++j) {
+                chol[((size_t)g * D + i) * LS + j] = (float)L[(size_t)i * D + j];
+                m->chol64[((size_t)g * D + i) * D + j] = L[(size_t)i * D + j];
+            }
         for (int i = 0; i < D; ++i) means[(size_t)g * D + i] = (float)mu[i];
     }
     m->gmm_tab_bytes = gtab.size() * sizeof(float4);
@@ -254,8 +259,8 @@ extern "C" int mgb_model_create(const mgb_model_desc* d, int device, mgb_model**
         m->d_Bsplit = nullptr;
     }
     if (mgb_score_tc_prepare_model(m) != MGB_OK) {
-        cudaFree(m->d_Bgmm);
-        m->d_Bgmm = nullptr;
+        cudaFree(m->d_Bgmm); cudaFree(m->d_Bsamp);
+        m->d_Bgmm = nullptr; m->d_Bsamp = nullptr;
     }
     *out = m;
     return MGB_OK;
@@ -266,7 +271,7 @@ extern "C" void mgb_model_destroy(mgb_model* m) {
     cudaSetDevice(m->device);
     cudaFree(m->d_E); cudaFree(m->d_mean); cudaFree(m->d_gmm_tab); cudaFree(m->d_gmm_c); cudaFree(m->d_chol);
     cudaFree(m->d_means); cudaFree(m->d_parent); cudaFree(m->d_type); cudaFree(m->d_channel); cudaFree(m->d_offset);
-    cudaFree(m->d_fixed_rot); cudaFree(m->d_Bsplit); cudaFree(m->d_Bgmm); cudaFree(m->d_ws);
+    cudaFree(m->d_fixed_rot); cudaFree(m->d_Bsplit); cudaFree(m->d_Bgmm); cudaFree(m->d_Bsamp); cudaFree(m->d_ws);
     for (int b = 0; b < 2; ++b) {
         if (m->pinned[b]) cudaFreeHost(m->pinned[b]);
         cudaFree(m->d_stage[b]);

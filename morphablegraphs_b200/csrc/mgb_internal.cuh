@@ -108,6 +108,10 @@ struct mgb_model {
     std::vector<double> gmm_bias;   // [G][D]   -mu_g . P_g
     float* d_Bgmm = nullptr;
     int tcg_Kp = 0, tcg_Np = 0, tcg_NC = 0, tcg_KC = 0, tcg_CW = 0;
+    std::vector<double> chol64;     // [G][D][D] lower Cholesky factors of the covariances, fp64
+    std::vector<double> means64;    // [G][D]
+    float* d_Bsamp = nullptr;       // sampling operand: per component [L_g^T ; mu_g], one N-chunk each
+    int tcs_Kp = 0, tcs_Np = 0, tcs_NC = 0, tcs_KC = 0;
     // private streams / staging for the host-buffer entry
     cudaStream_t copy_stream = nullptr, compute_stream = nullptr;
     void* pinned[2] = {nullptr, nullptr};
@@ -208,4 +212,4 @@ int mgb_score_tc_prepare_model(mgb_model* m);
 int mgb_score_tc_prepare_constraints(const mgb_model* m, mgb_constraints* c);
 bool mgb_score_tc_usable(const mgb_model* m, const mgb_constraints* c, float quality_scale);
 int mgb_launch_score_tc(const mgb_model* m, const mgb_constraints* c, const ScoreParams& p, int s_is_f64, float quality_scale,
-                        cudaStream_t stream);
+                        int sample, cudaStream_t stream);

@@ -635,9 +635,9 @@ int mgb_launch_score(const mgb_model* m, const mgb_constraints* c, int mode, con
 
     int rc;
     const int D = m->D;
-    if (mode == MODE_S && mgb_score_tc_usable(m, c, quality_scale)) {
-        // large latent spaces: contraction + GMM log-density on the tensor cores (mgb_tc.cu)
-        rc = mgb_launch_score_tc(m, c, p, s_is_f64, quality_scale, stream);
+    if ((mode == MODE_S || mode == MODE_SAMPLE) && mgb_score_tc_usable(m, c, quality_scale)) {
+        // large latent spaces: sampling, contraction and GMM log-density on the tensor cores (mgb_tc.cu)
+        rc = mgb_launch_score_tc(m, c, p, s_is_f64, quality_scale, mode == MODE_SAMPLE ? 1 : 0, stream);
     } else if (mode == MODE_FRAMES) {
         rc = launch_variant<0, 1, MODE_FRAMES, float>(p, plan, stream);
     } else if (mode == MODE_SAMPLE) {

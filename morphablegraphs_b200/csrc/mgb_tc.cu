@@ -118,19 +118,32 @@ __device__ __forceinline__ TcBars tc_bars(unsigned char* base) {
 // The constant operands of one tile pass: up to two packed matrices that share the A tile
 // (e.g. the contracted constraint quads, then the GMM precision factors), streamed in order.
 struct TcSegs {
-    TcB seg[2];
+    TcB seg[3];
     int n;
+    int samp_seg;                       // >= 0: this operand (one N-chunk per GMM component) is multiplied first, by the tile's own
+                                        // component only, against the first of TWO fills of the A tile (z, then s = mu + L z)
+    int tile_first[MGB_MAX_GMM + 1];    // sampling mode: first tile of every component (tiles never straddle components)
+    int G;
 };
+// component of tile T (sampling mode)
+__device__ __forceinline__ int tc_tile_comp(const int* tile_first, int G, long long T) {
+    int g = 0;
+    while (g + 1 < G && T >= tile_first[g + 1]) ++g;
+    return g;
+}
 
 // warp 0, one lane: stream every stage image of every operand once per tile
 __device__ __forceinline__ void tc_b_producer(const TcSegs& S, unsigned char* sm_stage, size_t stage_bytes, int nst, const TcBars& bars,
-                                              long long my_tiles) {
+                                              long long my_tiles, const int* tile_first = nullptr) {
     unsigned int it = 0;
     for (long long t = 0; t < my_tiles; ++t) {
+        const int gcomp = (S.samp_seg >= 0) ? tc_tile_comp(tile_first, S.G, blockIdx.x + t * gridDim.x) : 0;
         for (int sg = 0; sg < S.n; ++sg) {
             const TcB& B = S.seg[sg];
-            const int n_nc = B.n_nc(), n_kc = B.n_kc();
-            for (int c = 0; c < n_nc; ++c) {
+            const bool samp = sg == S.samp_seg;
+            const int c_lo = samp ? gcomp : 0, c_hi = samp ? gcomp + 1 : B.n_nc();
+            const int n_kc = B.n_kc();
+            for (int c = c_lo; c < c_hi; ++c) {
                 const int wc = B.wc(c);
                 for (int kc = 0; kc < n_kc; ++kc, ++it) {
                     const int st = it % nst;
@@ -148,16 +161,21 @@ __device__ __forceinline__ void tc_b_producer(const TcSegs& S, unsigned char* sm
 // warp 1, one lane: all MMAs of this CTA.  Chunk number cc (counted over all operands and tiles)
 // accumulates into TMEM buffer cc & 1.
 __device__ __forceinline__ void tc_mma_issuer(const TcSegs& S, uint32_t a_hi_addr, uint32_t a_lo_addr, uint32_t stage_addr, size_t stage_bytes,
-                                              int nst, const TcBars& bars, uint32_t tmem_base, long long my_tiles) {
-    unsigned int it = 0, cc = 0;
+                                              int nst, const TcBars& bars, uint32_t tmem_base, long long my_tiles,
+                                              const int* tile_first = nullptr) {
+    unsigned int it = 0, cc = 0, fill = 0;
     const uint32_t A_LBO = TC_M * 16, SBO = 128;
     for (long long t = 0; t < my_tiles; ++t) {
-        mgb_mbar_wait(bars.a_full, (unsigned int)(t & 1));
+        const int gcomp = (S.samp_seg >= 0) ? tc_tile_comp(tile_first, S.G, blockIdx.x + t * gridDim.x) : 0;
+        mgb_mbar_wait(bars.a_full, fill & 1u);
+        ++fill;
         mgb_tc_fence_after();
         for (int sg = 0; sg < S.n; ++sg) {
             const TcB& B = S.seg[sg];
-            const int n_nc = B.n_nc(), n_kc = B.n_kc();
-            for (int c = 0; c < n_nc; ++c, ++cc) {
+            const bool samp = sg == S.samp_seg;
+            const int c_lo = samp ? gcomp : 0, c_hi = samp ? gcomp + 1 : B.n_nc();
+            const int n_kc = B.n_kc();
+            for (int c = c_lo; c < c_hi; ++c, ++cc) {
                 const int wc = B.wc(c);
                 const unsigned int buf = cc & 1u;
                 mgb_mbar_wait(&bars.t_empty[buf], ((cc >> 1) & 1u) ^ 1u);
@@ -188,6 +206,11 @@ __device__ __forceinline__ void tc_mma_issuer(const TcSegs& S, uint32_t a_hi_add
                     mgb_umma_commit(&bars.b_empty[st]);
                 }
                 mgb_umma_commit(&bars.t_full[buf]);
+            }
+            if (samp) {  // the A tile is refilled with the drawn latent vectors before the other operands
+                mgb_mbar_wait(bars.a_full, fill & 1u);
+                ++fill;
+                mgb_tc_fence_after();
             }
         }
         mgb_umma_commit(bars.a_empty);
@@ -273,6 +296,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mgb_backproject_tc_kernel(const
             TcSegs S;
             S.seg[0] = p.B;
             S.n = 1;
+            S.samp_seg = -1;
             tc_b_producer(S, smem + plan.b_stage, plan.stage_bytes, p.nst, bars, my_tiles);
         }
     } else if (warp == 1) {
@@ -280,6 +304,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mgb_backproject_tc_kernel(const
             TcSegs S;
             S.seg[0] = p.B;
             S.n = 1;
+            S.samp_seg = -1;
             tc_mma_issuer(S, mgb_smem_u32(smem + plan.a_hi), mgb_smem_u32(smem + plan.a_lo), mgb_smem_u32(smem + plan.b_stage),
                           plan.stage_bytes, p.nst, bars, tmem_base, my_tiles);
         }
@@ -531,10 +556,13 @@ struct TcScoreParams {
     int ops_in_smem;   // program + constants staged in shared memory (else read through L1)
     int CW;            // GMM columns per component
     int cpc;           // components per N-chunk
+    int seg_s;         // sampling operand (fused K1), -1 if the candidates come from memory
+    int CWs;           // its columns per component
+    long long n_tiles; // tiles of this launch (sampling mode: per-component tiling)
 };
 
 struct TcScoreSmem {
-    size_t a_hi, a_lo, b_stage, qv, ops, cst, lp, redc, redi, bars, sbar, tmem_ptr, flag, total;
+    size_t a_hi, a_lo, b_stage, qv, ops, cst, lp, redc, redi, bars, sbar, tmem_ptr, flag, tfirst, total;
     size_t stage_bytes;
 };
 __host__ __device__ inline TcScoreSmem tc_score_smem_plan(int Kp, size_t stage_bytes, int nst, int QS, int n_ops, int n_cst) {
@@ -554,13 +582,14 @@ __host__ __device__ inline TcScoreSmem tc_score_smem_plan(int Kp, size_t stage_b
     p.sbar = off; off += 8;
     p.tmem_ptr = off; off += 8;
     p.flag = off; off += 8;
+    p.tfirst = off; off += (MGB_MAX_GMM + 1) * 4 + 12;
     p.total = off;
     return p;
 }
 
 __device__ __forceinline__ bool tc_better(float c1, long long i1, float c2, long long i2) { return (c1 < c2) || (c1 == c2 && i1 < i2); }
 
-template <typename SIn>
+template <typename SIn, bool SAMPLE>
 __global__ void __launch_bounds__(TC_THREADS, 1) mgb_score_tc_kernel(const __grid_constant__ TcScoreParams p) {
     extern __shared__ __align__(1024) unsigned char smem[];
     const ScoreParams& sp = p.sp;
@@ -575,8 +604,11 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mgb_score_tc_kernel(const __gri
     float* sm_lp = reinterpret_cast<float*>(smem + L.lp);
     float* qv = reinterpret_cast<float*>(smem + L.qv);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const long long n_tiles = (sp.n + TC_M - 1) / TC_M;
+    const long long n_tiles = p.n_tiles;
     const long long my_tiles = (n_tiles > blockIdx.x) ? (n_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+    int* sm_tile_first = reinterpret_cast<int*>(smem + L.tfirst);
+    if (SAMPLE)
+        for (int i = threadIdx.x; i <= MGB_MAX_GMM; i += TC_THREADS) sm_tile_first[i] = p.segs.tile_first[i];
 
     if (p.ops_in_smem) {
         for (int i = threadIdx.x; i < sp.n_ops; i += TC_THREADS) sm_ops[i] = sp.ops[i];
@@ -607,11 +639,11 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mgb_score_tc_kernel(const __gri
     const int n_nc_g = p.seg_g >= 0 ? p.segs.seg[p.seg_g].n_nc() : 0;
 
     if (warp == 0) {
-        if (lane == 0) tc_b_producer(p.segs, smem + L.b_stage, L.stage_bytes, p.nst, bars, my_tiles);
+        if (lane == 0) tc_b_producer(p.segs, smem + L.b_stage, L.stage_bytes, p.nst, bars, my_tiles, sm_tile_first);
     } else if (warp == 1) {
         if (lane == 0)
             tc_mma_issuer(p.segs, mgb_smem_u32(smem + L.a_hi), mgb_smem_u32(smem + L.a_lo), mgb_smem_u32(smem + L.b_stage), L.stage_bytes,
-                          p.nst, bars, tmem_base, my_tiles);
+                          p.nst, bars, tmem_base, my_tiles, sm_tile_first);
     } else if (warp < 6) {
         // ================= group 0: A producer, quad drain, constraint program, selection =================
         const int wq = warp & 3;
@@ -627,37 +659,96 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mgb_score_tc_kernel(const __gri
         long long best_i = LLONG_MAX;
         unsigned int cc = 0, sload = 0;
         for (long long t = 0; t < my_tiles; ++t) {
-            const long long g0 = (blockIdx.x + t * gridDim.x) * TC_M;
-            const long long idx = g0 + row;
-            const bool valid = idx < sp.n;
-            // ---- A tile: [s | 1] split into TF32 hi / lo -------------------------------------------
+            const long long T = blockIdx.x + t * gridDim.x;
+            long long g0 = T * TC_M, idx, gi = 0;
+            bool valid;
             float m2 = 0.f;
-            for (int piece = 0; piece < NH; ++piece) {
-                const long long r0 = g0 + (long long)piece * RP;
-                const long long rows_here = max(0LL, min((long long)RP, sp.n - r0));
-                asm volatile("bar.sync 3, 128;" ::: "memory");  // the area is free: program of the previous tile / previous piece done
-                if (sp.s_aligned && rows_here == RP) {
-                    if (tid0 == 0) {
-                        const unsigned int bytes = (unsigned int)(RP * D * sizeof(SIn));
-                        mgb_fence_proxy_async();  // generic-proxy accesses of the area are ordered before the async-proxy write
-                        mgb_mbar_expect_tx(s_full, bytes);
-                        mgb_bulk_g2s(raw, s_glob + (size_t)r0 * D, bytes, s_full);
+            if constexpr (SAMPLE) {
+                // ---- fused K1: this tile holds (up to) 128 consecutive candidates of ONE mixture component -------
+                const int g = tc_tile_comp(sm_tile_first, sp.G, T);
+                const long long lo = max(sp.prefix.v[g], sp.index_base), hi = min(sp.prefix.v[g + 1], sp.index_base + sp.n);
+                const long long gstart = lo + (T - sm_tile_first[g]) * TC_M;
+                gi = gstart + row;
+                valid = gi < hi;
+                idx = gi - sp.index_base;
+                const uint2 key = make_uint2((unsigned int)sp.seed, (unsigned int)(sp.seed >> 32));
+                mgb_mbar_wait(bars.a_empty, (unsigned int)(t & 1) ^ 1u);
+                // fill 1 of A: [z | 1], z = the standard normals mgb_sample draws for global index gi
+                for (int k0 = 0; k0 < p.Kp; k0 += 4) {
+                    float z[4] = {0.f, 0.f, 0.f, 0.f};
+                    if (valid && k0 < D) mgb_normal4((unsigned long long)gi, (unsigned int)(k0 >> 2), key, z);
+                    float h[4], l[4];
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        const int k = k0 + q;
+                        const float v = !valid ? 0.f : (k < D ? z[q] : (k == D ? 1.f : 0.f));
+                        mgb_tf32_split(v, h[q], l[q]);
                     }
-                    mgb_mbar_wait(s_full, sload & 1u);
-                    ++sload;
-                } else {
-                    const long long remaining = rows_here * D;
-                    for (int e = tid0; e < RP * D; e += 128) raw[e] = (e < remaining) ? s_glob[(size_t)r0 * D + e] : (SIn)0;
-                    asm volatile("bar.sync 3, 128;" ::: "memory");
+                    const uint32_t off = mgb_canon_off((uint32_t)row, (uint32_t)k0, TC_M);
+                    *reinterpret_cast<float4*>(smem + L.a_hi + off) = make_float4(h[0], h[1], h[2], h[3]);
+                    *reinterpret_cast<float4*>(smem + L.a_lo + off) = make_float4(l[0], l[1], l[2], l[3]);
                 }
-                if (piece == 0) mgb_mbar_wait(bars.a_empty, (unsigned int)(t & 1) ^ 1u);
-                if (row / RP == piece) {
-                    const SIn* mine = raw + (size_t)(row - piece * RP) * D;
-                    tc_write_a_row(smem + L.a_hi, smem + L.a_lo, row, p.Kp, valid ? D + 1 : 0, [&](int k) {
-                        const float v = k < D ? (float)mine[k] : 1.f;
-                        if (k < D) m2 = fmaf(v, v, m2);
-                        return v;
-                    });
+                mgb_fence_proxy_async();
+                mgb_mbar_arrive(bars.a_full);
+                // s = mu_g + L_g z comes back in TMEM; fill 2 of A: [s | 1]
+                {
+                    const unsigned int buf = cc & 1u;
+                    mgb_mbar_wait(&bars.t_full[buf], (cc >> 1) & 1u);
+                    mgb_tc_fence_after();
+                    const uint32_t base = lane_addr + buf * TC_BUF_COLS;
+                    for (int b0 = 0; b0 < p.Kp; b0 += 8) {
+                        float v[8];
+                        mgb_tmem_ld8(base + b0, v);
+                        float h[8], l[8];
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) {
+                            const int k = b0 + i;
+                            const float x = !valid ? 0.f : (k < D ? v[i] : (k == D ? 1.f : 0.f));
+                            if (k < D) m2 = fmaf(x, x, m2);
+                            mgb_tf32_split(x, h[i], l[i]);
+                        }
+#pragma unroll
+                        for (int i = 0; i < 8; i += 4) {
+                            const uint32_t off = mgb_canon_off((uint32_t)row, (uint32_t)(b0 + i), TC_M);
+                            *reinterpret_cast<float4*>(smem + L.a_hi + off) = make_float4(h[i], h[i + 1], h[i + 2], h[i + 3]);
+                            *reinterpret_cast<float4*>(smem + L.a_lo + off) = make_float4(l[i], l[i + 1], l[i + 2], l[i + 3]);
+                        }
+                    }
+                    mgb_tc_fence_before();
+                    mgb_mbar_arrive_relaxed(&bars.t_empty[buf]);
+                    ++cc;
+                }
+            } else {
+                idx = g0 + row;
+                valid = idx < sp.n;
+                // ---- A tile: [s | 1] split into TF32 hi / lo -------------------------------------------
+                for (int piece = 0; piece < NH; ++piece) {
+                    const long long r0 = g0 + (long long)piece * RP;
+                    const long long rows_here = max(0LL, min((long long)RP, sp.n - r0));
+                    asm volatile("bar.sync 3, 128;" ::: "memory");  // the area is free: program of the previous tile / previous piece done
+                    if (sp.s_aligned && rows_here == RP) {
+                        if (tid0 == 0) {
+                            const unsigned int bytes = (unsigned int)(RP * D * sizeof(SIn));
+                            mgb_fence_proxy_async();  // generic-proxy accesses of the area are ordered before the async-proxy write
+                            mgb_mbar_expect_tx(s_full, bytes);
+                            mgb_bulk_g2s(raw, s_glob + (size_t)r0 * D, bytes, s_full);
+                        }
+                        mgb_mbar_wait(s_full, sload & 1u);
+                        ++sload;
+                    } else {
+                        const long long remaining = rows_here * D;
+                        for (int e = tid0; e < RP * D; e += 128) raw[e] = (e < remaining) ? s_glob[(size_t)r0 * D + e] : (SIn)0;
+                        asm volatile("bar.sync 3, 128;" ::: "memory");
+                    }
+                    if (piece == 0) mgb_mbar_wait(bars.a_empty, (unsigned int)(t & 1) ^ 1u);
+                    if (row / RP == piece) {
+                        const SIn* mine = raw + (size_t)(row - piece * RP) * D;
+                        tc_write_a_row(smem + L.a_hi, smem + L.a_lo, row, p.Kp, valid ? D + 1 : 0, [&](int k) {
+                            const float v = k < D ? (float)mine[k] : 1.f;
+                            if (k < D) m2 = fmaf(v, v, m2);
+                            return v;
+                        });
+                    }
                 }
             }
             mgb_fence_proxy_async();
@@ -764,6 +855,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mgb_score_tc_kernel(const __gri
         for (long long t = 0; t < my_tiles; ++t) {
             // the quad chunks belong to group 0, but this group still has to OBSERVE every phase of the accumulator
             // barriers: a parity wait is only meaningful when the waiter is at most one phase ahead of the barrier
+            if (SAMPLE) {
+                mgb_mbar_wait(&bars.t_full[cc & 1u], (cc >> 1) & 1u);
+                ++cc;
+            }
             for (int c = 0; c < n_nc_q; ++c, ++cc) mgb_mbar_wait(&bars.t_full[cc & 1u], (cc >> 1) & 1u);
             float mx = -INFINITY, ssum = 0.f;
             int g = 0;
@@ -862,6 +957,25 @@ int mgb_score_tc_prepare_model(mgb_model* m) {
     MGB_CUDA(cudaMalloc((void**)&m->d_Bgmm, packed.size() * sizeof(float)));
     MGB_CUDA(cudaMemcpy(m->d_Bgmm, packed.data(), packed.size() * sizeof(float), cudaMemcpyHostToDevice));
     m->tcg_Kp = B.Kp; m->tcg_Np = B.Np; m->tcg_NC = B.NC; m->tcg_KC = B.KC; m->tcg_CW = CW;
+    // sampling operand: s = z . L_g^T + mu_g, one N-chunk per component (row D meets the 1 of the A tile)
+    const int CWs = (D + 15) & ~15;
+    if (CWs <= TC_BUF_COLS && G <= MGB_MAX_GMM) {
+        TcB S;
+        S.data = nullptr;
+        S.Kp = B.Kp;
+        S.Np = G * CWs;
+        S.NC = CWs;
+        S.KC = TC_SCORE_KC;
+        std::vector<float> ps = tc_pack_b(S, D + 1, G * CWs, [&](int k, int n) -> double {
+            const int g = n / CWs, j = n % CWs;
+            if (j >= D) return 0.0;
+            if (k == D) return m->means64[(size_t)g * D + j];
+            return k <= j ? m->chol64[((size_t)g * D + j) * D + k] : 0.0;
+        });
+        MGB_CUDA(cudaMalloc((void**)&m->d_Bsamp, ps.size() * sizeof(float)));
+        MGB_CUDA(cudaMemcpy(m->d_Bsamp, ps.data(), ps.size() * sizeof(float), cudaMemcpyHostToDevice));
+        m->tcs_Kp = S.Kp; m->tcs_Np = S.Np; m->tcs_NC = S.NC; m->tcs_KC = S.KC;
+    }
     return MGB_OK;
 }
 
@@ -931,12 +1045,21 @@ int mgb_score_tc_prepare_constraints(const mgb_model* m, mgb_constraints* c) {
     return MGB_OK;
 }
 
-static bool tc_score_plan(const mgb_model* m, const mgb_constraints* c, float quality_scale, TcScoreParams* out, size_t* smem_out) {
+static bool tc_score_plan(const mgb_model* m, const mgb_constraints* c, float quality_scale, int sample, TcScoreParams* out, size_t* smem_out) {
     TcScoreParams p;
     memset(&p, 0, sizeof(p));
-    p.seg_q = p.seg_g = -1;
+    p.seg_q = p.seg_g = p.seg_s = -1;
     p.segs.n = 0;
+    p.segs.samp_seg = -1;
+    p.segs.G = m->G;
     p.Kp = (m->D + 1 + 7) & ~7;
+    if (sample) {  // must be the first operand: it is multiplied against the first fill of the A tile
+        if (!m->d_Bsamp) return false;
+        TcB& B = p.segs.seg[p.segs.n];
+        B.data = m->d_Bsamp; B.Kp = m->tcs_Kp; B.Np = m->tcs_Np; B.NC = m->tcs_NC; B.KC = m->tcs_KC;
+        p.seg_s = p.segs.samp_seg = p.segs.n++;
+        p.CWs = m->tcs_NC;
+    }
     const bool use_q = c && c->n_quads > 0;
     const bool use_g = quality_scale != 0.f;
     if (use_q) {
@@ -954,7 +1077,7 @@ static bool tc_score_plan(const mgb_model* m, const mgb_constraints* c, float qu
         p.CW = m->tcg_CW;
         p.cpc = m->tcg_NC / m->tcg_CW;
     }
-    if (p.segs.n == 0) return false;
+    if (p.segs.n == (sample ? 1 : 0)) return false;
     p.QS = std::max(use_q ? std::min(c->tcq_Np, TC_SCORE_QCHUNK) : 0, m->D) | 1;
     size_t stage_bytes = 0;
     for (int i = 0; i < p.segs.n; ++i) stage_bytes = std::max(stage_bytes, (size_t)2 * p.segs.seg[i].NC * p.segs.seg[i].KC * 4);
@@ -979,28 +1102,42 @@ bool mgb_score_tc_usable(const mgb_model* m, const mgb_constraints* c, float qua
     if (tc_disabled() || m->D < TC_SCORE_MIN_D) return false;
     TcScoreParams p;
     size_t smem;
-    return tc_score_plan(m, c, quality_scale, &p, &smem);
+    return tc_score_plan(m, c, quality_scale, 0, &p, &smem) && m->d_Bsamp != nullptr;
 }
 
 int mgb_launch_score_tc(const mgb_model* m, const mgb_constraints* c, const ScoreParams& sp, int s_is_f64, float quality_scale,
-                        cudaStream_t stream) {
+                        int sample, cudaStream_t stream) {
     TcScoreParams p;
     size_t smem = 0;
-    MGB_REQUIRE(tc_score_plan(m, c, quality_scale, &p, &smem), "tensor-core score path is not available for this model / constraint set");
+    MGB_REQUIRE(tc_score_plan(m, c, quality_scale, sample, &p, &smem), "tensor-core score path is not available for this model / constraint set");
     p.sp = sp;
     p.sp.ops = c ? c->d_ops_tc : nullptr;
+    p.n_tiles = (sp.n + TC_M - 1) / TC_M;
+    if (sample) {
+        // tiles never straddle mixture components: component g owns ceil(len_g / 128) tiles of this shard
+        int acc = 0;
+        for (int g = 0; g < m->G; ++g) {
+            p.segs.tile_first[g] = acc;
+            const long long lo = std::max<long long>(sp.prefix.v[g], sp.index_base), hi = std::min<long long>(sp.prefix.v[g + 1], sp.index_base + sp.n);
+            if (hi > lo) acc += (int)((hi - lo + TC_M - 1) / TC_M);
+        }
+        for (int g = m->G; g <= MGB_MAX_GMM; ++g) p.segs.tile_first[g] = acc;
+        p.n_tiles = acc;
+    }
     static bool configured = false;
     if (!configured) {
-        MGB_CUDA(cudaFuncSetAttribute(mgb_score_tc_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM_BUDGET));
-        MGB_CUDA(cudaFuncSetAttribute(mgb_score_tc_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM_BUDGET));
+        MGB_CUDA(cudaFuncSetAttribute(mgb_score_tc_kernel<float, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM_BUDGET));
+        MGB_CUDA(cudaFuncSetAttribute(mgb_score_tc_kernel<double, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM_BUDGET));
+        MGB_CUDA(cudaFuncSetAttribute(mgb_score_tc_kernel<float, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM_BUDGET));
         configured = true;
     }
-    const long long n_tiles = (sp.n + TC_M - 1) / TC_M;
-    const int grid = (int)std::min<long long>(n_tiles, tc_num_sms());
-    if (s_is_f64)
-        mgb_score_tc_kernel<double><<<grid, TC_THREADS, smem, stream>>>(p);
+    const int grid = (int)std::max<long long>(1, std::min<long long>(p.n_tiles, tc_num_sms()));
+    if (sample)
+        mgb_score_tc_kernel<float, true><<<grid, TC_THREADS, smem, stream>>>(p);
+    else if (s_is_f64)
+        mgb_score_tc_kernel<double, false><<<grid, TC_THREADS, smem, stream>>>(p);
     else
-        mgb_score_tc_kernel<float><<<grid, TC_THREADS, smem, stream>>>(p);
+        mgb_score_tc_kernel<float, false><<<grid, TC_THREADS, smem, stream>>>(p);
     mgb_count_launch();
     MGB_CUDA(cudaGetLastError());
     return MGB_OK;

@@ -280,3 +280,50 @@ def test_errors_are_loud(big):
         engine.DeviceConstraints(big.dm, mpc)
     with pytest.raises(engine.MgbError):
         big.dc.score(big.dm.sample(10, seed=1), k=100)     # k outside [0, 64] is refused by the library
+
+
+# ---------------------------------------------------------------------------
+# large latent space (D = 103, G = 32): the tensor-core kernels (tcgen05, 3xTF32)
+# ---------------------------------------------------------------------------
+@pytest.fixture(scope="module")
+def large():
+    from morphablegraphs_b200 import engine
+    c = Case("l_mixed")
+    c.dm = engine.DeviceModel(c.node, c.skeleton)
+    c.dc = engine.DeviceConstraints(c.dm, c.constraints, c.prev_frames)
+    return c
+
+
+def test_large_tc_against_oracle(large):
+    """K6-TC (contraction + GMM log-density on the tensor cores) against the numpy oracle on seeded
+    draws, incl. a ragged last tile, naturalness and magnitude terms; log-pdf alone (K5b-TC)."""
+    from oracle import np_oracle as O
+    dm, dc = large.dm, large.dc
+    n = 1000 + 37
+    S = dm.sample(n, seed=5)
+    S64 = S.cpu().numpy().astype(np.float64)
+    ref = O.candidate_costs(large.node, large.skeleton, large.constraints, S64, prev_frames=large.prev_frames)
+    lp_ref = O.gmm_logpdf(O.ModelArrays(large.node), S64)
+    res = dc.score(S, k=1, return_cost=True)
+    assert rel_err(res["cost"].cpu().numpy(), ref).max() < RTOL
+    assert rel_err(dm.logpdf(S).cpu().numpy(), lp_ref).max() < RTOL
+    resn = dc.score(S.double(), k=1, return_cost=True, quality_scale=0.1, magnitude_scale=2.0)       # float64 input path
+    refn = ref + 0.1 * (-lp_ref) + 2.0 * np.linalg.norm(S64, axis=1)
+    assert rel_err(resn["cost"].cpu().numpy(), refn).max() < RTOL
+    _check_argmin(refn, int(resn["best_idx"][0]), float(resn["best_cost"][0]))
+
+
+def test_large_fused_sample_score(large):
+    """mgb_sample_score on the tensor cores (z -> s = mu + L z as a GEMM, tiles aligned to mixture components)
+    == mgb_sample (SIMT) then mgb_score, up to the 3xTF32 rounding of s."""
+    dm, dc = large.dm, large.dc
+    for n, base, total in ((20_001, 0, 20_001), (9_000, 12_345, 60_000)):
+        counts = dm.component_counts(total, seed=11)
+        S = dm.sample(n, seed=11, counts=counts, index_base=base, n_total=total)
+        for kw in ({}, {"quality_scale": 0.1}, {"magnitude_scale": 2.0}):
+            a = dc.score(S, k=1, return_cost=True, index_base=base, **kw)
+            b = dc.sample_score(n, seed=11, counts=counts, n_total=total, index_base=base, k=1, return_cost=True, **kw)
+            ca, cb = a["cost"].cpu().numpy(), b["cost"].cpu().numpy()
+            assert rel_err(cb, ca).max() < 2e-5
+            ia, ib = int(a["best_idx"][0]), int(b["best_idx"][0])
+            assert ia == ib or abs(float(ca[ia - base]) - float(ca[ib - base])) < 2e-5 * max(1.0, abs(float(ca[ia - base])))
