@@ -11,7 +11,7 @@ the arg-min.
 """
 import numpy as np
 
-from . import engine
+from . import engine, sharding
 from .objective_functions import obj_spatial_error_sum, _device_constraints
 
 SAMPLING_MODE_RANDOM = "random_discrete"
@@ -98,13 +98,24 @@ class MotionPrimitiveGenerator(object):
         seed = int(self._rng.randint(0, 2 ** 31 - 1))
         n = int(self.n_random_samples)
         obj = self.objective
-        res = dc.sample_score(n, seed=seed, k=1, error_scale=getattr(obj, "error_scale", 1.0),
-                              quality_scale=getattr(obj, "quality_scale", 0.0), magnitude_scale=getattr(obj, "magnitude_scale", 0.0))
+        # one process per GPU: every rank holds the same generator state (same seed), scores its own
+        # index range of the job and the per-rank bests are exchanged (sharding.py)
+        rank, world = 0, 1
+        if sharding.is_distributed():
+            import torch.distributed as dist
+            rank, world = dist.get_rank(), dist.get_world_size()
+        base, n_mine = sharding.shard_range(n, rank, world)
+        counts = dm.component_counts(n, seed)
+        res = dc.sample_score(n_mine, seed=seed, counts=counts, n_total=n, index_base=base, k=1,
+                              error_scale=getattr(obj, "error_scale", 1.0), quality_scale=getattr(obj, "quality_scale", 0.0),
+                              magnitude_scale=getattr(obj, "magnitude_scale", 0.0))
         best_idx = int(res["best_idx"][0].item())
         min_error = float(res["best_cost"][0].item())
+        if world > 1:
+            min_error, best_idx = sharding.exchange_best(min_error, best_idx, device=dm.torch_device)
         mp_constraints.min_error = min_error
         mp_constraints.evaluations += n
-        best = dm.sample(1, seed=seed, index_base=best_idx, counts=res["counts"], n_total=n)
+        best = dm.sample(1, seed=seed, index_base=best_idx, counts=counts, n_total=n)
         return best[0].cpu().numpy().astype(np.float64)
 
     # ------------------------------------------------------------------ :220-228

@@ -1,0 +1,87 @@
+"""Host-side logic of the multi-GPU path on CPU: world_size-2 gloo processes exchange their
+per-rank best (cost, global index) and apply the reference's first-minimum rule
+(reference motion_primitive_generator.py:251-257); shard ranges tile the job."""
+import os
+import socket
+
+import numpy as np
+import pytest
+
+from morphablegraphs_b200 import sharding
+
+torch = pytest.importorskip("torch")
+
+
+def test_shard_ranges_tile_the_job():
+    for n in (0, 1, 7, 1000, 1_000_003):
+        for world in (1, 2, 3, 8):
+            nxt = 0
+            for r in range(world):
+                base, cnt = sharding.shard_range(n, r, world)
+                assert base == nxt and cnt >= 0
+                nxt = base + cnt
+            assert nxt == n
+            sizes = [sharding.shard_range(n, r, world)[1] for r in range(world)]
+            assert max(sizes) - min(sizes) <= 1
+
+
+def test_select_best_is_the_reference_rule():
+    # serial loop of the reference: strict '<' in index order
+    rng = np.random.RandomState(0)
+    for _ in range(200):
+        n = rng.randint(1, 12)
+        costs = rng.randint(0, 4, size=n).astype(float)
+        costs[rng.rand(n) < 0.2] = np.nan
+        idx = rng.permutation(100)[:n]
+        order = np.argsort(idx)
+        best_c, best_i = np.inf, None
+        for j in order:
+            if best_c > costs[j]:
+                best_c, best_i = costs[j], idx[j]
+        c, i = sharding.select_best(costs, idx)
+        if best_i is None:
+            assert (c, i) == (np.inf, 0)
+        else:
+            assert c == best_c and i == best_i
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    return port
+
+
+def _worker(rank, world, port, cases, out):
+    import torch.distributed as dist
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        assert sharding.is_distributed()
+        res = []
+        for case in cases:
+            cost, idx = case[rank]
+            res.append(sharding.exchange_best(cost, idx))
+        out[rank] = res
+    finally:
+        dist.destroy_process_group()
+
+
+def test_exchange_best_world2_gloo():
+    import torch.multiprocessing as mp
+    cases = [
+        [(3.0, 10), (2.0, 500_010)],                 # plain minimum on rank 1
+        [(1.5, 499_999), (1.5, 500_000)],            # tie -> lowest global index
+        [(float("nan"), 3), (7.0, 900_000)],         # NaN never wins
+        [(float("inf"), 0), (float("inf"), 500_000)],
+        [(0.25, 2 ** 40 + 1), (0.5, 5)],             # indices beyond 2**32 survive the float64 carrier
+    ]
+    expect = [(2.0, 500_010), (1.5, 499_999), (7.0, 900_000), (float("inf"), 0), (0.25, 2 ** 40 + 1)]
+    mgr = mp.Manager()
+    out = mgr.dict()
+    port = _free_port()
+    mp.spawn(_worker, args=(2, port, cases, out), nprocs=2, join=True)
+    for r in range(2):
+        assert [tuple(x) for x in out[r]] == expect
