@@ -79,7 +79,8 @@ def test_exchange_best_world2_gloo():
         [(0.25, 2 ** 40 + 1), (0.5, 5)],             # indices beyond 2**32 survive the float64 carrier
     ]
     expect = [(2.0, 500_010), (1.5, 499_999), (7.0, 900_000), (float("inf"), 0), (0.25, 2 ** 40 + 1)]
-    mgr = mp.Manager()
+    # spawn-context manager: a fork()ed manager process leaves the parent's BLAS thread pool wedged
+    mgr = mp.get_context("spawn").Manager()
     out = mgr.dict()
     port = _free_port()
     mp.spawn(_worker, args=(2, port, cases, out), nprocs=2, join=True)
