@@ -140,15 +140,20 @@ class ClockSampler(object):
 def cpu_pool(workload):
     from oracle import cpu_baseline as cb
     w = WORKLOADS[workload]
-    return cb.Pool(w["golden"], w["shape"], w["quality_scale"])
+    return cb.Pool(w["golden"], w["shape"], w["quality_scale"], chunk=16384 if w["shape"] == "S" else 512)
 
 
 def calibrate_cpu(pool, seconds):
-    """Candidates per sample so that one sample takes about `seconds` on this host."""
-    n0 = 20000 * pool.workers // 8 + 8000
-    dt = pool.run(n0, seed=11)
+    """Candidates per sample so that one sample takes about `seconds` on this host: grow a probe
+    batch until it takes >= 0.5 s (the L model is ~400x the S model per candidate), then scale."""
+    n0 = 64 * pool.workers
+    while True:
+        dt = pool.run(n0, seed=11)
+        if dt >= 0.5 or n0 >= 4_000_000:
+            break
+        n0 *= 4
     rate = n0 / dt
-    return max(n0, int(rate * seconds)), rate
+    return max(pool.workers * 16, int(rate * seconds)), rate
 
 
 def run_reference(args):

@@ -256,16 +256,43 @@ int mgb_logpdf(const mgb_model* m, const float* d_s, int64_t n, float* d_logpdf,
 int mgb_topk(const float* d_cost, int64_t n, int64_t index_base, int32_t k, float* d_best_cost,
              int64_t* d_best_idx, void* d_workspace, size_t workspace_bytes, void* stream);
 
-/* K7: one Lloyd iteration for every node of a cluster-tree level at once.
- * x[n, dim] (row stride ld), node[n] = tree node of each sample in this level,
- * centroids[n_nodes, 4, dim].  Assign writes label[n]; update accumulates
- * sums[n_nodes,4,dim] / counts[n_nodes,4] (zeroed by the caller).
- * Replaces sklearn KMeans(n_clusters=4).fit_predict per node
- * (space_partitioning/cluster_tree_node_builder.py:83-103). */
+/* K7: one Lloyd iteration (E-step + M-step sums) for every node of a cluster-tree level at once.
+ * x[n, dim] (row stride ld) with the samples of one node stored contiguously (any order is
+ * accepted; runs of equal node ids are what makes the accumulation cheap), node[n] = tree node of
+ * each sample in this level (NULL = one node), centroids[n_nodes, n_sub, dim].  Writes label[n];
+ * accumulates sums[n_nodes, n_sub, dim] / counts[n_nodes, n_sub] / inertia[1] (zeroed by the
+ * caller).  n_sub <= 8, dim <= 126.
+ * Replaces the E/M step inside sklearn KMeans(n_clusters=4).fit_predict per node
+ * (space_partitioning/cluster_tree_node_builder.py:83-103, clustering.py:74-80). */
 int mgb_kmeans_assign_update(const float* d_x, int64_t n, int32_t dim, int32_t ld,
                              const int32_t* d_node, const float* d_centroids, int32_t n_sub,
                              int32_t* d_label, float* d_sums, int32_t* d_counts,
                              float* d_inertia /* [1], accumulated */, void* stream);
+
+/* K7 driver: Lloyd iterations for a whole tree level until every node has converged
+ * (squared centre shift <= d_tol[node], sklearn's rule with d_tol = 1e-4 * mean variance of the
+ * node's samples) or max_iter is reached; the convergence count is read back every check_every
+ * iterations.  d_centroids[n_nodes, n_sub, dim]: seeds in, final centroids out (empty clusters
+ * keep their seed).  Distances use the first `dim` columns of a row; the sums cover the first
+ * dim_acc >= dim columns, so the caller gets the children's means over the full latent vector
+ * (cluster_tree_node_builder.py:62-69 takes np.mean over all columns) from the same pass:
+ * on return label / sums[n_nodes, n_sub, dim_acc] / counts[n_nodes, n_sub] /
+ * node_inertia[n_nodes] (may be NULL) belong to the FINAL centroids.  d_converged[n_nodes]: in =
+ * nodes to leave untouched (1), out = converged flags.  max_iter = 0 runs the E-step only (used
+ * with n_sub = 1 for the per-node mean and variance).  iters_done: host int, may be NULL. */
+int mgb_kmeans_level(const float* d_x, int64_t n, int32_t dim, int32_t dim_acc, int32_t ld,
+                     const int32_t* d_node, int32_t n_nodes, int32_t n_sub, float* d_centroids,
+                     const float* d_tol, int32_t max_iter, int32_t check_every, int32_t* d_label,
+                     float* d_sums, int32_t* d_counts, float* d_node_inertia,
+                     int32_t* d_converged, int32_t* iters_done, void* stream);
+
+/* K8: cost of every point of a cluster tree (node means and kd-tree points, one [n, D] table) under
+ * the step's constraints in one launch; the host walk of the tree then only looks costs up.
+ * Same arithmetic as mgb_score with d_cost set and no arg-min.  Replaces the obj(child.mean, data)
+ * / obj(node.point, data) calls of cluster_tree_node.py:113-138 and kdtree.py:138-161,233-250. */
+int mgb_node_costs(const mgb_model* m, const mgb_constraints* c, const void* d_points, int32_t is_f64,
+                   int64_t n, float error_scale, float quality_scale, float magnitude_scale,
+                   float* d_cost, void* stream);
 
 /* Diagnostic: measured fp32 FMA throughput (TFLOP/s) of `device`; the denominator of the
  * compute-bound fused score kernel's roofline in bench.py (no reference counterpart). */

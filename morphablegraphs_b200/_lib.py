@@ -113,6 +113,9 @@ SYMBOLS = {
     "mgb_logpdf": (C.c_int, [_vp, _vp, _i64, _vp, _vp]),
     "mgb_topk": (C.c_int, [_vp, _i64, _i64, _i32, _vp, _vp, _vp, _sz, _vp]),
     "mgb_kmeans_assign_update": (C.c_int, [_vp, _i64, _i32, _i32, _vp, _vp, _i32, _vp, _vp, _vp, _vp, _vp]),
+    "mgb_kmeans_level": (C.c_int, [_vp, _i64, _i32, _i32, _i32, _vp, _i32, _i32, _vp, _vp, _i32, _i32, _vp, _vp, _vp, _vp, _vp,
+                                   C.POINTER(C.c_int32), _vp]),
+    "mgb_node_costs": (C.c_int, [_vp, _vp, _vp, _i32, _i64, _f, _f, _f, _vp, _vp]),
     "mgb_fp32_fma_peak": (C.c_int, [_i32, _pd]),
     "mgb_launch_count": (C.c_int64, []),
     "mgb_last_error": (C.c_char_p, []),

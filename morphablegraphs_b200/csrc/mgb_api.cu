@@ -655,6 +655,15 @@ extern "C" int mgb_sample_score(const mgb_model* m, const mgb_constraints* c, in
                             nullptr, k, d_best_cost, d_best_idx, d_workspace, workspace_bytes, (cudaStream_t)stream);
 }
 
+extern "C" int mgb_node_costs(const mgb_model* m, const mgb_constraints* c, const void* d_points, int32_t is_f64, int64_t n,
+                              float err_scale, float quality_scale, float magnitude_scale, float* d_cost, void* stream) {
+    MGB_REQUIRE(c, "null constraints handle");
+    MGB_REQUIRE(n == 0 || (d_points && d_cost), "null argument");
+    // the tree's point table scored like any candidate batch, no selection: the walk needs every cost
+    return mgb_launch_score(m, c, 0, d_points, is_f64, nullptr, nullptr, 0, n, 0, err_scale, quality_scale, magnitude_scale, d_cost, nullptr,
+                            0, nullptr, nullptr, nullptr, 0, (cudaStream_t)stream);
+}
+
 extern "C" int mgb_logpdf(const mgb_model* m, const float* d_s, int64_t n, float* d_logpdf, void* stream) {
     MGB_REQUIRE(m && (n == 0 || (d_s && d_logpdf)), "null argument");
     // the score kernel with an empty program: cost = quality_scale * (-log p(s)) with quality_scale = -1

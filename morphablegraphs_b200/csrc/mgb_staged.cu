@@ -327,41 +327,6 @@ __global__ void __launch_bounds__(FK_BLOCK) mgb_fk_kernel(const float* __restric
     }
 }
 
-// ---------------------------------------------------------------------------
-// K7: one Lloyd step for a whole tree level.  Thread per sample: nearest of its
-// node's n_sub centroids, label out, then sums/counts accumulated with
-// warp-aggregated atomics when the whole warp hits the same (node, label).
-// ---------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) mgb_kmeans_kernel(const float* __restrict__ x, long long n, int dim, int ld, const int* __restrict__ node,
-                                                        const float* __restrict__ cent, int n_sub, int* __restrict__ label,
-                                                        float* __restrict__ sums, int* __restrict__ counts, float* __restrict__ inertia) {
-    float local_inertia = 0.f;
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
-        const int nd = node ? node[i] : 0;
-        const float* xi = x + (size_t)i * ld;
-        const float* cb = cent + (size_t)nd * n_sub * dim;
-        float best = INFINITY;
-        int bl = 0;
-        for (int k = 0; k < n_sub; ++k) {
-            float d = 0.f;
-            const float* ck = cb + (size_t)k * dim;
-            for (int j = 0; j < dim; ++j) {
-                float e = __ldg(xi + j) - __ldg(ck + j);
-                d = fmaf(e, e, d);
-            }
-            if (d < best) { best = d; bl = k; }
-        }
-        label[i] = bl;
-        local_inertia += best;
-        float* sb = sums + ((size_t)nd * n_sub + bl) * dim;
-        for (int j = 0; j < dim; ++j) atomicAdd(sb + j, __ldg(xi + j));
-        atomicAdd(counts + (size_t)nd * n_sub + bl, 1);
-    }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) local_inertia += __shfl_xor_sync(0xffffffffu, local_inertia, o);
-    if (inertia && (threadIdx.x & 31) == 0) atomicAdd(inertia, local_inertia);
-}
-
 }  // namespace
 
 // ===========================================================================
@@ -554,22 +519,6 @@ extern "C" int mgb_fk(const mgb_model* m, const float* d_frames, int64_t n_frame
     mgb_count_launch();
     MGB_CUDA(cudaGetLastError());
     MGB_CUDA(cudaFreeAsync(d_plan, stream));
-    return MGB_OK;
-}
-
-extern "C" int mgb_kmeans_assign_update(const float* d_x, int64_t n, int32_t dim, int32_t ld, const int32_t* d_node,
-                                        const float* d_centroids, int32_t n_sub, int32_t* d_label, float* d_sums,
-                                        int32_t* d_counts, float* d_inertia, void* stream_) {
-    cudaStream_t stream = (cudaStream_t)stream_;
-    MGB_REQUIRE(n == 0 || (d_x && d_centroids && d_label && d_sums && d_counts), "null argument");
-    MGB_REQUIRE(dim > 0 && ld >= dim && n_sub > 0, "bad shape");
-    if (n == 0) return MGB_OK;
-    long long blocks = (n + 255) / 256;
-    long long grid = (long long)sm_count() * 8;
-    if (grid > blocks) grid = blocks;
-    mgb_kmeans_kernel<<<(unsigned)grid, 256, 0, stream>>>(d_x, n, dim, ld, d_node, d_centroids, n_sub, d_label, d_sums, d_counts, d_inertia);
-    mgb_count_launch();
-    MGB_CUDA(cudaGetLastError());
     return MGB_OK;
 }
 

@@ -1,0 +1,282 @@
+// K7: level-synchronous k-means of the cluster-tree build.
+//
+// The reference subdivides one node at a time: sklearn KMeans(n_clusters=4).fit_predict on
+// data[indices, :dim] (space_partitioning/cluster_tree_node_builder.py:83-103,
+// space_partitioning/clustering.py:74-80), recursively.  Here every node of one tree level is
+// subdivided by the same launches: the samples are kept sorted by node (the host re-sorts them
+// after every level), one kernel does the E-step for every sample and accumulates the M-step
+// sums of every (node, cluster), a second small kernel turns the sums into centroids and tests
+// every node's convergence (sklearn's rule: squared centre shift <= tol * mean variance).
+//
+// HBM-bound: per sample and Lloyd iteration 4*ld + 4 bytes read (row + node id), 4 bytes written
+// (label).  The accumulation never goes through per-sample atomics: a warp walks a contiguous run
+// of samples 32 at a time, lane = sample for the distance part, then lane = column for the
+// accumulation part (the tile lives in shared memory), keeping the running sums of its current
+// node in registers and flushing them with one vector RED per (node, cluster) when the node
+// changes.
+#include <math.h>
+
+#include "mgb_internal.cuh"
+
+namespace {
+
+int sm_count_tree() {
+    static int n = 0;
+    if (n == 0) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+        if (n <= 0) n = 148;
+    }
+    return n;
+}
+
+constexpr int KM_WARPS = 4;
+
+// CH = ceil((dim_acc + 1) / 32): columns handled per lane; the extra "column" dim_acc carries
+// the member count and the inertia of the node.
+template <int NS, int CH>
+__global__ void __launch_bounds__(KM_WARPS * 32) mgb_kmeans_level_kernel(
+    const float* __restrict__ x, long long n, int dim, int dim_acc, int ld, const int* __restrict__ node,
+    const float* __restrict__ cent, int n_sub, int* __restrict__ label, float* __restrict__ sums,
+    int* __restrict__ counts, float* __restrict__ node_inertia, float* __restrict__ inertia, long long tiles_per_warp) {
+    extern __shared__ float sm_tiles[];
+    const int lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5;
+    float* tile = sm_tiles + (size_t)warp * 32 * ld;
+    const long long gwarp = (long long)blockIdx.x * KM_WARPS + warp;
+    const long long first = gwarp * tiles_per_warp * 32;
+    long long last = first + tiles_per_warp * 32;
+    if (last > n) last = n;
+
+    float acc[NS][CH];
+#pragma unroll
+    for (int k = 0; k < NS; ++k)
+#pragma unroll
+        for (int c = 0; c < CH; ++c) acc[k][c] = 0.f;
+    float acc_inertia = 0.f;   // only meaningful on the lane that owns column dim_acc
+    int cur = -1;
+    float total_inertia = 0.f;
+
+    auto flush = [&]() {
+        if (cur < 0) return;
+#pragma unroll
+        for (int c = 0; c < CH; ++c) {
+            const int col = lane + 32 * c;
+            if (col < dim_acc) {
+#pragma unroll
+                for (int k = 0; k < NS; ++k)
+                    if (k < n_sub && acc[k][c] != 0.f) atomicAdd(sums + ((size_t)cur * n_sub + k) * dim_acc + col, acc[k][c]);
+            } else if (col == dim_acc) {
+#pragma unroll
+                for (int k = 0; k < NS; ++k)
+                    if (k < n_sub && acc[k][c] != 0.f) atomicAdd(counts + (size_t)cur * n_sub + k, (int)acc[k][c]);
+                if (node_inertia) atomicAdd(node_inertia + cur, acc_inertia);
+            }
+#pragma unroll
+            for (int k = 0; k < NS; ++k) acc[k][c] = 0.f;
+        }
+        acc_inertia = 0.f;
+    };
+
+    for (long long t0 = first; t0 < last; t0 += 32) {
+        const int rows = (int)((last - t0 < 32) ? (last - t0) : 32);
+        // coalesced copy of rows x ld floats into the warp's tile
+        const float* src = x + (size_t)t0 * ld;
+        const int total = rows * ld;
+        for (int e = lane; e < total; e += 32) tile[e] = __ldcs(src + e);
+        __syncwarp();
+        // E-step: lane = sample
+        int nd = -1, lb = 0;
+        float best = 0.f;
+        if (lane < rows) {
+            nd = node ? __ldg(node + t0 + lane) : 0;
+            const float* xi = tile + lane * ld;
+            const float* cb = cent + (size_t)nd * n_sub * dim;
+            best = INFINITY;
+            for (int k = 0; k < n_sub; ++k) {
+                const float* ck = cb + (size_t)k * dim;
+                float d = 0.f;
+                for (int j = 0; j < dim; ++j) {
+                    const float e = xi[j] - __ldg(ck + j);
+                    d = fmaf(e, e, d);
+                }
+                if (d < best) { best = d; lb = k; }
+            }
+            label[t0 + lane] = lb;
+            total_inertia += best;
+        }
+        // M-step sums: lane = column, the 32 samples in order (node ids come in runs)
+        for (int s = 0; s < rows; ++s) {
+            const int snd = __shfl_sync(0xffffffffu, nd, s);
+            const int slb = __shfl_sync(0xffffffffu, lb, s);
+            const float sbest = __shfl_sync(0xffffffffu, best, s);
+            if (snd != cur) {
+                flush();
+                cur = snd;
+            }
+#pragma unroll
+            for (int c = 0; c < CH; ++c) {
+                const int col = lane + 32 * c;
+                float v = 0.f;
+                if (col < dim_acc) v = tile[s * ld + col];
+                else if (col == dim_acc) { v = 1.f; acc_inertia += sbest; }
+#pragma unroll
+                for (int k = 0; k < NS; ++k) acc[k][c] += (k == slb) ? v : 0.f;
+            }
+        }
+        __syncwarp();
+    }
+    flush();
+    if (inertia) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) total_inertia += __shfl_xor_sync(0xffffffffu, total_inertia, o);
+        if (lane == 0 && total_inertia != 0.f) atomicAdd(inertia, total_inertia);
+    }
+}
+
+// M-step finish + convergence test, one thread per node.  Empty clusters keep their centroid.
+__global__ void __launch_bounds__(128) mgb_kmeans_centroid_kernel(int n_nodes, int n_sub, int dim, int dim_acc,
+                                                                 const float* __restrict__ sums, const int* __restrict__ counts,
+                                                                 const float* __restrict__ tol, float* __restrict__ cent,
+                                                                 int* __restrict__ converged, int* __restrict__ n_active) {
+    const int nd = blockIdx.x * blockDim.x + threadIdx.x;
+    if (nd >= n_nodes) return;
+    if (converged[nd]) return;
+    float shift = 0.f;
+    for (int k = 0; k < n_sub; ++k) {
+        const int cnt = counts[(size_t)nd * n_sub + k];
+        if (cnt <= 0) continue;
+        const float inv = 1.f / (float)cnt;
+        float* c = cent + ((size_t)nd * n_sub + k) * dim;
+        const float* s = sums + ((size_t)nd * n_sub + k) * dim_acc;
+        for (int j = 0; j < dim; ++j) {
+            const float v = s[j] * inv;
+            const float e = v - c[j];
+            shift = fmaf(e, e, shift);
+            c[j] = v;
+        }
+    }
+    if (shift <= (tol ? tol[nd] : 0.f)) converged[nd] = 1;
+    else atomicAdd(n_active, 1);
+}
+
+template <int NS, int CH>
+int launch_level(const float* d_x, int64_t n, int dim, int dim_acc, int ld, const int* d_node, const float* d_cent, int n_sub,
+                 int* d_label, float* d_sums, int* d_counts, float* d_node_inertia, float* d_inertia, cudaStream_t stream) {
+    auto kern = mgb_kmeans_level_kernel<NS, CH>;
+    const size_t smem = (size_t)KM_WARPS * 32 * ld * sizeof(float);
+    MGB_REQUIRE(smem <= 200 * 1024, "row stride too large for the k-means kernel (ld <= 400)");
+    if (smem > 48 * 1024) MGB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const long long tiles = (n + 31) / 32;
+    int occ = 1;
+    MGB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, KM_WARPS * 32, smem));
+    if (occ < 1) occ = 1;
+    long long warps = (long long)sm_count_tree() * occ * KM_WARPS;
+    if (warps > tiles) warps = tiles;
+    const long long tpw = (tiles + warps - 1) / warps;
+    const long long used_warps = (tiles + tpw - 1) / tpw;
+    const long long grid = (used_warps + KM_WARPS - 1) / KM_WARPS;
+    kern<<<(unsigned)grid, KM_WARPS * 32, smem, stream>>>(d_x, n, dim, dim_acc, ld, d_node, d_cent, n_sub, d_label, d_sums, d_counts,
+                                                           d_node_inertia, d_inertia, tpw);
+    mgb_count_launch();
+    MGB_CUDA(cudaGetLastError());
+    return MGB_OK;
+}
+
+int dispatch_level(const float* d_x, int64_t n, int dim, int dim_acc, int ld, const int* d_node, const float* d_cent, int n_sub,
+                   int* d_label, float* d_sums, int* d_counts, float* d_node_inertia, float* d_inertia, cudaStream_t stream) {
+    const int ch = (dim_acc + 1 + 31) / 32;
+    MGB_REQUIRE(n_sub >= 1 && n_sub <= 8, "n_sub must be in 1..8");
+    MGB_REQUIRE(ch <= 4, "at most 127 accumulated columns");
+#define MGB_KM_CASE(NS, CH)                                                                                              \
+    return launch_level<NS, CH>(d_x, n, dim, dim_acc, ld, d_node, d_cent, n_sub, d_label, d_sums, d_counts, d_node_inertia, \
+                                d_inertia, stream)
+    if (n_sub <= 4) {
+        switch (ch) {
+            case 1: MGB_KM_CASE(4, 1);
+            case 2: MGB_KM_CASE(4, 2);
+            case 3: MGB_KM_CASE(4, 3);
+            default: MGB_KM_CASE(4, 4);
+        }
+    }
+    switch (ch) {
+        case 1: MGB_KM_CASE(8, 1);
+        case 2: MGB_KM_CASE(8, 2);
+        case 3: MGB_KM_CASE(8, 3);
+        default: MGB_KM_CASE(8, 4);
+    }
+#undef MGB_KM_CASE
+}
+
+}  // namespace
+
+extern "C" int mgb_kmeans_assign_update(const float* d_x, int64_t n, int32_t dim, int32_t ld, const int32_t* d_node,
+                                        const float* d_centroids, int32_t n_sub, int32_t* d_label, float* d_sums,
+                                        int32_t* d_counts, float* d_inertia, void* stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    MGB_REQUIRE(n == 0 || (d_x && d_centroids && d_label && d_sums && d_counts), "null argument");
+    MGB_REQUIRE(dim > 0 && ld >= dim && n_sub > 0, "bad shape");
+    if (n == 0) return MGB_OK;
+    return dispatch_level(d_x, n, dim, dim, ld, d_node, d_centroids, n_sub, d_label, d_sums, d_counts, nullptr, d_inertia, stream);
+}
+
+extern "C" int mgb_kmeans_level(const float* d_x, int64_t n, int32_t dim, int32_t dim_acc, int32_t ld, const int32_t* d_node,
+                                int32_t n_nodes, int32_t n_sub, float* d_centroids, const float* d_tol, int32_t max_iter,
+                                int32_t check_every, int32_t* d_label, float* d_sums, int32_t* d_counts, float* d_node_inertia,
+                                int32_t* d_converged, int32_t* iters_done, void* stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    MGB_REQUIRE(n >= 0 && n_nodes >= 0, "negative size");
+    if (iters_done) *iters_done = 0;
+    if (n == 0 || n_nodes == 0) return MGB_OK;
+    MGB_REQUIRE(d_x && d_centroids && d_label && d_sums && d_counts && d_converged, "null argument");
+    MGB_REQUIRE(dim > 0 && dim_acc >= dim && ld >= dim_acc && n_sub > 0, "bad shape");
+    MGB_REQUIRE(max_iter >= 0, "max_iter < 0");
+    if (check_every < 1) check_every = 4;
+    static thread_local int* h_active = nullptr;
+    static thread_local int* d_active = nullptr;
+    if (!h_active) {
+        MGB_CUDA(cudaHostAlloc((void**)&h_active, sizeof(int), cudaHostAllocDefault));
+    }
+    // the counter lives with the call's device (one handle per GPU, one device per process in practice)
+    static thread_local int d_active_dev = -1;
+    int dev = 0;
+    MGB_CUDA(cudaGetDevice(&dev));
+    if (!d_active || d_active_dev != dev) {
+        MGB_CUDA(cudaMalloc((void**)&d_active, sizeof(int)));
+        d_active_dev = dev;
+    }
+    const size_t sums_bytes = (size_t)n_nodes * n_sub * dim_acc * sizeof(float);
+    const size_t counts_bytes = (size_t)n_nodes * n_sub * sizeof(int);
+    auto e_step = [&]() -> int {
+        MGB_CUDA(cudaMemsetAsync(d_sums, 0, sums_bytes, stream));
+        MGB_CUDA(cudaMemsetAsync(d_counts, 0, counts_bytes, stream));
+        if (d_node_inertia) MGB_CUDA(cudaMemsetAsync(d_node_inertia, 0, (size_t)n_nodes * sizeof(float), stream));
+        return dispatch_level(d_x, n, dim, dim_acc, ld, d_node, d_centroids, n_sub, d_label, d_sums, d_counts, d_node_inertia,
+                              nullptr, stream);
+    };
+    int it = 0;
+    bool done = (max_iter == 0);
+    while (!done) {
+        int rc = e_step();
+        if (rc != MGB_OK) return rc;
+        MGB_CUDA(cudaMemsetAsync(d_active, 0, sizeof(int), stream));
+        mgb_kmeans_centroid_kernel<<<(n_nodes + 127) / 128, 128, 0, stream>>>(n_nodes, n_sub, dim, dim_acc, d_sums, d_counts, d_tol,
+                                                                              d_centroids, d_converged, d_active);
+        mgb_count_launch();
+        MGB_CUDA(cudaGetLastError());
+        ++it;
+        if (it >= max_iter) break;
+        if (it % check_every == 0) {
+            MGB_CUDA(cudaMemcpyAsync(h_active, d_active, sizeof(int), cudaMemcpyDeviceToHost, stream));
+            MGB_CUDA(cudaStreamSynchronize(stream));
+            if (*h_active == 0) done = true;
+        }
+    }
+    // labels, sums, counts and inertia that belong to the final centroids (sklearn re-runs the
+    // E-step after a tolerance stop; _kmeans_single_lloyd)
+    int rc = e_step();
+    if (rc != MGB_OK) return rc;
+    if (iters_done) *iters_done = it;
+    return MGB_OK;
+}

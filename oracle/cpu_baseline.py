@@ -74,15 +74,32 @@ def _work(args):
 class Pool(object):
     """Persistent worker pool so that process start-up is outside the timed region."""
 
-    def __init__(self, golden="s_config1", shape="S", quality_scale=0.0, workers=None):
+    def __init__(self, golden="s_config1", shape="S", quality_scale=0.0, workers=None, chunk=16384):
         self.workers = workers or os.cpu_count() or 1
+        self.chunk = chunk
         ctx = mp.get_context("spawn")
+        # one BLAS thread per worker: the variables must be in the environment BEFORE the child imports
+        # numpy (the initializer runs too late), otherwise workers x cores BLAS threads spin on each other
+        saved = {k: os.environ.get(k) for k in ("OMP_NUM_THREADS", "OPENBLAS_NUM_THREADS", "MKL_NUM_THREADS")}
+        for k in saved:
+            os.environ[k] = "1"
+        try:
+            self._start(ctx, golden, shape, quality_scale)
+        finally:
+            for k, v in saved.items():
+                if v is None:
+                    os.environ.pop(k, None)
+                else:
+                    os.environ[k] = v
+
+    def _start(self, ctx, golden, shape, quality_scale):
         self.pool = ctx.Pool(self.workers, initializer=_init, initargs=(golden, shape, quality_scale))
         # make sure every worker has finished its initialiser
         self.pool.map(_work, [(i, 64, 64) for i in range(self.workers * 2)])
 
-    def run(self, n_total, seed=0, chunk=16384):
+    def run(self, n_total, seed=0, chunk=None):
         """Sample and score n_total candidates across the workers; returns seconds."""
+        chunk = chunk or self.chunk
         per = int(np.ceil(n_total / float(self.workers * 4)))
         jobs = []
         left = n_total
