@@ -487,6 +487,22 @@ class DeviceConstraints(object):
             out["terms"] = terms
         return out
 
+    def node_costs(self, points, error_scale=1.0, quality_scale=0.0, magnitude_scale=0.0, out=None):
+        """K8 (mgb_node_costs): cost of every row of a cluster tree's point table [M, D]
+        (device tensor, float32 or float64) -> float32 device tensor [M]; no selection."""
+        torch = _torch()
+        dm = self.dmodel
+        assert isinstance(points, torch.Tensor) and points.device == dm.torch_device and points.is_contiguous()
+        assert points.dtype in (torch.float32, torch.float64) and points.dim() == 2 and points.shape[1] == dm.D
+        n = int(points.shape[0])
+        if out is None:
+            out = torch.empty((n,), dtype=torch.float32, device=dm.torch_device)
+        with torch.cuda.device(dm.device):
+            _lib.check(self.lib.mgb_node_costs(dm.handle, self.handle, C.c_void_p(points.data_ptr()),
+                                               1 if points.dtype == torch.float64 else 0, n, float(error_scale),
+                                               float(quality_scale), float(magnitude_scale), C.c_void_p(out.data_ptr()), dm._stream()))
+        return out
+
     def sample_score(self, n, seed=0, counts=None, n_total=None, index_base=0, k=1, error_scale=1.0, quality_scale=0.0,
                      magnitude_scale=0.0, return_cost=False):
         """Fused K1 + K6 (mgb_sample_score): draw candidates [index_base, index_base + n) of a job of
@@ -544,6 +560,41 @@ class DeviceConstraints(object):
         if return_cost:
             out["cost"] = cost
         return out
+
+
+def kmeans_level(x, dim, node, n_nodes, n_sub, centroids, tol=None, max_iter=300, check_every=4, dim_acc=None,
+                 frozen=None):
+    """K7 driver (mgb_kmeans_level) on torch CUDA tensors.  x [n, ld] float32 with the samples of a
+    node stored contiguously, node [n] int32 (or None = one node), centroids [n_nodes, n_sub, dim]
+    float32 (seeds in, final centroids out, in place).  Returns dict(label [n] int32,
+    sums [n_nodes, n_sub, dim_acc], counts [n_nodes, n_sub], inertia [n_nodes], converged [n_nodes],
+    iters) for the final centroids."""
+    torch = _torch()
+    lib = _lib.load()
+    if not x.is_cuda:
+        raise MgbError("kmeans_level needs CUDA tensors: morphablegraphs_b200 has no CPU fallback")
+    dev = x.device
+    assert x.dtype == torch.float32 and x.is_contiguous() and x.dim() == 2
+    n, ld = int(x.shape[0]), int(x.shape[1])
+    dim_acc = int(dim if dim_acc is None else dim_acc)
+    assert centroids.dtype == torch.float32 and centroids.is_contiguous() and tuple(centroids.shape) == (n_nodes, n_sub, dim)
+    if node is not None:
+        assert node.dtype == torch.int32 and node.is_contiguous() and node.shape[0] == n
+    label = torch.empty((n,), dtype=torch.int32, device=dev)
+    sums = torch.empty((n_nodes, n_sub, dim_acc), dtype=torch.float32, device=dev)
+    counts = torch.empty((n_nodes, n_sub), dtype=torch.int32, device=dev)
+    inertia = torch.empty((n_nodes,), dtype=torch.float32, device=dev)
+    converged = torch.zeros((n_nodes,), dtype=torch.int32, device=dev) if frozen is None else frozen.to(torch.int32).contiguous()
+    if tol is not None:
+        assert tol.dtype == torch.float32 and tol.is_contiguous() and tol.shape[0] == n_nodes
+    iters = C.c_int32(0)
+    ptr = lambda t: C.c_void_p(t.data_ptr()) if t is not None else C.c_void_p(0)
+    with torch.cuda.device(dev):
+        stream = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+        _lib.check(lib.mgb_kmeans_level(ptr(x), n, int(dim), dim_acc, ld, ptr(node), int(n_nodes), int(n_sub), ptr(centroids), ptr(tol),
+                                        int(max_iter), int(check_every), ptr(label), ptr(sums), ptr(counts), ptr(inertia),
+                                        ptr(converged), C.byref(iters), stream))
+    return {"label": label, "sums": sums, "counts": counts, "inertia": inertia, "converged": converged, "iters": int(iters.value)}
 
 
 def launch_count():

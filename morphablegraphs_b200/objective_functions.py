@@ -50,6 +50,15 @@ class _Objective(object):
         mp_constraints.evaluations += len(S)
         return res["cost"].astype(np.float64)
 
+    def batch_device(self, S_dev, data):
+        """Costs of a device-resident table [M, D] (float32/float64 CUDA tensor) -> float32 CUDA
+        tensor [M]: K8, the node-cost table of a cluster-tree search (space_partitioning.py)."""
+        mp_node, mp_constraints, prev_frames = data[:3]
+        dc = _device_constraints(mp_node, mp_constraints, prev_frames)
+        mp_constraints.evaluations += int(S_dev.shape[0])
+        return dc.node_costs(S_dev, error_scale=self.error_scale, quality_scale=self.quality_scale,
+                             magnitude_scale=self.magnitude_scale)
+
     def __call__(self, s, data):
         mp_constraints = data[1]
         v = float(self.batch(np.asarray(s, dtype=np.float64)[None, :], data)[0])

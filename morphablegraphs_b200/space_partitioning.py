@@ -1,0 +1,778 @@
+"""Cluster trees of the reference (space_partitioning/) behind the reference's names:
+`ClusterTree` (k-means hierarchy with kd-tree leaves) and `FeatureClusterTree` (k-means
+hierarchy down to single samples), each with
+`find_best_example_excluding_search_candidates(obj, data, n_candidates)` as called by
+`MotionStateGraphNode.search_best_sample` (reference motion_state_graph_node.py:119-142).
+
+Two things run on the GPU:
+
+* search (a20): the reference calls `obj(child.mean, data)` / `obj(kd_node.point, data)` one
+  point at a time while it walks the tree (cluster_tree.py:117-149, cluster_tree_node.py:113-138,
+  kdtree.py:138-161,233-250, feature_cluster_tree.py:129-187).  Here every point of the tree
+  (node means, kd-tree points) is one row of a device-resident table that is scored in ONE launch
+  per search (K8, `mgb_node_costs`); the walk itself then only looks costs up and restates the
+  reference's bookkeeping exactly, including its heap-array-prefix candidate selection (quirk Q4).
+  Objectives without a `.batch_device` / `.batch` method are called per point, lazily, like the
+  reference does.
+* build (a18): the reference recurses node by node with sklearn KMeans (cluster_tree_node_builder.py:
+  83-137, feature_cluster_tree.py:61-98).  Here a whole tree level is subdivided at once by the K7
+  kernels (`mgb_kmeans_level`), samples kept sorted by node between levels; the kd-trees of all
+  leaves are built together, one kd level per pass (kdtree.py:44-73: sort by axis `depth % dim`,
+  median `len // 2`).
+
+The flat layout: cluster nodes and kd nodes are rows of integer arrays; `points[M, D]` holds every
+evaluable point, `node_row` / `kd_row` index into it.
+"""
+import heapq
+
+import numpy as np
+
+from . import engine
+
+KDTREE_INNER = 1
+KDTREE_LEAF = 0
+
+
+class FlatClusterTree(object):
+    """Arrays of a ClusterTree.  Children of node i: child_idx[child_ptr[i]:child_ptr[i+1]],
+    child_is_kd tells whether an entry is a kd-tree root (index into the kd arrays) or a node."""
+
+    def __init__(self):
+        self.points = None          # [M, D] float64 (host)
+        self.node_row = None        # [n_nodes] row of the node mean
+        self.node_leaf = None       # [n_nodes] bool
+        self.child_ptr = None       # [n_nodes + 1]
+        self.child_idx = None
+        self.child_is_kd = None
+        self.kd_row = None          # [n_kd]
+        self.kd_left = None         # [n_kd] kd index or -1
+        self.kd_right = None
+        self.kd_inner = None        # [n_kd] bool
+        self.root = 0
+
+    @property
+    def n_nodes(self):
+        return len(self.node_row)
+
+    def children(self, i):
+        a, b = self.child_ptr[i], self.child_ptr[i + 1]
+        return self.child_idx[a:b], self.child_is_kd[a:b]
+
+
+def _tree_dict_from_reference(node):
+    """Reference ClusterTreeNode / KDTreeWrapper objects -> nested dicts (duck-typed:
+    `.clusters`, `.mean`, `.leaf`, `.type == "kdtree"`, `.kdtree.root` with `.point/.left/.right/.type`)."""
+    def kd(n):
+        if n is None:
+            return None
+        return {"point": [float(v) for v in n.point], "type": n.type, "left": kd(n.left), "right": kd(n.right)}
+
+    d = {"mean": np.asarray(node.mean, dtype=np.float64).tolist(), "leaf": bool(node.leaf), "children": []}
+    for c in node.clusters:
+        if getattr(c, "type", None) == "kdtree" or hasattr(c, "kdtree"):
+            d["children"].append({"kdtree": kd(c.kdtree.root)})
+        else:
+            d["children"].append(_tree_dict_from_reference(c))
+    return d
+
+
+def flatten_cluster_tree(root):
+    """Nested dict form ({"mean", "leaf", "children": [node | {"kdtree": kd}]}, kd = {"point", "type",
+    "left", "right"}) -> FlatClusterTree.  Node order: breadth-first, children in list order."""
+    points = []
+    node_row, node_leaf, child_lists = [], [], []
+    kd_row, kd_left, kd_right, kd_inner = [], [], [], []
+
+    def add_kd(k):
+        # iterative pre-order; returns kd index
+        idx0 = len(kd_row)
+        stack = [(k, -1, 0)]
+        while stack:
+            n, parent, side = stack.pop()
+            i = len(kd_row)
+            kd_row.append(len(points))
+            points.append(n["point"])
+            kd_left.append(-1)
+            kd_right.append(-1)
+            kd_inner.append(n["type"] == "inner")
+            if parent >= 0:
+                (kd_left if side == 0 else kd_right)[parent] = i
+            if n.get("right") is not None:
+                stack.append((n["right"], i, 1))
+            if n.get("left") is not None:
+                stack.append((n["left"], i, 0))
+        return idx0
+
+    queue = [root]
+    node_row.append(0)
+    points.append(root["mean"])
+    node_leaf.append(bool(root["leaf"]))
+    child_lists.append([])
+    qi = 0
+    ids = {id(root): 0}
+    while qi < len(queue):
+        n = queue[qi]
+        me = ids[id(n)]
+        qi += 1
+        for c in n["children"]:
+            if "kdtree" in c:
+                child_lists[me].append((add_kd(c["kdtree"]), True))
+            else:
+                i = len(node_row)
+                ids[id(c)] = i
+                node_row.append(len(points))
+                points.append(c["mean"])
+                node_leaf.append(bool(c["leaf"]))
+                child_lists.append([])
+                child_lists[me].append((i, False))
+                queue.append(c)
+    t = FlatClusterTree()
+    t.points = np.asarray(points, dtype=np.float64)
+    t.node_row = np.asarray(node_row, dtype=np.int64)
+    t.node_leaf = np.asarray(node_leaf, dtype=bool)
+    t.child_ptr = np.zeros(len(node_row) + 1, dtype=np.int64)
+    t.child_ptr[1:] = np.cumsum([len(c) for c in child_lists])
+    flat = [e for c in child_lists for e in c]
+    t.child_idx = np.asarray([e[0] for e in flat], dtype=np.int64)
+    t.child_is_kd = np.asarray([e[1] for e in flat], dtype=bool)
+    t.kd_row = np.asarray(kd_row, dtype=np.int64)
+    t.kd_left = np.asarray(kd_left, dtype=np.int64)
+    t.kd_right = np.asarray(kd_right, dtype=np.int64)
+    t.kd_inner = np.asarray(kd_inner, dtype=bool)
+    return t
+
+
+# ---------------------------------------------------------------------------
+# cost table (K8)
+# ---------------------------------------------------------------------------
+class _PointCosts(object):
+    """cost(row) for the rows of a tree's point table.  With a batch objective every row is scored
+    by one launch when the first cost is asked for; otherwise obj is called per row, lazily (the
+    reference's own behaviour)."""
+
+    def __init__(self, tree_owner, obj, data):
+        self.owner = tree_owner
+        self.obj = obj
+        self.data = data
+        self.table = None
+        self.lazy = {}
+        self.n_lookups = 0
+
+    def _fill(self):
+        pts = self.owner.points
+        if hasattr(self.obj, "batch_device"):
+            dev_pts = self.owner.device_points(self.obj, self.data)
+            self.table = self.obj.batch_device(dev_pts, self.data).cpu().numpy().astype(np.float64)
+        else:
+            self.table = np.asarray(self.obj.batch(pts, self.data), dtype=np.float64)
+
+    def __call__(self, row):
+        self.n_lookups += 1
+        if hasattr(self.obj, "batch_device") or hasattr(self.obj, "batch"):
+            if self.table is None:
+                self._fill()
+            return float(self.table[row])
+        if row not in self.lazy:
+            self.lazy[row] = float(self.obj(self.owner.points[row], self.data))
+        return self.lazy[row]
+
+
+def _heap_prefix(items, n):
+    """Quirk Q4: everything is pushed on a heap and a PREFIX OF THE HEAP ARRAY is taken
+    (cluster_tree_node.py:133-138) - not the n smallest."""
+    q = []
+    for it in items:
+        heapq.heappush(q, it)
+    return q[:n]
+
+
+def _kd_find_best_example(t, cost, kd_root):
+    """kdtree.py:233-250 with k = 1 (kdtree_wrapper_node.py:53-54): descend towards the cheaper
+    child, return (value, row) of the cheapest point on the path (ties: the shallower one)."""
+    rows = [t.kd_row[kd_root]]
+    q = []
+    heapq.heappush(q, (cost(rows[0]), 0))
+    node = kd_root
+    depth = 0
+    while node >= 0 and t.kd_inner[node]:
+        depth += 1
+        left, right = t.kd_left[node], t.kd_right[node]
+        # kdtree.py:138-161: both evaluated, right first; strict '<' prefers right on ties
+        if left >= 0 and right >= 0:
+            r_d = cost(t.kd_row[right])
+            l_d = cost(t.kd_row[left])
+            node, least = (left, l_d) if l_d < r_d else (right, r_d)
+        elif right >= 0:
+            node, least = right, cost(t.kd_row[right])
+        elif left >= 0:
+            node, least = left, cost(t.kd_row[left])
+        else:
+            node, least = -1, np.inf
+        if node >= 0:
+            heapq.heappush(q, (least, depth))
+            rows.append(t.kd_row[node])
+    value, d = q[0]
+    return value, rows[d]
+
+
+def _leaf_find_best_example(t, cost, node):
+    """cluster_tree_node.py:63-76 for a leaf: best over its kd-trees; ties on the value fall back to
+    comparing the point lists, like the reference's (value, list) tuples do."""
+    idx, is_kd = t.children(node)
+    q = []
+    if len(idx) > 0:
+        for c, kd in zip(idx, is_kd):
+            if kd:
+                v, row = _kd_find_best_example(t, cost, c)
+            else:                                   # leaf of a tree built without kd-trees: a single-sample node
+                row = t.node_row[c]
+                v = cost(row)
+            heapq.heappush(q, (v, tuple(t.points[row].tolist()), row))
+    else:
+        row = t.node_row[node]
+        heapq.heappush(q, (cost(row), tuple(t.points[row].tolist()), row))
+    v, _, row = heapq.heappop(q)
+    return v, row
+
+
+def cluster_tree_search(t, cost, n_candidates=1):
+    """cluster_tree.py:117-149 on a FlatClusterTree; returns (value, row of the sample in t.points)
+    or (inf, row of the root mean) when nothing was found."""
+    results = []
+    candidates = [(np.inf, 0, t.root)]
+    while len(candidates) > 0:
+        new_candidates = []
+        for c_idx, (value, _tie, node) in enumerate(candidates):
+            idx, is_kd = t.children(node)
+            # a node that kept > n_subdivisions samples at depth == max_level has kd-tree children but
+            # leaf == False (cluster_tree_node_builder.py:139-154); the reference's walk dies there on
+            # KDTreeWrapper.mean - here it is searched like a leaf
+            if not t.node_leaf[node] and not (len(idx) > 0 and is_kd.all()):
+                items = [(cost(t.node_row[c]), ci, int(c)) for ci, c in enumerate(idx)]
+                good = _heap_prefix(items, n_candidates)
+                for i, c in enumerate(good):
+                    heapq.heappush(new_candidates, (c[0], i, c[2]))
+            else:
+                v, row = _leaf_find_best_example(t, cost, node)
+                heapq.heappush(results, (v, c_idx, tuple(t.points[row].tolist()), row))
+        candidates = new_candidates[:n_candidates]
+    if len(results) > 0:
+        r = heapq.heappop(results)
+        return r[0], r[3]
+    return np.inf, t.node_row[t.root]
+
+
+class _DevicePointsMixin(object):
+    """Point table resident on the GPU of the objective's device model (uploaded once per device)."""
+
+    def device_points(self, obj, data):
+        torch = engine._torch()
+        from .objective_functions import _device_constraints
+        dm = _device_constraints(data[0], data[1], data[2]).dmodel
+        cache = self.__dict__.setdefault("_dev_points", {})
+        key = dm.device
+        if key not in cache or cache[key].shape[0] != len(self.points):
+            cache[key] = torch.as_tensor(np.ascontiguousarray(self.points, dtype=np.float64), device=dm.torch_device)
+        return cache[key]
+
+
+class ClusterTree(_DevicePointsMixin):
+    """reference space_partitioning/cluster_tree.py:43-149 (constructor arguments, `construct`,
+    `find_best_example_excluding_search_candidates`)."""
+
+    def __init__(self, n_subdivisions=4, max_level=4, dim=10, store_indices=False, use_kd_tree=True):
+        self.n_subdivisions = max(n_subdivisions, 1)
+        self.max_level = max(max_level, 1)
+        self.dim = dim
+        self.store_indices = store_indices
+        self.use_kd_tree = use_kd_tree
+        self.data = None
+        self.flat = None
+        self.build_info = None
+
+    # -- trees built elsewhere -------------------------------------------------------------
+    @classmethod
+    def from_reference(cls, ref_tree):
+        """A tree built (or unpickled) by the reference: ClusterTree with `.root`, `.data`."""
+        t = cls(ref_tree.n_subdivisions, ref_tree.max_level, ref_tree.dim)
+        t.data = getattr(ref_tree, "data", None)
+        t.flat = flatten_cluster_tree(_tree_dict_from_reference(ref_tree.root))
+        return t
+
+    @classmethod
+    def from_dict(cls, root, n_subdivisions=4, max_level=4, dim=10):
+        t = cls(n_subdivisions, max_level, dim)
+        t.flat = flatten_cluster_tree(root)
+        return t
+
+    @property
+    def points(self):
+        return self.flat.points
+
+    # -- build (a18) -----------------------------------------------------------------------
+    def construct(self, data, seeds=None, seed=0, device=None):
+        """cluster_tree.py:98-102 -> cluster_tree_node_builder.py:105-170, level-synchronous on the GPU.
+        seeds: optional callable (depth, node_ids, starts, counts, x_sorted) -> float32 [n_live, n_sub, dim]
+        initial centroids (parity runs inject the k-means++ picks of the CPU run); default: k-means++
+        drawn on the device from `seed`."""
+        self.data = np.asarray(data)
+        self.dim = min(self.data.shape[1], self.dim)
+        self.flat, self.build_info = build_cluster_tree(self.data, self.n_subdivisions, self.max_level, self.dim,
+                                                        self.use_kd_tree, seeds=seeds, seed=seed, device=device)
+        self.__dict__.pop("_dev_points", None)
+        return self
+
+    # -- search (a20) ----------------------------------------------------------------------
+    def find_best_example_excluding_search_candidates(self, obj, data, n_candidates=1):
+        cost = _PointCosts(self, obj, data)
+        value, row = cluster_tree_search(self.flat, cost, n_candidates)
+        self.last_search_lookups = cost.n_lookups
+        return value, self.flat.points[row].tolist()
+
+    def find_best_example_excluding_search(self, obj, data):
+        """cluster_tree.py:106-115: greedy descent (first minimum among the children), then the leaf."""
+        t = self.flat
+        cost = _PointCosts(self, obj, data)
+        node, level = t.root, 0
+        while level < self.max_level and not t.node_leaf[node]:
+            idx, is_kd = t.children(node)
+            if len(idx) == 0 or is_kd.all():
+                break
+            best_v, best_c = np.inf, idx[0]
+            for c in idx:
+                v = cost(t.node_row[c])
+                if v < best_v:
+                    best_v, best_c = v, c
+            node = int(best_c)
+            level += 1
+        v, row = _leaf_find_best_example(t, cost, node)
+        return v, t.points[row].tolist()
+
+
+# ---------------------------------------------------------------------------
+# FeatureClusterTree (feature_cluster_tree.py)
+# ---------------------------------------------------------------------------
+class FeatureClusterTree(_DevicePointsMixin):
+    """reference space_partitioning/feature_cluster_tree.py:55-187: k-means hierarchy over a feature
+    matrix down to single samples; a node's evaluable point is the mean of its samples' LATENT
+    vectors (options["use_feature_mean"] == False, :70-73).  Flat form: node_row (mean rows of
+    `points`), child_ptr/child_idx, node_sample (index into `data` of a leaf's first sample)."""
+
+    def __init__(self, features=None, data=None, indices=None, options=None, feature_args=None, seeds=None, seed=0,
+                 device=None):
+        self.data = None
+        self.points = None
+        self.node_row = self.child_ptr = self.child_idx = self.node_sample = None
+        self.args = feature_args
+        self._options = options
+        self.build_info = None
+        if features is not None:
+            self._construct(features, data, indices, options, seeds, seed, device)
+
+    def _construct(self, features, data, indices, options, seeds, seed, device):
+        assert indices is None, "the device build starts from the whole sample set"
+        if options.get("use_feature_mean", False):
+            raise engine.UnsupportedConstraintError("use_feature_mean: node means in feature space cannot be scored by the "
+                                                    "latent-space objective (reference feature_cluster_tree.py:70-71)")
+        self.data = np.asarray(data)
+        flat, info = build_feature_tree(np.asarray(features), self.data, int(options["n_subdivisions"]), seeds=seeds, seed=seed,
+                                        device=device)
+        self.points, self.node_row, self.child_ptr, self.child_idx, self.node_sample = flat
+        self.build_info = info
+
+    @classmethod
+    def from_dict(cls, root, data):
+        """{"mean", "indices", "children"} nested dicts (a serialised reference tree) -> flat form."""
+        t = cls()
+        t.data = np.asarray(data)
+        means, child_lists, samples = [], [], []
+        queue = [root]
+        ids = {id(root): 0}
+        means.append(root["mean"])
+        child_lists.append([])
+        samples.append(-1 if not root.get("indices") else int(root["indices"][0]))
+        qi = 0
+        while qi < len(queue):
+            n = queue[qi]
+            me = ids[id(n)]
+            qi += 1
+            for c in n["children"]:
+                i = len(means)
+                ids[id(c)] = i
+                means.append(c["mean"])
+                child_lists.append([])
+                samples.append(-1 if not c.get("indices") else int(c["indices"][0]))
+                child_lists[me].append(i)
+                queue.append(c)
+        t.points = np.asarray(means, dtype=np.float64)
+        t.node_row = np.arange(len(means), dtype=np.int64)
+        t.child_ptr = np.zeros(len(means) + 1, dtype=np.int64)
+        t.child_ptr[1:] = np.cumsum([len(c) for c in child_lists])
+        t.child_idx = np.asarray([e for c in child_lists for e in c], dtype=np.int64)
+        t.node_sample = np.asarray(samples, dtype=np.int64)
+        return t
+
+    @classmethod
+    def from_reference(cls, ref_tree):
+        def conv(n):
+            return {"mean": np.asarray(n._mean, dtype=np.float64).tolist(),
+                    "indices": None if n._indices is None else [int(i) for i in n._indices],
+                    "children": [conv(c) for c in n._children]}
+        return cls.from_dict(conv(ref_tree), ref_tree.data)
+
+    def _children(self, i):
+        return self.child_idx[self.child_ptr[i]:self.child_ptr[i + 1]]
+
+    def find_best_example_excluding_search_candidates(self, obj, args, n_candidates=1):
+        """feature_cluster_tree.py:154-187.  The reference appends `self.args` to the objective's data
+        tuple (:129); objectives here read data[:3] only."""
+        cost = _PointCosts(self, obj, tuple(args))
+        results = []
+        candidates = [(np.inf, 0)]
+        while len(candidates) > 0:
+            new_candidates = []
+            for value, node in candidates:
+                ch = self._children(node)
+                if len(ch) > 0:
+                    good = _heap_prefix([(cost(self.node_row[c]), int(c)) for c in ch], n_candidates)   # :150-152
+                    for c in good:
+                        heapq.heappush(new_candidates, c)
+                else:
+                    heapq.heappush(results, (value, node))
+            candidates = new_candidates[:n_candidates]
+        self.last_search_lookups = cost.n_lookups
+        if len(results) > 0:
+            value, node = heapq.heappop(results)
+            return value, self.data[self.node_sample[node]]
+        return np.inf, self.data[0]
+
+    def find_best_example_excluding_search(self, obj, args):
+        """:100-109: greedy descent, returns the leaf's sample."""
+        cost = _PointCosts(self, obj, tuple(args))
+        node = 0
+        while len(self._children(node)) > 0:
+            best_v, best_c = np.inf, self._children(node)[0]
+            for c in self._children(node):
+                v = cost(self.node_row[c])
+                if v < best_v:
+                    best_v, best_c = v, c
+            node = int(best_c)
+        return self.data[self.node_sample[node]]
+
+
+# ---------------------------------------------------------------------------
+# device build (a18): level-synchronous k-means + batched kd-trees
+# ---------------------------------------------------------------------------
+KMEANS_TOL = 1e-4        # sklearn KMeans default tol, relative to the mean per-column variance
+KMEANS_MAX_ITER = 300    # sklearn KMeans default
+
+
+def _lloyd_level(x, dim, node, n_nodes, n_sub, centroids, tol, dim_acc, max_iter=KMEANS_MAX_ITER):
+    """The only arithmetic of the build that is not index bookkeeping: K7 (no CPU fallback)."""
+    return engine.kmeans_level(x, dim, node, n_nodes, n_sub, centroids, tol=tol, max_iter=max_iter, dim_acc=dim_acc)
+
+
+def _segment_stats(x, dim, node, n_nodes, dim_acc):
+    """Per node: mean over the first dim_acc columns and sklearn's absolute tolerance
+    tol * mean_j var_j(x[:, :dim]) (sklearn.cluster._kmeans._tolerance), from two E-step-only passes
+    with a single 'cluster' per node: centroid 0 -> sums -> mean; centroid = mean -> inertia."""
+    torch = engine._torch()
+    zero = torch.zeros((n_nodes, 1, dim), dtype=torch.float32, device=x.device)
+    r = _lloyd_level(x, dim, node, n_nodes, 1, zero, None, dim_acc, max_iter=0)
+    cnt = r["counts"][:, 0].clamp(min=1).to(torch.float32)
+    mean = r["sums"][:, 0, :] / cnt[:, None]
+    cen = mean[:, None, :dim].contiguous()
+    r2 = _lloyd_level(x, dim, node, n_nodes, 1, cen, None, dim_acc, max_iter=0)
+    tol = (KMEANS_TOL * r2["inertia"] / (cnt * dim)).contiguous()
+    return mean, tol, r["counts"][:, 0]
+
+
+def _kmeanspp_seeds(x, dim, starts, counts, n_sub, gen):
+    """k-means++ picks for every node of the level at once (one trial per centre; sklearn tries
+    2 + log k candidates per centre, which changes the picks, not the algorithm - label parity with
+    a CPU run is only defined for injected seeds).  Index bookkeeping in
+    torch; x is sorted by node, node i owns rows [starts[i], starts[i] + counts[i])."""
+    torch = engine._torch()
+    n_nodes = starts.shape[0]
+    dev = x.device
+    node = torch.repeat_interleave(torch.arange(n_nodes, device=dev), counts)
+    cent = torch.empty((n_nodes, n_sub, dim), dtype=torch.float32, device=dev)
+    u = torch.rand((n_nodes, n_sub), generator=gen, device=dev, dtype=torch.float64)
+    first = starts + (u[:, 0] * counts).long().minimum(counts - 1)
+    cent[:, 0] = x[first, :dim]
+    d2 = ((x[:, :dim] - cent[node, 0]) ** 2).sum(dim=1).double()
+    for j in range(1, n_sub):
+        cs = torch.cumsum(d2, dim=0)
+        base = torch.where(starts > 0, cs[(starts - 1).clamp(min=0)], torch.zeros_like(cs[:1]).expand(n_nodes))
+        total = cs[starts + counts - 1] - base
+        target = base + u[:, j] * total
+        pick = torch.searchsorted(cs, target, right=True)
+        pick = torch.maximum(torch.minimum(pick, starts + counts - 1), starts)
+        cent[:, j] = x[pick, :dim]
+        d2 = torch.minimum(d2, ((x[:, :dim] - cent[node, j]) ** 2).sum(dim=1).double())
+    return cent.contiguous()
+
+
+def _build_kd_forest(X, rows, seg_len, dim):
+    """kd-trees of many point sets at once (kdtree.py:44-73 per set): at kd depth k every set is
+    sorted by column k % dim (stable, on top of the order the previous level left, like
+    list.sort on the parent's sub-list), the element at len // 2 becomes the node, the halves become
+    the next level's sets.  rows: sample ids, concatenated set after set; seg_len [S].
+    Returns (kd_point [n] sample ids, kd_left, kd_right, kd_inner, roots [S]) - torch tensors on X's device."""
+    torch = engine._torch()
+    dev = X.device
+    S = int(seg_len.shape[0])
+    cur_rows = rows
+    cur_seg = torch.repeat_interleave(torch.arange(S, device=dev), seg_len)
+    pts, lefts, rights, inners = [], [], [], []
+    roots = torch.arange(S, device=dev)
+    next_base = S
+    k = 0
+    n_seg = S
+    while cur_rows.numel() > 0:
+        vals = X[cur_rows, k % dim]
+        p1 = torch.argsort(vals, stable=True)
+        p2 = torch.argsort(cur_seg[p1], stable=True)
+        perm = p1[p2]
+        cur_rows, cur_seg = cur_rows[perm], cur_seg[perm]
+        lens = torch.bincount(cur_seg, minlength=n_seg)
+        starts = torch.cumsum(lens, 0) - lens
+        pos = torch.arange(cur_rows.numel(), device=dev) - starts[cur_seg]
+        med = lens // 2
+        inner = lens > 1
+        left_len = torch.where(inner, med, torch.zeros_like(med))
+        right_len = torch.where(inner, lens - med - 1, torch.zeros_like(med))
+        exists = torch.stack([left_len > 0, right_len > 0], dim=1).reshape(-1)
+        new_id = torch.cumsum(exists.long(), 0) - 1
+        pts.append(cur_rows[starts + med])
+        lefts.append(torch.where(exists[0::2], next_base + new_id[0::2], torch.full_like(med, -1)))
+        rights.append(torch.where(exists[1::2], next_base + new_id[1::2], torch.full_like(med, -1)))
+        inners.append(inner)
+        seg_med = med[cur_seg]
+        keep = pos != seg_med
+        side = (pos > seg_med).long()
+        cur_seg = new_id[2 * cur_seg + side][keep]
+        cur_rows = cur_rows[keep]
+        n_seg = int(exists.sum().item())
+        next_base += n_seg
+        k += 1
+    if not pts:
+        e = torch.empty(0, dtype=torch.long, device=dev)
+        return e, e, e, e.bool(), roots
+    return torch.cat(pts), torch.cat(lefts), torch.cat(rights), torch.cat(inners), roots
+
+
+def _device_of(device):
+    torch = engine._torch()
+    if device is not None:
+        return torch.device(device)
+    if not torch.cuda.is_available():
+        raise engine.MgbError("no CUDA device: the cluster-tree build has no CPU fallback")
+    return torch.device("cuda", torch.cuda.current_device())
+
+
+def _subdivide_level(Xl, dim, n_sub, starts, counts, depth, gids, seeds, gen, dim_acc):
+    """One tree level: k-means of every live node, samples re-sorted by (node, label).
+    Returns (perm, child_node [n_children] index of the parent within the level, child_counts,
+    child_means [n_children, dim_acc], parent_mean [n_live, dim_acc], iterations)."""
+    torch = engine._torch()
+    n_live = int(starts.shape[0])
+    node64 = torch.repeat_interleave(torch.arange(n_live, device=Xl.device), counts)
+    node = node64.to(torch.int32).contiguous()
+    mean, tol, _ = _segment_stats(Xl, dim, node, n_live, dim_acc)
+    if seeds is not None:
+        cent = seeds(depth, gids, starts, counts, Xl)
+        cent = torch.as_tensor(cent, dtype=torch.float32, device=Xl.device).contiguous()
+    else:
+        cent = _kmeanspp_seeds(Xl, dim, starts, counts, n_sub, gen)
+    r = _lloyd_level(Xl, dim, node, n_live, n_sub, cent, tol, dim_acc)
+    key = node64 * n_sub + r["label"].long()
+    perm = torch.argsort(key, stable=True)
+    flat_counts = r["counts"].reshape(-1).long()
+    ck = torch.nonzero(flat_counts > 0).reshape(-1)          # ascending = (node, label) order
+    cc = flat_counts[ck]
+    means = r["sums"].reshape(-1, dim_acc)[ck] / cc[:, None].to(torch.float32)
+    return perm, ck // n_sub, cc, means, mean, r["iters"]
+
+
+def build_cluster_tree(data, n_sub, max_level, dim, use_kd_tree=True, seeds=None, seed=0, device=None):
+    """cluster_tree_node_builder.py:105-170 level by level.  Node rule per depth d and member count c:
+    c > n_sub -> k-means into <= n_sub children (nodes while d < max_level, kd-trees at d == max_level);
+    otherwise a leaf holding one kd-tree of its members.  Returns (FlatClusterTree, info)."""
+    torch = engine._torch()
+    if not use_kd_tree:
+        raise engine.MgbError("device build implements use_kd_tree=True (the reference builder's setting, "
+                              "construction/cluster_tree_builder.py:235-247)")
+    dev = _device_of(device)
+    gen = torch.Generator(device=dev)
+    gen.manual_seed(int(seed))
+    data = np.asarray(data)
+    N, D = data.shape
+    X = torch.as_tensor(np.ascontiguousarray(data, dtype=np.float32), device=dev)
+    node_means = [None]                       # list of [*, D] tensors, root first
+    node_leaf = [torch.zeros(1, dtype=torch.bool, device=dev)]
+    edges_parent, edges_child = [], []        # node -> node edges, in (parent, label) order per level
+    kd_owner, kd_len, kd_rows = [], [], []    # kd sets in creation order
+    n_nodes = 1
+    info = {"levels": [], "n_samples": int(N)}
+    Xl = X
+    order_l = torch.arange(N, device=dev)
+    gids = torch.zeros(1, dtype=torch.long, device=dev)
+    starts = torch.zeros(1, dtype=torch.long, device=dev)
+    counts = torch.full((1,), N, dtype=torch.long, device=dev)
+    if not (N > n_sub and n_sub > 1):
+        # the root itself is a leaf (cluster_tree_node_builder.py:131-133)
+        node_means[0] = X.double().mean(dim=0, keepdim=True).float()
+        node_leaf[0][0] = True
+        kd_owner.append(gids)
+        kd_len.append(counts)
+        kd_rows.append(order_l)
+        gids = gids[:0]
+    depth = 0
+    while gids.numel() > 0:
+        perm, child_node, cc, cmeans, pmean, iters = _subdivide_level(Xl, dim, n_sub, starts, counts, depth, gids, seeds, gen, D)
+        if depth == 0:
+            node_means[0] = pmean
+        Xl, order_l = Xl[perm], order_l[perm]
+        cstarts = torch.cumsum(cc, 0) - cc
+        parents = gids[child_node]
+        info["levels"].append({"depth": depth, "nodes": int(gids.numel()), "samples": int(Xl.shape[0]), "lloyd_iterations": int(iters)})
+        if depth < max_level:
+            n_children = int(cc.numel())
+            cg = n_nodes + torch.arange(n_children, device=dev)
+            n_nodes += n_children
+            live = cc > n_sub
+            node_means.append(cmeans)
+            node_leaf.append(~live)
+            edges_parent.append(parents)
+            edges_child.append(cg)
+            # leaves: one kd-tree each over their members
+            kd_owner.append(cg[~live])
+            kd_len.append(cc[~live])
+            sample_live = torch.repeat_interleave(live, cc)
+            kd_rows.append(order_l[~sample_live])
+            Xl, order_l = Xl[sample_live].contiguous(), order_l[sample_live]
+            gids, counts = cg[live], cc[live]
+            starts = torch.cumsum(counts, 0) - counts
+        else:
+            # depth == max_level: every cluster becomes a kd-tree of its parent (which keeps leaf == False)
+            kd_owner.append(parents)
+            kd_len.append(cc)
+            kd_rows.append(order_l)
+            gids = gids[:0]
+        depth += 1
+    owner = torch.cat(kd_owner) if kd_owner else torch.empty(0, dtype=torch.long, device=dev)
+    seg_len = torch.cat(kd_len) if kd_len else owner
+    rows = torch.cat(kd_rows) if kd_rows else owner
+    kd_pt, kd_l, kd_r, kd_in, roots = _build_kd_forest(X, rows, seg_len, dim)
+    # ---- flat arrays on the host ------------------------------------------------------------
+    t = FlatClusterTree()
+    means = torch.cat(node_means).double().cpu().numpy()
+    t.points = np.concatenate([means, np.asarray(data, dtype=np.float64)], axis=0)
+    t.node_row = np.arange(n_nodes, dtype=np.int64)
+    t.node_leaf = torch.cat(node_leaf).cpu().numpy()
+    ep = torch.cat(edges_parent).cpu().numpy() if edges_parent else np.empty(0, dtype=np.int64)
+    ec = torch.cat(edges_child).cpu().numpy() if edges_child else np.empty(0, dtype=np.int64)
+    kp = owner.cpu().numpy()
+    kc = roots.cpu().numpy()
+    par = np.concatenate([ep, kp])
+    chi = np.concatenate([ec, kc])
+    iskd = np.concatenate([np.zeros(len(ep), dtype=bool), np.ones(len(kp), dtype=bool)])
+    o = np.argsort(par, kind="stable")
+    t.child_idx, t.child_is_kd = chi[o], iskd[o]
+    t.child_ptr = np.zeros(n_nodes + 1, dtype=np.int64)
+    t.child_ptr[1:] = np.cumsum(np.bincount(par, minlength=n_nodes))
+    t.kd_row = n_nodes + kd_pt.cpu().numpy()
+    t.kd_left, t.kd_right, t.kd_inner = kd_l.cpu().numpy(), kd_r.cpu().numpy(), kd_in.cpu().numpy()
+    info["n_nodes"] = n_nodes
+    info["n_kd_nodes"] = int(len(t.kd_row))
+    return t, info
+
+
+def build_feature_tree(features, data, n_sub, seeds=None, seed=0, device=None):
+    """feature_cluster_tree.py:61-98 + clustering.py:105-129 level by level.  Node rule for member count c:
+    c > n_sub -> k-means on the feature rows into <= n_sub children (if one cluster swallows every
+    member: one single-sample child per member, :90-93); 1 < c <= n_sub -> one single-sample child per
+    member; c == 1 -> leaf.  A node's point is the mean of its members' rows of `data` (:72-73).
+    Returns ((points, node_row, child_ptr, child_idx, node_sample), info)."""
+    torch = engine._torch()
+    dev = _device_of(device)
+    gen = torch.Generator(device=dev)
+    gen.manual_seed(int(seed))
+    features = np.asarray(features)
+    data = np.asarray(data)
+    N, Fd = features.shape
+    D = data.shape[1]
+    X = torch.as_tensor(np.ascontiguousarray(np.concatenate([features, data], axis=1), dtype=np.float32), device=dev)
+    means, exact, first_sample = [None], [torch.full((1,), -1, dtype=torch.long, device=dev)], [torch.zeros(1, dtype=torch.long, device=dev)]
+    edges_parent, edges_child = [], []
+    n_nodes = 1
+    info = {"levels": [], "n_samples": int(N)}
+    Xl, order_l = X, torch.arange(N, device=dev)
+    gids = torch.zeros(1, dtype=torch.long, device=dev)
+    starts = torch.zeros(1, dtype=torch.long, device=dev)
+    counts = torch.full((1,), N, dtype=torch.long, device=dev)
+
+    def add_singletons(parent_gid_per_sample, sample_ids):
+        nonlocal n_nodes
+        m = int(sample_ids.numel())
+        if m == 0:
+            return
+        g = n_nodes + torch.arange(m, device=dev)
+        n_nodes += m
+        means.append(torch.zeros((m, D), dtype=torch.float32, device=dev))
+        exact.append(sample_ids)
+        first_sample.append(sample_ids)
+        edges_parent.append(parent_gid_per_sample)
+        edges_child.append(g)
+
+    if N <= n_sub:
+        means[0] = X[:, Fd:].double().mean(dim=0, keepdim=True).float()
+        if N > 1:
+            add_singletons(torch.zeros(N, dtype=torch.long, device=dev), order_l)
+        else:
+            exact[0][0] = 0
+        gids = gids[:0]
+    depth = 0
+    while gids.numel() > 0:
+        perm, child_node, cc, cmeans, pmean, iters = _subdivide_level(Xl, Fd, n_sub, starts, counts, depth, gids, seeds, gen, Fd + D)
+        if depth == 0:
+            means[0] = pmean[:, Fd:]
+        Xl, order_l = Xl[perm], order_l[perm]
+        info["levels"].append({"depth": depth, "nodes": int(gids.numel()), "samples": int(Xl.shape[0]), "lloyd_iterations": int(iters)})
+        cstarts = torch.cumsum(cc, 0) - cc
+        degenerate = cc == counts[child_node]
+        normal = ~degenerate
+        n_children = int(normal.sum().item())
+        cg = torch.full_like(cc, -1)
+        cg[normal] = n_nodes + torch.arange(n_children, device=dev)
+        n_nodes += n_children
+        single = normal & (cc == 1)
+        means.append(cmeans[normal][:, Fd:])
+        exact.append(torch.where(single, order_l[cstarts], torch.full_like(cc, -1))[normal])
+        first_sample.append(order_l[cstarts][normal])
+        edges_parent.append(gids[child_node][normal])
+        edges_child.append(cg[normal])
+        small = normal & (cc > 1) & (cc <= n_sub)
+        live = normal & (cc > n_sub)
+        child_of_sample = torch.repeat_interleave(torch.arange(cc.numel(), device=dev), cc)
+        expand = (degenerate | small)[child_of_sample]
+        parent_of_sample = torch.where(degenerate, gids[child_node], cg)[child_of_sample]
+        add_singletons(parent_of_sample[expand], order_l[expand])
+        sample_live = live[child_of_sample]
+        Xl, order_l = Xl[sample_live].contiguous(), order_l[sample_live]
+        gids, counts = cg[live], cc[live]
+        starts = torch.cumsum(counts, 0) - counts
+        depth += 1
+    pts = torch.cat(means).double().cpu().numpy()
+    ex = torch.cat(exact).cpu().numpy()
+    sel = ex >= 0
+    pts[sel] = np.asarray(data, dtype=np.float64)[ex[sel]]
+    par = torch.cat(edges_parent).cpu().numpy() if edges_parent else np.empty(0, dtype=np.int64)
+    chi = torch.cat(edges_child).cpu().numpy() if edges_child else np.empty(0, dtype=np.int64)
+    o = np.argsort(par, kind="stable")
+    child_ptr = np.zeros(n_nodes + 1, dtype=np.int64)
+    child_ptr[1:] = np.cumsum(np.bincount(par, minlength=n_nodes))
+    info["n_nodes"] = n_nodes
+    flat = (pts, np.arange(n_nodes, dtype=np.int64), child_ptr, chi[o], torch.cat(first_sample).cpu().numpy())
+    return flat, info

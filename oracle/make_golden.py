@@ -230,6 +230,47 @@ def run_tree_case(ns, n_data=400, n_candidates_list=(1, 2, 5), seed=11):
             v, s = ftree.find_best_example_excluding_search_candidates(obj, (node, mpc, None), nc)
         res.append(np.concatenate([[v], np.asarray(s, dtype=np.float64)]))
     out["feature_tree_results"] = np.array(res)
+    # ---- builds with INJECTED seeds: the reference's own builder code, its
+    # sklearn KMeans handed fixed initial centres (members at positions len*j//k of the node's member
+    # list) so that the subdivision is reproducible by the oracle restatement and the device build
+    import sklearn.cluster
+
+    class SeededKMeans(object):
+        def __init__(self, n_clusters=4):
+            self.k = n_clusters
+
+        def fit_predict(self, X):
+            X = np.asarray(X)
+            init = X[[(len(X) * j) // self.k for j in range(self.k)]]
+            return sklearn.cluster.KMeans(n_clusters=self.k, init=init, n_init=1, algorithm="lloyd").fit_predict(X)
+
+    import types
+    shim = types.SimpleNamespace(KMeans=SeededKMeans)
+    builder_mod = sys.modules[ns.cluster_tree.ClusterTreeNodeBuilder.__module__]
+    clustering_mod = sys.modules[ns.feature_cluster_tree.find_clusters.__module__]
+    saved = builder_mod.cluster, clustering_mod.cluster
+    builder_mod.cluster = clustering_mod.cluster = shim
+    try:
+        with _quiet():
+            for tag, max_level in (("seeded6", 6), ("seeded2", 2)):
+                tree = ns.cluster_tree.ClusterTree(4, max_level, K, store_indices=True, use_kd_tree=True)
+                tree.construct(data)
+                out["cluster_tree_%s_json" % tag] = np.array(json.dumps(serialize_cluster_tree(tree.root)))
+                if max_level == 6:
+                    res = []
+                    for nc in n_candidates_list:
+                        v, s = tree.find_best_example_excluding_search_candidates(obj, (node, mpc, None), nc)
+                        res.append(np.concatenate([[v], np.asarray(s, dtype=np.float64)]))
+                    out["cluster_tree_seeded6_results"] = np.array(res)
+            ftree = ns.feature_cluster_tree.FeatureClusterTree(data[:, :K], data, None, opts, [])
+            out["feature_tree_seeded_json"] = np.array(json.dumps(serialize_feature_tree(ftree)))
+            res = []
+            for nc in n_candidates_list:
+                v, s = ftree.find_best_example_excluding_search_candidates(obj, (node, mpc, None), nc)
+                res.append(np.concatenate([[v], np.asarray(s, dtype=np.float64)]))
+            out["feature_tree_seeded_results"] = np.array(res)
+    finally:
+        builder_mod.cluster, clustering_mod.cluster = saved
     return out
 
 
@@ -259,6 +300,11 @@ def serialize_feature_tree(node):
 def main():
     ns = refload.load()
     os.makedirs(GOLDEN_DIR, exist_ok=True)
+    if "--only-tree" in sys.argv:
+        out = run_tree_case(ns)
+        np.savez_compressed(os.path.join(GOLDEN_DIR, "s_tree.npz"), **out)
+        print("s_tree", out["cluster_tree_results"][:, 0], out["cluster_tree_seeded6_results"][:, 0], out["feature_tree_seeded_results"][:, 0])
+        return 0
     cases = [
         ("s_config1", dict(shape="S", which="config1", n_samples=96, seed=2024)),
         ("s_mixed", dict(shape="S", which="mixed", n_samples=64, seed=2025)),

@@ -593,3 +593,148 @@ def heap_prefix(values_with_payload, n):
     for item in values_with_payload:
         heapq.heappush(q, item)
     return q[:n]
+
+
+def injected_seed_rows(n_members, n_sub):
+    """The injected-seed rule of the seeded golden builds (oracle/make_golden.py: SeededKMeans):
+    initial centres = members at positions len * j // k of the node's member list."""
+    return [(n_members * j) // n_sub for j in range(n_sub)]
+
+
+def _kd_dict(points, dim, depth=0):
+    """kdtree.py:44-73: sort by axis depth % dim (list.sort: stable), median len // 2."""
+    if len(points) > 1:
+        axis = depth % dim
+        points = sorted(points, key=lambda p: p[axis])
+        median = len(points) // 2
+        left, right = points[:median], points[median + 1:]
+        return {"point": list(map(float, points[median])), "type": "inner",
+                "left": _kd_dict(left, dim, depth + 1) if len(left) > 0 else None,
+                "right": _kd_dict(right, dim, depth + 1) if len(right) > 0 else None}
+    return {"point": list(map(float, points[0])), "type": "leaf", "left": None, "right": None}
+
+
+def build_cluster_tree_dict(data, n_sub=4, max_level=4, dim=10, indices=None, depth=0):
+    """cluster_tree_node_builder.py:105-170 (use_kd_tree=True) with injected seeds; nested dicts in the
+    layout of make_golden.serialize_cluster_tree."""
+    data = np.asarray(data, dtype=np.float64)
+    dim = min(dim, data.shape[1])
+    idx = np.arange(len(data)) if indices is None else np.asarray(indices)
+    mean = data[idx].mean(axis=0)
+    n = len(idx)
+    children = []
+    if n > n_sub and n_sub > 1:
+        leaf = False
+        X = data[idx, :dim]
+        labels, _, _ = kmeans_lloyd(X, X[injected_seed_rows(n, n_sub)])
+        for j in range(n_sub):
+            members = idx[labels == j]
+            if len(members) == 0:
+                continue
+            if depth < max_level:
+                children.append(build_cluster_tree_dict(data, n_sub, max_level, dim, members, depth + 1))
+            else:
+                children.append({"kdtree": _kd_dict(data[members].tolist(), dim)})
+    else:
+        leaf = True
+        children.append({"kdtree": _kd_dict(data[idx].tolist(), dim)})
+    return {"mean": mean.tolist(), "leaf": leaf, "children": children}
+
+
+def build_feature_tree_dict(features, data, n_sub=4, indices=None):
+    """feature_cluster_tree.py:61-98 + clustering.py:105-129 with injected seeds; nested dicts in the
+    layout of make_golden.serialize_feature_tree."""
+    features = np.asarray(features, dtype=np.float64)
+    data = np.asarray(data, dtype=np.float64)
+    idx = list(range(len(features))) if indices is None else list(indices)
+    node = {"mean": data[idx].mean(axis=0).tolist(), "indices": None if indices is None else [int(i) for i in idx], "children": []}
+    if len(idx) > 1:
+        all_eq = len(idx) < 10 and all(np.array_equal(features[a], features[idx[0]]) for a in idx)
+        if all_eq:
+            clusters = [[i] for i in idx]
+        elif len(idx) > n_sub:
+            X = features[idx]
+            labels, _, _ = kmeans_lloyd(X, X[injected_seed_rows(len(idx), n_sub)])
+            clusters = [[i for i, l in zip(idx, labels) if l == j] for j in range(n_sub)]
+            clusters = [c for c in clusters if len(c) > 0]
+            if len(clusters) == 1:
+                clusters = [[i] for i in idx]
+        else:
+            clusters = [[i] for i in idx]
+        for c in clusters:
+            node["children"].append(build_feature_tree_dict(features, data, n_sub, c))
+    return node
+
+
+def _kd_search_dict(kd, cost):
+    """kdtree.py:233-250, k = 1."""
+    pts = [kd["point"]]
+    q = [(cost(kd["point"]), 0)]
+    node, depth = kd, 0
+    while node is not None and node["type"] == "inner":
+        depth += 1
+        left, right = node["left"], node["right"]
+        if left is not None and right is not None:
+            r_d, l_d = cost(right["point"]), cost(left["point"])
+            node, least = (left, l_d) if l_d < r_d else (right, r_d)
+        elif right is not None:
+            node, least = right, cost(right["point"])
+        elif left is not None:
+            node, least = left, cost(left["point"])
+        else:
+            node, least = None, np.inf
+        if node is not None:
+            heapq.heappush(q, (least, depth))
+            pts.append(node["point"])
+    return q[0][0], pts[q[0][1]]
+
+
+def cluster_tree_search_dict(root, cost, n_candidates=1):
+    """cluster_tree.py:117-149 + cluster_tree_node.py:63-76,113-138 on the nested-dict tree;
+    cost(point list) -> float."""
+    results, candidates, serial = [], [(np.inf, 0, 0, root)], 0
+    while candidates:
+        new = []
+        for c_idx, (value, _t, _s, node) in enumerate(candidates):
+            if not node["leaf"]:
+                items = []
+                for ci, c in enumerate(node["children"]):
+                    serial += 1
+                    items.append((cost(c["mean"]), ci, serial, c))
+                for i, c in enumerate(heap_prefix(items, n_candidates)):
+                    serial += 1
+                    heapq.heappush(new, (c[0], i, serial, c[3]))
+            else:
+                q = []
+                for c in node["children"]:
+                    heapq.heappush(q, _kd_search_dict(c["kdtree"], cost))
+                v, sample = heapq.heappop(q)
+                heapq.heappush(results, (v, c_idx, sample))
+        candidates = new[:n_candidates]
+    if results:
+        r = heapq.heappop(results)
+        return r[0], r[2]
+    return np.inf, root["mean"]
+
+
+def feature_tree_search_dict(root, data, cost, n_candidates=1):
+    """feature_cluster_tree.py:154-187."""
+    results, candidates, serial = [], [(np.inf, 0, root)], 0
+    while candidates:
+        new = []
+        for value, _s, node in candidates:
+            if len(node["children"]) > 0:
+                items = []
+                for c in node["children"]:
+                    serial += 1
+                    items.append((cost(c["mean"]), serial, c))
+                for c in heap_prefix(items, n_candidates):
+                    heapq.heappush(new, c)
+            else:
+                serial += 1
+                heapq.heappush(results, (value, serial, node))
+        candidates = new[:n_candidates]
+    if results:
+        value, _, node = heapq.heappop(results)
+        return value, np.asarray(data)[node["indices"][0]]
+    return np.inf, np.asarray(data)[0]
