@@ -271,6 +271,22 @@ def run_tree_case(ns, n_data=400, n_candidates_list=(1, 2, 5), seed=11):
             out["feature_tree_seeded_results"] = np.array(res)
     finally:
         builder_mod.cluster, clustering_mod.cluster = saved
+    # ---- euclidean PCA features (a19): the reference's features.map_motions_to_euclidean_pca on motions
+    # evaluated like construction/cluster_tree_builder.py:293-301 (every integer canonical frame), with
+    # use_time_parameters=False (the time-warp branch raises under numpy 2, quirk Q3)
+    n_feat = 120
+    motions = []
+    for sv in data[:n_feat]:
+        spline = node.back_project(sv, use_time_parameters=False)
+        motions.append([spline.evaluate(fi) for fi in range(int(node.get_n_canonical_frames()))])
+    motions = np.array(motions)
+    with _quiet():
+        feats, pca = ns.features.map_motions_to_euclidean_pca(motions, skeleton, ns.features.END_EFFECTORS2, step=1)
+        clouds = np.array(ns.features.map_motions_to_euclidean_space(motions[:4], skeleton, ns.features.END_EFFECTORS2, step=1))
+    out["euclid_n_samples"] = np.array(n_feat)
+    out["euclid_point_clouds"] = clouds
+    out["euclid_features"] = np.asarray(feats)
+    out["euclid_explained_variance_ratio"] = np.asarray(pca.explained_variance_ratio_)
     return out
 
 

@@ -738,3 +738,35 @@ def feature_tree_search_dict(root, data, cost, n_candidates=1):
         value, _, node = heapq.heappop(results)
         return value, np.asarray(data)[node["indices"][0]]
     return np.inf, np.asarray(data)[0]
+
+
+# --------------------------------------------------------------------------
+# euclidean PCA features of the cluster-tree build (a19)
+# --------------------------------------------------------------------------
+END_EFFECTORS2 = ["LeftUpLeg", "RightUpLeg", "RightHand", "Bip01_R_Finger2", "LeftHand", "Bip01_L_Finger2", "RightFoot",
+                  "Bip01_R_Toe0", "LeftFoot", "Bip01_L_Toe0"]        # space_partitioning/features.py:32
+
+
+def euclidean_point_clouds(model, skeleton, S, joint_names=END_EFFECTORS2):
+    """construction/cluster_tree_builder.py:293-301 (every integer canonical frame of the back-projected
+    spline) + space_partitioning/features.py:133-153 with step = 1: [M, F * len(joints) * 3], frame-major,
+    joints in list order."""
+    ma = model if isinstance(model, ModelArrays) else ModelArrays(model)
+    S = np.atleast_2d(np.asarray(S, dtype=np.float64))
+    frames = eval_frames(ma, back_project_coeffs(ma, S), np.arange(ma.F, dtype=np.float64))     # [M, F, P]
+    M, F, P = frames.shape
+    pos = fk_positions(skeleton, frames.reshape(M * F, P), joint_names)                      # [M*F, J, 3]
+    return pos.reshape(M, F * len(joint_names) * 3)
+
+
+def pca_by_variance(X, variance=0.95):
+    """sklearn PCA(n_components=0.95).fit_transform (features.py:125-130): centre, SVD, keep the
+    smallest number of components whose explained-variance ratio sums to more than `variance`.
+    Component signs are a convention (sklearn's svd_flip); callers must compare sign-invariantly."""
+    X = np.asarray(X, dtype=np.float64)
+    Xc = X - X.mean(axis=0)
+    U, s, Vt = np.linalg.svd(Xc, full_matrices=False)
+    ev = s ** 2 / (len(X) - 1)
+    ratio = ev / ev.sum()
+    k = int(np.searchsorted(np.cumsum(ratio), variance, side="right") + 1)
+    return Xc @ Vt[:k].T, ratio[:k]

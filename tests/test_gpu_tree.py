@@ -218,3 +218,51 @@ def test_full_size_build_and_search_properties(tc):
         assert len(hit) >= 1
         assert abs(cost_all[hit[0]] - v) <= RTOL * max(1.0, abs(v))
         assert v >= float(exhaustive["best_cost"][0]) - 1e-4
+
+
+def test_euclidean_pca_features(tc):
+    """a19 on the device (K2 -> K3 -> K4 chunked, covariance PCA) against the reference's point clouds and
+    features: same number of components, same explained variance, same features up to component sign."""
+    from morphablegraphs_b200 import features as feat
+    from morphablegraphs_b200.objective_functions import _device_constraints
+    dm = _device_constraints(tc.node, tc.mpc, None).dmodel
+    g = tc.g
+    n = int(g["euclid_n_samples"])
+    clouds = feat.map_samples_to_euclidean_space(dm, tc.data[:n], feat.END_EFFECTORS2, chunk=50)
+    ref_clouds = g["euclid_point_clouds"]
+    got = clouds[:4].cpu().numpy()
+    assert (np.abs(got - ref_clouds) / np.maximum(np.abs(ref_clouds), 1.0)).max() < RTOL
+    f, ratio = feat.pca_by_variance(clouds)
+    f = f.cpu().numpy()
+    ref = g["euclid_features"]
+    assert f.shape == ref.shape
+    assert np.abs(ratio - g["euclid_explained_variance_ratio"]).max() < 1e-5
+    scale = np.abs(ref).max()
+    assert np.abs(np.abs(f) - np.abs(ref)).max() < 2e-4 * scale
+    # what the tree build consumes: pairwise distances (sign-free)
+    d_ref = np.linalg.norm(ref[:40, None] - ref[None, :40], axis=2)
+    d_got = np.linalg.norm(f[:40, None] - f[None, :40], axis=2)
+    assert np.abs(d_got - d_ref).max() < 2e-4 * max(1.0, d_ref.max())
+
+
+def test_feature_tree_on_euclidean_features_full_chain(tc):
+    """Config 5 (ii) end to end at a size the test finishes quickly: 20k samples -> euclidean PCA features
+    -> FeatureClusterTree on the device -> search; every sample is exactly one leaf."""
+    from morphablegraphs_b200 import features as feat, space_partitioning as sp
+    from morphablegraphs_b200.objective_functions import obj_spatial_error_sum, _device_constraints
+    dc = _device_constraints(tc.node, tc.mpc, None)
+    dm = dc.dmodel
+    n = 20000
+    S = dm.sample(n, seed=123)
+    f, ratio = feat.map_to_euclidean_pca(dm, S)
+    assert 0.95 <= ratio.sum() <= 1.0 + 1e-9
+    data = S.cpu().numpy().astype(np.float64)
+    opts = {"n_subdivisions": 4, "clustering_method": 0, "use_feature_mean": False}
+    tree = sp.FeatureClusterTree(f.cpu().numpy(), data, None, opts, [], seed=3)
+    leaves = np.where(np.diff(tree.child_ptr) == 0)[0]
+    assert np.array_equal(np.sort(tree.node_sample[leaves]), np.arange(n))
+    v, s = tree.find_best_example_excluding_search_candidates(obj_spatial_error_sum, (tc.node, tc.mpc, None), 5)
+    hit = np.where((data == np.asarray(s)).all(axis=1))[0]
+    assert len(hit) == 1
+    cost = dc.score(S, k=1, return_cost=True)["cost"].cpu().numpy()
+    assert abs(cost[hit[0]] - v) <= RTOL * max(1.0, abs(v))

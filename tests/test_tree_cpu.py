@@ -246,3 +246,16 @@ def test_level_synchronous_feature_build_bookkeeping(tc, monkeypatch):
         for x, y in zip(ca, cb):
             walk(int(x), int(y))
     walk(0, 0)
+
+
+def test_oracle_euclidean_pca_features_match_reference(tc):
+    """a19: point clouds and PCA(0.95) features of features.map_motions_to_euclidean_pca (component
+    signs are sklearn's svd_flip convention: compared up to sign)."""
+    g = tc.g
+    pc = O.euclidean_point_clouds(tc.ma, tc.skeleton, tc.data[:4])
+    assert np.abs(pc - g["euclid_point_clouds"]).max() < 1e-9
+    n = int(g["euclid_n_samples"])
+    f, ratio = O.pca_by_variance(O.euclidean_point_clouds(tc.ma, tc.skeleton, tc.data[:n]))
+    assert f.shape == g["euclid_features"].shape
+    assert np.abs(ratio - g["euclid_explained_variance_ratio"]).max() < 1e-12
+    assert np.abs(np.abs(f) - np.abs(g["euclid_features"])).max() < 1e-8
