@@ -9,11 +9,12 @@
 // every node's convergence (sklearn's rule: squared centre shift <= tol * mean variance).
 //
 // HBM-bound: per sample and Lloyd iteration 4*ld + 4 bytes read (row + node id), 4 bytes written
-// (label).  The accumulation never goes through per-sample atomics: a warp walks a contiguous run
-// of samples 32 at a time, lane = sample for the distance part, then lane = column for the
-// accumulation part (the tile lives in shared memory), keeping the running sums of its current
-// node in registers and flushing them with one vector RED per (node, cluster) when the node
-// changes.
+// (label).  The accumulation never goes through per-sample atomics: a warp walks a contiguous range
+// of samples 32 at a time, lane = sample for the distance part, then lane = (group, column) for the
+// accumulation part (the tile lives in shared memory; the 32 / W lane groups split the samples of a
+// run of equal node ids), keeping the running sums of its current node in registers and flushing
+// them with one vector RED per (node, cluster) when the node changes.  Member counts come from
+// ballots, the inertia from a warp reduction at flush time.
 #include <math.h>
 
 #include "mgb_internal.cuh"
@@ -33,14 +34,15 @@ int sm_count_tree() {
 
 constexpr int KM_WARPS = 4;
 
-// CH = ceil((dim_acc + 1) / 32): columns handled per lane; the extra "column" dim_acc carries
-// the member count and the inertia of the node.
+// CH = ceil(dim_acc / 32): columns handled per lane.  W (power of two, >= dim_acc when CH == 1, else 32)
+// is the width of a lane group; the 32 / W groups of a warp split the samples of a run between them.
 template <int NS, int CH>
 __global__ void __launch_bounds__(KM_WARPS * 32) mgb_kmeans_level_kernel(
     const float* __restrict__ x, long long n, int dim, int dim_acc, int ld, const int* __restrict__ node,
     const float* __restrict__ cent, int n_sub, int* __restrict__ label, float* __restrict__ sums,
-    int* __restrict__ counts, float* __restrict__ node_inertia, float* __restrict__ inertia, long long tiles_per_warp) {
+    int* __restrict__ counts, float* __restrict__ node_inertia, float* __restrict__ inertia, long long tiles_per_warp, int W) {
     extern __shared__ float sm_tiles[];
+    const unsigned FULL = 0xffffffffu;
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
     float* tile = sm_tiles + (size_t)warp * 32 * ld;
@@ -48,35 +50,45 @@ __global__ void __launch_bounds__(KM_WARPS * 32) mgb_kmeans_level_kernel(
     const long long first = gwarp * tiles_per_warp * 32;
     long long last = first + tiles_per_warp * 32;
     if (last > n) last = n;
+    const int G = 32 / W;          // lane groups
+    const int g = lane / W;        // my group
+    const int col0 = lane % W;     // my column (CH == 1) / first column (CH > 1: W == 32)
 
     float acc[NS][CH];
+    int cnt[NS];
 #pragma unroll
-    for (int k = 0; k < NS; ++k)
+    for (int k = 0; k < NS; ++k) {
+        cnt[k] = 0;
 #pragma unroll
         for (int c = 0; c < CH; ++c) acc[k][c] = 0.f;
-    float acc_inertia = 0.f;   // only meaningful on the lane that owns column dim_acc
+    }
+    float inertia_part = 0.f;      // per lane, of the current node's run(s)
+    float total_inertia = 0.f;     // lane 0
     int cur = -1;
-    float total_inertia = 0.f;
 
-    auto flush = [&]() {
+    auto flush = [&]() {           // warp-uniform call
         if (cur < 0) return;
 #pragma unroll
-        for (int c = 0; c < CH; ++c) {
-            const int col = lane + 32 * c;
-            if (col < dim_acc) {
+        for (int k = 0; k < NS; ++k) {
 #pragma unroll
-                for (int k = 0; k < NS; ++k)
-                    if (k < n_sub && acc[k][c] != 0.f) atomicAdd(sums + ((size_t)cur * n_sub + k) * dim_acc + col, acc[k][c]);
-            } else if (col == dim_acc) {
-#pragma unroll
-                for (int k = 0; k < NS; ++k)
-                    if (k < n_sub && acc[k][c] != 0.f) atomicAdd(counts + (size_t)cur * n_sub + k, (int)acc[k][c]);
-                if (node_inertia) atomicAdd(node_inertia + cur, acc_inertia);
+            for (int c = 0; c < CH; ++c) {
+                float v = acc[k][c];
+                for (int o = W; o < 32; o <<= 1) v += __shfl_xor_sync(FULL, v, o);
+                const int col = col0 + 32 * c;
+                if (g == 0 && k < n_sub && col < dim_acc && v != 0.f) atomicAdd(sums + ((size_t)cur * n_sub + k) * dim_acc + col, v);
+                acc[k][c] = 0.f;
             }
-#pragma unroll
-            for (int k = 0; k < NS; ++k) acc[k][c] = 0.f;
+            if (lane == 0 && k < n_sub && cnt[k] != 0) atomicAdd(counts + (size_t)cur * n_sub + k, cnt[k]);
+            cnt[k] = 0;
         }
-        acc_inertia = 0.f;
+        float t = inertia_part;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(FULL, t, o);
+        if (lane == 0) {
+            if (node_inertia && t != 0.f) atomicAdd(node_inertia + cur, t);
+            total_inertia += t;
+        }
+        inertia_part = 0.f;
     };
 
     for (long long t0 = first; t0 < last; t0 += 32) {
@@ -104,35 +116,41 @@ __global__ void __launch_bounds__(KM_WARPS * 32) mgb_kmeans_level_kernel(
                 if (d < best) { best = d; lb = k; }
             }
             label[t0 + lane] = lb;
-            total_inertia += best;
         }
-        // M-step sums: lane = column, the 32 samples in order (node ids come in runs)
-        for (int s = 0; s < rows; ++s) {
-            const int snd = __shfl_sync(0xffffffffu, nd, s);
-            const int slb = __shfl_sync(0xffffffffu, lb, s);
-            const float sbest = __shfl_sync(0xffffffffu, best, s);
-            if (snd != cur) {
+        // M-step sums, one run of equal node ids at a time (the samples are sorted by node)
+        const int prev = __shfl_up_sync(FULL, nd, 1);
+        unsigned heads = __ballot_sync(FULL, lane < rows && (lane == 0 || nd != prev));
+        while (heads) {
+            const int a = __ffs(heads) - 1;
+            heads &= heads - 1;
+            const int b = heads ? (__ffs(heads) - 1) : rows;
+            const int run_nd = __shfl_sync(FULL, nd, a);
+            if (run_nd != cur) {
                 flush();
-                cur = snd;
+                cur = run_nd;
             }
+            const bool in_run = lane >= a && lane < b;
 #pragma unroll
-            for (int c = 0; c < CH; ++c) {
-                const int col = lane + 32 * c;
-                float v = 0.f;
-                if (col < dim_acc) v = tile[s * ld + col];
-                else if (col == dim_acc) { v = 1.f; acc_inertia += sbest; }
+            for (int k = 0; k < NS; ++k) cnt[k] += __popc(__ballot_sync(FULL, in_run && lb == k));
+            if (in_run) inertia_part += best;
+            const int iters = (b - a + G - 1) / G;
+            for (int it = 0; it < iters; ++it) {
+                const int s = a + it * G + g;
+                const bool on = s < b;
+                const int slb = __shfl_sync(FULL, lb, on ? s : a);
 #pragma unroll
-                for (int k = 0; k < NS; ++k) acc[k][c] += (k == slb) ? v : 0.f;
+                for (int c = 0; c < CH; ++c) {
+                    const int col = col0 + 32 * c;
+                    const float v = (on && col < dim_acc) ? tile[s * ld + col] : 0.f;
+#pragma unroll
+                    for (int k = 0; k < NS; ++k) acc[k][c] += (k == slb) ? v : 0.f;
+                }
             }
         }
         __syncwarp();
     }
     flush();
-    if (inertia) {
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) total_inertia += __shfl_xor_sync(0xffffffffu, total_inertia, o);
-        if (lane == 0 && total_inertia != 0.f) atomicAdd(inertia, total_inertia);
-    }
+    if (inertia && lane == 0 && total_inertia != 0.f) atomicAdd(inertia, total_inertia);
 }
 
 // M-step finish + convergence test, one thread per node.  Empty clusters keep their centroid.
@@ -177,8 +195,13 @@ int launch_level(const float* d_x, int64_t n, int dim, int dim_acc, int ld, cons
     const long long tpw = (tiles + warps - 1) / warps;
     const long long used_warps = (tiles + tpw - 1) / tpw;
     const long long grid = (used_warps + KM_WARPS - 1) / KM_WARPS;
+    int W = 32;
+    if (CH == 1) {
+        W = 4;
+        while (W < dim_acc) W <<= 1;
+    }
     kern<<<(unsigned)grid, KM_WARPS * 32, smem, stream>>>(d_x, n, dim, dim_acc, ld, d_node, d_cent, n_sub, d_label, d_sums, d_counts,
-                                                           d_node_inertia, d_inertia, tpw);
+                                                           d_node_inertia, d_inertia, tpw, W);
     mgb_count_launch();
     MGB_CUDA(cudaGetLastError());
     return MGB_OK;
@@ -186,9 +209,9 @@ int launch_level(const float* d_x, int64_t n, int dim, int dim_acc, int ld, cons
 
 int dispatch_level(const float* d_x, int64_t n, int dim, int dim_acc, int ld, const int* d_node, const float* d_cent, int n_sub,
                    int* d_label, float* d_sums, int* d_counts, float* d_node_inertia, float* d_inertia, cudaStream_t stream) {
-    const int ch = (dim_acc + 1 + 31) / 32;
+    const int ch = (dim_acc + 31) / 32;
     MGB_REQUIRE(n_sub >= 1 && n_sub <= 8, "n_sub must be in 1..8");
-    MGB_REQUIRE(ch <= 4, "at most 127 accumulated columns");
+    MGB_REQUIRE(ch <= 4, "at most 128 accumulated columns");
 #define MGB_KM_CASE(NS, CH)                                                                                              \
     return launch_level<NS, CH>(d_x, n, dim, dim_acc, ld, d_node, d_cent, n_sub, d_label, d_sums, d_counts, d_node_inertia, \
                                 d_inertia, stream)

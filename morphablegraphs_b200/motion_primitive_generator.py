@@ -67,7 +67,9 @@ class MotionPrimitiveGenerator(object):
         else:
             mp_constraints = in_mp_constraints
             prev_frames_copy = prev_frames
-        if self.constrained_sampling_mode == SAMPLING_MODE_CLUSTER_TREE_SEARCH and graph_node.cluster_tree is not None:
+        if self.constrained_sampling_mode == SAMPLING_MODE_RANDOM_SPLINE:
+            sample = self._get_best_fit_sample_using_mgrd(graph_node, mp_constraints)
+        elif self.constrained_sampling_mode == SAMPLING_MODE_CLUSTER_TREE_SEARCH and graph_node.cluster_tree is not None:
             sample = self._get_best_fit_sample_using_cluster_tree(graph_node, mp_constraints, prev_frames_copy)
         else:
             sample = self._get_best_fit_sample_using_gmm(graph_node, mp_constraints, prev_mp_name, prev_frames_copy, prev_parameters)
@@ -117,6 +119,18 @@ class MotionPrimitiveGenerator(object):
         mp_constraints.evaluations += n
         best = dm.sample(1, seed=seed, index_base=best_idx, counts=counts, n_total=n)
         return best[0].cpu().numpy().astype(np.float64)
+
+    # ------------------------------------------------------------------ :167-177
+    def _get_best_fit_sample_using_mgrd(self, graph_node, mp_constraints):
+        """The reference's batched slot (samples [N, D] -> scores [N] -> np.argmin), scored by the engine
+        (mgrd_sample_filter.py of this package)."""
+        from .mgrd_sample_filter import MGRDSampleFilter, motion_primitive_get_random_samples
+        samples = motion_primitive_get_random_samples(graph_node, self.n_random_samples)
+        scores = MGRDSampleFilter.score_samples_cartesian(graph_node, samples, mp_constraints)
+        best_idx = int(np.argmin(scores))
+        mp_constraints.min_error = float(scores[best_idx])
+        mp_constraints.evaluations += len(samples)
+        return samples[best_idx]
 
     # ------------------------------------------------------------------ :220-228
     def _get_best_fit_sample_using_cluster_tree(self, graph_node, constraints, prev_frames, n_candidates=-1):

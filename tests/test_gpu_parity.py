@@ -140,6 +140,32 @@ def test_generator_api(case):
         assert abs(ref - case.constraints.min_error) <= RTOL * max(1.0, abs(ref))
 
 
+def test_mgrd_shaped_batch_slot(case):
+    """a17: the reference's batched slot (samples [N, D] -> scores [N] -> argmin,
+    motion_primitive_generator.py:167-177, mgrd_sample_filter.py:52-75) served by the engine: scores of the
+    position constraints the reference hands to mgrd (unset axes -> 0, orientation dropped)."""
+    if case.prev_frames is not None:
+        pytest.skip("local constraints only")
+    from morphablegraphs_b200 import MotionPrimitiveGenerator, MotionPrimitiveConstraints
+    from morphablegraphs_b200.mgrd_sample_filter import MGRDSampleFilter
+    from oracle import np_oracle as O
+    cart = MGRDSampleFilter.extract_cartesian_constraints(case.constraints)
+    scores = MGRDSampleFilter.score_samples_cartesian(case.node, case.samples, case.constraints)
+    assert scores.shape == (len(case.samples),)
+    if len(cart) == 0:
+        assert not scores.any()
+        return
+    mpc = MotionPrimitiveConstraints()
+    mpc.skeleton, mpc.is_local, mpc.constraints = case.skeleton, True, cart
+    ref = O.candidate_costs(case.node, case.skeleton, mpc, case.samples)
+    assert rel_err(scores, ref).max() < RTOL
+    gen = MotionPrimitiveGenerator(None, {"n_random_samples": 256, "constrained_sampling_mode": "random_spline"},
+                                   skeleton=case.skeleton, seed=3)
+    s = gen.generate_constrained_sample(case.node, case.constraints)
+    got = O.candidate_costs(case.node, case.skeleton, mpc, np.asarray(s)[None])[0]
+    assert abs(got - case.constraints.min_error) <= RTOL * max(1.0, abs(got))
+
+
 # ---------------------------------------------------------------------------
 # size-independent properties at the benchmark's full size
 # ---------------------------------------------------------------------------
