@@ -351,10 +351,21 @@ def run_b200(args):
         t = torch.tensor([e2e_t], dtype=torch.float64, device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e_t = float(t.item())
+    # plain pinned H2D copy of the same bytes: what the PCIe link of this box gives (context for e2e)
+    dst = torch.empty((n, dm.D), dtype=torch.float64, device=dev)
+    dst.copy_(host, non_blocking=True)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(3):
+        dst.copy_(host, non_blocking=True)
+    torch.cuda.synchronize()
+    h2d_gbs = 3 * n * dm.D * 8 / (time.perf_counter() - t0) * 1e-9
+    del dst
     t_clock1 = time.perf_counter()
     e2e = {"value": n * world * e2e_steps / e2e_t, "unit": UNIT, "h2d_bytes_per_step": int(n * dm.D * 8) * world,
            "d2h_bytes_per_step": 12 * world, "steps": e2e_steps, "ms_per_step": 1e3 * e2e_t / e2e_steps,
-           "call": "MotionPrimitiveGenerator.evaluate_samples_using_constraints -> mgb_score_host, float64 pinned host samples"}
+           "call": "MotionPrimitiveGenerator.evaluate_samples_using_constraints -> mgb_score_host, float64 pinned host samples",
+           "pinned_h2d_copy_gbs": h2d_gbs, "h2d_share_of_step": (n * dm.D * 8 / (h2d_gbs * 1e9)) / (e2e_t / e2e_steps)}
     if rank == 0:
         clocks.stop()
     clk = clocks.summary(t_wall0, t_clock1) if rank == 0 else None

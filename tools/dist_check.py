@@ -1,0 +1,45 @@
+#!/usr/bin/env python
+"""Under torchrun (one rank per GPU): the sharded generator step returns, on every rank, exactly the
+sample a single-GPU run of the same job returns (Philox is keyed by the global index, the per-rank
+bests are exchanged with the first-minimum rule)."""
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import numpy as np  # noqa: E402
+import torch  # noqa: E402
+import torch.distributed as dist  # noqa: E402
+import bench  # noqa: E402
+from morphablegraphs_b200 import MotionPrimitiveGenerator, engine, sharding  # noqa: E402
+
+
+def main():
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    rank, world = dist.get_rank(), dist.get_world_size()
+    node, skeleton, mpc, prev = bench.build_case("S1M")
+    n = 1_000_003
+    gen = MotionPrimitiveGenerator(None, {"n_random_samples": n}, skeleton=skeleton, seed=11)
+    s_dist = gen._get_best_fit_sample_using_gmm(node, mpc)
+    e_dist = mpc.min_error
+    # the same job on this rank alone
+    dm = engine.DeviceModel(node, skeleton, local)
+    dc = engine.DeviceConstraints(dm, mpc, prev)
+    seed = int(np.random.RandomState(11).randint(0, 2 ** 31 - 1))
+    counts = dm.component_counts(n, seed)
+    res = dc.sample_score(n, seed=seed, counts=counts, n_total=n, index_base=0, k=1)
+    idx = int(res["best_idx"][0]); e_one = float(res["best_cost"][0])
+    s_one = dm.sample(1, seed=seed, index_base=idx, counts=counts, n_total=n)[0].cpu().numpy().astype(np.float64)
+    ok = np.array_equal(s_dist, s_one) and e_dist == e_one
+    flags = [None] * world
+    dist.all_gather_object(flags, (bool(ok), e_dist, idx))
+    if rank == 0:
+        print("world", world, "per-rank (ok, min_error, single-GPU idx):", flags)
+    dist.destroy_process_group()
+    sys.exit(0 if all(f[0] for f in flags) else 1)
+
+
+if __name__ == "__main__":
+    main()
