@@ -166,7 +166,7 @@ def calibrate_cpu(pool, seconds):
     return max(pool.workers * 16, int(rate * seconds)), rate
 
 
-def run_reference(args):
+def run_reference(args, emit=print):
     """`--impl reference`: the reference's CPU path (numpy port, oracle/np_oracle.py; the reference
     itself is not installable on the GPU box: anim_utils/transformations are absent) on
     all host cores; each step = a bounded sample of the workload (sample -> score -> arg-min)."""
@@ -192,7 +192,7 @@ def run_reference(args):
            "cpu_baseline": {"value": value, "unit": UNIT, "cores": pool.workers, "kind": "port", "sample": sample},
            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
            "gpu_launches": 0}
-    print(json.dumps(out))
+    emit(json.dumps(out))
     return 0
 
 
@@ -287,11 +287,25 @@ def run_b200(args):
     S = torch.empty((n, dm.D), dtype=torch.float32, device=dev)
     gathered = torch.empty((world, 2), dtype=torch.float64, device=dev) if world > 1 else None
     state = {"seed": 0}
+    peer, exchange_kind = None, "none (1 GPU)"
+    if world > 1:
+        from morphablegraphs_b200 import sharding
+        try:
+            peer = sharding.PeerExchange(dev)
+            exchange_kind = "mgb_exchange_best: P2P stores into every peer's slot array over NVLink + in-kernel first-minimum reduction"
+        except Exception as e:                    # symmetric memory unavailable: NCCL all-gather (still a GPU path)
+            exchange_kind = "nccl all_gather of (cost, index) [peer memory unavailable: %s]" % str(e)[:120]
+        flag = torch.tensor([1.0 if peer is not None else 0.0], device=dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        if float(flag.item()) == 0.0:
+            peer = None
 
     def step():
         """one pass of the hot path over this rank's shard: fused sample + score + arg-min (-> exchange)"""
         state["seed"] += 1
         res = dc.sample_score(n, seed=state["seed"], counts=counts, n_total=n * world, index_base=rank * n, k=1, quality_scale=qs)
+        if peer is not None:
+            return peer.exchange(res["best_cost"], res["best_idx"])
         if world > 1:
             mine = torch.stack([res["best_cost"][0].double(), res["best_idx"][0].double()])
             dist.all_gather_into_tensor(gathered.view(-1), mine)
@@ -321,6 +335,8 @@ def run_b200(args):
         dist.barrier()
     t_wall1 = time.perf_counter()
     launches = engine.launch_count() - launches0
+    if peer is not None:
+        peer.check()
     total_ms = float(sum(e0.elapsed_time(e1) for e0, e1 in evs))
     if world > 1:
         t = torch.tensor([total_ms], dtype=torch.float64, device=dev)
@@ -369,7 +385,7 @@ def run_b200(args):
     if rank == 0:
         clocks.stop()
     clk = clocks.summary(t_wall0, t_clock1) if rank == 0 else None
-    return dict(torch=torch, dist=dist, dm=dm, dc=dc, lib=lib, flush=flush, S=S, counts=counts, n=n, qs=qs, rank=rank,
+    return dict(exchange=exchange_kind, torch=torch, dist=dist, dm=dm, dc=dc, lib=lib, flush=flush, S=S, counts=counts, n=n, qs=qs, rank=rank,
                 world=world, local=local, value=value, total_ms=total_ms, launches=launches, e2e=e2e, clocks=clk, w=w)
 
 
@@ -421,8 +437,16 @@ def kernel_rooflines(ctx, args):
 
 def main():
     args = parse_args()
+    # exactly ONE line on stdout: libraries (NCCL prints its version banner there) go to stderr
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+
+    def emit(line):
+        os.write(real_stdout, (line + "\n").encode())
+
     if args.impl == "reference":
-        return run_reference(args)
+        return run_reference(args, emit)
     ctx = run_b200(args)
     rank, world = ctx["rank"], ctx["world"]
     kr, hbm_peak, fp32_peak, peak_src = kernel_rooflines(ctx, args)
@@ -463,11 +487,11 @@ def main():
            "ms_per_step": ctx["total_ms"] / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
            "dtype": "f32", "data": "synthetic",
            "config": {"workload": args.workload, "description": ctx["w"]["desc"], "candidates_per_gpu_per_step": ctx["n"],
-                      "l2": "flushed (384 MB fill, untimed) before every timed step", "parallelism": "candidates sharded x%d" % world},
+                      "l2": "flushed (384 MB fill, untimed) before every timed step", "parallelism": "candidates sharded x%d" % world, "exchange": ctx["exchange"]},
            "roofline": roof, "kernels": kr, "e2e": ctx["e2e"], "gpu_launches": ctx["launches"], "clocks": ctx["clocks"]}
     if world == 1 and not args.no_cpu_baseline:
         out["cpu_baseline"] = cpu_baseline_leg(args)
-    print(json.dumps(out))
+    emit(json.dumps(out))
     if world > 1:
         ctx["dist"].destroy_process_group()
     return 0

@@ -294,6 +294,20 @@ int mgb_node_costs(const mgb_model* m, const mgb_constraints* c, const void* d_p
                    int64_t n, float error_scale, float quality_scale, float magnitude_scale,
                    float* d_cost, void* stream);
 
+/* Multi-GPU (one box): exchange of every rank's best (cost, global index) through NVLink peer memory and
+ * reduction with the first-minimum rule (lowest cost, lowest index on ties, NaN never wins;
+ * motion_primitive_generator.py:251-257 applied across ranks).  d_peer_slots: DEVICE array of `world`
+ * pointers, entry r = base of rank r's slot array (mgb_exchange_slot_bytes(world) bytes, zero-filled once,
+ * mapped into this process - e.g. torch symmetric memory or cudaIpc); the call stores this rank's record in
+ * every peer's array, waits for all peers' records of step `seq` in its own array and writes the winner to
+ * d_out_cost[1] / d_out_idx[1].  seq: 1, 2, 3, ... identical on all ranks, incremented per call.
+ * spin_limit <= 0: default (~1 s); on expiry d_err[0] = 1 + missing rank and the kernel returns.
+ * Asynchronous on `stream`; replaces a 16-byte ncclAllGather + host-side selection. */
+size_t mgb_exchange_slot_bytes(int32_t world);
+int mgb_exchange_best(const float* d_my_cost, const int64_t* d_my_idx, void* const* d_peer_slots,
+                      int32_t rank, int32_t world, uint32_t seq, int64_t spin_limit, float* d_out_cost,
+                      int64_t* d_out_idx, int32_t* d_err, void* stream);
+
 /* Diagnostic: measured fp32 FMA throughput (TFLOP/s) of `device`; the denominator of the
  * compute-bound fused score kernel's roofline in bench.py (no reference counterpart). */
 int mgb_fp32_fma_peak(int32_t device, double* tflops);

@@ -115,6 +115,8 @@ SYMBOLS = {
     "mgb_kmeans_assign_update": (C.c_int, [_vp, _i64, _i32, _i32, _vp, _vp, _i32, _vp, _vp, _vp, _vp, _vp]),
     "mgb_kmeans_level": (C.c_int, [_vp, _i64, _i32, _i32, _i32, _vp, _i32, _i32, _vp, _vp, _i32, _i32, _vp, _vp, _vp, _vp, _vp,
                                    C.POINTER(C.c_int32), _vp]),
+    "mgb_exchange_slot_bytes": (C.c_size_t, [_i32]),
+    "mgb_exchange_best": (C.c_int, [_vp, _vp, _vp, _i32, _i32, C.c_uint32, _i64, _vp, _vp, _vp, _vp]),
     "mgb_node_costs": (C.c_int, [_vp, _vp, _vp, _i32, _i64, _f, _f, _f, _vp, _vp]),
     "mgb_fp32_fma_peak": (C.c_int, [_i32, _pd]),
     "mgb_launch_count": (C.c_int64, []),

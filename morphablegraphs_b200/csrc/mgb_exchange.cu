@@ -1,0 +1,97 @@
+// Exchange of the per-GPU best (cost, global index) over NVLink peer memory.
+//
+// The reference is single-process; its arg-min is the serial loop of
+// motion_primitive_generator.py:251-257 (strict '<', first minimum wins).  With the candidates of a step
+// sharded over the GPUs of one box the only exchange of the path is every rank's best (cost, index).
+// A step at S takes ~76 us on one B200, so a library all-gather (tens of us of launch + protocol
+// latency) would halve the throughput; here every rank stores its 16-byte record straight into every
+// peer's slot array (P2P stores through NVLink / NVSwitch), then waits for the peers' records in its
+// OWN memory and reduces them - one 32-thread launch, no host round trip.
+//
+// Slot layout per rank: 2 * world records (double-buffered by the parity of the step sequence number: a
+// rank can run at most one step ahead of the slowest peer, because it needs that peer's record to finish
+// its own step).  A record is {cost, seq, idx}; payload first, fence, then seq (the flag).
+#include <math.h>
+
+#include "mgb_internal.cuh"
+
+namespace {
+
+struct __align__(16) MgbBestSlot {
+    float cost;
+    unsigned int seq;
+    long long idx;
+};
+
+__device__ __forceinline__ void st_release_sys_u32(unsigned int* p, unsigned int v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned int ld_acquire_sys_u32(const unsigned int* p) {
+    unsigned int v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+
+__global__ void __launch_bounds__(32) mgb_exchange_best_kernel(const float* __restrict__ my_cost, const long long* __restrict__ my_idx,
+                                                              void* const* __restrict__ peer_slots, int rank, int world, unsigned int seq,
+                                                              long long spin_limit, float* __restrict__ out_cost,
+                                                              long long* __restrict__ out_idx, int* __restrict__ err) {
+    const int lane = threadIdx.x;
+    const int buf = (int)(seq & 1u) * world;
+    float c = INFINITY;
+    long long i = 0x7fffffffffffffffLL;
+    bool have = false;
+    if (lane < world) {
+        // publish my record in peer `lane`'s slot array (my own included)
+        MgbBestSlot* dst = reinterpret_cast<MgbBestSlot*>(peer_slots[lane]) + buf + rank;
+        const float mc = my_cost[0];
+        const long long mi = my_idx[0];
+        *reinterpret_cast<volatile float*>(&dst->cost) = mc;
+        *reinterpret_cast<volatile long long*>(&dst->idx) = mi;
+        st_release_sys_u32(&dst->seq, seq);
+        // wait for peer `lane`'s record in MY array
+        const MgbBestSlot* src = reinterpret_cast<const MgbBestSlot*>(peer_slots[rank]) + buf + lane;
+        long long spins = 0;
+        while (ld_acquire_sys_u32(&src->seq) != seq) {
+            if (++spins > spin_limit) {
+                atomicExch(err, 1 + lane);      // which peer never arrived
+                break;
+            }
+            __nanosleep(40);
+        }
+        c = *reinterpret_cast<const volatile float*>(&src->cost);
+        i = *reinterpret_cast<const volatile long long*>(&src->idx);
+        have = (c == c);                        // NaN never wins (reference: `min_error > error`)
+    }
+    // first-minimum rule across ranks: lowest cost, lowest global index on ties
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const float oc = __shfl_xor_sync(0xffffffffu, c, o);
+        const long long oi = __shfl_xor_sync(0xffffffffu, i, o);
+        const bool oh = __shfl_xor_sync(0xffffffffu, have ? 1 : 0, o) != 0;
+        const bool take = oh && (!have || oc < c || (oc == c && oi < i));
+        if (take) { c = oc; i = oi; have = true; }
+    }
+    if (lane == 0) {
+        out_cost[0] = have ? c : INFINITY;
+        out_idx[0] = have ? i : 0;
+    }
+}
+
+}  // namespace
+
+extern "C" size_t mgb_exchange_slot_bytes(int32_t world) { return (size_t)2 * (world > 0 ? world : 1) * sizeof(MgbBestSlot); }
+
+extern "C" int mgb_exchange_best(const float* d_my_cost, const int64_t* d_my_idx, void* const* d_peer_slots, int32_t rank, int32_t world,
+                                 uint32_t seq, int64_t spin_limit, float* d_out_cost, int64_t* d_out_idx, int32_t* d_err, void* stream) {
+    MGB_REQUIRE(d_my_cost && d_my_idx && d_peer_slots && d_out_cost && d_out_idx && d_err, "null argument");
+    MGB_REQUIRE(world >= 1 && world <= 32 && rank >= 0 && rank < world, "rank / world out of range (one box: world <= 32)");
+    MGB_REQUIRE(seq != 0, "seq 0 is the cleared state of the slots; start at 1");
+    if (spin_limit <= 0) spin_limit = 20000000;       // ~1 s of 40 ns sleeps, then the error flag is raised
+    mgb_exchange_best_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(d_my_cost, reinterpret_cast<const long long*>(d_my_idx), d_peer_slots, rank,
+                                                                 world, seq, spin_limit, d_out_cost, reinterpret_cast<long long*>(d_out_idx),
+                                                                 d_err);
+    mgb_count_launch();
+    MGB_CUDA(cudaGetLastError());
+    return MGB_OK;
+}

@@ -111,10 +111,17 @@ class MotionPrimitiveGenerator(object):
         res = dc.sample_score(n_mine, seed=seed, counts=counts, n_total=n, index_base=base, k=1,
                               error_scale=getattr(obj, "error_scale", 1.0), quality_scale=getattr(obj, "quality_scale", 0.0),
                               magnitude_scale=getattr(obj, "magnitude_scale", 0.0))
-        best_idx = int(res["best_idx"][0].item())
-        min_error = float(res["best_cost"][0].item())
-        if world > 1:
-            min_error, best_idx = sharding.exchange_best(min_error, best_idx, device=dm.torch_device)
+        peer = sharding.peer_exchange(dm.torch_device) if world > 1 else None
+        if peer is not None:
+            # per-rank bests exchanged and reduced on the device over NVLink peer memory (mgb_exchange_best)
+            oc, oi = peer.exchange(res["best_cost"], res["best_idx"])
+            best_idx, min_error = int(oi.item()), float(oc.item())
+            peer.check()
+        else:
+            best_idx = int(res["best_idx"][0].item())
+            min_error = float(res["best_cost"][0].item())
+            if world > 1:
+                min_error, best_idx = sharding.exchange_best(min_error, best_idx, device=dm.torch_device)
         mp_constraints.min_error = min_error
         mp_constraints.evaluations += n
         best = dm.sample(1, seed=seed, index_base=best_idx, counts=counts, n_total=n)

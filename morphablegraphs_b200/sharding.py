@@ -58,3 +58,81 @@ def exchange_best(cost, index, device=None, group=None):
     dist.all_gather_into_tensor(gathered.view(-1), mine, group=group)
     g = gathered.cpu().numpy()
     return select_best(g[:, 0], g[:, 1].astype(np.int64))
+
+
+class PeerExchange(object):
+    """The same exchange without a library collective on the step's critical path: every rank stores its
+    16-byte record into every peer's slot array through NVLink peer memory and reduces the records that
+    arrive in its own (csrc/mgb_exchange.cu, `mgb_exchange_best`) - one 32-thread launch per step, results
+    stay on the device.  Peer pointers come from torch's symmetric-memory allocator (CUDA VMM handles
+    exchanged through the process group's store); construction is collective.  Raises if symmetric memory
+    is not available - callers then stay on `exchange_best` (NCCL), which is still a GPU path."""
+
+    def __init__(self, device, group=None, slots=None, peer_ptrs=None, rank=None, world=None):
+        import ctypes as C
+        import torch
+        from . import _lib
+        self._C, self.torch, self.lib = C, torch, _lib.load()
+        self.device = torch.device(device)
+        if peer_ptrs is None:
+            import torch.distributed as dist
+            import torch.distributed._symmetric_memory as symm
+            self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
+            nbytes = int(self.lib.mgb_exchange_slot_bytes(self.world))
+            self.slots = symm.empty(nbytes // 4, dtype=torch.int32, device=self.device)
+            self.slots.zero_()
+            g = group if group is not None else dist.group.WORLD
+            self.handle = symm.rendezvous(self.slots, g.group_name if hasattr(g, "group_name") else g)
+            peer_ptrs = [int(p) for p in self.handle.buffer_ptrs]
+            torch.cuda.synchronize(self.device)
+            dist.barrier(group)                      # every rank's slots are zeroed before anyone publishes
+        else:                                        # tests: several "ranks" inside one process
+            self.rank, self.world, self.slots, self.handle = int(rank), int(world), slots, None
+        self.peer_ptrs = torch.tensor(peer_ptrs, dtype=torch.int64, device=self.device)
+        self.out_cost = torch.empty(1, dtype=torch.float32, device=self.device)
+        self.out_idx = torch.empty(1, dtype=torch.int64, device=self.device)
+        self.err = torch.zeros(1, dtype=torch.int32, device=self.device)
+        self.seq = 0
+
+    def exchange(self, best_cost, best_idx, spin_limit=0):
+        """best_cost float32[>=1], best_idx int64[>=1] device tensors of this rank -> (out_cost[1], out_idx[1])
+        device tensors holding the job-wide winner; asynchronous on the current stream."""
+        C, torch = self._C, self.torch
+        from . import _lib
+        self.seq += 1
+        if self.seq >= 2 ** 32:
+            self.seq = 1
+        p = lambda t: C.c_void_p(t.data_ptr())
+        with torch.cuda.device(self.device):
+            _lib.check(self.lib.mgb_exchange_best(p(best_cost), p(best_idx), p(self.peer_ptrs), self.rank, self.world,
+                                                  C.c_uint32(self.seq), C.c_int64(int(spin_limit)), p(self.out_cost), p(self.out_idx),
+                                                  p(self.err), C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)))
+        return self.out_cost, self.out_idx
+
+    def check(self):
+        """Synchronising: raises if a peer's record never arrived."""
+        e = int(self.err.item())
+        if e:
+            from ._lib import MgbError
+            raise MgbError("peer exchange timed out waiting for rank %d" % (e - 1))
+
+
+_PEERS = {}
+
+
+def peer_exchange(device):
+    """Process-wide PeerExchange of `device` (created collectively on first use by every rank at the same
+    point of the program), or None when peer memory cannot be set up on ANY rank - then every rank uses
+    the NCCL all-gather."""
+    import torch
+    import torch.distributed as dist
+    key = str(device)
+    if key not in _PEERS:
+        try:
+            p = PeerExchange(device)
+        except Exception:
+            p = None
+        flag = torch.tensor([1.0 if p is not None else 0.0], device=device)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        _PEERS[key] = p if float(flag.item()) == 1.0 else None
+    return _PEERS[key]

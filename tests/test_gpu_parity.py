@@ -353,3 +353,49 @@ def test_large_fused_sample_score(large):
             assert rel_err(cb, ca).max() < 2e-5
             ia, ib = int(a["best_idx"][0]), int(b["best_idx"][0])
             assert ia == ib or abs(float(ca[ia - base]) - float(ca[ib - base])) < 2e-5 * max(1.0, abs(float(ca[ia - base])))
+
+
+def test_peer_exchange_kernel_single_process():
+    """mgb_exchange_best with several 'ranks' inside one process: one slot array per rank on the same GPU,
+    one stream per rank (the kernels wait for each other's records, so they must be co-resident: 1 CTA of
+    32 threads each).  Winner = lowest cost, lowest global index on ties, NaN never wins; repeated steps
+    exercise the parity double-buffering."""
+    import ctypes as C
+    from morphablegraphs_b200 import _lib, sharding
+    lib = _lib.load()
+    dev = torch.device("cuda", 0)
+    for world in (1, 2, 4, 8):
+        nbytes = int(lib.mgb_exchange_slot_bytes(world))
+        slots = [torch.zeros(nbytes // 4, dtype=torch.int32, device=dev) for _ in range(world)]
+        ptrs = [int(t.data_ptr()) for t in slots]
+        ranks = [sharding.PeerExchange(dev, slots=slots[r], peer_ptrs=ptrs, rank=r, world=world) for r in range(world)]
+        streams = [torch.cuda.Stream(dev) for _ in range(world)]
+        rng = np.random.RandomState(world)
+        for step in range(6):
+            costs = rng.randint(0, 3, size=world).astype(np.float32)
+            if step == 2:
+                costs[:] = 1.5                              # all tie -> lowest index
+            if step == 3 and world > 1:
+                costs[0] = np.nan                           # NaN never wins
+            if step == 4:
+                costs[:] = np.nan                           # nothing finite -> (inf, 0)
+            idx = (rng.permutation(world) * 1000 + 2 ** 40).astype(np.int64)
+            cs = [torch.tensor([costs[r]], dtype=torch.float32, device=dev) for r in range(world)]
+            ix = [torch.tensor([idx[r]], dtype=torch.int64, device=dev) for r in range(world)]
+            torch.cuda.synchronize()
+            outs = []
+            for r in range(world):
+                with torch.cuda.stream(streams[r]):
+                    outs.append(ranks[r].exchange(cs[r], ix[r], spin_limit=2_000_000))
+            torch.cuda.synchronize()
+            want_c, want_i = sharding.select_best(costs, idx)
+            for r in range(world):
+                ranks[r].check()
+                oc, oi = float(outs[r][0].item()), int(outs[r][1].item())
+                assert (oc == want_c or (np.isinf(oc) and np.isinf(want_c))) and oi == want_i, (world, step, r, oc, oi, want_c, want_i)
+    # a peer that never shows up raises instead of hanging
+    slots = [torch.zeros(int(lib.mgb_exchange_slot_bytes(2)) // 4, dtype=torch.int32, device=dev) for _ in range(2)]
+    lone = sharding.PeerExchange(dev, slots=slots[0], peer_ptrs=[int(t.data_ptr()) for t in slots], rank=0, world=2)
+    lone.exchange(torch.zeros(1, device=dev), torch.zeros(1, dtype=torch.int64, device=dev), spin_limit=1000)
+    with pytest.raises(_lib.MgbError):
+        lone.check()

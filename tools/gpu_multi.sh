@@ -3,6 +3,7 @@
 tag=${1:-rXX}; N=${2:-2}
 out=gpurun_out; mkdir -p $out
 nvidia-smi -L > $out/${tag}_smi.txt
+timeout 300 python -m pytest tests/test_gpu_parity.py -m gpu -q -x -k "peer_exchange or mgrd" > $out/${tag}_pytest_peer.log 2>&1; echo "pytest peer rc=$?"; tail -4 $out/${tag}_pytest_peer.log
 for n in 1 $N; do
   if [ $n -eq 1 ]; then L="python"; else L="python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port 29511"; fi
   timeout 600 $L bench.py --gpus $n --steps 20 --warmup 5 > $out/${tag}_bench_S1M_n$n.json 2> $out/${tag}_bench_S1M_n$n.err; echo "S1M n=$n rc=$?"
