@@ -15,6 +15,7 @@
 // run of equal node ids), keeping the running sums of its current node in registers and flushing
 // them with one vector RED per (node, cluster) when the node changes.  Member counts come from
 // ballots, the inertia from a warp reduction at flush time.
+#include <cuda_pipeline.h>
 #include <math.h>
 
 #include "mgb_internal.cuh"
@@ -91,13 +92,25 @@ __global__ void __launch_bounds__(KM_WARPS * 32) mgb_kmeans_level_kernel(
         inertia_part = 0.f;
     };
 
-    for (long long t0 = first; t0 < last; t0 += 32) {
+    // double-buffered tiles: the next tile's rows are in flight (cp.async) while this one is processed
+    float* tiles[2] = {tile, tile + (size_t)KM_WARPS * 32 * ld};
+    auto fetch = [&](long long t0, float* dst) {
+        if (t0 < last) {
+            const int rows = (int)((last - t0 < 32) ? (last - t0) : 32);
+            const float* src = x + (size_t)t0 * ld;
+            const int total = rows * ld;
+            for (int e = lane; e < total; e += 32) __pipeline_memcpy_async(dst + e, src + e, sizeof(float));
+        }
+        __pipeline_commit();
+    };
+    fetch(first, tiles[0]);
+    int pb = 0;
+    for (long long t0 = first; t0 < last; t0 += 32, pb ^= 1) {
         const int rows = (int)((last - t0 < 32) ? (last - t0) : 32);
-        // coalesced copy of rows x ld floats into the warp's tile
-        const float* src = x + (size_t)t0 * ld;
-        const int total = rows * ld;
-        for (int e = lane; e < total; e += 32) tile[e] = __ldcs(src + e);
+        fetch(t0 + 32, tiles[pb ^ 1]);
+        __pipeline_wait_prior(1);
         __syncwarp();
+        tile = tiles[pb];
         // E-step: lane = sample
         int nd = -1, lb = 0;
         float best = 0.f;
@@ -183,8 +196,8 @@ template <int NS, int CH>
 int launch_level(const float* d_x, int64_t n, int dim, int dim_acc, int ld, const int* d_node, const float* d_cent, int n_sub,
                  int* d_label, float* d_sums, int* d_counts, float* d_node_inertia, float* d_inertia, cudaStream_t stream) {
     auto kern = mgb_kmeans_level_kernel<NS, CH>;
-    const size_t smem = (size_t)KM_WARPS * 32 * ld * sizeof(float);
-    MGB_REQUIRE(smem <= 200 * 1024, "row stride too large for the k-means kernel (ld <= 400)");
+    const size_t smem = (size_t)2 * KM_WARPS * 32 * ld * sizeof(float);
+    MGB_REQUIRE(smem <= 200 * 1024, "row stride too large for the k-means kernel (ld <= 200)");
     if (smem > 48 * 1024) MGB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const long long tiles = (n + 31) / 32;
     int occ = 1;

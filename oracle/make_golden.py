@@ -187,6 +187,56 @@ def run_case(ns, shape, which, n_samples, seed, translation_maxima=(1.0, 1.0, 1.
     return out, (node, skeleton, mpc, S, prev_frames)
 
 
+def run_walk_case(ns, n_steps=6, n_samples=48, seed=31):
+    """BASELINE config 3 in miniature: a walk over several primitives (one S-shaped model per graph
+    node, its own model seed), every step picked by the reference's own
+    `evaluate_samples_using_constraints` loop on the non-local path (candidates aligned to the previous
+    step's last frames, motion_primitive_constraints.py:110-115), the chosen motion aligned and appended
+    like graph_walk.py does.  Stores per step what the engine needs to replay the decision."""
+    from anim_utils.animation_data.motion_concatenation import align_quaternion_frames
+    shape = "S"
+    cfg = syn.SHAPES[shape]
+    F = cfg["n_frames"]
+    skeleton = refload.make_skeleton(syn.make_skeleton_desc(cfg["n_joints"]))
+    names = ["walk_beginLeftStance", "walk_rightStance", "walk_leftStance", "walk_endRightStance"]
+    seeds = [syn.SEED_MODEL + 17 * k for k in range(len(names))]
+    nodes = [refload.make_graph_node(ns, syn.make_model_json(shape, seed=sd, name=nm), name=nm) for nm, sd in zip(names, seeds)]
+    order = [0, 1, 2, 1, 2, 3][:n_steps]
+    np.random.seed(seed)
+    rng = np.random.RandomState(syn.SEED_CONSTRAINTS)
+    obj = ns.objective_functions.obj_spatial_error_sum
+    out = {"node_names_json": np.array(json.dumps(names)), "model_seeds": np.array(seeds), "order": np.array(order)}
+    prev_frames = None
+    for step, k in enumerate(order):
+        node = nodes[k]
+        specs = make_specs(ns, node, skeleton, F, rng, "config1" if step % 2 == 0 else "mixed")
+        if prev_frames is not None:
+            # the transition term compares with the end of the previous step (pose_constraint.py:48-67)
+            specs = [sp_ for sp_ in specs if sp_["class"] != "PoseConstraint"]
+        S = node.sample_low_dimensional_vectors(n_samples)
+        mpc = build_mp_constraints(ns, skeleton, specs, is_local=prev_frames is None)
+        gen = ns.motion_primitive_generator.MotionPrimitiveGenerator.__new__(ns.motion_primitive_generator.MotionPrimitiveGenerator)
+        gen.objective = obj
+        with _quiet():
+            costs = np.array([obj(s_, (node, mpc, prev_frames)) for s_ in S])
+            best, min_error = gen.evaluate_samples_using_constraints(S, node, mpc, prev_frames)
+        spline = node.back_project(best, use_time_parameters=False)
+        if prev_frames is not None:
+            spline.coeffs = align_quaternion_frames(skeleton, skeleton.aligning_root_node, spline.coeffs, prev_frames, None)
+        with _quiet():
+            frames = np.asarray(spline.get_motion_vector())
+        out["step%d_samples" % step] = S
+        out["step%d_specs_json" % step] = np.array(json.dumps(specs))
+        out["step%d_costs" % step] = costs
+        out["step%d_best_idx" % step] = np.array(int(np.where((S == best).all(axis=1))[0][0]))
+        out["step%d_min_error" % step] = np.array(min_error)
+        if prev_frames is not None:
+            out["step%d_prev_frames" % step] = np.asarray(prev_frames)
+        out["step%d_last_frames" % step] = frames[-3:]
+        prev_frames = frames[-3:]
+    return out
+
+
 def run_tree_case(ns, n_data=400, n_candidates_list=(1, 2, 5), seed=11):
     """ClusterTree (k-means + kd leaves) and FeatureClusterTree built by the
     reference (KMeans seeded through numpy's global state) and searched with
@@ -316,6 +366,12 @@ def serialize_feature_tree(node):
 def main():
     ns = refload.load()
     os.makedirs(GOLDEN_DIR, exist_ok=True)
+    if "--only-walk" in sys.argv:
+        out = run_walk_case(ns)
+        np.savez_compressed(os.path.join(GOLDEN_DIR, "s_walk.npz"), **out)
+        print("s_walk", [int(out["step%d_best_idx" % i]) for i in range(len(out["order"]))],
+              [float(out["step%d_min_error" % i]) for i in range(len(out["order"]))])
+        return 0
     if "--only-tree" in sys.argv:
         out = run_tree_case(ns)
         np.savez_compressed(os.path.join(GOLDEN_DIR, "s_tree.npz"), **out)

@@ -399,3 +399,20 @@ def test_peer_exchange_kernel_single_process():
     lone.exchange(torch.zeros(1, device=dev), torch.zeros(1, dtype=torch.int64, device=dev), spin_limit=1000)
     with pytest.raises(_lib.MgbError):
         lone.check()
+
+
+def test_walk_sequence_matches_reference_decisions():
+    """Config 3 in miniature: a six-step walk over four primitives whose every decision was taken by the
+    reference's generator loop (tests/golden/s_walk.npz); the engine, given the same samples, constraints
+    and previous frames, must choose the same candidate at every step."""
+    from morphablegraphs_b200 import MotionPrimitiveGenerator
+    from tests.walk_common import WalkCase
+    w = WalkCase()
+    gen = MotionPrimitiveGenerator(None, {"n_random_samples": 64}, skeleton=w.skeleton, seed=1)
+    for i in range(len(w.order)):
+        st = w.step(i)
+        best, min_error = gen.evaluate_samples_using_constraints(st["samples"], st["node"], st["constraints"], st["prev_frames"])
+        idx = int(np.where((st["samples"] == best).all(axis=1))[0][0])
+        _check_argmin(st["costs"], idx, min_error)
+        assert idx == st["best_idx"], "step %d" % i
+        assert abs(min_error - st["min_error"]) <= RTOL * max(1.0, abs(st["min_error"]))
