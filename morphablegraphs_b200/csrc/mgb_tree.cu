@@ -93,7 +93,8 @@ __global__ void __launch_bounds__(KM_WARPS * 32) mgb_kmeans_level_kernel(
     };
 
     // double-buffered tiles: the next tile's rows are in flight (cp.async) while this one is processed
-    float* tiles[2] = {tile, tile + (size_t)KM_WARPS * 32 * ld};
+    float* const tile0 = tile;
+    const size_t tstride = (size_t)KM_WARPS * 32 * ld;
     auto fetch = [&](long long t0, float* dst) {
         if (t0 < last) {
             const int rows = (int)((last - t0 < 32) ? (last - t0) : 32);
@@ -103,31 +104,43 @@ __global__ void __launch_bounds__(KM_WARPS * 32) mgb_kmeans_level_kernel(
         }
         __pipeline_commit();
     };
-    fetch(first, tiles[0]);
+    fetch(first, tile0);
+    int nd_next = (first + lane < last) ? (node ? __ldg(node + first + lane) : 0) : -1;
     int pb = 0;
     for (long long t0 = first; t0 < last; t0 += 32, pb ^= 1) {
         const int rows = (int)((last - t0 < 32) ? (last - t0) : 32);
-        fetch(t0 + 32, tiles[pb ^ 1]);
+        fetch(t0 + 32, tile0 + (pb ? 0 : tstride));
         __pipeline_wait_prior(1);
         __syncwarp();
-        tile = tiles[pb];
-        // E-step: lane = sample
+        tile = tile0 + (pb ? tstride : 0);
+        // E-step: lane = sample; the NS distances advance together so that NS independent centroid loads are
+        // in flight per column.  The node id of the NEXT tile is fetched now and used one iteration later.
         int nd = -1, lb = 0;
         float best = 0.f;
+        const int nd_cur = nd_next;
+        if (t0 + 32 + lane < last) nd_next = node ? __ldg(node + t0 + 32 + lane) : 0;
         if (lane < rows) {
-            nd = node ? __ldg(node + t0 + lane) : 0;
+            nd = nd_cur;
             const float* xi = tile + lane * ld;
             const float* cb = cent + (size_t)nd * n_sub * dim;
-            best = INFINITY;
-            for (int k = 0; k < n_sub; ++k) {
-                const float* ck = cb + (size_t)k * dim;
-                float d = 0.f;
-                for (int j = 0; j < dim; ++j) {
-                    const float e = xi[j] - __ldg(ck + j);
-                    d = fmaf(e, e, d);
+            float d[NS];
+#pragma unroll
+            for (int k = 0; k < NS; ++k) d[k] = 0.f;
+#pragma unroll 2
+            for (int j = 0; j < dim; ++j) {
+                const float xv = xi[j];
+#pragma unroll
+                for (int k = 0; k < NS; ++k) {
+                    if (k < n_sub) {
+                        const float e = xv - __ldg(cb + k * dim + j);
+                        d[k] = fmaf(e, e, d[k]);
+                    }
                 }
-                if (d < best) { best = d; lb = k; }
             }
+            best = INFINITY;
+#pragma unroll
+            for (int k = 0; k < NS; ++k)
+                if (k < n_sub && d[k] < best) { best = d[k]; lb = k; }
             label[t0 + lane] = lb;
         }
         // M-step sums, one run of equal node ids at a time (the samples are sorted by node)
