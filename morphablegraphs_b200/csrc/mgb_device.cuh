@@ -27,10 +27,18 @@ __device__ __forceinline__ float mgb_u01(unsigned int x) {  // (0, 1]
     return fmaf((float)(x >> 8), 1.0f / 16777216.0f, 0.5f / 16777216.0f);
 }
 
+__device__ __forceinline__ float mgb_sqrt_approx(float x) {
+    float y;
+    asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+
 // four standard normals of global index gi, block b (Box-Muller on one Philox call)
 __device__ __forceinline__ void mgb_normal4(unsigned long long gi, unsigned int b, uint2 key, float z[4]) {
     const uint4 r = mgb_philox4x32_10(make_uint4((unsigned int)gi, (unsigned int)(gi >> 32), b, 0x6d67u), key);
-    const float r0 = sqrtf(-2.f * __logf(mgb_u01(r.x))), r1 = sqrtf(-2.f * __logf(mgb_u01(r.z)));
+    // radius: sqrt.approx (one MUFU, <= 2 ulp) instead of the IEEE sqrtf sequence - the draw is a random
+    // number, and both users of this function (mgb_sample, the fused kernels) share it bit for bit
+    const float r0 = mgb_sqrt_approx(-2.f * __logf(mgb_u01(r.x))), r1 = mgb_sqrt_approx(-2.f * __logf(mgb_u01(r.z)));
     float s0, c0, s1, c1;
     __sincosf(6.283185307179586f * mgb_u01(r.y), &s0, &c0);
     __sincosf(6.283185307179586f * mgb_u01(r.w), &s1, &c1);

@@ -174,6 +174,7 @@ __global__ void __launch_bounds__(MGB_BLOCK) mgb_score_kernel(const __grid_const
         mgb_tma_load_1d(sm_tile, s_glob + (size_t)blockIdx.x * TILE * D, (unsigned int)tile_bytes, &sm_bar[0]);
 
     int it = 0;
+    int g_hint = 0;
     for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
         const long long base = tile * TILE;
         const int buf = (p.nbuf == 2) ? (it & 1) : 0;
@@ -217,8 +218,10 @@ __global__ void __launch_bounds__(MGB_BLOCK) mgb_score_kernel(const __grid_const
             myrow[c] = reinterpret_cast<float*>(sm_tile) + (size_t)r * SROW;
             if (MODE == MODE_SAMPLE) {
                 const unsigned long long gi = (unsigned long long)(p.index_base + idx[c]);
-                int g = 0;
-                while (g + 1 < p.G && (long long)gi >= p.prefix.v[g + 1]) ++g;
+                // mixture component of the global index (samples are stacked in component order): the search
+                // resumes from the component of the thread's previous candidate - indices only grow
+                while (g_hint + 1 < p.G && (long long)gi >= p.prefix.v[g_hint + 1]) ++g_hint;
+                const int g = g_hint;
                 const uint2 key = make_uint2((unsigned int)p.seed, (unsigned int)(p.seed >> 32));
                 if (NREG > 0) {
                     mgb_sample_row_reg<NR>(reinterpret_cast<const float4*>(chol + (size_t)g * D * p.LS), p.LS, mus + (size_t)g * D, D, gi, key, s[c]);
