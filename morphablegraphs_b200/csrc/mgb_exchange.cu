@@ -38,6 +38,10 @@ __global__ void __launch_bounds__(32) mgb_exchange_best_kernel(const float* __re
                                                               long long* __restrict__ out_idx, int* __restrict__ err) {
     const int lane = threadIdx.x;
     const int buf = (int)(seq & 1u) * world;
+    // launched with programmatic stream serialization: this grid may be resident before the score kernel
+    // in front of it has drained; everything above this line overlaps its tail, the wait below orders the
+    // read of my_cost / my_idx after its completion
+    asm volatile("griddepcontrol.wait;" ::: "memory");
     float c = INFINITY;
     long long i = 0x7fffffffffffffffLL;
     bool have = false;
@@ -88,9 +92,19 @@ extern "C" int mgb_exchange_best(const float* d_my_cost, const int64_t* d_my_idx
     MGB_REQUIRE(world >= 1 && world <= 32 && rank >= 0 && rank < world, "rank / world out of range (one box: world <= 32)");
     MGB_REQUIRE(seq != 0, "seq 0 is the cleared state of the slots; start at 1");
     if (spin_limit <= 0) spin_limit = 20000000;       // ~1 s of 40 ns sleeps, then the error flag is raised
-    mgb_exchange_best_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(d_my_cost, reinterpret_cast<const long long*>(d_my_idx), d_peer_slots, rank,
-                                                                 world, seq, spin_limit, d_out_cost, reinterpret_cast<long long*>(d_out_idx),
-                                                                 d_err);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(1);
+    cfg.blockDim = dim3(32);
+    cfg.dynamicSmemBytes = 0;
+    cfg.stream = (cudaStream_t)stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    MGB_CUDA(cudaLaunchKernelEx(&cfg, mgb_exchange_best_kernel, d_my_cost, reinterpret_cast<const long long*>(d_my_idx), d_peer_slots, (int)rank,
+                                (int)world, (unsigned int)seq, (long long)spin_limit, d_out_cost, reinterpret_cast<long long*>(d_out_idx),
+                                (int*)d_err));
     mgb_count_launch();
     MGB_CUDA(cudaGetLastError());
     return MGB_OK;
