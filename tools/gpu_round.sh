@@ -5,6 +5,7 @@ tag=${1:-rXX}
 out=gpurun_out
 mkdir -p $out
 nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm --format=csv > $out/${tag}_smi.txt 2>&1
+timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > $out/${tag}_smoke.log 2>&1; echo "smoke rc=$?"; tail -1 $out/${tag}_smoke.log
 timeout 900 python -m pytest tests -m gpu -x -q > $out/${tag}_pytest.log 2>&1; echo "pytest rc=$?" | tee -a $out/${tag}_pytest.log
 tail -3 $out/${tag}_pytest.log
 timeout 600 python bench.py --steps 20 --warmup 5 > $out/${tag}_bench_S1M.json 2> $out/${tag}_bench_S1M.err; echo "bench S1M rc=$?"
