@@ -266,3 +266,37 @@ def test_feature_tree_on_euclidean_features_full_chain(tc):
     assert len(hit) == 1
     cost = dc.score(S, k=1, return_cost=True)["cost"].cpu().numpy()
     assert abs(cost[hit[0]] - v) <= RTOL * max(1.0, abs(v))
+
+
+@pytest.mark.parametrize("n,max_level", [(1, 3), (3, 3), (5, 1), (37, 2), (1000, 3)])
+def test_device_build_edge_sizes(n, max_level):
+    """Tiny / ragged sets and duplicated rows through the real K7 path against the oracle's recursion."""
+    from morphablegraphs_b200 import space_partitioning as sp
+    rng = np.random.RandomState(n)
+    data = rng.randn(n, 6).astype(np.float32).astype(np.float64)
+    if n >= 37:
+        data[5:17] = data[5]
+    dim = 4
+    seeds = lambda depth, gids, starts, counts, x: _injected(depth, gids, starts, counts, x, dim)
+    tree = sp.ClusterTree(4, max_level, dim).construct(data, seeds=seeds)
+    ref = O.build_cluster_tree_dict(data, 4, max_level, dim)
+    _same_cluster_tree(_flat_to_dict(tree.flat), ref, tol=5e-5)
+
+
+def test_kmeans_level_empty_and_frozen():
+    engine = _engine()
+    x = torch.zeros((0, 5), dtype=torch.float32, device="cuda")
+    cent = torch.zeros((1, 4, 3), dtype=torch.float32, device="cuda")
+    r = engine.kmeans_level(x, 3, None, 1, 4, cent, dim_acc=5)
+    assert r["label"].numel() == 0 and r["iters"] == 0
+    # a frozen node keeps its centroids; the others move
+    rng = np.random.RandomState(0)
+    X = torch.as_tensor(rng.randn(2000, 4).astype(np.float32), device="cuda")
+    node = torch.repeat_interleave(torch.arange(2, dtype=torch.int32, device="cuda"), 1000)
+    seeds = torch.as_tensor(rng.randn(2, 4, 4).astype(np.float32), device="cuda").contiguous()
+    cent = seeds.clone()
+    frozen = torch.tensor([1, 0], dtype=torch.int32, device="cuda")
+    tol = torch.zeros(2, dtype=torch.float32, device="cuda")
+    r = engine.kmeans_level(X, 4, node, 2, 4, cent, tol=tol, max_iter=20, frozen=frozen)
+    assert torch.equal(cent[0], seeds[0]) and not torch.equal(cent[1], seeds[1])
+    assert int(r["counts"].sum()) == 2000

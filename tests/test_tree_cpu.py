@@ -259,3 +259,64 @@ def test_oracle_euclidean_pca_features_match_reference(tc):
     assert f.shape == g["euclid_features"].shape
     assert np.abs(ratio - g["euclid_explained_variance_ratio"]).max() < 1e-12
     assert np.abs(np.abs(f) - np.abs(g["euclid_features"])).max() < 1e-8
+
+
+@pytest.mark.parametrize("n,max_level", [(1, 3), (3, 3), (4, 3), (5, 1), (37, 2), (200, 4)])
+def test_level_synchronous_build_edge_sizes(monkeypatch, n, max_level):
+    """Tiny and ragged sample sets, duplicated rows (k-means cannot split them: one child keeps every member
+    until max_level), root-is-a-leaf: the level-synchronous build against the oracle's recursion."""
+    monkeypatch.setattr(sp, "_lloyd_level", _oracle_lloyd_level)
+    rng = np.random.RandomState(n)
+    data = rng.randn(n, 6)
+    if n >= 37:
+        data[5:17] = data[5]                 # a dozen identical samples
+    dim = 4
+    seeds = lambda depth, gids, starts, counts, x: _injected(depth, gids, starts, counts, x, dim)
+    flat, info = sp.build_cluster_tree(data, 4, max_level, dim, seeds=seeds, device="cpu")
+    # float32 rows on the product side: build the oracle tree from the same rounded data
+    ref = O.build_cluster_tree_dict(data.astype(np.float32).astype(np.float64), 4, max_level, dim)
+    got = _flat_to_dict(flat)
+
+    def strip(d):        # kd points are rows of the float64 data on the product side: compare in float32
+        if "kdtree" in d:
+            def k(x):
+                return None if x is None else {"point": np.float32(x["point"]).tolist(), "type": x["type"], "left": k(x["left"]), "right": k(x["right"])}
+            return {"kdtree": k(d["kdtree"])}
+        return {"mean": d["mean"], "leaf": d["leaf"], "children": [strip(c) for c in d["children"]]}
+    _same_cluster_tree(strip(got), strip(ref), tol=2e-5)
+    assert info["n_kd_nodes"] == n
+
+
+def test_feature_tree_edge_sizes(monkeypatch):
+    monkeypatch.setattr(sp, "_lloyd_level", _oracle_lloyd_level)
+    for n in (1, 2, 4, 5, 23):
+        rng = np.random.RandomState(100 + n)
+        data = rng.randn(n, 5)
+        feats = data[:, :3].copy()
+        if n == 23:
+            feats[3:9] = feats[3]            # identical feature rows: one cluster swallows them -> single-sample children
+        seeds = lambda depth, gids, starts, counts, x: _injected(depth, gids, starts, counts, x, 3)
+        (points, node_row, child_ptr, child_idx, node_sample), info = sp.build_feature_tree(feats, data, 4, seeds=seeds, device="cpu")
+        leaves = np.where(np.diff(child_ptr) == 0)[0]
+        assert np.array_equal(np.sort(node_sample[leaves]), np.arange(n))        # every sample is exactly one leaf
+        ref = sp.FeatureClusterTree.from_dict(O.build_feature_tree_dict(feats.astype(np.float32).astype(np.float64),
+                                                                        data.astype(np.float32).astype(np.float64), 4), data)
+
+        def walk(a, b):
+            assert np.allclose(points[node_row[a]], ref.points[ref.node_row[b]], rtol=0, atol=2e-5)
+            ca, cb = child_idx[child_ptr[a]:child_ptr[a + 1]], ref._children(b)
+            assert len(ca) == len(cb), (n, a, b)
+            for x, y in zip(ca, cb):
+                walk(int(x), int(y))
+        walk(0, 0)
+
+
+def test_unsupported_tree_options_are_loud():
+    from morphablegraphs_b200 import engine
+    with pytest.raises(engine.MgbError):
+        sp.build_cluster_tree(np.zeros((10, 3)), 4, 2, 3, use_kd_tree=False, device="cpu")
+    with pytest.raises(engine.MgbError):
+        sp.FeatureClusterTree(np.zeros((10, 3)), np.zeros((10, 3)), None, {"n_subdivisions": 4, "use_feature_mean": True}, [], device="cpu")
+    if not torch.cuda.is_available():
+        with pytest.raises(engine.MgbError):          # no CPU fallback for the build itself
+            sp.ClusterTree(4, 2, 3).construct(np.zeros((10, 3)))
