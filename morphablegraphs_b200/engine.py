@@ -580,10 +580,11 @@ def kmeans_level(x, dim, node, n_nodes, n_sub, centroids, tol=None, max_iter=300
     assert centroids.dtype == torch.float32 and centroids.is_contiguous() and tuple(centroids.shape) == (n_nodes, n_sub, dim)
     if node is not None:
         assert node.dtype == torch.int32 and node.is_contiguous() and node.shape[0] == n
+    alloc = torch.zeros if n == 0 else torch.empty          # the library returns early on an empty sample set
     label = torch.empty((n,), dtype=torch.int32, device=dev)
-    sums = torch.empty((n_nodes, n_sub, dim_acc), dtype=torch.float32, device=dev)
-    counts = torch.empty((n_nodes, n_sub), dtype=torch.int32, device=dev)
-    inertia = torch.empty((n_nodes,), dtype=torch.float32, device=dev)
+    sums = alloc((n_nodes, n_sub, dim_acc), dtype=torch.float32, device=dev)
+    counts = alloc((n_nodes, n_sub), dtype=torch.int32, device=dev)
+    inertia = alloc((n_nodes,), dtype=torch.float32, device=dev)
     converged = torch.zeros((n_nodes,), dtype=torch.int32, device=dev) if frozen is None else frozen.to(torch.int32).contiguous()
     if tol is not None:
         assert tol.dtype == torch.float32 and tol.is_contiguous() and tol.shape[0] == n_nodes

@@ -45,20 +45,30 @@ def map_samples_to_euclidean_space(dmodel, samples, joint_names=END_EFFECTORS2, 
     return out
 
 
-def pca_by_variance(X, variance=0.95):
+def pca_by_variance(X, variance=0.95, sharded=False, group=None):
     """PCA(n_components=variance).fit_transform on the device: X [M, d] float32 -> (features [M, k] float32,
     explained-variance ratios [k] float64).  Covariance accumulated in float64 from fp32 chunk products,
-    symmetric eigen-decomposition in float64."""
+    symmetric eigen-decomposition in float64.  sharded=True: X holds this rank's rows only; the row count,
+    the column sums and the d x d covariance are all-reduced, every rank gets the
+    same basis and projects its own rows."""
     torch = engine._torch()
     M, d = int(X.shape[0]), int(X.shape[1])
-    mean = X.double().mean(dim=0)
+    total = torch.tensor([float(M)], dtype=torch.float64, device=X.device)
+    colsum = X.double().sum(dim=0)
+    if sharded:
+        import torch.distributed as dist
+        dist.all_reduce(total, group=group)
+        dist.all_reduce(colsum, group=group)
+    mean = colsum / total
     cov = torch.zeros((d, d), dtype=torch.float64, device=X.device)
     step = 131072
     mean32 = mean.float()
     for a in range(0, M, step):
         Xc = X[a:a + step] - mean32
         cov += (Xc.t() @ Xc).double()
-    cov /= max(M - 1, 1)
+    if sharded:
+        dist.all_reduce(cov, group=group)
+    cov /= max(float(total.item()) - 1.0, 1.0)
     ev, V = torch.linalg.eigh(cov)
     ev, V = ev.flip(0).clamp(min=0), V.flip(1)
     ratio = ev / ev.sum()

@@ -162,6 +162,22 @@ class _PointCosts(object):
         pts = self.owner.points
         if hasattr(self.obj, "batch_device"):
             dev_pts = self.owner.device_points(self.obj, self.data)
+            from . import sharding
+            if sharding.is_distributed() and getattr(self.owner, "shard_search", False):
+                # K8 sharded by point id: every rank scores its slice, the slices are all-gathered
+                import torch.distributed as dist
+                rank, world = dist.get_rank(), dist.get_world_size()
+                torch = engine._torch()
+                M = int(dev_pts.shape[0])
+                per = (M + world - 1) // world
+                lo, hi = min(M, rank * per), min(M, (rank + 1) * per)
+                mine = torch.zeros(per, dtype=torch.float32, device=dev_pts.device)
+                if hi > lo:
+                    mine[:hi - lo] = self.obj.batch_device(dev_pts[lo:hi].contiguous(), self.data)
+                full = torch.empty(per * world, dtype=torch.float32, device=dev_pts.device)
+                dist.all_gather_into_tensor(full, mine)
+                self.table = full[:M].cpu().numpy().astype(np.float64)
+                return
             self.table = self.obj.batch_device(dev_pts, self.data).cpu().numpy().astype(np.float64)
         else:
             self.table = np.asarray(self.obj.batch(pts, self.data), dtype=np.float64)
@@ -317,8 +333,17 @@ class ClusterTree(_DevicePointsMixin):
         drawn on the device from `seed`."""
         self.data = np.asarray(data)
         self.dim = min(self.data.shape[1], self.dim)
-        self.flat, self.build_info = build_cluster_tree(self.data, self.n_subdivisions, self.max_level, self.dim,
-                                                        self.use_kd_tree, seeds=seeds, seed=seed, device=device)
+        from . import sharding
+        if sharding.is_distributed():
+            # one process per GPU: the Lloyd sums are all-reduced, every rank ends with the same tree.  `seeds` is
+            # then a callable (depth, node_ids, global_counts) -> global member positions [n_live, n_sub]
+            if not self.use_kd_tree:
+                raise engine.MgbError("device build implements use_kd_tree=True")
+            self.flat, self.build_info = build_cluster_tree_sharded(self.data, self.n_subdivisions, self.max_level, self.dim,
+                                                                    seeds=seeds, seed=seed, device=device)
+        else:
+            self.flat, self.build_info = build_cluster_tree(self.data, self.n_subdivisions, self.max_level, self.dim,
+                                                            self.use_kd_tree, seeds=seeds, seed=seed, device=device)
         self.__dict__.pop("_dev_points", None)
         return self
 
@@ -776,3 +801,237 @@ def build_feature_tree(features, data, n_sub, seeds=None, seed=0, device=None):
     info["n_nodes"] = n_nodes
     flat = (pts, np.arange(n_nodes, dtype=np.int64), child_ptr, chi[o], torch.cat(first_sample).cpu().numpy())
     return flat, info
+
+
+# ---------------------------------------------------------------------------
+# sharded build (SURVEY.md section 8e, config 5 on several GPUs): the samples of every tree node are split
+# between the ranks by contiguous id ranges; per Lloyd iteration ONE all-reduce of the per-node sums and
+# counts is the path's real exchange step (NCCL on the GPUs, gloo in the CPU tests).  Every decision
+# (children, live / leaf, centroids) is taken from the all-reduced numbers, so all ranks build the same
+# tree; the kd-tree members are all-gathered as sample ids at the end (the data itself is replicated).
+# ---------------------------------------------------------------------------
+def _dist():
+    import torch.distributed as dist
+    return dist
+
+
+def _allreduce(t, group=None):
+    _dist().all_reduce(t, group=group)
+    return t
+
+
+def _allgather_var(t, group=None):
+    """Concatenation over ranks (rank order) of 1-D tensors of different lengths."""
+    torch = engine._torch()
+    dist = _dist()
+    world = dist.get_world_size(group)
+    n = torch.tensor([t.numel()], dtype=torch.long, device=t.device)
+    sizes = [torch.zeros_like(n) for _ in range(world)]
+    dist.all_gather(sizes, n, group=group)
+    sizes = [int(s.item()) for s in sizes]
+    m = max(max(sizes), 1)
+    buf = torch.zeros(m, dtype=t.dtype, device=t.device)
+    buf[:t.numel()] = t
+    out = [torch.empty_like(buf) for _ in range(world)]
+    dist.all_gather(out, buf, group=group)
+    return torch.cat([o[:s] for o, s in zip(out, sizes)])
+
+
+def _pick_global_rows(Xl, starts, lcounts, pos, group=None):
+    """Rows at GLOBAL member positions pos [n_live, k] of every node (a node's global member list is the
+    concatenation over ranks of its local members): the owner contributes the row, one all-reduce."""
+    torch = engine._torch()
+    dist = _dist()
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    allc = [torch.zeros_like(lcounts) for _ in range(world)]
+    dist.all_gather(allc, lcounts.contiguous(), group=group)
+    allc = torch.stack(allc)                                  # [world, n_live]
+    offset = torch.cumsum(allc, 0)[rank] - allc[rank]         # members held by lower ranks
+    local = pos - offset[:, None]
+    mine = (local >= 0) & (local < lcounts[:, None])
+    idx = (starts[:, None] + local).clamp(min=0, max=max(Xl.shape[0] - 1, 0))
+    rows = torch.zeros(pos.shape + (Xl.shape[1],), dtype=torch.float32, device=Xl.device)
+    if Xl.shape[0] > 0:
+        rows = torch.where(mine[..., None], Xl[idx], rows)
+    return _allreduce(rows, group)
+
+
+def _sharded_seeds(Xl, dim, node64, starts, lcounts, gcounts, n_sub, seeds, depth, gids, gen, group):
+    """Initial centroids, identical on every rank.  seeds: optional callable (depth, gids, global_counts) ->
+    global member positions [n_live, n_sub]; default k-means++ (one trial per centre) with the D^2 sampling
+    split in two stages: owner rank from the all-gathered per-rank totals, member from the local cumsum."""
+    torch = engine._torch()
+    dist = _dist()
+    dev = Xl.device
+    n_live = int(starts.shape[0])
+    if seeds is not None:
+        pos = torch.as_tensor(seeds(depth, gids, gcounts), dtype=torch.long, device=dev)
+        return _pick_global_rows(Xl, starts, lcounts, pos, group)[..., :dim].contiguous()
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    u = torch.rand((n_live, n_sub), generator=gen, device=dev, dtype=torch.float64)
+    cent = torch.empty((n_live, n_sub, dim), dtype=torch.float32, device=dev)
+    pos0 = (u[:, :1] * gcounts[:, None]).long().minimum(gcounts[:, None] - 1)
+    cent[:, 0] = _pick_global_rows(Xl, starts, lcounts, pos0, group)[:, 0, :dim]
+    d2 = ((Xl[:, :dim] - cent[node64, 0]) ** 2).sum(dim=1).double()
+    for j in range(1, n_sub):
+        ltot = torch.zeros(n_live, dtype=torch.float64, device=dev).index_add_(0, node64, d2)
+        allt = [torch.zeros_like(ltot) for _ in range(world)]
+        dist.all_gather(allt, ltot, group=group)
+        allt = torch.stack(allt)
+        cum = torch.cumsum(allt, 0)
+        target = u[:, j] * cum[-1]
+        owner = (cum <= target[None, :]).sum(0).clamp(max=world - 1)          # first rank whose cumulative total exceeds it
+        ltarget = target - (cum[rank] - allt[rank])
+        cs = torch.cumsum(d2, 0)
+        base = torch.where(starts > 0, cs[(starts - 1).clamp(min=0, max=max(cs.numel() - 1, 0))] if cs.numel() else torch.zeros(n_live, dtype=torch.float64, device=dev),
+                           torch.zeros(n_live, dtype=torch.float64, device=dev))
+        pick = torch.searchsorted(cs, base + ltarget, right=True) if cs.numel() else torch.zeros(n_live, dtype=torch.long, device=dev)
+        pick = torch.maximum(torch.minimum(pick, starts + lcounts - 1), starts).clamp(min=0, max=max(Xl.shape[0] - 1, 0))
+        mine = (owner == rank) & (lcounts > 0)
+        row = torch.zeros((n_live, dim), dtype=torch.float32, device=dev)
+        if Xl.shape[0] > 0:
+            row = torch.where(mine[:, None], Xl[pick, :dim], row)
+        cent[:, j] = _allreduce(row, group)
+        d2 = torch.minimum(d2, ((Xl[:, :dim] - cent[node64, j]) ** 2).sum(dim=1).double())
+    return cent.contiguous()
+
+
+def _subdivide_level_sharded(Xl, dim, n_sub, starts, lcounts, depth, gids, seeds, gen, dim_acc, group):
+    """One level of the sharded build: tolerance, seeds and every Lloyd M-step from all-reduced sums.
+    Returns (perm, child_node, global child counts, local child counts, child means, parent means, iterations)."""
+    torch = engine._torch()
+    dev = Xl.device
+    n_live = int(starts.shape[0])
+    node64 = torch.repeat_interleave(torch.arange(n_live, device=dev), lcounts)
+    node = node64.to(torch.int32).contiguous()
+
+    def e_step(centroids, k):
+        r = _lloyd_level(Xl, dim, node, n_live, k, centroids, None, dim_acc, max_iter=0)
+        return r, _allreduce(r["sums"].clone(), group), _allreduce(r["counts"].clone(), group), _allreduce(r["inertia"].clone(), group)
+
+    # per-node mean and sklearn's tolerance from the global moments
+    zero = torch.zeros((n_live, 1, dim), dtype=torch.float32, device=dev)
+    _, gs, gc, _ = e_step(zero, 1)
+    gcounts = gc[:, 0].long()
+    cnt = gcounts.clamp(min=1).to(torch.float32)
+    mean = gs[:, 0, :] / cnt[:, None]
+    _, _, _, gin = e_step(mean[:, None, :dim].contiguous(), 1)
+    tol = KMEANS_TOL * gin / (cnt * dim)
+    cent = _sharded_seeds(Xl, dim, node64, starts, lcounts, gcounts, n_sub, seeds, depth, gids, gen, group)
+    conv = torch.zeros(n_live, dtype=torch.bool, device=dev)
+    iters = 0
+    for it in range(KMEANS_MAX_ITER):
+        _, gs, gc, _ = e_step(cent, n_sub)
+        has = (gc > 0)[..., None]
+        new = torch.where(has, gs[..., :dim] / gc.clamp(min=1)[..., None].to(torch.float32), cent)
+        new = torch.where(conv[:, None, None], cent, new)
+        shift = ((new - cent) ** 2).sum(dim=(1, 2))
+        conv = conv | (shift <= tol)
+        cent = new.contiguous()
+        iters = it + 1
+        if iters % 4 == 0 and bool(conv.all().item()):
+            break
+    r, gs, gc, _ = e_step(cent, n_sub)                     # labels and sums that belong to the final centroids
+    key = node64 * n_sub + r["label"].long()
+    perm = torch.argsort(key, stable=True)
+    gflat = gc.reshape(-1).long()
+    ck = torch.nonzero(gflat > 0).reshape(-1)
+    gcc = gflat[ck]
+    lcc = r["counts"].reshape(-1).long()[ck]
+    means = gs.reshape(-1, dim_acc)[ck] / gcc[:, None].to(torch.float32)
+    return perm, ck // n_sub, gcc, lcc, means, mean, iters
+
+
+def build_cluster_tree_sharded(data, n_sub, max_level, dim, seeds=None, seed=0, device=None, group=None):
+    """build_cluster_tree with the samples split between the ranks of `group` (rank r works on the ids
+    shard_range(N, r, world)); `data` is the full array on every rank.  Collective: every rank returns the
+    same (FlatClusterTree, info)."""
+    torch = engine._torch()
+    from . import sharding
+    dist = _dist()
+    rank, world = dist.get_rank(group), dist.get_world_size(group)
+    dev = _device_of(device)
+    gen = torch.Generator(device=dev)
+    gen.manual_seed(int(seed))
+    data = np.asarray(data)
+    N, D = data.shape
+    X = torch.as_tensor(np.ascontiguousarray(data, dtype=np.float32), device=dev)
+    base, n_mine = sharding.shard_range(N, rank, world)
+    if not (N > n_sub and n_sub > 1):
+        return build_cluster_tree(data, n_sub, max_level, dim, True, None, seed, device)     # nothing to share
+    node_means, node_leaf = [None], [torch.zeros(1, dtype=torch.bool, device=dev)]
+    edges_parent, edges_child = [], []
+    kd_owner, kd_rows_local, kd_seg_local = [], [], []
+    n_nodes, n_seg = 1, 0
+    info = {"levels": [], "n_samples": int(N), "world": world}
+    Xl = X[base:base + n_mine].contiguous()
+    order_l = torch.arange(base, base + n_mine, device=dev)
+    gids = torch.zeros(1, dtype=torch.long, device=dev)
+    starts = torch.zeros(1, dtype=torch.long, device=dev)
+    lcounts = torch.full((1,), n_mine, dtype=torch.long, device=dev)
+    depth = 0
+    while gids.numel() > 0:
+        perm, child_node, gcc, lcc, cmeans, pmean, iters = _subdivide_level_sharded(Xl, dim, n_sub, starts, lcounts, depth, gids, seeds,
+                                                                                     gen, D, group)
+        if depth == 0:
+            node_means[0] = pmean
+        Xl, order_l = Xl[perm], order_l[perm]
+        parents = gids[child_node]
+        info["levels"].append({"depth": depth, "nodes": int(gids.numel()), "local_samples": int(Xl.shape[0]), "lloyd_iterations": int(iters)})
+        if depth < max_level:
+            n_children = int(gcc.numel())
+            cg = n_nodes + torch.arange(n_children, device=dev)
+            n_nodes += n_children
+            live = gcc > n_sub
+            node_means.append(cmeans)
+            node_leaf.append(~live)
+            edges_parent.append(parents)
+            edges_child.append(cg)
+            owners, seg_lens = cg[~live], lcc[~live]
+            sample_live = torch.repeat_interleave(live, lcc)
+            retired = order_l[~sample_live]
+            Xl, order_l = Xl[sample_live].contiguous(), order_l[sample_live]
+            gids, lcounts = cg[live], lcc[live]
+            starts = torch.cumsum(lcounts, 0) - lcounts
+        else:
+            owners, seg_lens, retired = parents, lcc, order_l
+            gids = gids[:0]
+        kd_owner.append(owners)
+        kd_rows_local.append(retired)
+        kd_seg_local.append(n_seg + torch.repeat_interleave(torch.arange(owners.numel(), device=dev), seg_lens))
+        n_seg += int(owners.numel())
+        depth += 1
+    # kd-tree members: ids of every rank, grouped by segment, ascending id inside a segment
+    rows = _allgather_var(torch.cat(kd_rows_local), group)
+    segs = _allgather_var(torch.cat(kd_seg_local), group)
+    o = torch.argsort(rows, stable=True)
+    o = o[torch.argsort(segs[o], stable=True)]
+    rows, segs = rows[o], segs[o]
+    seg_len = torch.bincount(segs, minlength=n_seg)
+    owner = torch.cat(kd_owner)
+    kd_pt, kd_l, kd_r, kd_in, roots = _build_kd_forest(X, rows, seg_len, dim)
+    return _assemble_flat_tree(data, n_nodes, node_means, node_leaf, edges_parent, edges_child, owner, roots, kd_pt, kd_l, kd_r, kd_in, info)
+
+
+def _assemble_flat_tree(data, n_nodes, node_means, node_leaf, edges_parent, edges_child, owner, roots, kd_pt, kd_l, kd_r, kd_in, info):
+    torch = engine._torch()
+    t = FlatClusterTree()
+    means = torch.cat(node_means).double().cpu().numpy()
+    t.points = np.concatenate([means, np.asarray(data, dtype=np.float64)], axis=0)
+    t.node_row = np.arange(n_nodes, dtype=np.int64)
+    t.node_leaf = torch.cat(node_leaf).cpu().numpy()
+    ep = torch.cat(edges_parent).cpu().numpy() if edges_parent else np.empty(0, dtype=np.int64)
+    ec = torch.cat(edges_child).cpu().numpy() if edges_child else np.empty(0, dtype=np.int64)
+    kp, kc = owner.cpu().numpy(), roots.cpu().numpy()
+    par = np.concatenate([ep, kp])
+    chi = np.concatenate([ec, kc])
+    iskd = np.concatenate([np.zeros(len(ep), dtype=bool), np.ones(len(kp), dtype=bool)])
+    o = np.argsort(par, kind="stable")
+    t.child_idx, t.child_is_kd = chi[o], iskd[o]
+    t.child_ptr = np.zeros(n_nodes + 1, dtype=np.int64)
+    t.child_ptr[1:] = np.cumsum(np.bincount(par, minlength=n_nodes))
+    t.kd_row = n_nodes + kd_pt.cpu().numpy()
+    t.kd_left, t.kd_right, t.kd_inner = kd_l.cpu().numpy(), kd_r.cpu().numpy(), kd_in.cpu().numpy()
+    info["n_nodes"] = n_nodes
+    info["n_kd_nodes"] = int(len(t.kd_row))
+    return t, info

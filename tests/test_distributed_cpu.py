@@ -86,3 +86,44 @@ def test_exchange_best_world2_gloo():
     mp.spawn(_worker, args=(2, port, cases, out), nprocs=2, join=True)
     for r in range(2):
         assert [tuple(x) for x in out[r]] == expect
+
+
+# ---------------------------------------------------------------------------------------------
+# sharded cluster-tree build (config 5 on several GPUs): world-size-2 gloo, K7 replaced by the oracle's
+# E-step (no GPU here) - checks the all-reduce bookkeeping: every rank ends with the tree a single process builds
+# ---------------------------------------------------------------------------------------------
+def _tree_worker(rank, world, port, max_level, out):
+    import json
+    import torch.distributed as dist
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from morphablegraphs_b200 import space_partitioning as sp
+        from tests.test_tree_cpu import TreeCase, _oracle_lloyd_level, _flat_to_dict
+        sp._lloyd_level = _oracle_lloyd_level
+        tc = TreeCase()
+        seeds = lambda depth, gids, gcounts: torch.stack([(gcounts * j) // 4 for j in range(4)], dim=1)
+        tree = sp.ClusterTree(4, max_level, tc.K).construct(tc.data, seeds=seeds, device="cpu")
+        out[rank] = json.dumps(_flat_to_dict(tree.flat))
+        # default seeding (distributed k-means++): ranks must still agree with each other
+        tree2 = sp.ClusterTree(4, 3, tc.K).construct(tc.data, seed=9, device="cpu")
+        out[10 + rank] = json.dumps(_flat_to_dict(tree2.flat))
+        out[20 + rank] = int(tree2.build_info["n_kd_nodes"])
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("max_level", [6, 2])
+def test_sharded_tree_build_world2_gloo(max_level):
+    import json
+    import torch.multiprocessing as mp
+    from tests.test_tree_cpu import TreeCase, _same_cluster_tree
+    mgr = mp.get_context("spawn").Manager()
+    out = mgr.dict()
+    mp.spawn(_tree_worker, args=(2, _free_port(), max_level, out), nprocs=2, join=True)
+    tc = TreeCase()
+    ref = json.loads(str(tc.g["cluster_tree_seeded%d_json" % max_level]))       # built by the reference's own builder
+    for r in range(2):
+        _same_cluster_tree(json.loads(out[r]), ref, tol=2e-5)
+    assert out[10] == out[11] and out[20] == out[21] == len(tc.data)
