@@ -211,6 +211,7 @@ def cpu_baseline_leg(args):
         n_loop = 1500
         out["loop_port"] = {"value": cb.loop_port_rate(w["golden"], w["shape"], n=n_loop), "unit": UNIT, "cores": 1,
                             "sample": "%d candidates through the per-candidate loop port (the reference's own call structure)" % n_loop}
+        out["tree_build_port"] = cb.tree_build_rate(w["golden"], w["shape"], m=10000)
     return out
 
 

@@ -128,3 +128,16 @@ def loop_port_rate(golden="s_config1", shape="S", n=1500, seed=3):
     t0 = time.perf_counter()
     O.loop_evaluate_one_position(ma, skeleton, mpc.constraints[0], S)
     return n / (time.perf_counter() - t0)
+
+
+def tree_build_rate(golden="s_config1", shape="S", m=10000, seed=4):
+    """Config 5 on the CPU: the oracle's recursive cluster-tree build (np_oracle.build_cluster_tree_dict: numpy Lloyd per
+    node, kd-tree leaves - the reference's cluster_tree_node_builder.py call structure) over m latent samples, one core."""
+    from oracle import np_oracle as O
+    node, skeleton, mpc, ma, _ = build_case(golden, shape)
+    S, _ = O.gmm_sample(ma, m, np.random.RandomState(seed))
+    t0 = time.perf_counter()
+    O.build_cluster_tree_dict(S, 4, 8, ma.K if hasattr(ma, "K") else 10)
+    dt = time.perf_counter() - t0
+    return {"value": m / dt, "unit": "samples/s", "cores": 1, "seconds": dt,
+            "sample": "%d latent samples, 4 subdivisions, max_level 8, recursive build (oracle port of cluster_tree_node_builder.py)" % m}

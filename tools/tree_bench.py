@@ -3,7 +3,8 @@
 latent samples of the S primitive, plus the euclidean-PCA feature chain.  Not a bench.py line (the
 metric there is candidates/s of the sample-and-evaluate step); prints one JSON object for profiles/.
 
-usage: python tools/tree_bench.py [--m 1000000] [--levels 8] [--cpu-m 10000] [--no-features]"""
+usage: python tools/tree_bench.py [--m 1000000] [--levels 8] [--no-features]
+(the CPU port of the build is timed by bench.py's cpu_baseline leg, key tree_build_port)"""
 import argparse
 import json
 import os
@@ -31,7 +32,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--m", type=int, default=1_000_000)
     ap.add_argument("--levels", type=int, default=8)
-    ap.add_argument("--cpu-m", type=int, default=10000)
+    ap.add_argument("--cpu-m", type=int, default=0, help="unused (the CPU build is timed by bench.py's cpu_baseline leg: tree_build_port)")
     ap.add_argument("--no-features", action="store_true")
     a = ap.parse_args()
     node, skeleton, mpc, prev = bench.build_case("S1M")
@@ -94,14 +95,6 @@ def main():
         (v, s), t = wall(lambda: ftree.find_best_example_excluding_search_candidates(obj_spatial_error_sum, data_t, 5))
         (v, s), t = wall(lambda: ftree.find_best_example_excluding_search_candidates(obj_spatial_error_sum, data_t, 5))
         out["feature_tree_search"] = {"seconds": t, "value": v}
-    # ---- CPU: the oracle's recursive build (sklearn-equivalent Lloyd per node) on a bounded sample ---------
-    if a.cpu_m > 0:
-        from oracle import np_oracle as O
-        t0 = time.perf_counter()
-        O.build_cluster_tree_dict(data[:a.cpu_m], 4, a.levels, K)
-        dt = time.perf_counter() - t0
-        out["cpu_port_build"] = {"samples": a.cpu_m, "seconds": dt, "samples_per_s": a.cpu_m / dt, "cores": 1,
-                                 "kind": "port (oracle/np_oracle.py: recursive build, numpy Lloyd per node)"}
     print(json.dumps(out))
 
 
