@@ -38,7 +38,9 @@ class FlatClusterTree(object):
     child_is_kd tells whether an entry is a kd-tree root (index into the kd arrays) or a node."""
 
     def __init__(self):
-        self.points = None          # [M, D] float64 (host)
+        self._points = None         # [M, D] float64 (host); device-built trees keep (node means, data) apart
+        self._parts = None          # and only concatenate them if somebody asks for the whole table
+        self.device_table = None    # float32 [M, D] torch tensor left on the GPU by the device build
         self.node_row = None        # [n_nodes] row of the node mean
         self.node_leaf = None       # [n_nodes] bool
         self.child_ptr = None       # [n_nodes + 1]
@@ -49,6 +51,32 @@ class FlatClusterTree(object):
         self.kd_right = None
         self.kd_inner = None        # [n_kd] bool
         self.root = 0
+
+    @property
+    def points(self):
+        if self._points is None and self._parts is not None:
+            self._points = np.concatenate(self._parts, axis=0)
+        return self._points
+
+    @points.setter
+    def points(self, value):
+        self._points = value
+
+    @property
+    def n_points(self):
+        if self._points is not None:
+            return len(self._points)
+        return sum(len(p) for p in self._parts)
+
+    def point(self, row):
+        """One row of the point table without materialising it."""
+        if self._points is not None:
+            return self._points[row]
+        for part in self._parts:
+            if row < len(part):
+                return part[row]
+            row -= len(part)
+        raise IndexError(row)
 
     @property
     def n_nodes(self):
@@ -189,7 +217,7 @@ class _PointCosts(object):
                 self._fill()
             return float(self.table[row])
         if row not in self.lazy:
-            self.lazy[row] = float(self.obj(self.owner.points[row], self.data))
+            self.lazy[row] = float(self.obj(self.owner.point(row), self.data))
         return self.lazy[row]
 
 
@@ -243,10 +271,10 @@ def _leaf_find_best_example(t, cost, node):
             else:                                   # leaf of a tree built without kd-trees: a single-sample node
                 row = t.node_row[c]
                 v = cost(row)
-            heapq.heappush(q, (v, tuple(t.points[row].tolist()), row))
+            heapq.heappush(q, (v, tuple(t.point(row).tolist()), row))
     else:
         row = t.node_row[node]
-        heapq.heappush(q, (cost(row), tuple(t.points[row].tolist()), row))
+        heapq.heappush(q, (cost(row), tuple(t.point(row).tolist()), row))
     v, _, row = heapq.heappop(q)
     return v, row
 
@@ -270,7 +298,7 @@ def cluster_tree_search(t, cost, n_candidates=1):
                     heapq.heappush(new_candidates, (c[0], i, c[2]))
             else:
                 v, row = _leaf_find_best_example(t, cost, node)
-                heapq.heappush(results, (v, c_idx, tuple(t.points[row].tolist()), row))
+                heapq.heappush(results, (v, c_idx, tuple(t.point(row).tolist()), row))
         candidates = new_candidates[:n_candidates]
     if len(results) > 0:
         r = heapq.heappop(results)
@@ -279,7 +307,16 @@ def cluster_tree_search(t, cost, n_candidates=1):
 
 
 class _DevicePointsMixin(object):
-    """Point table resident on the GPU of the objective's device model (uploaded once per device)."""
+    """Point table resident on the GPU of the objective's device model (uploaded once per device; a tree built
+    on the device keeps the float32 table it already has there - the score kernels compute in fp32 either way)."""
+
+    def n_points(self):
+        flat = getattr(self, "flat", None)
+        return flat.n_points if flat is not None else len(self.points)
+
+    def point(self, row):
+        flat = getattr(self, "flat", None)
+        return flat.point(row) if flat is not None else self.points[row]
 
     def device_points(self, obj, data):
         torch = engine._torch()
@@ -287,8 +324,13 @@ class _DevicePointsMixin(object):
         dm = _device_constraints(data[0], data[1], data[2]).dmodel
         cache = self.__dict__.setdefault("_dev_points", {})
         key = dm.device
-        if key not in cache or cache[key].shape[0] != len(self.points):
-            cache[key] = torch.as_tensor(np.ascontiguousarray(self.points, dtype=np.float64), device=dm.torch_device)
+        if key not in cache or cache[key].shape[0] != self.n_points():
+            flat = getattr(self, "flat", None)
+            table = getattr(flat, "device_table", None) if flat is not None else None
+            if table is not None and table.device == dm.torch_device:
+                cache[key] = table
+            else:
+                cache[key] = torch.as_tensor(np.ascontiguousarray(self.points, dtype=np.float64), device=dm.torch_device)
         return cache[key]
 
 
@@ -352,7 +394,7 @@ class ClusterTree(_DevicePointsMixin):
         cost = _PointCosts(self, obj, data)
         value, row = cluster_tree_search(self.flat, cost, n_candidates)
         self.last_search_lookups = cost.n_lookups
-        return value, self.flat.points[row].tolist()
+        return value, np.asarray(self.flat.point(row)).tolist()
 
     def find_best_example_excluding_search(self, obj, data):
         """cluster_tree.py:106-115: greedy descent (first minimum among the children), then the leaf."""
@@ -371,7 +413,7 @@ class ClusterTree(_DevicePointsMixin):
             node = int(best_c)
             level += 1
         v, row = _leaf_find_best_example(t, cost, node)
-        return v, t.points[row].tolist()
+        return v, np.asarray(t.point(row)).tolist()
 
 
 # ---------------------------------------------------------------------------
@@ -654,8 +696,20 @@ def build_cluster_tree(data, n_sub, max_level, dim, use_kd_tree=True, seeds=None
         kd_rows.append(order_l)
         gids = gids[:0]
     depth = 0
+    import os
+    import time
+    timing = {} if os.environ.get("MGB_TREE_TIMING") else None
+
+    def tick(name, t0):
+        if timing is not None:
+            torch.cuda.synchronize() if dev.type == "cuda" else None
+            timing[name] = timing.get(name, 0.0) + time.perf_counter() - t0
+        return time.perf_counter()
+
+    t0 = time.perf_counter()
     while gids.numel() > 0:
         perm, child_node, cc, cmeans, pmean, iters = _subdivide_level(Xl, dim, n_sub, starts, counts, depth, gids, seeds, gen, D)
+        t0 = tick("subdivide (stats, seeds, Lloyd, sort key)", t0)
         if depth == 0:
             node_means[0] = pmean
         Xl, order_l = Xl[perm], order_l[perm]
@@ -686,14 +740,20 @@ def build_cluster_tree(data, n_sub, max_level, dim, use_kd_tree=True, seeds=None
             kd_rows.append(order_l)
             gids = gids[:0]
         depth += 1
+        t0 = tick("level bookkeeping", t0)
     owner = torch.cat(kd_owner) if kd_owner else torch.empty(0, dtype=torch.long, device=dev)
     seg_len = torch.cat(kd_len) if kd_len else owner
     rows = torch.cat(kd_rows) if kd_rows else owner
     kd_pt, kd_l, kd_r, kd_in, roots = _build_kd_forest(X, rows, seg_len, dim)
+    t0 = tick("kd forest", t0)
+    if timing is not None:
+        info["timing"] = timing
     # ---- flat arrays on the host ------------------------------------------------------------
     t = FlatClusterTree()
-    means = torch.cat(node_means).double().cpu().numpy()
-    t.points = np.concatenate([means, np.asarray(data, dtype=np.float64)], axis=0)
+    means_dev = torch.cat(node_means)
+    t._parts = [means_dev.double().cpu().numpy(), np.asarray(data, dtype=np.float64)]
+    if dev.type == "cuda":
+        t.device_table = torch.cat([means_dev.float(), X], dim=0).contiguous()
     t.node_row = np.arange(n_nodes, dtype=np.int64)
     t.node_leaf = torch.cat(node_leaf).cpu().numpy()
     ep = torch.cat(edges_parent).cpu().numpy() if edges_parent else np.empty(0, dtype=np.int64)
@@ -711,6 +771,8 @@ def build_cluster_tree(data, n_sub, max_level, dim, use_kd_tree=True, seeds=None
     t.kd_left, t.kd_right, t.kd_inner = kd_l.cpu().numpy(), kd_r.cpu().numpy(), kd_in.cpu().numpy()
     info["n_nodes"] = n_nodes
     info["n_kd_nodes"] = int(len(t.kd_row))
+    if timing is not None:
+        tick("host assembly", t0)
     return t, info
 
 
@@ -1010,14 +1072,17 @@ def build_cluster_tree_sharded(data, n_sub, max_level, dim, seeds=None, seed=0, 
     seg_len = torch.bincount(segs, minlength=n_seg)
     owner = torch.cat(kd_owner)
     kd_pt, kd_l, kd_r, kd_in, roots = _build_kd_forest(X, rows, seg_len, dim)
-    return _assemble_flat_tree(data, n_nodes, node_means, node_leaf, edges_parent, edges_child, owner, roots, kd_pt, kd_l, kd_r, kd_in, info)
+    return _assemble_flat_tree(data, X, n_nodes, node_means, node_leaf, edges_parent, edges_child, owner, roots, kd_pt, kd_l, kd_r, kd_in, info)
 
 
-def _assemble_flat_tree(data, n_nodes, node_means, node_leaf, edges_parent, edges_child, owner, roots, kd_pt, kd_l, kd_r, kd_in, info):
+def _assemble_flat_tree(data, X, n_nodes, node_means, node_leaf, edges_parent, edges_child, owner, roots, kd_pt, kd_l, kd_r, kd_in, info):
     torch = engine._torch()
+    dev = X.device
     t = FlatClusterTree()
-    means = torch.cat(node_means).double().cpu().numpy()
-    t.points = np.concatenate([means, np.asarray(data, dtype=np.float64)], axis=0)
+    means_dev = torch.cat(node_means)
+    t._parts = [means_dev.double().cpu().numpy(), np.asarray(data, dtype=np.float64)]
+    if dev.type == "cuda":
+        t.device_table = torch.cat([means_dev.float(), X], dim=0).contiguous()
     t.node_row = np.arange(n_nodes, dtype=np.int64)
     t.node_leaf = torch.cat(node_leaf).cpu().numpy()
     ep = torch.cat(edges_parent).cpu().numpy() if edges_parent else np.empty(0, dtype=np.int64)
