@@ -183,18 +183,24 @@ __device__ __forceinline__ void mgb_tma_load_1d(void* dst_smem, const void* src_
                  : "memory");
 }
 
+// suspend-time hint of try_wait: a waiting warp sleeps in hardware (until the phase completes or the hint expires)
+// instead of re-issuing the probe - in the warp-specialised kernels the waiters share their scheduler with the
+// one working warp, and 58 % of all executed instructions were probes (profiles/README.md, r01_z)
+#ifndef MGB_MBAR_SUSPEND_NS
+#define MGB_MBAR_SUSPEND_NS 2000u
+#endif
 __device__ __forceinline__ void mgb_mbar_wait(unsigned long long* bar, unsigned int parity) {
     const unsigned int b = mgb_smem_u32(bar);
     asm volatile(
         "{\n"
         ".reg .pred p;\n"
         "MGB_WAIT_%=:\n"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, %2;\n"
         "@p bra MGB_DONE_%=;\n"
         "bra MGB_WAIT_%=;\n"
         "MGB_DONE_%=:\n"
         "}\n" ::"r"(b),
-        "r"(parity)
+        "r"(parity), "r"(MGB_MBAR_SUSPEND_NS)
         : "memory");
 }
 
