@@ -86,7 +86,7 @@ __host__ __device__ inline TcSmem tc_smem_plan(int Kp, int NC, int KC, int nst, 
     p.stage_bytes = (size_t)2 * NC * KC * 4;
     p.b_stage = off; off += p.stage_bytes * nst;
     p.out_stage = off; off += (W > 0) ? (size_t)nbuf * TC_M * (W + 4) * 4 : 0;
-    p.bars = off; off += 8 * (2 * TC_MAX_STAGES + 2 + 4);
+    p.bars = off; off += 8 * (2 * TC_MAX_STAGES + 2 + 6);
     p.tmem_ptr = off; off += 16;
     p.total = off;
     return p;
@@ -97,8 +97,8 @@ struct TcBars {
     unsigned long long* b_empty;  // [TC_MAX_STAGES]
     unsigned long long* a_full;
     unsigned long long* a_empty;
-    unsigned long long* t_full;   // [2]
-    unsigned long long* t_empty;  // [2]
+    unsigned long long* t_full;   // [3]
+    unsigned long long* t_empty;  // [3]
 };
 
 __device__ __forceinline__ TcBars tc_bars(unsigned char* base) {
@@ -109,7 +109,7 @@ __device__ __forceinline__ TcBars tc_bars(unsigned char* base) {
     b.a_full = p + 2 * TC_MAX_STAGES;
     b.a_empty = p + 2 * TC_MAX_STAGES + 1;
     b.t_full = p + 2 * TC_MAX_STAGES + 2;
-    b.t_empty = p + 2 * TC_MAX_STAGES + 4;
+    b.t_empty = p + 2 * TC_MAX_STAGES + 5;
     return b;
 }
 
@@ -124,7 +124,59 @@ struct TcSegs {
                                         // component only, against the first of TWO fills of the A tile (z, then s = mu + L z)
     int tile_first[MGB_MAX_GMM + 1];    // sampling mode: first tile of every component (tiles never straddle components)
     int G;
+    int dbg_mode;  // EXPERIMENT
+    int split_q, split_g;               // both >= 0: the chunks of these two operands are issued INTERLEAVED (q0 g0 q1 g1 ...),
+                                        // split_q's (and the sampling operand's) into TMEM buffer 0, split_g's into buffer 1, so
+                                        // that each operand has its own consumer group and neither waits behind the other
 };
+
+// chunk schedule of one tile, shared by the B producer and the MMA issuer: f(segment, chunk, stream, is_sampling).
+// stream -1: all chunks alternate between the two 256-column TMEM buffers.  Split mode: stream 0 (sampling operand and
+// split_q) alternates between two 128-column buffers at columns 0 / 128, stream 1 (split_g) owns the 256 columns at 256;
+// the quad stream is issued one chunk ahead and the GMM chunks are spread evenly between the quad chunks, so that the
+// quad consumer (the longer of the two) is not held up by GMM chunks.
+template <typename F>
+__device__ __forceinline__ void tc_for_each_chunk(const TcSegs& S, int gcomp, F f) {
+    const bool split = S.split_q >= 0 && S.split_g >= 0;
+    for (int sg = 0; sg < S.n; ++sg) {
+        if (sg == S.samp_seg) {
+            f(sg, gcomp, split ? 0 : -1, true);
+        } else if (!split) {
+            for (int c = 0; c < S.seg[sg].n_nc(); ++c) f(sg, c, -1, false);
+        }
+    }
+    if (split) {
+        const int nq = S.seg[S.split_q].n_nc(), ng = S.seg[S.split_g].n_nc();
+        int qi = 0, gi = 0;
+        if (nq > 0) f(S.split_q, qi++, 0, false);
+        while (qi < nq || gi < ng) {
+            if (qi < nq) f(S.split_q, qi++, 0, false);
+            // the GMM chunks are spread evenly over the quad chunks (ng / nq per quad chunk), the rest after the last one
+            while (gi < ng && (qi >= nq || (long long)gi * nq < (long long)(qi - 1) * ng)) f(S.split_g, gi++, 1, false);
+        }
+    }
+}
+
+// TMEM buffer, barrier phase and first column of the next chunk of a stream (cc: chunks so far, all streams; cq / ug:
+// chunks so far of stream 0 / 1)
+struct TcSlot {
+    unsigned int buf, phase, col;
+};
+__device__ __forceinline__ TcSlot tc_next_slot(int stream, unsigned int& cc, unsigned int& cq, unsigned int& ug) {
+    TcSlot r;
+    if (stream < 0) {
+        r.buf = cc & 1u; r.phase = (cc >> 1) & 1u; r.col = r.buf * TC_BUF_COLS;
+    } else if (stream == 0) {
+        r.buf = cq & 1u; r.phase = (cq >> 1) & 1u; r.col = r.buf * (TC_BUF_COLS / 2);
+        ++cq;
+    } else {
+        r.buf = 2u; r.phase = ug & 1u; r.col = TC_BUF_COLS;
+        ++ug;
+    }
+    ++cc;
+    return r;
+}
+
 // component of tile T (sampling mode)
 __device__ __forceinline__ int tc_tile_comp(const int* tile_first, int G, long long T) {
     int g = 0;
@@ -132,89 +184,100 @@ __device__ __forceinline__ int tc_tile_comp(const int* tile_first, int G, long l
     return g;
 }
 
-// warp 0, one lane: stream every stage image of every operand once per tile
+// warp 0, one lane: stream every stage image of every operand once per tile.  The stage ring position (st, ph) and the
+// source pointer advance by additions only: this lane and the MMA lane below are single threads on the critical path.
 __device__ __forceinline__ void tc_b_producer(const TcSegs& S, unsigned char* sm_stage, size_t stage_bytes, int nst, const TcBars& bars,
                                               long long my_tiles, const int* tile_first = nullptr) {
-    unsigned int it = 0;
+    int st = 0;
+    unsigned int ph = 0;
+    unsigned char* dst = sm_stage;
     for (long long t = 0; t < my_tiles; ++t) {
         const int gcomp = (S.samp_seg >= 0) ? tc_tile_comp(tile_first, S.G, blockIdx.x + t * gridDim.x) : 0;
-        for (int sg = 0; sg < S.n; ++sg) {
+        tc_for_each_chunk(S, gcomp, [&](int sg, int c, int, bool) {
             const TcB& B = S.seg[sg];
-            const bool samp = sg == S.samp_seg;
-            const int c_lo = samp ? gcomp : 0, c_hi = samp ? gcomp + 1 : B.n_nc();
-            const int n_kc = B.n_kc();
-            for (int c = c_lo; c < c_hi; ++c) {
-                const int wc = B.wc(c);
-                for (int kc = 0; kc < n_kc; ++kc, ++it) {
-                    const int st = it % nst;
-                    const unsigned int ph = (it / nst) & 1u;
-                    mgb_mbar_wait(&bars.b_empty[st], ph ^ 1u);
-                    const unsigned int bytes = (unsigned int)(2 * wc * B.wk(kc) * 4);
-                    mgb_mbar_expect_tx(&bars.b_full[st], bytes);
-                    mgb_bulk_g2s(sm_stage + (size_t)st * stage_bytes, B.data + B.off(c, kc), bytes, &bars.b_full[st]);
-                }
+            const int KC = B.KC, Kp = B.Kp;
+            const int wc = B.wc(c);
+            const float* src = B.data + B.off(c, 0);
+            for (int k0 = 0; k0 < Kp; k0 += KC) {
+                const int wk = min(KC, Kp - k0);
+                mgb_mbar_wait(&bars.b_empty[st], ph ^ 1u);
+                const unsigned int bytes = (unsigned int)(2 * wc * wk * 4);
+                mgb_mbar_expect_tx(&bars.b_full[st], bytes);
+                mgb_bulk_g2s(dst, src, bytes, &bars.b_full[st]);
+                src += 2 * wc * wk;      // stage images of one N-chunk are consecutive: [hi wc x wk][lo wc x wk]
+                dst += stage_bytes;
+                if (++st == nst) { st = 0; ph ^= 1u; dst = sm_stage; }
             }
-        }
+        });
     }
 }
 
-// warp 1, one lane: all MMAs of this CTA.  Chunk number cc (counted over all operands and tiles)
-// accumulates into TMEM buffer cc & 1.
+__device__ long long g_tc_cycles[16];
+
+// warp 1, one lane: all MMAs of this CTA.  A chunk accumulates into the TMEM buffer its schedule entry names
+// (split mode) or into alternating buffers (chunk number cc & 1); a buffer's barrier phase is the number of times
+// it has been used.
 __device__ __forceinline__ void tc_mma_issuer(const TcSegs& S, uint32_t a_hi_addr, uint32_t a_lo_addr, uint32_t stage_addr, size_t stage_bytes,
                                               int nst, const TcBars& bars, uint32_t tmem_base, long long my_tiles,
                                               const int* tile_first = nullptr) {
-    unsigned int it = 0, cc = 0, fill = 0;
+    unsigned int cc = 0, cq = 0, ug = 0, fill = 0;
     const uint32_t A_LBO = TC_M * 16, SBO = 128;
+    // descriptors differ only in their 14-bit start-address field (bytes >> 4): build them once, then add
+    const uint64_t da_hi0 = mgb_umma_desc(a_hi_addr, A_LBO, SBO), da_lo0 = mgb_umma_desc(a_lo_addr, A_LBO, SBO);
+    const uint32_t stage16 = (uint32_t)(stage_bytes >> 4), ring16 = stage_addr >> 4;
+    int st = 0;
+    unsigned int ph = 0;
+    uint32_t b16 = ring16;               // (address of stage st) >> 4
+    const bool dbgi = S.samp_seg >= 0 && blockIdx.x == 0;
+    long long w_te = 0, w_bf = 0, w_af = 0, tq = 0;
+#define MGB_TC_W(acc, stmt) { if (dbgi) tq = clock64(); stmt; if (dbgi) acc += clock64() - tq; }
     for (long long t = 0; t < my_tiles; ++t) {
         const int gcomp = (S.samp_seg >= 0) ? tc_tile_comp(tile_first, S.G, blockIdx.x + t * gridDim.x) : 0;
-        mgb_mbar_wait(bars.a_full, fill & 1u);
+        MGB_TC_W(w_af, mgb_mbar_wait(bars.a_full, fill & 1u))
         ++fill;
         mgb_tc_fence_after();
-        for (int sg = 0; sg < S.n; ++sg) {
+        tc_for_each_chunk(S, gcomp, [&](int sg, int c, int want_buf, bool samp) {
             const TcB& B = S.seg[sg];
-            const bool samp = sg == S.samp_seg;
-            const int c_lo = samp ? gcomp : 0, c_hi = samp ? gcomp + 1 : B.n_nc();
-            const int n_kc = B.n_kc();
-            for (int c = c_lo; c < c_hi; ++c, ++cc) {
-                const int wc = B.wc(c);
-                const unsigned int buf = cc & 1u;
-                mgb_mbar_wait(&bars.t_empty[buf], ((cc >> 1) & 1u) ^ 1u);
+            const int KC = B.KC, Kp = B.Kp;
+            const int wc = B.wc(c);
+            const TcSlot slot = tc_next_slot(want_buf, cc, cq, ug);
+            const unsigned int buf = slot.buf;
+            MGB_TC_W(w_te, mgb_mbar_wait(&bars.t_empty[buf], slot.phase ^ 1u))
+            mgb_tc_fence_after();
+            const uint32_t d_addr = tmem_base + slot.col;
+            const uint32_t idesc = mgb_umma_idesc_tf32(TC_M, wc);
+            const uint64_t db0 = mgb_umma_desc(0u, (uint32_t)wc * 16, SBO);
+            uint32_t acc = 0;
+            uint32_t a16 = 0;            // (byte offset of the K-slice in the A tile) >> 4: 8 columns of K = 2 * A_LBO bytes
+            for (int k0 = 0; k0 < Kp; k0 += KC) {
+                const int wk = min(KC, Kp - k0);
+                MGB_TC_W(w_bf, mgb_mbar_wait(&bars.b_full[st], ph))
                 mgb_tc_fence_after();
-                const uint32_t d_addr = tmem_base + buf * TC_BUF_COLS;
-                const uint32_t idesc = mgb_umma_idesc_tf32(TC_M, wc);
-                const uint32_t B_LBO = (uint32_t)wc * 16;
-                uint32_t acc = 0;
-                for (int kc = 0; kc < n_kc; ++kc, ++it) {
-                    const int st = it % nst;
-                    mgb_mbar_wait(&bars.b_full[st], (it / nst) & 1u);
-                    mgb_tc_fence_after();
-                    const int wk = B.wk(kc);
-                    const uint32_t b_hi = stage_addr + (uint32_t)(st * stage_bytes);
-                    const uint32_t b_lo = b_hi + (uint32_t)(wc * wk * 4);
-                    for (int j = 0; j < wk / 8; ++j) {
-                        const uint32_t a_off = (uint32_t)((kc * B.KC) / 4 + 2 * j) * A_LBO;
-                        const uint32_t b_off = (uint32_t)(2 * j) * B_LBO;
-                        const uint64_t da_hi = mgb_umma_desc(a_hi_addr + a_off, A_LBO, SBO);
-                        const uint64_t da_lo = mgb_umma_desc(a_lo_addr + a_off, A_LBO, SBO);
-                        const uint64_t db_hi = mgb_umma_desc(b_hi + b_off, B_LBO, SBO);
-                        const uint64_t db_lo = mgb_umma_desc(b_lo + b_off, B_LBO, SBO);
-                        mgb_umma_tf32(d_addr, da_lo, db_hi, idesc, acc);  // small terms first
-                        mgb_umma_tf32(d_addr, da_hi, db_lo, idesc, 1u);
-                        mgb_umma_tf32(d_addr, da_hi, db_hi, idesc, 1u);
-                        acc = 1u;
-                    }
-                    mgb_umma_commit(&bars.b_empty[st]);
+                const uint32_t lo16 = (uint32_t)(wc * wk) >> 2;      // the lo block follows the hi block: wc * wk * 4 bytes
+                uint32_t bj16 = b16;
+                for (int j = 0; j < wk; j += 8, a16 += 2 * A_LBO / 16, bj16 += 2 * wc) {
+                    const uint64_t da_hi = da_hi0 + a16, da_lo = da_lo0 + a16;
+                    const uint64_t db_hi = db0 + bj16, db_lo = db_hi + lo16;
+                    mgb_umma_tf32(d_addr, da_lo, db_hi, idesc, acc);  // small terms first
+                    mgb_umma_tf32(d_addr, da_hi, db_lo, idesc, 1u);
+                    mgb_umma_tf32(d_addr, da_hi, db_hi, idesc, 1u);
+                    acc = 1u;
                 }
-                mgb_umma_commit(&bars.t_full[buf]);
+                mgb_umma_commit(&bars.b_empty[st]);
+                b16 += stage16;
+                if (++st == nst) { st = 0; ph ^= 1u; b16 = ring16; }
             }
+            mgb_umma_commit(&bars.t_full[buf]);
             if (samp) {  // the A tile is refilled with the drawn latent vectors before the other operands
-                mgb_mbar_wait(bars.a_full, fill & 1u);
+                MGB_TC_W(w_af, mgb_mbar_wait(bars.a_full, fill & 1u))
                 ++fill;
                 mgb_tc_fence_after();
             }
-        }
+        });
         mgb_umma_commit(bars.a_empty);
     }
+    if (dbgi) { g_tc_cycles[13] += w_te; g_tc_cycles[14] += w_bf; g_tc_cycles[15] += w_af; }
+#undef MGB_TC_W
 }
 
 // one row of A: hi / lo split of `cnt` values (zero padded to Kp), written as float4 chunks
@@ -297,6 +360,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mgb_backproject_tc_kernel(const
             S.seg[0] = p.B;
             S.n = 1;
             S.samp_seg = -1;
+            S.split_q = S.split_g = -1; S.dbg_mode = 0;
             tc_b_producer(S, smem + plan.b_stage, plan.stage_bytes, p.nst, bars, my_tiles);
         }
     } else if (warp == 1) {
@@ -305,6 +369,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mgb_backproject_tc_kernel(const
             S.seg[0] = p.B;
             S.n = 1;
             S.samp_seg = -1;
+            S.split_q = S.split_g = -1; S.dbg_mode = 0;
             tc_mma_issuer(S, mgb_smem_u32(smem + plan.a_hi), mgb_smem_u32(smem + plan.a_lo), mgb_smem_u32(smem + plan.b_stage),
                           plan.stage_bytes, p.nst, bars, tmem_base, my_tiles);
         }
@@ -578,7 +643,7 @@ __host__ __device__ inline TcScoreSmem tc_score_smem_plan(int Kp, size_t stage_b
     p.lp = off; off += TC_M * 4;
     p.redc = off; off += 16;
     p.redi = off; off += 32;
-    p.bars = off; off += 8 * (2 * TC_MAX_STAGES + 2 + 4);
+    p.bars = off; off += 8 * (2 * TC_MAX_STAGES + 2 + 6);
     p.sbar = off; off += 8;
     p.tmem_ptr = off; off += 8;
     p.flag = off; off += 8;
@@ -586,6 +651,16 @@ __host__ __device__ inline TcScoreSmem tc_score_smem_plan(int Kp, size_t stage_b
     p.total = off;
     return p;
 }
+
+// cycle counters of CTA 0's first group-0 thread (diagnostic: mgb_debug_tc_cycles): 0 wait a_empty, 1 draw + fill z,
+// 2 wait sampling MMA, 3 refill [s|1], 4 wait quad chunks, 5 drain quad chunks, 6 constraint program, 7 wait GMM group,
+// 8 tiles, 9 total
+#define MGB_TC_T(i)                                     \
+    if (dbg) {                                          \
+        const long long now_ = clock64();               \
+        g_tc_cycles[i] += now_ - tmark;                 \
+        tmark = now_;                                   \
+    }
 
 __device__ __forceinline__ bool tc_better(float c1, long long i1, float c2, long long i2) { return (c1 < c2) || (c1 == c2 && i1 < i2); }
 
@@ -623,7 +698,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mgb_score_tc_kernel(const __gri
         }
         mgb_mbar_init(bars.a_full, 128);
         mgb_mbar_init(bars.a_empty, 1);
-        for (int i = 0; i < 2; ++i) {
+        for (int i = 0; i < 3; ++i) {
             mgb_mbar_init(&bars.t_full[i], 1);
             mgb_mbar_init(&bars.t_empty[i], 128);
         }
@@ -657,7 +732,11 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mgb_score_tc_kernel(const __gri
         SIn* raw = reinterpret_cast<SIn*>(qv);
         float best_c = INFINITY;
         long long best_i = LLONG_MAX;
-        unsigned int cc = 0, sload = 0;
+        unsigned int cc = 0, sload = 0, uq = 0, ug0 = 0;   // uq: chunks of the quad stream consumed by this group (split mode)
+        const bool split = p.segs.split_q >= 0 && p.segs.split_g >= 0;
+        const bool dbg = SAMPLE && blockIdx.x == 0 && tid0 == 0;
+        long long tmark = clock64();
+        const long long tstart = tmark;
         for (long long t = 0; t < my_tiles; ++t) {
             const long long T = blockIdx.x + t * gridDim.x;
             long long g0 = T * TC_M, idx, gi = 0;
@@ -673,6 +752,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mgb_score_tc_kernel(const __gri
                 idx = gi - sp.index_base;
                 const uint2 key = make_uint2((unsigned int)sp.seed, (unsigned int)(sp.seed >> 32));
                 mgb_mbar_wait(bars.a_empty, (unsigned int)(t & 1) ^ 1u);
+                MGB_TC_T(0)
                 // fill 1 of A: [z | 1], z = the standard normals mgb_sample draws for global index gi
                 for (int k0 = 0; k0 < p.Kp; k0 += 4) {
                     float z[4] = {0.f, 0.f, 0.f, 0.f};
@@ -690,12 +770,15 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mgb_score_tc_kernel(const __gri
                 }
                 mgb_fence_proxy_async();
                 mgb_mbar_arrive(bars.a_full);
+                MGB_TC_T(1)
                 // s = mu_g + L_g z comes back in TMEM; fill 2 of A: [s | 1]
                 {
-                    const unsigned int buf = cc & 1u;
-                    mgb_mbar_wait(&bars.t_full[buf], (cc >> 1) & 1u);
+                    const TcSlot slot = tc_next_slot(split ? 0 : -1, cc, uq, ug0);
+                    const unsigned int buf = slot.buf;
+                    mgb_mbar_wait(&bars.t_full[buf], slot.phase);
+                    MGB_TC_T(2)
                     mgb_tc_fence_after();
-                    const uint32_t base = lane_addr + buf * TC_BUF_COLS;
+                    const uint32_t base = lane_addr + slot.col;
                     for (int b0 = 0; b0 < p.Kp; b0 += 8) {
                         float v[8];
                         mgb_tmem_ld8(base + b0, v);
@@ -716,7 +799,6 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mgb_score_tc_kernel(const __gri
                     }
                     mgb_tc_fence_before();
                     mgb_mbar_arrive_relaxed(&bars.t_empty[buf]);
-                    ++cc;
                 }
             } else {
                 idx = g0 + row;
@@ -753,6 +835,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mgb_score_tc_kernel(const __gri
             }
             mgb_fence_proxy_async();
             mgb_mbar_arrive(bars.a_full);
+            MGB_TC_T(3)
             // ---- quad chunks: TMEM -> this thread's row of the quad-value area, then the part of the constraint
             //      program that reads them (every chunk holds whole time slots; kinematic state carries over) -----
             float total = 0.f;
@@ -764,22 +847,26 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mgb_score_tc_kernel(const __gri
                 total = fmaf(w, e, total);
                 if (sp.terms != nullptr && valid) sp.terms[(size_t)term * sp.n + idx] += e;
             };
-            for (int c = 0; c < n_nc_q; ++c, ++cc) {
+            for (int c = 0; c < n_nc_q; ++c) {
                 const TcB& B = p.segs.seg[p.seg_q];
-                const unsigned int buf = cc & 1u;
-                mgb_mbar_wait(&bars.t_full[buf], (cc >> 1) & 1u);
+                const TcSlot slot = tc_next_slot(split ? 0 : -1, cc, uq, ug0);
+                const unsigned int buf = slot.buf;
+                mgb_mbar_wait(&bars.t_full[buf], slot.phase);
+                MGB_TC_T(4)
                 mgb_tc_fence_after();
                 const int wc = B.wc(c);
                 for (int b0 = 0; b0 < wc; b0 += 32) {
                     float v[32];
-                    mgb_tmem_ld32(lane_addr + buf * TC_BUF_COLS + b0, v);
+                    mgb_tmem_ld32(lane_addr + slot.col + b0, v);
 #pragma unroll
                     for (int i = 0; i < 32; ++i)
                         if (b0 + i < wc) qv[(size_t)row * QS + b0 + i] = v[i];
                 }
                 mgb_tc_fence_before();
                 mgb_mbar_arrive_relaxed(&bars.t_empty[buf]);
-                interp.run(ops, __ldg(p.phase + c), __ldg(p.phase + c + 1), cst, quad, emit);
+                MGB_TC_T(5)
+                if (!(p.segs.dbg_mode & 2)) interp.run(ops, __ldg(p.phase + c), __ldg(p.phase + c + 1), cst, quad, emit);
+                MGB_TC_T(6)
             }
             cc += n_nc_g;
             float cost = sp.err_scale * total;
@@ -787,6 +874,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mgb_score_tc_kernel(const __gri
                 asm volatile("bar.sync 2, 256;" ::: "memory");  // group 1 has published -log p(s) of this tile
                 cost = fmaf(sp.quality_scale, sm_lp[row], cost);
             }
+            MGB_TC_T(7)
+            if (dbg) g_tc_cycles[8] += 1;
             if (sp.magnitude_scale != 0.f) cost = fmaf(sp.magnitude_scale, sqrtf(m2), cost);
             if (valid) {
                 if (sp.cost) sp.cost[idx] = cost;
@@ -794,6 +883,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mgb_score_tc_kernel(const __gri
                 if (tc_better(cost, gi, best_c, best_i)) { best_c = cost; best_i = gi; }
             }
         }
+        if (dbg) g_tc_cycles[9] += clock64() - tstart;
         // ---- selection: group-0 arg-min, per-CTA partial, last CTA folds (first minimum wins) ----------
         if (sp.want_best) {
             float* sm_redc = reinterpret_cast<float*>(smem + L.redc);
@@ -851,22 +941,32 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mgb_score_tc_kernel(const __gri
         const int row = 32 * wq + lane;
         const uint32_t lane_addr = tmem_base + ((uint32_t)(32 * wq) << 16);
         const int CW = p.CW, G = sp.G;
-        unsigned int cc = 0;
+        unsigned int cc = 0, ug = 0;                 // ug: uses of TMEM buffer 1 by this group (split mode)
+        const bool dbg1 = SAMPLE && blockIdx.x == 0 && threadIdx.x == 64 + 128;
+        long long tc1 = 0;
+        const long long t1start = clock64();
+        const bool split = p.segs.split_q >= 0 && p.segs.split_g >= 0;
         for (long long t = 0; t < my_tiles; ++t) {
-            // the quad chunks belong to group 0, but this group still has to OBSERVE every phase of the accumulator
-            // barriers: a parity wait is only meaningful when the waiter is at most one phase ahead of the barrier
-            if (SAMPLE) {
-                mgb_mbar_wait(&bars.t_full[cc & 1u], (cc >> 1) & 1u);
-                ++cc;
+            // alternating mode: the quad chunks belong to group 0, but this group still has to OBSERVE every phase of the
+            // accumulator barriers (a parity wait is only meaningful when the waiter is at most one phase ahead of the
+            // barrier).  Split mode: buffer 1 and its barriers are this group's alone.
+            if (!split) {
+                if (SAMPLE) {
+                    mgb_mbar_wait(&bars.t_full[cc & 1u], (cc >> 1) & 1u);
+                    ++cc;
+                }
+                for (int c = 0; c < n_nc_q; ++c, ++cc) mgb_mbar_wait(&bars.t_full[cc & 1u], (cc >> 1) & 1u);
             }
-            for (int c = 0; c < n_nc_q; ++c, ++cc) mgb_mbar_wait(&bars.t_full[cc & 1u], (cc >> 1) & 1u);
             float mx = -INFINITY, ssum = 0.f;
             int g = 0;
             for (int c = 0; c < n_nc_g; ++c, ++cc) {
-                const unsigned int buf = cc & 1u;
-                mgb_mbar_wait(&bars.t_full[buf], (cc >> 1) & 1u);
+                const unsigned int buf = split ? 2u : (cc & 1u);
+                long long tw0 = dbg1 ? clock64() : 0;
+                mgb_mbar_wait(&bars.t_full[buf], split ? (ug & 1u) : ((cc >> 1) & 1u));
+                ++ug;
+                if (dbg1) { const long long now_ = clock64(); g_tc_cycles[10] += now_ - tw0; tc1 = now_; }
                 mgb_tc_fence_after();
-                const uint32_t base = lane_addr + buf * TC_BUF_COLS;
+                const uint32_t base = lane_addr + (split ? TC_BUF_COLS : buf * TC_BUF_COLS);
                 for (int j = 0; j < p.cpc && g < G; ++j, ++g) {
                     // y = (s - mu_g) . P_g occupies CW columns; padding columns are exact zeros
                     float qf0 = 0.f, qf1 = 0.f;
@@ -899,10 +999,12 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mgb_score_tc_kernel(const __gri
                 }
                 mgb_tc_fence_before();
                 mgb_mbar_arrive_relaxed(&bars.t_empty[buf]);
+                if (dbg1) g_tc_cycles[11] += clock64() - tc1;
             }
             sm_lp[row] = -(mx + __logf(ssum));
             asm volatile("bar.sync 2, 256;" ::: "memory");
         }
+        if (dbg1) g_tc_cycles[12] += clock64() - t1start;
     }
     mgb_tc_fence_before();
     __syncthreads();
@@ -1078,6 +1180,10 @@ static bool tc_score_plan(const mgb_model* m, const mgb_constraints* c, float qu
         p.cpc = m->tcg_NC / m->tcg_CW;
     }
     if (p.segs.n == (sample ? 1 : 0)) return false;
+    // quads and GMM both present: interleave their chunks, one TMEM buffer and one consumer group each
+    p.segs.dbg_mode = getenv("MGB_TC_EXP") ? atoi(getenv("MGB_TC_EXP")) : 0;  // EXPERIMENT
+    p.segs.split_q = (use_q && use_g) ? p.seg_q : -1;
+    p.segs.split_g = (use_q && use_g) ? p.seg_g : -1;
     p.QS = std::max(use_q ? std::min(c->tcq_Np, TC_SCORE_QCHUNK) : 0, m->D) | 1;
     size_t stage_bytes = 0;
     for (int i = 0; i < p.segs.n; ++i) stage_bytes = std::max(stage_bytes, (size_t)2 * p.segs.seg[i].NC * p.segs.seg[i].KC * 4);
@@ -1140,5 +1246,14 @@ int mgb_launch_score_tc(const mgb_model* m, const mgb_constraints* c, const Scor
         mgb_score_tc_kernel<float, false><<<grid, TC_THREADS, smem, stream>>>(p);
     mgb_count_launch();
     MGB_CUDA(cudaGetLastError());
+    return MGB_OK;
+}
+
+
+// diagnostic (not part of include/mgb200.h): read and clear the cycle counters of the fused tensor-core step kernel
+extern "C" int mgb_debug_tc_cycles(long long* out16) {
+    long long zero[16] = {0};
+    MGB_CUDA(cudaMemcpyFromSymbol(out16, g_tc_cycles, sizeof(zero)));
+    MGB_CUDA(cudaMemcpyToSymbol(g_tc_cycles, zero, sizeof(zero)));
     return MGB_OK;
 }
