@@ -47,9 +47,9 @@ WORKLOADS = {
 # dram__bytes_read.sum + dram__bytes_write.sum of the step kernel, per launch, from the committed
 # `ncu --set full` captures (profiles/); the captures ran 1M candidates, scaled to the workload's launch
 TRAFFIC = {
-    "S1M": {"bytes": 131328.0, "source": "profiles/r01_z_ncu_k1k6_S_raw.csv: 88.8 KB read + 42.5 KB written per 1M-candidate launch "
+    "S1M": {"bytes": 123904.0, "source": "profiles/r01_zb_ncu_k1k6_S_raw.csv: 88.6 KB read + 35.3 KB written per 1M-candidate launch "
                                           "(tables + arg-min partials; candidates are never stored)"},
-    "L4M": {"bytes": 4.0 * 7849728.0, "source": "profiles/r01_z_ncu_k1k6_L_raw.csv: 7.84 MB read + 5.4 KB written per 1M candidates "
+    "L4M": {"bytes": 4.0 * 7906304.0, "source": "profiles/r01_zb_ncu_k1k6_L_raw.csv: 7.90 MB read + 5.6 KB written per 1M candidates "
                                                  "(packed operands re-read from L2/HBM per tile), x4 for the 4M launch"},
 }
 

@@ -47,8 +47,11 @@ struct MgbInterp {
 
     template <typename QuadFn, typename EmitFn>
     __device__ __forceinline__ void run(const MgbOp* __restrict__ ops, int pc0, int pc1, const float* __restrict__ cst, QuadFn quad, EmitFn emit) {
+        if (pc0 >= pc1) return;
+        MgbOp next = ops[pc0];
         for (int pc = pc0; pc < pc1; ++pc) {
-            const MgbOp op = ops[pc];
+            const MgbOp op = next;
+            if (pc + 1 < pc1) next = ops[pc + 1];   // the decode of the next op overlaps this op's arithmetic
             const float* cs = cst + op.c;
             switch (op.code) {
                 case OP_ROOT: {

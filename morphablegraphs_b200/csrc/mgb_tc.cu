@@ -124,7 +124,6 @@ struct TcSegs {
                                         // component only, against the first of TWO fills of the A tile (z, then s = mu + L z)
     int tile_first[MGB_MAX_GMM + 1];    // sampling mode: first tile of every component (tiles never straddle components)
     int G;
-    int dbg_mode;  // EXPERIMENT
     int split_q, split_g;               // both >= 0: the chunks of these two operands are issued INTERLEAVED (q0 g0 q1 g1 ...),
                                         // split_q's (and the sampling operand's) into TMEM buffer 0, split_g's into buffer 1, so
                                         // that each operand has its own consumer group and neither waits behind the other
@@ -360,7 +359,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mgb_backproject_tc_kernel(const
             S.seg[0] = p.B;
             S.n = 1;
             S.samp_seg = -1;
-            S.split_q = S.split_g = -1; S.dbg_mode = 0;
+            S.split_q = S.split_g = -1;
             tc_b_producer(S, smem + plan.b_stage, plan.stage_bytes, p.nst, bars, my_tiles);
         }
     } else if (warp == 1) {
@@ -369,7 +368,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mgb_backproject_tc_kernel(const
             S.seg[0] = p.B;
             S.n = 1;
             S.samp_seg = -1;
-            S.split_q = S.split_g = -1; S.dbg_mode = 0;
+            S.split_q = S.split_g = -1;
             tc_mma_issuer(S, mgb_smem_u32(smem + plan.a_hi), mgb_smem_u32(smem + plan.a_lo), mgb_smem_u32(smem + plan.b_stage),
                           plan.stage_bytes, p.nst, bars, tmem_base, my_tiles);
         }
@@ -652,9 +651,10 @@ __host__ __device__ inline TcScoreSmem tc_score_smem_plan(int Kp, size_t stage_b
     return p;
 }
 
-// cycle counters of CTA 0's first group-0 thread (diagnostic: mgb_debug_tc_cycles): 0 wait a_empty, 1 draw + fill z,
-// 2 wait sampling MMA, 3 refill [s|1], 4 wait quad chunks, 5 drain quad chunks, 6 constraint program, 7 wait GMM group,
-// 8 tiles, 9 total
+// cycle counters of CTA 0 (diagnostic: mgb_debug_tc_cycles, tools/tc_cycles.py).  First group-0 thread: 0 wait a_empty,
+// 1 draw + fill z, 2 wait sampling MMA, 3 refill [s|1], 4 wait quad chunks, 5 drain quad chunks, 6 constraint program,
+// 7 wait GMM group, 8 tiles, 9 total; first group-1 thread: 10 wait chunk, 11 consume, 12 total; MMA lane: 13 wait
+// t_empty, 14 wait b_full, 15 wait a_full
 #define MGB_TC_T(i)                                     \
     if (dbg) {                                          \
         const long long now_ = clock64();               \
@@ -865,7 +865,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mgb_score_tc_kernel(const __gri
                 mgb_tc_fence_before();
                 mgb_mbar_arrive_relaxed(&bars.t_empty[buf]);
                 MGB_TC_T(5)
-                if (!(p.segs.dbg_mode & 2)) interp.run(ops, __ldg(p.phase + c), __ldg(p.phase + c + 1), cst, quad, emit);
+                interp.run(ops, __ldg(p.phase + c), __ldg(p.phase + c + 1), cst, quad, emit);
                 MGB_TC_T(6)
             }
             cc += n_nc_g;
@@ -1181,7 +1181,6 @@ static bool tc_score_plan(const mgb_model* m, const mgb_constraints* c, float qu
     }
     if (p.segs.n == (sample ? 1 : 0)) return false;
     // quads and GMM both present: interleave their chunks, one TMEM buffer and one consumer group each
-    p.segs.dbg_mode = getenv("MGB_TC_EXP") ? atoi(getenv("MGB_TC_EXP")) : 0;  // EXPERIMENT
     p.segs.split_q = (use_q && use_g) ? p.seg_q : -1;
     p.segs.split_g = (use_q && use_g) ? p.seg_g : -1;
     p.QS = std::max(use_q ? std::min(c->tcq_Np, TC_SCORE_QCHUNK) : 0, m->D) | 1;
