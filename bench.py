@@ -16,7 +16,9 @@ A step (device arm, `value`): ONE fused launch (mgb_sample_score: K1 GMM samplin
 score + arg-min; + for N > 1 the exchange of every rank's best (cost, index)); model and constraint
 tables resident in HBM.  K1 and K6 are also timed as separate kernels (`kernels`).
 `e2e`: the reference-facing call with HOST samples (float64, pinned) -> mgb_score_host -> best
-(cost, index) back on the host; H2D and D2H inside the timed region.
+(cost, index) back on the host; H2D and D2H inside the timed region.  `e2e.generator_call`: the planner-facing
+call, MotionPrimitiveGenerator.generate_constrained_sample (constraints in, best latent vector out; candidates
+drawn on the device), timed by wall clock with the constraint compile + upload inside.
 """
 import argparse
 import json
@@ -383,6 +385,44 @@ def run_b200(args):
            "d2h_bytes_per_step": 12 * world, "steps": e2e_steps, "ms_per_step": 1e3 * e2e_t / e2e_steps,
            "call": "MotionPrimitiveGenerator.evaluate_samples_using_constraints -> mgb_score_host, float64 pinned host samples",
            "pinned_h2d_copy_gbs": h2d_gbs, "h2d_share_of_step": (n * dm.D * 8 / (h2d_gbs * 1e9)) / (e2e_t / e2e_steps)}
+    # ---- the generator call itself: what the reference's planner calls once per motion-primitive step ----------------
+    # (reference motion_primitive_generator.py:126-161 -> :192-206).  Host inputs: the step's constraint objects (their
+    # program + tables are compiled and uploaded inside the call: the cache is dropped every step, as a new step brings new
+    # constraints); candidates are drawn on the device; host outputs: the winning latent vector and its error.
+    from morphablegraphs_b200 import MotionPrimitiveGenerator
+    from morphablegraphs_b200.objective_functions import ObjSpatialErrorAndNaturalness
+    gen = MotionPrimitiveGenerator(None, {"n_random_samples": n * world, "use_local_coordinates": prev is None}, skeleton=skeleton, seed=11)
+    if qs != 0.0:
+        gen.objective = ObjSpatialErrorAndNaturalness(1.0, qs)
+
+    def gen_call():
+        if hasattr(mpc, "_mgb_cache"):
+            del mpc._mgb_cache
+        return gen.generate_constrained_sample(node, mpc, prev_frames=prev)
+
+    for _ in range(2):
+        best_s = gen_call()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    l0 = engine.launch_count()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        best_s = gen_call()
+    torch.cuda.synchronize()
+    gen_t = time.perf_counter() - t0
+    gen_launches = engine.launch_count() - l0
+    if world > 1:
+        t = torch.tensor([gen_t], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        gen_t = float(t.item())
+    e2e["generator_call"] = {"value": n * world * e2e_steps / gen_t, "unit": UNIT, "ms_per_step": 1e3 * gen_t / e2e_steps, "steps": e2e_steps,
+                             "launches_per_step": gen_launches / e2e_steps, "d2h_bytes_per_step": int(best_s.shape[0]) * 4 + 12,
+                             "call": "MotionPrimitiveGenerator.generate_constrained_sample(node, constraints), n_random_samples = %d: "
+                                     "constraint program compiled + uploaded, candidates drawn on the device (K1 fused), best latent "
+                                     "vector and min_error returned to the host" % (n * world),
+                             "min_error": float(mpc.min_error)}
+    t_clock1 = time.perf_counter()
     if rank == 0:
         clocks.stop()
     clk = clocks.summary(t_wall0, t_clock1) if rank == 0 else None

@@ -554,19 +554,18 @@ extern "C" int mgb_constraints_pack(const mgb_model* m, const mgb_constraint_des
     c->KP = KP;
     c->tab.assign((size_t)c->n_quads * (KP + 1) * 4, 0.f);
     c->tab64.assign((size_t)c->n_quads * (KP + 1) * 4, 0.0);
-    for (int q = 0; q < c->n_quads; ++q) {
-        const int slot = C.quads[q].first, group = C.quads[q].second;
-        const int ch0 = group < 0 ? 0 : 3 + 4 * group;
-        const int nch = group < 0 ? 3 : 4;
-        for (int ch = 0; ch < nch; ++ch) {
-            for (int k = 0; k <= K; ++k) {
+    // row k of the basis outermost: E is [K, M] row-major with M = n_coeffs * P (45 KB per row at L), so the gather over the
+    // quads' columns stays inside one row at a time (this runs once per motion-primitive step, on the planner's thread)
+    for (int k = 0; k <= K; ++k) {
+        const double* basis = (k < K) ? m->E.data() + (size_t)k * M : m->mean.data();
+        const int row = (k < K) ? 1 + k : 0;
+        for (int q = 0; q < c->n_quads; ++q) {
+            const int slot = C.quads[q].first, group = C.quads[q].second;
+            const int ch0 = group < 0 ? 0 : 3 + 4 * group;
+            const int nch = group < 0 ? 3 : 4;
+            for (int ch = 0; ch < nch; ++ch) {
                 double acc = 0.0;
-                for (int i = 0; i < 4; ++i) {
-                    const int col = (C.spans[slot] + i) * P + ch0 + ch;
-                    const double basis = (k < K) ? m->E[(size_t)k * M + col] : m->mean[col];
-                    acc += C.weights[4 * slot + i] * basis;
-                }
-                const int row = (k < K) ? 1 + k : 0;
+                for (int i = 0; i < 4; ++i) acc += C.weights[4 * slot + i] * basis[(C.spans[slot] + i) * P + ch0 + ch];
                 c->tab[((size_t)q * (KP + 1) + row) * 4 + ch] = (float)acc;
                 c->tab64[((size_t)q * (KP + 1) + row) * 4 + ch] = acc;
             }
