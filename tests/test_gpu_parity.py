@@ -355,6 +355,47 @@ def test_large_fused_sample_score(large):
             assert ia == ib or abs(float(ca[ia - base]) - float(ca[ib - base])) < 2e-5 * max(1.0, abs(float(ca[ia - base])))
 
 
+@pytest.mark.parametrize("n_gmm,n_spatial,n_constraints", [(1, 40, 1), (2, 37, 1), (3, 60, 4), (9, 48, 2), (32, 33, 1)])
+def test_tc_chunk_schedule_shapes(n_gmm, n_spatial, n_constraints):
+    """The tensor-core step kernel interleaves the chunks of the quad operand with the chunks of the GMM operand
+    (two quad buffers + one GMM buffer in TMEM).  Models whose operand chunk counts differ in every way from the L
+    fixture (one GMM chunk, one quad chunk, more GMM chunks than quad chunks and the reverse), scored in both
+    modes (samples from memory / drawn in the kernel) with and without the naturalness term, against the oracle."""
+    from oracle import np_oracle as O
+    from morphablegraphs_b200 import engine, synthetic as syn
+    from morphablegraphs_b200 import Skeleton, MotionStateGraphNode, MotionPrimitiveConstraints, CONSTRAINT_FACTORY
+    shape = dict(n_frames=60, n_joints=19, n_spatial=n_spatial, n_time=3, n_gmm=n_gmm)
+    skeleton = Skeleton.from_desc(syn.make_skeleton_desc(19))
+    node = MotionStateGraphNode()
+    node._initialize_from_json(None, syn.make_model_json(shape, seed=100 + n_gmm))
+    node.set_skeleton(skeleton)
+    joints = ["RightHand", "LeftFoot", "Head", "LeftHand"]
+    rng = np.random.RandomState(n_gmm)
+    specs = [syn.spec("GlobalTransformConstraint",
+                      syn.position_constraint_desc(joints[i % 4], list(rng.uniform(-50, 100, 3)), [59, 30, 0, 45][i % 4], 60),
+                      weight=1.0 + 0.5 * i) for i in range(n_constraints)]
+    mpc = MotionPrimitiveConstraints()
+    mpc.skeleton, mpc.is_local = skeleton, True
+    mpc.constraints = syn.build_constraints(CONSTRAINT_FACTORY, skeleton, specs)
+    dm = engine.DeviceModel(node, skeleton)
+    dc = engine.DeviceConstraints(dm, mpc, None)
+    assert dm.D >= 33                                           # the tensor-core path
+    for n, base, total in ((128, 0, 128), (1000 + 37, 0, 1000 + 37), (2500, 777, 9000)):
+        counts = dm.component_counts(total, seed=3)
+        S = dm.sample(n, seed=3, counts=counts, index_base=base, n_total=total)
+        S64 = S.cpu().numpy().astype(np.float64)
+        ref = O.candidate_costs(node, skeleton, mpc, S64)
+        lp = O.gmm_logpdf(O.ModelArrays(node), S64)
+        for qs in (0.0, 0.1):
+            want = ref + qs * (-lp)
+            a = dc.score(S, k=1, return_cost=True, index_base=base, quality_scale=qs)
+            b = dc.sample_score(n, seed=3, counts=counts, n_total=total, index_base=base, k=1, return_cost=True, quality_scale=qs)
+            assert rel_err(a["cost"].cpu().numpy(), want).max() < RTOL
+            assert rel_err(b["cost"].cpu().numpy(), want).max() < RTOL
+            _check_argmin(want, int(a["best_idx"][0]) - base, float(a["best_cost"][0]))
+            _check_argmin(want, int(b["best_idx"][0]) - base, float(b["best_cost"][0]))
+
+
 def test_peer_exchange_kernel_single_process():
     """mgb_exchange_best with several 'ranks' inside one process: one slot array per rank on the same GPU,
     one stream per rank (the kernels wait for each other's records, so they must be co-resident: 1 CTA of
