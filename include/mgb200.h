@@ -18,8 +18,14 @@
  *    `h_*` pointers are host memory.
  *  - calls taking `stream` are asynchronous on that cudaStream_t (passed as
  *    void*); NULL is the legacy default stream.
- *  - a model / constraints handle is immutable after creation and may be used
- *    from several host threads; workspace is per call.
+ *  - the tables of a model / constraints handle are immutable after creation, and
+ *    the entries that take caller-owned device pointers + a stream (mgb_sample,
+ *    mgb_score, mgb_sample_score, mgb_backproject, ...) may be called on one
+ *    handle from several host threads, each with its own workspace and stream.
+ *    The HOST-BUFFER entries (mgb_score_host, mgb_generate_best, mgb_score_options)
+ *    use staging buffers and streams owned by the model handle: calls on the same
+ *    model handle are serialised by a per-handle mutex; different handles run
+ *    concurrently.
  *  - there is no CPU fallback: every compute entry fails with MGB_E_CUDA when
  *    no sm_100-class device is usable.
  */

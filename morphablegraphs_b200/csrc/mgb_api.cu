@@ -681,16 +681,14 @@ extern "C" int mgb_score_frames(const mgb_model* m, const mgb_constraints* c, co
                             k, d_best_cost, d_best_idx, d_workspace, workspace_bytes, (cudaStream_t)stream);
 }
 
-static std::mutex g_host_mutex;
-
 extern "C" int mgb_score_host(const mgb_model* m_, const mgb_constraints* c, const void* h_s, int32_t s_is_f64, int64_t n,
                               int64_t index_base, float err_scale, float quality_scale, float magnitude_scale, float* h_cost, int32_t k,
                               float* h_best_cost, int64_t* h_best_idx) {
     MGB_REQUIRE(m_ && c && (h_s || n == 0), "null argument");
     MGB_REQUIRE(k >= 0 && k <= 64, "k must be in [0, 64]");
     MGB_REQUIRE(k == 0 || (h_best_cost && h_best_idx), "k > 0 needs h_best_cost / h_best_idx");
-    std::lock_guard<std::mutex> lock(g_host_mutex);
     mgb_model* m = const_cast<mgb_model*>(m_);  // staging buffers are lazily created caches
+    std::lock_guard<std::mutex> lock(m->host_mutex);
     MGB_CUDA(cudaSetDevice(m->device));
     const size_t elt = s_is_f64 ? sizeof(double) : sizeof(float);
     const size_t row = (size_t)m->D * elt;
@@ -705,13 +703,14 @@ extern "C" int mgb_score_host(const mgb_model* m_, const mgb_constraints* c, con
         }
     }
     if (m->stage_bytes < chunk_bytes) {
+        // both chunks may still be in flight from the previous call's tail only if it failed: drain first
+        MGB_CUDA(cudaStreamSynchronize(m->compute_stream));
         for (int b = 0; b < 2; ++b) {
-            if (m->pinned[b]) cudaFreeHost(m->pinned[b]);
             cudaFree(m->d_stage[b]);
-            m->pinned[b] = nullptr;
             m->d_stage[b] = nullptr;
-            MGB_CUDA(cudaMalloc(&m->d_stage[b], chunk_bytes));
         }
+        m->stage_bytes = 0;
+        for (int b = 0; b < 2; ++b) MGB_CUDA(cudaMalloc(&m->d_stage[b], chunk_bytes));
         m->stage_bytes = chunk_bytes;
     }
     const int64_t n_chunks = n > 0 ? (n + CH - 1) / CH : 0;
@@ -740,8 +739,15 @@ extern "C" int mgb_score_host(const mgb_model* m_, const mgb_constraints* c, con
     bool host_pinned = false;
     if (n > 0 && cudaPointerGetAttributes(&attr, h_s) == cudaSuccess) host_pinned = (attr.type == cudaMemoryTypeHost);
     cudaGetLastError();  // pageable memory reports an error on old drivers; clear it
-    if (!host_pinned && n > 0 && !m->pinned[0]) {
+    if (!host_pinned && n > 0 && m->pinned_bytes < chunk_bytes) {
+        // sized separately from d_stage: a pinned-input call may have grown d_stage without ever allocating these
+        for (int b = 0; b < 2; ++b) {
+            if (m->pinned[b]) cudaFreeHost(m->pinned[b]);
+            m->pinned[b] = nullptr;
+        }
+        m->pinned_bytes = 0;
         for (int b = 0; b < 2; ++b) MGB_CUDA(cudaMallocHost(&m->pinned[b], chunk_bytes));
+        m->pinned_bytes = chunk_bytes;
     }
     for (int64_t ch = 0; ch < n_chunks; ++ch) {
         const int b = (int)(ch & 1);

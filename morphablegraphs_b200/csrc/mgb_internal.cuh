@@ -4,6 +4,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -31,6 +32,35 @@ void mgb_count_launch(int n = 1);
             return MGB_E_INVALID;         \
         }                                 \
     } while (0)
+
+// ---------------------------------------------------------------------------
+// per-DEVICE one-time kernel configuration: cudaFuncSetAttribute applies to the current device only, so a
+// process that drives several GPUs must opt every one of them in (a per-process flag would leave the second
+// device at the 48 KB default)
+// ---------------------------------------------------------------------------
+#define MGB_MAX_DEVICES 64
+template <typename Kern>
+inline int mgb_opt_in_smem(Kern kern, bool (&done)[MGB_MAX_DEVICES], int bytes) {
+    int dev = 0;
+    MGB_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= MGB_MAX_DEVICES || !done[dev]) {
+        MGB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+        if (dev >= 0 && dev < MGB_MAX_DEVICES) done[dev] = true;
+    }
+    return MGB_OK;
+}
+// SM count of the CURRENT device (cached per device)
+inline int mgb_num_sms() {
+    static int cache[MGB_MAX_DEVICES] = {0};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= MGB_MAX_DEVICES) return 148;
+    if (cache[dev] == 0) {
+        int n = 0;
+        cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+        cache[dev] = n > 0 ? n : 148;
+    }
+    return cache[dev];
+}
 
 // ---------------------------------------------------------------------------
 // scoring program (built by mgb_constraints_pack, interpreted by the score kernels)
@@ -112,11 +142,13 @@ struct mgb_model {
     std::vector<double> means64;    // [G][D]
     float* d_Bsamp = nullptr;       // sampling operand: per component [L_g^T ; mu_g], one N-chunk each
     int tcs_Kp = 0, tcs_Np = 0, tcs_NC = 0, tcs_KC = 0;
-    // private streams / staging for the host-buffer entry
+    // private streams / staging for the host-buffer entries; calls on one handle are serialised by host_mutex
+    std::mutex host_mutex;
     cudaStream_t copy_stream = nullptr, compute_stream = nullptr;
     void* pinned[2] = {nullptr, nullptr};
     void* d_stage[2] = {nullptr, nullptr};
-    size_t stage_bytes = 0;
+    size_t stage_bytes = 0;   // size of each d_stage buffer
+    size_t pinned_bytes = 0;  // size of each pinned buffer (allocated only for pageable inputs)
     void* d_ws = nullptr;
     size_t ws_bytes = 0;
     cudaEvent_t ev_copied[2] = {nullptr, nullptr}, ev_done[2] = {nullptr, nullptr};

@@ -450,16 +450,7 @@ __global__ void mgb_topk_final(const float* part_cost, const long long* part_idx
     }
 }
 
-int g_num_sms = 0;
-int num_sms() {
-    if (g_num_sms == 0) {
-        int dev = 0;
-        cudaGetDevice(&dev);
-        cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev);
-        if (g_num_sms <= 0) g_num_sms = 148;
-    }
-    return g_num_sms;
-}
+int num_sms() { return mgb_num_sms(); }
 
 constexpr size_t MGB_SMEM_MAX = 220 * 1024;
 
@@ -470,11 +461,8 @@ struct SmemPlan {
 template <int NREG, int CPT, int MODE, typename SIn>
 int launch_variant(ScoreParams& p, const SmemPlan& plan, cudaStream_t stream) {
     auto kern = mgb_score_kernel<NREG, CPT, MODE, SIn>;
-    static bool configured = false;
-    if (!configured) {
-        MGB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)MGB_SMEM_MAX));
-        configured = true;
-    }
+    static bool configured[MGB_MAX_DEVICES] = {false};
+    if (int rc = mgb_opt_in_smem(kern, configured, (int)MGB_SMEM_MAX)) return rc;
     size_t tile = 0;  // bytes of one tile buffer
     if (MODE == MODE_S || (MODE == MODE_FRAMES && p.s != nullptr)) tile = (size_t)MGB_BLOCK * CPT * p.D * (NREG == 0 ? sizeof(float) : sizeof(SIn));
     if (MODE == MODE_SAMPLE && NREG == 0) tile = (size_t)MGB_BLOCK * CPT * (p.D | 1) * sizeof(float);
@@ -497,14 +485,7 @@ int launch_variant(ScoreParams& p, const SmemPlan& plan, cudaStream_t stream) {
     return MGB_OK;
 }
 
-int cpt_preference() {
-    static int v = -1;
-    if (v < 0) {
-        const char* e = getenv("MGB_CPT");
-        v = (e && atoi(e) == 1) ? 1 : 2;
-    }
-    return v;
-}
+constexpr int cpt_preference() { return 2; }
 
 template <int MODE, typename SIn>
 int launch_shape(int D, ScoreParams& p, const SmemPlan& plan, cudaStream_t stream) {

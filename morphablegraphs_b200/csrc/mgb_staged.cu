@@ -343,11 +343,8 @@ static int launch_sample(const mgb_model* m, const MgbGmmPrefix& prefix, int64_t
     const int in_smem = (2 * tile_bytes + chol_bytes <= 96 * 1024) ? 1 : 0;
     const size_t smem = 2 * tile_bytes + (in_smem ? chol_bytes : 0) + 128;
     MGB_REQUIRE(smem <= 200 * 1024, "latent dimension too large for the sampler");
-    static bool configured = false;
-    if (!configured) {
-        MGB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        configured = true;
-    }
+    static bool configured[MGB_MAX_DEVICES] = {false};
+    if (int rc = mgb_opt_in_smem(kern, configured, 200 * 1024)) return rc;
     long long n_tiles = (n + sb - 1) / sb;
     int occ = 1;
     MGB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, sb, smem));
@@ -505,11 +502,8 @@ extern "C" int mgb_fk(const mgb_model* m, const float* d_frames, int64_t n_frame
         if (smem <= 100 * 1024 || fkb == 32) break;
     }
     MGB_REQUIRE(smem <= 200 * 1024, "frame tile too large for shared memory");
-    static bool configured = false;
-    if (!configured) {
-        MGB_CUDA(cudaFuncSetAttribute(mgb_fk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        configured = true;
-    }
+    static bool configured[MGB_MAX_DEVICES] = {false};
+    if (int rc = mgb_opt_in_smem(mgb_fk_kernel, configured, 200 * 1024)) return rc;
     int occ = 1;
     MGB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, mgb_fk_kernel, fkb, smem));
     long long n_tiles = (n_frames + fkb - 1) / fkb;

@@ -69,7 +69,6 @@ struct TcBackprojectParams {
     int nst;            // B stages
     int W;              // epilogue staging width: a warp writes W consecutive floats of a row back to back
     int nbuf;           // staging buffers (1 or 2)
-    int dbg;            // MGB_TC_DBG bits (timing experiments): 1 = no global stores, 2 = no TMEM reads either
 };
 
 // shared-memory carve-up, identical on host and device
@@ -211,7 +210,11 @@ __device__ __forceinline__ void tc_b_producer(const TcSegs& S, unsigned char* sm
     }
 }
 
+// Cycle counters of CTA 0 (tools/tc_cycles.py) exist only in a -DMGB_TC_PROFILE build; the product build carries
+// neither the counters nor the clock reads.
+#ifdef MGB_TC_PROFILE
 __device__ long long g_tc_cycles[16];
+#endif
 
 // warp 1, one lane: all MMAs of this CTA.  A chunk accumulates into the TMEM buffer its schedule entry names
 // (split mode) or into alternating buffers (chunk number cc & 1); a buffer's barrier phase is the number of times
@@ -227,9 +230,13 @@ __device__ __forceinline__ void tc_mma_issuer(const TcSegs& S, uint32_t a_hi_add
     int st = 0;
     unsigned int ph = 0;
     uint32_t b16 = ring16;               // (address of stage st) >> 4
+#ifdef MGB_TC_PROFILE
     const bool dbgi = S.samp_seg >= 0 && blockIdx.x == 0;
     long long w_te = 0, w_bf = 0, w_af = 0, tq = 0;
 #define MGB_TC_W(acc, stmt) { if (dbgi) tq = clock64(); stmt; if (dbgi) acc += clock64() - tq; }
+#else
+#define MGB_TC_W(acc, stmt) { stmt; }
+#endif
     for (long long t = 0; t < my_tiles; ++t) {
         const int gcomp = (S.samp_seg >= 0) ? tc_tile_comp(tile_first, S.G, blockIdx.x + t * gridDim.x) : 0;
         MGB_TC_W(w_af, mgb_mbar_wait(bars.a_full, fill & 1u))
@@ -275,7 +282,9 @@ __device__ __forceinline__ void tc_mma_issuer(const TcSegs& S, uint32_t a_hi_add
         });
         mgb_umma_commit(bars.a_empty);
     }
+#ifdef MGB_TC_PROFILE
     if (dbgi) { g_tc_cycles[13] += w_te; g_tc_cycles[14] += w_bf; g_tc_cycles[15] += w_af; }
+#endif
 #undef MGB_TC_W
 }
 
@@ -416,7 +425,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mgb_backproject_tc_kernel(const
                     if (ncol > 0) {
                         if (p.nbuf == 1) asm volatile("bar.sync 1, 256;" ::: "memory");  // stores of the previous group have read the staging
                         // TMEM -> registers -> staging, thread-per-row: this warp moves columns [h W/2, (h+1) W/2) of its 32 rows
-                        for (int b0 = h * (W >> 1); b0 < (h + 1) * (W >> 1) && b0 < ncol && !(p.dbg & 4); b0 += 32) {
+                        for (int b0 = h * (W >> 1); b0 < (h + 1) * (W >> 1) && b0 < ncol; b0 += 32) {
                             float v[32];
                             mgb_tmem_ld32(lane_addr + buf * TC_BUF_COLS + w0 + b0, v);
 #pragma unroll
@@ -431,9 +440,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mgb_backproject_tc_kernel(const
                     asm volatile("bar.sync 1, 256;" ::: "memory");  // staging of this group complete
                     float* obase = p.out + (size_t)(tile0 + 16 * ew) * M + col0;
                     const float* srows = stg + (size_t)16 * ew * SS;
-                    if (p.dbg & 1) {
-                        if (srows[lane] == 123.456f) obase[0] = 0.f;
-                    } else if (vec == 4) {
+                    if (vec == 4) {
                         tc_store_rows<float4>(srows, SS, obase, M, n_rows, ncol, W, lane);
                     } else if (vec == 2) {
                         tc_store_rows<float2>(srows, SS, obase, M, n_rows, ncol, W, lane);
@@ -513,8 +520,10 @@ bool tc_plan_b(TcB& B, int K, int N, int* nst_out, int* W_out = nullptr, int* nb
     // epilogue staging (width, buffers) in order of preference, then B stage depth / size
     const int cand[5][2] = {{128, 2}, {256, 1}, {128, 1}, {64, 2}, {64, 1}};
     int forced_w = 0, forced_nb = 0;
+#ifdef MGB_TC_PROFILE
     if (const char* e = getenv("MGB_TC_W")) forced_w = atoi(e);
     if (const char* e = getenv("MGB_TC_NBUF")) forced_nb = atoi(e);
+#endif
     for (int wi = 0; wi < (W_out ? 5 : 1); ++wi) {
         const int W = W_out ? cand[wi][0] : 0, nbuf = W_out ? cand[wi][1] : 1;
         if (W_out && ((forced_w && W != forced_w) || (forced_nb && nbuf != forced_nb))) continue;
@@ -534,16 +543,7 @@ bool tc_plan_b(TcB& B, int K, int N, int* nst_out, int* W_out = nullptr, int* nb
     return false;
 }
 
-int tc_num_sms() {
-    static int n = 0;
-    if (n == 0) {
-        int dev = 0;
-        cudaGetDevice(&dev);
-        cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
-        if (n <= 0) n = 148;
-    }
-    return n;
-}
+int tc_num_sms() { return mgb_num_sms(); }
 
 }  // namespace
 
@@ -577,13 +577,9 @@ int mgb_backproject_tc(const mgb_model* m, const float* d_s, int64_t n, float* d
     p.nbuf = m->tc_nbuf;
     p.s = d_s; p.mean = m->d_mean; p.out = d_coeffs;
     p.n = n; p.D = m->D; p.K = m->K; p.M = m->M;
-    { const char* e = getenv("MGB_TC_DBG"); p.dbg = e ? atoi(e) : 0; }
     const size_t smem = tc_smem_plan(p.B.Kp, p.B.NC, p.B.KC, p.nst, p.W, p.nbuf).total;
-    static bool configured = false;
-    if (!configured) {
-        MGB_CUDA(cudaFuncSetAttribute(mgb_backproject_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM_BUDGET));
-        configured = true;
-    }
+    static bool configured[MGB_MAX_DEVICES] = {false};
+    if (int rc = mgb_opt_in_smem(mgb_backproject_tc_kernel, configured, (int)TC_SMEM_BUDGET)) return rc;
     const long long n_tiles = (n + TC_M - 1) / TC_M;
     const int grid = (int)std::min<long long>(n_tiles, tc_num_sms());
     mgb_backproject_tc_kernel<<<grid, TC_THREADS, smem, stream>>>(p);
@@ -655,12 +651,16 @@ __host__ __device__ inline TcScoreSmem tc_score_smem_plan(int Kp, size_t stage_b
 // 1 draw + fill z, 2 wait sampling MMA, 3 refill [s|1], 4 wait quad chunks, 5 drain quad chunks, 6 constraint program,
 // 7 wait GMM group, 8 tiles, 9 total; first group-1 thread: 10 wait chunk, 11 consume, 12 total; MMA lane: 13 wait
 // t_empty, 14 wait b_full, 15 wait a_full
+#ifdef MGB_TC_PROFILE
 #define MGB_TC_T(i)                                     \
     if (dbg) {                                          \
         const long long now_ = clock64();               \
         g_tc_cycles[i] += now_ - tmark;                 \
         tmark = now_;                                   \
     }
+#else
+#define MGB_TC_T(i)
+#endif
 
 __device__ __forceinline__ bool tc_better(float c1, long long i1, float c2, long long i2) { return (c1 < c2) || (c1 == c2 && i1 < i2); }
 
@@ -734,9 +734,11 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mgb_score_tc_kernel(const __gri
         long long best_i = LLONG_MAX;
         unsigned int cc = 0, sload = 0, uq = 0, ug0 = 0;   // uq: chunks of the quad stream consumed by this group (split mode)
         const bool split = p.segs.split_q >= 0 && p.segs.split_g >= 0;
+#ifdef MGB_TC_PROFILE
         const bool dbg = SAMPLE && blockIdx.x == 0 && tid0 == 0;
         long long tmark = clock64();
         const long long tstart = tmark;
+#endif
         for (long long t = 0; t < my_tiles; ++t) {
             const long long T = blockIdx.x + t * gridDim.x;
             long long g0 = T * TC_M, idx, gi = 0;
@@ -875,7 +877,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mgb_score_tc_kernel(const __gri
                 cost = fmaf(sp.quality_scale, sm_lp[row], cost);
             }
             MGB_TC_T(7)
+#ifdef MGB_TC_PROFILE
             if (dbg) g_tc_cycles[8] += 1;
+#endif
             if (sp.magnitude_scale != 0.f) cost = fmaf(sp.magnitude_scale, sqrtf(m2), cost);
             if (valid) {
                 if (sp.cost) sp.cost[idx] = cost;
@@ -883,7 +887,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mgb_score_tc_kernel(const __gri
                 if (tc_better(cost, gi, best_c, best_i)) { best_c = cost; best_i = gi; }
             }
         }
+#ifdef MGB_TC_PROFILE
         if (dbg) g_tc_cycles[9] += clock64() - tstart;
+#endif
         // ---- selection: group-0 arg-min, per-CTA partial, last CTA folds (first minimum wins) ----------
         if (sp.want_best) {
             float* sm_redc = reinterpret_cast<float*>(smem + L.redc);
@@ -942,9 +948,11 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mgb_score_tc_kernel(const __gri
         const uint32_t lane_addr = tmem_base + ((uint32_t)(32 * wq) << 16);
         const int CW = p.CW, G = sp.G;
         unsigned int cc = 0, ug = 0;                 // ug: uses of TMEM buffer 1 by this group (split mode)
+#ifdef MGB_TC_PROFILE
         const bool dbg1 = SAMPLE && blockIdx.x == 0 && threadIdx.x == 64 + 128;
         long long tc1 = 0;
         const long long t1start = clock64();
+#endif
         const bool split = p.segs.split_q >= 0 && p.segs.split_g >= 0;
         for (long long t = 0; t < my_tiles; ++t) {
             // alternating mode: the quad chunks belong to group 0, but this group still has to OBSERVE every phase of the
@@ -961,10 +969,14 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mgb_score_tc_kernel(const __gri
             int g = 0;
             for (int c = 0; c < n_nc_g; ++c, ++cc) {
                 const unsigned int buf = split ? 2u : (cc & 1u);
+#ifdef MGB_TC_PROFILE
                 long long tw0 = dbg1 ? clock64() : 0;
+#endif
                 mgb_mbar_wait(&bars.t_full[buf], split ? (ug & 1u) : ((cc >> 1) & 1u));
                 ++ug;
+#ifdef MGB_TC_PROFILE
                 if (dbg1) { const long long now_ = clock64(); g_tc_cycles[10] += now_ - tw0; tc1 = now_; }
+#endif
                 mgb_tc_fence_after();
                 const uint32_t base = lane_addr + (split ? TC_BUF_COLS : buf * TC_BUF_COLS);
                 for (int j = 0; j < p.cpc && g < G; ++j, ++g) {
@@ -999,12 +1011,16 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mgb_score_tc_kernel(const __gri
                 }
                 mgb_tc_fence_before();
                 mgb_mbar_arrive_relaxed(&bars.t_empty[buf]);
+#ifdef MGB_TC_PROFILE
                 if (dbg1) g_tc_cycles[11] += clock64() - tc1;
+#endif
             }
             sm_lp[row] = -(mx + __logf(ssum));
             asm volatile("bar.sync 2, 256;" ::: "memory");
         }
+#ifdef MGB_TC_PROFILE
         if (dbg1) g_tc_cycles[12] += clock64() - t1start;
+#endif
     }
     mgb_tc_fence_before();
     __syncthreads();
@@ -1023,12 +1039,16 @@ constexpr int TC_SCORE_KC = 8;
 constexpr int TC_SCORE_QCHUNK = 128;  // columns of one chunk of the quad operand = 32 quads: what one pass of the program sees
 
 bool tc_disabled() {
+#ifdef MGB_TC_PROFILE
     static int v = -1;
     if (v < 0) {
         const char* e = getenv("MGB_NO_TC");
         v = (e && atoi(e) != 0) ? 1 : 0;
     }
     return v == 1;
+#else
+    return false;
+#endif
 }
 }  // namespace
 
@@ -1229,13 +1249,10 @@ int mgb_launch_score_tc(const mgb_model* m, const mgb_constraints* c, const Scor
         for (int g = m->G; g <= MGB_MAX_GMM; ++g) p.segs.tile_first[g] = acc;
         p.n_tiles = acc;
     }
-    static bool configured = false;
-    if (!configured) {
-        MGB_CUDA(cudaFuncSetAttribute(mgb_score_tc_kernel<float, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM_BUDGET));
-        MGB_CUDA(cudaFuncSetAttribute(mgb_score_tc_kernel<double, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM_BUDGET));
-        MGB_CUDA(cudaFuncSetAttribute(mgb_score_tc_kernel<float, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM_BUDGET));
-        configured = true;
-    }
+    static bool cfg_a[MGB_MAX_DEVICES] = {false}, cfg_b[MGB_MAX_DEVICES] = {false}, cfg_c[MGB_MAX_DEVICES] = {false};
+    if (int rc = mgb_opt_in_smem(mgb_score_tc_kernel<float, false>, cfg_a, (int)TC_SMEM_BUDGET)) return rc;
+    if (int rc = mgb_opt_in_smem(mgb_score_tc_kernel<double, false>, cfg_b, (int)TC_SMEM_BUDGET)) return rc;
+    if (int rc = mgb_opt_in_smem(mgb_score_tc_kernel<float, true>, cfg_c, (int)TC_SMEM_BUDGET)) return rc;
     const int grid = (int)std::max<long long>(1, std::min<long long>(p.n_tiles, tc_num_sms()));
     if (sample)
         mgb_score_tc_kernel<float, true><<<grid, TC_THREADS, smem, stream>>>(p);
@@ -1249,10 +1266,12 @@ int mgb_launch_score_tc(const mgb_model* m, const mgb_constraints* c, const Scor
 }
 
 
-// diagnostic (not part of include/mgb200.h): read and clear the cycle counters of the fused tensor-core step kernel
+// diagnostic of a -DMGB_TC_PROFILE build (not part of include/mgb200.h): read and clear the cycle counters
+#ifdef MGB_TC_PROFILE
 extern "C" int mgb_debug_tc_cycles(long long* out16) {
     long long zero[16] = {0};
     MGB_CUDA(cudaMemcpyFromSymbol(out16, g_tc_cycles, sizeof(zero)));
     MGB_CUDA(cudaMemcpyToSymbol(g_tc_cycles, zero, sizeof(zero)));
     return MGB_OK;
 }
+#endif

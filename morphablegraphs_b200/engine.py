@@ -410,10 +410,10 @@ def flatten_constraints(dmodel, mp_constraints):
 class DeviceConstraints(object):
     """A MotionPrimitiveConstraints list compiled for the GPU (mgb_constraints handle)."""
 
-    def __init__(self, dmodel, mp_constraints, prev_frames=None):
+    def __init__(self, dmodel, mp_constraints, prev_frames=None, flat=None):
         self.dmodel = dmodel
         self.lib = dmodel.lib
-        descs, n, parr, n_points, times = flatten_constraints(dmodel, mp_constraints)
+        descs, n, parr, n_points, times = flat if flat is not None else flatten_constraints(dmodel, mp_constraints)
         align = _lib.AlignDesc()
         align.mode = 0
         is_local = bool(getattr(mp_constraints, "is_local", False))

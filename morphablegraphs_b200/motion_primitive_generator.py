@@ -2,21 +2,26 @@
 (reference motion_generator/motion_primitive_generator.py:47-261) whose
 sample-and-evaluate loop runs on the GPU.
 
-Drop-in points kept: `generate_constrained_sample`, `_get_best_fit_sample_using_gmm`,
+Drop-in points kept: `generate_constrained_motion_spline`, `generate_constrained_sample`,
+`generate_random_sample`, `_get_best_fit_sample_using_gmm`,
 `evaluate_samples_using_constraints`, `_get_best_fit_sample_using_cluster_tree`,
 the `objective` attribute, and the bookkeeping on the constraints object
-(`min_error`, `evaluations`, first-minimum tie-break, returned row is a row of
-the input `samples`).  The scipy local optimiser stays on the host, seeded by
-the arg-min.
+(`min_error`, `evaluations`, `time`, first-minimum tie-break, returned row is a row of
+the input `samples`).  The local optimiser is whatever the caller injects as
+`numerical_minimizer`: the reference's scipy LeastSquares on the host, or this
+package's batched device Levenberg-Marquardt (optimization.py).
 """
+import time
+
 import numpy as np
 
-from . import engine, sharding
-from .objective_functions import obj_spatial_error_sum, _device_constraints
+from . import sharding
+from .objective_functions import obj_spatial_error_sum, objective_scales, _device_constraints
 
 SAMPLING_MODE_RANDOM = "random_discrete"
 SAMPLING_MODE_CLUSTER_TREE_SEARCH = "cluster_tree_search"
 SAMPLING_MODE_RANDOM_SPLINE = "random_spline"
+SPATIAL_CONSTRAINT_TYPE_KEYFRAME_POSE = "keyframe_pose"
 
 # hot-path keys of reference algorithm_configuration.py:141-257
 DEFAULT_ALGORITHM_CONFIG = {
@@ -38,12 +43,17 @@ class MotionPrimitiveGenerator(object):
         self._action_constraints = action_constraints
         self.set_algorithm_config(dict(DEFAULT_ALGORITHM_CONFIG, **(algorithm_config or {})))
         self.skeleton = skeleton
+        self.action_name = None
+        self.prev_action_name = None
+        self._motion_state_graph = None
         if action_constraints is not None:
             self.action_name = action_constraints.action_name
+            self.prev_action_name = getattr(action_constraints, "prev_action_name", None)
             self._motion_state_graph = action_constraints.motion_state_graph
             self.skeleton = self._motion_state_graph.skeleton
         self.objective = obj_spatial_error_sum
         self._rng = np.random.RandomState(seed)
+        self._rng_shared = seed is not None     # an explicit seed is the same on every rank by construction
         self.numerical_minimizer = None
 
     def set_algorithm_config(self, algorithm_config):
@@ -58,6 +68,28 @@ class MotionPrimitiveGenerator(object):
         self.constrained_sampling_mode = algorithm_config.get("constrained_sampling_mode", SAMPLING_MODE_RANDOM)
         self.n_cluster_search_candidates = int(algorithm_config.get("n_cluster_search_candidates", 2))
         self.use_local_coordinates = algorithm_config.get("use_local_coordinates", True)
+
+    # ------------------------------------------------------------------ :83-124
+    def generate_constrained_motion_spline(self, mp_constraints, prev_graph_walk):
+        """Calls generate_constrained_sample and back-projects the result to a MotionSpline; sets
+        `mp_constraints.time` (one of the bookkeeping fields a drop-in keeps)."""
+        node_key = (self.action_name, mp_constraints.motion_primitive_name)
+        if len(prev_graph_walk.steps) > 0:
+            prev_mp_name = prev_graph_walk.steps[-1].node_key[1]
+            prev_parameters = prev_graph_walk.steps[-1].parameters
+        else:
+            prev_mp_name = ""
+            prev_parameters = None
+        start = time.time()
+        if self.use_constraints and len(mp_constraints.constraints) > 0:
+            graph_node = self._motion_state_graph.nodes[node_key]
+            parameters = self.generate_constrained_sample(graph_node, mp_constraints, prev_mp_name,
+                                                          prev_graph_walk.get_quat_frames(), prev_parameters)
+        else:  # no constraints were given
+            parameters = self.generate_random_sample(node_key, prev_mp_name, prev_parameters)
+        mp_constraints.time = time.time() - start
+        motion_spline = self._motion_state_graph.nodes[node_key].back_project(parameters, use_time_parameters=False)
+        return motion_spline, parameters
 
     # ------------------------------------------------------------------ :126-161
     def generate_constrained_sample(self, graph_node, in_mp_constraints, prev_mp_name="", prev_frames=None, prev_parameters=None):
@@ -83,23 +115,61 @@ class MotionPrimitiveGenerator(object):
         return (mp_constraints.use_local_optimization and not self.use_transition_model and
                 self.numerical_minimizer is not None and mp_constraints.min_error >= self.optimization_start_error_threshold)
 
+    # ------------------------------------------------------------------ :179-190
     def _optimize_parameters_numerically(self, initial_guess, graph_node, mp_constraints, prev_frames):
-        """:179-190 - host scipy optimiser injected by the caller (`numerical_minimizer`); untouched."""
+        """Pose constraints are dropped first and the residuals are normalised by the start error, as the
+        reference does; the minimiser itself is the caller's (`numerical_minimizer`)."""
+        mp_constraints.constraints = [c for c in mp_constraints.constraints if c.constraint_type != SPATIAL_CONSTRAINT_TYPE_KEYFRAME_POSE]
+        if len(mp_constraints.constraints) == 0:
+            return initial_guess
         data = (graph_node, mp_constraints, prev_frames, self._settings["error_scale_factor"],
                 self._settings["quality_scale_factor"], 1.0)
+        error_sum = max(abs(np.sum(self.numerical_minimizer._objective_function(initial_guess, data))), 1.0)
+        data = (graph_node, mp_constraints, prev_frames, self._settings["error_scale_factor"],
+                self._settings["quality_scale_factor"], error_sum)
         self.numerical_minimizer.set_objective_function_parameters(data)
         return self.numerical_minimizer.run(initial_guess=initial_guess)
+
+    # ------------------------------------------------------------------ :208-218
+    def generate_random_sample(self, node_key, prev_mp_name="", prev_parameters=None):
+        """One unconstrained draw (what motion_generator.py:233 falls back to when a step has no constraints)."""
+        nodes = self._motion_state_graph.nodes
+        prev_key = (self.prev_action_name, prev_mp_name)
+        if (self.use_transition_model and prev_parameters is not None and prev_key in nodes
+                and nodes[prev_key].has_transition_model(node_key)):
+            return nodes[prev_key].predict_parameters(node_key, prev_parameters)
+        return nodes[node_key].sample_low_dimensional_vector()
+
+    def _predict_gmm(self, mp_name, prev_mp_name, prev_parameters):
+        to_key = (self.action_name, mp_name)
+        return self._motion_state_graph.nodes[(self.prev_action_name, prev_mp_name)].predict_gmm(to_key, prev_parameters)
+
+    def _step_seed(self):
+        """Seed of one sample-and-evaluate step.  Under torch.distributed every rank must score the SAME job
+        (same multinomial split, same Philox key): a generator built without an explicit seed synchronises its
+        stream once, by broadcasting a seed from rank 0 (collective: every rank reaches its first step together)."""
+        if sharding.is_distributed() and not self._rng_shared:
+            self._rng = np.random.RandomState(sharding.broadcast_seed(int(self._rng.randint(0, 2 ** 31 - 1))))
+            self._rng_shared = True
+        return int(self._rng.randint(0, 2 ** 31 - 1))
 
     # ------------------------------------------------------------------ :192-206
     def _get_best_fit_sample_using_gmm(self, graph_node, mp_constraints, prev_mp_name="", prev_frames=None, prev_parameters=None):
         """Sample N and score them in ONE fused launch (mgb_sample_score: K1 + K6, candidates never
-        leave the registers), arg-min on the device; the winning row is regenerated from its
+        leave the registers), arg-min on the device; the winning row is re-drawn by the kernel's last CTA from its
         global index (Philox is keyed by it) and only that row and its cost come back to the host."""
+        if self.use_transition_model and prev_parameters is not None:
+            # :195-197 - candidates from the transition model's predicted mixture (host sampler of the caller's
+            # model object), scored by the same kernels through the host-sample entry
+            samples = self._predict_gmm(mp_constraints.motion_primitive_name, prev_mp_name, prev_parameters).sample(self.n_random_samples)
+            if isinstance(samples, tuple):      # sklearn >= 0.18 returns (X, component labels)
+                samples = samples[0]
+            return self.evaluate_samples_using_constraints(samples, graph_node, mp_constraints, prev_frames)[0]
         dc = _device_constraints(graph_node, mp_constraints, prev_frames)
         dm = dc.dmodel
-        seed = int(self._rng.randint(0, 2 ** 31 - 1))
+        error_scale, quality_scale, magnitude_scale = objective_scales(self.objective)
+        seed = self._step_seed()
         n = int(self.n_random_samples)
-        obj = self.objective
         # one process per GPU: every rank holds the same generator state (same seed), scores its own
         # index range of the job and the per-rank bests are exchanged (sharding.py)
         rank, world = 0, 1
@@ -109,8 +179,7 @@ class MotionPrimitiveGenerator(object):
         base, n_mine = sharding.shard_range(n, rank, world)
         counts = dm.component_counts(n, seed)
         res = dc.sample_score(n_mine, seed=seed, counts=counts, n_total=n, index_base=base, k=1,
-                              error_scale=getattr(obj, "error_scale", 1.0), quality_scale=getattr(obj, "quality_scale", 0.0),
-                              magnitude_scale=getattr(obj, "magnitude_scale", 0.0))
+                              error_scale=error_scale, quality_scale=quality_scale, magnitude_scale=magnitude_scale)
         peer = sharding.peer_exchange(dm.torch_device) if world > 1 else None
         if peer is not None:
             # per-rank bests exchanged and reduced on the device over NVLink peer memory (mgb_exchange_best)
@@ -156,9 +225,8 @@ class MotionPrimitiveGenerator(object):
             samples = samples.astype(np.float64)
         samples_c = np.ascontiguousarray(samples)
         dc = _device_constraints(mp_node, constraints, prev_frames)
-        obj = self.objective
-        res = dc.score_host(samples_c, k=1, error_scale=getattr(obj, "error_scale", 1.0),
-                            quality_scale=getattr(obj, "quality_scale", 0.0), magnitude_scale=getattr(obj, "magnitude_scale", 0.0))
+        error_scale, quality_scale, magnitude_scale = objective_scales(self.objective)
+        res = dc.score_host(samples_c, k=1, error_scale=error_scale, quality_scale=quality_scale, magnitude_scale=magnitude_scale)
         best_idx = int(res["best_idx"][0])
         min_error = float(res["best_cost"][0])
         constraints.min_error = min_error

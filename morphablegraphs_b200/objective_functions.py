@@ -7,21 +7,47 @@ that scores a whole candidate batch in one launch.
 Each call compiles the constraint list once per (constraints object, prev_frames)
 and caches the device program on the constraints object.
 """
+import ctypes as C
+
 import numpy as np
 
-from . import engine
+from . import engine, _lib
+from ._lib import MgbError
+
+
+def constraints_key(dm, flat, mp_constraints, prev_frames):
+    """Content key of a compiled constraint program: the flattened descriptors (type, joints, time
+    slots, targets, weights, masks), the pose points, the evaluation times, `is_local` and the last
+    previous frame (what the alignment reads).  In-place mutation of a constraint - the reference's
+    planner rewrites `canonical_keyframe` before scoring, graph_walk_planner.py:199-203 - therefore
+    yields a new key and a recompile; object identity is never trusted."""
+    descs, n, parr, n_points, times = flat
+    is_local = bool(getattr(mp_constraints, "is_local", False))
+    prev = b""
+    if not is_local and prev_frames is not None:
+        prev = np.ascontiguousarray(prev_frames[-1], dtype=np.float64).tobytes()
+    start_pose = getattr(mp_constraints, "start_pose", None) is not None
+    return (id(dm), n, n_points, bytes(descs)[:n * C.sizeof(_lib.ConstraintDesc)],
+            bytes(parr)[:n_points * C.sizeof(_lib.PosePoint)], times.tobytes(), is_local, prev, start_pose)
 
 
 def _device_constraints(mp_node, mp_constraints, prev_frames):
+    """DeviceConstraints of (model, constraint list, prev_frames), cached on the constraints object under a
+    CONTENT key (see constraints_key): the constraint list is flattened on every call - that is the cheap
+    part - and the program is recompiled and re-uploaded only when a byte of it changed."""
     mp = getattr(mp_node, "motion_primitive", mp_node)
     skeleton = mp_constraints.skeleton
     dm = mp.device_model(skeleton) if hasattr(mp, "device_model") else _foreign_model(mp_node, skeleton)
+    flat = engine.flatten_constraints(dm, mp_constraints)
+    key = constraints_key(dm, flat, mp_constraints, prev_frames)
     cache = getattr(mp_constraints, "_mgb_cache", None)
-    key = (id(dm), len(mp_constraints.constraints), None if prev_frames is None else id(prev_frames))
     if cache is None or cache[0] != key:
-        dc = engine.DeviceConstraints(dm, mp_constraints, prev_frames)
-        mp_constraints._mgb_cache = (key, dc)
-        cache = mp_constraints._mgb_cache
+        dc = engine.DeviceConstraints(dm, mp_constraints, prev_frames, flat=flat)
+        cache = (key, dc)
+        try:
+            mp_constraints._mgb_cache = cache
+        except AttributeError:      # objects with __slots__: no cache, still correct
+            pass
     return cache[1]
 
 
@@ -89,3 +115,25 @@ class ObjSpatialErrorAndNaturalness(_Objective):
 
 obj_spatial_error_sum = _ObjSpatialErrorSum()
 obj_spatial_error_sum_and_magnitude = _ObjSpatialErrorSumAndMagnitude()
+
+# the reference's own scalar objectives, recognised by function name when a caller assigns the plain
+# function (mg_state_planner.py:250 does `generator.objective = obj_spatial_error_sum_and_magnitude`)
+_KNOWN_OBJECTIVES = {
+    "obj_spatial_error_sum": (1.0, 0.0, 0.0),                   # objective_functions.py:142-160
+    "obj_spatial_error_sum_and_magnitude": (1.0, 0.0, 2.0),     # mg_state_planner.py:110-129
+}
+
+
+def objective_scales(obj):
+    """(error_scale, quality_scale, magnitude_scale) of an objective the device path can evaluate:
+    one of this module's objective objects, or one of the reference's scalar objective FUNCTIONS
+    recognised by `__name__`.  Anything else raises - a term is never dropped silently
+    (SURVEY.md 8(b))."""
+    if isinstance(obj, _Objective):
+        return float(obj.error_scale), float(obj.quality_scale), float(obj.magnitude_scale)
+    name = getattr(obj, "__name__", None)
+    if callable(obj) and name in _KNOWN_OBJECTIVES:
+        return _KNOWN_OBJECTIVES[name]
+    raise MgbError("objective %r is not one of the objectives the device path evaluates (%s, or an object of "
+                   "morphablegraphs_b200.objective_functions); refusing to score with a different formula"
+                   % (obj, ", ".join(sorted(_KNOWN_OBJECTIVES))))

@@ -45,6 +45,16 @@ def is_distributed():
     return dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1
 
 
+def broadcast_seed(seed, group=None):
+    """Rank 0's seed on every rank (one int64 broadcast; NCCL on the GPUs, gloo in the CPU tests)."""
+    import torch
+    import torch.distributed as dist
+    dev = torch.device("cuda", torch.cuda.current_device()) if dist.get_backend(group) == "nccl" else torch.device("cpu")
+    t = torch.tensor([int(seed)], dtype=torch.int64, device=dev)
+    dist.broadcast(t, src=0, group=group)
+    return int(t.item())
+
+
 def exchange_best(cost, index, device=None, group=None):
     """All-gather this rank's best (cost, global index); every rank returns the same winner.
     float64 carries indices exactly up to 2**53."""
@@ -101,7 +111,7 @@ class PeerExchange(object):
         from . import _lib
         self.seq += 1
         if self.seq >= 2 ** 32:
-            self.seq = 1
+            self.seq = 2            # 2**32 - 1 is odd: wrapping to an even value keeps the slot parity alternating
         p = lambda t: C.c_void_p(t.data_ptr())
         with torch.cuda.device(self.device):
             _lib.check(self.lib.mgb_exchange_best(p(best_cost), p(best_idx), p(self.peer_ptrs), self.rank, self.world,
@@ -113,6 +123,7 @@ class PeerExchange(object):
         """Synchronising: raises if a peer's record never arrived."""
         e = int(self.err.item())
         if e:
+            self.err.zero_()        # one timeout must not poison every later step
             from ._lib import MgbError
             raise MgbError("peer exchange timed out waiting for rank %d" % (e - 1))
 

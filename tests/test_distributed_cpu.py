@@ -127,3 +127,30 @@ def test_sharded_tree_build_world2_gloo(max_level):
     for r in range(2):
         _same_cluster_tree(json.loads(out[r]), ref, tol=2e-5)
     assert out[10] == out[11] and out[20] == out[21] == len(tc.data)
+
+
+# ---------------------------------------------------------------------------------------------
+# a generator built WITHOUT a seed must still score the same job on every rank
+# ---------------------------------------------------------------------------------------------
+def _seed_worker(rank, world, port, out):
+    import torch.distributed as dist
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from morphablegraphs_b200 import MotionPrimitiveGenerator
+        gen = MotionPrimitiveGenerator(None, {"n_random_samples": 8}, seed=None)     # rank-local entropy
+        out[rank] = [gen._step_seed() for _ in range(4)]
+        gen2 = MotionPrimitiveGenerator(None, {"n_random_samples": 8}, seed=77)      # explicit: no collective needed
+        out[10 + rank] = [gen2._step_seed() for _ in range(2)]
+    finally:
+        dist.destroy_process_group()
+
+
+def test_unseeded_generator_shares_step_seeds_world2_gloo():
+    import torch.multiprocessing as mp
+    mgr = mp.get_context("spawn").Manager()
+    out = mgr.dict()
+    mp.spawn(_seed_worker, args=(2, _free_port(), out), nprocs=2, join=True)
+    assert list(out[0]) == list(out[1]) and len(set(out[0])) == 4
+    assert list(out[10]) == list(out[11])

@@ -457,3 +457,99 @@ def test_walk_sequence_matches_reference_decisions():
         _check_argmin(st["costs"], idx, min_error)
         assert idx == st["best_idx"], "step %d" % i
         assert abs(min_error - st["min_error"]) <= RTOL * max(1.0, abs(st["min_error"]))
+
+
+# ---------------------------------------------------------------------------
+# boundary holes closed in round 2 (VERDICT r01 "weak" 1, 2)
+# ---------------------------------------------------------------------------
+def test_in_place_constraint_mutation_recompiles():
+    """graph_walk_planner.py:199-203 rewrites `canonical_keyframe` on the SAME constraint objects before every
+    scoring call: the cached device program must follow (content key, objective_functions.constraints_key)."""
+    from oracle import np_oracle as O
+    from morphablegraphs_b200 import MotionPrimitiveGenerator
+    c = Case("s_mixed")
+    gen = MotionPrimitiveGenerator(None, {"n_random_samples": 64}, skeleton=c.skeleton, seed=3)
+    S = np.ascontiguousarray(c.samples)
+    best0, e0 = gen.evaluate_samples_using_constraints(S, c.node, c.constraints, None)
+    ref0 = O.candidate_costs(c.node, c.skeleton, c.constraints, S)
+    assert abs(e0 - ref0.min()) <= RTOL * max(1.0, abs(ref0.min()))
+    con = c.constraints.constraints[0]
+    con.canonical_keyframe = con.canonical_keyframe / 2.0      # in place, same object, same list length
+    con.position[1] += 7.5
+    con.weight_factor = 3.0
+    best1, e1 = gen.evaluate_samples_using_constraints(S, c.node, c.constraints, None)
+    ref1 = O.candidate_costs(c.node, c.skeleton, c.constraints, S)
+    assert abs(ref1.min() - ref0.min()) > 1e-2                  # the mutation matters ...
+    assert abs(e1 - ref1.min()) <= RTOL * max(1.0, abs(ref1.min()))   # ... and the engine saw it
+    _check_argmin(ref1, int(np.where((S == best1).all(axis=1))[0][0]), e1)
+    # unchanged content: the compiled program is reused (same handle object)
+    dc_a = c.constraints._mgb_cache[1]
+    gen.evaluate_samples_using_constraints(S, c.node, c.constraints, None)
+    assert c.constraints._mgb_cache[1] is dc_a
+
+
+def test_prev_frames_content_is_part_of_the_key():
+    from oracle import np_oracle as O
+    from morphablegraphs_b200 import MotionPrimitiveGenerator
+    c = Case("s_nonlocal")
+    gen = MotionPrimitiveGenerator(None, {"n_random_samples": 32, "use_local_coordinates": False}, skeleton=c.skeleton, seed=3)
+    S = np.ascontiguousarray(c.samples)
+    prev = np.array(c.prev_frames, dtype=np.float64)
+    _, e0 = gen.evaluate_samples_using_constraints(S, c.node, c.constraints, prev)
+    prev[-1, 0] += 25.0                                         # same array object, edited in place
+    prev[-1, 2] -= 10.0
+    _, e1 = gen.evaluate_samples_using_constraints(S, c.node, c.constraints, prev)
+    ref1 = O.candidate_costs(c.node, c.skeleton, c.constraints, S, prev)
+    assert abs(e1 - e0) > 1e-2
+    assert abs(e1 - ref1.min()) <= RTOL * max(1.0, abs(ref1.min()))
+
+
+def test_reference_style_plain_function_objective():
+    """mg_state_planner.py:250 assigns the plain function obj_spatial_error_sum_and_magnitude: the engine must
+    score error + 2|s| (mapped by name), and refuse callables it does not know."""
+    from oracle import np_oracle as O
+    from morphablegraphs_b200 import MotionPrimitiveGenerator
+    from morphablegraphs_b200._lib import MgbError
+    c = Case("s_config1")
+    S = np.ascontiguousarray(c.samples)
+    ref = O.candidate_costs(c.node, c.skeleton, c.constraints, S)
+    gen = MotionPrimitiveGenerator(None, {"n_random_samples": 64}, skeleton=c.skeleton, seed=3)
+
+    def obj_spatial_error_sum_and_magnitude(s, data):     # stands for the reference's function object
+        raise AssertionError("the host callable is never used on the device path")
+
+    gen.objective = obj_spatial_error_sum_and_magnitude
+    best, e = gen.evaluate_samples_using_constraints(S, c.node, c.constraints, None)
+    ref_mag = ref + 2.0 * np.linalg.norm(S, axis=1)
+    assert abs(e - ref_mag.min()) <= RTOL * max(1.0, abs(ref_mag.min()))
+    assert abs(e - c.g["magnitude_cost"].min()) <= RTOL * max(1.0, abs(e))
+    s_best = gen.generate_constrained_sample(c.node, c.constraints)       # fused path takes the same scales
+    assert abs(c.constraints.min_error - (O.candidate_costs(c.node, c.skeleton, c.constraints, s_best[None])[0]
+                                          + 2.0 * np.linalg.norm(s_best))) <= 2 * RTOL * max(1.0, c.constraints.min_error)
+    gen.objective = lambda s, data: 0.0
+    with pytest.raises(MgbError):
+        gen.evaluate_samples_using_constraints(S, c.node, c.constraints, None)
+    with pytest.raises(MgbError):
+        gen.generate_constrained_sample(c.node, c.constraints)
+
+
+def test_host_entry_buffer_sequence():
+    """pinned float64 input, then pageable float32, then pageable float64 with more than one
+    chunk (2^18 rows) - the pinned staging buffers must grow with the chunk size."""
+    from oracle import np_oracle as O
+    c = Case("s_config1")
+    from morphablegraphs_b200 import engine
+    dm = engine.DeviceModel(c.node, c.skeleton)
+    dc = engine.DeviceConstraints(dm, c.constraints)
+    n = (1 << 18) + 4097
+    S32 = dm.sample(n, seed=5).cpu().numpy()
+    S64 = S32.astype(np.float64)
+    pinned = torch.from_numpy(S64).pin_memory()
+    r_a = dc.score_host(pinned, k=1, return_cost=True)
+    r_b = dc.score_host(S32, k=1, return_cost=True)
+    r_c = dc.score_host(S64, k=1, return_cost=True)
+    assert np.array_equal(r_a["cost"], r_b["cost"]) and np.array_equal(r_a["cost"], r_c["cost"])
+    assert int(r_a["best_idx"][0]) == int(r_b["best_idx"][0]) == int(r_c["best_idx"][0])
+    sub = np.random.RandomState(0).choice(n, 512, replace=False)
+    ref = O.candidate_costs(c.node, c.skeleton, c.constraints, S64[sub])
+    assert rel_err(r_c["cost"][sub], ref).max() < RTOL

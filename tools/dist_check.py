@@ -33,6 +33,12 @@ def main():
     idx = int(res["best_idx"][0]); e_one = float(res["best_cost"][0])
     s_one = dm.sample(1, seed=seed, index_base=idx, counts=counts, n_total=n)[0].cpu().numpy().astype(np.float64)
     ok = np.array_equal(s_dist, s_one) and e_dist == e_one
+    # a generator built WITHOUT a seed: rank 0's stream is broadcast once, so every rank still returns the same sample
+    gen_u = MotionPrimitiveGenerator(None, {"n_random_samples": n}, skeleton=skeleton, seed=None)
+    s_u = gen_u._get_best_fit_sample_using_gmm(node, mpc)
+    got = [None] * world
+    dist.all_gather_object(got, (s_u.tolist(), float(mpc.min_error)))
+    ok = ok and all(g == got[0] for g in got)
     flags = [None] * world
     dist.all_gather_object(flags, (bool(ok), e_dist, idx))
     if rank == 0:
