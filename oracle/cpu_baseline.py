@@ -141,3 +141,81 @@ def tree_build_rate(golden="s_config1", shape="S", m=10000, seed=4):
     dt = time.perf_counter() - t0
     return {"value": m / dt, "unit": "samples/s", "cores": 1, "seconds": dt,
             "sample": "%d latent samples, 4 subdivisions, max_level 8, recursive build (oracle port of cluster_tree_node_builder.py)" % m}
+
+
+# ---------------------------------------------------------------------------------------------
+# kind = "reference": the reference's OWN loop (MotionPrimitiveGenerator.evaluate_samples_using_constraints,
+# motion_primitive_generator.py:230-261 -> obj_spatial_error_sum -> MotionPrimitiveConstraints.evaluate -> the
+# reference's constraint classes, MotionPrimitive.back_project, MotionSpline.evaluate, sklearn GMM sampler), loaded
+# unmodified by oracle/refload.py from /root/reference or from the staged copy oracle/_ref/ (GPU box).  Only the
+# third-party anim_utils / transformations arithmetic underneath comes from oracle/standin (absent upstream packages).
+# The loop is single-threaded Python; "all host cores" = one independent copy of the loop per core.
+# ---------------------------------------------------------------------------------------------
+def reference_available():
+    from oracle import refload
+    return refload.available()
+
+
+def _init_ref(golden, shape, quality_scale):
+    import io
+    import json
+    import sys
+    from oracle import refload, make_golden
+    from morphablegraphs_b200 import synthetic as syn
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    g = np.load(os.path.join(root, "tests", "golden", golden + ".npz"), allow_pickle=False)
+    sys.stdout = io.StringIO()           # the reference prints "best sample ..." per call and "MGRD is not installed" on import
+    ns = refload.load()
+    cfg = syn.SHAPES[shape]
+    skeleton = refload.make_skeleton(syn.make_skeleton_desc(cfg["n_joints"]))
+    node = refload.make_graph_node(ns, syn.make_model_json(shape, translation_maxima=tuple(g["translation_maxima"])))
+    mpc = make_golden.build_mp_constraints(ns, skeleton, json.loads(str(g["specs_json"])), is_local=bool(g["is_local"]))
+    prev = g["prev_frames"] if "prev_frames" in g.files else None
+    gen = ns.motion_primitive_generator.MotionPrimitiveGenerator.__new__(ns.motion_primitive_generator.MotionPrimitiveGenerator)
+    ref_obj = ns.objective_functions.obj_spatial_error_sum
+    if quality_scale != 0.0:
+        # the reference's scalar naturalness objective never returns (quirk Q7); its usable form is the expression of
+        # objective_functions.py:256 added to the spatial error, evaluated with the reference's own GMM object
+        gmm = node.get_gaussian_mixture_model()
+
+        def objective(s, data):
+            return ref_obj(s, data) - gmm.score(np.asarray(s).reshape(1, -1)) * quality_scale
+        gen.objective = objective
+    else:
+        gen.objective = ref_obj
+    _STATE["ref"] = (gen, node, mpc, prev)
+
+
+def _work_ref(args):
+    seed, n = args
+    gen, node, mpc, prev = _STATE["ref"]
+    np.random.seed(seed)                  # sklearn's sampler draws from numpy's global state (motion_primitive.py:182-189)
+    samples = node.sample_low_dimensional_vectors(n)
+    best, err = gen.evaluate_samples_using_constraints(samples, node, mpc, prev)
+    sys_out = __import__("sys").stdout
+    if hasattr(sys_out, "truncate"):
+        sys_out.seek(0)
+        sys_out.truncate(0)
+    return float(err), n
+
+
+class RefPool(Pool):
+    """Same interface as Pool, every worker running the reference's own per-candidate loop."""
+
+    def _start(self, ctx, golden, shape, quality_scale):
+        self.pool = ctx.Pool(self.workers, initializer=_init_ref, initargs=(golden, shape, quality_scale))
+        self.pool.map(_work_ref, [(i, 2) for i in range(self.workers * 2)])
+
+    def run(self, n_total, seed=0, chunk=None):
+        per = max(1, int(np.ceil(n_total / float(self.workers))))
+        jobs, left, j = [], n_total, 0
+        while left > 0:
+            m = min(per, left)
+            jobs.append((seed * 100003 + j, m))
+            left -= m
+            j += 1
+        t0 = time.perf_counter()
+        res = self.pool.map(_work_ref, jobs)
+        dt = time.perf_counter() - t0
+        assert sum(r[1] for r in res) == n_total
+        return dt

@@ -69,6 +69,26 @@ def make_specs(ns, node, skeleton, F, rng, which):
         specs.append(syn.spec("GlobalTransformConstraint",
                               syn.position_constraint_desc("RightFoot", pos(0, "RightFoot", F - 1), F - 1, F), 1.0, 1.0))
         return specs
+    if which == "cfg4":
+        # right-hand position at F-1, root position + 2-D direction at F-1, transition
+        # PoseConstraint (5 joints) at keyframes 0/1 (pose at 0, root velocity from 1); naturalness is part of the objective
+        specs.append(syn.spec("GlobalTransformConstraint",
+                              syn.position_constraint_desc("RightHand", pos(0, "RightHand", F - 1), F - 1, F), 1.0, 1.0))
+        specs.append(syn.spec("GlobalTransformConstraint",
+                              syn.position_constraint_desc("Hips", pos(1, "Hips", F - 1), F - 1, F), 1.0, 1.0))
+        specs.append(syn.spec("Direction2DConstraint",
+                              {"canonical_keyframe": F - 1, "dir_vector": [0.3, 0.0, 1.0],
+                               "semanticAnnotation": syn.sem()}, 1.0, 0.05))
+        names = ["Hips", "LeftHand", "RightHand", "LeftFoot", "RightFoot"]
+        f0 = spl[2].evaluate(0)
+        f1 = spl[2].evaluate(1)
+        cloud = [skeleton.nodes[n].get_global_position(f0).tolist() for n in names]
+        vel = (skeleton.nodes["Hips"].get_global_position(f1) - np.array(cloud[0])).tolist()
+        specs.append(syn.spec("PoseConstraint",
+                              {"canonical_keyframe": 0, "frame_constraint": cloud, "velocity_constraint": vel,
+                               "semanticAnnotation": syn.sem("start"), "node_names": names,
+                               "weights": [skeleton.joint_weight_map[n] for n in names]}, 1.0, 1.0))
+        return specs
     # mixed set: every keyframe constraint type of SURVEY.md Appendix C
     p = pos(0, "RightHand", F - 1)
     q = skeleton.nodes["RightHand"].get_global_orientation_quaternion(spl[1].evaluate(F - 1)).tolist()
@@ -110,7 +130,9 @@ def make_specs(ns, node, skeleton, F, rng, which):
     return specs
 
 
-def run_case(ns, shape, which, n_samples, seed, translation_maxima=(1.0, 1.0, 1.0), non_local=False, n_joints=None):
+def run_case(ns, shape, which, n_samples, seed, translation_maxima=(1.0, 1.0, 1.0), non_local=False, n_joints=None, n_full=None):
+    """n_full: number of leading candidates for which the per-stage outputs (coefficients, key frames, FK positions,
+    motion vectors) are stored; the costs / terms / arg-min always cover all n_samples."""
     cfg = syn.SHAPES[shape]
     F = cfg["n_frames"]
     mj = syn.make_model_json(shape, translation_maxima=translation_maxima)
@@ -142,19 +164,21 @@ def run_case(ns, shape, which, n_samples, seed, translation_maxima=(1.0, 1.0, 1.
     if prev_frames is not None:
         out["prev_frames"] = np.asarray(prev_frames)
     # --- reference outputs -------------------------------------------------
-    splines = [node.back_project(s, use_time_parameters=False) for s in S]
+    n_full = n_samples if n_full is None else min(n_full, n_samples)
+    out["n_full"] = np.array(n_full)
+    splines = [node.back_project(s, use_time_parameters=False) for s in S[:n_full]]
     out["coeffs"] = np.array([sp.coeffs.copy() for sp in splines])
     key_times = sorted({float(sp_["desc"]["canonical_keyframe"]) for sp_ in specs
                         if sp_["desc"].get("canonical_keyframe") is not None})
     out["key_times"] = np.array(key_times)
     out["key_frames"] = np.array([[sp.evaluate(t) for t in key_times] for sp in splines])
-    n_mv = min(4, n_samples)
+    n_mv = min(4, n_full)
     with _quiet():
         out["motion_vectors"] = np.array([splines[i].get_motion_vector() for i in range(n_mv)])
     fk_names = list(skel_desc["nodes"].keys())
     out["fk_names_json"] = np.array(json.dumps(fk_names))
     out["fk_positions"] = np.array([[skeleton.nodes[n].get_global_position(out["key_frames"][i, -1])
-                                     for n in fk_names] for i in range(n_samples)])
+                                     for n in fk_names] for i in range(n_full)])
     # per-term errors and total cost through the reference's own loop
     terms = np.zeros((len(mpc.constraints), n_samples))
     costs = np.zeros(n_samples)
@@ -185,6 +209,77 @@ def run_case(ns, shape, which, n_samples, seed, translation_maxima=(1.0, 1.0, 1.
     out["naturalness_cost"] = costs * 1.0 + 0.1 * (-out["logpdf"])   # error_scale 1, quality_scale 0.1
     out["magnitude_cost"] = costs + 2.0 * np.linalg.norm(S, axis=1)   # mg_state_planner.py:129
     return out, (node, skeleton, mpc, S, prev_frames)
+
+
+def run_local_case(ns, shape="S", n_samples=64, seed=2031):
+    """a8: a GLOBAL constraint set (every constraint type, non-trivial weights) with a non-identity
+    `aligning_transform`, brought to the primitive's local frame by the reference's own
+    `transform_constraints_to_local_cos` (motion_primitive_constraints.py:268-378, incl. quirk Q5: position /
+    relative / CA constraints come back with weight 1.0 and without their orientation), then scored by the
+    reference's loop - what `generate_constrained_sample` does on the default `use_local_coordinates=True` path."""
+    from tests.common import describe_constraint
+    from transformations import quaternion_matrix, quaternion_about_axis
+    cfg = syn.SHAPES[shape]
+    F = cfg["n_frames"]
+    mj = syn.make_model_json(shape)
+    skeleton = refload.make_skeleton(syn.make_skeleton_desc(cfg["n_joints"]))
+    node = refload.make_graph_node(ns, mj)
+    np.random.seed(seed)
+    local_specs = make_specs(ns, node, skeleton, F, None, "mixed")
+    for i, sp_ in enumerate(local_specs):          # weights that Q5 must reset (or keep) visibly
+        sp_["weight"] = [2.5, 0.5, 1.7, 0.02, 1.5, 1.3, 0.7, 2.0, 3.0][i]
+    S = node.sample_low_dimensional_vectors(n_samples)
+    T = quaternion_matrix(quaternion_about_axis(0.9, [0, 1, 0]))
+    T[:3, 3] = [250.0, 0.0, -130.0]
+    # express the targets in the GLOBAL frame: x_global = T x_local (directions without the translation)
+    def gp(p, w=1.0):
+        if p is None:
+            return None
+        idx = [i for i in range(3) if p[i] is None]  # masked axis (the rotation is about y, so a masked height stays masked)
+        q = np.dot(T, [0.0 if x is None else x for x in p] + [w])[:3].tolist()
+        for i in idx:
+            q[i] = None
+        return q
+    specs = json.loads(json.dumps(local_specs))
+    for sp_ in specs:
+        d = sp_["desc"]
+        if sp_["class"] in ("GlobalTransformConstraint", "RelativeTransformConstraint", "GlobalTransformCAConstraint", "LookAtConstraint"):
+            d["position"] = gp(d["position"])
+        elif sp_["class"] == "Direction2DConstraint":
+            d["dir_vector"] = gp(d["dir_vector"], 0.0)
+        elif sp_["class"] == "PoseConstraint":
+            d["frame_constraint"] = [gp(p) for p in d["frame_constraint"]]
+        elif sp_["class"] == "TwoHandConstraintSet":
+            d["positions"] = [gp(p) for p in d["positions"]]
+        elif sp_["class"] == "FeetConstraint":
+            d["left"], d["right"] = gp(d["left"]), gp(d["right"])
+    mpc = build_mp_constraints(ns, skeleton, specs, is_local=False)
+    mpc.aligning_transform = T
+    mpc.use_local_optimization = True
+    with _quiet():
+        local = mpc.transform_constraints_to_local_cos()
+    assert local is not mpc and local.is_local
+    out = {"samples": S, "specs_json": np.array(json.dumps(specs)), "shape": np.array(shape),
+           "translation_maxima": np.array([1.0, 1.0, 1.0]), "is_local": np.array(False), "aligning_transform": T,
+           "local_desc_json": np.array(json.dumps([describe_constraint(c) for c in local.constraints])),
+           "local_use_local_optimization": np.array(bool(local.use_local_optimization))}
+    obj = ns.objective_functions.obj_spatial_error_sum
+    terms = np.zeros((len(local.constraints), n_samples))
+    costs = np.zeros(n_samples)
+    with _quiet():
+        for i, s_ in enumerate(S):
+            sp = node.back_project(s_, use_time_parameters=False)
+            for j, c in enumerate(local.constraints):
+                terms[j, i] = c.evaluate_motion_spline(sp)
+            costs[i] = obj(s_, (node, local, None))
+        gen = ns.motion_primitive_generator.MotionPrimitiveGenerator.__new__(ns.motion_primitive_generator.MotionPrimitiveGenerator)
+        gen.objective = obj
+        best, min_error = gen.evaluate_samples_using_constraints(S, node, local, None)
+    out["terms"] = terms
+    out["costs"] = costs
+    out["best_idx"] = np.array(int(np.where((S == best).all(axis=1))[0][0]))
+    out["min_error"] = np.array(min_error)
+    return out
 
 
 def run_walk_case(ns, n_steps=6, n_samples=48, seed=31):
@@ -371,6 +466,20 @@ def main():
         np.savez_compressed(os.path.join(GOLDEN_DIR, "s_walk.npz"), **out)
         print("s_walk", [int(out["step%d_best_idx" % i]) for i in range(len(out["order"]))],
               [float(out["step%d_min_error" % i]) for i in range(len(out["order"]))])
+        return 0
+    if "--only-round2" in sys.argv:
+        # fixtures added in round 2: reference-made goldens at the sizes SURVEY.md 8(d) states
+        out = run_local_case(ns)
+        np.savez_compressed(os.path.join(GOLDEN_DIR, "s_local.npz"), **out)
+        print("s_local", out["costs"][:3], int(out["best_idx"]), float(out["min_error"]))
+        for name, kw in (("s_config1_10k", dict(shape="S", which="config1", n_samples=10000, seed=2024, n_full=16)),
+                         ("l_cfg4", dict(shape="L", which="cfg4", n_samples=1000, seed=2032, n_full=8)),
+                         ("l_mixed_1k", dict(shape="L", which="mixed", n_samples=1000, seed=2029, n_full=4))):
+            if "--skip-" + name in sys.argv:
+                continue
+            out, _ = run_case(ns, **kw)
+            np.savez_compressed(os.path.join(GOLDEN_DIR, name + ".npz"), **out)
+            print(name, "costs[:3]", out["costs"][:3], "best", int(out["best_idx"]), float(out["min_error"]), flush=True)
         return 0
     if "--only-tree" in sys.argv:
         out = run_tree_case(ns)

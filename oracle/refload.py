@@ -19,13 +19,43 @@ import os
 import sys
 import types
 
-REFERENCE_ROOT = "/root/reference"
 _PKG = "morphablegraphs"
-_STANDIN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "standin")
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_STANDIN = os.path.join(_HERE, "standin")
+# The reference tree where it lies (build container), else the staged copy of its hot-path modules that
+# `stage_reference()` (called by __graft_entry__.build()) puts under the git-ignored oracle/_ref/ so that the
+# reference's OWN loop can be timed on the GPU box, where /root/reference does not exist.
+SOURCE_ROOT = "/root/reference"
+STAGED_ROOT = os.path.join(_HERE, "_ref")
+REFERENCE_ROOT = SOURCE_ROOT if os.path.isdir(os.path.join(SOURCE_ROOT, _PKG)) else STAGED_ROOT
 
 
 def available():
     return os.path.isdir(os.path.join(REFERENCE_ROOT, _PKG))
+
+
+def stage_reference():
+    """Copy the reference modules this loader executes (and nothing else) from /root/reference into
+    oracle/_ref/, unmodified, keeping their relative paths.  oracle/_ref/ is listed in .gitignore (never
+    committed) but not in .gpurunignore (it travels to the GPU box like a built .so).  Returns the number
+    of files staged; a no-op when /root/reference is absent."""
+    import shutil
+    if not os.path.isdir(os.path.join(SOURCE_ROOT, _PKG)) or REFERENCE_ROOT != SOURCE_ROOT:
+        return 0
+    load()
+    n = 0
+    for name, mod in list(sys.modules.items()):
+        f = getattr(mod, "__file__", None)
+        if not (name == _PKG or name.startswith(_PKG + ".")) or not f or not f.startswith(SOURCE_ROOT + os.sep):
+            continue
+        dst = os.path.join(STAGED_ROOT, os.path.relpath(f, SOURCE_ROOT))
+        os.makedirs(os.path.dirname(dst), exist_ok=True)
+        shutil.copyfile(f, dst)
+        n += 1
+    with open(os.path.join(STAGED_ROOT, "README"), "w") as fh:
+        fh.write("Unmodified copies of %d reference modules (dfki-asr/morphablegraphs) staged by oracle/refload.py:stage_reference()\n"
+                 "for the CPU baseline on the GPU box.  Git-ignored; never edit, never commit.\n" % n)
+    return n
 
 
 def _stub(name, relpath, **attrs):

@@ -553,3 +553,60 @@ def test_host_entry_buffer_sequence():
     sub = np.random.RandomState(0).choice(n, 512, replace=False)
     ref = O.candidate_costs(c.node, c.skeleton, c.constraints, S64[sub])
     assert rel_err(r_c["cost"][sub], ref).max() < RTOL
+
+
+# ---------------------------------------------------------------------------
+# reference-made goldens at the sizes SURVEY.md 8(d) states (round 2)
+# ---------------------------------------------------------------------------
+@pytest.mark.parametrize("name", ["s_config1_10k", "l_cfg4", "l_mixed_1k"])
+def test_reference_goldens_at_size(name):
+    """config 1's 10 000 reference-drawn samples, config 4's constraint set on the L model (1000 reference-scored
+    candidates), the mixed L set at 1000: GPU costs / terms / arg-min against the reference's own loop."""
+    from morphablegraphs_b200 import engine
+    c = Case(name)
+    g = c.g
+    dm = engine.DeviceModel(c.node, c.skeleton)
+    dc = engine.DeviceConstraints(dm, c.constraints)
+    S = torch.as_tensor(c.samples, device="cuda")
+    res = dc.score(S, k=1, return_cost=True, return_terms=True)
+    assert rel_err(res["terms"].cpu().numpy(), g["terms"]).max() < RTOL
+    assert rel_err(res["cost"].cpu().numpy(), g["costs"]).max() < RTOL
+    _check_argmin(g["costs"], int(res["best_idx"][0]), float(res["best_cost"][0]))
+    nat = dc.score(S, k=1, return_cost=True, quality_scale=0.1)
+    assert rel_err(nat["cost"].cpu().numpy(), g["naturalness_cost"]).max() < RTOL
+    _check_argmin(g["naturalness_cost"], int(nat["best_idx"][0]), float(nat["best_cost"][0]))
+    # the reference-facing host entry on the same float64 array
+    h = dc.score_host(np.ascontiguousarray(c.samples), k=1, return_cost=True, quality_scale=0.1)
+    assert np.array_equal(h["cost"], nat["cost"].cpu().numpy()) and int(h["best_idx"][0]) == int(nat["best_idx"][0])
+
+
+def test_local_coordinates_default_path():
+    """a8 on the device path: a GLOBAL constraint set with a non-identity aligning_transform goes through
+    generate_constrained_sample(use_local_coordinates=True) = transform_constraints_to_local_cos (quirk Q5) + scoring;
+    costs against the reference's loop on the reference-transformed set (tests/golden/s_local.npz)."""
+    from oracle import np_oracle as O
+    from morphablegraphs_b200 import MotionPrimitiveGenerator
+    c = Case("s_local")
+    g = c.g
+    c.constraints.aligning_transform = np.array(g["aligning_transform"])
+    gen = MotionPrimitiveGenerator(None, {"n_random_samples": 4096, "use_local_coordinates": True}, skeleton=c.skeleton, seed=5)
+    local = c.constraints.transform_constraints_to_local_cos()
+    S = np.ascontiguousarray(c.samples)
+    best, e = gen.evaluate_samples_using_constraints(S, c.node, local, None)
+    assert int(np.where((S == best).all(axis=1))[0][0]) == int(g["best_idx"])
+    assert abs(e - float(g["min_error"])) <= RTOL * max(1.0, abs(e))
+    from morphablegraphs_b200 import engine
+    dc = engine.DeviceConstraints(engine.DeviceModel(c.node, c.skeleton), local)
+    res = dc.score(torch.as_tensor(S, device="cuda"), k=1, return_cost=True, return_terms=True)
+    assert rel_err(res["terms"].cpu().numpy(), g["terms"]).max() < RTOL
+    assert rel_err(res["cost"].cpu().numpy(), g["costs"]).max() < RTOL
+    # the whole generator call on the global set: the winner's error is its cost under the LOCAL set
+    s = gen.generate_constrained_sample(c.node, c.constraints)
+    ref = O.candidate_costs(c.node, c.skeleton, local, s[None])[0]
+    assert abs(c.constraints.min_error - ref) <= 2 * RTOL * max(1.0, abs(ref))
+    assert c.constraints.evaluations == 4096
+    # the global set scored WITHOUT the transform is a different (much larger) number: the transform is not a no-op
+    c.constraints.is_local = True
+    wrong = O.candidate_costs(c.node, c.skeleton, c.constraints, s[None])[0]
+    c.constraints.is_local = False
+    assert abs(wrong - ref) > 10.0

@@ -1,0 +1,151 @@
+"""Round-2 fixtures, CPU side: the reference-made goldens at the sizes SURVEY.md 8(d) states pin the oracle
+(`s_config1_10k`: config 1's 10 000 reference-drawn samples; `l_cfg4`: config 4's constraint set on the L model;
+`l_mixed_1k`), the local-frame transform a8 (`s_local`: the reference's own transform_constraints_to_local_cos
+incl. quirk Q5) pins the product's host mirror, and the reference's OWN objects (loaded unmodified through
+oracle/refload.py) flatten to the same descriptor tables as the mirror classes."""
+import ctypes as C
+import json
+
+import numpy as np
+import pytest
+
+from oracle import np_oracle as O
+from tests.common import Case, rel_err, describe_constraint, assert_same_description
+from morphablegraphs_b200 import engine, _lib
+from morphablegraphs_b200 import synthetic as syn
+from morphablegraphs_b200 import objective_functions as OF
+
+BIG = ["s_config1_10k", "l_cfg4", "l_mixed_1k"]
+
+
+@pytest.mark.parametrize("name", BIG)
+def test_oracle_against_reference_costs_at_size(name):
+    c = Case(name)
+    g = c.g
+    n = len(c.samples)
+    assert n >= 1000
+    cost, terms = O.candidate_costs(c.node, c.skeleton, c.constraints, c.samples, None, return_terms=True)
+    assert rel_err(terms, g["terms"]).max() < 1e-8
+    assert rel_err(cost, g["costs"]).max() < 1e-8
+    idx, err = O.first_argmin(cost)
+    assert idx == int(g["best_idx"]) and abs(err - float(g["min_error"])) < 1e-8 * max(1.0, abs(err))
+    ma = O.ModelArrays(c.node)
+    assert rel_err(O.gmm_logpdf(ma, c.samples), g["logpdf"]).max() < 1e-9
+    c_nat = O.candidate_costs(c.node, c.skeleton, c.constraints, c.samples, None, error_scale=1.0, quality_scale=0.1)
+    assert rel_err(c_nat, g["naturalness_cost"]).max() < 1e-8
+    nf = int(g["n_full"])
+    coeffs = O.back_project_coeffs(ma, c.samples[:nf])
+    assert rel_err(coeffs, g["coeffs"]).max() < 1e-9
+    assert rel_err(O.eval_frames(ma, coeffs, g["key_times"]), g["key_frames"]).max() < 1e-9
+
+
+def test_config4_constraint_set_is_the_surveys():
+    """right-hand position at F-1, root position + 2-D direction at F-1, 5-joint PoseConstraint
+    at keyframes 0 / 1."""
+    c = Case("l_cfg4")
+    F = syn.SHAPES["L"]["n_frames"]
+    kinds = [(s["class"], s["desc"].get("joint"), s["desc"]["canonical_keyframe"]) for s in c.specs]
+    assert kinds == [("GlobalTransformConstraint", "RightHand", F - 1), ("GlobalTransformConstraint", "Hips", F - 1),
+                     ("Direction2DConstraint", None, F - 1), ("PoseConstraint", None, 0)]
+    pose = c.specs[3]["desc"]
+    assert len(pose["node_names"]) == 5 and pose["velocity_constraint"] is not None
+
+
+# ---------------------------------------------------------------------------
+# a8: transform_constraints_to_local_cos
+# ---------------------------------------------------------------------------
+@pytest.fixture(scope="module")
+def local_case():
+    c = Case("s_local")
+    c.constraints.aligning_transform = np.array(c.g["aligning_transform"])
+    c.constraints.use_local_optimization = True
+    return c
+
+
+def test_local_transform_matches_reference(local_case):
+    c = local_case
+    ref = json.loads(str(c.g["local_desc_json"]))
+    assert not c.constraints.is_local
+    local = c.constraints.transform_constraints_to_local_cos()
+    assert local is not c.constraints and local.is_local and local.skeleton is c.skeleton
+    assert local.use_local_optimization == bool(c.g["local_use_local_optimization"])
+    assert local.start_pose == {"orientation": [0, 0, 0], "position": [0, 0, 0]}
+    mine = [describe_constraint(x) for x in local.constraints]
+    assert len(mine) == len(ref)
+    for a, b in zip(mine, ref):
+        assert_same_description(a, b)
+    # quirk Q5, spelled out: position / relative / CA come back with weight 1.0 and no orientation; the others keep theirs
+    by_type = {d["type"]: d for d in mine}
+    src = {s_["class"]: s_["weight"] for s_ in c.specs}
+    assert by_type["keyframe_relative_position"]["weight_factor"] == 1.0 and src["RelativeTransformConstraint"] != 1.0
+    assert by_type["ca_constraint"]["weight_factor"] == 1.0 and src["GlobalTransformCAConstraint"] != 1.0
+    assert all(d["weight_factor"] == 1.0 and d["orientation"] is None for d in mine if d["type"] == "keyframe_position")
+    for cls, typ in (("Direction2DConstraint", "keyframe_2d_direction"), ("PoseConstraint", "keyframe_pose"),
+                     ("TwoHandConstraintSet", "keyframe_two_hands"), ("FeetConstraint", "keyframe_feet"),
+                     ("LookAtConstraint", "keyframe_look_at")):
+        assert by_type[typ]["weight_factor"] == src[cls] != 1.0
+    # already local / no transform: returned unchanged (motion_primitive_constraints.py:269-270)
+    assert local.transform_constraints_to_local_cos() is local
+
+
+def test_oracle_scores_the_local_set_like_the_reference(local_case):
+    c = local_case
+    local = c.constraints.transform_constraints_to_local_cos()
+    cost, terms = O.candidate_costs(c.node, c.skeleton, local, c.samples, None, return_terms=True)
+    assert rel_err(terms, c.g["terms"]).max() < 1e-8
+    assert rel_err(cost, c.g["costs"]).max() < 1e-8
+    assert O.first_argmin(cost)[0] == int(c.g["best_idx"])
+
+
+# ---------------------------------------------------------------------------
+# "accepts the reference's own objects": reference classes -> the same flat tables as the mirror classes
+# ---------------------------------------------------------------------------
+class _StubModel(object):
+    def __init__(self, skeleton):
+        self.node_index = engine.pack_skeleton(skeleton)["index"]
+        self.skeleton = skeleton
+
+
+def _flat_bytes(flat):
+    descs, n, parr, n_points, times = flat
+    return (n, n_points, bytes(descs)[:n * C.sizeof(_lib.ConstraintDesc)], bytes(parr)[:n_points * C.sizeof(_lib.PosePoint)],
+            times.tobytes())
+
+
+@pytest.mark.parametrize("name", ["s_mixed", "s_local", "l_cfg4"])
+def test_reference_objects_flatten_like_the_mirror(name):
+    from oracle import refload, make_golden
+    if not refload.available():
+        pytest.skip("reference modules not present (neither /root/reference nor oracle/_ref)")
+    ns = refload.load()
+    c = Case(name)
+    ref_skel = refload.make_skeleton(c.skeleton_desc)                   # anim_utils stand-in Skeleton
+    ref_node = refload.make_graph_node(ns, c.model_json)                # the reference's MotionStateGraphNode
+    ref_mpc = make_golden.build_mp_constraints(ns, ref_skel, c.specs, is_local=bool(c.g["is_local"]))   # reference classes
+    assert type(ref_mpc).__module__.startswith("morphablegraphs.") and type(ref_mpc.constraints[0]).__module__.startswith("morphablegraphs.")
+    if name == "s_local":
+        ref_mpc.aligning_transform = np.array(c.g["aligning_transform"])
+        c.constraints.aligning_transform = np.array(c.g["aligning_transform"])
+        ref_mpc, mine = ref_mpc.transform_constraints_to_local_cos(), c.constraints.transform_constraints_to_local_cos()
+    else:
+        mine = c.constraints
+    # skeleton packing reads the same fields of either skeleton class
+    a, b = engine.pack_skeleton(ref_skel), engine.pack_skeleton(c.skeleton)
+    assert a["names"] == b["names"] and a["aligning_node"] == b["aligning_node"]
+    for k in ("parent", "type", "channel", "offset", "rotation"):
+        assert np.array_equal(a[k], b[k]), k
+    # constraint tables
+    fa = engine.flatten_constraints(_StubModel(ref_skel), ref_mpc)
+    fb = engine.flatten_constraints(_StubModel(c.skeleton), mine)
+    assert _flat_bytes(fa) == _flat_bytes(fb)
+    # and therefore the same cache key content
+    ka = OF.constraints_key(None, fa, ref_mpc, None)
+    kb = OF.constraints_key(None, fb, mine, None)
+    assert ka[1:] == kb[1:]
+    # model arrays the packer reads (DeviceModel.__init__): identical numbers from the reference's model object
+    mp_ref, mp_mine = ref_node.motion_primitive, c.node.motion_primitive
+    for k in ("eigen_vectors", "mean_vector", "knots"):
+        assert np.array_equal(np.asarray(mp_ref.s_pca[k]), np.asarray(mp_mine.s_pca[k])), k
+    assert np.array_equal(mp_ref.translation_maxima, mp_mine.translation_maxima)
+    gr, gm = mp_ref.gaussian_mixture_model, mp_mine.gaussian_mixture_model
+    assert np.array_equal(gr.weights_, gm.weights_) and np.array_equal(gr.means_, gm.means_) and np.array_equal(gr.covariances_, gm.covariances_)
