@@ -32,7 +32,7 @@ def build(force=False, verbose=False):
     objdir = os.path.join(CSRC, "build")
     os.makedirs(objdir, exist_ok=True)
     hdr_time = max(os.path.getmtime(p) for p in headers)
-    flags = [f for f in NVCC_FLAGS if f != "-shared"]
+    flags = [f for f in NVCC_FLAGS if f != "-shared"] + os.environ.get("MGB_NVCC_EXTRA", "").split()   # e.g. -DMGB_TC_PROFILE (diagnostic builds)
     jobs = []
     objs = []
     for src in srcs:

@@ -96,8 +96,8 @@ struct TcBars {
     unsigned long long* b_empty;  // [TC_MAX_STAGES]
     unsigned long long* a_full;
     unsigned long long* a_empty;
-    unsigned long long* t_full;   // [3]
-    unsigned long long* t_empty;  // [3]
+    unsigned long long* t_full;   // [2 owners][2 buffers]: accumulator buffer b holds a finished chunk for consumer group `owner`
+    unsigned long long* t_empty;  // [2 buffers]
 };
 
 __device__ __forceinline__ TcBars tc_bars(unsigned char* base) {
@@ -108,7 +108,7 @@ __device__ __forceinline__ TcBars tc_bars(unsigned char* base) {
     b.a_full = p + 2 * TC_MAX_STAGES;
     b.a_empty = p + 2 * TC_MAX_STAGES + 1;
     b.t_full = p + 2 * TC_MAX_STAGES + 2;
-    b.t_empty = p + 2 * TC_MAX_STAGES + 5;
+    b.t_empty = p + 2 * TC_MAX_STAGES + 6;
     return b;
 }
 
@@ -123,56 +123,48 @@ struct TcSegs {
                                         // component only, against the first of TWO fills of the A tile (z, then s = mu + L z)
     int tile_first[MGB_MAX_GMM + 1];    // sampling mode: first tile of every component (tiles never straddle components)
     int G;
-    int split_q, split_g;               // both >= 0: the chunks of these two operands are issued INTERLEAVED (q0 g0 q1 g1 ...),
-                                        // split_q's (and the sampling operand's) into TMEM buffer 0, split_g's into buffer 1, so
-                                        // that each operand has its own consumer group and neither waits behind the other
+    int il_q, il_g;                     // both >= 0: the chunks of these two operands are issued INTERLEAVED (q0 q1 g.. q2 g.. ...):
+                                        // il_q's chunks are consumed by epilogue group 0, il_g's by group 1
 };
 
-// chunk schedule of one tile, shared by the B producer and the MMA issuer: f(segment, chunk, stream, is_sampling).
-// stream -1: all chunks alternate between the two 256-column TMEM buffers.  Split mode: stream 0 (sampling operand and
-// split_q) alternates between two 128-column buffers at columns 0 / 128, stream 1 (split_g) owns the 256 columns at 256;
-// the quad stream is issued one chunk ahead and the GMM chunks are spread evenly between the quad chunks, so that the
-// quad consumer (the longer of the two) is not held up by GMM chunks.
+// Accumulators: every chunk of a tile, whatever its operand, goes to the two 256-column TMEM buffers in turn (chunk number
+// & 1).  A chunk has an OWNER - the epilogue group that consumes it: 0 = group 0 (quads), 1 = group 1 (GMM), 2 = both (the
+// sampling chunk: both groups read their half of s and refill the A tile; group 0 releases the buffer).  Every owner has its
+// own "full" barrier per buffer, so a group only ever waits on barriers all of whose phases it observes (a parity wait is
+// ambiguous for a waiter that can fall two phases behind).
+enum { TC_OWN_G0 = 0, TC_OWN_G1 = 1, TC_OWN_BOTH = 2 };
+
+// chunk schedule of one tile, shared by the B producer, the MMA issuer and the consumer groups: f(segment, chunk, owner,
+// is_sampling).  Interleaved mode: the quad stream is issued one chunk ahead and the GMM chunks are spread evenly between
+// the quad chunks, so that the quad consumer (the constraint program: the longer of the two) always has its next chunk ready.
 template <typename F>
 __device__ __forceinline__ void tc_for_each_chunk(const TcSegs& S, int gcomp, F f) {
-    const bool split = S.split_q >= 0 && S.split_g >= 0;
+    const bool il = S.il_q >= 0 && S.il_g >= 0;
     for (int sg = 0; sg < S.n; ++sg) {
         if (sg == S.samp_seg) {
-            f(sg, gcomp, split ? 0 : -1, true);
-        } else if (!split) {
-            for (int c = 0; c < S.seg[sg].n_nc(); ++c) f(sg, c, -1, false);
+            f(sg, gcomp, (int)TC_OWN_BOTH, true);
+        } else if (!il) {
+            for (int c = 0; c < S.seg[sg].n_nc(); ++c) f(sg, c, sg == S.il_g ? (int)TC_OWN_G1 : (int)TC_OWN_G0, false);
         }
     }
-    if (split) {
-        const int nq = S.seg[S.split_q].n_nc(), ng = S.seg[S.split_g].n_nc();
+    if (il) {
+        const int nq = S.seg[S.il_q].n_nc(), ng = S.seg[S.il_g].n_nc();
         int qi = 0, gi = 0;
-        if (nq > 0) f(S.split_q, qi++, 0, false);
+        if (nq > 0) f(S.il_q, qi++, (int)TC_OWN_G0, false);
         while (qi < nq || gi < ng) {
-            if (qi < nq) f(S.split_q, qi++, 0, false);
+            if (qi < nq) f(S.il_q, qi++, (int)TC_OWN_G0, false);
             // the GMM chunks are spread evenly over the quad chunks (ng / nq per quad chunk), the rest after the last one
-            while (gi < ng && (qi >= nq || (long long)gi * nq < (long long)(qi - 1) * ng)) f(S.split_g, gi++, 1, false);
+            while (gi < ng && (qi >= nq || (long long)gi * nq < (long long)(qi - 1) * ng)) f(S.il_g, gi++, (int)TC_OWN_G1, false);
         }
     }
 }
 
-// TMEM buffer, barrier phase and first column of the next chunk of a stream (cc: chunks so far, all streams; cq / ug:
-// chunks so far of stream 0 / 1)
-struct TcSlot {
-    unsigned int buf, phase, col;
-};
-__device__ __forceinline__ TcSlot tc_next_slot(int stream, unsigned int& cc, unsigned int& cq, unsigned int& ug) {
-    TcSlot r;
-    if (stream < 0) {
-        r.buf = cc & 1u; r.phase = (cc >> 1) & 1u; r.col = r.buf * TC_BUF_COLS;
-    } else if (stream == 0) {
-        r.buf = cq & 1u; r.phase = (cq >> 1) & 1u; r.col = r.buf * (TC_BUF_COLS / 2);
-        ++cq;
-    } else {
-        r.buf = 2u; r.phase = ug & 1u; r.col = TC_BUF_COLS;
-        ++ug;
-    }
-    ++cc;
-    return r;
+// phase bit of "full" barrier (owner, buf), kept as one bit each of a 4-bit mask
+__device__ __forceinline__ unsigned int tc_full_phase(unsigned int& mask, int owner, unsigned int buf) {
+    const unsigned int bit = 1u << (2 * owner + buf);
+    const unsigned int ph = (mask & bit) ? 1u : 0u;
+    mask ^= bit;
+    return ph;
 }
 
 // component of tile T (sampling mode)
@@ -216,13 +208,13 @@ __device__ __forceinline__ void tc_b_producer(const TcSegs& S, unsigned char* sm
 __device__ long long g_tc_cycles[16];
 #endif
 
-// warp 1, one lane: all MMAs of this CTA.  A chunk accumulates into the TMEM buffer its schedule entry names
-// (split mode) or into alternating buffers (chunk number cc & 1); a buffer's barrier phase is the number of times
-// it has been used.
+// warp 1, one lane: all MMAs of this CTA.  Chunk number cc accumulates into TMEM buffer cc & 1; the finished chunk is
+// published on the "full" barrier(s) of its owner(s).  all_own0: every chunk is published on owner 0's barriers (the
+// back-projection kernel, whose epilogue warps all drain every chunk).
 __device__ __forceinline__ void tc_mma_issuer(const TcSegs& S, uint32_t a_hi_addr, uint32_t a_lo_addr, uint32_t stage_addr, size_t stage_bytes,
                                               int nst, const TcBars& bars, uint32_t tmem_base, long long my_tiles,
-                                              const int* tile_first = nullptr) {
-    unsigned int cc = 0, cq = 0, ug = 0, fill = 0;
+                                              const int* tile_first = nullptr, bool all_own0 = false) {
+    unsigned int cc = 0, fill = 0;
     const uint32_t A_LBO = TC_M * 16, SBO = 128;
     // descriptors differ only in their 14-bit start-address field (bytes >> 4): build them once, then add
     const uint64_t da_hi0 = mgb_umma_desc(a_hi_addr, A_LBO, SBO), da_lo0 = mgb_umma_desc(a_lo_addr, A_LBO, SBO);
@@ -242,15 +234,15 @@ __device__ __forceinline__ void tc_mma_issuer(const TcSegs& S, uint32_t a_hi_add
         MGB_TC_W(w_af, mgb_mbar_wait(bars.a_full, fill & 1u))
         ++fill;
         mgb_tc_fence_after();
-        tc_for_each_chunk(S, gcomp, [&](int sg, int c, int want_buf, bool samp) {
+        tc_for_each_chunk(S, gcomp, [&](int sg, int c, int owner, bool samp) {
             const TcB& B = S.seg[sg];
             const int KC = B.KC, Kp = B.Kp;
             const int wc = B.wc(c);
-            const TcSlot slot = tc_next_slot(want_buf, cc, cq, ug);
-            const unsigned int buf = slot.buf;
-            MGB_TC_W(w_te, mgb_mbar_wait(&bars.t_empty[buf], slot.phase ^ 1u))
+            const unsigned int buf = cc & 1u;
+            MGB_TC_W(w_te, mgb_mbar_wait(&bars.t_empty[buf], ((cc >> 1) & 1u) ^ 1u))
+            ++cc;
             mgb_tc_fence_after();
-            const uint32_t d_addr = tmem_base + slot.col;
+            const uint32_t d_addr = tmem_base + buf * TC_BUF_COLS;
             const uint32_t idesc = mgb_umma_idesc_tf32(TC_M, wc);
             const uint64_t db0 = mgb_umma_desc(0u, (uint32_t)wc * 16, SBO);
             uint32_t acc = 0;
@@ -273,7 +265,8 @@ __device__ __forceinline__ void tc_mma_issuer(const TcSegs& S, uint32_t a_hi_add
                 b16 += stage16;
                 if (++st == nst) { st = 0; ph ^= 1u; b16 = ring16; }
             }
-            mgb_umma_commit(&bars.t_full[buf]);
+            if (all_own0 || owner != TC_OWN_G1) mgb_umma_commit(&bars.t_full[buf]);
+            if (!all_own0 && owner != TC_OWN_G0) mgb_umma_commit(&bars.t_full[2 + buf]);
             if (samp) {  // the A tile is refilled with the drawn latent vectors before the other operands
                 MGB_TC_W(w_af, mgb_mbar_wait(bars.a_full, fill & 1u))
                 ++fill;
@@ -368,7 +361,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mgb_backproject_tc_kernel(const
             S.seg[0] = p.B;
             S.n = 1;
             S.samp_seg = -1;
-            S.split_q = S.split_g = -1;
+            S.il_q = S.il_g = -1;
             tc_b_producer(S, smem + plan.b_stage, plan.stage_bytes, p.nst, bars, my_tiles);
         }
     } else if (warp == 1) {
@@ -377,9 +370,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mgb_backproject_tc_kernel(const
             S.seg[0] = p.B;
             S.n = 1;
             S.samp_seg = -1;
-            S.split_q = S.split_g = -1;
+            S.il_q = S.il_g = -1;
             tc_mma_issuer(S, mgb_smem_u32(smem + plan.a_hi), mgb_smem_u32(smem + plan.a_lo), mgb_smem_u32(smem + plan.b_stage),
-                          plan.stage_bytes, p.nst, bars, tmem_base, my_tiles);
+                          plan.stage_bytes, p.nst, bars, tmem_base, my_tiles, nullptr, true);
         }
     } else {
         const int wq = warp & 3;            // TMEM lane quarter of this warp
@@ -614,8 +607,7 @@ struct TcScoreParams {
     int QS;            // floats per candidate row of the quad-value area (also the raw-sample staging)
     const int* phase;  // [quad chunks + 1] first op of every chunk's part of the program
     int ops_in_smem;   // program + constants staged in shared memory (else read through L1)
-    int CW;            // GMM columns per component
-    int cpc;           // components per N-chunk
+    int CW;            // GMM columns per component (a multiple of 8; components are packed densely and may straddle N-chunks)
     int seg_s;         // sampling operand (fused K1), -1 if the candidates come from memory
     int CWs;           // its columns per component
     long long n_tiles; // tiles of this launch (sampling mode: per-component tiling)
@@ -635,7 +627,7 @@ __host__ __device__ inline TcScoreSmem tc_score_smem_plan(int Kp, size_t stage_b
     p.qv = off; off += ((size_t)TC_M * QS * 4 + 15) & ~(size_t)15;
     p.ops = off; off += (size_t)n_ops * sizeof(MgbOp);
     p.cst = off; off += (size_t)((n_cst + 3) & ~3) * 4;
-    p.lp = off; off += TC_M * 4;
+    p.lp = off; off += 2 * TC_M * 4;   // -log p(s) and group 1's share of |s|^2
     p.redc = off; off += 16;
     p.redi = off; off += 32;
     p.bars = off; off += 8 * (2 * TC_MAX_STAGES + 2 + 6);
@@ -691,17 +683,16 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mgb_score_tc_kernel(const __gri
     }
     const MgbOp* ops = p.ops_in_smem ? sm_ops : sp.ops;
     const float* cst = p.ops_in_smem ? sm_cst : sp.cst;
+    const bool g1_active = SAMPLE || p.seg_g >= 0;   // group 1 shares the A fills of the sampling mode and owns the GMM chunks
     if (threadIdx.x == 0) {
         for (int i = 0; i < TC_MAX_STAGES; ++i) {
             mgb_mbar_init(&bars.b_full[i], 1);
             mgb_mbar_init(&bars.b_empty[i], 1);
         }
-        mgb_mbar_init(bars.a_full, 128);
+        mgb_mbar_init(bars.a_full, SAMPLE ? 256 : 128);
         mgb_mbar_init(bars.a_empty, 1);
-        for (int i = 0; i < 3; ++i) {
-            mgb_mbar_init(&bars.t_full[i], 1);
-            mgb_mbar_init(&bars.t_empty[i], 128);
-        }
+        for (int i = 0; i < 4; ++i) mgb_mbar_init(&bars.t_full[i], 1);
+        for (int i = 0; i < 2; ++i) mgb_mbar_init(&bars.t_empty[i], 128);
         mgb_mbar_init(s_full, 1);
         mgb_fence_barrier_init();
     }
@@ -710,8 +701,62 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mgb_score_tc_kernel(const __gri
     __syncthreads();
     mgb_tc_fence_after();
     const uint32_t tmem_base = *tmem_ptr;
-    const int n_nc_q = p.seg_q >= 0 ? p.segs.seg[p.seg_q].n_nc() : 0;
-    const int n_nc_g = p.seg_g >= 0 ? p.segs.seg[p.seg_g].n_nc() : 0;
+    float* sm_m2 = sm_lp + TC_M;   // group 1's share of |s|^2 (sampling mode)
+
+    // ---- sampling mode, both epilogue groups: half h of row `row` of the two A fills --------------------------------
+    // K columns [k_lo, k_hi) of the A tile belong to group h: group 0 takes the first Kh columns (a multiple of 8), group 1 the rest
+    const int Kh = ((p.Kp >> 1) + 7) & ~7;
+    // fill 1: [z | 1], z = the standard normals mgb_sample draws for global index gi
+    auto fill_z = [&](int row, int k_lo, int k_hi, bool valid, long long gi) {
+        const int D = sp.D;
+        const uint2 key = make_uint2((unsigned int)sp.seed, (unsigned int)(sp.seed >> 32));
+        for (int k0 = k_lo; k0 < k_hi; k0 += 4) {
+            float z[4] = {0.f, 0.f, 0.f, 0.f};
+            if (valid && k0 < D) mgb_normal4((unsigned long long)gi, (unsigned int)(k0 >> 2), key, z);
+            float h[4], l[4];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const int k = k0 + q;
+                const float v = !valid ? 0.f : (k < D ? z[q] : (k == D ? 1.f : 0.f));
+                mgb_tf32_split(v, h[q], l[q]);
+            }
+            const uint32_t off = mgb_canon_off((uint32_t)row, (uint32_t)k0, TC_M);
+            *reinterpret_cast<float4*>(smem + L.a_hi + off) = make_float4(h[0], h[1], h[2], h[3]);
+            *reinterpret_cast<float4*>(smem + L.a_lo + off) = make_float4(l[0], l[1], l[2], l[3]);
+        }
+    };
+    // fill 2: s = mu_g + L_g z comes back in TMEM (columns [k_lo, k_hi) of this thread's lane); A becomes [s | 1]; returns the
+    // thread's share of |s|^2
+    auto fill_s = [&](int row, uint32_t tbase, int k_lo, int k_hi, bool valid) -> float {
+        const int D = sp.D;
+        float m2 = 0.f;
+        for (int b0 = k_lo; b0 < k_hi; b0 += 8) {
+            float v[8];
+            mgb_tmem_ld8(tbase + b0, v);
+            float h[8], l[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const int k = b0 + i;
+                const float x = !valid ? 0.f : (k < D ? v[i] : (k == D ? 1.f : 0.f));
+                if (k < D) m2 = fmaf(x, x, m2);
+                mgb_tf32_split(x, h[i], l[i]);
+            }
+#pragma unroll
+            for (int i = 0; i < 8; i += 4) {
+                const uint32_t off = mgb_canon_off((uint32_t)row, (uint32_t)(b0 + i), TC_M);
+                *reinterpret_cast<float4*>(smem + L.a_hi + off) = make_float4(h[i], h[i + 1], h[i + 2], h[i + 3]);
+                *reinterpret_cast<float4*>(smem + L.a_lo + off) = make_float4(l[i], l[i + 1], l[i + 2], l[i + 3]);
+            }
+        }
+        return m2;
+    };
+    // candidate of (tile T, row) in sampling mode: a tile holds (up to) 128 consecutive candidates of ONE mixture component
+    auto sample_row = [&](long long T, int row, int& g, long long& gi, bool& valid) {
+        g = tc_tile_comp(sm_tile_first, sp.G, T);
+        const long long lo = max(sp.prefix.v[g], sp.index_base), hi = min(sp.prefix.v[g + 1], sp.index_base + sp.n);
+        gi = lo + (T - sm_tile_first[g]) * TC_M + row;
+        valid = gi < hi;
+    };
 
     if (warp == 0) {
         if (lane == 0) tc_b_producer(p.segs, smem + L.b_stage, L.stage_bytes, p.nst, bars, my_tiles, sm_tile_first);
@@ -732,8 +777,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mgb_score_tc_kernel(const __gri
         SIn* raw = reinterpret_cast<SIn*>(qv);
         float best_c = INFINITY;
         long long best_i = LLONG_MAX;
-        unsigned int cc = 0, sload = 0, uq = 0, ug0 = 0;   // uq: chunks of the quad stream consumed by this group (split mode)
-        const bool split = p.segs.split_q >= 0 && p.segs.split_g >= 0;
+        unsigned int cc = 0, sload = 0, fmask = 0;   // cc: chunks of this CTA so far (all owners); fmask: phase bits of the full barriers
 #ifdef MGB_TC_PROFILE
         const bool dbg = SAMPLE && blockIdx.x == 0 && tid0 == 0;
         long long tmark = clock64();
@@ -744,64 +788,14 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mgb_score_tc_kernel(const __gri
             long long g0 = T * TC_M, idx, gi = 0;
             bool valid;
             float m2 = 0.f;
+            int gcomp = 0;
             if constexpr (SAMPLE) {
-                // ---- fused K1: this tile holds (up to) 128 consecutive candidates of ONE mixture component -------
-                const int g = tc_tile_comp(sm_tile_first, sp.G, T);
-                const long long lo = max(sp.prefix.v[g], sp.index_base), hi = min(sp.prefix.v[g + 1], sp.index_base + sp.n);
-                const long long gstart = lo + (T - sm_tile_first[g]) * TC_M;
-                gi = gstart + row;
-                valid = gi < hi;
+                // ---- fused K1, fill 1 of A (this group's half of the row) -----------------------------------------
+                sample_row(T, row, gcomp, gi, valid);
                 idx = gi - sp.index_base;
-                const uint2 key = make_uint2((unsigned int)sp.seed, (unsigned int)(sp.seed >> 32));
                 mgb_mbar_wait(bars.a_empty, (unsigned int)(t & 1) ^ 1u);
                 MGB_TC_T(0)
-                // fill 1 of A: [z | 1], z = the standard normals mgb_sample draws for global index gi
-                for (int k0 = 0; k0 < p.Kp; k0 += 4) {
-                    float z[4] = {0.f, 0.f, 0.f, 0.f};
-                    if (valid && k0 < D) mgb_normal4((unsigned long long)gi, (unsigned int)(k0 >> 2), key, z);
-                    float h[4], l[4];
-#pragma unroll
-                    for (int q = 0; q < 4; ++q) {
-                        const int k = k0 + q;
-                        const float v = !valid ? 0.f : (k < D ? z[q] : (k == D ? 1.f : 0.f));
-                        mgb_tf32_split(v, h[q], l[q]);
-                    }
-                    const uint32_t off = mgb_canon_off((uint32_t)row, (uint32_t)k0, TC_M);
-                    *reinterpret_cast<float4*>(smem + L.a_hi + off) = make_float4(h[0], h[1], h[2], h[3]);
-                    *reinterpret_cast<float4*>(smem + L.a_lo + off) = make_float4(l[0], l[1], l[2], l[3]);
-                }
-                mgb_fence_proxy_async();
-                mgb_mbar_arrive(bars.a_full);
-                MGB_TC_T(1)
-                // s = mu_g + L_g z comes back in TMEM; fill 2 of A: [s | 1]
-                {
-                    const TcSlot slot = tc_next_slot(split ? 0 : -1, cc, uq, ug0);
-                    const unsigned int buf = slot.buf;
-                    mgb_mbar_wait(&bars.t_full[buf], slot.phase);
-                    MGB_TC_T(2)
-                    mgb_tc_fence_after();
-                    const uint32_t base = lane_addr + slot.col;
-                    for (int b0 = 0; b0 < p.Kp; b0 += 8) {
-                        float v[8];
-                        mgb_tmem_ld8(base + b0, v);
-                        float h[8], l[8];
-#pragma unroll
-                        for (int i = 0; i < 8; ++i) {
-                            const int k = b0 + i;
-                            const float x = !valid ? 0.f : (k < D ? v[i] : (k == D ? 1.f : 0.f));
-                            if (k < D) m2 = fmaf(x, x, m2);
-                            mgb_tf32_split(x, h[i], l[i]);
-                        }
-#pragma unroll
-                        for (int i = 0; i < 8; i += 4) {
-                            const uint32_t off = mgb_canon_off((uint32_t)row, (uint32_t)(b0 + i), TC_M);
-                            *reinterpret_cast<float4*>(smem + L.a_hi + off) = make_float4(h[i], h[i + 1], h[i + 2], h[i + 3]);
-                            *reinterpret_cast<float4*>(smem + L.a_lo + off) = make_float4(l[i], l[i + 1], l[i + 2], l[i + 3]);
-                        }
-                    }
-                    mgb_tc_fence_before();
-                    mgb_mbar_arrive_relaxed(&bars.t_empty[buf]);
-                }
+                fill_z(row, 0, Kh, valid, gi);
             } else {
                 idx = g0 + row;
                 valid = idx < sp.n;
@@ -837,9 +831,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mgb_score_tc_kernel(const __gri
             }
             mgb_fence_proxy_async();
             mgb_mbar_arrive(bars.a_full);
-            MGB_TC_T(3)
-            // ---- quad chunks: TMEM -> this thread's row of the quad-value area, then the part of the constraint
-            //      program that reads them (every chunk holds whole time slots; kinematic state carries over) -----
+            MGB_TC_T(1)
+            // ---- this group's chunks: the sampling chunk (second fill of A), then the quad chunks: TMEM -> this thread's
+            //      row of the quad-value area, then the part of the constraint program that reads them (every chunk holds
+            //      whole time slots; the kinematic state carries over) --------------------------------------------------
             float total = 0.f;
             MgbInterp<1> interp;
             interp.init();
@@ -849,17 +844,28 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mgb_score_tc_kernel(const __gri
                 total = fmaf(w, e, total);
                 if (sp.terms != nullptr && valid) sp.terms[(size_t)term * sp.n + idx] += e;
             };
-            for (int c = 0; c < n_nc_q; ++c) {
-                const TcB& B = p.segs.seg[p.seg_q];
-                const TcSlot slot = tc_next_slot(split ? 0 : -1, cc, uq, ug0);
-                const unsigned int buf = slot.buf;
-                mgb_mbar_wait(&bars.t_full[buf], slot.phase);
-                MGB_TC_T(4)
+            tc_for_each_chunk(p.segs, gcomp, [&](int sg, int c, int owner, bool samp) {
+                const unsigned int buf = cc & 1u;
+                ++cc;
+                if (owner == TC_OWN_G1) return;
+                mgb_mbar_wait(&bars.t_full[buf], tc_full_phase(fmask, 0, buf));
                 mgb_tc_fence_after();
-                const int wc = B.wc(c);
+                const uint32_t tbase = lane_addr + buf * TC_BUF_COLS;
+                if (samp) {
+                    MGB_TC_T(2)
+                    m2 = fill_s(row, tbase, 0, Kh, valid);
+                    mgb_tc_fence_before();
+                    mgb_mbar_arrive_relaxed(&bars.t_empty[buf]);   // group 1's reads of this buffer are ordered by its a_full arrival
+                    mgb_fence_proxy_async();
+                    mgb_mbar_arrive(bars.a_full);
+                    MGB_TC_T(3)
+                    return;
+                }
+                MGB_TC_T(4)
+                const int wc = p.segs.seg[sg].wc(c);
                 for (int b0 = 0; b0 < wc; b0 += 32) {
                     float v[32];
-                    mgb_tmem_ld32(lane_addr + slot.col + b0, v);
+                    mgb_tmem_ld32(tbase + b0, v);
 #pragma unroll
                     for (int i = 0; i < 32; ++i)
                         if (b0 + i < wc) qv[(size_t)row * QS + b0 + i] = v[i];
@@ -869,12 +875,12 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mgb_score_tc_kernel(const __gri
                 MGB_TC_T(5)
                 interp.run(ops, __ldg(p.phase + c), __ldg(p.phase + c + 1), cst, quad, emit);
                 MGB_TC_T(6)
-            }
-            cc += n_nc_g;
+            });
             float cost = sp.err_scale * total;
-            if (p.seg_g >= 0) {
-                asm volatile("bar.sync 2, 256;" ::: "memory");  // group 1 has published -log p(s) of this tile
-                cost = fmaf(sp.quality_scale, sm_lp[row], cost);
+            if (g1_active) {
+                asm volatile("bar.sync 2, 256;" ::: "memory");  // group 1 has published -log p(s) and its share of |s|^2 of this tile
+                if (p.seg_g >= 0) cost = fmaf(sp.quality_scale, sm_lp[row], cost);
+                if (SAMPLE) m2 += sm_m2[row];
             }
             MGB_TC_T(7)
 #ifdef MGB_TC_PROFILE
@@ -883,8 +889,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mgb_score_tc_kernel(const __gri
             if (sp.magnitude_scale != 0.f) cost = fmaf(sp.magnitude_scale, sqrtf(m2), cost);
             if (valid) {
                 if (sp.cost) sp.cost[idx] = cost;
-                const long long gi = sp.index_base + idx;
-                if (tc_better(cost, gi, best_c, best_i)) { best_c = cost; best_i = gi; }
+                const long long gidx = sp.index_base + idx;
+                if (tc_better(cost, gidx, best_c, best_i)) { best_c = cost; best_i = gidx; }
             }
         }
 #ifdef MGB_TC_PROFILE
@@ -941,72 +947,90 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mgb_score_tc_kernel(const __gri
                 }
             }
         }
-    } else if (p.seg_g >= 0) {
-        // ================= group 1: GMM log-density straight from TMEM =================
+    } else if (g1_active) {
+        // ================= group 1: its half of the A fills (sampling mode); GMM log-density straight from TMEM ==========
         const int wq = warp & 3;
         const int row = 32 * wq + lane;
         const uint32_t lane_addr = tmem_base + ((uint32_t)(32 * wq) << 16);
         const int CW = p.CW, G = sp.G;
-        unsigned int cc = 0, ug = 0;                 // ug: uses of TMEM buffer 1 by this group (split mode)
+        unsigned int cc = 0, fmask = 0;
 #ifdef MGB_TC_PROFILE
         const bool dbg1 = SAMPLE && blockIdx.x == 0 && threadIdx.x == 64 + 128;
         long long tc1 = 0;
         const long long t1start = clock64();
 #endif
-        const bool split = p.segs.split_q >= 0 && p.segs.split_g >= 0;
         for (long long t = 0; t < my_tiles; ++t) {
-            // alternating mode: the quad chunks belong to group 0, but this group still has to OBSERVE every phase of the
-            // accumulator barriers (a parity wait is only meaningful when the waiter is at most one phase ahead of the
-            // barrier).  Split mode: buffer 1 and its barriers are this group's alone.
-            if (!split) {
-                if (SAMPLE) {
-                    mgb_mbar_wait(&bars.t_full[cc & 1u], (cc >> 1) & 1u);
-                    ++cc;
-                }
-                for (int c = 0; c < n_nc_q; ++c, ++cc) mgb_mbar_wait(&bars.t_full[cc & 1u], (cc >> 1) & 1u);
+            const long long T = blockIdx.x + t * gridDim.x;
+            int gcomp = 0;
+            long long gi = 0;
+            bool valid = false;
+            float m2 = 0.f;
+            if constexpr (SAMPLE) {
+                sample_row(T, row, gcomp, gi, valid);
+                mgb_mbar_wait(bars.a_empty, (unsigned int)(t & 1) ^ 1u);
+                fill_z(row, Kh, p.Kp, valid, gi);
+                mgb_fence_proxy_async();
+                mgb_mbar_arrive(bars.a_full);
             }
-            float mx = -INFINITY, ssum = 0.f;
-            int g = 0;
-            for (int c = 0; c < n_nc_g; ++c, ++cc) {
-                const unsigned int buf = split ? 2u : (cc & 1u);
+            // GMM columns are packed densely: component g owns columns [g CW, (g + 1) CW) of the operand, CW a multiple of 8, and a
+            // component may straddle two chunks - the running sum of squares carries over
+            float mx = -INFINITY, ssum = 0.f, qf0 = 0.f, qf1 = 0.f;
+            int g = 0, left = CW;
+            tc_for_each_chunk(p.segs, gcomp, [&](int sg, int c, int owner, bool samp) {
+                const unsigned int buf = cc & 1u;
+                ++cc;
+                if (owner == TC_OWN_G0) return;
 #ifdef MGB_TC_PROFILE
                 long long tw0 = dbg1 ? clock64() : 0;
 #endif
-                mgb_mbar_wait(&bars.t_full[buf], split ? (ug & 1u) : ((cc >> 1) & 1u));
-                ++ug;
+                mgb_mbar_wait(&bars.t_full[2 + buf], tc_full_phase(fmask, 1, buf));
 #ifdef MGB_TC_PROFILE
                 if (dbg1) { const long long now_ = clock64(); g_tc_cycles[10] += now_ - tw0; tc1 = now_; }
 #endif
                 mgb_tc_fence_after();
-                const uint32_t base = lane_addr + (split ? TC_BUF_COLS : buf * TC_BUF_COLS);
-                for (int j = 0; j < p.cpc && g < G; ++j, ++g) {
-                    // y = (s - mu_g) . P_g occupies CW columns; padding columns are exact zeros
-                    float qf0 = 0.f, qf1 = 0.f;
-                    int b0 = 0;
-                    for (; b0 + 32 <= CW; b0 += 32) {
-                        float v[32];
-                        mgb_tmem_ld32(base + j * CW + b0, v);
-#pragma unroll
-                        for (int i = 0; i < 32; i += 2) {
-                            qf0 = fmaf(v[i], v[i], qf0);
-                            qf1 = fmaf(v[i + 1], v[i + 1], qf1);
-                        }
-                    }
-                    for (; b0 < CW; b0 += 8) {
-                        float v[8];
-                        mgb_tmem_ld8(base + j * CW + b0, v);
-#pragma unroll
-                        for (int i = 0; i < 8; i += 2) {
-                            qf0 = fmaf(v[i], v[i], qf0);
-                            qf1 = fmaf(v[i + 1], v[i + 1], qf1);
-                        }
-                    }
-                    const float lp = __ldg(sp.gmm_c + g) - 0.5f * (qf0 + qf1);
-                    if (lp > mx) {
-                        ssum = ssum * __expf(mx - lp) + 1.f;
-                        mx = lp;
+                const uint32_t tbase = lane_addr + buf * TC_BUF_COLS;
+                if (samp) {
+                    m2 = fill_s(row, tbase, Kh, p.Kp, valid);
+                    mgb_tc_fence_before();      // this thread's TMEM reads are complete before the arrival below
+                    mgb_fence_proxy_async();
+                    mgb_mbar_arrive(bars.a_full);
+                    return;
+                }
+                const int wc = p.segs.seg[sg].wc(c);   // a multiple of 16
+                for (int b0 = 0; b0 < wc; b0 += 32) {
+                    float v[32];
+                    if (b0 + 32 <= wc) {
+                        mgb_tmem_ld32(tbase + b0, v);
                     } else {
-                        ssum += __expf(lp - mx);
+                        float w16[16];
+                        mgb_tmem_ld16(tbase + b0, w16);
+#pragma unroll
+                        for (int i = 0; i < 16; ++i) { v[i] = w16[i]; v[16 + i] = 0.f; }
+                    }
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                        if (b0 + 8 * u < wc) {
+#pragma unroll
+                            for (int i = 0; i < 8; i += 2) {
+                                qf0 = fmaf(v[8 * u + i], v[8 * u + i], qf0);
+                                qf1 = fmaf(v[8 * u + i + 1], v[8 * u + i + 1], qf1);
+                            }
+                            left -= 8;
+                            if (left == 0) {   // y = (s - mu_g) . P_g complete (padding columns are exact zeros)
+                                if (g < G) {
+                                    const float lp = __ldg(sp.gmm_c + g) - 0.5f * (qf0 + qf1);
+                                    if (lp > mx) {
+                                        ssum = ssum * __expf(mx - lp) + 1.f;
+                                        mx = lp;
+                                    } else {
+                                        ssum += __expf(lp - mx);
+                                    }
+                                }
+                                ++g;
+                                left = CW;
+                                qf0 = qf1 = 0.f;
+                            }
+                        }
                     }
                 }
                 mgb_tc_fence_before();
@@ -1014,8 +1038,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mgb_score_tc_kernel(const __gri
 #ifdef MGB_TC_PROFILE
                 if (dbg1) g_tc_cycles[11] += clock64() - tc1;
 #endif
-            }
+            });
             sm_lp[row] = -(mx + __logf(ssum));
+            sm_m2[row] = m2;
             asm volatile("bar.sync 2, 256;" ::: "memory");
         }
 #ifdef MGB_TC_PROFILE
@@ -1055,21 +1080,12 @@ bool tc_disabled() {
 int mgb_score_tc_prepare_model(mgb_model* m) {
     if (m->D < TC_SCORE_MIN_D) return MGB_OK;
     const int D = m->D, G = m->G;
-    int CW = (D + 7) & ~7;
-    int cpc = std::max(1, TC_BUF_COLS / CW);
-    if ((cpc * CW) % 16 != 0) {
-        CW = (D + 15) & ~15;
-        cpc = std::max(1, TC_BUF_COLS / CW);
-    }
-    if (CW > TC_BUF_COLS) {
-        mgb_set_error("tensor-core score: D = %d exceeds one accumulator buffer", D);
-        return MGB_E_UNSUPPORTED;
-    }
+    const int CW = (D + 7) & ~7;
     TcB B;
     B.data = nullptr;
     B.Kp = (D + 1 + 7) & ~7;
     B.Np = (G * CW + 15) & ~15;
-    B.NC = cpc * CW;
+    B.NC = std::min(TC_BUF_COLS, B.Np);   // 128 x 256 x 8 is the efficient tcgen05 shape: an MMA costs max(~123, N / 2) cycles
     B.KC = TC_SCORE_KC;
     std::vector<float> packed = tc_pack_b(B, D + 1, G * CW, [&](int k, int n) -> double {
         const int g = n / CW, j = n % CW;
@@ -1197,12 +1213,11 @@ static bool tc_score_plan(const mgb_model* m, const mgb_constraints* c, float qu
         B.data = m->d_Bgmm; B.Kp = m->tcg_Kp; B.Np = m->tcg_Np; B.NC = m->tcg_NC; B.KC = m->tcg_KC;
         p.seg_g = p.segs.n++;
         p.CW = m->tcg_CW;
-        p.cpc = m->tcg_NC / m->tcg_CW;
     }
     if (p.segs.n == (sample ? 1 : 0)) return false;
     // quads and GMM both present: interleave their chunks, one TMEM buffer and one consumer group each
-    p.segs.split_q = (use_q && use_g) ? p.seg_q : -1;
-    p.segs.split_g = (use_q && use_g) ? p.seg_g : -1;
+    p.segs.il_q = (use_q && use_g) ? p.seg_q : -1;
+    p.segs.il_g = use_g ? p.seg_g : -1;   // also names the operand whose chunks belong to epilogue group 1
     p.QS = std::max(use_q ? std::min(c->tcq_Np, TC_SCORE_QCHUNK) : 0, m->D) | 1;
     size_t stage_bytes = 0;
     for (int i = 0; i < p.segs.n; ++i) stage_bytes = std::max(stage_bytes, (size_t)2 * p.segs.seg[i].NC * p.segs.seg[i].KC * 4);
