@@ -208,13 +208,15 @@ __device__ __forceinline__ void tc_b_producer(const TcSegs& S, unsigned char* sm
 __device__ long long g_tc_cycles[16];
 #endif
 
-// warp 1, one lane: all MMAs of this CTA.  Chunk number cc accumulates into TMEM buffer cc & 1; the finished chunk is
+// warp 1, ALL lanes converged, the MMAs and commits issued by one elected lane (a loop run by a single lane inside a
+// divergent branch costs ~60 % more issue time per K-step: tools/micro/mma_issue2.cu): all MMAs of this CTA.  Chunk number cc accumulates into TMEM buffer cc & 1; the finished chunk is
 // published on the "full" barrier(s) of its owner(s).  all_own0: every chunk is published on owner 0's barriers (the
 // back-projection kernel, whose epilogue warps all drain every chunk).
 __device__ __forceinline__ void tc_mma_issuer(const TcSegs& S, uint32_t a_hi_addr, uint32_t a_lo_addr, uint32_t stage_addr, size_t stage_bytes,
                                               int nst, const TcBars& bars, uint32_t tmem_base, long long my_tiles,
                                               const int* tile_first = nullptr, bool all_own0 = false) {
     unsigned int cc = 0, fill = 0;
+    const bool leader = mgb_elect_one();
     const uint32_t A_LBO = TC_M * 16, SBO = 128;
     // descriptors differ only in their 14-bit start-address field (bytes >> 4): build them once, then add
     const uint64_t da_hi0 = mgb_umma_desc(a_hi_addr, A_LBO, SBO), da_lo0 = mgb_umma_desc(a_lo_addr, A_LBO, SBO);
@@ -256,27 +258,34 @@ __device__ __forceinline__ void tc_mma_issuer(const TcSegs& S, uint32_t a_hi_add
                 for (int j = 0; j < wk; j += 8, a16 += 2 * A_LBO / 16, bj16 += 2 * wc) {
                     const uint64_t da_hi = da_hi0 + a16, da_lo = da_lo0 + a16;
                     const uint64_t db_hi = db0 + bj16, db_lo = db_hi + lo16;
-                    mgb_umma_tf32(d_addr, da_lo, db_hi, idesc, acc);  // small terms first
-                    mgb_umma_tf32(d_addr, da_hi, db_lo, idesc, 1u);
-                    mgb_umma_tf32(d_addr, da_hi, db_hi, idesc, 1u);
+                    if (leader) {
+                        mgb_umma_tf32(d_addr, da_lo, db_hi, idesc, acc);  // small terms first
+                        mgb_umma_tf32(d_addr, da_hi, db_lo, idesc, 1u);
+                        mgb_umma_tf32(d_addr, da_hi, db_hi, idesc, 1u);
+                    }
                     acc = 1u;
                 }
-                mgb_umma_commit(&bars.b_empty[st]);
+                if (leader) mgb_umma_commit(&bars.b_empty[st]);
+                __syncwarp();
                 b16 += stage16;
                 if (++st == nst) { st = 0; ph ^= 1u; b16 = ring16; }
             }
-            if (all_own0 || owner != TC_OWN_G1) mgb_umma_commit(&bars.t_full[buf]);
-            if (!all_own0 && owner != TC_OWN_G0) mgb_umma_commit(&bars.t_full[2 + buf]);
+            if (leader) {
+                if (all_own0 || owner != TC_OWN_G1) mgb_umma_commit(&bars.t_full[buf]);
+                if (!all_own0 && owner != TC_OWN_G0) mgb_umma_commit(&bars.t_full[2 + buf]);
+            }
+            __syncwarp();
             if (samp) {  // the A tile is refilled with the drawn latent vectors before the other operands
                 MGB_TC_W(w_af, mgb_mbar_wait(bars.a_full, fill & 1u))
                 ++fill;
                 mgb_tc_fence_after();
             }
         });
-        mgb_umma_commit(bars.a_empty);
+        if (leader) mgb_umma_commit(bars.a_empty);
+        __syncwarp();
     }
 #ifdef MGB_TC_PROFILE
-    if (dbgi) { g_tc_cycles[13] += w_te; g_tc_cycles[14] += w_bf; g_tc_cycles[15] += w_af; }
+    if (dbgi && leader) { g_tc_cycles[13] += w_te; g_tc_cycles[14] += w_bf; g_tc_cycles[15] += w_af; }
 #endif
 #undef MGB_TC_W
 }
@@ -365,7 +374,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mgb_backproject_tc_kernel(const
             tc_b_producer(S, smem + plan.b_stage, plan.stage_bytes, p.nst, bars, my_tiles);
         }
     } else if (warp == 1) {
-        if (lane == 0) {
+        {
             TcSegs S;
             S.seg[0] = p.B;
             S.n = 1;
@@ -761,8 +770,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mgb_score_tc_kernel(const __gri
     if (warp == 0) {
         if (lane == 0) tc_b_producer(p.segs, smem + L.b_stage, L.stage_bytes, p.nst, bars, my_tiles, sm_tile_first);
     } else if (warp == 1) {
-        if (lane == 0)
-            tc_mma_issuer(p.segs, mgb_smem_u32(smem + L.a_hi), mgb_smem_u32(smem + L.a_lo), mgb_smem_u32(smem + L.b_stage), L.stage_bytes,
+        tc_mma_issuer(p.segs, mgb_smem_u32(smem + L.a_hi), mgb_smem_u32(smem + L.a_lo), mgb_smem_u32(smem + L.b_stage), L.stage_bytes,
                           p.nst, bars, tmem_base, my_tiles, sm_tile_first);
     } else if (warp < 6) {
         // ================= group 0: A producer, quad drain, constraint program, selection =================
@@ -1060,7 +1068,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mgb_score_tc_kernel(const __gri
 // ---- host side of K6-TC -------------------------------------------------------------------
 namespace {
 constexpr int TC_SCORE_MIN_D = 33;  // smaller latent spaces stay on the register-resident SIMT kernel
-constexpr int TC_SCORE_KC = 8;
+// K rows per stage: a stage slot holds 2 (hi, lo) x 256 x 8 floats = 16 KB; operands of <= 128 columns put 16 rows into it, which
+// halves the number of barrier round trips of their (latency-bound) chunks
+constexpr int tc_score_kc(int NC) { return NC <= 128 ? 16 : 8; }
 constexpr int TC_SCORE_QCHUNK = 128;  // columns of one chunk of the quad operand = 32 quads: what one pass of the program sees
 
 bool tc_disabled() {
@@ -1085,8 +1095,8 @@ int mgb_score_tc_prepare_model(mgb_model* m) {
     B.data = nullptr;
     B.Kp = (D + 1 + 7) & ~7;
     B.Np = (G * CW + 15) & ~15;
-    B.NC = std::min(TC_BUF_COLS, B.Np);   // 128 x 256 x 8 is the efficient tcgen05 shape: an MMA costs max(~123, N / 2) cycles
-    B.KC = TC_SCORE_KC;
+    B.NC = std::min(TC_BUF_COLS, B.Np);   // N = 256: the lane that issues the MMAs needs ~65 cycles per MMA, the pipe N / 2
+    B.KC = tc_score_kc(B.NC);
     std::vector<float> packed = tc_pack_b(B, D + 1, G * CW, [&](int k, int n) -> double {
         const int g = n / CW, j = n % CW;
         if (j >= D) return 0.0;
@@ -1103,7 +1113,7 @@ int mgb_score_tc_prepare_model(mgb_model* m) {
         S.Kp = B.Kp;
         S.Np = G * CWs;
         S.NC = CWs;
-        S.KC = TC_SCORE_KC;
+        S.KC = tc_score_kc(S.NC);
         std::vector<float> ps = tc_pack_b(S, D + 1, G * CWs, [&](int k, int n) -> double {
             const int g = n / CWs, j = n % CWs;
             if (j >= D) return 0.0;
@@ -1145,7 +1155,7 @@ int mgb_score_tc_prepare_constraints(const mgb_model* m, mgb_constraints* c) {
     B.Kp = (D + 1 + 7) & ~7;
     B.Np = (4 * n_pos + 15) & ~15;
     B.NC = std::min(TC_SCORE_QCHUNK, B.Np);
-    B.KC = TC_SCORE_KC;
+    B.KC = tc_score_kc(B.NC);
     // row k < K: basis row k of the quad; row D (the one that meets the 1 of the A tile): the mean
     std::vector<float> packed = tc_pack_b(B, D + 1, 4 * n_pos, [&](int k, int n) -> double {
         const int q = quad_at[n >> 2], ch = n & 3;

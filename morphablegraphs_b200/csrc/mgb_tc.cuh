@@ -55,6 +55,13 @@ __device__ __forceinline__ void mgb_tmem_dealloc(uint32_t taddr, uint32_t ncols)
 __device__ __forceinline__ void mgb_tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void mgb_tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 
+// one lane of a converged warp (elect.sync): the issuer of the warp's tcgen05.mma / tcgen05.commit
+__device__ __forceinline__ bool mgb_elect_one() {
+    unsigned int pred;
+    asm volatile("{\n.reg .pred p;\nelect.sync _|p, 0xffffffff;\nselp.u32 %0, 1, 0, p;\n}\n" : "=r"(pred));
+    return pred != 0;
+}
+
 // ---------------------------------------------------------------------------
 // descriptors
 // ---------------------------------------------------------------------------
