@@ -719,42 +719,61 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mgb_score_tc_kernel(const __gri
     auto fill_z = [&](int row, int k_lo, int k_hi, bool valid, long long gi) {
         const int D = sp.D;
         const uint2 key = make_uint2((unsigned int)sp.seed, (unsigned int)(sp.seed >> 32));
-        for (int k0 = k_lo; k0 < k_hi; k0 += 4) {
-            float z[4] = {0.f, 0.f, 0.f, 0.f};
-            if (valid && k0 < D) mgb_normal4((unsigned long long)gi, (unsigned int)(k0 >> 2), key, z);
-            float h[4], l[4];
+        // four independent Philox / Box-Muller chains per iteration: a warp has its scheduler almost to itself here, and one
+        // chain is a sequence of dependent integer multiplies
+        for (int k0 = k_lo; k0 < k_hi; k0 += 16) {
+            float z[4][4];
 #pragma unroll
-            for (int q = 0; q < 4; ++q) {
-                const int k = k0 + q;
-                const float v = !valid ? 0.f : (k < D ? z[q] : (k == D ? 1.f : 0.f));
-                mgb_tf32_split(v, h[q], l[q]);
+            for (int u = 0; u < 4; ++u) {
+                mgb_normal4((unsigned long long)gi, (unsigned int)((k0 >> 2) + u), key, z[u]);   // unconditional: the chains interleave
             }
-            const uint32_t off = mgb_canon_off((uint32_t)row, (uint32_t)k0, TC_M);
-            *reinterpret_cast<float4*>(smem + L.a_hi + off) = make_float4(h[0], h[1], h[2], h[3]);
-            *reinterpret_cast<float4*>(smem + L.a_lo + off) = make_float4(l[0], l[1], l[2], l[3]);
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                if (k0 + 4 * u < k_hi) {
+                    float h[4], l[4];
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        const int k = k0 + 4 * u + q;
+                        const float v = !valid ? 0.f : (k < D ? z[u][q] : (k == D ? 1.f : 0.f));
+                        mgb_tf32_split(v, h[q], l[q]);
+                    }
+                    const uint32_t off = mgb_canon_off((uint32_t)row, (uint32_t)(k0 + 4 * u), TC_M);
+                    *reinterpret_cast<float4*>(smem + L.a_hi + off) = make_float4(h[0], h[1], h[2], h[3]);
+                    *reinterpret_cast<float4*>(smem + L.a_lo + off) = make_float4(l[0], l[1], l[2], l[3]);
+                }
+            }
         }
     };
-    // fill 2: s = mu_g + L_g z comes back in TMEM (columns [k_lo, k_hi) of this thread's lane); A becomes [s | 1]; returns the
-    // thread's share of |s|^2
+    // fill 2: s = mu_g + L_g z comes back in TMEM (columns [k_lo, k_hi) of this thread's lane, a multiple of 8); A becomes
+    // [s | 1]; returns the thread's share of |s|^2
     auto fill_s = [&](int row, uint32_t tbase, int k_lo, int k_hi, bool valid) -> float {
         const int D = sp.D;
         float m2 = 0.f;
-        for (int b0 = k_lo; b0 < k_hi; b0 += 8) {
-            float v[8];
-            mgb_tmem_ld8(tbase + b0, v);
-            float h[8], l[8];
+        for (int b0 = k_lo; b0 < k_hi; b0 += 16) {
+            float v[16];
+            if (b0 + 16 <= k_hi) {
+                mgb_tmem_ld16(tbase + b0, v);
+            } else {
+                float w8[8];
+                mgb_tmem_ld8(tbase + b0, w8);
 #pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                const int k = b0 + i;
-                const float x = !valid ? 0.f : (k < D ? v[i] : (k == D ? 1.f : 0.f));
-                if (k < D) m2 = fmaf(x, x, m2);
-                mgb_tf32_split(x, h[i], l[i]);
+                for (int i = 0; i < 8; ++i) { v[i] = w8[i]; v[8 + i] = 0.f; }
             }
 #pragma unroll
-            for (int i = 0; i < 8; i += 4) {
-                const uint32_t off = mgb_canon_off((uint32_t)row, (uint32_t)(b0 + i), TC_M);
-                *reinterpret_cast<float4*>(smem + L.a_hi + off) = make_float4(h[i], h[i + 1], h[i + 2], h[i + 3]);
-                *reinterpret_cast<float4*>(smem + L.a_lo + off) = make_float4(l[i], l[i + 1], l[i + 2], l[i + 3]);
+            for (int u = 0; u < 4; ++u) {
+                if (b0 + 4 * u < k_hi) {
+                    float h[4], l[4];
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        const int k = b0 + 4 * u + q;
+                        const float x = !valid ? 0.f : (k < D ? v[4 * u + q] : (k == D ? 1.f : 0.f));
+                        if (k < D) m2 = fmaf(x, x, m2);
+                        mgb_tf32_split(x, h[q], l[q]);
+                    }
+                    const uint32_t off = mgb_canon_off((uint32_t)row, (uint32_t)(b0 + 4 * u), TC_M);
+                    *reinterpret_cast<float4*>(smem + L.a_hi + off) = make_float4(h[0], h[1], h[2], h[3]);
+                    *reinterpret_cast<float4*>(smem + L.a_lo + off) = make_float4(l[0], l[1], l[2], l[3]);
+                }
             }
         }
         return m2;
