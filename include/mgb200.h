@@ -91,6 +91,9 @@ typedef struct {
 #define MGB_CT_FEET 5       /* keyframe_feet                                         */
 #define MGB_CT_LOOK_AT 6    /* keyframe_look_at                                      */
 #define MGB_CT_CA 7         /* ca_constraint: min over frames                        */
+#define MGB_CT_JOINT_ROT 8  /* JointRotationConstraint (joint_rotation_constraint.py:62-75)            */
+#define MGB_CT_QUAT_FRAME 9 /* keyframe_pose given as a quaternion frame: PoseConstraintQuatFrame      */
+#define MGB_CT_LOCAL_TRAJ 10 /* local_trajectory: LocalTrajectoryConstraint, sum over all frames       */
 
 #define MGB_MAX_POSE_POINTS 32
 
@@ -108,6 +111,19 @@ typedef struct {
  *  LOOK_AT  : node[0]=head joint, target          (look_at_constraint.py:58-68)
  *  CA       : node[0], time_slot = first of n_slots consecutive slots, axis_mask, target
  *             (global_transform_ca_constraint.py:34-40)
+ *  JOINT_ROT: node[0] (an animated joint or the root), time_slot (frame_index), orient_q = the
+ *             target rotation as a unit quaternion; error = |R_target - R(q/|q|)|_F of the joint's
+ *             own frame channels, no forward kinematics (joint_rotation_constraint.py:62-75)
+ *  QUAT_FRAME: time_slot (frame 0), points_offset/n_points: one pose point per compared joint with
+ *             node, weight and target = (x, y, z) of the target UNIT quaternion taken with w >= 0;
+ *             error = sum_i weight_i |R(target_i) - R(q_i/|q_i|)|_F
+ *             (pose_constraint_quat_frame.py:47-52 through anim_utils' calculate_weighted_frame_distance_quat)
+ *  LOCAL_TRAJ: node[0], time_slot = first of n_slots consecutive slots (the integer frames),
+ *             offset[0] = start_t, offset[1] = arc-length step of the trajectory table,
+ *             points_offset/n_points: the trajectory sampled at arc length i * step, i = 0 .. n_points - 2,
+ *             (n_points - 2) * step = full arc length, last entry = the last control point
+ *             (returned beyond the end); only target x and z are read
+ *             (local_trajectory_constraint.py:58-83, parameterized_spline.py:131-148)
  */
 typedef struct {
     int32_t type;

@@ -86,7 +86,7 @@ class AlignDesc(C.Structure):
     _fields_ = [("mode", C.c_int32), ("prev_heading_deg", C.c_double), ("prev_root", C.c_double * 3)]
 
 
-CT_POSITION, CT_RELATIVE, CT_DIR2D, CT_POSE, CT_TWO_HANDS, CT_FEET, CT_LOOK_AT, CT_CA = range(8)
+CT_POSITION, CT_RELATIVE, CT_DIR2D, CT_POSE, CT_TWO_HANDS, CT_FEET, CT_LOOK_AT, CT_CA, CT_JOINT_ROT, CT_QUAT_FRAME, CT_LOCAL_TRAJ = range(11)
 MAX_POSE_POINTS = 32
 
 # every symbol include/mgb200.h declares: (restype, argtypes)

@@ -143,7 +143,137 @@ class LookAtConstraint(KeyframeConstraintBase):
         self.target_position = constraint_desc["position"]
 
 
+SPATIAL_CONSTRAINT_TYPE_LOCAL_TRAJECTORY = "local_trajectory"
+
+
+def _quaternion_matrix3(q):
+    """3x3 part of transformations.quaternion_matrix (w, x, y, z): identity below 4 eps."""
+    q = np.array(q, dtype=np.float64)
+    n = float(np.dot(q, q))
+    if n < np.finfo(float).eps * 4.0:
+        return np.identity(3)
+    q *= np.sqrt(2.0 / n)
+    o = np.outer(q, q)
+    return np.array([[1.0 - o[2, 2] - o[3, 3], o[1, 2] - o[3, 0], o[1, 3] + o[2, 0]],
+                     [o[1, 2] + o[3, 0], 1.0 - o[1, 1] - o[3, 3], o[2, 3] - o[1, 0]],
+                     [o[1, 3] - o[2, 0], o[2, 3] + o[1, 0], 1.0 - o[1, 1] - o[2, 2]]])
+
+
+def _euler_matrix3_rxyz(ai, aj, ak):
+    """3x3 part of transformations.euler_matrix(ai, aj, ak, axes='rxyz'): rotating frame, x then y then z,
+    i.e. R = Rx(ai) Ry(aj) Rz(ak)."""
+    ci, si = np.cos(ai), np.sin(ai)
+    cj, sj = np.cos(aj), np.sin(aj)
+    ck, sk = np.cos(ak), np.sin(ak)
+    rx = np.array([[1, 0, 0], [0, ci, -si], [0, si, ci]])
+    ry = np.array([[cj, 0, sj], [0, 1, 0], [-sj, 0, cj]])
+    rz = np.array([[ck, -sk, 0], [sk, ck, 0], [0, 0, 1]])
+    return rx.dot(ry).dot(rz)
+
+
+class JointRotationConstraint(KeyframeConstraintBase):
+    """reference joint_rotation_constraint.py:32-53: the joint's own rotation at `frame_index`
+    against a target rotation, Frobenius norm of the matrix difference.  `constraint_rotmat` is 4x4
+    like the reference's (transformations returns homogeneous matrices); `constraint_type` stays None
+    as in the reference, the engine recognises the class by `constraint_rotmat`."""
+
+    def __init__(self, skeleton, constraint_desc, precision, weight_factor=1.0):
+        super(JointRotationConstraint, self).__init__(constraint_desc, precision, weight_factor)
+        self.skeleton = skeleton
+        self.joint_name = constraint_desc["joint_name"]
+        self.rotation_type = constraint_desc["rotation_type"]
+        self.rotation_constraint = constraint_desc["rotation_constraint"]
+        self.frame_idx = constraint_desc["frame_index"]
+        self.constraint_rotmat = np.identity(4)
+        if self.rotation_type == "euler":
+            rad = [float(np.deg2rad(a)) for a in self.rotation_constraint]
+            self.constraint_rotmat[:3, :3] = _euler_matrix3_rxyz(rad[0], rad[1], rad[2])
+        elif self.rotation_type == "quaternion":
+            quat = np.asarray(self.rotation_constraint, dtype=np.float64)
+            quat = quat / np.linalg.norm(quat)
+            self.constraint_rotmat[:3, :3] = _quaternion_matrix3(quat)
+        else:
+            raise ValueError("Unknown rotation type!")
+
+
+class PoseConstraintQuatFrame(KeyframeConstraintBase):
+    """reference pose_constraint_quat_frame.py:30-38: `frame_constraint` is a whole quaternion frame
+    (root translation + one quaternion per animated joint), compared at frame 0 joint by joint (root
+    excluded) with the skeleton's joint weights."""
+
+    def __init__(self, skeleton, constraint_desc, precision, weight_factor=1.0):
+        super(PoseConstraintQuatFrame, self).__init__(constraint_desc, precision, weight_factor)
+        self.skeleton = skeleton
+        self.pose_constraint = constraint_desc["frame_constraint"]
+        self.constraint_type = SPATIAL_CONSTRAINT_TYPE_KEYFRAME_POSE
+
+
+class LocalTrajectoryConstraint(KeyframeConstraintBase):
+    """reference local_trajectory_constraint.py:32-41.  `trajectory` is any object with the reference's
+    ParameterizedSpline interface (`query_point_by_absolute_arc_length`, `full_arc_length`,
+    `get_last_control_point`), e.g. the reference's own spline or an `ArcLengthTable`."""
+
+    def __init__(self, skeleton, constraint_desc, precision, weight_factor=1.0):
+        super(LocalTrajectoryConstraint, self).__init__(constraint_desc, precision, weight_factor)
+        self.constraint_type = SPATIAL_CONSTRAINT_TYPE_LOCAL_TRAJECTORY
+        self.trajectory = constraint_desc["trajectory"]
+        self.start_t = constraint_desc["start_t"]
+        self.n_canonical_frames = constraint_desc["n_canonical_frames"]
+        self.joint_name = constraint_desc["joint_name"]
+        self.skeleton = skeleton
+
+
+class ArcLengthTable(object):
+    """A trajectory tabulated by arc length: `points[i]` = the point at arc length `i * step`,
+    `(len(points) - 1) * step` = the full arc length, linear in between, `last_control_point`
+    beyond the end (what parameterized_spline.py:131-148 returns there).  This is the form in which
+    the engine ships ANY trajectory object to the device (`tabulate_trajectory`); constructing one
+    directly skips the per-point host queries."""
+
+    N_DEFAULT = 2048
+
+    def __init__(self, points, step, last_control_point=None):
+        self.points = np.ascontiguousarray(points, dtype=np.float64)
+        self.step = float(step)
+        self.full_arc_length = self.step * (len(self.points) - 1)
+        self.last_control_point = np.asarray(self.points[-1] if last_control_point is None else last_control_point, dtype=np.float64)
+
+    def get_last_control_point(self):
+        return self.last_control_point
+
+    def query_point_by_absolute_arc_length(self, t):
+        if t > self.full_arc_length:
+            return self.last_control_point
+        u = max(float(t), 0.0) / self.step
+        i = min(int(u), len(self.points) - 2)
+        f = u - i
+        return self.points[i] + f * (self.points[i + 1] - self.points[i])
+
+
+def tabulate_trajectory(trajectory, n=ArcLengthTable.N_DEFAULT):
+    """ArcLengthTable of a trajectory object (cached on the object: the table of a planner's path is
+    built once, not once per motion-primitive step)."""
+    if isinstance(trajectory, ArcLengthTable):
+        return trajectory
+    cached = getattr(trajectory, "_mgb_arc_table", None)
+    full = float(trajectory.full_arc_length)
+    if cached is not None and cached[0] == (full, n):
+        return cached[1]
+    step = full / n
+    pts = np.array([np.asarray(trajectory.query_point_by_absolute_arc_length(min(i * step, full)), dtype=np.float64)[:3] for i in range(n + 1)])
+    last = trajectory.get_last_control_point() if hasattr(trajectory, "get_last_control_point") else trajectory.spline.get_last_control_point()
+    table = ArcLengthTable(pts, step, np.asarray(last, dtype=np.float64)[:3])
+    try:
+        trajectory._mgb_arc_table = ((full, n), table)
+    except AttributeError:
+        pass
+    return table
+
+
 CONSTRAINT_FACTORY = {
+    "JointRotationConstraint": JointRotationConstraint,
+    "PoseConstraintQuatFrame": PoseConstraintQuatFrame,
+    "LocalTrajectoryConstraint": LocalTrajectoryConstraint,
     "GlobalTransformConstraint": GlobalTransformConstraint,
     "RelativeTransformConstraint": RelativeTransformConstraint,
     "Direction2DConstraint": Direction2DConstraint,

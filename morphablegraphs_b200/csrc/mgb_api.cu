@@ -292,6 +292,7 @@ struct Action {
     int code;
     int a, b;
     std::vector<float> cst;
+    int cst_at = -1;  // >= 0: the constants already sit in the pool at this offset (shared by several ops)
 };
 
 struct Compiler {
@@ -304,6 +305,7 @@ struct Compiler {
     std::vector<MgbOp> ops;
     std::vector<float> cst;
     std::vector<std::map<int, std::vector<Action>>> attach;  // [slot][node] -> actions
+    std::vector<std::vector<Action>> free_actions;           // [slot] -> actions that read raw channels of the slot (no FK walk)
     int scratch_used = 0;
     int max_depth = 0;
 
@@ -324,6 +326,12 @@ struct Compiler {
     void op(int code, int a, int b, const std::vector<float>& v) {
         MgbOp o;
         o.code = code; o.a = a; o.b = b; o.c = push_cst(v);
+        ops.push_back(o);
+    }
+    void op_action(const Action& a) {
+        if (a.cst_at < 0) { op(a.code, a.a, a.b, a.cst); return; }
+        MgbOp o;
+        o.code = a.code; o.a = a.a; o.b = a.b; o.c = a.cst_at;
         ops.push_back(o);
     }
     int alloc_scratch(int n) {
@@ -356,7 +364,7 @@ struct Compiler {
         }
         auto it = attach[slot].find(node);
         if (it != attach[slot].end())
-            for (const Action& a : it->second) op(a.code, a.a, a.b, a.cst);
+            for (const Action& a : it->second) op_action(a);
         std::vector<int> kids;
         for (int c : m->children[node])
             if (need[c]) kids.push_back(c);
@@ -372,6 +380,8 @@ struct Compiler {
     }
 
     void emit_slot(int slot) {
+        // quads are numbered in emission order (the quads of a slot stay contiguous): the channel becomes a quad here
+        for (const Action& a : free_actions[slot]) op(a.code, a.a, a.code == OP_JROT ? quad(slot, a.b) : a.b, a.cst);
         if (attach[slot].empty()) return;
         std::vector<char> need(m->n_nodes, 0);
         for (auto& kv : attach[slot]) {
@@ -415,12 +425,14 @@ extern "C" int mgb_constraints_pack(const mgb_model* m, const mgb_constraint_des
     C.weights[4 * CP0] = 1.0;
     C.weights[4 * CP0 + 1] = C.weights[4 * CP0 + 2] = C.weights[4 * CP0 + 3] = 0.0;
     C.attach.resize(n_times + 1);
+    C.free_actions.resize(n_times + 1);
 
     auto check_node = [&](int nd) { return nd >= 0 && nd < m->n_nodes; };
     auto check_slot = [&](int s) { return s >= 0 && s < n_times; };
     struct Final { int code, a, b; std::vector<float> cst; };
     std::vector<Final> finals;
     std::vector<MgbOp> begins;
+    C.cst.push_back(0.f);  // offset 0 is a valid dummy for ops without constants
 
     for (int j = 0; j < n; ++j) {
         const mgb_constraint_desc& c = cd[j];
@@ -519,6 +531,64 @@ extern "C" int mgb_constraints_pack(const mgb_model* m, const mgb_constraint_des
                 finals.push_back({OP_CA_END, j, sc, {w}});
                 break;
             }
+            case MGB_CT_JOINT_ROT:
+            case MGB_CT_QUAT_FRAME: {
+                MGB_REQUIRE(check_slot(c.time_slot), "constraint %d: bad time slot", j);
+                // target rotation matrix of a unit quaternion (transformations.quaternion_matrix), fp64
+                auto rot_action = [&](int node, const double q[4], double inner) -> int {
+                    MGB_REQUIRE(check_node(node) && m->channel[node] >= 0, "constraint %d: node %d has no quaternion channels", j, node);
+                    const double n2 = q[0] * q[0] + q[1] * q[1] + q[2] * q[2] + q[3] * q[3];
+                    MGB_REQUIRE(n2 > 0, "constraint %d: zero target quaternion", j);
+                    const double s2 = 2.0 / n2, qw = q[0], qx = q[1], qy = q[2], qz = q[3];
+                    const double R[9] = {1 - (qy * qy + qz * qz) * s2, (qx * qy - qw * qz) * s2, (qx * qz + qw * qy) * s2,
+                                         (qx * qy + qw * qz) * s2, 1 - (qx * qx + qz * qz) * s2, (qy * qz - qw * qx) * s2,
+                                         (qx * qz - qw * qy) * s2, (qy * qz + qw * qx) * s2, 1 - (qx * qx + qy * qy) * s2};
+                    std::vector<float> v = {w, (float)inner};
+                    for (int i = 0; i < 9; ++i) v.push_back((float)R[i]);
+                    v.push_back(m->type[node] == MGB_NODE_ROOT ? 1.f : 0.f);
+                    C.free_actions[c.time_slot].push_back({OP_JROT, j, m->channel[node], v});   // b: channel now, quad at emission
+                    return MGB_OK;
+                };
+                if (c.type == MGB_CT_JOINT_ROT) {
+                    if (int rc = rot_action(c.node[0], c.orient_q, 1.0)) return rc;
+                } else {
+                    MGB_REQUIRE(c.n_points > 0 && points && c.points_offset >= 0 && c.points_offset + c.n_points <= n_points,
+                                "constraint %d: pose points out of range", j);
+                    for (int q = 0; q < c.n_points; ++q) {
+                        const mgb_pose_point& pp = points[c.points_offset + q];
+                        const double v2 = pp.target[0] * pp.target[0] + pp.target[1] * pp.target[1] + pp.target[2] * pp.target[2];
+                        MGB_REQUIRE(v2 <= 1.0 + 1e-9, "constraint %d: pose point %d is not the vector part of a unit quaternion", j, q);
+                        const double quat[4] = {sqrt(std::max(0.0, 1.0 - v2)), pp.target[0], pp.target[1], pp.target[2]};
+                        if (int rc = rot_action(pp.node, quat, pp.weight)) return rc;
+                    }
+                }
+                break;
+            }
+            case MGB_CT_LOCAL_TRAJ: {
+                MGB_REQUIRE(check_node(c.node[0]) && c.n_slots > 0 && check_slot(c.time_slot) && check_slot(c.time_slot + c.n_slots - 1),
+                            "constraint %d: bad node / slot range", j);
+                MGB_REQUIRE(c.n_points >= 3 && points && c.points_offset >= 0 && c.points_offset + c.n_points <= n_points && c.offset[1] > 0,
+                            "constraint %d: bad trajectory table", j);
+                const int sc = C.alloc_scratch(6);
+                MgbOp b;
+                b.code = OP_LT_BEGIN; b.a = sc; b.b = 0; b.c = C.push_cst({(float)c.offset[0]});
+                begins.push_back(b);
+                const int nt = c.n_points - 2;
+                std::vector<float> v = {(float)(1.0 / c.offset[1]), (float)nt, (float)(nt * c.offset[1])};
+                for (int q = 0; q < c.n_points; ++q) {
+                    v.push_back((float)points[c.points_offset + q].target[0]);
+                    v.push_back((float)points[c.points_offset + q].target[2]);
+                }
+                // one copy of the table in the constant pool, shared by the per-frame ops
+                const int tab_off = C.push_cst(v);
+                for (int f = 0; f < c.n_slots; ++f) {
+                    Action a{OP_LT_ACC, sc, 0, {}};
+                    a.cst_at = tab_off;
+                    C.add(c.time_slot + f, c.node[0], a);
+                }
+                finals.push_back({OP_LT_END, j, sc, {w}});
+                break;
+            }
             default:
                 mgb_set_error("constraint %d: type %d is outside the device path", j, c.type);
                 return MGB_E_UNSUPPORTED;
@@ -527,7 +597,6 @@ extern "C" int mgb_constraints_pack(const mgb_model* m, const mgb_constraint_des
     MGB_REQUIRE(C.scratch_used <= MGB_SCRATCH_FLOATS, "constraint set needs %d scratch floats (max %d)", C.scratch_used, MGB_SCRATCH_FLOATS);
 
     // ---- program: [CA begins] [alignment prelude] [slots ...] [finals] -------
-    C.cst.push_back(0.f);  // offset 0 is a valid dummy for ops without constants
     for (const MgbOp& b : begins) C.ops.push_back(b);
     const bool do_align = align && align->mode == 1;
     if (do_align) {
@@ -592,6 +661,7 @@ extern "C" int mgb_constraints_pack(const mgb_model* m, const mgb_constraint_des
         };
         if (o.code == OP_ROOT) { o.a = remap(o.a); o.b = remap(o.b); }
         else if (o.code == OP_JOINT || o.code == OP_ALIGN) { o.a = remap(o.a); }
+        else if (o.code == OP_JROT) { o.b = remap(o.b); }
     }
     if (!frames_ok) c->ops_frames.clear();
     c->cst = C.cst;

@@ -92,6 +92,10 @@ enum MgbOpCode : int32_t {
     OP_CA_ACC = 16,   // a = scratch offset, b = axis mask, c -> target[3]
     OP_CA_END = 17,   // a = term, b = scratch offset, c -> weight
     OP_RESET = 18,    // G = identity (between slots; not required, kept for clarity)
+    OP_JROT = 19,     // a = term, b = rotation quad of the joint (raw channels, no FK), c -> weight, inner weight, target R[9], is_root
+    OP_LT_BEGIN = 20, // a = scratch offset (6 floats: sum, arc length, last position[3], started), c -> start_t
+    OP_LT_ACC = 21,   // a = scratch offset, c -> step, n_table, full arc length, table (x, z) * (n_table + 1) [last = last control point]
+    OP_LT_END = 22,   // a = term, b = scratch offset, c -> weight
 };
 
 #define MGB_SCRATCH_FLOATS 160

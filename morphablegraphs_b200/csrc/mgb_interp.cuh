@@ -275,6 +275,77 @@ struct MgbInterp {
                     for (int c = 0; c < CPT; ++c) emit(c, op.a, cs[0], scratch[c][op.b]);
                     break;
                 }
+                case OP_JROT: {
+                    // |R_target - R(q / |q|)|_F of one joint's own quaternion channels (no FK): JointRotationConstraint
+                    // (joint_rotation_constraint.py:62-75) and, summed with inner weights, PoseConstraintQuatFrame
+                    float4 q[CPT];
+                    quad(op.b, q);
+#pragma unroll
+                    for (int c = 0; c < CPT; ++c) {
+                        float qw = q[c].x, qx = q[c].y, qy = q[c].z, qz = q[c].w;
+                        if (cs[11] != 0.f) {   // root joint: the aligned frame carries the aligning rotation about +y
+                            const float w2 = al_qw[c] * qw - al_qy[c] * qy, x2 = al_qw[c] * qx + al_qy[c] * qz;
+                            const float y2 = al_qw[c] * qy + al_qy[c] * qw, z2 = al_qw[c] * qz - al_qy[c] * qx;
+                            qw = w2; qx = x2; qy = y2; qz = z2;
+                        }
+                        const float n = fmaf(qw, qw, fmaf(qx, qx, fmaf(qy, qy, qz * qz)));
+                        const float s2 = __fdividef(2.f, n);
+                        const float xx = qx * qx * s2, yy = qy * qy * s2, zz = qz * qz * s2;
+                        const float xy = qx * qy * s2, xz = qx * qz * s2, yz = qy * qz * s2;
+                        const float wx = qw * qx * s2, wy = qw * qy * s2, wz = qw * qz * s2;
+                        const float R[9] = {1.f - yy - zz, xy - wz, xz + wy, xy + wz, 1.f - xx - zz, yz - wx, xz - wy, yz + wx, 1.f - xx - yy};
+                        float d = 0.f;
+#pragma unroll
+                        for (int i = 0; i < 9; ++i) { const float e = cs[2 + i] - R[i]; d = fmaf(e, e, d); }
+                        emit(c, op.a, cs[0], cs[1] * sqrtf(d));
+                    }
+                    break;
+                }
+                case OP_LT_BEGIN: {
+#pragma unroll
+                    for (int c = 0; c < CPT; ++c) {
+                        scratch[c][op.a] = 0.f;
+                        scratch[c][op.a + 1] = cs[0];
+                        scratch[c][op.a + 5] = 0.f;
+                    }
+                    break;
+                }
+                case OP_LT_ACC: {
+                    // LocalTrajectoryConstraint.get_spline_distance (local_trajectory_constraint.py:66-83): the arc length walked by
+                    // the joint so far picks the target on the trajectory, tabulated by arc length (linear between samples)
+                    const float step_inv = cs[0], full = cs[2];
+                    const int nt = (int)cs[1];
+                    const float* tb = cs + 3;
+#pragma unroll
+                    for (int c = 0; c < CPT; ++c) {
+                        float* st = scratch[c] + op.a;
+                        const float px = G[c].tx, py = G[c].ty, pz = G[c].tz;
+                        if (st[5] != 0.f) {
+                            const float dx = st[2] - px, dy = st[3] - py, dz = st[4] - pz;
+                            st[1] += sqrtf(fmaf(dx, dx, fmaf(dy, dy, dz * dz)));
+                        }
+                        float tx, tz;
+                        if (st[1] <= full) {
+                            const float u = fmaxf(st[1], 0.f) * step_inv;
+                            int i0 = min((int)u, nt - 1);
+                            const float f = u - (float)i0;
+                            tx = fmaf(f, tb[2 * i0 + 2] - tb[2 * i0], tb[2 * i0]);
+                            tz = fmaf(f, tb[2 * i0 + 3] - tb[2 * i0 + 1], tb[2 * i0 + 1]);
+                        } else {   // beyond the end: the last control point
+                            tx = tb[2 * nt + 2];
+                            tz = tb[2 * nt + 3];
+                        }
+                        const float ex = tx - px, ez = tz - pz;
+                        st[0] += fmaf(ex, ex, ez * ez);
+                        st[2] = px; st[3] = py; st[4] = pz; st[5] = 1.f;
+                    }
+                    break;
+                }
+                case OP_LT_END: {
+#pragma unroll
+                    for (int c = 0; c < CPT; ++c) emit(c, op.a, cs[0], scratch[c][op.b]);
+                    break;
+                }
                 default:
                     break;
             }

@@ -1189,15 +1189,16 @@ int mgb_score_tc_prepare_constraints(const mgb_model* m, mgb_constraints* c) {
     int chunk = 0;
     for (size_t i = 0; i < c->ops_tc.size(); ++i) {
         MgbOp& o = c->ops_tc[i];
-        const bool qa = o.code == OP_ROOT || o.code == OP_JOINT || o.code == OP_ALIGN, qb = o.code == OP_ROOT;
-        if (!qa) continue;
-        const int ca = pos[o.a] / NQC, cb = qb ? pos[o.b] / NQC : ca;
+        // quad operands: a of ROOT / JOINT / ALIGN, b of ROOT / JROT
+        const bool qa = o.code == OP_ROOT || o.code == OP_JOINT || o.code == OP_ALIGN, qb = o.code == OP_ROOT || o.code == OP_JROT;
+        if (!qa && !qb) continue;
+        const int ca = qa ? pos[o.a] / NQC : pos[o.b] / NQC, cb = qb ? pos[o.b] / NQC : ca;
         if (ca != cb || ca < chunk) {
             mgb_set_error("tensor-core score: program is not monotone in its quads");
             return MGB_E_UNSUPPORTED;
         }
         while (chunk < ca) c->phase_tc[++chunk] = (int)i;
-        o.a = pos[o.a] % NQC;
+        if (qa) o.a = pos[o.a] % NQC;
         if (qb) o.b = pos[o.b] % NQC;
     }
     while (chunk < n_chunks) c->phase_tc[++chunk] = (int)c->ops_tc.size();

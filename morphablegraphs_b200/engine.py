@@ -165,6 +165,7 @@ class DeviceModel(object):
         sk = pack_skeleton(skeleton)
         self.node_index = sk["index"]
         self.node_names = sk["names"]
+        self.channel_node = {int(ch): i for i, ch in enumerate(sk["channel"]) if ch >= 0}
         offset = np.ascontiguousarray(sk["offset"], dtype=np.float64)
         rotation = np.ascontiguousarray(sk["rotation"], dtype=np.float64)
         d = _lib.ModelDesc()
@@ -296,6 +297,27 @@ def _mask_and_target(position):
     return mask, tgt
 
 
+def _quaternion_from_rotmat(R):
+    """Unit quaternion (w, x, y, z), w >= 0, of a rotation matrix (Shepperd's method, fp64)."""
+    R = np.asarray(R, dtype=np.float64)[:3, :3]
+    t = np.trace(R)
+    if t > 0.0:
+        s = np.sqrt(t + 1.0) * 2.0
+        q = [0.25 * s, (R[2, 1] - R[1, 2]) / s, (R[0, 2] - R[2, 0]) / s, (R[1, 0] - R[0, 1]) / s]
+    elif R[0, 0] > R[1, 1] and R[0, 0] > R[2, 2]:
+        s = np.sqrt(1.0 + R[0, 0] - R[1, 1] - R[2, 2]) * 2.0
+        q = [(R[2, 1] - R[1, 2]) / s, 0.25 * s, (R[0, 1] + R[1, 0]) / s, (R[0, 2] + R[2, 0]) / s]
+    elif R[1, 1] > R[2, 2]:
+        s = np.sqrt(1.0 + R[1, 1] - R[0, 0] - R[2, 2]) * 2.0
+        q = [(R[0, 2] - R[2, 0]) / s, (R[0, 1] + R[1, 0]) / s, 0.25 * s, (R[1, 2] + R[2, 1]) / s]
+    else:
+        s = np.sqrt(1.0 + R[2, 2] - R[0, 0] - R[1, 1]) * 2.0
+        q = [(R[1, 0] - R[0, 1]) / s, (R[0, 2] + R[2, 0]) / s, (R[1, 2] + R[2, 1]) / s, 0.25 * s]
+    q = np.asarray(q, dtype=np.float64)
+    q /= np.linalg.norm(q)
+    return -q if q[0] < 0.0 else q
+
+
 def flatten_constraints(dmodel, mp_constraints):
     """MotionPrimitiveConstraints -> (ConstraintDesc[], PosePoint[], times).
     Field names per type: SURVEY.md Appendix C / the reference classes cited in
@@ -313,10 +335,10 @@ def flatten_constraints(dmodel, mp_constraints):
         return slot_of[t]
 
     clist = list(mp_constraints.constraints)
-    # CA constraints need consecutive slots for the integer frames 0..F-1: allocate them first
+    # CA / local-trajectory constraints need consecutive slots for the integer frames 0..F-1: allocate them first
     ca_frames = 0
     for c in clist:
-        if c.constraint_type == "ca_constraint":
+        if c.constraint_type in ("ca_constraint", "local_trajectory"):
             ca_frames = max(ca_frames, int(c.n_canonical_frames))
     for f in range(ca_frames):
         slot(float(f))
@@ -328,11 +350,58 @@ def flatten_constraints(dmodel, mp_constraints):
             raise UnsupportedConstraintError("joint %r is not in the packed skeleton" % (name,))
         return idx[name]
 
+    def channel_node(channel):
+        # node whose quaternion occupies frame channels [3 + 4 channel, 7 + 4 channel) (mg_state_planner.py:288)
+        if channel not in dmodel.channel_node:
+            raise UnsupportedConstraintError("no joint with quaternion frame index %d" % channel)
+        return dmodel.channel_node[channel]
+
     for j, c in enumerate(clist):
         d = descs[j]
         ct = c.constraint_type
         d.weight = float(c.weight_factor)
-        if ct in ("keyframe_position", "keyframe_relative_position"):
+        if ct is None and hasattr(c, "constraint_rotmat"):
+            # JointRotationConstraint (joint_rotation_constraint.py:62-75): channel = position of the joint in node_name_frame_map
+            d.type = _lib.CT_JOINT_ROT
+            d.node[0] = channel_node(list(skeleton.node_name_frame_map.keys()).index(c.joint_name))
+            d.time_slot = slot(c.frame_idx)
+            d.orient_q = (C.c_double * 4)(*_quaternion_from_rotmat(c.constraint_rotmat))
+        elif ct == "keyframe_pose" and not hasattr(c, "node_names"):
+            # PoseConstraintQuatFrame (pose_constraint_quat_frame.py:47-52): frame 0, joints 1.. against the target frame,
+            # weight i of skeleton.get_joint_weights() on joint i + 1 (anim_utils calculate_weighted_frame_distance_quat)
+            weights = list(skeleton.get_joint_weights())
+            target = np.asarray(c.pose_constraint, dtype=np.float64)
+            d.type = _lib.CT_QUAT_FRAME
+            d.time_slot = slot(0.0)
+            d.points_offset = len(points)
+            d.n_points = len(weights) - 1
+            for i in range(len(weights) - 1):
+                q = target[3 + 4 * (i + 1):7 + 4 * (i + 1)]
+                q = q / np.linalg.norm(q)
+                if q[0] < 0.0:
+                    q = -q
+                pp = _lib.PosePoint()
+                pp.node = channel_node(i + 1)
+                pp.target = (C.c_double * 3)(float(q[1]), float(q[2]), float(q[3]))
+                pp.weight = float(weights[i])
+                points.append(pp)
+        elif ct == "local_trajectory":
+            from .constraints import tabulate_trajectory
+            table = tabulate_trajectory(c.trajectory)
+            d.type = _lib.CT_LOCAL_TRAJ
+            d.node[0] = node(c.joint_name)
+            d.time_slot = 0
+            d.n_slots = int(c.n_canonical_frames)
+            d.offset = (C.c_double * 4)(float(c.start_t), float(table.step), 0.0, 0.0)
+            d.points_offset = len(points)
+            d.n_points = len(table.points) + 1
+            for pt in list(table.points) + [table.last_control_point]:
+                pp = _lib.PosePoint()
+                pp.node = 0
+                pp.target = (C.c_double * 3)(float(pt[0]), float(pt[1]), float(pt[2]))
+                pp.weight = 0.0
+                points.append(pp)
+        elif ct in ("keyframe_position", "keyframe_relative_position"):
             d.type = _lib.CT_POSITION if ct == "keyframe_position" else _lib.CT_RELATIVE
             d.node[0] = node(c.joint_name)
             d.time_slot = slot(c.canonical_keyframe)
@@ -356,8 +425,6 @@ def flatten_constraints(dmodel, mp_constraints):
             d.time_slot = slot(c.canonical_keyframe)
             d.dir = (C.c_double * 2)(float(c.target_dir[0]), float(c.target_dir[1]))
         elif ct == "keyframe_pose":
-            if not hasattr(c, "node_names"):
-                raise UnsupportedConstraintError("PoseConstraintQuatFrame is outside the device path")
             n = len(c.node_names)
             if n > _lib.MAX_POSE_POINTS:
                 raise UnsupportedConstraintError("pose constraint with %d points (max %d)" % (n, _lib.MAX_POSE_POINTS))

@@ -254,12 +254,23 @@ def spec(cls_name, desc, precision=1.0, weight=1.0):
     return {"class": cls_name, "desc": desc, "precision": precision, "weight": weight}
 
 
-def build_constraints(factory, skeleton, specs):
+def build_constraints(factory, skeleton, specs, trajectories=None):
     """Instantiate constraint objects from specs.  `factory` maps class name ->
     constructor with the reference's signature
     `(skeleton, constraint_desc, precision, weight_factor)`; the reference's
-    classes and this package's mirror classes both fit."""
+    classes and this package's mirror classes both fit.  A descriptor's
+    `"trajectory"` entry, when it is a plain dict (specs are JSON), is replaced by
+    `trajectories(dict)` - default: an `ArcLengthTable` from its `points` / `step` /
+    `last_control_point`."""
     out = []
     for sp in specs:
-        out.append(factory[sp["class"]](skeleton, dict(sp["desc"]), sp["precision"], sp["weight"]))
+        desc = dict(sp["desc"])
+        if isinstance(desc.get("trajectory"), dict):
+            if trajectories is not None:
+                desc["trajectory"] = trajectories(desc["trajectory"])
+            else:
+                from .constraints import ArcLengthTable
+                t = desc["trajectory"]
+                desc["trajectory"] = ArcLengthTable(t["points"], t["step"], t.get("last_control_point"))
+        out.append(factory[sp["class"]](skeleton, desc, sp["precision"], sp["weight"]))
     return out

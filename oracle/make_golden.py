@@ -44,14 +44,26 @@ def reference_factory(ns):
         "FeetConstraint": sc.FeetConstraint,
         "LookAtConstraint": sc.LookAtConstraint,
         "GlobalTransformCAConstraint": ns.ca_constraint.GlobalTransformCAConstraint,
+        "JointRotationConstraint": ns.joint_rotation_constraint.JointRotationConstraint,
+        "PoseConstraintQuatFrame": ns.pose_constraint_quat_frame.PoseConstraintQuatFrame,
+        "LocalTrajectoryConstraint": ns.local_trajectory_constraint.LocalTrajectoryConstraint,
     }
+
+
+def reference_trajectory(ns):
+    """desc["trajectory"] dict -> the reference's own arc-length parameterised Catmull-Rom spline
+    (constraints/spatial_constraints/splines/parameterized_spline.py)."""
+    def make(t):
+        with _quiet():
+            return ns.parameterized_spline.ParameterizedSpline([np.array(p, dtype=np.float64) for p in t["control_points"]])
+    return make
 
 
 def build_mp_constraints(ns, skeleton, specs, is_local=True):
     mpc = ns.motion_primitive_constraints.MotionPrimitiveConstraints()
     mpc.skeleton = skeleton
     mpc.is_local = is_local
-    mpc.constraints = syn.build_constraints(reference_factory(ns), skeleton, specs)
+    mpc.constraints = syn.build_constraints(reference_factory(ns), skeleton, specs, reference_trajectory(ns))
     return mpc
 
 
@@ -66,6 +78,33 @@ def make_specs(ns, node, skeleton, F, rng, which):
 
     specs = []
     if which == "config1":
+        specs.append(syn.spec("GlobalTransformConstraint",
+                              syn.position_constraint_desc("RightFoot", pos(0, "RightFoot", F - 1), F - 1, F), 1.0, 1.0))
+        return specs
+    if which == "rot":
+        # round 2: the constraint types of SURVEY.md rows a12 / a13 that read joint rotations or walk all frames
+        from morphablegraphs_b200.constraints import tabulate_trajectory
+        joints = list(skeleton.node_name_frame_map.keys())
+        jn = joints[5]
+        ji = joints.index(jn)
+        q = np.array(spl[0].evaluate(F // 2)[3 + 4 * ji:7 + 4 * ji], dtype=np.float64)
+        specs.append(syn.spec("JointRotationConstraint",
+                              {"joint_name": jn, "rotation_type": "quaternion", "rotation_constraint": (q * 1.7).tolist(),
+                               "frame_index": F // 2, "canonical_keyframe": F // 2, "semanticAnnotation": syn.sem("mid")}, 1.0, 1.3))
+        specs.append(syn.spec("JointRotationConstraint",
+                              {"joint_name": joints[0], "rotation_type": "euler", "rotation_constraint": [10.0, 35.0, -5.0],
+                               "frame_index": F - 1, "canonical_keyframe": F - 1, "semanticAnnotation": syn.sem()}, 1.0, 0.6))
+        specs.append(syn.spec("PoseConstraintQuatFrame",
+                              {"canonical_keyframe": 0, "frame_constraint": np.asarray(spl[1].evaluate(0)).tolist(),
+                               "semanticAnnotation": syn.sem("start")}, 1.0, 2.0))
+        cps = [[0.0, 0.0, 0.0], [5.0, 0.0, 15.0], [12.0, 0.0, 30.0], [10.0, 0.0, 45.0], [0.0, 0.0, 60.0], [-8.0, 0.0, 80.0]]
+        traj = reference_trajectory(ns)({"control_points": cps})
+        tab = tabulate_trajectory(traj)
+        specs.append(syn.spec("LocalTrajectoryConstraint",
+                              {"canonical_keyframe": None, "joint_name": "Hips", "start_t": 5.0, "n_canonical_frames": F,
+                               "semanticAnnotation": syn.sem("path"),
+                               "trajectory": {"control_points": cps, "points": tab.points.tolist(), "step": tab.step,
+                                              "last_control_point": tab.last_control_point.tolist()}}, 1.0, 0.01))
         specs.append(syn.spec("GlobalTransformConstraint",
                               syn.position_constraint_desc("RightFoot", pos(0, "RightFoot", F - 1), F - 1, F), 1.0, 1.0))
         return specs
@@ -494,12 +533,17 @@ def main():
         ("xs_mixed", dict(shape="XS", which="mixed", n_samples=32, seed=2028)),
         ("l_mixed", dict(shape="L", which="mixed", n_samples=12, seed=2029)),
     ]
+    if "--only-rot" in sys.argv:
+        cases = [("s_rot", dict(shape="S", which="rot", n_samples=64, seed=2033)),
+                 ("s_rot_nonlocal", dict(shape="S", which="rot", n_samples=32, seed=2034, non_local=True))]
     for name, kw in cases:
         out, _ = run_case(ns, **kw)
         # keep fixtures small: coefficients only for the first 8 candidates
         out["coeffs"] = out["coeffs"][:8]
         np.savez_compressed(os.path.join(GOLDEN_DIR, name + ".npz"), **out)
         print(name, "costs[:3]", out["costs"][:3], "best", int(out["best_idx"]), float(out["min_error"]))
+    if "--only-rot" in sys.argv:
+        return 0
     out = run_tree_case(ns)
     np.savez_compressed(os.path.join(GOLDEN_DIR, "s_tree.npz"), **out)
     print("s_tree", out["cluster_tree_results"][:, 0], out["feature_tree_results"][:, 0])

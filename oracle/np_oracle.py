@@ -273,6 +273,42 @@ def term_errors(c, ma, skeleton, coeffs):
     `c.evaluate_motion_spline` returns)."""
     ct = c.constraint_type
     N = coeffs.shape[0]
+    if ct is None and hasattr(c, "constraint_rotmat"):
+        # reference joint_rotation_constraint.py:62-75: |R_target - R(q / |q|)|_F of the joint's own channels
+        frame = _frames_at(ma, coeffs, c.frame_idx)
+        ji = list(skeleton.node_name_frame_map.keys()).index(c.joint_name)
+        q = frame[:, 3 + 4 * ji:7 + 4 * ji]
+        R = quaternion_matrix_batch(q / np.linalg.norm(q, axis=1, keepdims=True))
+        Rt = np.asarray(c.constraint_rotmat, dtype=np.float64)[:3, :3]
+        return np.sqrt(np.sum((Rt[None] - R) ** 2, axis=(1, 2)))
+    if ct == "keyframe_pose" and not hasattr(c, "node_names"):
+        # reference pose_constraint_quat_frame.py:47-52 through anim_utils' calculate_weighted_frame_distance_quat
+        # (PARITY UNPINNED, see oracle/standin): joints 1.., weight i on joint i + 1, rotation-matrix distance
+        frame = _frames_at(ma, coeffs, 0)
+        w = list(skeleton.get_joint_weights())
+        tgt = np.asarray(c.pose_constraint, dtype=np.float64)
+        err = np.zeros(N)
+        for i in range(len(w) - 1):
+            q = frame[:, 3 + 4 * (i + 1):7 + 4 * (i + 1)]
+            R = quaternion_matrix_batch(q / np.linalg.norm(q, axis=1, keepdims=True))
+            qt = tgt[3 + 4 * (i + 1):7 + 4 * (i + 1)]
+            Rt = quaternion_matrix_batch((qt / np.linalg.norm(qt))[None])[0]
+            err += w[i] * np.sqrt(np.sum((Rt[None] - R) ** 2, axis=(1, 2)))
+        return err
+    if ct == "local_trajectory":
+        # reference local_trajectory_constraint.py:58-83: walk the frames, the arc length covered so far picks the target
+        times = list(range(int(c.n_canonical_frames)))
+        frames = eval_frames(ma, coeffs, times)
+        p = fk_global(skeleton, frames, c.joint_name)[1]         # [N, F, 3]
+        err = np.zeros(N)
+        for n in range(N):
+            t = float(c.start_t)
+            for f in range(p.shape[1]):
+                if f > 0:
+                    t += np.linalg.norm(p[n, f - 1] - p[n, f])
+                target = c.trajectory.query_point_by_absolute_arc_length(t)
+                err[n] += (target[0] - p[n, f, 0]) ** 2 + (target[2] - p[n, f, 2]) ** 2
+        return err
     if ct in ("keyframe_position", "keyframe_relative_position"):
         frame = _frames_at(ma, coeffs, c.canonical_keyframe)
         err = np.zeros(N)

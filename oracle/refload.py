@@ -134,6 +134,9 @@ def load():
     ns.spatial_constraints = imp(_PKG + ".constraints.spatial_constraints")
     ns.ca_constraint = imp(_PKG + ".constraints.spatial_constraints.keyframe_constraints.global_transform_ca_constraint")
     ns.joint_rotation_constraint = imp(_PKG + ".constraints.spatial_constraints.keyframe_constraints.joint_rotation_constraint")
+    ns.pose_constraint_quat_frame = imp(_PKG + ".constraints.spatial_constraints.keyframe_constraints.pose_constraint_quat_frame")
+    ns.local_trajectory_constraint = imp(_PKG + ".constraints.spatial_constraints.keyframe_constraints.local_trajectory_constraint")
+    ns.parameterized_spline = imp(_PKG + ".constraints.spatial_constraints.splines.parameterized_spline")
     ns.motion_primitive_constraints = imp(_PKG + ".constraints.motion_primitive_constraints")
     ns.objective_functions = imp(_PKG + ".motion_generator.optimization.objective_functions")
     ns.motion_primitive_generator = imp(_PKG + ".motion_generator.motion_primitive_generator")

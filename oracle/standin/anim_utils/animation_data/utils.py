@@ -93,14 +93,20 @@ def calculate_point_cloud_distance(a, b):
 
 
 def quat_distance(quat_a, quat_b):
+    """PARITY UNPINNED (anim_utils is absent).  Restated after the reference's own in-tree twin of this
+    comparison, JointRotationConstraint.evaluate_frame (joint_rotation_constraint.py:62-75): normalise
+    both quaternions, Frobenius norm of the difference of their rotation matrices."""
+    from transformations import quaternion_matrix
     quat_a = np.asarray(quat_a, dtype=np.float64)
     quat_b = np.asarray(quat_b, dtype=np.float64)
-    if np.dot(quat_a, quat_b) < 0:
-        return np.linalg.norm(quat_a + quat_b)
-    return np.linalg.norm(quat_a - quat_b)
+    quat_a = quat_a / np.linalg.norm(quat_a)
+    quat_b = quat_b / np.linalg.norm(quat_b)
+    return float(np.linalg.norm(np.ravel(quaternion_matrix(quat_a) - quaternion_matrix(quat_b))))
 
 
 def calculate_weighted_frame_distance_quat(quat_frame_a, quat_frame_b, weights):
+    """PARITY UNPINNED.  Joint i + 1 weighted by weights[i], root excluded - the loop the reference's own
+    residual form of the same comparison runs (pose_constraint_quat_frame.py:60-70)."""
     diff = 0.0
     for i in range(len(weights) - 1):
         q1 = quat_frame_a[(i + 1) * 4 + 3:(i + 2) * 4 + 3]

@@ -339,6 +339,53 @@ def test_large_tc_against_oracle(large):
     _check_argmin(refn, int(resn["best_idx"][0]), float(resn["best_cost"][0]))
 
 
+def test_large_rotation_and_trajectory_terms(large):
+    """JointRotationConstraint (root and inner joint), the quaternion-frame pose term and a LocalTrajectoryConstraint
+    on the L model: the raw-channel ops ride the tensor-core path (their quads are remapped per chunk) and agree
+    with the oracle; sampled and given candidates agree with each other."""
+    from oracle import np_oracle as O
+    from morphablegraphs_b200 import engine, synthetic as syn, MotionPrimitiveConstraints, CONSTRAINT_FACTORY
+    from morphablegraphs_b200.constraints import ArcLengthTable
+    dm = large.dm
+    F = large.F
+    joints = list(large.skeleton.node_name_frame_map.keys())
+    ma = O.ModelArrays(large.node)
+    held = dm.sample(2, seed=77).cpu().numpy().astype(np.float64)
+    fr = O.eval_frames(ma, O.back_project_coeffs(ma, held), [0.0, F // 2])
+    ji = 23
+    q = fr[0, 1, 3 + 4 * ji:7 + 4 * ji]
+    pts = np.stack([np.linspace(0.0, 9.0, 65) ** 1.5, np.zeros(65), np.linspace(0.0, 70.0, 65)], axis=1)
+    step = float(np.mean(np.linalg.norm(pts[1:] - pts[:-1], axis=1)))
+    specs = [syn.spec("JointRotationConstraint", {"joint_name": joints[ji], "rotation_type": "quaternion", "rotation_constraint": q.tolist(),
+                                                  "frame_index": F // 2, "canonical_keyframe": F // 2, "semanticAnnotation": syn.sem()}, 1.0, 1.5),
+             syn.spec("JointRotationConstraint", {"joint_name": joints[0], "rotation_type": "euler", "rotation_constraint": [5.0, -20.0, 3.0],
+                                                  "frame_index": F - 1, "canonical_keyframe": F - 1, "semanticAnnotation": syn.sem()}, 1.0, 0.7),
+             syn.spec("LocalTrajectoryConstraint", {"canonical_keyframe": None, "joint_name": "Hips", "start_t": 2.0, "n_canonical_frames": F,
+                                                    "semanticAnnotation": syn.sem(), "trajectory": {"points": pts.tolist(), "step": step}}, 1.0, 0.02),
+             syn.spec("GlobalTransformConstraint", syn.position_constraint_desc("RightHand", [10.0, 120.0, 50.0], F - 1, F), 1.0, 1.0)]
+    mpc = MotionPrimitiveConstraints()
+    mpc.skeleton = large.skeleton
+    mpc.is_local = True
+    mpc.constraints = syn.build_constraints(CONSTRAINT_FACTORY, large.skeleton, specs)
+    # the quaternion-frame pose term of the reference asserts a 79-float frame (pose_constraint_quat_frame.py:38); the device op
+    # is the same per-joint rotation distance, exercised here on the 283-float frame of the L skeleton through the mirror class
+    mpc.constraints.append(CONSTRAINT_FACTORY["PoseConstraintQuatFrame"](large.skeleton, {"canonical_keyframe": 0, "frame_constraint": fr[1, 0].tolist(),
+                                                                                        "semanticAnnotation": syn.sem()}, 1.0, 0.3))
+    dc = engine.DeviceConstraints(dm, mpc)
+    n = 700
+    S = dm.sample(n, seed=6)
+    S64 = S.cpu().numpy().astype(np.float64)
+    ref, ref_terms = O.candidate_costs(large.node, large.skeleton, mpc, S64, return_terms=True)
+    res = dc.score(S, k=1, return_cost=True, return_terms=True)
+    assert rel_err(res["terms"].cpu().numpy(), ref_terms).max() < RTOL
+    assert rel_err(res["cost"].cpu().numpy(), ref).max() < RTOL
+    _check_argmin(ref, int(res["best_idx"][0]), float(res["best_cost"][0]))
+    counts = dm.component_counts(n, seed=6)
+    fused = dc.sample_score(n, seed=6, counts=counts, k=1, return_cost=True, quality_scale=0.1)
+    staged = dc.score(dm.sample(n, seed=6, counts=counts), k=1, return_cost=True, quality_scale=0.1)
+    assert rel_err(fused["cost"].cpu().numpy(), staged["cost"].cpu().numpy()).max() < RTOL
+
+
 def test_large_fused_sample_score(large):
     """mgb_sample_score on the tensor cores (z -> s = mu + L z as a GEMM, tiles aligned to mixture components)
     == mgb_sample (SIMT) then mgb_score, up to the 3xTF32 rounding of s."""

