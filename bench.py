@@ -492,6 +492,42 @@ def measure_e2e(gpu, case, dm, dc, n, n_total, base, qs, counts, steps):
                                      "constraint program compiled + uploaded, candidates drawn on the device (K1 fused), best latent "
                                      "vector and min_error returned to the host" % n_total,
                              "min_error": float(mpc.min_error)}
+    if gpu.world == 1 and dm.D <= 32:
+        # ---- cross-option batching: the planner's option loop (graph_walk_planner.py:216-226,
+        # mg_state_planner.py:946-968: every outgoing edge scored with n_random_samples = 100, one after another) as ONE
+        # launch (generate_constrained_samples -> mgb_sample_score_multi) against one generate_constrained_sample per option
+        from morphablegraphs_b200 import MotionPrimitiveConstraints
+        n_opt, n_s = 4, 100
+        gen4 = MotionPrimitiveGenerator(None, {"n_random_samples": n_s, "use_local_coordinates": prev is None}, skeleton=skeleton, seed=12)
+        opts = []
+        for j in range(n_opt):
+            o = MotionPrimitiveConstraints()
+            o.skeleton, o.is_local, o.constraints = mpc.skeleton, mpc.is_local, mpc.constraints
+            opts.append((node, o, prev))
+
+        def touch():
+            state["i"] += 1
+            c0.weight_factor = 1.0 + 1e-6 * (state["i"] % 2)
+
+        def timed(fn, reps=50):
+            for _ in range(5):
+                touch(); fn()
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            for _ in range(reps):
+                touch(); fn()
+            torch.cuda.synchronize()
+            return 1e3 * (time.perf_counter() - t0) / reps
+
+        l0 = engine.launch_count()
+        ms_batch = timed(lambda: gen4.generate_constrained_samples(opts))
+        launches_batch = (engine.launch_count() - l0) / 55.0
+        ms_seq = timed(lambda: [gen4.generate_constrained_sample(o[0], o[1], prev_frames=o[2]) for o in opts])
+        c0.weight_factor = 1.0
+        e2e["option_batch"] = {"options": n_opt, "samples_per_option": n_s, "ms_one_launch": ms_batch, "ms_one_call_per_option": ms_seq,
+                               "launches_per_batch": launches_batch,
+                               "call": "MotionPrimitiveGenerator.generate_constrained_samples(options) -> mgb_sample_score_multi: constraint programs "
+                                       "compiled + uploaded, all options drawn, scored and reduced in one launch, results in one D2H copy"}
     return e2e
 
 

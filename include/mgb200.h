@@ -234,6 +234,35 @@ int mgb_sample_score(const mgb_model* m, const mgb_constraints* c, int64_t n, in
                      float magnitude_scale, float* d_cost /*[n] or NULL*/, int32_t k, float* d_best_cost,
                      int64_t* d_best_idx, void* d_workspace, size_t workspace_bytes, void* stream);
 
+/* The planner-facing form of mgb_sample_score: ONE call per motion-primitive step that returns, in host
+ * memory, the best cost, its global index and the winning latent vector itself (re-drawn on the device by the
+ * CTA that folds the per-CTA minima - no second launch, one D2H copy, one synchronisation).  Replaces the
+ * whole of _get_best_fit_sample_using_gmm (motion_primitive_generator.py:192-206).  h_best_row [D] or NULL.
+ * Serialised per device (library-owned result buffers). */
+int mgb_sample_score_best(const mgb_model* m, const mgb_constraints* c, int64_t n, int64_t index_base,
+                          const int64_t* h_counts, uint64_t seed, float err_scale, float quality_scale,
+                          float magnitude_scale, float* h_best_cost, int64_t* h_best_idx,
+                          float* h_best_row, void* stream);
+
+/* Cross-option batching: the outgoing options of a planner step - each its own (model, constraint
+ * program, sample count, seed) - sampled, scored and reduced in ONE launch, one arg-min per option.
+ * The reference scores them one after another (GraphWalkPlanner._evaluate_options,
+ * graph_walk_planner.py:216-226; MGStatePlanner.select_best_option, mg_state_planner.py:946-968).
+ * Results per option in host memory: h_best_cost[i], h_best_idx[i], h_best_rows[i * row_stride ...] (or NULL).
+ * All models on one device and of one kernel class (latent dimension <= 16, or <= 32); otherwise
+ * MGB_E_UNSUPPORTED and the caller issues one mgb_sample_score_best per option.  At most 64 options. */
+typedef struct {
+    const mgb_model* model;
+    const mgb_constraints* constraints;
+    int64_t n;            /* candidates of this option                                   */
+    int64_t index_base;   /* first global index (0 unless the option itself is sharded)   */
+    const int64_t* counts; /* [G] per-component counts of the option's whole job           */
+    uint64_t seed;
+    float err_scale, quality_scale, magnitude_scale;
+} mgb_option;
+int mgb_sample_score_multi(const mgb_option* options, int32_t n_options, float* h_best_cost,
+                           int64_t* h_best_idx, float* h_best_rows, int32_t row_stride, void* stream);
+
 /* Same through HOST buffers (pageable or pinned): chunked H2D on a copy stream
  * overlapped with scoring, D2H of the k results; synchronous.  This is the
  * call the reference-side shim makes with the numpy array it already holds. */

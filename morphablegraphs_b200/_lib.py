@@ -86,6 +86,13 @@ class AlignDesc(C.Structure):
     _fields_ = [("mode", C.c_int32), ("prev_heading_deg", C.c_double), ("prev_root", C.c_double * 3)]
 
 
+class Option(C.Structure):
+    """mgb_option (include/mgb200.h): one outgoing option of a planner step."""
+    _fields_ = [("model", C.c_void_p), ("constraints", C.c_void_p), ("n", C.c_int64), ("index_base", C.c_int64),
+                ("counts", C.POINTER(C.c_int64)), ("seed", C.c_uint64), ("err_scale", C.c_float), ("quality_scale", C.c_float),
+                ("magnitude_scale", C.c_float)]
+
+
 CT_POSITION, CT_RELATIVE, CT_DIR2D, CT_POSE, CT_TWO_HANDS, CT_FEET, CT_LOOK_AT, CT_CA, CT_JOINT_ROT, CT_QUAT_FRAME, CT_LOCAL_TRAJ = range(11)
 MAX_POSE_POINTS = 32
 
@@ -105,6 +112,9 @@ SYMBOLS = {
     "mgb_score_workspace_bytes": (_sz, [_i64, _i32]),
     "mgb_score": (C.c_int, [_vp, _vp, _vp, _i32, _i64, _i64, _f, _f, _f, _vp, _vp, _i32, _vp, _vp, _vp, _sz, _vp]),
     "mgb_sample_score": (C.c_int, [_vp, _vp, _i64, _i64, C.POINTER(C.c_int64), C.c_uint64, _f, _f, _f, _vp, _i32, _vp, _vp, _vp, _sz, _vp]),
+    "mgb_sample_score_best": (C.c_int, [_vp, _vp, _i64, _i64, C.POINTER(C.c_int64), C.c_uint64, _f, _f, _f, C.POINTER(C.c_float),
+                                        C.POINTER(C.c_int64), _vp, _vp]),
+    "mgb_sample_score_multi": (C.c_int, [C.POINTER(Option), _i32, _vp, _vp, _vp, _i32, _vp]),
     "mgb_score_host": (C.c_int, [_vp, _vp, _vp, _i32, _i64, _i64, _f, _f, _f, _vp, _i32, _vp, _vp]),
     "mgb_backproject": (C.c_int, [_vp, _vp, _i64, _vp, _i32, _vp]),
     "mgb_eval_frames": (C.c_int, [_vp, _vp, _i64, _pd, _i32, _pi32, _pd, _vp, _vp]),

@@ -9,6 +9,8 @@
 #include <map>
 #include <mutex>
 
+#include <stddef.h>
+
 #include "mgb_internal.cuh"
 
 // ---------------------------------------------------------------------------
@@ -101,6 +103,8 @@ static int upload(T** dst, const std::vector<T>& src) {
     MGB_CUDA(cudaMemcpy(*dst, src.data(), sizeof(T) * src.size(), cudaMemcpyHostToDevice));
     return MGB_OK;
 }
+
+static void pack_pool_free(mgb_model* m);
 
 // ---------------------------------------------------------------------------
 // model
@@ -278,9 +282,55 @@ extern "C" void mgb_model_destroy(mgb_model* m) {
         if (m->ev_copied[b]) cudaEventDestroy(m->ev_copied[b]);
         if (m->ev_done[b]) cudaEventDestroy(m->ev_done[b]);
     }
+    pack_pool_free(m);
     if (m->copy_stream) cudaStreamDestroy(m->copy_stream);
     if (m->compute_stream) cudaStreamDestroy(m->compute_stream);
     delete m;
+}
+
+// ---------------------------------------------------------------------------
+// constraint-table blocks of a model (MgbPackBlock)
+// ---------------------------------------------------------------------------
+static int pack_block_acquire(const mgb_model* m, size_t bytes, MgbPackBlock** out) {
+    std::lock_guard<std::mutex> lock(m->pool_mutex);
+    if (!m->pack_stream) MGB_CUDA(cudaStreamCreateWithFlags(&m->pack_stream, cudaStreamNonBlocking));
+    MgbPackBlock* best = nullptr;
+    for (MgbPackBlock* b : m->pool)
+        if (!b->busy && b->bytes >= bytes && (!best || b->bytes < best->bytes)) best = b;
+    if (!best) {
+        best = new MgbPackBlock();
+        best->bytes = std::max<size_t>((bytes + 65535) & ~(size_t)65535, 65536);
+        cudaError_t e = cudaMalloc((void**)&best->dev, best->bytes);
+        if (e == cudaSuccess) e = cudaMallocHost((void**)&best->pin, best->bytes);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&best->copied, cudaEventDisableTiming);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&best->used, cudaEventDisableTiming);
+        if (e != cudaSuccess) {
+            mgb_set_error("constraint table block of %zu bytes: %s", best->bytes, cudaGetErrorString(e));
+            cudaFree(best->dev);
+            cudaFreeHost(best->pin);
+            delete best;
+            return MGB_E_CUDA;
+        }
+        m->pool.push_back(best);
+    } else {
+        MGB_CUDA(cudaEventSynchronize(best->copied));   // the pinned mirror is free again (long done in practice)
+    }
+    best->busy = true;
+    *out = best;
+    return MGB_OK;
+}
+
+static void pack_pool_free(mgb_model* m) {
+    for (MgbPackBlock* b : m->pool) {
+        cudaFree(b->dev);
+        cudaFreeHost(b->pin);
+        if (b->copied) cudaEventDestroy(b->copied);
+        if (b->used) cudaEventDestroy(b->used);
+        delete b;
+    }
+    m->pool.clear();
+    if (m->pack_stream) cudaStreamDestroy(m->pack_stream);
+    m->pack_stream = nullptr;
 }
 
 // ---------------------------------------------------------------------------
@@ -672,13 +722,37 @@ extern "C" int mgb_constraints_pack(const mgb_model* m, const mgb_constraint_des
     c->weights.assign(C.weights.begin(), C.weights.begin() + (size_t)4 * n_times);
 
     MGB_CUDA(cudaSetDevice(m->device));
-    int rc = MGB_OK;
-    std::vector<float4> tab4((size_t)c->n_quads * (KP + 1));
-    for (size_t i = 0; i < tab4.size(); ++i) tab4[i] = make_float4(c->tab[4 * i], c->tab[4 * i + 1], c->tab[4 * i + 2], c->tab[4 * i + 3]);
-    if ((rc = upload(&c->d_tab, tab4)) || (rc = upload(&c->d_ops_fused, c->ops_fused)) || (rc = upload(&c->d_ops_frames, c->ops_frames)) ||
-        (rc = upload(&c->d_cst, c->cst))) {
-        mgb_constraints_destroy(c);
+    // ---- one block, one asynchronous copy: [tab4 | ops_fused | ops_frames | cst], each part 256-byte aligned ----------
+    auto al = [](size_t b) { return (b + 255) & ~(size_t)255; };
+    const size_t sz_tab = (size_t)c->n_quads * (KP + 1) * sizeof(float4), sz_of = c->ops_fused.size() * sizeof(MgbOp),
+                 sz_ofr = c->ops_frames.size() * sizeof(MgbOp), sz_cst = c->cst.size() * sizeof(float);
+    const size_t o_tab = 0, o_of = al(sz_tab), o_ofr = o_of + al(sz_of), o_cst = o_ofr + al(sz_ofr), total = o_cst + al(sz_cst);
+    MgbPackBlock* blk = nullptr;
+    if (int rc = pack_block_acquire(m, total, &blk)) {
+        delete c;
         return rc;
+    }
+    c->block = blk;
+    {
+        float* t = reinterpret_cast<float*>(blk->pin + o_tab);
+        memcpy(t, c->tab.data(), sz_tab);    // tab is [n_quads][KP + 1][4] floats = the float4 table
+        if (sz_of) memcpy(blk->pin + o_of, c->ops_fused.data(), sz_of);
+        if (sz_ofr) memcpy(blk->pin + o_ofr, c->ops_frames.data(), sz_ofr);
+        if (sz_cst) memcpy(blk->pin + o_cst, c->cst.data(), sz_cst);
+    }
+    c->d_tab = sz_tab ? reinterpret_cast<float4*>(blk->dev + o_tab) : nullptr;
+    c->d_ops_fused = sz_of ? reinterpret_cast<MgbOp*>(blk->dev + o_of) : nullptr;
+    c->d_ops_frames = sz_ofr ? reinterpret_cast<MgbOp*>(blk->dev + o_ofr) : nullptr;
+    c->d_cst = sz_cst ? reinterpret_cast<float*>(blk->dev + o_cst) : nullptr;
+    {
+        cudaError_t e = cudaStreamWaitEvent(m->pack_stream, blk->used, 0);      // launches that still read the block's previous tenant
+        if (e == cudaSuccess) e = cudaMemcpyAsync(blk->dev, blk->pin, total, cudaMemcpyHostToDevice, m->pack_stream);
+        if (e == cudaSuccess) e = cudaEventRecord(blk->copied, m->pack_stream);
+        if (e != cudaSuccess) {
+            mgb_set_error("constraint table upload failed: %s", cudaGetErrorString(e));
+            mgb_constraints_destroy(c);
+            return MGB_E_CUDA;
+        }
     }
     if (mgb_score_tc_prepare_constraints(m, c) != MGB_OK) {  // e.g. a slot with more quads than one chunk: SIMT path only
         cudaFree(c->d_Bq); cudaFree(c->d_ops_tc); cudaFree(c->d_phase_tc);
@@ -691,8 +765,20 @@ extern "C" int mgb_constraints_pack(const mgb_model* m, const mgb_constraint_des
 extern "C" void mgb_constraints_destroy(mgb_constraints* c) {
     if (!c) return;
     cudaFree(c->d_Bq); cudaFree(c->d_ops_tc); cudaFree(c->d_phase_tc);
-    cudaFree(c->d_tab); cudaFree(c->d_ops_fused); cudaFree(c->d_ops_frames); cudaFree(c->d_cst);
+    if (c->block && c->model) {     // back to the model's pool; kernels in flight are covered by the block's `used` event
+        std::lock_guard<std::mutex> lock(c->model->pool_mutex);
+        c->block->busy = false;
+    }
     delete c;
+}
+
+int mgb_constraints_before_launch(const mgb_constraints* c, cudaStream_t stream) {
+    if (c && c->block) MGB_CUDA(cudaStreamWaitEvent(stream, c->block->copied, 0));
+    return MGB_OK;
+}
+int mgb_constraints_after_launch(const mgb_constraints* c, cudaStream_t stream) {
+    if (c && c->block) MGB_CUDA(cudaEventRecord(c->block->used, stream));
+    return MGB_OK;
 }
 
 extern "C" int32_t mgb_constraints_n_terms(const mgb_constraints* c) { return c ? c->n_terms : 0; }
@@ -722,6 +808,107 @@ extern "C" int mgb_sample_score(const mgb_model* m, const mgb_constraints* c, in
     MGB_REQUIRE(c, "null constraints handle");
     return mgb_launch_score(m, c, 2, nullptr, 0, nullptr, h_counts, seed, n, index_base, err_scale, quality_scale, magnitude_scale, d_cost,
                             nullptr, k, d_best_cost, d_best_idx, d_workspace, workspace_bytes, (cudaStream_t)stream);
+}
+
+// ---------------------------------------------------------------------------
+// planner-facing entries: results (cost, index, winning row) come back to HOST memory in one copy
+// ---------------------------------------------------------------------------
+namespace {
+constexpr int SCR_MAX_JOBS = 64;
+constexpr int SCR_ROW = 256;    // floats per winning row (latent dimension <= 256)
+struct ScrResult {
+    float cost;
+    int pad;
+    long long idx;
+    float row[SCR_ROW];
+};
+struct DevScratch {
+    std::mutex mu;
+    bool ready = false;
+    unsigned char* d_ws = nullptr;
+    size_t ws_stride = 0;
+    ScrResult* d_res = nullptr;
+    ScrResult* h_res = nullptr;          // pinned
+    ScoreParams* d_params = nullptr;
+    ScoreParams* h_params = nullptr;     // pinned
+    int* d_first = nullptr;
+    int* h_first = nullptr;              // pinned
+};
+DevScratch g_scratch[MGB_MAX_DEVICES];
+
+int scratch_for(int device, DevScratch** out) {
+    MGB_REQUIRE(device >= 0 && device < MGB_MAX_DEVICES, "device %d out of range", device);
+    DevScratch& s = g_scratch[device];
+    if (!s.ready) {
+        MGB_CUDA(cudaSetDevice(device));
+        s.ws_stride = (mgb_score_workspace_bytes(0, 1) + 255) & ~(size_t)255;
+        MGB_CUDA(cudaMalloc((void**)&s.d_ws, s.ws_stride * SCR_MAX_JOBS));
+        MGB_CUDA(cudaMemset(s.d_ws, 0, s.ws_stride * SCR_MAX_JOBS));
+        MGB_CUDA(cudaMalloc((void**)&s.d_res, sizeof(ScrResult) * SCR_MAX_JOBS));
+        MGB_CUDA(cudaMallocHost((void**)&s.h_res, sizeof(ScrResult) * SCR_MAX_JOBS));
+        MGB_CUDA(cudaMalloc((void**)&s.d_params, sizeof(ScoreParams) * SCR_MAX_JOBS));
+        MGB_CUDA(cudaMallocHost((void**)&s.h_params, sizeof(ScoreParams) * SCR_MAX_JOBS));
+        MGB_CUDA(cudaMalloc((void**)&s.d_first, sizeof(int) * (SCR_MAX_JOBS + 1)));
+        MGB_CUDA(cudaMallocHost((void**)&s.h_first, sizeof(int) * (SCR_MAX_JOBS + 1)));
+        s.ready = true;
+    }
+    *out = &s;
+    return MGB_OK;
+}
+}  // namespace
+
+extern "C" int mgb_sample_score_best(const mgb_model* m, const mgb_constraints* c, int64_t n, int64_t index_base, const int64_t* h_counts,
+                                     uint64_t seed, float err_scale, float quality_scale, float magnitude_scale, float* h_best_cost,
+                                     int64_t* h_best_idx, float* h_best_row, void* stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    MGB_REQUIRE(m && h_best_cost && h_best_idx, "null argument");
+    MGB_REQUIRE(!h_best_row || m->D <= SCR_ROW, "latent dimension %d exceeds the result record (%d)", m->D, SCR_ROW);
+    DevScratch* s = nullptr;
+    if (int rc = scratch_for(m->device, &s)) return rc;
+    std::lock_guard<std::mutex> lock(s->mu);
+    MGB_CUDA(cudaSetDevice(m->device));
+    int rc = mgb_launch_score(m, c, 2, nullptr, 0, nullptr, h_counts, seed, n, index_base, err_scale, quality_scale, magnitude_scale, nullptr,
+                              nullptr, 1, &s->d_res[0].cost, (int64_t*)&s->d_res[0].idx, s->d_ws, s->ws_stride, stream,
+                              h_best_row ? s->d_res[0].row : nullptr);
+    if (rc != MGB_OK) return rc;
+    const size_t bytes = offsetof(ScrResult, row) + (h_best_row ? sizeof(float) * m->D : 0);
+    MGB_CUDA(cudaMemcpyAsync(s->h_res, s->d_res, bytes, cudaMemcpyDeviceToHost, stream));
+    MGB_CUDA(cudaStreamSynchronize(stream));
+    *h_best_cost = s->h_res[0].cost;
+    *h_best_idx = s->h_res[0].idx;
+    if (h_best_row) memcpy(h_best_row, s->h_res[0].row, sizeof(float) * m->D);
+    return MGB_OK;
+}
+
+extern "C" int mgb_sample_score_multi(const mgb_option* options, int32_t n_options, float* h_best_cost, int64_t* h_best_idx,
+                                      float* h_best_rows, int32_t row_stride, void* stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    MGB_REQUIRE(options && n_options > 0 && h_best_cost && h_best_idx, "null argument");
+    MGB_REQUIRE(n_options <= SCR_MAX_JOBS, "at most %d options per launch", SCR_MAX_JOBS);
+    const int device = options[0].model ? options[0].model->device : -1;
+    DevScratch* s = nullptr;
+    if (int rc = scratch_for(device, &s)) return rc;
+    std::lock_guard<std::mutex> lock(s->mu);
+    MGB_CUDA(cudaSetDevice(device));
+    std::vector<MgbJob> jobs(n_options);
+    for (int j = 0; j < n_options; ++j) {
+        const mgb_option& o = options[j];
+        MGB_REQUIRE(o.model && o.counts, "option %d: null model / counts", j);
+        MGB_REQUIRE(!h_best_rows || (o.model->D <= SCR_ROW && o.model->D <= row_stride), "option %d: latent dimension %d exceeds the row stride", j,
+                    o.model->D);
+        jobs[j] = {o.model, o.constraints, o.n, o.index_base, o.counts, o.seed, o.err_scale, o.quality_scale, o.magnitude_scale,
+                   &s->d_res[j].cost, (int64_t*)&s->d_res[j].idx, h_best_rows ? s->d_res[j].row : nullptr};
+    }
+    int rc = mgb_launch_score_multi(jobs.data(), n_options, s->h_params, s->h_first, s->d_params, s->d_first, s->d_ws, s->ws_stride, stream);
+    if (rc != MGB_OK) return rc;
+    MGB_CUDA(cudaMemcpyAsync(s->h_res, s->d_res, sizeof(ScrResult) * n_options, cudaMemcpyDeviceToHost, stream));
+    MGB_CUDA(cudaStreamSynchronize(stream));
+    for (int j = 0; j < n_options; ++j) {
+        h_best_cost[j] = s->h_res[j].cost;
+        h_best_idx[j] = s->h_res[j].idx;
+        if (h_best_rows) memcpy(h_best_rows + (size_t)j * row_stride, s->h_res[j].row, sizeof(float) * options[j].model->D);
+    }
+    return MGB_OK;
 }
 
 extern "C" int mgb_node_costs(const mgb_model* m, const mgb_constraints* c, const void* d_points, int32_t is_f64, int64_t n,

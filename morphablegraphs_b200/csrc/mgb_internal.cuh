@@ -101,6 +101,18 @@ enum MgbOpCode : int32_t {
 #define MGB_SCRATCH_FLOATS 160
 #define MGB_STACK_DEPTH 8
 
+// One reusable (device block, pinned mirror) pair for the tables of a constraint program: mgb_constraints_pack runs once per
+// motion-primitive step on the planner's thread, so it must not cudaMalloc / cudaFree / block on a copy.  A block is filled
+// through its pinned mirror with ONE asynchronous copy on the model's pack stream; launches wait for `copied` on their own
+// stream and record `used` after themselves, and a later pack that reuses the block waits for `used` on the pack stream.
+struct MgbPackBlock {
+    unsigned char* dev = nullptr;
+    unsigned char* pin = nullptr;
+    size_t bytes = 0;
+    cudaEvent_t copied = nullptr, used = nullptr;
+    bool busy = false;
+};
+
 struct mgb_model {
     int device = 0;
     int F = 0, Nb = 0, P = 0, K = 0, D = 0, G = 0, M = 0;  // M = Nb * P
@@ -156,6 +168,10 @@ struct mgb_model {
     void* d_ws = nullptr;
     size_t ws_bytes = 0;
     cudaEvent_t ev_copied[2] = {nullptr, nullptr}, ev_done[2] = {nullptr, nullptr};
+    // constraint-table blocks (see MgbPackBlock); mutable state of an otherwise immutable handle, guarded by pool_mutex
+    mutable std::mutex pool_mutex;
+    mutable std::vector<MgbPackBlock*> pool;
+    mutable cudaStream_t pack_stream = nullptr;
 };
 
 struct mgb_constraints {
@@ -183,11 +199,16 @@ struct mgb_constraints {
     std::vector<double> times;
     std::vector<int> spans;
     std::vector<double> weights;
-    float4* d_tab = nullptr;
+    float4* d_tab = nullptr;      // the four tables below live in `block` (one allocation, one copy)
     MgbOp* d_ops_fused = nullptr;
     MgbOp* d_ops_frames = nullptr;
     float* d_cst = nullptr;
+    MgbPackBlock* block = nullptr;
 };
+
+// stream ordering of a constraint handle's tables around a launch on `stream` (no-ops for c == NULL)
+int mgb_constraints_before_launch(const mgb_constraints* c, cudaStream_t stream);
+int mgb_constraints_after_launch(const mgb_constraints* c, cudaStream_t stream);
 
 #define MGB_MAX_GMM 64
 struct MgbGmmPrefix {  // job-wide prefix sums of the per-component sample counts (component-ordered stacking)
@@ -232,6 +253,7 @@ struct ScoreParams {
     unsigned int* done_count;  // [1]
     float* best_cost;
     long long* best_idx;
+    float* best_row;           // MODE_SAMPLE: [D] the winning latent vector, re-drawn by the CTA that folds the partials (or NULL)
 };
 
 // launchers implemented in the kernel translation units
@@ -240,12 +262,26 @@ int mgb_launch_score(const mgb_model* m, const mgb_constraints* c, int mode, con
                      const float* d_frames, const int64_t* h_counts, uint64_t seed, int64_t n, int64_t index_base, float err_scale,
                      float quality_scale, float magnitude_scale, float* d_cost, float* d_terms, int k,
                      float* d_best_cost, int64_t* d_best_idx, void* d_ws, size_t ws_bytes,
-                     cudaStream_t stream);
+                     cudaStream_t stream, float* d_best_row = nullptr);
+// one fused sample + score + arg-min job of a multi-job launch (mgb_sample_score_multi)
+struct MgbJob {
+    const mgb_model* m;
+    const mgb_constraints* c;
+    int64_t n, index_base;
+    const int64_t* h_counts;
+    uint64_t seed;
+    float err_scale, quality_scale, magnitude_scale;
+    float* d_best_cost;
+    int64_t* d_best_idx;
+    float* d_best_row;
+};
+int mgb_launch_score_multi(const MgbJob* jobs, int n_jobs, ScoreParams* h_params, int* h_first, ScoreParams* d_params, int* d_first,
+                           unsigned char* d_ws, size_t ws_stride, cudaStream_t stream);
 int mgb_backproject_tc(const mgb_model* m, const float* d_s, int64_t n, float* d_coeffs, cudaStream_t stream);
 int mgb_backproject_tc_prepare(mgb_model* m);
 // tensor-core score path (mgb_tc.cu): operands are packed at handle creation for models with D > 32
 int mgb_score_tc_prepare_model(mgb_model* m);
 int mgb_score_tc_prepare_constraints(const mgb_model* m, mgb_constraints* c);
-bool mgb_score_tc_usable(const mgb_model* m, const mgb_constraints* c, float quality_scale);
+bool mgb_score_tc_usable(const mgb_model* m, const mgb_constraints* c, float quality_scale, int sample);
 int mgb_launch_score_tc(const mgb_model* m, const mgb_constraints* c, const ScoreParams& p, int s_is_f64, float quality_scale,
                         int sample, cudaStream_t stream);

@@ -31,6 +31,7 @@
 #include <math.h>
 #include <stdlib.h>
 
+#include <algorithm>
 #include <type_traits>
 
 #include "mgb_device.cuh"
@@ -98,9 +99,10 @@ __device__ __forceinline__ void dot_rows_mem(const float4* __restrict__ row, int
 // MODE     : MODE_S (candidates from global memory), MODE_FRAMES (pose channels from
 //            materialised frames, staged pipeline K5a), MODE_SAMPLE (fused K1: candidates drawn in-kernel)
 // ---------------------------------------------------------------------------
+// cta / n_cta: this CTA's position among the CTAs that share the job `p` (the whole grid for a single job; a slice of the
+// grid when several jobs - the outgoing options of a planner step - run in one launch)
 template <int NREG, int CPT, int MODE, typename SIn>
-__global__ void __launch_bounds__(MGB_BLOCK) mgb_score_kernel(const __grid_constant__ ScoreParams p) {
-    extern __shared__ __align__(128) unsigned char smem_raw[];
+__device__ __forceinline__ void score_body(const ScoreParams& p, const int cta, const int n_cta, unsigned char* smem_raw) {
     constexpr int TILE = MGB_BLOCK * CPT;
     constexpr int NR = NREG > 0 ? NREG : 1;
     // element type of the shared-memory tile: large latent vectors (NREG == 0) are kept as float
@@ -170,18 +172,18 @@ __global__ void __launch_bounds__(MGB_BLOCK) mgb_score_kernel(const __grid_const
     const SIn* __restrict__ s_glob = reinterpret_cast<const SIn*>(p.s);
     auto tile_by_tma = [&](long long tile) -> bool { return use_tma && (tile + 1) * TILE <= p.n; };
     unsigned int phase[2] = {0u, 0u};
-    if (use_tma && tid == 0 && blockIdx.x < n_tiles && tile_by_tma(blockIdx.x))
-        mgb_tma_load_1d(sm_tile, s_glob + (size_t)blockIdx.x * TILE * D, (unsigned int)tile_bytes, &sm_bar[0]);
+    if (use_tma && tid == 0 && cta < n_tiles && tile_by_tma(cta))
+        mgb_tma_load_1d(sm_tile, s_glob + (size_t)cta * TILE * D, (unsigned int)tile_bytes, &sm_bar[0]);
 
     int it = 0;
     int g_hint = 0;
-    for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
+    for (long long tile = cta; tile < n_tiles; tile += n_cta, ++it) {
         const long long base = tile * TILE;
         const int buf = (p.nbuf == 2) ? (it & 1) : 0;
         const TIn* sm_s = reinterpret_cast<const TIn*>(sm_tile + (size_t)buf * tile_bytes);
         if (load_s) {
             if (p.nbuf == 2) {
-                const long long next = tile + gridDim.x;
+                const long long next = tile + n_cta;
                 if (tid == 0 && next < n_tiles && tile_by_tma(next))
                     mgb_tma_load_1d(sm_tile + (size_t)(buf ^ 1) * tile_bytes, s_glob + (size_t)next * TILE * D, (unsigned int)tile_bytes,
                                     &sm_bar[buf ^ 1]);
@@ -360,18 +362,18 @@ __global__ void __launch_bounds__(MGB_BLOCK) mgb_score_kernel(const __grid_const
     }
     __shared__ bool is_last;
     if (tid == 0) {
-        p.part_cost[blockIdx.x] = best_c;
-        p.part_idx[blockIdx.x] = best_i;
+        p.part_cost[cta] = best_c;
+        p.part_idx[cta] = best_i;
         __threadfence();
         unsigned int t = atomicAdd(p.done_count, 1u);
-        is_last = (t == gridDim.x - 1);
+        is_last = (t == (unsigned int)n_cta - 1);
     }
     __syncthreads();
     if (!is_last) return;
     __threadfence();
     best_c = INFINITY;
     best_i = LLONG_MAX;
-    for (int b = tid; b < (int)gridDim.x; b += MGB_BLOCK) {
+    for (int b = tid; b < n_cta; b += MGB_BLOCK) {
         float oc = __ldcg(p.part_cost + b);
         long long oi = __ldcg(p.part_idx + b);
         if (better(oc, oi, best_c, best_i)) { best_c = oc; best_i = oi; }
@@ -392,7 +394,60 @@ __global__ void __launch_bounds__(MGB_BLOCK) mgb_score_kernel(const __grid_const
         p.best_cost[0] = best_c;
         p.best_idx[0] = best_i;
         *p.done_count = 0u;  // ready for the next launch
+        if (MODE == MODE_SAMPLE && p.best_row != nullptr) {
+            // the winning latent vector, re-drawn from its global index (what mgb_sample writes for that index, bit for bit)
+            int g = 0;
+            while (g + 1 < p.G && best_i >= p.prefix.v[g + 1]) ++g;
+            const uint2 key = make_uint2((unsigned int)p.seed, (unsigned int)(p.seed >> 32));
+            if constexpr (NREG > 0) {
+                float row[NR];
+                mgb_sample_row_reg<NR>(reinterpret_cast<const float4*>(p.chol + (size_t)g * D * p.LS), p.LS, p.means + (size_t)g * D, D,
+                                       (unsigned long long)best_i, key, row);
+#pragma unroll
+                for (int k = 0; k < NR; ++k)
+                    if (k < D) p.best_row[k] = row[k];
+            } else {
+                mgb_sample_row_mem(p.chol + (size_t)g * D * p.LS, p.LS, p.means + (size_t)g * D, D, (unsigned long long)best_i, key, p.best_row);
+            }
+        }
     }
+}
+
+template <int NREG, int CPT, int MODE, typename SIn>
+__global__ void __launch_bounds__(MGB_BLOCK) mgb_score_kernel(const __grid_constant__ ScoreParams p) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    score_body<NREG, CPT, MODE, SIn>(p, (int)blockIdx.x, (int)gridDim.x, smem_raw);
+}
+
+// Several independent sample-and-score jobs in ONE launch: the outgoing options of a planner step (reference
+// graph_walk_planner.py:216-226, mg_state_planner.py:946-968 score them one after another).  jobs[j] is a complete
+// ScoreParams (own model tables, constraint program, workspace slice, results); CTAs [first[j], first[j + 1]) work on job j.
+struct MultiParams {
+    const ScoreParams* jobs;
+    const int* first;   // [n_jobs + 1]
+    int n_jobs;
+};
+
+template <int NREG, int CPT>
+__global__ void __launch_bounds__(MGB_BLOCK) mgb_score_multi_kernel(const MultiParams mp) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    __shared__ ScoreParams sp;
+    __shared__ int s_job, s_first, s_cnt;
+    if (threadIdx.x == 0) {
+        int j = 0;
+        while (j + 1 < mp.n_jobs && (int)blockIdx.x >= __ldg(mp.first + j + 1)) ++j;
+        s_job = j;
+        s_first = __ldg(mp.first + j);
+        s_cnt = __ldg(mp.first + j + 1) - s_first;
+    }
+    __syncthreads();
+    {
+        const unsigned int* src = reinterpret_cast<const unsigned int*>(mp.jobs + s_job);
+        unsigned int* dst = reinterpret_cast<unsigned int*>(&sp);
+        for (int i = threadIdx.x; i < (int)(sizeof(ScoreParams) / 4); i += MGB_BLOCK) dst[i] = __ldg(src + i);
+    }
+    __syncthreads();
+    score_body<NREG, CPT, MODE_SAMPLE, float>(sp, (int)blockIdx.x - s_first, s_cnt, smem_raw);
 }
 
 // ---------------------------------------------------------------------------
@@ -507,40 +562,12 @@ extern "C" size_t mgb_score_workspace_bytes(int64_t n, int32_t k) {
     return parts * (sizeof(float) + sizeof(long long)) + 256;
 }
 
-int mgb_launch_score(const mgb_model* m, const mgb_constraints* c, int mode, const void* d_s, int s_is_f64,
-                     const float* d_frames, const int64_t* h_counts, uint64_t seed, int64_t n, int64_t index_base, float err_scale,
-                     float quality_scale, float magnitude_scale, float* d_cost, float* d_terms, int k,
-                     float* d_best_cost, int64_t* d_best_idx, void* d_ws, size_t ws_bytes,
-                     cudaStream_t stream) {
-    MGB_REQUIRE(m, "null model handle");
-    MGB_REQUIRE(!c || c->model == m, "constraints were packed for a different model");
-    MGB_REQUIRE(n >= 0, "negative n");
-    MGB_REQUIRE(k >= 0 && k <= 64, "k must be in [0, 64]");
-    MGB_REQUIRE(mode >= MODE_S && mode <= MODE_SAMPLE, "bad mode");
+// Fills the kernel parameters of one job and its shared-memory plan (everything but the launch).
+static int build_score_params(const mgb_model* m, const mgb_constraints* c, int mode, const void* d_s, const float* d_frames,
+                              const int64_t* h_counts, uint64_t seed, int64_t n, int64_t index_base, float err_scale, float quality_scale,
+                              float magnitude_scale, float* d_cost, float* d_terms, int k, float* d_best_cost, int64_t* d_best_idx,
+                              float* d_best_row, void* d_ws, ScoreParams& p, SmemPlan& plan) {
     const bool frames = mode == MODE_FRAMES;
-    MGB_REQUIRE(!frames || d_frames, "d_frames is NULL");
-    MGB_REQUIRE(mode != MODE_S || d_s || n == 0, "d_s is NULL");
-    MGB_REQUIRE(!(frames && s_is_f64), "frames mode takes float32 s");
-    MGB_REQUIRE(!d_terms || c, "d_terms needs a constraint set");
-    if ((quality_scale != 0.f || magnitude_scale != 0.f) && frames) MGB_REQUIRE(d_s, "logpdf / magnitude need d_s");
-    if (k > 0) {
-        MGB_REQUIRE(d_best_cost && d_best_idx, "k > 0 needs d_best_cost / d_best_idx");
-        MGB_REQUIRE(d_ws && ws_bytes >= mgb_score_workspace_bytes(n, k), "workspace too small");
-        MGB_REQUIRE(k == 1 || d_cost, "k > 1 needs d_cost");
-    }
-    if (n == 0) {
-        if (k > 0) {
-            // empty batch: reference returns index 0 / inf
-            float inf = INFINITY;
-            for (int j = 0; j < k; ++j) {
-                MGB_CUDA(cudaMemcpyAsync(d_best_cost + j, &inf, sizeof(float), cudaMemcpyHostToDevice, stream));
-                MGB_CUDA(cudaMemcpyAsync(d_best_idx + j, &index_base, sizeof(int64_t), cudaMemcpyHostToDevice, stream));
-            }
-            MGB_CUDA(cudaStreamSynchronize(stream));
-        }
-        return MGB_OK;
-    }
-    ScoreParams p;
     memset(&p, 0, sizeof(p));
     if (c) {
         p.tab = c->d_tab;
@@ -583,6 +610,7 @@ int mgb_launch_score(const mgb_model* m, const mgb_constraints* c, int mode, con
     p.done_count = reinterpret_cast<unsigned int*>(ws + parts * (sizeof(long long) + sizeof(float)));
     p.best_cost = d_best_cost;
     p.best_idx = reinterpret_cast<long long*>(d_best_idx);
+    p.best_row = d_best_row;
     if (mode == MODE_SAMPLE) {
         MGB_REQUIRE(h_counts, "sampling needs the per-component counts");
         MGB_REQUIRE(m->G <= MGB_MAX_GMM, "at most %d mixture components are supported by the sampler", MGB_MAX_GMM);
@@ -595,7 +623,6 @@ int mgb_launch_score(const mgb_model* m, const mgb_constraints* c, int mode, con
         MGB_REQUIRE(index_base >= 0 && index_base + n <= p.prefix.v[m->G], "component counts (%lld) do not cover [%lld, %lld)",
                     p.prefix.v[m->G], (long long)index_base, (long long)(index_base + n));
     }
-
     // shared-memory budget: tables go to shared memory when they fit
     const size_t tab_bytes = (frames || !c) ? 0 : (size_t)c->n_quads * (c->KP + 1) * sizeof(float4);
     const size_t gmm_bytes = (quality_scale != 0.f) ? (size_t)m->G * m->NQ * (m->DP + 1) * sizeof(float4) : 0;
@@ -611,15 +638,58 @@ int mgb_launch_score(const mgb_model* m, const mgb_constraints* c, int mode, con
     fixed += (size_t)((p.n_cst + 3) & ~3) * sizeof(float);
     fixed += 32 * sizeof(float) + 32 * sizeof(long long) + 2 * sizeof(unsigned long long);
     fixed = (fixed + 127) & ~(size_t)127;
-    SmemPlan plan;
     plan.fixed = fixed + 128;  // slack for the base alignment of the dynamic segment
+    return MGB_OK;
+}
+
+int mgb_launch_score(const mgb_model* m, const mgb_constraints* c, int mode, const void* d_s, int s_is_f64,
+                     const float* d_frames, const int64_t* h_counts, uint64_t seed, int64_t n, int64_t index_base, float err_scale,
+                     float quality_scale, float magnitude_scale, float* d_cost, float* d_terms, int k,
+                     float* d_best_cost, int64_t* d_best_idx, void* d_ws, size_t ws_bytes,
+                     cudaStream_t stream, float* d_best_row) {
+    MGB_REQUIRE(m, "null model handle");
+    MGB_REQUIRE(!c || c->model == m, "constraints were packed for a different model");
+    MGB_REQUIRE(n >= 0, "negative n");
+    MGB_REQUIRE(k >= 0 && k <= 64, "k must be in [0, 64]");
+    MGB_REQUIRE(mode >= MODE_S && mode <= MODE_SAMPLE, "bad mode");
+    const bool frames = mode == MODE_FRAMES;
+    MGB_REQUIRE(!frames || d_frames, "d_frames is NULL");
+    MGB_REQUIRE(mode != MODE_S || d_s || n == 0, "d_s is NULL");
+    MGB_REQUIRE(!(frames && s_is_f64), "frames mode takes float32 s");
+    MGB_REQUIRE(!d_terms || c, "d_terms needs a constraint set");
+    MGB_REQUIRE(!d_best_row || (mode == MODE_SAMPLE && k == 1), "the winning row is re-drawn only by the fused sample + score step with k = 1");
+    if ((quality_scale != 0.f || magnitude_scale != 0.f) && frames) MGB_REQUIRE(d_s, "logpdf / magnitude need d_s");
+    if (k > 0) {
+        MGB_REQUIRE(d_best_cost && d_best_idx, "k > 0 needs d_best_cost / d_best_idx");
+        MGB_REQUIRE(d_ws && ws_bytes >= mgb_score_workspace_bytes(n, k), "workspace too small");
+        MGB_REQUIRE(k == 1 || d_cost, "k > 1 needs d_cost");
+    }
+    if (n == 0) {
+        if (k > 0) {
+            // empty batch: reference returns index 0 / inf
+            float inf = INFINITY;
+            for (int j = 0; j < k; ++j) {
+                MGB_CUDA(cudaMemcpyAsync(d_best_cost + j, &inf, sizeof(float), cudaMemcpyHostToDevice, stream));
+                MGB_CUDA(cudaMemcpyAsync(d_best_idx + j, &index_base, sizeof(int64_t), cudaMemcpyHostToDevice, stream));
+            }
+            if (d_best_row) MGB_CUDA(cudaMemsetAsync(d_best_row, 0, sizeof(float) * m->D, stream));
+            MGB_CUDA(cudaStreamSynchronize(stream));
+        }
+        return MGB_OK;
+    }
+    ScoreParams p;
+    SmemPlan plan;
+    if (int rc = build_score_params(m, c, mode, d_s, d_frames, h_counts, seed, n, index_base, err_scale, quality_scale, magnitude_scale, d_cost,
+                                    d_terms, k, d_best_cost, d_best_idx, d_best_row, d_ws, p, plan))
+        return rc;
     // the completion counter in the workspace must be zero on entry: the caller zero-fills a
     // fresh workspace once (include/mgb200.h) and the kernel re-arms it at the end of every launch
     if (d_terms) MGB_CUDA(cudaMemsetAsync(d_terms, 0, (size_t)c->n_terms * n * sizeof(float), stream));
+    if (int rcb = mgb_constraints_before_launch(c, stream)) return rcb;   // the program's tables were uploaded on the model's pack stream
 
     int rc;
     const int D = m->D;
-    if ((mode == MODE_S || mode == MODE_SAMPLE) && mgb_score_tc_usable(m, c, quality_scale)) {
+    if ((mode == MODE_S || mode == MODE_SAMPLE) && mgb_score_tc_usable(m, c, quality_scale, mode == MODE_SAMPLE ? 1 : 0)) {
         // large latent spaces: sampling, contraction and GMM log-density on the tensor cores (mgb_tc.cu)
         rc = mgb_launch_score_tc(m, c, p, s_is_f64, quality_scale, mode == MODE_SAMPLE ? 1 : 0, stream);
     } else if (mode == MODE_FRAMES) {
@@ -632,9 +702,82 @@ int mgb_launch_score(const mgb_model* m, const mgb_constraints* c, int mode, con
         rc = launch_shape<MODE_S, float>(D, p, plan, stream);
     }
     if (rc != MGB_OK) return rc;
+    if (int rca = mgb_constraints_after_launch(c, stream)) return rca;
     if (k > 1) {
         return mgb_topk(d_cost, n, index_base, k, d_best_cost, d_best_idx, d_ws, ws_bytes, stream);
     }
+    return MGB_OK;
+}
+
+// ---------------------------------------------------------------------------
+// several jobs, one launch (mgb_sample_score_multi)
+// ---------------------------------------------------------------------------
+template <int NREG>
+static int launch_multi(const ScoreParams* d_jobs, const int* d_first, int n_jobs, int total_ctas, size_t smem, cudaStream_t stream) {
+    auto kern = mgb_score_multi_kernel<NREG, 1>;
+    static bool configured[MGB_MAX_DEVICES] = {false};
+    if (int rc = mgb_opt_in_smem(kern, configured, (int)MGB_SMEM_MAX)) return rc;
+    MultiParams mp;
+    mp.jobs = d_jobs;
+    mp.first = d_first;
+    mp.n_jobs = n_jobs;
+    kern<<<(unsigned)total_ctas, MGB_BLOCK, smem, stream>>>(mp);
+    mgb_count_launch();
+    MGB_CUDA(cudaGetLastError());
+    return MGB_OK;
+}
+
+int mgb_launch_score_multi(const MgbJob* jobs, int n_jobs, ScoreParams* h_params /*pinned, [n_jobs]*/, int* h_first /*pinned, [n_jobs + 1]*/,
+                           ScoreParams* d_params, int* d_first, unsigned char* d_ws, size_t ws_stride, cudaStream_t stream) {
+    MGB_REQUIRE(n_jobs > 0, "no jobs");
+    const int D0 = jobs[0].m->D;
+    const int cls = D0 <= 16 ? 16 : (D0 <= 32 ? 32 : 0);
+    size_t smem_max = 0;
+    long long n_sum = 0;
+    for (int j = 0; j < n_jobs; ++j) {
+        const MgbJob& J = jobs[j];
+        MGB_REQUIRE(J.m && J.n > 0, "job %d: empty", j);
+        MGB_REQUIRE(!J.c || J.c->model == J.m, "job %d: constraints were packed for a different model", j);
+        MGB_REQUIRE(J.m->device == jobs[0].m->device, "job %d: models live on different devices", j);
+        const int D = J.m->D;
+        if ((D <= 16 ? 16 : (D <= 32 ? 32 : 0)) != cls || mgb_score_tc_usable(J.m, J.c, J.quality_scale, 1)) {
+            mgb_set_error("jobs of one launch must share a kernel class (latent dimension <= 16, <= 32, or larger without the tensor-core path)");
+            return MGB_E_UNSUPPORTED;
+        }
+        SmemPlan plan;
+        if (int rc = build_score_params(J.m, J.c, MODE_SAMPLE, nullptr, nullptr, J.h_counts, J.seed, J.n, J.index_base, J.err_scale, J.quality_scale,
+                                        J.magnitude_scale, nullptr, nullptr, 1, J.d_best_cost, J.d_best_idx, J.d_best_row, d_ws + (size_t)j * ws_stride,
+                                        h_params[j], plan))
+            return rc;
+        size_t tile = (cls == 0) ? (size_t)MGB_BLOCK * (D | 1) * sizeof(float) : 0;
+        tile = (tile + 127) & ~(size_t)127;
+        h_params[j].nbuf = 1;
+        smem_max = std::max(smem_max, plan.fixed + tile);
+        n_sum += J.n;
+    }
+    MGB_REQUIRE(smem_max <= MGB_SMEM_MAX, "constraint program / candidate tile too large for shared memory (%zu bytes)", smem_max);
+    // CTAs per job: proportional to its candidates, at least one, at most its tiles and the per-job partial slots
+    const int budget = num_sms() * 4;
+    int total = 0;
+    h_first[0] = 0;
+    for (int j = 0; j < n_jobs; ++j) {
+        const long long tiles = (jobs[j].n + MGB_BLOCK - 1) / MGB_BLOCK;
+        long long ctas = std::max<long long>(1, (long long)budget * jobs[j].n / std::max<long long>(1, n_sum));
+        ctas = std::min<long long>(std::min<long long>(ctas, tiles), 148 * 16);
+        total += (int)ctas;
+        h_first[j + 1] = total;
+    }
+    MGB_CUDA(cudaMemcpyAsync(d_params, h_params, sizeof(ScoreParams) * n_jobs, cudaMemcpyHostToDevice, stream));
+    MGB_CUDA(cudaMemcpyAsync(d_first, h_first, sizeof(int) * (n_jobs + 1), cudaMemcpyHostToDevice, stream));
+    for (int j = 0; j < n_jobs; ++j)
+        if (int rc = mgb_constraints_before_launch(jobs[j].c, stream)) return rc;
+    int rc;
+    if (cls == 16) rc = launch_multi<16>(d_params, d_first, n_jobs, total, smem_max, stream);
+    else if (cls == 32) rc = launch_multi<32>(d_params, d_first, n_jobs, total, smem_max, stream);
+    else rc = launch_multi<0>(d_params, d_first, n_jobs, total, smem_max, stream);
+    if (rc != MGB_OK) return rc;
+    for (int j = 0; j < n_jobs; ++j)
+        if (int rca = mgb_constraints_after_launch(jobs[j].c, stream)) return rca;
     return MGB_OK;
 }
 extern "C" int mgb_topk(const float* d_cost, int64_t n, int64_t index_base, int32_t k, float* d_best_cost,

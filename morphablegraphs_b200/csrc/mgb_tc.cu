@@ -971,6 +971,14 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mgb_score_tc_kernel(const __gri
                     sp.best_cost[0] = best_c;
                     sp.best_idx[0] = best_i;
                     *sp.done_count = 0u;  // ready for the next launch
+                    if (SAMPLE && sp.best_row != nullptr) {
+                        // the winning latent vector as mgb_sample writes it for that global index (fp32 Cholesky product; the
+                        // tile scored its tensor-core product, equal to ~1e-6)
+                        int g = 0;
+                        while (g + 1 < sp.G && best_i >= sp.prefix.v[g + 1]) ++g;
+                        mgb_sample_row_mem(sp.chol + (size_t)g * sp.D * sp.LS, sp.LS, sp.means + (size_t)g * sp.D, sp.D, (unsigned long long)best_i,
+                                           make_uint2((unsigned int)sp.seed, (unsigned int)(sp.seed >> 32)), sp.best_row);
+                    }
                 }
             }
         }
@@ -1268,11 +1276,11 @@ static bool tc_score_plan(const mgb_model* m, const mgb_constraints* c, float qu
     return false;
 }
 
-bool mgb_score_tc_usable(const mgb_model* m, const mgb_constraints* c, float quality_scale) {
+bool mgb_score_tc_usable(const mgb_model* m, const mgb_constraints* c, float quality_scale, int sample) {
     if (tc_disabled() || m->D < TC_SCORE_MIN_D) return false;
     TcScoreParams p;
     size_t smem;
-    return tc_score_plan(m, c, quality_scale, 0, &p, &smem) && m->d_Bsamp != nullptr;
+    return tc_score_plan(m, c, quality_scale, sample, &p, &smem);
 }
 
 int mgb_launch_score_tc(const mgb_model* m, const mgb_constraints* c, const ScoreParams& sp, int s_is_f64, float quality_scale,

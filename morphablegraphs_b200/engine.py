@@ -213,7 +213,14 @@ class DeviceModel(object):
     def component_counts(self, n_total, seed):
         """Multinomial split over components, drawn on the host like sklearn's sampler does
         (GaussianMixture.sample: rng.multinomial(n, weights_))."""
-        rng = np.random.RandomState(None if seed is None else (int(seed) & 0x7FFFFFFF))
+        if seed is None:
+            return np.random.RandomState(None).multinomial(int(n_total), self.gmm_weights).astype(np.int64)
+        # re-seeding a kept RandomState gives the stream of RandomState(seed) at 1 % of the cost of constructing one
+        # (the constructor alone is ~0.3 ms: four times the 1M-candidate kernel of the S primitive)
+        rng = self.__dict__.get("_count_rng")
+        if rng is None:
+            rng = self.__dict__["_count_rng"] = np.random.RandomState(0)
+        rng.seed(int(seed) & 0x7FFFFFFF)
         return rng.multinomial(int(n_total), self.gmm_weights).astype(np.int64)
 
     def sample(self, n, seed=0, index_base=0, counts=None, n_total=None, out=None):
@@ -247,8 +254,17 @@ class DeviceModel(object):
         times = np.ascontiguousarray(np.atleast_1d(times), dtype=np.float64)
         spans = np.zeros(len(times), dtype=np.int32)
         weights = np.zeros((len(times), 4), dtype=np.float64)
+        cache = self.__dict__.get("_basis_cache")
+        if cache is None:
+            cache = self.__dict__["_basis_cache"] = {}
         for i, t in enumerate(times):
-            spans[i], weights[i] = spline_basis(self.knots, float(t))
+            key = float(t)
+            hit = cache.get(key)
+            if hit is None:         # the same FITPACK call the reference makes, once per distinct time of this model
+                if len(cache) > 4096:
+                    cache.clear()
+                hit = cache[key] = spline_basis(self.knots, key)
+            spans[i], weights[i] = hit
         return times, spans, weights
 
     def eval_frames(self, coeffs, times, out=None):
@@ -598,6 +614,24 @@ class DeviceConstraints(object):
             out["cost"] = cost
         return out
 
+    def sample_score_best(self, n, seed=0, counts=None, n_total=None, index_base=0, error_scale=1.0, quality_scale=0.0,
+                          magnitude_scale=0.0):
+        """The planner-facing step (mgb_sample_score_best): draw + score + arg-min in one launch and get
+        (best_cost, best_global_index, winning latent vector as float64 numpy [D]) back with one copy and one
+        synchronisation.  What `_get_best_fit_sample_using_gmm` needs, nothing else."""
+        dm = self.dmodel
+        n_total = int(n if n_total is None else n_total)
+        if counts is None:
+            counts = dm.component_counts(n_total, seed)
+        counts = np.ascontiguousarray(counts, dtype=np.int64)
+        cost, idx = C.c_float(), C.c_int64()
+        row = np.empty(dm.D, dtype=np.float32)
+        with _torch().cuda.device(dm.device):
+            _lib.check(self.lib.mgb_sample_score_best(dm.handle, self.handle, int(n), int(index_base), counts.ctypes.data_as(C.POINTER(C.c_int64)),
+                                                      C.c_uint64(int(seed) & 0xFFFFFFFFFFFFFFFF), float(error_scale), float(quality_scale),
+                                                      float(magnitude_scale), C.byref(cost), C.byref(idx), C.c_void_p(row.ctypes.data), dm._stream()))
+        return float(cost.value), int(idx.value), row.astype(np.float64)
+
     def score_host(self, samples, k=1, error_scale=1.0, quality_scale=0.0, magnitude_scale=0.0, return_cost=False,
                    index_base=0):
         """Score HOST candidates (numpy float32/float64 [n, D], or a pinned CPU torch tensor):
@@ -627,6 +661,43 @@ class DeviceConstraints(object):
         if return_cost:
             out["cost"] = cost
         return out
+
+
+def sample_score_multi(options):
+    """Cross-option batching (mgb_sample_score_multi): `options` is a list of dicts with keys `dc` (DeviceConstraints),
+    `n`, `seed` and optionally `counts`, `error_scale`, `quality_scale`, `magnitude_scale`.  All options are drawn,
+    scored and reduced in ONE launch; returns a list of (best_cost, best_index, latent vector float64 [D]) per option.
+    Raises MgbError (code MGB_E_UNSUPPORTED) when the options do not share a kernel class - the caller then issues one
+    `sample_score_best` per option."""
+    lib = _lib.load()
+    m = len(options)
+    arr = (_lib.Option * m)()
+    keep = []
+    dmax = 0
+    for j, o in enumerate(options):
+        dc = o["dc"]
+        dm = dc.dmodel
+        n = int(o["n"])
+        seed = int(o.get("seed", 0))
+        counts = o.get("counts")
+        if counts is None:
+            counts = dm.component_counts(n, seed)
+        counts = np.ascontiguousarray(counts, dtype=np.int64)
+        keep.append(counts)
+        a = arr[j]
+        a.model, a.constraints, a.n, a.index_base = dm.handle, dc.handle, n, int(o.get("index_base", 0))
+        a.counts = counts.ctypes.data_as(C.POINTER(C.c_int64))
+        a.seed = seed & 0xFFFFFFFFFFFFFFFF
+        a.err_scale, a.quality_scale, a.magnitude_scale = float(o.get("error_scale", 1.0)), float(o.get("quality_scale", 0.0)), float(o.get("magnitude_scale", 0.0))
+        dmax = max(dmax, dm.D)
+    cost = np.empty(m, dtype=np.float32)
+    idx = np.empty(m, dtype=np.int64)
+    rows = np.zeros((m, dmax), dtype=np.float32)
+    dm0 = options[0]["dc"].dmodel
+    with _torch().cuda.device(dm0.device):
+        _lib.check(lib.mgb_sample_score_multi(arr, m, C.c_void_p(cost.ctypes.data), C.c_void_p(idx.ctypes.data), C.c_void_p(rows.ctypes.data),
+                                              int(dmax), dm0._stream()))
+    return [(float(cost[j]), int(idx[j]), rows[j, :options[j]["dc"].dmodel.D].astype(np.float64)) for j in range(m)]
 
 
 def kmeans_level(x, dim, node, n_nodes, n_sub, centroids, tol=None, max_iter=300, check_every=4, dim_acc=None,

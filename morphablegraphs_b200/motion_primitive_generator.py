@@ -176,8 +176,15 @@ class MotionPrimitiveGenerator(object):
         if sharding.is_distributed():
             import torch.distributed as dist
             rank, world = dist.get_rank(), dist.get_world_size()
-        base, n_mine = sharding.shard_range(n, rank, world)
         counts = dm.component_counts(n, seed)
+        if world == 1:
+            # one call: launch, winner re-drawn by the kernel, (cost, index, row) back in one copy
+            min_error, best_idx, best = dc.sample_score_best(n, seed=seed, counts=counts, error_scale=error_scale,
+                                                             quality_scale=quality_scale, magnitude_scale=magnitude_scale)
+            mp_constraints.min_error = min_error
+            mp_constraints.evaluations += n
+            return best
+        base, n_mine = sharding.shard_range(n, rank, world)
         res = dc.sample_score(n_mine, seed=seed, counts=counts, n_total=n, index_base=base, k=1,
                               error_scale=error_scale, quality_scale=quality_scale, magnitude_scale=magnitude_scale)
         peer = sharding.peer_exchange(dm.torch_device) if world > 1 else None
@@ -195,6 +202,42 @@ class MotionPrimitiveGenerator(object):
         mp_constraints.evaluations += n
         best = dm.sample(1, seed=seed, index_base=best_idx, counts=counts, n_total=n)
         return best[0].cpu().numpy().astype(np.float64)
+
+    # ------------------------------------------------------------------ graph_walk_planner.py:216-226, mg_state_planner.py:946-968
+    def generate_constrained_samples(self, options):
+        """Cross-option batching.  `options`: list of `(graph_node, in_mp_constraints, prev_frames)`
+        - the outgoing edges a planner scores one after another with `generate_constrained_sample`.  All of them are
+        sampled, scored and reduced in ONE launch; returns the list of best latent vectors and leaves `min_error` /
+        `evaluations` on every constraints object exactly as the per-option calls would.  Options whose models do not
+        share a kernel class are scored by one call each (still on the device)."""
+        from . import engine
+        error_scale, quality_scale, magnitude_scale = objective_scales(self.objective)
+        n = int(self.n_random_samples)
+        jobs, locals_ = [], []
+        for graph_node, in_c, prev_frames in options:
+            if self.use_local_coordinates:
+                mp_c, prev = in_c.transform_constraints_to_local_cos(), None
+            else:
+                mp_c, prev = in_c, prev_frames
+            dc = _device_constraints(graph_node, mp_c, prev)
+            jobs.append(dict(dc=dc, n=n, seed=self._step_seed(), error_scale=error_scale, quality_scale=quality_scale,
+                             magnitude_scale=magnitude_scale))
+            locals_.append(mp_c)
+        try:
+            results = engine.sample_score_multi(jobs)
+        except engine.MgbError as e:
+            if "kernel class" not in str(e):
+                raise
+            results = [j["dc"].sample_score_best(j["n"], seed=j["seed"], error_scale=error_scale, quality_scale=quality_scale,
+                                                 magnitude_scale=magnitude_scale) for j in jobs]
+        out = []
+        for (graph_node, in_c, prev_frames), mp_c, (cost, idx, row) in zip(options, locals_, results):
+            mp_c.min_error = cost
+            mp_c.evaluations += n
+            in_c.min_error = mp_c.min_error
+            in_c.evaluations = mp_c.evaluations
+            out.append(row)
+        return out
 
     # ------------------------------------------------------------------ :167-177
     def _get_best_fit_sample_using_mgrd(self, graph_node, mp_constraints):

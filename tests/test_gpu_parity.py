@@ -657,3 +657,77 @@ def test_local_coordinates_default_path():
     wrong = O.candidate_costs(c.node, c.skeleton, c.constraints, s[None])[0]
     c.constraints.is_local = False
     assert abs(wrong - ref) > 10.0
+
+
+# ---------------------------------------------------------------------------
+# planner-facing entries: one call per step, cross-option batching
+# ---------------------------------------------------------------------------
+def test_sample_score_best_returns_the_row_it_scored():
+    """mgb_sample_score_best == mgb_sample_score + mgb_sample(1, best_idx): same cost and index, and the row re-drawn
+    by the kernel's last CTA is the row of that global index, bit for bit."""
+    from morphablegraphs_b200 import engine
+    c = Case("s_mixed")
+    dm = engine.DeviceModel(c.node, c.skeleton)
+    dc = engine.DeviceConstraints(dm, c.constraints)
+    for n, seed, qs in ((10, 3, 0.0), (5000, 4, 0.1), (70001, 5, 0.0)):
+        counts = dm.component_counts(n, seed)
+        cost, idx, row = dc.sample_score_best(n, seed=seed, counts=counts, quality_scale=qs, magnitude_scale=0.5)
+        ref = dc.sample_score(n, seed=seed, counts=counts, k=1, quality_scale=qs, magnitude_scale=0.5)
+        assert idx == int(ref["best_idx"][0]) and cost == float(ref["best_cost"][0])
+        want = dm.sample(1, seed=seed, index_base=idx, counts=counts, n_total=n)[0].cpu().numpy()
+        assert np.array_equal(row.astype(np.float32), want)
+
+
+def test_sample_score_best_large(large):
+    dm, dc = large.dm, large.dc
+    n, seed = 3000, 9
+    counts = dm.component_counts(n, seed)
+    cost, idx, row = dc.sample_score_best(n, seed=seed, counts=counts, quality_scale=0.1)
+    ref = dc.sample_score(n, seed=seed, counts=counts, k=1, quality_scale=0.1)
+    assert idx == int(ref["best_idx"][0]) and cost == float(ref["best_cost"][0])
+    want = dm.sample(1, seed=seed, index_base=idx, counts=counts, n_total=n)[0].cpu().numpy()
+    assert np.array_equal(row.astype(np.float32), want)
+
+
+def test_options_scored_in_one_launch_equal_separate_calls():
+    """f4: four outgoing options (four different primitives, their own constraint sets and seeds) x 10 samples - and
+    x 20 000 samples - in ONE launch give exactly the per-option (cost, index, row) of four separate calls; one kernel
+    launch is counted for the batch."""
+    from morphablegraphs_b200 import engine
+    from tests.walk_common import WalkCase
+    w = WalkCase()
+    dms = [engine.DeviceModel(nd, w.skeleton) for nd in w.nodes]
+    opts = []
+    for i in range(4):
+        st = w.step(i)
+        k = w.order[i]
+        opts.append((dms[k], engine.DeviceConstraints(dms[k], st["constraints"], st["prev_frames"])))
+    for n in (10, 20000):
+        jobs = [dict(dc=dc, n=n + 3 * j, seed=100 + j, magnitude_scale=2.0 if j == 1 else 0.0) for j, (dm, dc) in enumerate(opts)]
+        before = engine.launch_count()
+        multi = engine.sample_score_multi(jobs)
+        assert engine.launch_count() - before == 1
+        for j, (dm, dc) in enumerate(opts):
+            cost, idx, row = dc.sample_score_best(n + 3 * j, seed=100 + j, magnitude_scale=2.0 if j == 1 else 0.0)
+            assert multi[j][0] == cost and multi[j][1] == idx and np.array_equal(multi[j][2], row), (n, j)
+
+
+def test_generator_scores_all_options_at_once():
+    """MotionPrimitiveGenerator.generate_constrained_samples (the planner's option loop in one launch) leaves the same
+    min_error / evaluations on every constraints object and returns the same latent vectors as one
+    generate_constrained_sample per option with the same seed stream."""
+    from morphablegraphs_b200 import MotionPrimitiveGenerator
+    from tests.walk_common import WalkCase
+    w = WalkCase()
+    cfgd = {"n_random_samples": 500, "use_local_coordinates": False}
+    a = MotionPrimitiveGenerator(None, cfgd, skeleton=w.skeleton, seed=5)
+    b = MotionPrimitiveGenerator(None, cfgd, skeleton=w.skeleton, seed=5)
+    steps_a = [w.step(i) for i in range(4)]
+    steps_b = [w.step(i) for i in range(4)]
+    got = a.generate_constrained_samples([(s["node"], s["constraints"], s["prev_frames"]) for s in steps_a])
+    for s, row in zip(steps_b, got):
+        want = b.generate_constrained_sample(s["node"], s["constraints"], "", s["prev_frames"], None)
+        assert np.array_equal(row, want)
+    for sa, sb in zip(steps_a, steps_b):
+        assert sa["constraints"].min_error == sb["constraints"].min_error
+        assert sa["constraints"].evaluations == sb["constraints"].evaluations == 500

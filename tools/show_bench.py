@@ -1,0 +1,28 @@
+#!/usr/bin/env python
+"""One-screen summary of a bench.py JSON line: python tools/show_bench.py <file>"""
+import json
+import sys
+
+d = json.load(open(sys.argv[1]))
+
+
+def show(name, x):
+    e = x.get("e2e", {})
+    g = e.get("generator_call", {})
+    print("%-11s value %.4g  ms/step %.4g  roof %.3f (%s)  e2e %.4g  generator_call %.4g ms (%s launches)" % (
+        name, x["value"], x["ms_per_step"], x["roofline"]["frac"], x["roofline"]["bound"], e.get("value", float("nan")),
+        g.get("ms_per_step", float("nan")), g.get("launches_per_step")))
+    ob = e.get("option_batch")
+    if ob:
+        print("            option batch: %d options x %d samples: %.3f ms in one launch, %.3f ms one call per option" % (
+            ob["options"], ob["samples_per_option"], ob["ms_one_launch"], ob["ms_one_call_per_option"]))
+    if "cpu_baseline" in x:
+        print("            cpu", x["cpu_baseline"].get("value"), x["cpu_baseline"].get("kind"))
+    if "kernels" in x:
+        print("            ", {k: round(v["ms"], 4) for k, v in x["kernels"].items()})
+
+
+show(d["config"]["workload"], d)
+for k, v in d.get("workloads", {}).items():
+    show(k, v)
+print(d.get("clocks"))
