@@ -492,6 +492,29 @@ def measure_e2e(gpu, case, dm, dc, n, n_total, base, qs, counts, steps):
                                      "constraint program compiled + uploaded, candidates drawn on the device (K1 fused), best latent "
                                      "vector and min_error returned to the host" % n_total,
                              "min_error": float(mpc.min_error)}
+    if gpu.world == 1:
+        # ---- local optimiser: batched Levenberg-Marquardt on the residual-vector objective, 8 seeds in one
+        # launch (mgb_lm_refine), pose constraints dropped as motion_primitive_generator.py:181 does
+        try:
+            from morphablegraphs_b200 import MotionPrimitiveConstraints as _MPC
+            mo = _MPC()
+            mo.skeleton, mo.is_local = mpc.skeleton, mpc.is_local
+            mo.constraints = [c_ for c_ in mpc.constraints if c_.constraint_type != "keyframe_pose"]
+            dco = engine.DeviceConstraints(dm, mo, prev)
+            seeds = dm.sample(8, seed=77)
+            r0 = dco.lm_refine(seeds, quality_scale=qs, max_iter=100)
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            for _ in range(5):
+                r0 = dco.lm_refine(seeds, quality_scale=qs, max_iter=100)
+            ms_lm = 1e3 * (time.perf_counter() - t0) / 5
+            e2e["optimizer"] = {"seeds": 8, "max_jacobians": 100, "ms_per_batch": ms_lm, "residuals": dco.n_residuals(),
+                                "cost_start_mean": float(np.mean(r0["cost_start"])), "cost_mean": float(np.mean(r0["cost"])),
+                                "jacobians_mean": float(np.mean(r0["iterations"])),
+                                "call": "DeviceConstraints.lm_refine -> mgb_lm_refine: one CTA per seed, forward-difference Jacobian + "
+                                        "damped normal equations in shared memory, one launch for the whole minimisation"}
+        except engine.MgbError as e:
+            e2e["optimizer"] = {"unavailable": str(e)}
     if gpu.world == 1 and dm.D <= 32:
         # ---- cross-option batching: the planner's option loop (graph_walk_planner.py:216-226,
         # mg_state_planner.py:946-968: every outgoing edge scored with n_random_samples = 100, one after another) as ONE

@@ -263,6 +263,27 @@ typedef struct {
 int mgb_sample_score_multi(const mgb_option* options, int32_t n_options, float* h_best_cost,
                            int64_t* h_best_idx, float* h_best_rows, int32_t row_stride, void* stream);
 
+/* ---- residual vectors and the local optimiser --------------------------------------
+ * K9: the weighted residual vector of every candidate, d_out[n, R] with R = mgb_constraints_n_residuals(c):
+ * MotionPrimitiveConstraints.get_residual_vector (motion_primitive_constraints.py:124-146) - per constraint
+ * what its class returns from get_residual_vector_spline (1 value; two hands 3; pose one per point; local
+ * trajectory one per frame), times weight_factor, in list order; no zero padding. */
+int32_t mgb_constraints_n_residuals(const mgb_constraints* c);
+int mgb_residuals(const mgb_model* m, const mgb_constraints* c, const float* d_s, int64_t n, float* d_out,
+                  void* stream);
+/* K10: Levenberg-Marquardt on the residual objective
+ *   r_i(s) = (err_scale * residual_i(s) + quality_scale * (-log p(s))) / init_error_sum
+ * (obj_spatial_error_residual_vector_and_naturalness, objective_functions.py:239-267), one CTA per seed,
+ * the whole minimisation in ONE launch: replaces LeastSquares.run -> scipy leastsq (least_squares.py:35-64)
+ * as called by _optimize_parameters_numerically (motion_primitive_generator.py:179-190), for n_seeds start
+ * points at once (e.g. the top-k of mgb_sample_score).  init_error_sum <= 0: max(|sum r(s0)|, 1) per seed,
+ * as the reference computes it.  max_iter = Jacobian evaluations.  d_out_s[n_seeds, D]; d_out_err[n_seeds, 4]
+ * = sum of the weighted residuals at the result (the reference's min_error), 0.5|r|^2 (un-normalised) at the
+ * seed and at the result, iterations used. */
+int mgb_lm_refine(const mgb_model* m, const mgb_constraints* c, const float* d_seeds, int32_t n_seeds,
+                  float err_scale, float quality_scale, float init_error_sum, int32_t max_iter,
+                  float* d_out_s, float* d_out_err, void* stream);
+
 /* Same through HOST buffers (pageable or pinned): chunked H2D on a copy stream
  * overlapped with scoring, D2H of the k results; synchronous.  This is the
  * call the reference-side shim makes with the numpy array it already holds. */

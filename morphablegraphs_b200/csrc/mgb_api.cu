@@ -479,6 +479,7 @@ extern "C" int mgb_constraints_pack(const mgb_model* m, const mgb_constraint_des
 
     auto check_node = [&](int nd) { return nd >= 0 && nd < m->n_nodes; };
     auto check_slot = [&](int s) { return s >= 0 && s < n_times; };
+    std::map<int, int> lt_term_of_scratch;   // local-trajectory scratch offset -> constraint (residual-vector program)
     struct Final { int code, a, b; std::vector<float> cst; };
     std::vector<Final> finals;
     std::vector<MgbOp> begins;
@@ -624,7 +625,8 @@ extern "C" int mgb_constraints_pack(const mgb_model* m, const mgb_constraint_des
                 b.code = OP_LT_BEGIN; b.a = sc; b.b = 0; b.c = C.push_cst({(float)c.offset[0]});
                 begins.push_back(b);
                 const int nt = c.n_points - 2;
-                std::vector<float> v = {(float)(1.0 / c.offset[1]), (float)nt, (float)(nt * c.offset[1])};
+                std::vector<float> v = {(float)(1.0 / c.offset[1]), (float)nt, (float)(nt * c.offset[1]), w};
+                lt_term_of_scratch[sc] = j;
                 for (int q = 0; q < c.n_points; ++q) {
                     v.push_back((float)points[c.points_offset + q].target[0]);
                     v.push_back((float)points[c.points_offset + q].target[2]);
@@ -691,6 +693,40 @@ extern "C" int mgb_constraints_pack(const mgb_model* m, const mgb_constraint_des
         }
     }
     c->ops_fused = C.ops;
+    // ---- residual-vector program: residual layout = constraints in list order, each with the residuals
+    //      its class returns from get_residual_vector_spline (1; two hands 3; pose / quaternion frame one per point; local
+    //      trajectory one per frame); fields that named a term now name a residual ---------------------------------------
+    {
+        std::vector<int> res_base(n + 1, 0);
+        for (int j = 0; j < n; ++j) {
+            int cnt = 1;
+            if (cd[j].type == MGB_CT_TWO_HANDS) cnt = 3;
+            else if (cd[j].type == MGB_CT_POSE || cd[j].type == MGB_CT_QUAT_FRAME) cnt = cd[j].n_points;
+            else if (cd[j].type == MGB_CT_LOCAL_TRAJ) cnt = cd[j].n_slots;
+            res_base[j + 1] = res_base[j] + cnt;
+        }
+        c->n_resid = res_base[n];
+        c->ops_resid = C.ops;
+        std::vector<int> seen(n, 0);   // JROT ops / local-trajectory frames of a constraint met so far (program order = point / frame order)
+        for (MgbOp& o : c->ops_resid) {
+            switch (o.code) {
+                case OP_POS: case OP_ORIENT: case OP_REL: case OP_DIR2D: case OP_LOOKAT: case OP_FEET: case OP_CA_END:
+                case OP_TWOHANDS: case OP_POSE:
+                    o.a = res_base[o.a];
+                    break;
+                case OP_JROT:
+                    o.a = res_base[o.a] + (cd[o.a].type == MGB_CT_QUAT_FRAME ? seen[o.a]++ : 0);
+                    break;
+                case OP_LT_ACC: {
+                    const int term = lt_term_of_scratch[o.a];
+                    o.b = res_base[term] + seen[term]++;
+                    break;
+                }
+                default:
+                    break;
+            }
+        }
+    }
     c->quad_slot.resize(C.quads.size());
     for (size_t q = 0; q < C.quads.size(); ++q) c->quad_slot[q] = C.quads[q].first;
     // frames-mode program: quads index channels of the materialised frames
@@ -725,8 +761,9 @@ extern "C" int mgb_constraints_pack(const mgb_model* m, const mgb_constraint_des
     // ---- one block, one asynchronous copy: [tab4 | ops_fused | ops_frames | cst], each part 256-byte aligned ----------
     auto al = [](size_t b) { return (b + 255) & ~(size_t)255; };
     const size_t sz_tab = (size_t)c->n_quads * (KP + 1) * sizeof(float4), sz_of = c->ops_fused.size() * sizeof(MgbOp),
-                 sz_ofr = c->ops_frames.size() * sizeof(MgbOp), sz_cst = c->cst.size() * sizeof(float);
-    const size_t o_tab = 0, o_of = al(sz_tab), o_ofr = o_of + al(sz_of), o_cst = o_ofr + al(sz_ofr), total = o_cst + al(sz_cst);
+                 sz_ofr = c->ops_frames.size() * sizeof(MgbOp), sz_cst = c->cst.size() * sizeof(float), sz_ors = c->ops_resid.size() * sizeof(MgbOp);
+    const size_t o_tab = 0, o_of = al(sz_tab), o_ofr = o_of + al(sz_of), o_cst = o_ofr + al(sz_ofr), o_ors = o_cst + al(sz_cst),
+                 total = o_ors + al(sz_ors);
     MgbPackBlock* blk = nullptr;
     if (int rc = pack_block_acquire(m, total, &blk)) {
         delete c;
@@ -739,11 +776,13 @@ extern "C" int mgb_constraints_pack(const mgb_model* m, const mgb_constraint_des
         if (sz_of) memcpy(blk->pin + o_of, c->ops_fused.data(), sz_of);
         if (sz_ofr) memcpy(blk->pin + o_ofr, c->ops_frames.data(), sz_ofr);
         if (sz_cst) memcpy(blk->pin + o_cst, c->cst.data(), sz_cst);
+        if (sz_ors) memcpy(blk->pin + o_ors, c->ops_resid.data(), sz_ors);
     }
     c->d_tab = sz_tab ? reinterpret_cast<float4*>(blk->dev + o_tab) : nullptr;
     c->d_ops_fused = sz_of ? reinterpret_cast<MgbOp*>(blk->dev + o_of) : nullptr;
     c->d_ops_frames = sz_ofr ? reinterpret_cast<MgbOp*>(blk->dev + o_ofr) : nullptr;
     c->d_cst = sz_cst ? reinterpret_cast<float*>(blk->dev + o_cst) : nullptr;
+    c->d_ops_resid = sz_ors ? reinterpret_cast<MgbOp*>(blk->dev + o_ors) : nullptr;
     {
         cudaError_t e = cudaStreamWaitEvent(m->pack_stream, blk->used, 0);      // launches that still read the block's previous tenant
         if (e == cudaSuccess) e = cudaMemcpyAsync(blk->dev, blk->pin, total, cudaMemcpyHostToDevice, m->pack_stream);

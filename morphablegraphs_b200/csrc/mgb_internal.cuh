@@ -94,7 +94,8 @@ enum MgbOpCode : int32_t {
     OP_RESET = 18,    // G = identity (between slots; not required, kept for clarity)
     OP_JROT = 19,     // a = term, b = rotation quad of the joint (raw channels, no FK), c -> weight, inner weight, target R[9], is_root
     OP_LT_BEGIN = 20, // a = scratch offset (6 floats: sum, arc length, last position[3], started), c -> start_t
-    OP_LT_ACC = 21,   // a = scratch offset, c -> step, n_table, full arc length, table (x, z) * (n_table + 1) [last = last control point]
+    OP_LT_ACC = 21,   // a = scratch offset, b = residual index (residual program), c -> 1 / step, n_table, full arc length, weight,
+                      // table (x, z) * (n_table + 2) [entry n_table + 1 = last control point]
     OP_LT_END = 22,   // a = term, b = scratch offset, c -> weight
 };
 
@@ -184,6 +185,9 @@ struct mgb_constraints {
     int KP = 0;  // K rounded up to a multiple of 4: quad q occupies tab[q * (KP + 1) ...], bias first
     bool needs_s = false;  // program itself never needs s beyond K; logpdf/magnitude decided per call
     std::vector<MgbOp> ops_fused;   // quads index the contracted table
+    std::vector<MgbOp> ops_resid;   // the same program in residual-vector form: term fields hold residual indices
+    int n_resid = 0;                // length of the residual vector (before the reference's zero padding to len(s))
+    MgbOp* d_ops_resid = nullptr;
     std::vector<MgbOp> ops_frames;  // quads index channels of materialised frames: slot * P + channel
     std::vector<float> cst;
     std::vector<float> tab;  // [n_quads][KP+1][4]

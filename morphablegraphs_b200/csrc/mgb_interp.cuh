@@ -28,7 +28,11 @@ __device__ __forceinline__ float dist3(const float* a, const float* b) {
 
 // Interpreter state + resumable execution: run(ops, pc0, pc1, ...) executes ops [pc0, pc1) and keeps the
 // kinematic state, so a caller that receives the quad values in pieces can interleave (tensor-core kernel).
-template <int CPT>
+// RESID: residual-vector form (reference motion_primitive_constraints.py:124-146 + the constraint classes'
+// get_residual_vector_spline): the `term` handed to emit() is a RESIDUAL index taken from the residual program
+// (mgb_constraints::ops_resid); the two-hands term emits its 3 distances, the pose term its per-point distances (no mean,
+// no velocity term), a local trajectory one error per frame.
+template <int CPT, bool RESID = false>
 struct MgbInterp {
     MgbXf G[CPT];
     float al_c[CPT], al_s[CPT], al_dx[CPT], al_dz[CPT], al_qw[CPT], al_qy[CPT];
@@ -202,7 +206,13 @@ struct MgbInterp {
                         const float* lp = scratch[c] + op.b;
                         const float* rp = scratch[c] + op.b + 3;
                         const float mid[3] = {lp[0] + 0.5f * (rp[0] - lp[0]), lp[1] + 0.5f * (rp[1] - lp[1]), lp[2] + 0.5f * (rp[2] - lp[2])};
-                        emit(c, op.a, cs[0], dist3(cs + 1, mid) + dist3(cs + 4, lp) + dist3(cs + 7, rp));
+                        if (RESID) {   // two_hand_constraint.py:68-80
+                            emit(c, op.a, cs[0], dist3(cs + 1, mid));
+                            emit(c, op.a + 1, cs[0], dist3(cs + 4, lp));
+                            emit(c, op.a + 2, cs[0], dist3(cs + 7, rp));
+                        } else {
+                            emit(c, op.a, cs[0], dist3(cs + 1, mid) + dist3(cs + 4, lp) + dist3(cs + 7, rp));
+                        }
                     }
                     break;
                 }
@@ -247,8 +257,11 @@ struct MgbInterp {
                             const float tx = ct * bx + st * bz + ox;
                             const float tz = -st * bx + ct * bz + oz;
                             const float ex = tg[4 * j] - tx, ey = tg[4 * j + 1] - by, ez = tg[4 * j + 2] - tz;
-                            dsum += sqrtf(fmaf(ex, ex, fmaf(ey, ey, ez * ez)));
+                            const float dj = sqrtf(fmaf(ex, ex, fmaf(ey, ey, ez * ez)));
+                            dsum += dj;
+                            if (RESID) emit(c, op.a + j, cs[0], dj);   // pose_constraint.py:107-121
                         }
+                        if (RESID) continue;
                         float e = dsum / (float)np;
                         if (cs[2] != 0.f) {
                             const float* r2 = pts + 3 * np;
@@ -315,7 +328,7 @@ struct MgbInterp {
                     // the joint so far picks the target on the trajectory, tabulated by arc length (linear between samples)
                     const float step_inv = cs[0], full = cs[2];
                     const int nt = (int)cs[1];
-                    const float* tb = cs + 3;
+                    const float* tb = cs + 4;   // cs[3] = weight (residual form)
 #pragma unroll
                     for (int c = 0; c < CPT; ++c) {
                         float* st = scratch[c] + op.a;
@@ -337,11 +350,13 @@ struct MgbInterp {
                         }
                         const float ex = tx - px, ez = tz - pz;
                         st[0] += fmaf(ex, ex, ez * ez);
+                        if (RESID) emit(c, op.b, tb[-1], fmaf(ex, ex, ez * ez));   // one residual per frame; tb[-1] = weight
                         st[2] = px; st[3] = py; st[4] = pz; st[5] = 1.f;
                     }
                     break;
                 }
                 case OP_LT_END: {
+                    if (RESID) break;
 #pragma unroll
                     for (int c = 0; c < CPT; ++c) emit(c, op.a, cs[0], scratch[c][op.b]);
                     break;

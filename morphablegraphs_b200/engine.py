@@ -632,6 +632,40 @@ class DeviceConstraints(object):
                                                       float(magnitude_scale), C.byref(cost), C.byref(idx), C.c_void_p(row.ctypes.data), dm._stream()))
         return float(cost.value), int(idx.value), row.astype(np.float64)
 
+    # -- K9 / K10: residual vectors and the local optimiser ------------------------------------
+    def n_residuals(self):
+        return int(self.lib.mgb_constraints_n_residuals(self.handle))
+
+    def residuals(self, s):
+        """Weighted residual vectors [n, R] (float32 CUDA tensor) of candidates s [n, D]:
+        MotionPrimitiveConstraints.get_residual_vector (motion_primitive_constraints.py:124-146), batched."""
+        torch = _torch()
+        dm = self.dmodel
+        s = dm._f32(s)
+        n = int(s.shape[0])
+        out = torch.empty((n, self.n_residuals()), dtype=torch.float32, device=dm.torch_device)
+        with torch.cuda.device(dm.device):
+            _lib.check(self.lib.mgb_residuals(dm.handle, self.handle, C.c_void_p(s.data_ptr()), n, C.c_void_p(out.data_ptr()), dm._stream()))
+        return out
+
+    def lm_refine(self, seeds, error_scale=1.0, quality_scale=0.0, init_error_sum=0.0, max_iter=50):
+        """Levenberg-Marquardt from every row of seeds [k, D] in one launch (mgb_lm_refine).  Returns
+        dict(s [k, D] float64 numpy, min_error [k] = sum of the weighted residuals at the result, cost_start [k],
+        cost [k] = 0.5 |r|^2 of the un-normalised residual objective, iterations [k])."""
+        torch = _torch()
+        dm = self.dmodel
+        seeds = dm._f32(np.atleast_2d(seeds) if not isinstance(seeds, torch.Tensor) else seeds)
+        k = int(seeds.shape[0])
+        out_s = torch.empty((k, dm.D), dtype=torch.float32, device=dm.torch_device)
+        out_e = torch.empty((k, 4), dtype=torch.float32, device=dm.torch_device)
+        with torch.cuda.device(dm.device):
+            _lib.check(self.lib.mgb_lm_refine(dm.handle, self.handle, C.c_void_p(seeds.data_ptr()), k, float(error_scale), float(quality_scale),
+                                              float(init_error_sum), int(max_iter), C.c_void_p(out_s.data_ptr()), C.c_void_p(out_e.data_ptr()),
+                                              dm._stream()))
+        e = out_e.cpu().numpy().astype(np.float64)
+        return {"s": out_s.cpu().numpy().astype(np.float64), "min_error": e[:, 0], "cost_start": e[:, 1], "cost": e[:, 2],
+                "iterations": e[:, 3].astype(np.int64)}
+
     def score_host(self, samples, k=1, error_scale=1.0, quality_scale=0.0, magnitude_scale=0.0, return_cost=False,
                    index_base=0):
         """Score HOST candidates (numpy float32/float64 [n, D], or a pinned CPU torch tensor):

@@ -321,6 +321,58 @@ def run_local_case(ns, shape="S", n_samples=64, seed=2031):
     return out
 
 
+def run_resid_case(ns, name_of_set="mixed", shape="S", n_samples=24, seed=2041, n_opt=3):
+    """f1: the reference's own residual-vector objective (motion_primitive_constraints.py:124-146,
+    objective_functions.py:239-267) on reference-drawn samples, and the reference's own LeastSquares
+    (least_squares.py:35-64 -> scipy leastsq) from the best of them, as _optimize_parameters_numerically runs it
+    (motion_primitive_generator.py:179-190: pose constraints dropped, residuals normalised by the start error)."""
+    import importlib
+    cfg = syn.SHAPES[shape]
+    F = cfg["n_frames"]
+    skeleton = refload.make_skeleton(syn.make_skeleton_desc(cfg["n_joints"]))
+    node = refload.make_graph_node(ns, syn.make_model_json(shape))
+    np.random.seed(seed)
+    specs = make_specs(ns, node, skeleton, F, None, name_of_set)
+    S = node.sample_low_dimensional_vectors(n_samples)
+    mpc = build_mp_constraints(ns, skeleton, specs, is_local=True)
+    obj = ns.objective_functions.obj_spatial_error_residual_vector_and_naturalness
+    out = {"samples": S, "specs_json": np.array(json.dumps(specs)), "shape": np.array(shape),
+           "translation_maxima": np.array([1.0, 1.0, 1.0]), "is_local": np.array(True)}
+    with _quiet():
+        out["residual_vectors"] = np.array([mpc.get_residual_vector(node, s_, None) for s_ in S])
+        out["objective_q01"] = np.array([obj(s_, (node, mpc, None, 1.0, 0.1, 1.0)) for s_ in S])
+    # the optimiser, exactly as the generator drives it
+    ls_mod = importlib.import_module("morphablegraphs.motion_generator.optimization.least_squares")
+    mpc_opt = build_mp_constraints(ns, skeleton, specs, is_local=True)
+    mpc_opt.constraints = [c for c in mpc_opt.constraints if c.constraint_type != "keyframe_pose"]
+    out["opt_specs_json"] = np.array(json.dumps([sp_ for sp_ in specs if sp_["class"] not in ("PoseConstraint", "PoseConstraintQuatFrame")]))
+    costs = np.array([ns.objective_functions.obj_spatial_error_sum(s_, (node, mpc_opt, None)) for s_ in S])
+    order = np.argsort(costs)[:n_opt]
+    seeds, results, start_cost, final_cost, final_min_error = [], [], [], [], []
+    for qs in (0.0, 0.1):
+        for i in order:
+            ls = ls_mod.LeastSquares({"max_iterations": 500, "verbose": False})
+            ls.set_objective_function(obj)
+            data = (node, mpc_opt, None, 1.0, qs, 1.0)
+            with _quiet():
+                error_sum = max(abs(np.sum(obj(S[i], data))), 1.0)
+                data = (node, mpc_opt, None, 1.0, qs, error_sum)
+                ls.set_objective_function_parameters(data)
+                x = ls.run(initial_guess=S[i].copy())
+                r0 = obj(S[i], (node, mpc_opt, None, 1.0, qs, 1.0))
+                r1 = obj(x, (node, mpc_opt, None, 1.0, qs, 1.0))
+            seeds.append(S[i]); results.append(x)
+            start_cost.append(0.5 * np.sum(r0 ** 2)); final_cost.append(0.5 * np.sum(r1 ** 2))
+            final_min_error.append(mpc_opt.min_error)
+    out["opt_quality_scales"] = np.array([0.0] * n_opt + [0.1] * n_opt)
+    out["opt_seeds"] = np.array(seeds)
+    out["opt_results"] = np.array(results)
+    out["opt_start_cost"] = np.array(start_cost)
+    out["opt_final_cost"] = np.array(final_cost)
+    out["opt_final_min_error"] = np.array(final_min_error)
+    return out
+
+
 def run_walk_case(ns, n_steps=6, n_samples=48, seed=31):
     """BASELINE config 3 in miniature: a walk over several primitives (one S-shaped model per graph
     node, its own model seed), every step picked by the reference's own
@@ -505,6 +557,11 @@ def main():
         np.savez_compressed(os.path.join(GOLDEN_DIR, "s_walk.npz"), **out)
         print("s_walk", [int(out["step%d_best_idx" % i]) for i in range(len(out["order"]))],
               [float(out["step%d_min_error" % i]) for i in range(len(out["order"]))])
+        return 0
+    if "--only-resid" in sys.argv:
+        out = run_resid_case(ns)
+        np.savez_compressed(os.path.join(GOLDEN_DIR, "s_resid.npz"), **out)
+        print("s_resid R =", out["residual_vectors"].shape, "start", out["opt_start_cost"], "final", out["opt_final_cost"])
         return 0
     if "--only-round2" in sys.argv:
         # fixtures added in round 2: reference-made goldens at the sizes SURVEY.md 8(d) states

@@ -514,6 +514,89 @@ def candidate_costs(model, skeleton, constraints, S, prev_frames=None, error_sca
     return cost
 
 
+# --------------------------------------------------------------------------
+# residual-vector form (f1)
+# --------------------------------------------------------------------------
+def term_residuals(c, ma, skeleton, coeffs):
+    """[N, n_res]: what `c.get_residual_vector_spline` returns per candidate (unweighted).  One value for most classes
+    (their evaluate); two_hand_constraint.py:68-80 three distances; pose_constraint.py:107-121 one distance per point
+    (no mean, no velocity term); pose_constraint_quat_frame.py:60-70 one weighted rotation distance per joint;
+    local_trajectory_constraint.py:66-90 one error per frame."""
+    ct = c.constraint_type
+    N = coeffs.shape[0]
+    if ct == "keyframe_two_hands":
+        frame = _frames_at(ma, coeffs, c.canonical_keyframe)
+        lp = fk_global(skeleton, frame, c.joint_names[0])[1]
+        rp = fk_global(skeleton, frame, c.joint_names[1])[1]
+        center = np.asarray(c.target_center, dtype=np.float64)
+        return np.stack([np.linalg.norm(center - (lp + 0.5 * (rp - lp)), axis=1),
+                         np.linalg.norm(np.asarray(c.positions[0], dtype=np.float64) - lp, axis=1),
+                         np.linalg.norm(np.asarray(c.positions[1], dtype=np.float64) - rp, axis=1)], axis=1)
+    if ct == "keyframe_pose" and hasattr(c, "node_names"):
+        f1 = _frames_at(ma, coeffs, c.canonical_keyframe)
+        pc = fk_positions(skeleton, f1, c.node_names)
+        a = np.asarray(c.pose_constraint, dtype=np.float64)
+        w = np.asarray(c.weights, dtype=np.float64)
+        W = w.sum()
+        num_l = np.sum(w * (a[:, 0] * pc[:, :, 2] - pc[:, :, 0] * a[:, 2]), axis=1)
+        den_l = np.sum(w * (a[:, 0] * pc[:, :, 0] + a[:, 2] * pc[:, :, 2]), axis=1)
+        sax, saz = np.sum(w * a[:, 0]), np.sum(w * a[:, 2])
+        sbx, sbz = np.sum(w * pc[:, :, 0], axis=1), np.sum(w * pc[:, :, 2], axis=1)
+        theta = np.arctan2(num_l - (sax * sbz - sbx * saz) / W, den_l - (sax * sbx + saz * sbz) / W)
+        cth, sth = np.cos(theta), np.sin(theta)
+        ox = (sax - sbx * cth - sbz * sth) / W
+        oz = (saz + sbx * sth - sbz * cth) / W
+        tx = cth[:, None] * pc[:, :, 0] + sth[:, None] * pc[:, :, 2] + ox[:, None]
+        tz = -sth[:, None] * pc[:, :, 0] + cth[:, None] * pc[:, :, 2] + oz[:, None]
+        return np.sqrt((a[:, 0] - tx) ** 2 + (a[:, 1] - pc[:, :, 1]) ** 2 + (a[:, 2] - tz) ** 2)
+    if ct == "keyframe_pose":
+        frame = _frames_at(ma, coeffs, 0)
+        w = list(skeleton.get_joint_weights())
+        tgt = np.asarray(c.pose_constraint, dtype=np.float64)
+        out = np.zeros((N, len(w) - 1))
+        for i in range(len(w) - 1):
+            q = frame[:, 3 + 4 * (i + 1):7 + 4 * (i + 1)]
+            R = quaternion_matrix_batch(q / np.linalg.norm(q, axis=1, keepdims=True))
+            qt = tgt[3 + 4 * (i + 1):7 + 4 * (i + 1)]
+            Rt = quaternion_matrix_batch((qt / np.linalg.norm(qt))[None])[0]
+            out[:, i] = w[i] * np.sqrt(np.sum((Rt[None] - R) ** 2, axis=(1, 2)))
+        return out
+    if ct == "local_trajectory":
+        times = list(range(int(c.n_canonical_frames)))
+        p = fk_global(skeleton, eval_frames(ma, coeffs, times), c.joint_name)[1]
+        out = np.zeros((N, len(times)))
+        for n in range(N):
+            t = float(c.start_t)
+            for f in range(p.shape[1]):
+                if f > 0:
+                    t += np.linalg.norm(p[n, f - 1] - p[n, f])
+                target = c.trajectory.query_point_by_absolute_arc_length(t)
+                out[n, f] = (target[0] - p[n, f, 0]) ** 2 + (target[2] - p[n, f, 2]) ** 2
+        return out
+    return term_errors(c, ma, skeleton, coeffs)[:, None]
+
+
+def residual_vectors(model, skeleton, constraints, S, prev_frames=None):
+    """[N, R] weighted residual vectors: reference motion_primitive_constraints.py:124-146."""
+    ma = model if isinstance(model, ModelArrays) else ModelArrays(model)
+    S = np.atleast_2d(np.asarray(S, dtype=np.float64))
+    coeffs = back_project_coeffs(ma, S)
+    if not constraints.is_local and prev_frames is not None:
+        coeffs = align_coeffs_to_prev_frames(ma, skeleton, coeffs, prev_frames)
+    return np.concatenate([c.weight_factor * term_residuals(c, ma, skeleton, coeffs) for c in constraints.constraints], axis=1)
+
+
+def residual_objective(model, skeleton, constraints, S, prev_frames=None, error_scale=1.0, quality_scale=0.0, init_error_sum=1.0):
+    """[N, max(R, D)]: reference objective_functions.py:239-267 (obj_spatial_error_residual_vector_and_naturalness)."""
+    ma = model if isinstance(model, ModelArrays) else ModelArrays(model)
+    S = np.atleast_2d(np.asarray(S, dtype=np.float64))
+    r = residual_vectors(ma, skeleton, constraints, S, prev_frames) * error_scale
+    r = r + (-gmm_logpdf(ma, S) * quality_scale)[:, None]
+    if r.shape[1] < S.shape[1]:
+        r = np.concatenate([r, np.zeros((S.shape[0], S.shape[1] - r.shape[1]))], axis=1)
+    return r / init_error_sum
+
+
 def first_argmin(cost):
     """reference motion_primitive_generator.py:251-257: strict `>` so the first
     minimum wins; NaN never wins."""

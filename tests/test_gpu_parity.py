@@ -731,3 +731,75 @@ def test_generator_scores_all_options_at_once():
     for sa, sb in zip(steps_a, steps_b):
         assert sa["constraints"].min_error == sb["constraints"].min_error
         assert sa["constraints"].evaluations == sb["constraints"].evaluations == 500
+
+
+# ---------------------------------------------------------------------------
+# f1: residual vectors (K9) and the batched Levenberg-Marquardt (K10)
+# ---------------------------------------------------------------------------
+def _opt_case():
+    import json
+    from morphablegraphs_b200 import synthetic as syn, MotionPrimitiveConstraints, CONSTRAINT_FACTORY
+    c = Case("s_resid")
+    mpc = MotionPrimitiveConstraints()
+    mpc.skeleton, mpc.is_local = c.skeleton, True
+    mpc.constraints = syn.build_constraints(CONSTRAINT_FACTORY, c.skeleton, json.loads(str(c.g["opt_specs_json"])))
+    return c, mpc
+
+
+def test_residual_vectors_match_the_reference():
+    from morphablegraphs_b200 import engine
+    c = Case("s_resid")
+    dm = engine.DeviceModel(c.node, c.skeleton)
+    dc = engine.DeviceConstraints(dm, c.constraints)
+    r = dc.residuals(c.samples).cpu().numpy()
+    assert r.shape == c.g["residual_vectors"].shape
+    assert rel_err(r, c.g["residual_vectors"]).max() < RTOL
+    # the objective function with the reference's signature, evaluated on the device
+    from morphablegraphs_b200.optimization import obj_spatial_error_residual_vector_and_naturalness as obj
+    v = obj(c.samples[3], (c.node, c.constraints, None, 1.0, 0.1, 1.0))
+    assert rel_err(v, c.g["objective_q01"][3]).max() < RTOL
+    assert abs(c.constraints.min_error - c.g["residual_vectors"][3].sum()) < RTOL * abs(c.g["residual_vectors"][3].sum())
+
+
+def test_device_least_squares_reaches_the_reference_optimisers_error():
+    """mgb_lm_refine from the seeds the reference's own LeastSquares (scipy leastsq, maxfev 500) started from: the
+    error it reaches - re-evaluated in float64 by the oracle - is not worse than the reference's result (1e-3
+    relative), for quality_scale 0 and 0.1; all seeds of a quality scale are refined in ONE launch."""
+    from oracle import np_oracle as O
+    from morphablegraphs_b200 import engine
+    from morphablegraphs_b200.optimization import DeviceLeastSquares
+    c, mpc = _opt_case()
+    g = c.g
+    for qs in (0.0, 0.1):
+        sel = np.where(g["opt_quality_scales"] == qs)[0]
+        ls = DeviceLeastSquares({"max_iterations": 500})
+        ls.set_objective_function_parameters((c.node, mpc, None, 1.0, qs, 0.0))
+        before = engine.launch_count()
+        res = ls.run_batch(g["opt_seeds"][sel])
+        assert engine.launch_count() - before == 1
+        r1 = O.residual_objective(c.node, c.skeleton, mpc, res["s"], quality_scale=qs)
+        cost64 = 0.5 * np.sum(r1 ** 2, axis=1)
+        assert rel_err(res["cost"], cost64).max() < 1e-3                      # the kernel's own account of where it ended
+        assert rel_err(res["cost_start"], g["opt_start_cost"][sel]).max() < 1e-3
+        assert (cost64 <= g["opt_final_cost"][sel] * (1.0 + 1e-3)).all(), (qs, cost64, g["opt_final_cost"][sel])
+        assert (res["cost"] < res["cost_start"]).all()
+
+
+def test_generator_runs_the_device_optimiser():
+    """generate_constrained_sample with use_local_optimization: the arg-min seeds the device Levenberg-Marquardt through the
+    reference's numerical_minimizer slot (motion_primitive_generator.py:179-190); the error does not go up."""
+    from morphablegraphs_b200 import MotionPrimitiveGenerator
+    from morphablegraphs_b200.optimization import DeviceLeastSquares
+    c, mpc = _opt_case()
+    cfgd = {"n_random_samples": 2000, "local_optimization_mode": "keyframes",
+            "local_optimization_settings": {"start_error_threshold": 0.0, "error_scale_factor": 1.0, "quality_scale_factor": 0.1,
+                                            "max_iterations": 500, "verbose": False}}
+    plain = MotionPrimitiveGenerator(None, cfgd, skeleton=c.skeleton, seed=3)
+    s0 = plain.generate_constrained_sample(c.node, mpc)
+    e0 = mpc.min_error
+    opt = MotionPrimitiveGenerator(None, cfgd, skeleton=c.skeleton, seed=3)
+    opt.numerical_minimizer = DeviceLeastSquares(cfgd["local_optimization_settings"])
+    mpc.use_local_optimization = True
+    s1 = opt.generate_constrained_sample(c.node, mpc)
+    assert s1.shape == s0.shape and not np.array_equal(s0, s1)
+    assert mpc.min_error < e0

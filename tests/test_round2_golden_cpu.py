@@ -174,3 +174,23 @@ def test_reference_objects_flatten_like_the_mirror(name):
     assert np.array_equal(mp_ref.translation_maxima, mp_mine.translation_maxima)
     gr, gm = mp_ref.gaussian_mixture_model, mp_mine.gaussian_mixture_model
     assert np.array_equal(gr.weights_, gm.weights_) and np.array_equal(gr.means_, gm.means_) and np.array_equal(gr.covariances_, gm.covariances_)
+
+
+# ---------------------------------------------------------------------------
+# f1: residual-vector objective, pinned by the reference's own functions (tests/golden/s_resid.npz)
+# ---------------------------------------------------------------------------
+def test_oracle_residual_vectors_match_the_reference():
+    c = Case("s_resid")
+    r = O.residual_vectors(c.node, c.skeleton, c.constraints, c.samples)
+    assert r.shape == c.g["residual_vectors"].shape
+    assert rel_err(r, c.g["residual_vectors"]).max() < 1e-9
+    obj = O.residual_objective(c.node, c.skeleton, c.constraints, c.samples, quality_scale=0.1)
+    assert rel_err(obj, c.g["objective_q01"]).max() < 1e-9
+    # the sum of the residual vector is the scalar objective for every class but the pose term (mean vs per point) ...
+    cost, terms = O.candidate_costs(c.node, c.skeleton, c.constraints, c.samples, return_terms=True)
+    keep = [i for i, k in enumerate(c.constraints.constraints) if k.constraint_type != "keyframe_pose"]
+    mpc2 = type(c.constraints)()
+    mpc2.skeleton, mpc2.is_local = c.skeleton, True
+    mpc2.constraints = [c.constraints.constraints[i] for i in keep]
+    assert rel_err(O.residual_vectors(c.node, c.skeleton, mpc2, c.samples).sum(axis=1),
+                   sum(c.constraints.constraints[i].weight_factor * terms[i] for i in keep)).max() < 1e-9
