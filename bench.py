@@ -328,7 +328,7 @@ class Gpu(object):
             from morphablegraphs_b200 import sharding
             try:
                 self.peer = sharding.PeerExchange(self.dev)
-                self.exchange_kind = "mgb_exchange_best: P2P stores into every peer's slot array over NVLink + in-kernel first-minimum reduction"
+                self.exchange_kind = "in the score kernel's epilogue (mgb_sample_score_sharded): P2P stores into every peer's slot array over NVLink + first-minimum reduction by the folding CTA"
             except Exception as e:                    # symmetric memory unavailable: NCCL all-gather (still a GPU path)
                 self.exchange_kind = "nccl all_gather of (cost, index) [peer memory unavailable: %s]" % str(e)[:120]
             flag = torch.tensor([1.0 if self.peer is not None else 0.0], device=self.dev)
@@ -383,9 +383,9 @@ def measure_steps(gpu, dm, dc, n, n_total, base, qs, counts, steps, warmup):
 
     def step():
         state["seed"] += 1
+        if gpu.peer is not None:       # one launch: the exchange of the per-rank best runs in the score kernel's epilogue
+            return dc.sample_score_sharded(n, gpu.peer, seed=state["seed"], counts=counts, n_total=n_total, index_base=base, quality_scale=qs)
         res = dc.sample_score(n, seed=state["seed"], counts=counts, n_total=n_total, index_base=base, k=1, quality_scale=qs)
-        if gpu.peer is not None:
-            return gpu.peer.exchange(res["best_cost"], res["best_idx"])
         if gpu.world > 1:
             mine = torch.stack([res["best_cost"][0].double(), res["best_idx"][0].double()])
             gpu.dist.all_gather_into_tensor(gpu.gathered.view(-1), mine)
@@ -667,6 +667,44 @@ def measure_workload(gpu, workload, args, steps, warmup, headline):
     return res
 
 
+def measure_config3(gpu, n_per_step=1_000_000):
+    """BASELINE configs[2]: the action list of the reference's examples/example_input.json (walk, pickRight, carryRight,
+    placeRight = 17 motion-primitive steps) over the synthetic 14-primitive graph, loaded from the reference's archive format
+    into resident device models; 1M candidates per step in total, sharded over the ranks (125 k per GPU on 8), every step one
+    planner-facing call (constraints built on the host from the walk so far -> compile + upload -> fused sample / score /
+    arg-min -> exchange of the per-rank best -> winner back-projected and appended).  Wall clock, steps are sequential."""
+    import io
+    torch = gpu.torch
+    from morphablegraphs_b200 import synthetic as syn, MotionPrimitiveGenerator, graph_synthesis as GS, engine
+    from morphablegraphs_b200.motion_state_graph import MotionStateGraphLoader, graph_to_bytes
+    blob = graph_to_bytes(syn.make_graph_data())
+    t0 = time.perf_counter()
+    ld = MotionStateGraphLoader()
+    ld.set_data_source(io.BytesIO(blob))
+    graph = ld.build(resident=True)
+    torch.cuda.synchronize()
+    load_s = time.perf_counter() - t0
+    gen = MotionPrimitiveGenerator(None, {"n_random_samples": n_per_step, "use_local_coordinates": False}, skeleton=graph.skeleton, seed=21)
+    synth = GS.GraphWalkSynthesizer(graph, gen)
+    synth.run(syn.EXAMPLE_INPUT, max_steps=3)
+    torch.cuda.synchronize()
+    gpu.barrier()
+    l0 = engine.launch_count()
+    t0 = time.perf_counter()
+    out = synth.run(syn.EXAMPLE_INPUT)
+    torch.cuda.synchronize()
+    t1 = time.perf_counter()
+    gpu.windows.append((t0, t1))
+    dt = gpu.max_over_ranks(t1 - t0)
+    return {"value": len(out) * n_per_step / dt, "unit": UNIT, "motion_primitive_steps": len(out), "candidates_per_step_all_gpus": n_per_step,
+            "candidates_per_gpu_per_step": n_per_step // gpu.world, "ms_per_motion_primitive_step": 1e3 * dt / len(out), "total_ms": 1e3 * dt,
+            "launches_per_step": (engine.launch_count() - l0) / float(len(out)), "graph_load_s": load_s, "archive_bytes": len(blob),
+            "primitives_resident": len(graph.nodes), "scaling": "strong", "timing": "wall clock around the whole synthesis, max over ranks",
+            "mean_min_error": float(np.mean([r["min_error"] for r in out])),
+            "description": "configs[2]: examples/example_input.json action list over the synthetic walk / pick / carry / place graph "
+                           "(graph_synthesis.GraphWalkSynthesizer), non-local path (candidates aligned to the walk so far)"}
+
+
 def main():
     args = parse_args()
     # exactly ONE line on stdout: libraries (NCCL prints its version banner there) go to stderr
@@ -688,6 +726,9 @@ def main():
     if not args.only:
         for name in SECONDARY[args.workload]:
             others[name] = measure_workload(gpu, name, args, max(3, min(args.steps, 10)), args.warmup, headline=False)
+    c3 = None
+    if not args.only:
+        c3 = measure_config3(gpu)
     if gpu.rank == 0:
         clocks.stop()
     gpu.barrier()
@@ -707,6 +748,8 @@ def main():
         out["cpu_baseline"] = cpu_baseline_leg(args.workload, args.cpu_seconds, extras=True)
         for name in others:
             others[name]["cpu_baseline"] = cpu_baseline_leg(name, max(3.0, args.cpu_seconds * 0.5))
+    if c3 is not None:
+        others["C3"] = c3
     if others:
         out["workloads"] = others
     emit(json.dumps(out))

@@ -244,6 +244,29 @@ int mgb_sample_score_best(const mgb_model* m, const mgb_constraints* c, int64_t 
                           float magnitude_scale, float* h_best_cost, int64_t* h_best_idx,
                           float* h_best_row, void* stream);
 
+/* The same with the candidates of the step SHARDED over the GPUs of one box (this rank: global indices
+ * [index_base, index_base + n) of the job whose per-component counts are h_counts): the CTA that folds this
+ * rank's minima also exchanges the 16-byte (cost, index) record with every peer through NVLink peer memory and
+ * reduces the records arriving in its own slot array - the step stays ONE launch per rank, every rank returns the
+ * job-wide winner and re-draws the same winning row.  Slot arrays: mgb_exchange_slot_bytes(world) bytes per rank,
+ * zero-filled, peer-mapped (e.g. torch symmetric memory); seq: a step counter > 0 shared by the ranks. */
+typedef struct {
+    void* const* d_peer_slots; /* device array [world] of the ranks' slot arrays (this rank's own included) */
+    int32_t rank, world;
+    uint32_t seq;
+    int64_t spin_limit;        /* polls before the error flag is raised; <= 0: default (~1 s)             */
+    int32_t* d_err;            /* device int: 1 + peer that never arrived                                 */
+} mgb_exchange_desc;
+/* device-resident form (k = 1; results stay in d_best_cost / d_best_idx on every rank) */
+int mgb_sample_score_sharded(const mgb_model* m, const mgb_constraints* c, int64_t n, int64_t index_base,
+                             const int64_t* h_counts, uint64_t seed, float err_scale, float quality_scale,
+                             float magnitude_scale, const mgb_exchange_desc* x, float* d_best_cost,
+                             int64_t* d_best_idx, void* d_workspace, size_t workspace_bytes, void* stream);
+int mgb_sample_score_best_sharded(const mgb_model* m, const mgb_constraints* c, int64_t n, int64_t index_base,
+                                  const int64_t* h_counts, uint64_t seed, float err_scale, float quality_scale,
+                                  float magnitude_scale, const mgb_exchange_desc* x, float* h_best_cost,
+                                  int64_t* h_best_idx, float* h_best_row, void* stream);
+
 /* Cross-option batching: the outgoing options of a planner step - each its own (model, constraint
  * program, sample count, seed) - sampled, scored and reduced in ONE launch, one arg-min per option.
  * The reference scores them one after another (GraphWalkPlanner._evaluate_options,

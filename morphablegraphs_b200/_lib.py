@@ -86,6 +86,12 @@ class AlignDesc(C.Structure):
     _fields_ = [("mode", C.c_int32), ("prev_heading_deg", C.c_double), ("prev_root", C.c_double * 3)]
 
 
+class ExchangeDesc(C.Structure):
+    """mgb_exchange_desc (include/mgb200.h)."""
+    _fields_ = [("d_peer_slots", C.c_void_p), ("rank", C.c_int32), ("world", C.c_int32), ("seq", C.c_uint32),
+                ("spin_limit", C.c_int64), ("d_err", C.c_void_p)]
+
+
 class Option(C.Structure):
     """mgb_option (include/mgb200.h): one outgoing option of a planner step."""
     _fields_ = [("model", C.c_void_p), ("constraints", C.c_void_p), ("n", C.c_int64), ("index_base", C.c_int64),
@@ -114,6 +120,10 @@ SYMBOLS = {
     "mgb_sample_score": (C.c_int, [_vp, _vp, _i64, _i64, C.POINTER(C.c_int64), C.c_uint64, _f, _f, _f, _vp, _i32, _vp, _vp, _vp, _sz, _vp]),
     "mgb_sample_score_best": (C.c_int, [_vp, _vp, _i64, _i64, C.POINTER(C.c_int64), C.c_uint64, _f, _f, _f, C.POINTER(C.c_float),
                                         C.POINTER(C.c_int64), _vp, _vp]),
+    "mgb_sample_score_sharded": (C.c_int, [_vp, _vp, _i64, _i64, C.POINTER(C.c_int64), C.c_uint64, _f, _f, _f, C.POINTER(ExchangeDesc),
+                                           _vp, _vp, _vp, _sz, _vp]),
+    "mgb_sample_score_best_sharded": (C.c_int, [_vp, _vp, _i64, _i64, C.POINTER(C.c_int64), C.c_uint64, _f, _f, _f, C.POINTER(ExchangeDesc),
+                                                C.POINTER(C.c_float), C.POINTER(C.c_int64), _vp, _vp]),
     "mgb_sample_score_multi": (C.c_int, [C.POINTER(Option), _i32, _vp, _vp, _vp, _i32, _vp]),
     "mgb_constraints_n_residuals": (_i32, [_vp]),
     "mgb_residuals": (C.c_int, [_vp, _vp, _vp, _i64, _vp, _vp]),

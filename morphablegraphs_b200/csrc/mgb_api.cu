@@ -849,6 +849,32 @@ extern "C" int mgb_sample_score(const mgb_model* m, const mgb_constraints* c, in
                             nullptr, k, d_best_cost, d_best_idx, d_workspace, workspace_bytes, (cudaStream_t)stream);
 }
 
+static int exchange_from_desc(const mgb_exchange_desc* x, MgbExchange& xch) {
+    memset(&xch, 0, sizeof(xch));
+    if (!x) return MGB_OK;
+    MGB_REQUIRE(x->d_peer_slots && x->d_err, "exchange: null argument");
+    MGB_REQUIRE(x->world >= 1 && x->world <= 32 && x->rank >= 0 && x->rank < x->world, "exchange: rank / world out of range (one box: world <= 32)");
+    MGB_REQUIRE(x->seq != 0, "exchange: seq 0 is the cleared state of the slots; start at 1");
+    xch.peer_slots = x->d_peer_slots;
+    xch.rank = x->rank;
+    xch.world = x->world;
+    xch.seq = x->seq;
+    xch.spin_limit = x->spin_limit > 0 ? x->spin_limit : 20000000;
+    xch.err = x->d_err;
+    return MGB_OK;
+}
+
+extern "C" int mgb_sample_score_sharded(const mgb_model* m, const mgb_constraints* c, int64_t n, int64_t index_base, const int64_t* h_counts,
+                                        uint64_t seed, float err_scale, float quality_scale, float magnitude_scale,
+                                        const mgb_exchange_desc* x, float* d_best_cost, int64_t* d_best_idx, void* d_workspace,
+                                        size_t workspace_bytes, void* stream) {
+    MGB_REQUIRE(c, "null constraints handle");
+    MgbExchange xch;
+    if (int rc = exchange_from_desc(x, xch)) return rc;
+    return mgb_launch_score(m, c, 2, nullptr, 0, nullptr, h_counts, seed, n, index_base, err_scale, quality_scale, magnitude_scale, nullptr,
+                            nullptr, 1, d_best_cost, d_best_idx, d_workspace, workspace_bytes, (cudaStream_t)stream, nullptr, x ? &xch : nullptr);
+}
+
 // ---------------------------------------------------------------------------
 // planner-facing entries: results (cost, index, winning row) come back to HOST memory in one copy
 // ---------------------------------------------------------------------------
@@ -899,8 +925,18 @@ int scratch_for(int device, DevScratch** out) {
 extern "C" int mgb_sample_score_best(const mgb_model* m, const mgb_constraints* c, int64_t n, int64_t index_base, const int64_t* h_counts,
                                      uint64_t seed, float err_scale, float quality_scale, float magnitude_scale, float* h_best_cost,
                                      int64_t* h_best_idx, float* h_best_row, void* stream_) {
+    return mgb_sample_score_best_sharded(m, c, n, index_base, h_counts, seed, err_scale, quality_scale, magnitude_scale, nullptr, h_best_cost,
+                                         h_best_idx, h_best_row, stream_);
+}
+
+extern "C" int mgb_sample_score_best_sharded(const mgb_model* m, const mgb_constraints* c, int64_t n, int64_t index_base, const int64_t* h_counts,
+                                             uint64_t seed, float err_scale, float quality_scale, float magnitude_scale,
+                                             const mgb_exchange_desc* x, float* h_best_cost, int64_t* h_best_idx, float* h_best_row,
+                                             void* stream_) {
     cudaStream_t stream = (cudaStream_t)stream_;
     MGB_REQUIRE(m && h_best_cost && h_best_idx, "null argument");
+    MgbExchange xch;
+    if (int rcx = exchange_from_desc(x, xch)) return rcx;
     MGB_REQUIRE(!h_best_row || m->D <= SCR_ROW, "latent dimension %d exceeds the result record (%d)", m->D, SCR_ROW);
     DevScratch* s = nullptr;
     if (int rc = scratch_for(m->device, &s)) return rc;
@@ -908,7 +944,7 @@ extern "C" int mgb_sample_score_best(const mgb_model* m, const mgb_constraints* 
     MGB_CUDA(cudaSetDevice(m->device));
     int rc = mgb_launch_score(m, c, 2, nullptr, 0, nullptr, h_counts, seed, n, index_base, err_scale, quality_scale, magnitude_scale, nullptr,
                               nullptr, 1, &s->d_res[0].cost, (int64_t*)&s->d_res[0].idx, s->d_ws, s->ws_stride, stream,
-                              h_best_row ? s->d_res[0].row : nullptr);
+                              h_best_row ? s->d_res[0].row : nullptr, x ? &xch : nullptr);
     if (rc != MGB_OK) return rc;
     const size_t bytes = offsetof(ScrResult, row) + (h_best_row ? sizeof(float) * m->D : 0);
     MGB_CUDA(cudaMemcpyAsync(s->h_res, s->d_res, bytes, cudaMemcpyDeviceToHost, stream));

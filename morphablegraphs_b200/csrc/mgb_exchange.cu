@@ -13,72 +13,26 @@
 // its own step).  A record is {cost, seq, idx}; payload first, fence, then seq (the flag).
 #include <math.h>
 
+#include "mgb_exchange.cuh"
 #include "mgb_internal.cuh"
 
 namespace {
-
-struct __align__(16) MgbBestSlot {
-    float cost;
-    unsigned int seq;
-    long long idx;
-};
-
-__device__ __forceinline__ void st_release_sys_u32(unsigned int* p, unsigned int v) {
-    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
-__device__ __forceinline__ unsigned int ld_acquire_sys_u32(const unsigned int* p) {
-    unsigned int v;
-    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-    return v;
-}
 
 __global__ void __launch_bounds__(32) mgb_exchange_best_kernel(const float* __restrict__ my_cost, const long long* __restrict__ my_idx,
                                                               void* const* __restrict__ peer_slots, int rank, int world, unsigned int seq,
                                                               long long spin_limit, float* __restrict__ out_cost,
                                                               long long* __restrict__ out_idx, int* __restrict__ err) {
-    const int lane = threadIdx.x;
-    const int buf = (int)(seq & 1u) * world;
     // launched with programmatic stream serialization: this grid may be resident before the score kernel
-    // in front of it has drained; everything above this line overlaps its tail, the wait below orders the
-    // read of my_cost / my_idx after its completion
+    // in front of it has drained; the wait below orders the read of my_cost / my_idx after its completion
     asm volatile("griddepcontrol.wait;" ::: "memory");
-    float c = INFINITY;
-    long long i = 0x7fffffffffffffffLL;
-    bool have = false;
-    if (lane < world) {
-        // publish my record in peer `lane`'s slot array (my own included)
-        MgbBestSlot* dst = reinterpret_cast<MgbBestSlot*>(peer_slots[lane]) + buf + rank;
-        const float mc = my_cost[0];
-        const long long mi = my_idx[0];
-        *reinterpret_cast<volatile float*>(&dst->cost) = mc;
-        *reinterpret_cast<volatile long long*>(&dst->idx) = mi;
-        st_release_sys_u32(&dst->seq, seq);
-        // wait for peer `lane`'s record in MY array
-        const MgbBestSlot* src = reinterpret_cast<const MgbBestSlot*>(peer_slots[rank]) + buf + lane;
-        long long spins = 0;
-        while (ld_acquire_sys_u32(&src->seq) != seq) {
-            if (++spins > spin_limit) {
-                atomicExch(err, 1 + lane);      // which peer never arrived
-                break;
-            }
-            __nanosleep(40);
-        }
-        c = *reinterpret_cast<const volatile float*>(&src->cost);
-        i = *reinterpret_cast<const volatile long long*>(&src->idx);
-        have = (c == c);                        // NaN never wins (reference: `min_error > error`)
-    }
-    // first-minimum rule across ranks: lowest cost, lowest global index on ties
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-        const float oc = __shfl_xor_sync(0xffffffffu, c, o);
-        const long long oi = __shfl_xor_sync(0xffffffffu, i, o);
-        const bool oh = __shfl_xor_sync(0xffffffffu, have ? 1 : 0, o) != 0;
-        const bool take = oh && (!have || oc < c || (oc == c && oi < i));
-        if (take) { c = oc; i = oi; have = true; }
-    }
-    if (lane == 0) {
-        out_cost[0] = have ? c : INFINITY;
-        out_idx[0] = have ? i : 0;
+    MgbExchange x;
+    x.peer_slots = peer_slots; x.rank = rank; x.world = world; x.seq = seq; x.spin_limit = spin_limit; x.err = err;
+    float c;
+    long long i;
+    mgb_exchange_warp(x, my_cost[0], my_idx[0], c, i);
+    if (threadIdx.x == 0) {
+        out_cost[0] = c;
+        out_idx[0] = i;
     }
 }
 

@@ -9,6 +9,7 @@
 #include <vector>
 
 #include "../../include/mgb200.h"
+#include "mgb_exchange.cuh"
 
 // ---------------------------------------------------------------------------
 // error handling: thread-local message, no exceptions across the ABI
@@ -257,6 +258,7 @@ struct ScoreParams {
     unsigned int* done_count;  // [1]
     float* best_cost;
     long long* best_idx;
+    MgbExchange xch;           // world > 1 (xch.peer_slots != NULL): the folding CTA exchanges this rank's best with its peers
     float* best_row;           // MODE_SAMPLE: [D] the winning latent vector, re-drawn by the CTA that folds the partials (or NULL)
 };
 
@@ -266,7 +268,7 @@ int mgb_launch_score(const mgb_model* m, const mgb_constraints* c, int mode, con
                      const float* d_frames, const int64_t* h_counts, uint64_t seed, int64_t n, int64_t index_base, float err_scale,
                      float quality_scale, float magnitude_scale, float* d_cost, float* d_terms, int k,
                      float* d_best_cost, int64_t* d_best_idx, void* d_ws, size_t ws_bytes,
-                     cudaStream_t stream, float* d_best_row = nullptr);
+                     cudaStream_t stream, float* d_best_row = nullptr, const MgbExchange* xch = nullptr);
 // one fused sample + score + arg-min job of a multi-job launch (mgb_sample_score_multi)
 struct MgbJob {
     const mgb_model* m;

@@ -387,10 +387,25 @@ __device__ __forceinline__ void score_body(const ScoreParams& p, const int cta, 
     __syncthreads();
     if ((tid & 31) == 0) { sm_redc[tid >> 5] = best_c; sm_redi[tid >> 5] = best_i; }
     __syncthreads();
+    if (tid < 32) {
+        // warp 0: fold the warp results, then (world > 1) exchange this rank's best with the peers over NVLink - in this CTA's
+        // epilogue, no second launch
+        if (tid == 0) {
+            for (int w = 1; w < MGB_BLOCK / 32; ++w)
+                if (better(sm_redc[w], sm_redi[w], best_c, best_i)) { best_c = sm_redc[w]; best_i = sm_redi[w]; }
+            if (best_i == LLONG_MAX) best_i = p.index_base;  // nothing finite: reference keeps index 0
+        }
+        best_c = __shfl_sync(0xffffffffu, best_c, 0);
+        best_i = __shfl_sync(0xffffffffu, best_i, 0);
+        if (p.xch.peer_slots != nullptr) {
+            float gc;
+            long long gi;
+            mgb_exchange_warp(p.xch, best_c, best_i, gc, gi);
+            best_c = gc;
+            best_i = gi;
+        }
+    }
     if (tid == 0) {
-        for (int w = 1; w < MGB_BLOCK / 32; ++w)
-            if (better(sm_redc[w], sm_redi[w], best_c, best_i)) { best_c = sm_redc[w]; best_i = sm_redi[w]; }
-        if (best_i == LLONG_MAX) best_i = p.index_base;  // nothing finite: reference keeps index 0
         p.best_cost[0] = best_c;
         p.best_idx[0] = best_i;
         *p.done_count = 0u;  // ready for the next launch
@@ -646,8 +661,9 @@ int mgb_launch_score(const mgb_model* m, const mgb_constraints* c, int mode, con
                      const float* d_frames, const int64_t* h_counts, uint64_t seed, int64_t n, int64_t index_base, float err_scale,
                      float quality_scale, float magnitude_scale, float* d_cost, float* d_terms, int k,
                      float* d_best_cost, int64_t* d_best_idx, void* d_ws, size_t ws_bytes,
-                     cudaStream_t stream, float* d_best_row) {
+                     cudaStream_t stream, float* d_best_row, const MgbExchange* xch) {
     MGB_REQUIRE(m, "null model handle");
+    MGB_REQUIRE(!xch || (k == 1 && n > 0), "the in-kernel exchange needs k = 1 and a non-empty shard");
     MGB_REQUIRE(!c || c->model == m, "constraints were packed for a different model");
     MGB_REQUIRE(n >= 0, "negative n");
     MGB_REQUIRE(k >= 0 && k <= 64, "k must be in [0, 64]");
@@ -682,6 +698,7 @@ int mgb_launch_score(const mgb_model* m, const mgb_constraints* c, int mode, con
     if (int rc = build_score_params(m, c, mode, d_s, d_frames, h_counts, seed, n, index_base, err_scale, quality_scale, magnitude_scale, d_cost,
                                     d_terms, k, d_best_cost, d_best_idx, d_best_row, d_ws, p, plan))
         return rc;
+    if (xch) p.xch = *xch;
     // the completion counter in the workspace must be zero on entry: the caller zero-fills a
     // fresh workspace once (include/mgb200.h) and the kernel re-arms it at the end of every launch
     if (d_terms) MGB_CUDA(cudaMemsetAsync(d_terms, 0, (size_t)c->n_terms * n * sizeof(float), stream));

@@ -964,10 +964,23 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mgb_score_tc_kernel(const __gri
                 asm volatile("bar.sync 3, 128;" ::: "memory");
                 if (lane == 0) { sm_redc[wq] = best_c; sm_redi[wq] = best_i; }
                 asm volatile("bar.sync 3, 128;" ::: "memory");
+                if (tid0 < 32) {   // the group's first warp: final fold, then (world > 1) the exchange with the peers in this epilogue
+                    if (tid0 == 0) {
+                        for (int w = 0; w < 4; ++w)
+                            if (tc_better(sm_redc[w], sm_redi[w], best_c, best_i)) { best_c = sm_redc[w]; best_i = sm_redi[w]; }
+                        if (best_i == LLONG_MAX) best_i = sp.index_base;  // nothing finite: reference keeps index 0
+                    }
+                    best_c = __shfl_sync(0xffffffffu, best_c, 0);
+                    best_i = __shfl_sync(0xffffffffu, best_i, 0);
+                    if (sp.xch.peer_slots != nullptr) {
+                        float gc;
+                        long long gi2;
+                        mgb_exchange_warp(sp.xch, best_c, best_i, gc, gi2);
+                        best_c = gc;
+                        best_i = gi2;
+                    }
+                }
                 if (tid0 == 0) {
-                    for (int w = 0; w < 4; ++w)
-                        if (tc_better(sm_redc[w], sm_redi[w], best_c, best_i)) { best_c = sm_redc[w]; best_i = sm_redi[w]; }
-                    if (best_i == LLONG_MAX) best_i = sp.index_base;  // nothing finite: reference keeps index 0
                     sp.best_cost[0] = best_c;
                     sp.best_idx[0] = best_i;
                     *sp.done_count = 0u;  // ready for the next launch

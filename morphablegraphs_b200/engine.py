@@ -614,8 +614,26 @@ class DeviceConstraints(object):
             out["cost"] = cost
         return out
 
+    def sample_score_sharded(self, n, peer, seed=0, counts=None, n_total=None, index_base=0, error_scale=1.0, quality_scale=0.0,
+                             magnitude_scale=0.0):
+        """This rank's shard of a step with the exchange of the per-rank best inside the kernel's epilogue
+        (mgb_sample_score_sharded): one launch, returns device tensors (best_cost[1], best_idx[1]) holding the JOB-WIDE winner."""
+        torch = _torch()
+        dm = self.dmodel
+        counts = np.ascontiguousarray(counts if counts is not None else dm.component_counts(int(n_total), seed), dtype=np.int64)
+        best_cost = torch.empty((1,), dtype=torch.float32, device=dm.torch_device)
+        best_idx = torch.empty((1,), dtype=torch.int64, device=dm.torch_device)
+        ws = dm.workspace()
+        desc = peer.next_desc()
+        with torch.cuda.device(dm.device):
+            _lib.check(self.lib.mgb_sample_score_sharded(dm.handle, self.handle, int(n), int(index_base), counts.ctypes.data_as(C.POINTER(C.c_int64)),
+                                                         C.c_uint64(int(seed) & 0xFFFFFFFFFFFFFFFF), float(error_scale), float(quality_scale),
+                                                         float(magnitude_scale), C.byref(desc), C.c_void_p(best_cost.data_ptr()),
+                                                         C.c_void_p(best_idx.data_ptr()), C.c_void_p(ws.data_ptr()), ws.numel(), dm._stream()))
+        return best_cost, best_idx
+
     def sample_score_best(self, n, seed=0, counts=None, n_total=None, index_base=0, error_scale=1.0, quality_scale=0.0,
-                          magnitude_scale=0.0):
+                          magnitude_scale=0.0, peer=None):
         """The planner-facing step (mgb_sample_score_best): draw + score + arg-min in one launch and get
         (best_cost, best_global_index, winning latent vector as float64 numpy [D]) back with one copy and one
         synchronisation.  What `_get_best_fit_sample_using_gmm` needs, nothing else."""
@@ -626,10 +644,13 @@ class DeviceConstraints(object):
         counts = np.ascontiguousarray(counts, dtype=np.int64)
         cost, idx = C.c_float(), C.c_int64()
         row = np.empty(dm.D, dtype=np.float32)
+        desc = peer.next_desc() if peer is not None else None     # world > 1: the exchange runs in the kernel's epilogue
         with _torch().cuda.device(dm.device):
-            _lib.check(self.lib.mgb_sample_score_best(dm.handle, self.handle, int(n), int(index_base), counts.ctypes.data_as(C.POINTER(C.c_int64)),
-                                                      C.c_uint64(int(seed) & 0xFFFFFFFFFFFFFFFF), float(error_scale), float(quality_scale),
-                                                      float(magnitude_scale), C.byref(cost), C.byref(idx), C.c_void_p(row.ctypes.data), dm._stream()))
+            _lib.check(self.lib.mgb_sample_score_best_sharded(dm.handle, self.handle, int(n), int(index_base),
+                                                              counts.ctypes.data_as(C.POINTER(C.c_int64)), C.c_uint64(int(seed) & 0xFFFFFFFFFFFFFFFF),
+                                                              float(error_scale), float(quality_scale), float(magnitude_scale),
+                                                              C.byref(desc) if desc is not None else None, C.byref(cost), C.byref(idx),
+                                                              C.c_void_p(row.ctypes.data), dm._stream()))
         return float(cost.value), int(idx.value), row.astype(np.float64)
 
     # -- K9 / K10: residual vectors and the local optimiser ------------------------------------

@@ -185,19 +185,19 @@ class MotionPrimitiveGenerator(object):
             mp_constraints.evaluations += n
             return best
         base, n_mine = sharding.shard_range(n, rank, world)
+        peer = sharding.peer_exchange(dm.torch_device)
+        if peer is not None:
+            # one launch per rank: the CTA that folds this rank's minima exchanges the 16-byte record with the peers over NVLink
+            # and re-draws the job-wide winner (every rank gets the same row)
+            min_error, best_idx, best = dc.sample_score_best(n_mine, seed=seed, counts=counts, n_total=n, index_base=base, error_scale=error_scale,
+                                                             quality_scale=quality_scale, magnitude_scale=magnitude_scale, peer=peer)
+            peer.check()
+            mp_constraints.min_error = min_error
+            mp_constraints.evaluations += n
+            return best
         res = dc.sample_score(n_mine, seed=seed, counts=counts, n_total=n, index_base=base, k=1,
                               error_scale=error_scale, quality_scale=quality_scale, magnitude_scale=magnitude_scale)
-        peer = sharding.peer_exchange(dm.torch_device) if world > 1 else None
-        if peer is not None:
-            # per-rank bests exchanged and reduced on the device over NVLink peer memory (mgb_exchange_best)
-            oc, oi = peer.exchange(res["best_cost"], res["best_idx"])
-            best_idx, min_error = int(oi.item()), float(oc.item())
-            peer.check()
-        else:
-            best_idx = int(res["best_idx"][0].item())
-            min_error = float(res["best_cost"][0].item())
-            if world > 1:
-                min_error, best_idx = sharding.exchange_best(min_error, best_idx, device=dm.torch_device)
+        min_error, best_idx = sharding.exchange_best(float(res["best_cost"][0].item()), int(res["best_idx"][0].item()), device=dm.torch_device)
         mp_constraints.min_error = min_error
         mp_constraints.evaluations += n
         best = dm.sample(1, seed=seed, index_base=best_idx, counts=counts, n_total=n)

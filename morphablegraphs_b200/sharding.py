@@ -119,6 +119,20 @@ class PeerExchange(object):
                                                   p(self.err), C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)))
         return self.out_cost, self.out_idx
 
+    def next_desc(self, spin_limit=0):
+        """mgb_exchange_desc of the NEXT step, for the entries that run the exchange inside the score kernel's epilogue
+        (mgb_sample_score_sharded / mgb_sample_score_best_sharded): advances the shared step counter exactly like
+        `exchange` does, so the two forms may be mixed as long as every rank makes the same sequence of calls."""
+        from . import _lib
+        self.seq += 1
+        if self.seq >= 2 ** 32:
+            self.seq = 2
+        d = _lib.ExchangeDesc()
+        d.d_peer_slots = self.peer_ptrs.data_ptr()
+        d.rank, d.world, d.seq, d.spin_limit = self.rank, self.world, self.seq, int(spin_limit)
+        d.d_err = self.err.data_ptr()
+        return d
+
     def check(self):
         """Synchronising: raises if a peer's record never arrived."""
         e = int(self.err.item())

@@ -117,3 +117,27 @@ def heading_degrees(skeleton, frame):
     m = skeleton.nodes[skeleton.aligning_root_node].get_global_matrix(frame)[:3, :3]
     p = np.dot(m, np.asarray(skeleton.aligning_root_dir, dtype=np.float64))
     return float(np.degrees(np.arctan2(p[0], p[2])))
+
+
+def align_frames(skeleton, new_frames, prev_frames):
+    """The chosen motion brought into the frame of the walk so far - anim_utils `align_quaternion_frames` with
+    `prev_frames` given (call sites motion_primitive_constraints.py:113, graph_walk.py; semantics SURVEY.md Appendix A,
+    in-tree near-copy mg_state_planner.py:92-107): rotate about +y by the heading difference between the last previous
+    frame and the first new frame, then translate in x / z so that the first new root lands on the last previous root.
+    The same transform the device applies to every candidate inside the score kernels (OP_ALIGN)."""
+    new_frames = np.array(new_frames, dtype=np.float64)
+    last = np.asarray(prev_frames[-1], dtype=np.float64)
+    ang = np.radians(heading_degrees(skeleton, last) - heading_degrees(skeleton, new_frames[0]))
+    ang = (ang + np.pi) % (2.0 * np.pi) - np.pi
+    c, s = np.cos(ang), np.sin(ang)
+    x, z = new_frames[:, 0].copy(), new_frames[:, 2].copy()
+    rx, rz = c * x + s * z, -s * x + c * z
+    new_frames[:, 0] = rx + (last[0] - rx[0])
+    new_frames[:, 2] = rz + (last[2] - rz[0])
+    qw, qy = np.cos(0.5 * ang), np.sin(0.5 * ang)      # quaternion_about_axis(ang, +y) (x) root quaternion
+    w0, x0, y0, z0 = (new_frames[:, 3 + i].copy() for i in range(4))
+    new_frames[:, 3] = qw * w0 - qy * y0
+    new_frames[:, 4] = qw * x0 + qy * z0
+    new_frames[:, 5] = qw * y0 + qy * w0
+    new_frames[:, 6] = qw * z0 - qy * x0
+    return new_frames

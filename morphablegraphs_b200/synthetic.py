@@ -183,7 +183,7 @@ def cubic_knots(n_frames, n_basis):
 
 
 def make_model_json(shape="S", seed=SEED_MODEL, translation_maxima=(1.0, 1.0, 1.0), name=None,
-                    animated_joints=None):
+                    animated_joints=None, root_travel=60.0):
     """Random-init motion primitive in the legacy JSON layout."""
     cfg = SHAPES[shape] if isinstance(shape, str) else dict(shape)
     F, J, K, Kt, G = cfg["n_frames"], cfg["n_joints"], cfg["n_spatial"], cfg["n_time"], cfg["n_gmm"]
@@ -198,7 +198,7 @@ def make_model_json(shape="S", seed=SEED_MODEL, translation_maxima=(1.0, 1.0, 1.
     tm = np.asarray(translation_maxima, dtype=np.float64)
     mean[:, 0] = 0.0
     mean[:, 1] = 90.0 / tm[1]
-    mean[:, 2] = np.linspace(0.0, 60.0, Nb) / tm[2]
+    mean[:, 2] = np.linspace(0.0, root_travel, Nb) / tm[2]
     quats = np.zeros((Nb, J, 4))
     quats[..., 0] = 1.0
     quats += rng.normal(0.0, 0.1, (Nb, J, 4))
@@ -274,3 +274,67 @@ def build_constraints(factory, skeleton, specs, trajectories=None):
                 desc["trajectory"] = ArcLengthTable(t["points"], t["step"], t.get("last_control_point"))
         out.append(factory[sp["class"]](skeleton, desc, sp["precision"], sp["weight"]))
     return out
+
+
+# ---------------------------------------------------------------------------
+# BASELINE config 3: a synthetic walk / pick / carry / place graph
+# ---------------------------------------------------------------------------
+LOCOMOTION_NODES = ["beginLeftStance", "beginRightStance", "leftStance", "rightStance", "endLeftStance", "endRightStance"]
+STEP_LENGTH = 60.0     # root travel of one synthetic step primitive (make_model_json)
+
+
+def make_graph_data(shape="S", seed=SEED_MODEL):
+    """The dictionary `ZipReader.get_graph_data` returns (reference utilities/zip_io.py:64-95) for a synthetic graph with the
+    actions of examples/example_input.json: `walk` and `carryRight` with the stance primitives of
+    motion_primitive_grounding.py:45-99, `pickRight` / `placeRight` as single-primitive actions; every node an S-shaped
+    random-init model with its own seed; meta information with start_states / end_states (action_meta_info.py:58-63) and the
+    keyframe labels start_contact / end_contact (examples/example_input.json:39,44,85,90)."""
+    cfg = SHAPES[shape]
+    F = cfg["n_frames"]
+    sub = collections.OrderedDict()
+    k = 0
+    for action in ("walk", "carryRight"):
+        nodes = collections.OrderedDict()
+        for mp in LOCOMOTION_NODES:
+            mm = make_model_json(shape, seed=seed + 17 * k, name="%s_%s" % (action, mp))
+            mm["keyframes"] = {"contact": F - 1}
+            nodes[mp] = {"name": "%s_%s" % (action, mp), "mm": mm}
+            k += 1
+        sub[action] = {"name": action, "nodes": nodes,
+                       "info": {"start_states": ["beginLeftStance", "beginRightStance"], "end_states": ["endLeftStance", "endRightStance"]}}
+    for action in ("pickRight", "placeRight"):
+        mm = make_model_json(shape, seed=seed + 17 * k, name="%s_reach" % action, root_travel=0.0)
+        mm["keyframes"] = {"start_contact": F // 2, "end_contact": F // 2}
+        sub[action] = {"name": action, "nodes": collections.OrderedDict([("reach", {"name": "%s_reach" % action, "mm": mm})]),
+                       "info": {"start_states": ["reach"], "end_states": ["reach"]}}
+        k += 1
+    transitions = collections.OrderedDict()
+    for action in ("walk", "carryRight"):
+        t = transitions
+        t["%s:beginLeftStance" % action] = ["%s:rightStance" % action, "%s:endRightStance" % action]
+        t["%s:beginRightStance" % action] = ["%s:leftStance" % action, "%s:endLeftStance" % action]
+        t["%s:leftStance" % action] = ["%s:rightStance" % action, "%s:endRightStance" % action]
+        t["%s:rightStance" % action] = ["%s:leftStance" % action, "%s:endLeftStance" % action]
+        nxt = "pickRight:reach" if action == "walk" else "placeRight:reach"
+        t["%s:endLeftStance" % action] = [nxt]
+        t["%s:endRightStance" % action] = [nxt]
+    transitions["pickRight:reach"] = ["carryRight:beginLeftStance", "carryRight:beginRightStance"]
+    transitions["placeRight:reach"] = ["walk:beginLeftStance", "walk:beginRightStance"]
+    return {"formatVersion": "4.0", "transitions": transitions, "startNode": ["walk", "beginLeftStance"],
+            "skeleton": make_skeleton_desc(cfg["n_joints"]), "subgraphs": sub}
+
+
+# reference examples/example_input.json, abridged to what graph_synthesis.read_input reads (positions verbatim)
+EXAMPLE_INPUT = {
+    "startPose": {"position": [530.110290527344, 268.851318359375, 0.0], "orientation": [0.0, 0.0, 91.4786896560991]},
+    "elementaryActions": [
+        {"action": "walk", "constraints": [{"joint": "Hips", "trajectoryConstraints": [
+            {"position": [530.110290527344, 268.851318359375, None]}, {"position": [355.0, 255.0, None]}, {"position": [195.0, 255.0, None]},
+            {"position": [147.011029052734, 206.885131835938, None]}, {"position": [60.0, 200.0, None]}, {"position": [30.0, 200.0, None]}]}]},
+        {"action": "pickRight", "constraints": [{"joint": "RightHand", "keyframeConstraints": [
+            {"position": [-30.0000009536743, 200.0, 130.0], "semanticAnnotation": {"start_contact": True}}]}]},
+        {"action": "carryRight", "constraints": [{"joint": "Hips", "trajectoryConstraints": [
+            {"position": [30.0000000000001, 200.0, None]}, {"position": [35.0, 215.0, None]}, {"position": [105.0, 285.0, None]},
+            {"position": [108.39608, 436.52072, None]}, {"position": [161.5512, 462.8008, None]}, {"position": [191.5512, 462.8008, None]}]}]},
+        {"action": "placeRight", "constraints": [{"joint": "RightHand", "keyframeConstraints": [
+            {"position": [251.5512, 462.8008, 129.296196185303], "semanticAnnotation": {"end_contact": True}}]}]}]}

@@ -321,6 +321,61 @@ def run_local_case(ns, shape="S", n_samples=64, seed=2031):
     return out
 
 
+def run_config3_case(ns, n_samples=10000, seed=4100, max_steps=None):
+    """BASELINE config 3 at the parity size SURVEY.md 8(d) row 3 states: the action list of examples/example_input.json
+    (walk / pickRight / carryRight / placeRight) over the synthetic graph, every motion-primitive step decided by the
+    reference's OWN generator loop (motion_primitive_generator.py:230-261) on 10 000 candidates drawn by the numpy
+    restatement of sklearn's sampler from a per-step seed (oracle.np_oracle.gmm_sample: the test redraws them), candidates
+    aligned to the walk so far (non-local path).  The step list and the constraint specs come from the product's driver
+    (morphablegraphs_b200/graph_synthesis.py) - they are INPUTS; decisions, costs and the frames carried to the next
+    step are the reference's."""
+    from anim_utils.animation_data.motion_concatenation import align_quaternion_frames
+    from morphablegraphs_b200 import graph_synthesis as GS
+    from morphablegraphs_b200.motion_state_graph import MotionStateGraphLoader
+    from oracle import np_oracle as O
+    gd = syn.make_graph_data()
+    ld = MotionStateGraphLoader()
+    ld.set_graph_data(gd)
+    graph = ld.build()                                            # product graph: planning only
+    skeleton = refload.make_skeleton(gd["skeleton"])              # reference-side skeleton (stand-in for anim_utils)
+    ref_nodes = {}
+    for action, entry in gd["subgraphs"].items():
+        for mp, nd in entry["nodes"].items():
+            ref_nodes[(action, mp)] = refload.make_graph_node(ns, nd["mm"], name=mp, action=action)
+    plan_input = GS.read_input(os.path.join(refload.SOURCE_ROOT, "examples", "example_input.json"))
+    steps = GS.plan_steps(graph, plan_input)
+    if max_steps:
+        steps = steps[:max_steps]
+    prev = GS.initial_frames(graph, plan_input, steps[0]["node_key"])
+    gen = ns.motion_primitive_generator.MotionPrimitiveGenerator.__new__(ns.motion_primitive_generator.MotionPrimitiveGenerator)
+    gen.objective = ns.objective_functions.obj_spatial_error_sum
+    out = {"n_steps": np.array(len(steps)), "n_samples": np.array(n_samples), "node_keys_json": np.array(json.dumps([list(s_["node_key"]) for s_ in steps]))}
+    for i, step in enumerate(steps):
+        node = ref_nodes[step["node_key"]]
+        specs = GS.step_specs(graph, step, prev)
+        mpc = build_mp_constraints(ns, skeleton, specs, is_local=False)
+        S, _ = O.gmm_sample(O.ModelArrays(node), n_samples, np.random.RandomState(seed + i))
+        costs = np.zeros(n_samples)
+        with _quiet():
+            for k, s_ in enumerate(S):
+                costs[k] = gen.objective(s_, (node, mpc, prev))
+            best, min_error = gen.evaluate_samples_using_constraints(S, node, mpc, prev)
+            frames = node.back_project(best, use_time_parameters=False).get_motion_vector()
+        frames = np.asarray(align_quaternion_frames(skeleton, skeleton.aligning_root_node, frames, prev, None))
+        bi = int(np.where((S == best).all(axis=1))[0][0])
+        out["step%d_seed" % i] = np.array(seed + i)
+        out["step%d_specs_json" % i] = np.array(json.dumps(specs))
+        out["step%d_prev_frames" % i] = np.asarray(prev)
+        out["step%d_costs" % i] = costs.astype(np.float32)
+        out["step%d_best_idx" % i] = np.array(bi)
+        out["step%d_best_sample" % i] = S[bi]
+        out["step%d_min_error" % i] = np.array(min_error)
+        out["step%d_last_frames" % i] = frames[-8:]
+        print("config3 step", i, step["node_key"], "best", bi, "min_error %.4f" % min_error, flush=True)
+        prev = frames[-8:]
+    return out
+
+
 def run_resid_case(ns, name_of_set="mixed", shape="S", n_samples=24, seed=2041, n_opt=3):
     """f1: the reference's own residual-vector objective (motion_primitive_constraints.py:124-146,
     objective_functions.py:239-267) on reference-drawn samples, and the reference's own LeastSquares
@@ -557,6 +612,10 @@ def main():
         np.savez_compressed(os.path.join(GOLDEN_DIR, "s_walk.npz"), **out)
         print("s_walk", [int(out["step%d_best_idx" % i]) for i in range(len(out["order"]))],
               [float(out["step%d_min_error" % i]) for i in range(len(out["order"]))])
+        return 0
+    if "--only-config3" in sys.argv:
+        out = run_config3_case(ns)
+        np.savez_compressed(os.path.join(GOLDEN_DIR, "s_config3.npz"), **out)
         return 0
     if "--only-resid" in sys.argv:
         out = run_resid_case(ns)

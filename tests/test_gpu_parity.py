@@ -803,3 +803,101 @@ def test_generator_runs_the_device_optimiser():
     s1 = opt.generate_constrained_sample(c.node, mpc)
     assert s1.shape == s0.shape and not np.array_equal(s0, s1)
     assert mpc.min_error < e0
+
+
+# ---------------------------------------------------------------------------
+# config 3 (J1): the example_input.json action list over the synthetic graph, loaded from the archive format
+# ---------------------------------------------------------------------------
+@pytest.fixture(scope="module")
+def config3_graph():
+    import io
+    from morphablegraphs_b200 import synthetic as syn
+    from morphablegraphs_b200.motion_state_graph import MotionStateGraphLoader, graph_to_bytes
+    ld = MotionStateGraphLoader()
+    ld.set_data_source(io.BytesIO(graph_to_bytes(syn.make_graph_data())))     # through the zip reader (f3)
+    g = ld.build(resident=True)
+    assert len(g.make_resident()) == 14
+    return g
+
+
+def test_config3_steps_match_the_reference_decisions(config3_graph):
+    """All 17 motion-primitive steps of examples/example_input.json (walk, pickRight, carryRight, placeRight): the
+    reference's own generator loop chose among 10 000 candidates per step (tests/golden/s_config3.npz, candidates redrawn
+    here from the stored seed by the oracle's restatement of sklearn's sampler); the engine must take the same decision
+    at every step and agree on all 170 000 costs."""
+    import json
+    from oracle import np_oracle as O
+    from morphablegraphs_b200 import MotionPrimitiveGenerator, graph_synthesis as GS
+    from tests.common import load_golden
+    g = load_golden("s_config3")
+    graph = config3_graph
+    keys = [tuple(k) for k in json.loads(str(g["node_keys_json"]))]
+    gen = MotionPrimitiveGenerator(None, {"n_random_samples": int(g["n_samples"]), "use_local_coordinates": False}, skeleton=graph.skeleton, seed=1)
+    for i, key in enumerate(keys):
+        node = graph.nodes[key]
+        S, _ = O.gmm_sample(O.ModelArrays(node), int(g["n_samples"]), np.random.RandomState(int(g["step%d_seed" % i])))
+        assert np.array_equal(S[int(g["step%d_best_idx" % i])], g["step%d_best_sample" % i])      # the redraw is the golden's draw
+        mpc = GS.build_constraints(graph, json.loads(str(g["step%d_specs_json" % i])))
+        prev = g["step%d_prev_frames" % i]
+        best, err = gen.evaluate_samples_using_constraints(S, node, mpc, prev)
+        ref = g["step%d_costs" % i].astype(np.float64)
+        bi = int(np.where((S == best).all(axis=1))[0][0])
+        _check_argmin(ref, bi, err)
+        assert abs(err - float(g["step%d_min_error" % i])) < RTOL * max(1.0, float(g["step%d_min_error" % i]))
+        from morphablegraphs_b200.objective_functions import _device_constraints
+        cost = _device_constraints(node, mpc, prev).score_host(np.ascontiguousarray(S), k=0, return_cost=True)["cost"]
+        assert rel_err(cost, ref).max() < 2 * RTOL        # the golden stores float32 costs
+
+
+def test_config3_synthesis_runs_end_to_end(config3_graph):
+    """The whole action list synthesised on the device (candidates drawn in-kernel, 100 000 per step): 17 steps, every step
+    starts where the previous one ended and ends near its goal."""
+    from morphablegraphs_b200 import MotionPrimitiveGenerator, graph_synthesis as GS
+    from tests.test_graph_cpu import EXAMPLE_INPUT
+    graph = config3_graph
+    gen = MotionPrimitiveGenerator(None, {"n_random_samples": 100000, "use_local_coordinates": False}, skeleton=graph.skeleton, seed=7)
+    out = GS.GraphWalkSynthesizer(graph, gen).run(EXAMPLE_INPUT)
+    assert len(out) == 17
+    for rec in out:
+        assert np.isfinite(rec["min_error"]) and rec["parameters"].shape == (13,)
+        assert np.abs(rec["last_frames"][0][:3]).max() < 1e4
+    for a, b in zip(out[:-1], out[1:]):
+        assert np.array_equal(a["last_frames"], b["prev_frames"])
+
+
+def test_exchange_fused_into_the_score_kernel():
+    """mgb_sample_score_sharded: several "ranks" of one process (own streams, own handles and workspaces) score their shard of
+    one job; the CTA that folds a rank's minima exchanges the record with the peers inside the kernel.  Every rank ends with
+    the winner of the single-GPU run of the whole job, for the register-resident kernel (S) and the tensor-core kernel (L)."""
+    import torch
+    from morphablegraphs_b200 import engine, sharding, _lib
+    lib = _lib.load()
+    dev = torch.device("cuda", 0)
+    for name, n, qs in (("s_config1", 60001, 0.0), ("l_cfg4", 3000, 0.1)):
+        c = Case(name)
+        dm0 = engine.DeviceModel(c.node, c.skeleton)
+        dc0 = engine.DeviceConstraints(dm0, c.constraints, c.prev_frames)
+        seed = 13
+        counts = dm0.component_counts(n, seed)
+        want_cost, want_idx, _ = dc0.sample_score_best(n, seed=seed, counts=counts, quality_scale=qs)
+        for world in (2, 4):
+            nbytes = int(lib.mgb_exchange_slot_bytes(world))
+            slots = [torch.zeros(nbytes // 4, dtype=torch.int32, device=dev) for _ in range(world)]
+            ptrs = [int(t.data_ptr()) for t in slots]
+            peers = [sharding.PeerExchange(dev, slots=slots[r], peer_ptrs=ptrs, rank=r, world=world) for r in range(world)]
+            dms = [engine.DeviceModel(c.node, c.skeleton) for _ in range(world)]
+            dcs = [engine.DeviceConstraints(dms[r], c.constraints, c.prev_frames) for r in range(world)]
+            streams = [torch.cuda.Stream(dev) for _ in range(world)]
+            torch.cuda.synchronize()
+            for step in range(2):
+                outs = []
+                before = engine.launch_count()
+                for r in range(world):
+                    base, n_r = sharding.shard_range(n, r, world)
+                    with torch.cuda.stream(streams[r]):
+                        outs.append(dcs[r].sample_score_sharded(n_r, peers[r], seed=seed, counts=counts, n_total=n, index_base=base, quality_scale=qs))
+                torch.cuda.synchronize()
+                assert engine.launch_count() - before == world          # one launch per rank and step
+                for r in range(world):
+                    peers[r].check()
+                    assert float(outs[r][0].item()) == want_cost and int(outs[r][1].item()) == want_idx, (name, world, r)

@@ -19,26 +19,29 @@ def main():
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     rank, world = dist.get_rank(), dist.get_world_size()
-    node, skeleton, mpc, prev = bench.build_case("S1M")
-    n = 1_000_003
-    gen = MotionPrimitiveGenerator(None, {"n_random_samples": n}, skeleton=skeleton, seed=11)
-    s_dist = gen._get_best_fit_sample_using_gmm(node, mpc)
-    e_dist = mpc.min_error
-    # the same job on this rank alone
-    dm = engine.DeviceModel(node, skeleton, local)
-    dc = engine.DeviceConstraints(dm, mpc, prev)
-    seed = int(np.random.RandomState(11).randint(0, 2 ** 31 - 1))
-    counts = dm.component_counts(n, seed)
-    res = dc.sample_score(n, seed=seed, counts=counts, n_total=n, index_base=0, k=1)
-    idx = int(res["best_idx"][0]); e_one = float(res["best_cost"][0])
-    s_one = dm.sample(1, seed=seed, index_base=idx, counts=counts, n_total=n)[0].cpu().numpy().astype(np.float64)
-    ok = np.array_equal(s_dist, s_one) and e_dist == e_one
-    # a generator built WITHOUT a seed: rank 0's stream is broadcast once, so every rank still returns the same sample
-    gen_u = MotionPrimitiveGenerator(None, {"n_random_samples": n}, skeleton=skeleton, seed=None)
-    s_u = gen_u._get_best_fit_sample_using_gmm(node, mpc)
-    got = [None] * world
-    dist.all_gather_object(got, (s_u.tolist(), float(mpc.min_error)))
-    ok = ok and all(g == got[0] for g in got)
+    ok, e_dist, idx = True, 0.0, -1
+    for wl, n, qs in (("S1M", 1_000_003, 0.0), ("L4M", 200_001, 0.1)):
+        from morphablegraphs_b200.objective_functions import ObjSpatialErrorAndNaturalness
+        node, skeleton, mpc, prev = bench.build_case(wl)
+        gen = MotionPrimitiveGenerator(None, {"n_random_samples": n, "use_local_coordinates": prev is None}, skeleton=skeleton, seed=11)
+        if qs:
+            gen.objective = ObjSpatialErrorAndNaturalness(1.0, qs)
+        # sharded: one launch per rank, the exchange of the per-rank best inside the kernel's epilogue
+        s_dist = gen._get_best_fit_sample_using_gmm(node, mpc, prev_frames=prev)
+        e_dist = mpc.min_error
+        # the same job on this rank alone
+        dm = engine.DeviceModel(node, skeleton, local)
+        dc = engine.DeviceConstraints(dm, mpc, prev)
+        seed = int(np.random.RandomState(11).randint(0, 2 ** 31 - 1))
+        counts = dm.component_counts(n, seed)
+        e_one, idx, s_one = dc.sample_score_best(n, seed=seed, counts=counts, quality_scale=qs)
+        ok = ok and np.array_equal(s_dist, s_one) and e_dist == e_one
+        # a generator built WITHOUT a seed: rank 0's stream is broadcast once, so every rank still returns the same sample
+        gen_u = MotionPrimitiveGenerator(None, {"n_random_samples": n, "use_local_coordinates": prev is None}, skeleton=skeleton, seed=None)
+        s_u = gen_u._get_best_fit_sample_using_gmm(node, mpc, prev_frames=prev)
+        got = [None] * world
+        dist.all_gather_object(got, (s_u.tolist(), float(mpc.min_error)))
+        ok = ok and all(g == got[0] for g in got)
     flags = [None] * world
     dist.all_gather_object(flags, (bool(ok), e_dist, idx))
     if rank == 0:

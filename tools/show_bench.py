@@ -24,5 +24,8 @@ def show(name, x):
 
 show(d["config"]["workload"], d)
 for k, v in d.get("workloads", {}).items():
-    show(k, v)
+    if "roofline" in v:
+        show(k, v)
+    else:
+        print("%-11s value %.4g  %s" % (k, v["value"], {a: b for a, b in v.items() if a not in ("value", "description", "unit", "timing")}))
 print(d.get("clocks"))
