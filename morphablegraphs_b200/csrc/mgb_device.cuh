@@ -1,5 +1,5 @@
 // Device-side building blocks shared by the kernels of libmgb200.so:
-// Philox4x32-10 + Box-Muller GMM sampling of one latent row, quaternion-form
+// Philox4x32 + Box-Muller GMM sampling of one latent row, quaternion-form
 // forward kinematics, 1-D TMA bulk copies with mbarrier completion.
 #pragma once
 #include <cuda_runtime.h>
@@ -8,12 +8,18 @@
 #define MGB_QUAT_EPS 8.881784197001252e-16f /* 4 * DBL_EPSILON: transformations.quaternion_matrix returns identity below it */
 
 // ---------------------------------------------------------------------------
-// Philox4x32-10 (Salmon et al. 2011); counter = (global index lo, hi, block, tag), key = seed
+// Philox4x32 (Salmon et al. 2011); counter = (global index lo, hi, block, tag), key = seed
 // ---------------------------------------------------------------------------
-__device__ __forceinline__ uint4 mgb_philox4x32_10(uint4 ctr, uint2 key) {
+// Rounds: 7 - the smallest count for which Salmon et al. report Philox4x32 to pass BigCrush ("Crush-resistant", SC'11 table 2);
+// 10 is the library default with a safety margin.  The draws feed a Monte-Carlo search whose candidates are checked
+// distributionally (tests), and Philox is ~25 % of the S step kernel's instruction stream.
+#ifndef MGB_PHILOX_ROUNDS
+#define MGB_PHILOX_ROUNDS 7
+#endif
+__device__ __forceinline__ uint4 mgb_philox4x32(uint4 ctr, uint2 key) {
     const unsigned int M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
 #pragma unroll
-    for (int r = 0; r < 10; ++r) {
+    for (int r = 0; r < MGB_PHILOX_ROUNDS; ++r) {
         const unsigned int hi0 = __umulhi(M0, ctr.x), lo0 = M0 * ctr.x;
         const unsigned int hi1 = __umulhi(M1, ctr.z), lo1 = M1 * ctr.z;
         ctr = make_uint4(hi1 ^ ctr.y ^ key.x, lo1, hi0 ^ ctr.w ^ key.y, lo0);
@@ -35,7 +41,7 @@ __device__ __forceinline__ float mgb_sqrt_approx(float x) {
 
 // four standard normals of global index gi, block b (Box-Muller on one Philox call)
 __device__ __forceinline__ void mgb_normal4(unsigned long long gi, unsigned int b, uint2 key, float z[4]) {
-    const uint4 r = mgb_philox4x32_10(make_uint4((unsigned int)gi, (unsigned int)(gi >> 32), b, 0x6d67u), key);
+    const uint4 r = mgb_philox4x32(make_uint4((unsigned int)gi, (unsigned int)(gi >> 32), b, 0x6d67u), key);
     // radius: sqrt.approx (one MUFU, <= 2 ulp) instead of the IEEE sqrtf sequence - the draw is a random
     // number, and both users of this function (mgb_sample, the fused kernels) share it bit for bit
     const float r0 = mgb_sqrt_approx(-2.f * __logf(mgb_u01(r.x))), r1 = mgb_sqrt_approx(-2.f * __logf(mgb_u01(r.z)));

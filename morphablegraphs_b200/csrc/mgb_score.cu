@@ -226,7 +226,10 @@ __device__ __forceinline__ void score_body(const ScoreParams& p, const int cta, 
                 const int g = g_hint;
                 const uint2 key = make_uint2((unsigned int)p.seed, (unsigned int)(p.seed >> 32));
                 if (NREG > 0) {
-                    mgb_sample_row_reg<NR>(reinterpret_cast<const float4*>(chol + (size_t)g * D * p.LS), p.LS, mus + (size_t)g * D, D, gi, key, s[c]);
+                    // without a density or magnitude term only the K spatial entries of s are ever read: rows >= K of the
+                    // Cholesky product (and the normals only they need) are dead - the entries that ARE computed keep their bits
+                    const int d_need = (p.quality_scale == 0.f && p.magnitude_scale == 0.f) ? p.K : D;
+                    mgb_sample_row_reg<NR>(reinterpret_cast<const float4*>(chol + (size_t)g * D * p.LS), p.LS, mus + (size_t)g * D, d_need, gi, key, s[c]);
                 } else {
                     mgb_sample_row_mem(chol + (size_t)g * D * p.LS, p.LS, mus + (size_t)g * D, D, gi, key, myrow[c]);
                 }
@@ -428,8 +431,13 @@ __device__ __forceinline__ void score_body(const ScoreParams& p, const int cta, 
     }
 }
 
+// 3 resident CTAs per SM (<= 85 registers): measured on B200 at S1M - uncapped the compiler takes more registers and the step
+// is 93 us, capped to 3 CTAs 65 us, to 4 CTAs (<= 64 registers) 72 us (profiles/r02_o)
+#ifndef MGB_SCORE_MIN_BLOCKS
+#define MGB_SCORE_MIN_BLOCKS 3
+#endif
 template <int NREG, int CPT, int MODE, typename SIn>
-__global__ void __launch_bounds__(MGB_BLOCK) mgb_score_kernel(const __grid_constant__ ScoreParams p) {
+__global__ void __launch_bounds__(MGB_BLOCK, MGB_SCORE_MIN_BLOCKS) mgb_score_kernel(const __grid_constant__ ScoreParams p) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     score_body<NREG, CPT, MODE, SIn>(p, (int)blockIdx.x, (int)gridDim.x, smem_raw);
 }

@@ -26,7 +26,7 @@ int sm_count() {
 
 #define SAMPLE_BLOCK 256
 
-// K1.  One thread draws one candidate (Philox4x32-10 keyed by the global index, Box-Muller,
+// K1.  One thread draws one candidate (Philox4x32 keyed by the global index, Box-Muller,
 // s = mu_g + L_g z with the Cholesky rows broadcast from shared memory as float4), writes its
 // row into a densely packed shared-memory tile [SAMPLE_BLOCK][D]; the tile (one contiguous
 // run of global memory) leaves with ONE TMA bulk store, double-buffered so the store of

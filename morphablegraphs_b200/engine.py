@@ -134,6 +134,9 @@ def lib_spline_basis(knots, t):
 # ---------------------------------------------------------------------------
 # model
 # ---------------------------------------------------------------------------
+_BASIS_CACHE = {}
+
+
 class DeviceModel(object):
     """One motion primitive + skeleton resident on one GPU (mgb_model handle)."""
 
@@ -254,13 +257,17 @@ class DeviceModel(object):
         times = np.ascontiguousarray(np.atleast_1d(times), dtype=np.float64)
         spans = np.zeros(len(times), dtype=np.int32)
         weights = np.zeros((len(times), 4), dtype=np.float64)
-        cache = self.__dict__.get("_basis_cache")
+        # shared by every model with the same knot vector (the primitives of a graph usually share it)
+        kk = self.__dict__.get("_knots_key")
+        if kk is None:
+            kk = self.__dict__["_knots_key"] = self.knots.tobytes()
+        cache = _BASIS_CACHE.get(kk)
         if cache is None:
-            cache = self.__dict__["_basis_cache"] = {}
+            cache = _BASIS_CACHE[kk] = {}
         for i, t in enumerate(times):
             key = float(t)
             hit = cache.get(key)
-            if hit is None:         # the same FITPACK call the reference makes, once per distinct time of this model
+            if hit is None:         # the same FITPACK call the reference makes, once per distinct (knot vector, time)
                 if len(cache) > 4096:
                     cache.clear()
                 hit = cache[key] = spline_basis(self.knots, key)
