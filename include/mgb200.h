@@ -286,6 +286,12 @@ typedef struct {
 int mgb_sample_score_multi(const mgb_option* options, int32_t n_options, float* h_best_cost,
                            int64_t* h_best_idx, float* h_best_rows, int32_t row_stride, void* stream);
 
+/* K11: d_C[d, d] (float64, row-major) += (X - mean)^T (X - mean) for the UPPER triangle (i <= j) of the feature covariance,
+ * X [n, d] float32 with row stride ld, mean [d] or NULL: the covariance of sklearn's PCA as the reference's
+ * map_motions_to_euclidean_pca calls it (space_partitioning/features.py:125-130), as a 3xTF32 tcgen05 contraction
+ * (2 n d^2 flop; 4.5 TFLOP at n = 1M, d = 1500).  The caller mirrors the triangle and divides by n - 1. */
+int mgb_syrk_upper(const float* d_X, int64_t n, int32_t d, int32_t ld, const float* d_mean, double* d_C, void* stream);
+
 /* ---- residual vectors and the local optimiser --------------------------------------
  * K9: the weighted residual vector of every candidate, d_out[n, R] with R = mgb_constraints_n_residuals(c):
  * MotionPrimitiveConstraints.get_residual_vector (motion_primitive_constraints.py:124-146) - per constraint

@@ -125,6 +125,7 @@ SYMBOLS = {
     "mgb_sample_score_best_sharded": (C.c_int, [_vp, _vp, _i64, _i64, C.POINTER(C.c_int64), C.c_uint64, _f, _f, _f, C.POINTER(ExchangeDesc),
                                                 C.POINTER(C.c_float), C.POINTER(C.c_int64), _vp, _vp]),
     "mgb_sample_score_multi": (C.c_int, [C.POINTER(Option), _i32, _vp, _vp, _vp, _i32, _vp]),
+    "mgb_syrk_upper": (C.c_int, [_vp, _i64, _i32, _i32, _vp, _vp, _vp]),
     "mgb_constraints_n_residuals": (_i32, [_vp]),
     "mgb_residuals": (C.c_int, [_vp, _vp, _vp, _i64, _vp, _vp]),
     "mgb_lm_refine": (C.c_int, [_vp, _vp, _vp, _i32, _f, _f, _f, _i32, _vp, _vp, _vp]),

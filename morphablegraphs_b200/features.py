@@ -9,7 +9,9 @@ flattened to one row per sample and reduced by `sklearn.decomposition.PCA(n_comp
 
 Here the point clouds come from the staged kernels K2 -> K3 -> K4 chunk by chunk (the motion
 [M, F, P] is never held as a whole: 15.8 GB at M = 1M for the S model), the PCA is a covariance
-eigen-decomposition on the device.  Component SIGNS are sklearn's svd_flip convention in the reference
+eigen-decomposition on the device: the covariance (the 4.5 TFLOP part at M = 1M) by the hand-written tcgen05 kernel K11
+(csrc/mgb_syrk.cu), the small d x d symmetric eigen-decomposition by cuSOLVER in float64, the projection onto the k kept
+components by a library GEMM (2 M d k flop, bound by the one read of X).  Component SIGNS are sklearn's svd_flip convention in the reference
 and unspecified here; everything downstream (k-means on the features) only sees distances, which do
 not depend on them.
 """
@@ -60,12 +62,18 @@ def pca_by_variance(X, variance=0.95, sharded=False, group=None):
         dist.all_reduce(total, group=group)
         dist.all_reduce(colsum, group=group)
     mean = colsum / total
-    cov = torch.zeros((d, d), dtype=torch.float64, device=X.device)
+    # K11 (mgb_syrk_upper): the 2 M d^2 contraction on the tensor cores (3xTF32, float64 result), upper triangle
+    import ctypes as C
+    from . import _lib
+    lib = _lib.load()
+    mean32 = mean.float().contiguous()
+    assert X.dtype == torch.float32 and X.stride(1) == 1
+    upper = torch.zeros((d, d), dtype=torch.float64, device=X.device)
+    with torch.cuda.device(X.device):
+        _lib.check(lib.mgb_syrk_upper(C.c_void_p(X.data_ptr()), M, d, int(X.stride(0)), C.c_void_p(mean32.data_ptr()),
+                                      C.c_void_p(upper.data_ptr()), C.c_void_p(torch.cuda.current_stream(X.device).cuda_stream)))
+    cov = upper + upper.t() - torch.diag(torch.diagonal(upper))
     step = 131072
-    mean32 = mean.float()
-    for a in range(0, M, step):
-        Xc = X[a:a + step] - mean32
-        cov += (Xc.t() @ Xc).double()
     if sharded:
         dist.all_reduce(cov, group=group)
     cov /= max(float(total.item()) - 1.0, 1.0)

@@ -300,3 +300,29 @@ def test_kmeans_level_empty_and_frozen():
     r = engine.kmeans_level(X, 4, node, 2, 4, cent, tol=tol, max_iter=20, frozen=frozen)
     assert torch.equal(cent[0], seeds[0]) and not torch.equal(cent[1], seeds[1])
     assert int(r["counts"].sum()) == 2000
+
+
+@pytest.mark.parametrize("n,d,pad", [(5007, 300, 4), (130, 77, 0), (40000, 1500, 0)])
+def test_syrk_tensor_core_covariance(n, d, pad):
+    """K11 (mgb_syrk_upper, 3xTF32 on tcgen05) against float64 numpy: upper triangle of (X - mean)^T (X - mean), ragged
+    tiles (d not a multiple of 128 / 256), ragged sample count, a row stride larger than d; accumulates into C."""
+    import ctypes as C
+    import torch
+    from morphablegraphs_b200 import _lib
+    lib = _lib.load()
+    rng = np.random.RandomState(n)
+    Xh = (rng.normal(0.0, 30.0, (n, d + pad)) + rng.normal(0.0, 50.0, (1, d + pad))).astype(np.float32)
+    X = torch.as_tensor(Xh, device="cuda")
+    mean = X[:, :d].double().mean(dim=0).float().contiguous()
+    out = torch.full((d, d), 1.0, dtype=torch.float64, device="cuda")
+    _lib.check(lib.mgb_syrk_upper(C.c_void_p(X.data_ptr()), n, d, d + pad, C.c_void_p(mean.data_ptr()), C.c_void_p(out.data_ptr()),
+                                  C.c_void_p(torch.cuda.current_stream().cuda_stream)))
+    torch.cuda.synchronize()
+    Xc = Xh[:, :d].astype(np.float64) - mean.cpu().numpy().astype(np.float64)
+    want = Xc.T.dot(Xc)
+    got = out.cpu().numpy()
+    iu = np.triu_indices(d)
+    scale = np.sqrt(np.outer(np.diag(want), np.diag(want)))[iu]
+    assert (np.abs(got[iu] - 1.0 - want[iu]) / scale).max() < 2e-5
+    il = np.tril_indices(d, -1)
+    assert (got[il] == 1.0).all()          # the lower triangle is not touched

@@ -6,16 +6,7 @@ out=gpurun_out; mkdir -p $out
 timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > $out/${tag}_smoke.log 2>&1; echo "smoke rc=$?"; tail -1 $out/${tag}_smoke.log
 timeout 1500 python -m pytest tests -m gpu -x -q > $out/${tag}_pytest.log 2>&1; echo "pytest rc=$?"; tail -4 $out/${tag}_pytest.log
 timeout 900 python bench.py --steps 20 --warmup 5 > $out/${tag}_bench.json 2> $out/${tag}_bench.err; echo "bench rc=$?"; tail -3 $out/${tag}_bench.err
-python - <<PY
-import json
-d=json.load(open('$out/${tag}_bench.json'))
-def show(name,x):
-    print(name, 'value %.4g'%x['value'], 'ms %.4g'%x['ms_per_step'], 'roof %.3f'%x['roofline']['frac'], 'e2e %.4g'%x['e2e']['value'], 'gen ms %.4g'%x['e2e']['generator_call']['ms_per_step'], 'cpu', x.get('cpu_baseline',{}).get('value'), x.get('cpu_baseline',{}).get('kind'))
-    print('   ', {k:round(v['ms'],4) for k,v in x['kernels'].items()})
-show(d['config']['workload'], d)
-for k,v in d.get('workloads',{}).items(): show(k,v)
-print(d['clocks'])
-PY
+python tools/show_bench.py $out/${tag}_bench.json
 timeout 600 python bench.py --impl reference --steps 3 --warmup 1 > $out/${tag}_bench_ref.json 2> $out/${tag}_bench_ref.err; echo "bench ref rc=$?"; cut -c1-300 $out/${tag}_bench_ref.json
 if [ "$2" = "ncu" ]; then
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file $out/${tag}_launches.csv \

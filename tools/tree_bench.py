@@ -86,9 +86,21 @@ def main():
     if not a.no_features:
         Mf = min(M, 1_000_000)
         (clouds), t_cloud = wall(lambda: feat.map_samples_to_euclidean_space(dm, S[:Mf]))
+        (fp, ratio), t_pca_first = wall(lambda: feat.pca_by_variance(clouds))
         (fp, ratio), t_pca = wall(lambda: feat.pca_by_variance(clouds))
-        out["euclidean_features"] = {"samples": Mf, "point_cloud_seconds": t_cloud, "pca_seconds": t_pca, "n_components": int(fp.shape[1]),
-                                     "cloud_bytes": int(clouds.numel() * 4)}
+        # K11 alone: the covariance contraction on the tensor cores
+        import ctypes as C
+        from morphablegraphs_b200 import _lib
+        dcl = int(clouds.shape[1])
+        mean = clouds.mean(dim=0).contiguous()
+        up = torch.zeros((dcl, dcl), dtype=torch.float64, device=clouds.device)
+        ms_syrk = bench.timed(torch, lambda: _lib.check(_lib.load().mgb_syrk_upper(
+            C.c_void_p(clouds.data_ptr()), Mf, dcl, dcl, C.c_void_p(mean.data_ptr()), C.c_void_p(up.data_ptr()),
+            C.c_void_p(torch.cuda.current_stream().cuda_stream))), 3, flush)
+        out["euclidean_features"] = {"samples": Mf, "point_cloud_seconds": t_cloud, "pca_seconds": t_pca, "pca_first_call_seconds": t_pca_first,
+                                     "n_components": int(fp.shape[1]), "cloud_bytes": int(clouds.numel() * 4),
+                                     "K11_syrk": {"ms": ms_syrk, "d": dcl, "algorithmic_tflops": 2.0 * Mf * dcl * dcl / (ms_syrk * 1e-3) * 1e-12,
+                                                  "note": "2 n d^2 flop of the full covariance / time; 3xTF32 on tcgen05, upper triangle computed"}}
         del clouds
         opts = {"n_subdivisions": 4, "clustering_method": 0, "use_feature_mean": False}
         f_host = fp.cpu().numpy()
