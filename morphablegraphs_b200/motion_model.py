@@ -164,14 +164,47 @@ class MotionPrimitive(object):
         s[0, :self.s_pca["n_components"]] = np.asarray(alpha, dtype=np.float32)
         return self.device_model().backproject(s)[0].cpu().numpy().astype(np.float64)
 
+    # -- time warping: host, once per CHOSEN sample; the frames are evaluated on the device ----------
+    def _mean_temporal(self):
+        """motion_primitive.py:259-266"""
+        import scipy.interpolate as si
+        return si.splev(self.canonical_time_range, (self.t_pca["knots"], self.t_pca["mean_vector"], 3))
+
+    def _back_transform_gamma_to_canonical_time_function(self, gamma):
+        """motion_primitive.py:289-302: t(t') = cumulative sum of exp(mean + harmonics . gamma) over the canonical frames, - 1."""
+        import scipy.interpolate as si
+        mean_t = self._mean_temporal()
+        eigen_coefs = list(zip(*self.t_pca["eigen_vectors"]))
+        t_eigen_discrete = np.array([si.splev(self.canonical_time_range, (self.t_pca["knots"], c, 3)) for c in eigen_coefs]).T
+        steps = np.exp(mean_t[:self.n_canonical_frames] + t_eigen_discrete[:self.n_canonical_frames].dot(np.asarray(gamma, dtype=np.float64)))
+        return np.cumsum(steps) - 1.0
+
+    def _invert_canonical_to_sample_time_function(self, canonical_time_function, speed=1.0):
+        """motion_primitive.py:304-318: spline through (t, t') inverted and sampled at the integer sample frames.  The
+        reference passes a FLOAT sample count to np.linspace, which numpy >= 1.18 refuses (quirk Q3); the count is the
+        integer older numpy truncated it to."""
+        import scipy.interpolate as si
+        x_sample = np.arange(self.n_canonical_frames)
+        sample_time_spline = si.splrep(canonical_time_function, x_sample, w=None, k=3)
+        num = int(np.round(canonical_time_function[-2]) * (1.0 / speed))
+        frames = np.linspace(1, stop=canonical_time_function[-2], num=num)
+        sample_time_function = si.splev(frames, sample_time_spline)
+        sample_time_function = np.insert(sample_time_function, 0, 0)
+        return np.insert(sample_time_function, len(sample_time_function), self.n_canonical_frames - 1)
+
+    def back_project_time_function(self, gamma, speed=1.0):
+        """motion_primitive.py:268-287 (smooth_time_parameters is False in the reference, :72)."""
+        return self._invert_canonical_to_sample_time_function(self._back_transform_gamma_to_canonical_time_function(gamma), speed)
+
     def back_project(self, s, use_time_parameters=True, speed=1.0):
         """motion_primitive.py:206-234; the scored path always passes use_time_parameters=False
-        (objective_functions.py:159)."""
-        if use_time_parameters and self.has_time_parameters:
-            raise NotImplementedError("time-warp back-projection is not on the device path (SURVEY.md f2; the "
-                                      "reference's own implementation raises under numpy >= 1.18, Q3)")
+        (objective_functions.py:159).  With time parameters the chosen sample's time function t'(t) is computed on
+        the host (back_project_time_function) and the motion is evaluated at those times by K3."""
         s = np.ravel(np.asarray(s, dtype=np.float64))
         coeffs = self.back_project_spatial_coeffs(s[:self.s_pca["n_components"]])
+        if use_time_parameters and self.has_time_parameters:
+            time_function = self.back_project_time_function(s[self.s_pca["n_components"]:], speed)
+            return MotionSpline(coeffs, time_function, self.s_pca["knots"], None, low_dimensional_parameters=s, owner=self)
         time_function = np.linspace(0, self.n_canonical_frames, int(self.n_canonical_frames * (1.0 / speed)))
         return MotionSpline(coeffs, time_function, self.s_pca["knots"], None, low_dimensional_parameters=s, owner=self)
 

@@ -321,6 +321,42 @@ def run_local_case(ns, shape="S", n_samples=64, seed=2031):
     return out
 
 
+@contextlib.contextmanager
+def _linspace_int_num():
+    """numpy >= 1.18 refuses the FLOAT sample count the reference hands to np.linspace in
+    _invert_canonical_to_sample_time_function (motion_primitive.py:314, quirk Q3); older numpy truncated it with int().
+    This restores exactly that truncation for the duration of the call - the reference module itself is not touched."""
+    orig = np.linspace
+
+    def linspace(start, stop, num=50, *a, **k):
+        return orig(start, stop, int(num), *a, **k)
+    np.linspace = linspace
+    try:
+        yield
+    finally:
+        np.linspace = orig
+
+
+def run_timewarp_case(ns, shape="S", n_samples=6, seed=2051):
+    """f2: the reference's own time-warp back-projection (motion_primitive.py:268-318) and the motion it yields
+    (MotionSpline.get_motion_vector at the warped times, motion_spline.py:71-92), for sklearn-drawn samples."""
+    node = refload.make_graph_node(ns, syn.make_model_json(shape))
+    np.random.seed(seed)
+    S = node.sample_low_dimensional_vectors(n_samples)
+    S[:, -3:] *= 8.0        # time parameters large enough that the warp is visible
+    out = {"samples": S, "shape": np.array(shape)}
+    mp = node.motion_primitive
+    for i, s_ in enumerate(S):
+        with _linspace_int_num(), _quiet():
+            spline = node.back_project(s_, use_time_parameters=True)
+            frames = spline.get_motion_vector()
+            canonical = mp._back_transform_gamma_to_canonical_time_function(s_[mp.s_pca["n_components"]:])
+        out["tw%d_canonical" % i] = np.asarray(canonical)
+        out["tw%d_time" % i] = np.asarray(spline.time_function)
+        out["tw%d_frames" % i] = np.asarray(frames)
+    return out
+
+
 def run_config3_case(ns, n_samples=10000, seed=4100, max_steps=None):
     """BASELINE config 3 at the parity size SURVEY.md 8(d) row 3 states: the action list of examples/example_input.json
     (walk / pickRight / carryRight / placeRight) over the synthetic graph, every motion-primitive step decided by the
@@ -612,6 +648,11 @@ def main():
         np.savez_compressed(os.path.join(GOLDEN_DIR, "s_walk.npz"), **out)
         print("s_walk", [int(out["step%d_best_idx" % i]) for i in range(len(out["order"]))],
               [float(out["step%d_min_error" % i]) for i in range(len(out["order"]))])
+        return 0
+    if "--only-timewarp" in sys.argv:
+        out = run_timewarp_case(ns)
+        np.savez_compressed(os.path.join(GOLDEN_DIR, "s_timewarp.npz"), **out)
+        print("s_timewarp", [len(out["tw%d_time" % i]) for i in range(len(out["samples"]))], out["tw0_time"][:4], out["tw0_time"][-3:])
         return 0
     if "--only-config3" in sys.argv:
         out = run_config3_case(ns)

@@ -901,3 +901,18 @@ def test_exchange_fused_into_the_score_kernel():
                 for r in range(world):
                     peers[r].check()
                     assert float(outs[r][0].item()) == want_cost and int(outs[r][1].item()) == want_idx, (name, world, r)
+
+
+def test_time_warped_motion_matches_the_reference():
+    """f2: back_project(s, use_time_parameters=True): the time function t'(t) on the host (pinned on the CPU), the motion
+    evaluated at the warped times by K3 - against the reference's own MotionSpline.get_motion_vector."""
+    from tests.common import load_golden
+    from morphablegraphs_b200 import MotionStateGraphNode, synthetic as syn
+    g = load_golden("s_timewarp")
+    node = MotionStateGraphNode()
+    node._initialize_from_json(None, syn.make_model_json(str(g["shape"])))
+    for i, s in enumerate(g["samples"]):
+        spline = node.back_project(s, use_time_parameters=True)
+        fr = spline.get_motion_vector()
+        assert fr.shape == g["tw%d_frames" % i].shape
+        assert rel_err(fr, g["tw%d_frames" % i]).max() < RTOL

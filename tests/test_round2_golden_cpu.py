@@ -194,3 +194,26 @@ def test_oracle_residual_vectors_match_the_reference():
     mpc2.constraints = [c.constraints.constraints[i] for i in keep]
     assert rel_err(O.residual_vectors(c.node, c.skeleton, mpc2, c.samples).sum(axis=1),
                    sum(c.constraints.constraints[i].weight_factor * terms[i] for i in keep)).max() < 1e-9
+
+
+# ---------------------------------------------------------------------------
+# f2: time-warp back-projection (host part), pinned by the reference's own functions (tests/golden/s_timewarp.npz)
+# ---------------------------------------------------------------------------
+def test_time_warp_functions_match_the_reference():
+    from tests.common import load_golden
+    from morphablegraphs_b200 import MotionStateGraphNode, synthetic as syn
+    g = load_golden("s_timewarp")
+    node = MotionStateGraphNode()
+    node._initialize_from_json(None, syn.make_model_json(str(g["shape"])))
+    mp = node.motion_primitive
+    K = mp.s_pca["n_components"]
+    for i, s in enumerate(g["samples"]):
+        can = mp._back_transform_gamma_to_canonical_time_function(s[K:])
+        assert rel_err(can, g["tw%d_canonical" % i]).max() < 1e-12
+        tf = mp.back_project_time_function(s[K:])
+        assert tf.shape == g["tw%d_time" % i].shape            # the warp changes the NUMBER of frames
+        assert rel_err(tf, g["tw%d_time" % i]).max() < 1e-10
+        # the oracle's spline evaluation at the warped times gives the reference's motion
+        ma = O.ModelArrays(node)
+        fr = O.eval_frames(ma, O.back_project_coeffs(ma, s[None]), tf)[0]
+        assert rel_err(fr, g["tw%d_frames" % i]).max() < 1e-9
