@@ -1,6 +1,6 @@
 #!/usr/bin/env python
 """Run ONE kernel of libmgb200.so a few times on cuda:0 (the target of ncu captures).
-usage: python tools/run_kernel.py <k1|k2tc|k2simt|k3|k6|k1k6|k5b> [--shape S|L] [--n N] [--reps R]"""
+usage: python tools/run_kernel.py <k1|k2tc|k2simt|k3|k4|k5a|k6|k1k6|k5b|k8|k9|k10|k11|multi> [--shape S|L] [--n N] [--reps R]"""
 import argparse
 import os
 import sys
@@ -33,6 +33,18 @@ def main():
     if a.kernel == "k3":
         dm.backproject(S, impl=2, out=coeffs)
         frames = torch.empty((n, len(dc.times), dm.P), dtype=torch.float32, device="cuda")
+    if a.kernel in ("k4", "k5a"):
+        frames = dm.eval_frames(dm.backproject(S), dc.times)
+        pos = torch.empty((n, len(dc.times), 5, 3), dtype=torch.float32, device="cuda")
+    if a.kernel == "k11":
+        import ctypes as C
+        from morphablegraphs_b200 import _lib
+        X = torch.randn((n, 1500), device="cuda") * 30
+        mean = X.mean(dim=0).contiguous()
+        up = torch.zeros((1500, 1500), dtype=torch.float64, device="cuda")
+    if a.kernel == "multi":
+        jobs = [dict(dc=engine.DeviceConstraints(dm, mpc, prev), n=max(1, n // 4), seed=5 + j) for j in range(4)]
+    seeds8 = dm.sample(8, seed=77)
     fns = {
         "k1": lambda: dm.sample(n, seed=7, counts=counts, out=S),
         "k2tc": lambda: dm.backproject(S, impl=2, out=coeffs),
@@ -41,6 +53,14 @@ def main():
         "k6": lambda: dc.score(S, k=1, quality_scale=qs),
         "k1k6": lambda: dc.sample_score(n, seed=7, counts=counts, k=1, quality_scale=qs),
         "k5b": lambda: dm.logpdf(S),
+        "k4": lambda: dm.fk(frames, ["Hips", "LeftHand", "RightHand", "LeftFoot", "RightFoot"], out=pos),
+        "k5a": lambda: dc.score(S, k=1, frames=frames),
+        "k8": lambda: dc.node_costs(S),
+        "k9": lambda: dc.residuals(S),
+        "k10": lambda: dc.lm_refine(seeds8, quality_scale=qs, max_iter=50),
+        "k11": lambda: _lib.check(_lib.load().mgb_syrk_upper(C.c_void_p(X.data_ptr()), n, 1500, 1500, C.c_void_p(mean.data_ptr()),
+                                                             C.c_void_p(up.data_ptr()), C.c_void_p(torch.cuda.current_stream().cuda_stream))),
+        "multi": lambda: engine.sample_score_multi(jobs),
     }
     fn = fns[a.kernel]
     torch.cuda.synchronize()
