@@ -84,8 +84,10 @@ def plan_steps(graph, plan_input):
     return steps
 
 
-def step_specs(graph, step, prev_frames):
-    """Constraint specs (class name + descriptor, synthetic.spec) of one step, in GLOBAL coordinates."""
+def step_specs(graph, step, prev_frames, pose_points=None):
+    """Constraint specs (class name + descriptor, synthetic.spec) of one step, in GLOBAL coordinates.
+    pose_points: optional [2, len(POSE_JOINTS), 3] global positions of POSE_JOINTS in the last two previous frames (the
+    synthesizer gets them from K4 on the device; without them the host skeleton is walked)."""
     node = graph.nodes[step["node_key"]]
     F = node.get_n_canonical_frames()
     skel = graph.skeleton
@@ -99,9 +101,13 @@ def step_specs(graph, step, prev_frames):
         specs.append(syn.spec("GlobalTransformConstraint",
                               syn.position_constraint_desc(step["joint"], step["position"], step["keyframe"], F, label="contact"), 1.0, 1.0))
     # transition continuity (motion_primitive_constraints_builder.py:286-306): pose of the last frame so far, root velocity
-    last, before = np.asarray(prev_frames[-1]), np.asarray(prev_frames[-2] if len(prev_frames) > 1 else prev_frames[-1])
-    cloud = [skel.nodes[n].get_global_position(last).tolist() for n in POSE_JOINTS]
-    vel = (np.asarray(cloud[0]) - skel.nodes["Hips"].get_global_position(before)).tolist()
+    if pose_points is not None:
+        cloud = np.asarray(pose_points[1], dtype=np.float64).tolist()
+        vel = (np.asarray(pose_points[1][0], dtype=np.float64) - np.asarray(pose_points[0][0], dtype=np.float64)).tolist()
+    else:
+        last, before = np.asarray(prev_frames[-1]), np.asarray(prev_frames[-2] if len(prev_frames) > 1 else prev_frames[-1])
+        cloud = [skel.nodes[n].get_global_position(last).tolist() for n in POSE_JOINTS]
+        vel = (np.asarray(cloud[0]) - skel.nodes["Hips"].get_global_position(before)).tolist()
     specs.append(syn.spec("PoseConstraint", {"canonical_keyframe": 0, "frame_constraint": cloud, "velocity_constraint": vel,
                                              "semanticAnnotation": syn.sem("start"), "node_names": POSE_JOINTS,
                                              "weights": [skel.joint_weight_map[n] for n in POSE_JOINTS]}, 1.0, 1.0))
@@ -135,8 +141,8 @@ def initial_frames(graph, plan_input, first_node_key):
 class GraphWalkSynthesizer(object):
     """Runs the step list with a MotionPrimitiveGenerator (this package's or the reference's: same interface)."""
 
-    def __init__(self, graph, generator, keep_frames=8):
-        self.graph, self.generator, self.keep_frames = graph, generator, keep_frames
+    def __init__(self, graph, generator, keep_frames=8, device_fk=False):
+        self.graph, self.generator, self.keep_frames, self.device_fk = graph, generator, keep_frames, device_fk
 
     def run(self, mg_input, max_steps=None, on_step=None):
         plan_input = read_input(mg_input)
@@ -145,9 +151,10 @@ class GraphWalkSynthesizer(object):
             steps = steps[:max_steps]
         prev = initial_frames(self.graph, plan_input, steps[0]["node_key"])
         out = []
+        pose_points = None
         for i, step in enumerate(steps):
             node = self.graph.nodes[step["node_key"]]
-            specs = step_specs(self.graph, step, prev)
+            specs = step_specs(self.graph, step, prev, pose_points)
             mpc = build_constraints(self.graph, specs)
             s = self.generator.generate_constrained_sample(node, mpc, "", prev, None)
             frames = node.back_project(s, use_time_parameters=False).get_motion_vector()
@@ -158,4 +165,10 @@ class GraphWalkSynthesizer(object):
             if on_step is not None:
                 on_step(i, rec)
             prev = frames[-self.keep_frames:]
+            if self.device_fk:
+                # the transition constraint of the next step needs the end-effector positions of the last two frames; K4 can
+                # supply them, but for TWO frames its per-call plan upload costs more (0.5 ms) than walking the host skeleton
+                # (0.2 ms, tools/c3_cost.py), so this is off by default
+                dm = node.motion_primitive.device_model(self.graph.skeleton)
+                pose_points = dm.fk(np.ascontiguousarray(frames[-2:], dtype=np.float32), POSE_JOINTS).cpu().numpy()
         return out
