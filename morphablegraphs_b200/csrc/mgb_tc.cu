@@ -616,6 +616,8 @@ struct TcScoreParams {
     int QS;            // floats per candidate row of the quad-value area (also the raw-sample staging)
     const int* phase;  // [quad chunks + 1] first op of every chunk's part of the program
     int ops_in_smem;   // program + constants staged in shared memory (else read through L1)
+    int draw_ahead;    // sampling mode, short constraint programs: group 0 draws the next tile's normals into the quad-value area
+                       // while it waits for this tile's GMM chunks (the draw is ~9 k of a ~99 k-cycle tile otherwise serial with the pipe)
     int CW;            // GMM columns per component (a multiple of 8; components are packed densely and may straddle N-chunks)
     int seg_s;         // sampling operand (fused K1), -1 if the candidates come from memory
     int CWs;           // its columns per component
@@ -716,16 +718,24 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mgb_score_tc_kernel(const __gri
     // K columns [k_lo, k_hi) of the A tile belong to group h: group 0 takes the first Kh columns (a multiple of 8), group 1 the rest
     const int Kh = ((p.Kp >> 1) + 7) & ~7;
     // fill 1: [z | 1], z = the standard normals mgb_sample draws for global index gi
-    auto fill_z = [&](int row, int k_lo, int k_hi, bool valid, long long gi) {
+    // pre: the row's normals were drawn one tile ahead into the quad-value area (draw_ahead below): only split + store is left
+    auto fill_z = [&](int row, int k_lo, int k_hi, bool valid, long long gi, const float* pre) {
         const int D = sp.D;
         const uint2 key = make_uint2((unsigned int)sp.seed, (unsigned int)(sp.seed >> 32));
         // four independent Philox / Box-Muller chains per iteration: a warp has its scheduler almost to itself here, and one
         // chain is a sequence of dependent integer multiplies
         for (int k0 = k_lo; k0 < k_hi; k0 += 16) {
             float z[4][4];
+            if (pre != nullptr) {
 #pragma unroll
-            for (int u = 0; u < 4; ++u) {
-                mgb_normal4((unsigned long long)gi, (unsigned int)((k0 >> 2) + u), key, z[u]);   // unconditional: the chains interleave
+                for (int u = 0; u < 4; ++u)
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) z[u][q] = (k0 + 4 * u + q < D) ? pre[k0 + 4 * u + q] : 0.f;
+            } else {
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    mgb_normal4((unsigned long long)gi, (unsigned int)((k0 >> 2) + u), key, z[u]);   // unconditional: the chains interleave
+                }
             }
 #pragma unroll
             for (int u = 0; u < 4; ++u) {
@@ -742,6 +752,22 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mgb_score_tc_kernel(const __gri
                     *reinterpret_cast<float4*>(smem + L.a_lo + off) = make_float4(l[0], l[1], l[2], l[3]);
                 }
             }
+        }
+    };
+    // all D normals of global index gi into dst (shared memory): run by group 0 for the NEXT tile while it would otherwise wait
+    // for the GMM chunks of this one
+    auto draw_ahead = [&](long long gi, float* dst) {
+        const int D = sp.D;
+        const uint2 key = make_uint2((unsigned int)sp.seed, (unsigned int)(sp.seed >> 32));
+        for (int k0 = 0; k0 < D; k0 += 16) {
+            float z[4][4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) mgb_normal4((unsigned long long)gi, (unsigned int)((k0 >> 2) + u), key, z[u]);
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+#pragma unroll
+                for (int q = 0; q < 4; ++q)
+                    if (k0 + 4 * u + q < D) dst[k0 + 4 * u + q] = z[u][q];
         }
     };
     // fill 2: s = mu_g + L_g z comes back in TMEM (columns [k_lo, k_hi) of this thread's lane, a multiple of 8); A becomes
@@ -822,7 +848,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mgb_score_tc_kernel(const __gri
                 idx = gi - sp.index_base;
                 mgb_mbar_wait(bars.a_empty, (unsigned int)(t & 1) ^ 1u);
                 MGB_TC_T(0)
-                fill_z(row, 0, Kh, valid, gi);
+                fill_z(row, 0, Kh, valid, gi, (p.draw_ahead && t > 0) ? qv + (size_t)row * QS : nullptr);
             } else {
                 idx = g0 + row;
                 valid = idx < sp.n;
@@ -904,6 +930,17 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mgb_score_tc_kernel(const __gri
                 MGB_TC_T(6)
             });
             float cost = sp.err_scale * total;
+            if constexpr (SAMPLE) {
+                if (p.draw_ahead && t + 1 < my_tiles) {
+                    // the quad values of this tile are consumed: the area takes the next tile's normals (both groups read them
+                    // after the barrier below, before the next quad chunk is drained into it)
+                    int g_;
+                    long long gi_;
+                    bool v_;
+                    sample_row(T + gridDim.x, row, g_, gi_, v_);
+                    if (v_) draw_ahead(gi_, qv + (size_t)row * QS);
+                }
+            }
             if (g1_active) {
                 asm volatile("bar.sync 2, 256;" ::: "memory");  // group 1 has published -log p(s) and its share of |s|^2 of this tile
                 if (p.seg_g >= 0) cost = fmaf(sp.quality_scale, sm_lp[row], cost);
@@ -1016,7 +1053,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mgb_score_tc_kernel(const __gri
             if constexpr (SAMPLE) {
                 sample_row(T, row, gcomp, gi, valid);
                 mgb_mbar_wait(bars.a_empty, (unsigned int)(t & 1) ^ 1u);
-                fill_z(row, Kh, p.Kp, valid, gi);
+                fill_z(row, Kh, p.Kp, valid, gi, (p.draw_ahead && t > 0) ? qv + (size_t)row * p.QS : nullptr);
                 mgb_fence_proxy_async();
                 mgb_mbar_arrive(bars.a_full);
             }
@@ -1270,6 +1307,8 @@ static bool tc_score_plan(const mgb_model* m, const mgb_constraints* c, float qu
     p.segs.il_q = (use_q && use_g) ? p.seg_q : -1;
     p.segs.il_g = use_g ? p.seg_g : -1;   // also names the operand whose chunks belong to epilogue group 1
     p.QS = std::max(use_q ? std::min(c->tcq_Np, TC_SCORE_QCHUNK) : 0, m->D) | 1;
+    // worth it only when group 0 has time to spare: GMM on, and at most two chunks of constraint program per tile
+    p.draw_ahead = (sample && use_g && (!use_q || (c->tcq_Np + TC_SCORE_QCHUNK - 1) / TC_SCORE_QCHUNK <= 2)) ? 1 : 0;
     size_t stage_bytes = 0;
     for (int i = 0; i < p.segs.n; ++i) stage_bytes = std::max(stage_bytes, (size_t)2 * p.segs.seg[i].NC * p.segs.seg[i].KC * 4);
     const int n_ops = c ? c->n_ops : 0, n_cst = c ? c->n_cst : 0;
