@@ -41,7 +41,10 @@ template <int NS, int CH>
 __global__ void __launch_bounds__(KM_WARPS * 32) mgb_kmeans_level_kernel(
     const float* __restrict__ x, long long n, int dim, int dim_acc, int ld, const int* __restrict__ node,
     const float* __restrict__ cent, int n_sub, int* __restrict__ label, float* __restrict__ sums,
-    int* __restrict__ counts, float* __restrict__ node_inertia, float* __restrict__ inertia, long long tiles_per_warp, int W) {
+    int* __restrict__ counts, float* __restrict__ node_inertia, float* __restrict__ inertia, long long tiles_per_warp, int W,
+    const int* __restrict__ skip) {
+    // skip: per-node flags (converged); a tile ALL of whose samples belong to flagged nodes is neither fetched nor processed -
+    // labels, sums and counts of such nodes are those of an earlier iteration and are not read again before the final pass
     extern __shared__ float sm_tiles[];
     const unsigned FULL = 0xffffffffu;
     const int lane = threadIdx.x & 31;
@@ -104,21 +107,33 @@ __global__ void __launch_bounds__(KM_WARPS * 32) mgb_kmeans_level_kernel(
         }
         __pipeline_commit();
     };
-    fetch(first, tile0);
-    int nd_next = (first + lane < last) ? (node ? __ldg(node + first + lane) : 0) : -1;
+    auto ids_of = [&](long long t0) -> int { return (t0 + lane < last) ? (node ? __ldg(node + t0 + lane) : 0) : -1; };
+    auto tile_skippable = [&](int nd_lane) -> bool {
+        return skip != nullptr && __all_sync(FULL, nd_lane < 0 || __ldg(skip + nd_lane) != 0);
+    };
+    // node ids run two tiles ahead of the tile being processed: whether tile t0 + 32 is fetched at all is decided from them
+    int nd_a = ids_of(first), nd_b = ids_of(first + 32);
+    bool skip_a = tile_skippable(nd_a);
+    if (!skip_a) fetch(first, tile0);
+    else __pipeline_commit();
     int pb = 0;
     for (long long t0 = first; t0 < last; t0 += 32, pb ^= 1) {
         const int rows = (int)((last - t0 < 32) ? (last - t0) : 32);
-        fetch(t0 + 32, tile0 + (pb ? 0 : tstride));
+        const bool skip_b = (t0 + 32 < last) ? tile_skippable(nd_b) : true;
+        if (!skip_b) fetch(t0 + 32, tile0 + (pb ? 0 : tstride));
+        else __pipeline_commit();
+        const int nd_c = ids_of(t0 + 64);
         __pipeline_wait_prior(1);
         __syncwarp();
         tile = tile0 + (pb ? tstride : 0);
+        const int nd_cur = nd_a;
+        const bool skip_cur = skip_a;
+        nd_a = nd_b; nd_b = nd_c; skip_a = skip_b;
+        if (skip_cur) continue;
         // E-step: lane = sample; the NS distances advance together so that NS independent centroid loads are
-        // in flight per column.  The node id of the NEXT tile is fetched now and used one iteration later.
+        // in flight per column.
         int nd = -1, lb = 0;
         float best = 0.f;
-        const int nd_cur = nd_next;
-        if (t0 + 32 + lane < last) nd_next = node ? __ldg(node + t0 + 32 + lane) : 0;
         if (lane < rows) {
             nd = nd_cur;
             const float* xi = tile + lane * ld;
@@ -183,8 +198,13 @@ __global__ void __launch_bounds__(KM_WARPS * 32) mgb_kmeans_level_kernel(
 __global__ void __launch_bounds__(128) mgb_kmeans_centroid_kernel(int n_nodes, int n_sub, int dim, int dim_acc,
                                                                  const float* __restrict__ sums, const int* __restrict__ counts,
                                                                  const float* __restrict__ tol, float* __restrict__ cent,
-                                                                 int* __restrict__ converged, int* __restrict__ n_active) {
+                                                                 int* __restrict__ converged, int* __restrict__ n_active,
+                                                                 int* __restrict__ n_active_next, float* __restrict__ sums_rw,
+                                                                 int* __restrict__ counts_rw) {
+    // n_active / n_active_next: two counters used alternately, this launch clears the one the NEXT iteration adds to (no memset
+    // between iterations); sums_rw / counts_rw: the sums this thread consumed are zeroed for the next E-step likewise
     const int nd = blockIdx.x * blockDim.x + threadIdx.x;
+    if (nd == 0) *n_active_next = 0;
     if (nd >= n_nodes) return;
     if (converged[nd]) return;
     float shift = 0.f;
@@ -201,13 +221,19 @@ __global__ void __launch_bounds__(128) mgb_kmeans_centroid_kernel(int n_nodes, i
             c[j] = v;
         }
     }
+    for (int k = 0; k < n_sub; ++k) {
+        counts_rw[(size_t)nd * n_sub + k] = 0;
+        float* sz = sums_rw + ((size_t)nd * n_sub + k) * dim_acc;
+        for (int j = 0; j < dim_acc; ++j) sz[j] = 0.f;
+    }
     if (shift <= (tol ? tol[nd] : 0.f)) converged[nd] = 1;
     else atomicAdd(n_active, 1);
 }
 
 template <int NS, int CH>
 int launch_level(const float* d_x, int64_t n, int dim, int dim_acc, int ld, const int* d_node, const float* d_cent, int n_sub,
-                 int* d_label, float* d_sums, int* d_counts, float* d_node_inertia, float* d_inertia, cudaStream_t stream) {
+                 int* d_label, float* d_sums, int* d_counts, float* d_node_inertia, float* d_inertia, cudaStream_t stream,
+                 const int* d_skip) {
     auto kern = mgb_kmeans_level_kernel<NS, CH>;
     const size_t smem = (size_t)2 * KM_WARPS * 32 * ld * sizeof(float);
     MGB_REQUIRE(smem <= 200 * 1024, "row stride too large for the k-means kernel (ld <= 200)");
@@ -227,20 +253,21 @@ int launch_level(const float* d_x, int64_t n, int dim, int dim_acc, int ld, cons
         while (W < dim_acc) W <<= 1;
     }
     kern<<<(unsigned)grid, KM_WARPS * 32, smem, stream>>>(d_x, n, dim, dim_acc, ld, d_node, d_cent, n_sub, d_label, d_sums, d_counts,
-                                                           d_node_inertia, d_inertia, tpw, W);
+                                                           d_node_inertia, d_inertia, tpw, W, d_skip);
     mgb_count_launch();
     MGB_CUDA(cudaGetLastError());
     return MGB_OK;
 }
 
 int dispatch_level(const float* d_x, int64_t n, int dim, int dim_acc, int ld, const int* d_node, const float* d_cent, int n_sub,
-                   int* d_label, float* d_sums, int* d_counts, float* d_node_inertia, float* d_inertia, cudaStream_t stream) {
+                   int* d_label, float* d_sums, int* d_counts, float* d_node_inertia, float* d_inertia, cudaStream_t stream,
+                   const int* d_skip = nullptr) {
     const int ch = (dim_acc + 31) / 32;
     MGB_REQUIRE(n_sub >= 1 && n_sub <= 8, "n_sub must be in 1..8");
     MGB_REQUIRE(ch <= 4, "at most 128 accumulated columns");
 #define MGB_KM_CASE(NS, CH)                                                                                              \
     return launch_level<NS, CH>(d_x, n, dim, dim_acc, ld, d_node, d_cent, n_sub, d_label, d_sums, d_counts, d_node_inertia, \
-                                d_inertia, stream)
+                                d_inertia, stream, d_skip)
     if (n_sub <= 4) {
         switch (ch) {
             case 1: MGB_KM_CASE(4, 1);
@@ -292,39 +319,44 @@ extern "C" int mgb_kmeans_level(const float* d_x, int64_t n, int32_t dim, int32_
     int dev = 0;
     MGB_CUDA(cudaGetDevice(&dev));
     if (!d_active || d_active_dev != dev) {
-        MGB_CUDA(cudaMalloc((void**)&d_active, sizeof(int)));
+        MGB_CUDA(cudaMalloc((void**)&d_active, 2 * sizeof(int)));
         d_active_dev = dev;
     }
     const size_t sums_bytes = (size_t)n_nodes * n_sub * dim_acc * sizeof(float);
     const size_t counts_bytes = (size_t)n_nodes * n_sub * sizeof(int);
-    auto e_step = [&]() -> int {
-        MGB_CUDA(cudaMemsetAsync(d_sums, 0, sums_bytes, stream));
-        MGB_CUDA(cudaMemsetAsync(d_counts, 0, counts_bytes, stream));
-        if (d_node_inertia) MGB_CUDA(cudaMemsetAsync(d_node_inertia, 0, (size_t)n_nodes * sizeof(float), stream));
-        return dispatch_level(d_x, n, dim, dim_acc, ld, d_node, d_centroids, n_sub, d_label, d_sums, d_counts, d_node_inertia,
-                              nullptr, stream);
+    // fresh = true: all accumulators cleared by memsets and every tile processed (first and final pass); otherwise the centroid
+    // kernel of the previous iteration has cleared what it consumed and tiles of converged nodes are skipped
+    auto e_step = [&](bool fresh) -> int {
+        if (fresh) {
+            MGB_CUDA(cudaMemsetAsync(d_sums, 0, sums_bytes, stream));
+            MGB_CUDA(cudaMemsetAsync(d_counts, 0, counts_bytes, stream));
+            if (d_node_inertia) MGB_CUDA(cudaMemsetAsync(d_node_inertia, 0, (size_t)n_nodes * sizeof(float), stream));
+        }
+        return dispatch_level(d_x, n, dim, dim_acc, ld, d_node, d_centroids, n_sub, d_label, d_sums, d_counts, fresh ? d_node_inertia : nullptr,
+                              nullptr, stream, fresh ? nullptr : d_converged);
     };
     int it = 0;
     bool done = (max_iter == 0);
+    MGB_CUDA(cudaMemsetAsync(d_active, 0, 2 * sizeof(int), stream));
     while (!done) {
-        int rc = e_step();
+        int rc = e_step(it == 0);
         if (rc != MGB_OK) return rc;
-        MGB_CUDA(cudaMemsetAsync(d_active, 0, sizeof(int), stream));
         mgb_kmeans_centroid_kernel<<<(n_nodes + 127) / 128, 128, 0, stream>>>(n_nodes, n_sub, dim, dim_acc, d_sums, d_counts, d_tol,
-                                                                              d_centroids, d_converged, d_active);
+                                                                              d_centroids, d_converged, d_active + (it & 1),
+                                                                              d_active + ((it + 1) & 1), d_sums, d_counts);
         mgb_count_launch();
         MGB_CUDA(cudaGetLastError());
         ++it;
         if (it >= max_iter) break;
         if (it % check_every == 0) {
-            MGB_CUDA(cudaMemcpyAsync(h_active, d_active, sizeof(int), cudaMemcpyDeviceToHost, stream));
+            MGB_CUDA(cudaMemcpyAsync(h_active, d_active + ((it - 1) & 1), sizeof(int), cudaMemcpyDeviceToHost, stream));
             MGB_CUDA(cudaStreamSynchronize(stream));
             if (*h_active == 0) done = true;
         }
     }
     // labels, sums, counts and inertia that belong to the final centroids (sklearn re-runs the
     // E-step after a tolerance stop; _kmeans_single_lloyd)
-    int rc = e_step();
+    int rc = e_step(true);
     if (rc != MGB_OK) return rc;
     if (iters_done) *iters_done = it;
     return MGB_OK;

@@ -70,6 +70,13 @@ def exchange_best(cost, index, device=None, group=None):
     return select_best(g[:, 0], g[:, 1].astype(np.int64))
 
 
+def default_spin_limit():
+    """Polls (40 ns sleeps) a rank waits for a peer's record before it raises instead of hanging: ~10 s by default - a rank may be
+    late by a first-call CUDA initialisation or a constraint compile -, MGB_EXCHANGE_SPIN_LIMIT overrides it."""
+    import os
+    return int(os.environ.get("MGB_EXCHANGE_SPIN_LIMIT", "250000000"))
+
+
 class PeerExchange(object):
     """The same exchange without a library collective on the step's critical path: every rank stores its
     16-byte record into every peer's slot array through NVLink peer memory and reduces the records that
@@ -115,7 +122,7 @@ class PeerExchange(object):
         p = lambda t: C.c_void_p(t.data_ptr())
         with torch.cuda.device(self.device):
             _lib.check(self.lib.mgb_exchange_best(p(best_cost), p(best_idx), p(self.peer_ptrs), self.rank, self.world,
-                                                  C.c_uint32(self.seq), C.c_int64(int(spin_limit)), p(self.out_cost), p(self.out_idx),
+                                                  C.c_uint32(self.seq), C.c_int64(int(spin_limit) or default_spin_limit()), p(self.out_cost), p(self.out_idx),
                                                   p(self.err), C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)))
         return self.out_cost, self.out_idx
 
@@ -129,7 +136,7 @@ class PeerExchange(object):
             self.seq = 2
         d = _lib.ExchangeDesc()
         d.d_peer_slots = self.peer_ptrs.data_ptr()
-        d.rank, d.world, d.seq, d.spin_limit = self.rank, self.world, self.seq, int(spin_limit)
+        d.rank, d.world, d.seq, d.spin_limit = self.rank, self.world, self.seq, int(spin_limit) or default_spin_limit()
         d.d_err = self.err.data_ptr()
         return d
 
