@@ -513,6 +513,7 @@ std::vector<float> tc_pack_b(TcB& B, int K, int N, Get get) {
 }
 
 constexpr size_t TC_SMEM_BUDGET = 220 * 1024;
+constexpr size_t TC_SCORE_SMEM_MAX = 227 * 1024;   // cudaDevAttrMaxSharedMemoryPerBlockOptin on sm_100
 
 // choose the chunking for an operand with K rows / N columns next to a resident A tile
 bool tc_plan_b(TcB& B, int K, int N, int* nst_out, int* W_out = nullptr, int* nbuf_out = nullptr) {
@@ -1312,17 +1313,23 @@ static bool tc_score_plan(const mgb_model* m, const mgb_constraints* c, float qu
     size_t stage_bytes = 0;
     for (int i = 0; i < p.segs.n; ++i) stage_bytes = std::max(stage_bytes, (size_t)2 * p.segs.seg[i].NC * p.segs.seg[i].KC * 4);
     const int n_ops = c ? c->n_ops : 0, n_cst = c ? c->n_cst : 0;
-    // preference: program in shared memory with >= 2 stages, else program read through L1
-    for (int in_smem = 1; in_smem >= 0; --in_smem) {
-        for (int nst = TC_MAX_STAGES; nst >= 2; --nst) {
-            const size_t total = tc_score_smem_plan(p.Kp, stage_bytes, nst, p.QS, in_smem ? n_ops : 0, in_smem ? n_cst : 0).total;
-            if (total + 1024 <= TC_SMEM_BUDGET) {
-                p.nst = nst;
-                p.ops_in_smem = in_smem;
-                *out = p;
-                *smem_out = total;
-                return true;
-            }
+    // The kernel has no static shared memory: the whole 227 KB opt-in maximum is available to the carve-up.  Short constraint
+    // programs (<= 2 quad chunks per tile: the operand stream is the critical path, it runs at ~70 % of the L2 throughput and a
+    // deeper ring hides its latency) take as many operand stages as fit, program in shared memory only if room is left
+    // (L4M: 4 stages 11.3 ms, 3 stages 11.6 ms); long programs keep program + constants in shared memory first (the stress
+    // set loses 12 % when they are read through L1).
+    const bool stages_first = p.draw_ahead != 0 || !use_q || (c->tcq_Np + TC_SCORE_QCHUNK - 1) / TC_SCORE_QCHUNK <= 2;
+    for (int pass = 0; pass < 2 * (TC_MAX_STAGES - 1); ++pass) {
+        int nst, in_smem;
+        if (stages_first) { nst = TC_MAX_STAGES - pass / 2; in_smem = 1 - (pass & 1); }
+        else { in_smem = pass < (TC_MAX_STAGES - 1) ? 1 : 0; nst = TC_MAX_STAGES - pass % (TC_MAX_STAGES - 1); }
+        const size_t total = tc_score_smem_plan(p.Kp, stage_bytes, nst, p.QS, in_smem ? n_ops : 0, in_smem ? n_cst : 0).total;
+        if (total <= TC_SCORE_SMEM_MAX) {
+            p.nst = nst;
+            p.ops_in_smem = in_smem;
+            *out = p;
+            *smem_out = total;
+            return true;
         }
     }
     return false;
@@ -1355,9 +1362,9 @@ int mgb_launch_score_tc(const mgb_model* m, const mgb_constraints* c, const Scor
         p.n_tiles = acc;
     }
     static bool cfg_a[MGB_MAX_DEVICES] = {false}, cfg_b[MGB_MAX_DEVICES] = {false}, cfg_c[MGB_MAX_DEVICES] = {false};
-    if (int rc = mgb_opt_in_smem(mgb_score_tc_kernel<float, false>, cfg_a, (int)TC_SMEM_BUDGET)) return rc;
-    if (int rc = mgb_opt_in_smem(mgb_score_tc_kernel<double, false>, cfg_b, (int)TC_SMEM_BUDGET)) return rc;
-    if (int rc = mgb_opt_in_smem(mgb_score_tc_kernel<float, true>, cfg_c, (int)TC_SMEM_BUDGET)) return rc;
+    if (int rc = mgb_opt_in_smem(mgb_score_tc_kernel<float, false>, cfg_a, (int)TC_SCORE_SMEM_MAX)) return rc;
+    if (int rc = mgb_opt_in_smem(mgb_score_tc_kernel<double, false>, cfg_b, (int)TC_SCORE_SMEM_MAX)) return rc;
+    if (int rc = mgb_opt_in_smem(mgb_score_tc_kernel<float, true>, cfg_c, (int)TC_SCORE_SMEM_MAX)) return rc;
     const int grid = (int)std::max<long long>(1, std::min<long long>(p.n_tiles, tc_num_sms()));
     if (sample)
         mgb_score_tc_kernel<float, true><<<grid, TC_THREADS, smem, stream>>>(p);
