@@ -22,10 +22,14 @@
  *    the entries that take caller-owned device pointers + a stream (mgb_sample,
  *    mgb_score, mgb_sample_score, mgb_backproject, ...) may be called on one
  *    handle from several host threads, each with its own workspace and stream.
- *    The HOST-BUFFER entries (mgb_score_host, mgb_generate_best, mgb_score_options)
- *    use staging buffers and streams owned by the model handle: calls on the same
- *    model handle are serialised by a per-handle mutex; different handles run
- *    concurrently.
+ *    The HOST-BUFFER entries use buffers owned by the library: mgb_score_host stages
+ *    through buffers and streams of the model handle (calls on one model handle are
+ *    serialised by a per-handle mutex, different handles run concurrently);
+ *    mgb_sample_score_best[_sharded] and mgb_sample_score_multi return their results
+ *    through one pinned record block per DEVICE (calls on one device are serialised);
+ *    mgb_constraints_pack takes its table block from a pool of the model handle
+ *    (mutex-protected) and uploads it on the handle's own stream - launches order
+ *    themselves against that upload with events.
  *  - there is no CPU fallback: every compute entry fails with MGB_E_CUDA when
  *    no sm_100-class device is usable.
  */
