@@ -219,7 +219,8 @@ int mgb_sample(const mgb_model* m, int64_t n, int64_t index_base, const int64_t*
  * NULL.  d_best_cost[k] / d_best_idx[k] (global index = index_base + i)
  * receive the k smallest costs, ties -> lowest index (first-minimum rule,
  * motion_primitive_generator.py:253-257); k == 0 skips selection.
- * k > 1 requires d_cost.  Workspace: mgb_score_workspace_bytes() bytes, zero-filled ONCE
+ * k > 1 requires d_cost.  Workspace: mgb_score_workspace_bytes(n, k) bytes (it grows with k > 1: the
+ * one-pass top-k keeps its per-CTA partials there; size it with the largest k you will pass), zero-filled ONCE
  * by the caller when it is allocated (it holds the cross-CTA completion counter, which the
  * kernel re-arms itself); one workspace must not be shared by concurrent streams. */
 size_t mgb_score_workspace_bytes(int64_t n, int32_t k);

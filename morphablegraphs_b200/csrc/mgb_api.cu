@@ -1048,7 +1048,7 @@ extern "C" int mgb_score_host(const mgb_model* m_, const mgb_constraints* c, con
     const int64_t n_chunks = n > 0 ? (n + CH - 1) / CH : 0;
     const bool need_all_costs = (h_cost != nullptr) || (k > 1);
     // workspace layout: [score ws][chunk best cost][chunk best idx][costs (optional)]
-    const size_t ws_score = mgb_score_workspace_bytes(n, 1);
+    const size_t ws_score = mgb_score_workspace_bytes(n, k > 1 ? k : 1);   // k > 1: mgb_topk keeps its stage-1 partials in it
     const size_t best_off = (ws_score + 255) & ~(size_t)255;
     const size_t n_best = (size_t)std::max<int64_t>(n_chunks, 64);
     const size_t idx_off = (best_off + n_best * sizeof(float) + 255) & ~(size_t)255;

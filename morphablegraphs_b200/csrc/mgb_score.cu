@@ -579,10 +579,10 @@ int launch_shape(int D, ScoreParams& p, const SmemPlan& plan, cudaStream_t strea
 
 extern "C" size_t mgb_score_workspace_bytes(int64_t n, int32_t k) {
     (void)n;
-    (void)k;
-    // per-CTA partials (cost + index) + completion counter, generously sized
+    // per-CTA partials (cost + index) + completion counter, generously sized; for k > 1 also the stage-1 partials of mgb_topk
     size_t parts = 148 * 16;
-    return parts * (sizeof(float) + sizeof(long long)) + 256;
+    const size_t argmin = parts * (sizeof(float) + sizeof(long long)) + 256;
+    return k > 1 ? argmin + (size_t)592 * 64 * (sizeof(float) + sizeof(long long)) : argmin;
 }
 
 // Fills the kernel parameters of one job and its shared-memory plan (everything but the launch).
@@ -805,14 +805,99 @@ int mgb_launch_score_multi(const MgbJob* jobs, int n_jobs, ScoreParams* h_params
         if (int rca = mgb_constraints_after_launch(jobs[j].c, stream)) return rca;
     return MGB_OK;
 }
+// ---------------------------------------------------------------------------
+// K5c, one pass: every CTA keeps its chunk of the cost array in shared memory and extracts the chunk's k smallest
+// (k block arg-mins over shared memory, a taken entry becomes NaN = "never wins"); one CTA then extracts the k smallest of
+// the grid * k partials the same way.  The cost array is read ONCE (the k-pass form read it k times with 2 k launches).
+// Order: (cost, global index) ascending; NaN never selected; slots beyond the finite + infinite entries get (inf, index_base).
+// ---------------------------------------------------------------------------
+namespace {
+
+constexpr int TOPK_CHUNK_MAX = 49152;   // floats of shared memory per CTA (192 KB)
+constexpr int TOPK_MAX_CTAS = 592;
+
+__device__ __forceinline__ void topk_block_argmin(float c, long long i, float* red_c, long long* red_i, float& out_c, long long& out_i) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const float oc = __shfl_xor_sync(0xffffffffu, c, o);
+        const long long oi = __shfl_xor_sync(0xffffffffu, i, o);
+        if (better(oc, oi, c, i)) { c = oc; i = oi; }
+    }
+    __syncthreads();
+    if ((threadIdx.x & 31) == 0) { red_c[threadIdx.x >> 5] = c; red_i[threadIdx.x >> 5] = i; }
+    __syncthreads();
+    c = red_c[0];
+    i = red_i[0];
+    for (int w = 1; w < MGB_BLOCK / 32; ++w)
+        if (better(red_c[w], red_i[w], c, i)) { c = red_c[w]; i = red_i[w]; }
+    out_c = c;
+    out_i = i;
+}
+
+// src_idx == nullptr: entry e of the chunk has global index index_base + first + e (stage 1); else the index is read (stage 2)
+__global__ void __launch_bounds__(MGB_BLOCK) mgb_topk_select_kernel(const float* __restrict__ cost, const long long* __restrict__ src_idx, long long n,
+                                                                   long long chunk, long long index_base, int k, float* __restrict__ out_cost,
+                                                                   long long* __restrict__ out_idx, int final_stage) {
+    extern __shared__ __align__(16) float sm_c[];
+    __shared__ float red_c[MGB_BLOCK / 32];
+    __shared__ long long red_i[MGB_BLOCK / 32];
+    const long long first = (long long)blockIdx.x * chunk;
+    const int cnt = (int)max(0LL, min(chunk, n - first));
+    for (int e = threadIdx.x; e < cnt; e += MGB_BLOCK) sm_c[e] = cost[first + e];
+    __syncthreads();
+    for (int j = 0; j < k; ++j) {
+        float bc = INFINITY;
+        long long bi = LLONG_MAX;
+        int be = -1;
+        for (int e = threadIdx.x; e < cnt; e += MGB_BLOCK) {
+            const float c = sm_c[e];
+            const long long gi = src_idx ? __ldg(src_idx + first + e) : index_base + first + e;
+            if (better(c, gi, bc, bi)) { bc = c; bi = gi; be = e; }
+        }
+        float wc;
+        long long wi;
+        topk_block_argmin(bc, bi, red_c, red_i, wc, wi);
+        if (be >= 0 && bi == wi && bc == wc) sm_c[be] = __int_as_float(0x7fc00000);   // taken: NaN never wins again (indices are unique)
+        if (threadIdx.x == 0) {
+            const bool none = (wi == LLONG_MAX);
+            out_cost[(size_t)blockIdx.x * k + j] = (none && !final_stage) ? __int_as_float(0x7fc00000) : wc;
+            out_idx[(size_t)blockIdx.x * k + j] = none ? (final_stage ? index_base : LLONG_MAX) : wi;
+        }
+        __syncthreads();
+    }
+}
+
+}  // namespace
+
 extern "C" int mgb_topk(const float* d_cost, int64_t n, int64_t index_base, int32_t k, float* d_best_cost,
                         int64_t* d_best_idx, void* d_workspace, size_t workspace_bytes, void* stream_) {
     cudaStream_t stream = (cudaStream_t)stream_;
     MGB_REQUIRE(d_cost && d_best_cost && d_best_idx, "null pointer");
     MGB_REQUIRE(k >= 1 && k <= 64, "k must be in [1, 64]");
     MGB_REQUIRE(d_workspace && workspace_bytes >= mgb_score_workspace_bytes(n, k), "workspace too small");
+    MGB_REQUIRE(n >= 0, "negative n");
+    // partials of stage 1 live in the workspace after the arg-min partials of the score kernels
     unsigned char* ws = reinterpret_cast<unsigned char*>(d_workspace);
     const size_t parts = 148 * 16;
+    unsigned char* tk = ws + parts * (sizeof(long long) + sizeof(float)) + 256;
+    long long ctas = std::max<long long>(1, std::min<long long>((n + 4095) / 4096, TOPK_MAX_CTAS));
+    long long chunk = std::max<long long>(1, (n + ctas - 1) / ctas);
+    if (k > 1 && chunk <= TOPK_CHUNK_MAX && ctas * k <= TOPK_CHUNK_MAX) {
+        long long* part_idx = reinterpret_cast<long long*>(tk);
+        float* part_cost = reinterpret_cast<float*>(tk + (size_t)TOPK_MAX_CTAS * 64 * sizeof(long long));
+        static bool configured[MGB_MAX_DEVICES] = {false};
+        if (int rc = mgb_opt_in_smem(mgb_topk_select_kernel, configured, TOPK_CHUNK_MAX * (int)sizeof(float))) return rc;
+        mgb_topk_select_kernel<<<(unsigned)ctas, MGB_BLOCK, (size_t)chunk * sizeof(float), stream>>>(d_cost, nullptr, n, chunk, index_base, k, part_cost,
+                                                                                                  part_idx, 0);
+        const long long m = ctas * k;
+        mgb_topk_select_kernel<<<1, MGB_BLOCK, (size_t)m * sizeof(float), stream>>>(part_cost, part_idx, m, m, index_base, k, d_best_cost,
+                                                                                  reinterpret_cast<long long*>(d_best_idx), 1);
+        mgb_count_launch(2);
+        MGB_CUDA(cudaGetLastError());
+        return MGB_OK;
+    }
+    // k = 1, or arrays too large for one shared-memory chunk per CTA: k passes, each a grid arg-min over the entries
+    // "after" the previous pick
     long long* part_idx = reinterpret_cast<long long*>(ws);
     float* part_cost = reinterpret_cast<float*>(ws + parts * sizeof(long long));
     long long n_tiles = (n + MGB_BLOCK - 1) / MGB_BLOCK;

@@ -199,7 +199,7 @@ class DeviceModel(object):
 
     def workspace(self):
         torch = _torch()
-        nbytes = int(self.lib.mgb_score_workspace_bytes(0, 1))
+        nbytes = int(self.lib.mgb_score_workspace_bytes(0, 64))      # large enough for every k (top-k keeps its partials in it)
         if self._ws is None or self._ws.numel() < nbytes:
             self._ws = torch.zeros(nbytes, dtype=torch.uint8, device=self.torch_device)
         return self._ws

@@ -916,3 +916,39 @@ def test_time_warped_motion_matches_the_reference():
         fr = spline.get_motion_vector()
         assert fr.shape == g["tw%d_frames" % i].shape
         assert rel_err(fr, g["tw%d_frames" % i]).max() < RTOL
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n", [0, 1, 3, 255, 4097, 100_003, 1_000_000])
+def test_topk_kernel_against_numpy(n):
+    """K5c through the C-ABI (mgb_topk) on raw cost arrays: order (cost, global index) ascending, ties -> lowest
+    index, NaN never selected, +inf selectable, slots beyond the selectable entries = (inf, index_base)
+    (the reference keeps the first minimum: motion_primitive_generator.py:245-252)."""
+    import ctypes as C
+    import torch
+    from morphablegraphs_b200 import _lib
+    lib = _lib.load()
+    rs = np.random.RandomState(n + 7)
+    cost = rs.randint(0, max(2, n // 3 + 1), size=n).astype(np.float32)      # many ties
+    if n > 10:
+        cost[rs.randint(0, n, size=n // 10)] = np.nan
+        cost[rs.randint(0, n, size=5)] = np.inf
+        cost[rs.randint(0, n, size=3)] = -np.inf
+    base = 12345
+    d_cost = torch.as_tensor(cost, device="cuda") if n else torch.zeros(1, device="cuda")
+    for k in (1, 5, 64):
+        ws = torch.zeros(int(lib.mgb_score_workspace_bytes(n, k)), dtype=torch.uint8, device="cuda")
+        bc = torch.empty(k, dtype=torch.float32, device="cuda")
+        bi = torch.empty(k, dtype=torch.int64, device="cuda")
+        rc = lib.mgb_topk(C.c_void_p(d_cost.data_ptr()), n, base, k, C.c_void_p(bc.data_ptr()), C.c_void_p(bi.data_ptr()),
+                          C.c_void_p(ws.data_ptr()), ws.numel(), C.c_void_p(torch.cuda.current_stream().cuda_stream))
+        assert rc == 0, lib.mgb_last_error().decode()
+        torch.cuda.synchronize()
+        ok = np.where(~np.isnan(cost))[0]
+        order = ok[np.lexsort((ok, cost[ok]))][:k]
+        want_i = np.full(k, base, dtype=np.int64)
+        want_c = np.full(k, np.inf, dtype=np.float32)
+        want_i[:len(order)] = order + base
+        want_c[:len(order)] = cost[order]
+        assert list(bi.cpu().numpy()) == list(want_i), (n, k)
+        assert np.array_equal(bc.cpu().numpy(), want_c), (n, k)
