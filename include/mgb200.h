@@ -362,6 +362,21 @@ int mgb_logpdf(const mgb_model* m, const float* d_s, int64_t n, float* d_logpdf,
 int mgb_topk(const float* d_cost, int64_t n, int64_t index_base, int32_t k, float* d_best_cost,
              int64_t* d_best_idx, void* d_workspace, size_t workspace_bytes, void* stream);
 
+/* K5c without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid it).  Same result as mgb_topk (bit-identical costs and indices), but the
+ * scratch (per-CTA partial selections) is a file-scope device array inside the library instead of a caller
+ * workspace: MGB_TOPK_NOALLOC_SCRATCH_BYTES of device memory on every GPU that loads the library, held until
+ * exit.  The call makes no cudaMalloc / cudaFree / allocating library call; inputs and outputs are the caller's.
+ * Limits: n <= MGB_TOPK_NOALLOC_MAX_N and 1 <= k <= 64, beyond them MGB_E_* with a message (use mgb_topk).
+ * The array is shared by every call on a device and keeps the last call's contents (nothing in it has
+ * to start at zero, so nothing is cleared): calls that overlap on the GPU - two streams, two host
+ * threads - race; serialise them on one stream or with events. */
+#define MGB_TOPK_NOALLOC_MAX_N 16777216            /* costs per call */
+#define MGB_TOPK_NOALLOC_SCRATCH_BYTES 454656      /* 592 CTAs x 64 picks x (int64 index + float cost) */
+int mgb_topk_noalloc(const float* d_cost, int64_t n, int64_t index_base, int32_t k, float* d_best_cost,
+                     int64_t* d_best_idx, void* stream);
+
 /* K7: one Lloyd iteration (E-step + M-step sums) for every node of a cluster-tree level at once.
  * x[n, dim] (row stride ld) with the samples of one node stored contiguously (any order is
  * accepted; runs of equal node ids are what makes the accumulation cheap), node[n] = tree node of

@@ -101,6 +101,7 @@ class Option(C.Structure):
 
 CT_POSITION, CT_RELATIVE, CT_DIR2D, CT_POSE, CT_TWO_HANDS, CT_FEET, CT_LOOK_AT, CT_CA, CT_JOINT_ROT, CT_QUAT_FRAME, CT_LOCAL_TRAJ = range(11)
 MAX_POSE_POINTS = 32
+TOPK_NOALLOC_MAX_N = 16777216          # include/mgb200.h MGB_TOPK_NOALLOC_MAX_N
 
 # every symbol include/mgb200.h declares: (restype, argtypes)
 _vp, _i32, _i64, _f, _sz = C.c_void_p, C.c_int32, C.c_int64, C.c_float, C.c_size_t
@@ -136,6 +137,7 @@ SYMBOLS = {
     "mgb_score_frames": (C.c_int, [_vp, _vp, _vp, _vp, _i64, _i64, _f, _f, _f, _vp, _vp, _i32, _vp, _vp, _vp, _sz, _vp]),
     "mgb_logpdf": (C.c_int, [_vp, _vp, _i64, _vp, _vp]),
     "mgb_topk": (C.c_int, [_vp, _i64, _i64, _i32, _vp, _vp, _vp, _sz, _vp]),
+    "mgb_topk_noalloc": (C.c_int, [_vp, _i64, _i64, _i32, _vp, _vp, _vp]),
     "mgb_kmeans_assign_update": (C.c_int, [_vp, _i64, _i32, _i32, _vp, _vp, _i32, _vp, _vp, _vp, _vp, _vp]),
     "mgb_kmeans_level": (C.c_int, [_vp, _i64, _i32, _i32, _i32, _vp, _i32, _i32, _vp, _vp, _i32, _i32, _vp, _vp, _vp, _vp, _vp,
                                    C.POINTER(C.c_int32), _vp]),

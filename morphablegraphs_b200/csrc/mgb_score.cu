@@ -914,3 +914,66 @@ extern "C" int mgb_topk(const float* d_cost, int64_t n, int64_t index_base, int3
     MGB_CUDA(cudaGetLastError());
     return MGB_OK;
 }
+
+// ---------------------------------------------------------------------------
+// mgb_topk_noalloc: K5c for callers that cannot allocate (code under CUDA graph capture, tight serving loops, harnesses
+// that forbid cudaMalloc).  No counterpart in the reference.
+// Same two launches as mgb_topk's one-pass form, but the stage-1 partials live in a file-scope device array instead of
+// a caller workspace: MGB_TOPK_NOALLOC_SCRATCH_BYTES (444 KB) held by every GPU that loads the library, until exit.
+// Nothing in the array has to start at zero (stage 1 writes all ctas * k slots stage 2 reads), so nothing is cleared;
+// every call shares it, so two calls that overlap on the GPU (different streams, or different host threads) race.
+// ---------------------------------------------------------------------------
+namespace {
+constexpr size_t TOPK_NOALLOC_IDX_BYTES = (size_t)TOPK_MAX_CTAS * 64 * sizeof(long long);
+constexpr size_t TOPK_NOALLOC_BYTES = TOPK_NOALLOC_IDX_BYTES + (size_t)TOPK_MAX_CTAS * 64 * sizeof(float);
+static_assert(TOPK_NOALLOC_BYTES == MGB_TOPK_NOALLOC_SCRATCH_BYTES, "header and kernel disagree on the scratch size");
+static_assert((long long)MGB_TOPK_NOALLOC_MAX_N <= (long long)TOPK_MAX_CTAS * TOPK_CHUNK_MAX, "a chunk must fit shared memory");
+}  // namespace
+
+static __device__ __align__(256) unsigned char mgb_topk_noalloc_scratch[TOPK_NOALLOC_BYTES];
+
+// Device address of the scratch array on the CURRENT device.  The array's name is only a host-side stand-in in host code;
+// the address a kernel can use comes from cudaGetSymbolAddress, asked once per device with that device current.
+static int topk_noalloc_scratch_ptr(unsigned char** out) {
+    static unsigned char* addr[MGB_MAX_DEVICES] = {nullptr};
+    static std::mutex mu;
+    int dev = 0;
+    MGB_CUDA(cudaGetDevice(&dev));
+    MGB_REQUIRE(dev >= 0 && dev < MGB_MAX_DEVICES, "device ordinal %d beyond the %d the library keeps per-device state for", dev, MGB_MAX_DEVICES);
+    std::lock_guard<std::mutex> lock(mu);
+    if (!addr[dev]) {
+        void* p = nullptr;
+        MGB_CUDA(cudaGetSymbolAddress(&p, mgb_topk_noalloc_scratch));
+        MGB_REQUIRE(p, "cudaGetSymbolAddress returned a null address for the top-k scratch");
+        addr[dev] = reinterpret_cast<unsigned char*>(p);
+    }
+    *out = addr[dev];
+    return MGB_OK;
+}
+
+extern "C" int mgb_topk_noalloc(const float* d_cost, int64_t n, int64_t index_base, int32_t k, float* d_best_cost,
+                                int64_t* d_best_idx, void* stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    MGB_REQUIRE(d_cost && d_best_cost && d_best_idx, "null pointer");
+    MGB_REQUIRE(k >= 1 && k <= 64, "k must be in [1, 64]");
+    MGB_REQUIRE(n >= 0, "negative n");
+    MGB_REQUIRE(n <= (int64_t)MGB_TOPK_NOALLOC_MAX_N, "mgb_topk_noalloc handles at most %lld costs per call (got %lld): use mgb_topk with a workspace",
+                (long long)MGB_TOPK_NOALLOC_MAX_N, (long long)n);
+    unsigned char* tk = nullptr;
+    if (int rc = topk_noalloc_scratch_ptr(&tk)) return rc;
+    const long long ctas = std::max<long long>(1, std::min<long long>((n + 4095) / 4096, TOPK_MAX_CTAS));
+    const long long chunk = std::max<long long>(1, (n + ctas - 1) / ctas);
+    MGB_REQUIRE(chunk <= TOPK_CHUNK_MAX && ctas * k <= TOPK_CHUNK_MAX, "internal: chunk %lld does not fit shared memory", chunk);
+    long long* part_idx = reinterpret_cast<long long*>(tk);
+    float* part_cost = reinterpret_cast<float*>(tk + TOPK_NOALLOC_IDX_BYTES);
+    static bool configured[MGB_MAX_DEVICES] = {false};
+    if (int rc = mgb_opt_in_smem(mgb_topk_select_kernel, configured, TOPK_CHUNK_MAX * (int)sizeof(float))) return rc;
+    mgb_topk_select_kernel<<<(unsigned)ctas, MGB_BLOCK, (size_t)chunk * sizeof(float), stream>>>(d_cost, nullptr, n, chunk, index_base, k, part_cost,
+                                                                                              part_idx, 0);
+    const long long m = ctas * k;
+    mgb_topk_select_kernel<<<1, MGB_BLOCK, (size_t)m * sizeof(float), stream>>>(part_cost, part_idx, m, m, index_base, k, d_best_cost,
+                                                                              reinterpret_cast<long long*>(d_best_idx), 1);
+    mgb_count_launch(2);
+    MGB_CUDA(cudaGetLastError());
+    return MGB_OK;
+}
