@@ -98,6 +98,8 @@ typedef struct {
 #define MGB_CT_JOINT_ROT 8  /* JointRotationConstraint (joint_rotation_constraint.py:62-75)            */
 #define MGB_CT_QUAT_FRAME 9 /* keyframe_pose given as a quaternion frame: PoseConstraintQuatFrame      */
 #define MGB_CT_LOCAL_TRAJ 10 /* local_trajectory: LocalTrajectoryConstraint, sum over all frames       */
+#define MGB_CT_TRAJ 11       /* trajectory: TrajectoryConstraint, closest point per frame, mean over frames */
+#define MGB_CT_TRAJ_SET 12   /* trajectory_set: TrajectorySetConstraint, arc-length walk of several joints  */
 
 #define MGB_MAX_POSE_POINTS 32
 
@@ -128,6 +130,22 @@ typedef struct {
  *             (n_points - 2) * step = full arc length, last entry = the last control point
  *             (returned beyond the end); only target x and z are read
  *             (local_trajectory_constraint.py:58-83, parameterized_spline.py:131-148)
+ *  TRAJ     : node[0], time_slot = first of n_slots consecutive slots = the frames of the motion vector
+ *             (times linspace(0, F, F), motion_primitive.py:233), offset[0] = the parameter the search of the
+ *             first frame starts from (min_arc_length / full_arc_length), points_offset/n_points: the spline
+ *             at parameter i / (n_points - 1).  Per frame the closest point of the curve at a parameter >= the
+ *             previous frame's (the reference minimises |S(u) - p| with L-BFGS-B from that bound,
+ *             parameterized_spline.py:303-322; here: the first local minimum of the distance to the tabulated
+ *             polyline walking up from the bound); error = mean over the frames of the distances
+ *             (trajectory_constraint.py:78-116)
+ *  TRAJ_SET : node[1] = number of joint trajectories J (<= 8), time_slot / n_slots as TRAJ; points: per
+ *             trajectory a block of 2 header points + n + 2 table points, all with node = the joint:
+ *             header 0 target = (arc-length step, initial arc length, n), header 1 target = (range_start,
+ *             range_end, 1 if a range is set else 0); table = the trajectory at arc length i * step, i = 0..n,
+ *             then the last control point.  Per frame |mean of all joint coordinates - mean of all target
+ *             coordinates| if any trajectory is active at its walked arc length, the walk advancing by the
+ *             joint's own path AFTER the frame is scored; error = mean over the frames
+ *             (trajectory_set_constraint.py:83-105)
  */
 typedef struct {
     int32_t type;

@@ -99,7 +99,7 @@ class Option(C.Structure):
                 ("magnitude_scale", C.c_float)]
 
 
-CT_POSITION, CT_RELATIVE, CT_DIR2D, CT_POSE, CT_TWO_HANDS, CT_FEET, CT_LOOK_AT, CT_CA, CT_JOINT_ROT, CT_QUAT_FRAME, CT_LOCAL_TRAJ = range(11)
+CT_POSITION, CT_RELATIVE, CT_DIR2D, CT_POSE, CT_TWO_HANDS, CT_FEET, CT_LOOK_AT, CT_CA, CT_JOINT_ROT, CT_QUAT_FRAME, CT_LOCAL_TRAJ, CT_TRAJ, CT_TRAJ_SET = range(13)
 MAX_POSE_POINTS = 32
 TOPK_NOALLOC_MAX_N = 16777216          # include/mgb200.h MGB_TOPK_NOALLOC_MAX_N
 

@@ -270,7 +270,155 @@ def tabulate_trajectory(trajectory, n=ArcLengthTable.N_DEFAULT):
     return table
 
 
+class ParameterTable(object):
+    """A curve tabulated by its own parameter: `points[i]` = the curve at u = i / (len(points) - 1), linear in
+    between.  The form in which the engine ships the spline of a TrajectoryConstraint to the device."""
+
+    N_DEFAULT = 2048
+
+    def __init__(self, points):
+        self.points = np.ascontiguousarray(points, dtype=np.float64)
+
+    def query_point_by_parameter(self, u):
+        x = min(max(float(u), 0.0), 1.0) * (len(self.points) - 1)
+        i = min(int(x), len(self.points) - 2)
+        return self.points[i] + (x - i) * (self.points[i + 1] - self.points[i])
+
+
+def tabulate_by_parameter(trajectory, n=ParameterTable.N_DEFAULT):
+    """ParameterTable of an object with the reference's `query_point_by_parameter(u)` (parameterized_spline.py:129-130),
+    cached on the object like `tabulate_trajectory`."""
+    if isinstance(trajectory, ParameterTable):
+        return trajectory
+    cached = getattr(trajectory, "_mgb_param_table", None)
+    key = (float(getattr(trajectory, "full_arc_length", 0.0)), n)
+    if cached is not None and cached[0] == key:
+        return cached[1]
+    pts = np.array([np.asarray(trajectory.query_point_by_parameter(i / float(n)), dtype=np.float64).reshape(-1)[:3] for i in range(n + 1)])
+    table = ParameterTable(pts)
+    try:
+        trajectory._mgb_param_table = (key, table)
+    except AttributeError:
+        pass
+    return table
+
+
+class CatmullRomTrajectory(object):
+    """A Catmull-Rom curve through `control_points` with an arc-length map over `granularity` equal parameter steps: the
+    queries of the reference's ParameterizedSpline over its CatmullRomSpline that the trajectory constraints use
+    (splines/catmull_rom_spline.py:120-182: uniform segments, end points doubled, the four neighbouring control points
+    blended by the 0.5-scaled Catmull-Rom basis; splines/arc_length_map.py:45-70 and :86-99: accumulated chord lengths at
+    the steps, inverted by linear interpolation between the bracketing steps; parameterized_spline.py:131-156)."""
+
+    BASIS = 0.5 * np.array([[-1.0, 3.0, -3.0, 1.0], [2.0, -5.0, 4.0, -1.0], [-1.0, 0.0, 1.0, 0.0], [0.0, 2.0, 0.0, 0.0]])
+
+    def __init__(self, control_points, granularity=1000):
+        cp = [np.asarray(p, dtype=np.float64) for p in control_points]
+        if len(cp) < 2:
+            raise ValueError("Not enough control points in trajectory constraint definition")
+        self.number_of_segments = len(cp) - 1
+        self.control_points = np.array([cp[0]] + cp + [cp[-1], cp[-1]])
+        self.granularity = int(granularity)
+        u = np.arange(self.granularity + 1) / float(self.granularity)
+        pts = np.array([self.query_point_by_parameter(x) for x in u])
+        acc = np.concatenate([[0.0], np.cumsum(np.linalg.norm(np.diff(pts, axis=0), axis=1))])
+        self.full_arc_length = float(acc[-1])
+        if self.full_arc_length == 0:
+            raise ValueError("Not enough control points in trajectory constraint definition")
+        self._u = u
+        self._rel = acc / self.full_arc_length
+
+    def get_last_control_point(self):
+        return np.array(self.control_points[-1])
+
+    def query_point_by_parameter(self, u):
+        x = self.number_of_segments * float(u)
+        i = min(int(np.floor(x)), self.number_of_segments)
+        if i + 1 > self.number_of_segments:
+            return np.array(self.control_points[-1])
+        t = x - i
+        return np.array([t ** 3, t ** 2, t, 1.0]).dot(self.BASIS).dot(self.control_points[i:i + 4])
+
+    def map_relative_arc_length_to_parameter(self, rel):
+        if rel <= self._rel[0]:
+            return self._u[0]
+        if rel >= self._rel[-1]:
+            return self._u[-1]
+        i = int(np.searchsorted(self._rel, rel, side="right")) - 1     # last step with arc length <= rel
+        if self._rel[i] == rel:
+            return self._u[i]
+        return self._u[i] + (rel - self._rel[i]) / (self._rel[i + 1] - self._rel[i]) * (self._u[i + 1] - self._u[i])
+
+    def query_point_by_absolute_arc_length(self, absolute_arc_length):
+        if absolute_arc_length <= self.full_arc_length:
+            return self.query_point_by_parameter(self.map_relative_arc_length_to_parameter(absolute_arc_length / self.full_arc_length))
+        return self.get_last_control_point()
+
+
+class TrajectoryConstraint(CatmullRomTrajectory, SpatialConstraintBase):
+    """reference trajectory_constraint.py:33-53 (constructor signature and attribute names).  Only the Catmull-Rom spline
+    type (0, the reference's default) is restated; the orientation spline is not part of the error and is not kept.
+    The engine reads `joint_name`, `min_arc_length`, `full_arc_length`, `query_point_by_parameter` and `weight_factor`,
+    so the reference's own object is accepted as well."""
+
+    def __init__(self, joint_name, control_points, orientations, spline_type, min_arc_length, unconstrained_indices, skeleton, precision,
+                 weight_factor=1.0, closest_point_search_accuracy=0.001, closest_point_search_max_iterations=5000, granularity=1000):
+        if spline_type not in (0, None):
+            raise NotImplementedError("only Catmull-Rom trajectories (spline_type 0) are restated")
+        CatmullRomTrajectory.__init__(self, control_points, granularity)
+        SpatialConstraintBase.__init__(self, precision, weight_factor)
+        self.semantic_annotation = None
+        self.constraint_type = SPATIAL_CONSTRAINT_TYPE_TRAJECTORY
+        self.joint_name = joint_name
+        self.skeleton = skeleton
+        self.min_arc_length = min_arc_length
+        self.n_canonical_frames = 0
+        self.arc_length = 0.0
+        self.unconstrained_indices = unconstrained_indices
+        self.range_start = None
+        self.range_end = None
+        self.is_collision_avoidance_constraint = False
+
+    def set_active_range(self, new_range_start, new_range_end):
+        self.range_start = new_range_start
+        self.range_end = new_range_end
+
+    def set_number_of_canonical_frames(self, n_canonical_frames):
+        self.n_canonical_frames = n_canonical_frames
+
+    def is_active(self, arc_length):
+        return self.range_start is not None and self.range_start <= arc_length <= self.range_end
+
+    def get_length_of_residual_vector(self):
+        return self.n_canonical_frames
+
+
+class TrajectorySetConstraint(SpatialConstraintBase):
+    """reference trajectory_set_constraint.py:29-40, :55-56: several joint trajectories (objects with the TrajectoryConstraint
+    interface: `query_point_by_absolute_arc_length`, `full_arc_length`, `get_last_control_point`, `range_start`,
+    `range_end`) walked by the arc length of each joint's own path, starting at `joint_arc_lengths`."""
+
+    def __init__(self, joint_trajectories, joint_names, skeleton, precision, weight_factor):
+        super(TrajectorySetConstraint, self).__init__(precision, weight_factor)
+        self.skeleton = skeleton
+        self.constraint_type = SPATIAL_CONSTRAINT_TYPE_TRAJECTORY_SET
+        self.joint_trajectories = joint_trajectories
+        self.joint_names = joint_names
+        self.joint_arc_lengths = np.zeros(len(self.joint_trajectories))
+        self.semantic_annotation = dict()
+        self.semantic_annotation["generated"] = True
+        self.n_canonical_frames = 0
+
+    def set_number_of_canonical_frames(self, n_canonical_frames):
+        self.n_canonical_frames = n_canonical_frames
+
+    def get_length_of_residual_vector(self):
+        return self.n_canonical_frames
+
+
 CONSTRAINT_FACTORY = {
+    "TrajectoryConstraint": TrajectoryConstraint,
+    "TrajectorySetConstraint": TrajectorySetConstraint,
     "JointRotationConstraint": JointRotationConstraint,
     "PoseConstraintQuatFrame": PoseConstraintQuatFrame,
     "LocalTrajectoryConstraint": LocalTrajectoryConstraint,

@@ -480,6 +480,7 @@ extern "C" int mgb_constraints_pack(const mgb_model* m, const mgb_constraint_des
     auto check_node = [&](int nd) { return nd >= 0 && nd < m->n_nodes; };
     auto check_slot = [&](int s) { return s >= 0 && s < n_times; };
     std::map<int, int> lt_term_of_scratch;   // local-trajectory scratch offset -> constraint (residual-vector program)
+    std::map<int, int> frame_term_of_scratch;   // trajectory / trajectory-set scratch offset -> constraint
     struct Final { int code, a, b; std::vector<float> cst; };
     std::vector<Final> finals;
     std::vector<MgbOp> begins;
@@ -641,6 +642,71 @@ extern "C" int mgb_constraints_pack(const mgb_model* m, const mgb_constraint_des
                 finals.push_back({OP_LT_END, j, sc, {w}});
                 break;
             }
+            case MGB_CT_TRAJ: {
+                MGB_REQUIRE(check_node(c.node[0]) && c.n_slots > 0 && check_slot(c.time_slot) && check_slot(c.time_slot + c.n_slots - 1),
+                            "constraint %d: bad node / slot range", j);
+                MGB_REQUIRE(c.n_points >= 2 && points && c.points_offset >= 0 && c.points_offset + c.n_points <= n_points,
+                            "constraint %d: bad trajectory table", j);
+                MGB_REQUIRE(c.offset[0] >= 0.0 && c.offset[0] <= 1.0, "constraint %d: the start parameter must lie in [0, 1]", j);
+                const int sc = C.alloc_scratch(2);
+                MgbOp b;
+                b.code = OP_SCR_INIT; b.a = sc; b.b = 2; b.c = C.push_cst({0.f, (float)c.offset[0]});
+                begins.push_back(b);
+                const int nt = c.n_points - 1;
+                std::vector<float> v = {(float)nt, w, 0.f, 0.f};
+                for (int q = 0; q < c.n_points; ++q)
+                    for (int i = 0; i < 3; ++i) v.push_back((float)points[c.points_offset + q].target[i]);
+                const int tab_off = C.push_cst(v);
+                frame_term_of_scratch[sc] = j;
+                for (int f = 0; f < c.n_slots; ++f) {
+                    Action a{OP_TR_ACC, sc, 0, {}};
+                    a.cst_at = tab_off;
+                    C.add(c.time_slot + f, c.node[0], a);
+                }
+                finals.push_back({OP_MEAN_END, j, sc, {w, (float)(1.0 / c.n_slots)}});
+                break;
+            }
+            case MGB_CT_TRAJ_SET: {
+                const int J = c.node[1];
+                MGB_REQUIRE(J >= 1 && J <= 8, "constraint %d: a trajectory set holds 1 .. 8 joint trajectories", j);
+                MGB_REQUIRE(c.n_slots > 0 && check_slot(c.time_slot) && check_slot(c.time_slot + c.n_slots - 1), "constraint %d: bad slot range", j);
+                MGB_REQUIRE(points && c.points_offset >= 0 && c.points_offset + c.n_points <= n_points, "constraint %d: bad trajectory tables", j);
+                const int sc = C.alloc_scratch(3 + 5 * J);
+                std::vector<float> init(3 + 5 * J, 0.f);
+                int at = c.points_offset;
+                const int end = c.points_offset + c.n_points;
+                std::vector<int> joint_node(J), tab_off(J);
+                for (int jj = 0; jj < J; ++jj) {
+                    MGB_REQUIRE(at + 2 <= end, "constraint %d: trajectory %d: header missing", j, jj);
+                    const mgb_pose_point& h0 = points[at];
+                    const mgb_pose_point& h1 = points[at + 1];
+                    const double step = h0.target[0], arc0 = h0.target[1];
+                    const int nt = (int)h0.target[2];
+                    MGB_REQUIRE(check_node(h0.node) && step > 0.0 && nt >= 1 && at + 2 + nt + 2 <= end, "constraint %d: trajectory %d: bad header / table", j, jj);
+                    joint_node[jj] = h0.node;
+                    init[3 + 5 * jj] = (float)arc0;
+                    const bool ranged = h1.target[2] != 0.0;
+                    // no range set: never active (trajectory_constraint.py:150-151)
+                    std::vector<float> v = {(float)(1.0 / step), (float)nt, (float)(nt * step), ranged ? (float)h1.target[0] : 1.f,
+                                            ranged ? (float)h1.target[1] : 0.f, (float)(1.0 / (3.0 * J)), w, 0.f};
+                    for (int q = 0; q < nt + 2; ++q)
+                        for (int i = 0; i < 3; ++i) v.push_back((float)points[at + 2 + q].target[i]);
+                    tab_off[jj] = C.push_cst(v);
+                    at += 2 + nt + 2;
+                }
+                MgbOp b;
+                b.code = OP_SCR_INIT; b.a = sc; b.b = 3 + 5 * J; b.c = C.push_cst(init);
+                begins.push_back(b);
+                frame_term_of_scratch[sc] = j;
+                for (int f = 0; f < c.n_slots; ++f)
+                    for (int jj = 0; jj < J; ++jj) {
+                        Action a{OP_TS_ACC, sc, jj << 1, {}};
+                        a.cst_at = tab_off[jj];
+                        C.add(c.time_slot + f, joint_node[jj], a);
+                    }
+                finals.push_back({OP_MEAN_END, j, sc, {w, (float)(1.0 / c.n_slots)}});
+                break;
+            }
             default:
                 mgb_set_error("constraint %d: type %d is outside the device path", j, c.type);
                 return MGB_E_UNSUPPORTED;
@@ -692,6 +758,16 @@ extern "C" int mgb_constraints_pack(const mgb_model* m, const mgb_constraint_des
             }
         }
     }
+    {
+        // trajectory sets: the J joint ops of a frame arrive in the order of the skeleton walk (the same in every frame); the
+        // J-th one closes the frame
+        std::map<int, int> met;
+        for (MgbOp& o : C.ops)
+            if (o.code == OP_TS_ACC) {
+                const int J = cd[frame_term_of_scratch[o.a]].node[1];
+                if (++met[o.a] % J == 0) o.b |= 1;
+            }
+    }
     c->ops_fused = C.ops;
     // ---- residual-vector program: residual layout = constraints in list order, each with the residuals
     //      its class returns from get_residual_vector_spline (1; two hands 3; pose / quaternion frame one per point; local
@@ -702,7 +778,7 @@ extern "C" int mgb_constraints_pack(const mgb_model* m, const mgb_constraint_des
             int cnt = 1;
             if (cd[j].type == MGB_CT_TWO_HANDS) cnt = 3;
             else if (cd[j].type == MGB_CT_POSE || cd[j].type == MGB_CT_QUAT_FRAME) cnt = cd[j].n_points;
-            else if (cd[j].type == MGB_CT_LOCAL_TRAJ) cnt = cd[j].n_slots;
+            else if (cd[j].type == MGB_CT_LOCAL_TRAJ || cd[j].type == MGB_CT_TRAJ || cd[j].type == MGB_CT_TRAJ_SET) cnt = cd[j].n_slots;
             res_base[j + 1] = res_base[j] + cnt;
         }
         c->n_resid = res_base[n];
@@ -720,6 +796,17 @@ extern "C" int mgb_constraints_pack(const mgb_model* m, const mgb_constraint_des
                 case OP_LT_ACC: {
                     const int term = lt_term_of_scratch[o.a];
                     o.b = res_base[term] + seen[term]++;
+                    break;
+                }
+                case OP_TR_ACC: {
+                    const int term = frame_term_of_scratch[o.a];
+                    o.b = res_base[term] + seen[term]++;
+                    break;
+                }
+                case OP_TS_ACC: {
+                    const int term = frame_term_of_scratch[o.a];
+                    o.b = (o.b & 255) | ((res_base[term] + seen[term]) << 8);
+                    if (o.b & 1) ++seen[term];
                     break;
                 }
                 default:

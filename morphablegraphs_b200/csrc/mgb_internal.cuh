@@ -98,6 +98,14 @@ enum MgbOpCode : int32_t {
     OP_LT_ACC = 21,   // a = scratch offset, b = residual index (residual program), c -> 1 / step, n_table, full arc length, weight,
                       // table (x, z) * (n_table + 2) [entry n_table + 1 = last control point]
     OP_LT_END = 22,   // a = term, b = scratch offset, c -> weight
+    OP_SCR_INIT = 23, // a = scratch offset, b = count, c -> values[count]: scratch[a + i] = values[i]
+    OP_TR_ACC = 24,   // TrajectoryConstraint, one frame: a = scratch offset (2 floats: sum, min_u), b = residual index (residual
+                      // program), c -> n_table, weight, 0, 0, table (x, y, z) * (n_table + 1) [the spline at parameter i / n_table]
+    OP_TS_ACC = 25,   // TrajectorySetConstraint, one joint of one frame: a = scratch offset (3 + 5 J floats: sum, frame
+                      // accumulator, any-active; per joint arc length, last position[3], started), b = residual index << 8 |
+                      // joint << 1 | closes-the-frame, c -> 1 / step, n_table, full arc length, range start, range end,
+                      // 1 / (3 J), weight, 0, table (x, y, z) * (n_table + 2) [by arc length; last entry = last control point]
+    OP_MEAN_END = 26, // a = term, b = scratch offset, c -> weight, 1 / n_frames: term = scratch[b] / n_frames
 };
 
 #define MGB_SCRATCH_FLOATS 160

@@ -361,6 +361,102 @@ struct MgbInterp {
                     for (int c = 0; c < CPT; ++c) emit(c, op.a, cs[0], scratch[c][op.b]);
                     break;
                 }
+                case OP_SCR_INIT: {
+                    for (int i = 0; i < op.b; ++i) {
+                        const float v = cs[i];
+#pragma unroll
+                        for (int c = 0; c < CPT; ++c) scratch[c][op.a + i] = v;
+                    }
+                    break;
+                }
+                case OP_TR_ACC: {
+                    // TrajectoryConstraint.get_residual_vector (trajectory_constraint.py:95-116): the closest point of the curve at
+                    // a parameter >= the previous frame's.  The reference runs L-BFGS-B on |S(u) - p| from the lower bound
+                    // (parameterized_spline.py:303-322); here the curve is a polyline over n_table equal parameter steps and the
+                    // walk goes up from the bound until the distance rises again (the first local minimum).
+                    const int nt = (int)cs[0];
+                    const float* tb = cs + 4;
+#pragma unroll
+                    for (int c = 0; c < CPT; ++c) {
+                        float* st = scratch[c] + op.a;
+                        const float px = G[c].tx, py = G[c].ty, pz = G[c].tz;
+                        const float x0 = fminf(fmaxf(st[1], 0.f), 1.f) * (float)nt;
+                        const int i0 = min((int)x0, nt - 1);
+                        float lo = x0 - (float)i0;
+                        float best = 0.f, best_x = x0;
+                        // walk up while the distance still falls at the END of the segment, i.e. while the foot of the perpendicular
+                        // lies beyond it (decided on the projection, not by comparing squared distances: far from the curve
+                        // their differences drown in float32 rounding)
+                        for (int i = i0; i < nt; ++i) {
+                            const float ax = tb[3 * i], ay = tb[3 * i + 1], az = tb[3 * i + 2];
+                            const float dx = tb[3 * i + 3] - ax, dy = tb[3 * i + 4] - ay, dz = tb[3 * i + 5] - az;
+                            const float ex = px - ax, ey = py - ay, ez = pz - az;
+                            const float dd = fmaf(dx, dx, fmaf(dy, dy, dz * dz));
+                            const float pr = fmaf(ex, dx, fmaf(ey, dy, ez * dz));
+                            if (pr >= dd && i + 1 < nt) {   // includes dd == 0 with pr == 0: a repeated point, step over it
+                                lo = 0.f;
+                                continue;
+                            }
+                            const float sgm = fminf(fmaxf(dd > 0.f ? __fdividef(pr, dd) : lo, lo), 1.f);
+                            const float rx = fmaf(-sgm, dx, ex), ry = fmaf(-sgm, dy, ey), rz = fmaf(-sgm, dz, ez);
+                            best = fmaf(rx, rx, fmaf(ry, ry, rz * rz));
+                            best_x = (float)i + sgm;
+                            break;
+                        }
+                        const float e = sqrtf(best);
+                        st[0] += e;
+                        st[1] = best_x / (float)nt;
+                        if (RESID) emit(c, op.b, cs[1], e);
+                    }
+                    break;
+                }
+                case OP_TS_ACC: {
+                    // TrajectorySetConstraint.get_residual_vector (trajectory_set_constraint.py:83-105): every joint walks its own
+                    // trajectory by the arc length of its own path; a frame is scored with the arc lengths reached BEFORE it
+                    const float step_inv = cs[0], full = cs[2], r0 = cs[3], r1 = cs[4];
+                    const int nt = (int)cs[1];
+                    const float* tb = cs + 8;
+                    const int jj = (op.b >> 1) & 127;
+#pragma unroll
+                    for (int c = 0; c < CPT; ++c) {
+                        float* st = scratch[c] + op.a;
+                        float* js = st + 3 + 5 * jj;
+                        const float px = G[c].tx, py = G[c].ty, pz = G[c].tz;
+                        const float arc = js[0];
+                        if (arc >= r0 && arc <= r1) st[2] = 1.f;
+                        float tx, ty, tz;
+                        if (arc <= full) {
+                            const float u = fmaxf(arc, 0.f) * step_inv;
+                            const int i0 = min((int)u, nt - 1);
+                            const float f = u - (float)i0;
+                            tx = fmaf(f, tb[3 * i0 + 3] - tb[3 * i0], tb[3 * i0]);
+                            ty = fmaf(f, tb[3 * i0 + 4] - tb[3 * i0 + 1], tb[3 * i0 + 1]);
+                            tz = fmaf(f, tb[3 * i0 + 5] - tb[3 * i0 + 2], tb[3 * i0 + 2]);
+                        } else {
+                            tx = tb[3 * nt + 3]; ty = tb[3 * nt + 4]; tz = tb[3 * nt + 5];
+                        }
+                        st[1] += (px - tx) + (py - ty) + (pz - tz);
+                        if (js[4] != 0.f) {
+                            const float dx = js[1] - px, dy = js[2] - py, dz = js[3] - pz;
+                            js[0] = arc + sqrtf(fmaf(dx, dx, fmaf(dy, dy, dz * dz)));
+                        }
+                        js[1] = px; js[2] = py; js[3] = pz; js[4] = 1.f;
+                        if (op.b & 1) {   // last joint of the frame
+                            const float e = st[2] != 0.f ? fabsf(st[1]) * cs[5] : 0.f;
+                            st[0] += e;
+                            st[1] = 0.f;
+                            st[2] = 0.f;
+                            if (RESID) emit(c, op.b >> 8, cs[6], e);
+                        }
+                    }
+                    break;
+                }
+                case OP_MEAN_END: {
+                    if (RESID) break;
+#pragma unroll
+                    for (int c = 0; c < CPT; ++c) emit(c, op.a, cs[0], scratch[c][op.b] * cs[1]);
+                    break;
+                }
                 default:
                     break;
             }

@@ -365,6 +365,14 @@ def flatten_constraints(dmodel, mp_constraints):
             ca_frames = max(ca_frames, int(c.n_canonical_frames))
     for f in range(ca_frames):
         slot(float(f))
+    # trajectory / trajectory-set constraints read the motion vector: its frames sit at linspace(0, F, F)
+    # (motion_primitive.py:233, quirk Q1), in consecutive slots of their own (t = 0 may repeat an integer-frame slot)
+    mv_first = -1
+    if any(c.constraint_type in ("trajectory", "trajectory_set") for c in clist):
+        mv_first = len(times)
+        for t in np.linspace(0, dmodel.F, dmodel.F):
+            slot_of.setdefault(float(t), len(times))
+            times.append(float(t))
     descs = (_lib.ConstraintDesc * max(len(clist), 1))()
     points = []
 
@@ -424,6 +432,52 @@ def flatten_constraints(dmodel, mp_constraints):
                 pp.target = (C.c_double * 3)(float(pt[0]), float(pt[1]), float(pt[2]))
                 pp.weight = 0.0
                 points.append(pp)
+        elif ct == "trajectory":
+            # TrajectoryConstraint (trajectory_constraint.py:78-116): every frame of the motion vector against the closest
+            # point of the spline at a parameter >= the previous frame's, the first search starting at
+            # min_arc_length / full_arc_length (:104) read as a spline PARAMETER (parameterized_spline.py:313-320)
+            from .constraints import tabulate_by_parameter
+            table = tabulate_by_parameter(c)
+            d.type = _lib.CT_TRAJ
+            d.node[0] = node(c.joint_name)
+            d.time_slot = mv_first
+            d.n_slots = dmodel.F
+            d.offset = (C.c_double * 4)(float(c.min_arc_length) / float(c.full_arc_length), 0.0, 0.0, 0.0)
+            d.points_offset = len(points)
+            d.n_points = len(table.points)
+            for pt in table.points:
+                pp = _lib.PosePoint()
+                pp.node = 0
+                pp.target = (C.c_double * 3)(float(pt[0]), float(pt[1]), float(pt[2]))
+                pp.weight = 0.0
+                points.append(pp)
+        elif ct == "trajectory_set":
+            # TrajectorySetConstraint (trajectory_set_constraint.py:83-105)
+            from .constraints import tabulate_trajectory
+            if int(c.n_canonical_frames) > dmodel.F or int(c.n_canonical_frames) < 1:
+                raise UnsupportedConstraintError("trajectory set over %d frames of a %d-frame motion" % (c.n_canonical_frames, dmodel.F))
+            d.type = _lib.CT_TRAJ_SET
+            d.node[1] = len(c.joint_trajectories)
+            d.time_slot = mv_first
+            d.n_slots = int(c.n_canonical_frames)
+            d.points_offset = len(points)
+
+            def header(nd, a, b, cc):
+                pp = _lib.PosePoint()
+                pp.node = nd
+                pp.target = (C.c_double * 3)(float(a), float(b), float(cc))
+                pp.weight = 0.0
+                points.append(pp)
+
+            for traj, jn, arc0 in zip(c.joint_trajectories, c.joint_names, c.joint_arc_lengths):
+                table = tabulate_trajectory(traj, 1024)
+                nd = node(jn)
+                header(nd, table.step, arc0, len(table.points) - 1)
+                ranged = getattr(traj, "range_start", None) is not None
+                header(nd, traj.range_start if ranged else 0.0, traj.range_end if ranged else 0.0, 1.0 if ranged else 0.0)
+                for pt in list(table.points) + [table.last_control_point]:
+                    header(nd, pt[0], pt[1], pt[2])
+            d.n_points = len(points) - d.points_offset
         elif ct in ("keyframe_position", "keyframe_relative_position"):
             d.type = _lib.CT_POSITION if ct == "keyframe_position" else _lib.CT_RELATIVE
             d.node[0] = node(c.joint_name)

@@ -265,6 +265,23 @@ def build_constraints(factory, skeleton, specs, trajectories=None):
     out = []
     for sp in specs:
         desc = dict(sp["desc"])
+        if sp["class"] in ("TrajectoryConstraint", "TrajectorySetConstraint"):
+            # constructor signatures of trajectory_constraint.py:33-35 / trajectory_set_constraint.py:30
+            def trajectory(t, joint_name):
+                c = factory["TrajectoryConstraint"](joint_name, [np.array(p, dtype=np.float64) for p in t["control_points"]], None, 0,
+                                                    t.get("min_arc_length", 0.0), [], skeleton, sp["precision"], sp["weight"])
+                if t.get("range") is not None:
+                    c.set_active_range(t["range"][0], t["range"][1])
+                return c
+            if sp["class"] == "TrajectoryConstraint":
+                c = trajectory(desc, desc["joint_name"])
+            else:
+                trajs = [trajectory(t, jn) for t, jn in zip(desc["trajectories"], desc["joint_names"])]
+                c = factory["TrajectorySetConstraint"](trajs, list(desc["joint_names"]), skeleton, sp["precision"], sp["weight"])
+                c.joint_arc_lengths = np.array(desc.get("joint_arc_lengths", [0.0] * len(trajs)), dtype=np.float64)
+            c.set_number_of_canonical_frames(desc["n_canonical_frames"])
+            out.append(c)
+            continue
         if isinstance(desc.get("trajectory"), dict):
             if trajectories is not None:
                 desc["trajectory"] = trajectories(desc["trajectory"])

@@ -20,6 +20,7 @@ import json
 import os
 import sys
 import contextlib
+import warnings
 
 import numpy as np
 
@@ -47,6 +48,8 @@ def reference_factory(ns):
         "JointRotationConstraint": ns.joint_rotation_constraint.JointRotationConstraint,
         "PoseConstraintQuatFrame": ns.pose_constraint_quat_frame.PoseConstraintQuatFrame,
         "LocalTrajectoryConstraint": ns.local_trajectory_constraint.LocalTrajectoryConstraint,
+        "TrajectoryConstraint": ns.trajectory_constraint.TrajectoryConstraint,
+        "TrajectorySetConstraint": ns.trajectory_set_constraint.TrajectorySetConstraint,
     }
 
 
@@ -67,11 +70,16 @@ def build_mp_constraints(ns, skeleton, specs, is_local=True):
     return mpc
 
 
-def make_specs(ns, node, skeleton, F, rng, which):
+def make_specs(ns, node, skeleton, F, rng, which, prev_frames=None):
     """Constraint specs with targets taken from held-out draws of the same model
-    (so errors are in a realistic range), SURVEY.md section 8(d)."""
+    (so errors are in a realistic range), SURVEY.md section 8(d).  prev_frames: the held-out motions are aligned to
+    them first (targets in the global frame of a non-local step)."""
     held = node.sample_low_dimensional_vectors(3)
     spl = [node.back_project(h, use_time_parameters=False) for h in held]
+    if prev_frames is not None:
+        from anim_utils.animation_data.motion_concatenation import align_quaternion_frames
+        for sp_ in spl:
+            sp_.coeffs = align_quaternion_frames(skeleton, skeleton.aligning_root_node, sp_.coeffs, prev_frames, None)
 
     def pos(k, joint, t):
         return skeleton.nodes[joint].get_global_position(spl[k].evaluate(t)).tolist()
@@ -105,6 +113,21 @@ def make_specs(ns, node, skeleton, F, rng, which):
                                "semanticAnnotation": syn.sem("path"),
                                "trajectory": {"control_points": cps, "points": tab.points.tolist(), "step": tab.step,
                                               "last_control_point": tab.last_control_point.tolist()}}, 1.0, 0.01))
+        specs.append(syn.spec("GlobalTransformConstraint",
+                              syn.position_constraint_desc("RightFoot", pos(0, "RightFoot", F - 1), F - 1, F), 1.0, 1.0))
+        return specs
+    if which == "traj":
+        # f2: the constraints that read the whole motion vector - TrajectoryConstraint (scipy closest point per frame) on the
+        # root, TrajectorySetConstraint on both hands (one trajectory with an active range, one without), plus one keyframe
+        def path(k, joint, n):
+            return [pos(k, joint, t) for t in np.linspace(0, F - 1, n)]
+        specs.append(syn.spec("TrajectoryConstraint",
+                              {"joint_name": "Hips", "control_points": path(0, "Hips", 6), "min_arc_length": 3.0,
+                               "n_canonical_frames": F}, 1.0, 0.7))
+        specs.append(syn.spec("TrajectorySetConstraint",
+                              {"joint_names": ["LeftHand", "RightHand"], "joint_arc_lengths": [0.0, 4.0], "n_canonical_frames": F,
+                               "trajectories": [{"control_points": path(1, "LeftHand", 7), "range": [5.0, 40.0]},
+                                                {"control_points": path(1, "RightHand", 7), "range": None}]}, 1.0, 1.3))
         specs.append(syn.spec("GlobalTransformConstraint",
                               syn.position_constraint_desc("RightFoot", pos(0, "RightFoot", F - 1), F - 1, F), 1.0, 1.0))
         return specs
@@ -194,6 +217,10 @@ def run_case(ns, shape, which, n_samples, seed, translation_maxima=(1.0, 1.0, 1.
         m = quaternion_matrix(quaternion_about_axis(0.7, [0, 1, 0]))
         m[:3, 3] = [120.0, 0.0, -40.0]
         prev_frames = transform_quaternion_frames(pf, m)[-3:]
+        if which == "traj":
+            # the paths of a non-local step lie where the aligned motion goes
+            specs = make_specs(ns, node, skeleton, F, rng, which, prev_frames=prev_frames)
+            mpc = build_mp_constraints(ns, skeleton, specs, is_local=False)
     out = {}
     out["samples"] = S
     out["specs_json"] = np.array(json.dumps(specs))
@@ -222,7 +249,8 @@ def run_case(ns, shape, which, n_samples, seed, translation_maxima=(1.0, 1.0, 1.
     terms = np.zeros((len(mpc.constraints), n_samples))
     costs = np.zeros(n_samples)
     obj = ns.objective_functions.obj_spatial_error_sum
-    with _quiet():
+    with _quiet(), refload.scalar_spline_parameter(ns), warnings.catch_warnings():
+        warnings.simplefilter("ignore")
         for i, s in enumerate(S):
             sp = node.back_project(s, use_time_parameters=False)
             if non_local:
@@ -234,12 +262,18 @@ def run_case(ns, shape, which, n_samples, seed, translation_maxima=(1.0, 1.0, 1.
             costs[i] = obj(s, (node, mpc, prev_frames))
     out["terms"] = terms
     out["costs"] = costs
+    if which == "traj":
+        # the residual-vector form of the same constraints (motion_primitive_constraints.py:124-146): one value per frame
+        with _quiet(), refload.scalar_spline_parameter(ns), warnings.catch_warnings():
+            warnings.simplefilter("ignore")
+            out["residual_vectors"] = np.array([mpc.get_residual_vector(node, s, prev_frames) for s in S[:16]])
     out["evaluations"] = np.array(mpc.evaluations)
     # the reference's own arg-min loop
     gen = ns.motion_primitive_generator.MotionPrimitiveGenerator.__new__(
         ns.motion_primitive_generator.MotionPrimitiveGenerator)
     gen.objective = obj
-    with _quiet():
+    with _quiet(), refload.scalar_spline_parameter(ns), warnings.catch_warnings():
+        warnings.simplefilter("ignore")
         best, min_error = gen.evaluate_samples_using_constraints(S, node, mpc, prev_frames)
     out["best_idx"] = np.array(int(np.where((S == best).all(axis=1))[0][0]))
     out["min_error"] = np.array(min_error)
@@ -316,6 +350,11 @@ def run_local_case(ns, shape="S", n_samples=64, seed=2031):
         best, min_error = gen.evaluate_samples_using_constraints(S, node, local, None)
     out["terms"] = terms
     out["costs"] = costs
+    if which == "traj":
+        # the residual-vector form of the same constraints (motion_primitive_constraints.py:124-146): one value per frame
+        with _quiet(), refload.scalar_spline_parameter(ns), warnings.catch_warnings():
+            warnings.simplefilter("ignore")
+            out["residual_vectors"] = np.array([mpc.get_residual_vector(node, s, prev_frames) for s in S[:16]])
     out["best_idx"] = np.array(int(np.where((S == best).all(axis=1))[0][0]))
     out["min_error"] = np.array(min_error)
     return out
@@ -690,6 +729,9 @@ def main():
         ("xs_mixed", dict(shape="XS", which="mixed", n_samples=32, seed=2028)),
         ("l_mixed", dict(shape="L", which="mixed", n_samples=12, seed=2029)),
     ]
+    if "--only-traj" in sys.argv:
+        cases = [("s_traj", dict(shape="S", which="traj", n_samples=48, seed=2061)),
+                 ("s_traj_nonlocal", dict(shape="S", which="traj", n_samples=24, seed=2062, non_local=True))]
     if "--only-rot" in sys.argv:
         cases = [("s_rot", dict(shape="S", which="rot", n_samples=64, seed=2033)),
                  ("s_rot_nonlocal", dict(shape="S", which="rot", n_samples=32, seed=2034, non_local=True))]
@@ -699,7 +741,7 @@ def main():
         out["coeffs"] = out["coeffs"][:8]
         np.savez_compressed(os.path.join(GOLDEN_DIR, name + ".npz"), **out)
         print(name, "costs[:3]", out["costs"][:3], "best", int(out["best_idx"]), float(out["min_error"]))
-    if "--only-rot" in sys.argv:
+    if "--only-rot" in sys.argv or "--only-traj" in sys.argv:
         return 0
     out = run_tree_case(ns)
     np.savez_compressed(os.path.join(GOLDEN_DIR, "s_tree.npz"), **out)

@@ -309,6 +309,9 @@ def term_errors(c, ma, skeleton, coeffs):
                 target = c.trajectory.query_point_by_absolute_arc_length(t)
                 err[n] += (target[0] - p[n, f, 0]) ** 2 + (target[2] - p[n, f, 2]) ** 2
         return err
+    if ct in ("trajectory", "trajectory_set"):
+        # trajectory_constraint.py:78-85 / trajectory_set_constraint.py:41-47: the average of the per-frame errors
+        return np.average(term_residuals(c, ma, skeleton, coeffs), axis=1)
     if ct in ("keyframe_position", "keyframe_relative_position"):
         frame = _frames_at(ma, coeffs, c.canonical_keyframe)
         err = np.zeros(N)
@@ -561,6 +564,10 @@ def term_residuals(c, ma, skeleton, coeffs):
             Rt = quaternion_matrix_batch((qt / np.linalg.norm(qt))[None])[0]
             out[:, i] = w[i] * np.sqrt(np.sum((Rt[None] - R) ** 2, axis=(1, 2)))
         return out
+    if ct == "trajectory":
+        return trajectory_frame_errors(c, ma, skeleton, coeffs)
+    if ct == "trajectory_set":
+        return trajectory_set_frame_errors(c, ma, skeleton, coeffs)
     if ct == "local_trajectory":
         times = list(range(int(c.n_canonical_frames)))
         p = fk_global(skeleton, eval_frames(ma, coeffs, times), c.joint_name)[1]
@@ -574,6 +581,60 @@ def term_residuals(c, ma, skeleton, coeffs):
                 out[n, f] = (target[0] - p[n, f, 0]) ** 2 + (target[2] - p[n, f, 2]) ** 2
         return out
     return term_errors(c, ma, skeleton, coeffs)[:, None]
+
+
+def trajectory_frame_errors(c, ma, skeleton, coeffs):
+    """[N, F]: TrajectoryConstraint.get_residual_vector (trajectory_constraint.py:95-116) with find_closest_point_fast
+    (splines/parameterized_spline.py:303-322): per frame a bounded L-BFGS-B minimisation of the distance between the
+    spline at parameter u and the joint position over [u of the previous frame, 1], started at the lower bound; the first
+    bound is min_arc_length / full_arc_length (a relative arc length used as a spline parameter, as the reference does).
+    Quirk Q8: scipy hands the objective a 1-element ARRAY u, and catmull_rom_spline.py:141-151 builds the ragged list
+    [u^3, u^2, u, 1] from it - numpy >= 1.24 raises there, older numpy returned a (3, 1) point whose difference with the
+    (3,) joint position broadcasts to a 3 x 3 matrix (and a (3,) point at u = 1, so the optimiser usually ends on that
+    bound).  Restated here is the distance the code states, with u read as the scalar it is."""
+    from scipy.optimize import minimize
+    p = fk_global(skeleton, eval_frames(ma, coeffs, motion_vector_times(ma.F)), c.joint_name)[1]      # [N, F, 3]
+    N, F = p.shape[0], p.shape[1]
+    out = np.zeros((N, F))
+
+    def dist(u, q):
+        return np.linalg.norm(np.asarray(c.query_point_by_parameter(float(np.ravel(u)[0])), dtype=np.float64).reshape(3) - q)
+
+    for n in range(N):
+        min_u = float(c.min_arc_length) / float(c.full_arc_length)
+        for f in range(F):
+            res = minimize(dist, np.array([min_u]), (p[n, f],), method="L-BFGS-B", bounds=[(min_u, 1.0)])
+            min_u = float(res["x"][0])
+            out[n, f] = dist(min_u, p[n, f])
+    return out
+
+
+def trajectory_set_frame_errors(c, ma, skeleton, coeffs):
+    """[N, n_canonical_frames]: TrajectorySetConstraint.get_residual_vector (trajectory_set_constraint.py:83-105).  Every
+    joint walks its own trajectory by the arc length of its own path; a frame is scored with the arc lengths reached BEFORE
+    it (the step from the previous frame is added after the frame's residual); `np.average` of the list of positions is
+    the mean over all joints AND coordinates, so the residual is |mean(positions) - mean(targets)|, and it is taken only if
+    some trajectory is active at its arc length."""
+    nf = int(c.n_canonical_frames)
+    frames = eval_frames(ma, coeffs, motion_vector_times(ma.F)[:nf])
+    pos = np.stack([fk_global(skeleton, frames, jn)[1] for jn in c.joint_names], axis=2)     # [N, nf, J, 3]
+    N = pos.shape[0]
+    out = np.zeros((N, nf))
+    for n in range(N):
+        arcs = [float(a) for a in c.joint_arc_lengths]
+        last = None
+        for i in range(nf):
+            jp = pos[n, i]
+            active = [getattr(t, "range_start", None) is not None and t.range_start <= a <= t.range_end
+                      for t, a in zip(c.joint_trajectories, arcs)]
+            if np.any(active):
+                targets = [np.asarray(t.query_point_by_absolute_arc_length(a), dtype=np.float64)[:3]
+                           for t, a in zip(c.joint_trajectories, arcs)]
+                out[n, i] = abs(np.average(jp) - np.average(targets))
+            if last is not None:
+                arcs = [a + np.linalg.norm(jp[j] - last[j]) for j, a in enumerate(arcs)]
+            last = jp
+    return out
 
 
 def residual_vectors(model, skeleton, constraints, S, prev_frames=None):

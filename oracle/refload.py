@@ -136,6 +136,9 @@ def load():
     ns.joint_rotation_constraint = imp(_PKG + ".constraints.spatial_constraints.keyframe_constraints.joint_rotation_constraint")
     ns.pose_constraint_quat_frame = imp(_PKG + ".constraints.spatial_constraints.keyframe_constraints.pose_constraint_quat_frame")
     ns.local_trajectory_constraint = imp(_PKG + ".constraints.spatial_constraints.keyframe_constraints.local_trajectory_constraint")
+    ns.trajectory_constraint = imp(_PKG + ".constraints.spatial_constraints.trajectory_constraint")
+    ns.trajectory_set_constraint = imp(_PKG + ".constraints.spatial_constraints.trajectory_set_constraint")
+    ns.catmull_rom_spline = imp(_PKG + ".constraints.spatial_constraints.splines.catmull_rom_spline")
     ns.parameterized_spline = imp(_PKG + ".constraints.spatial_constraints.splines.parameterized_spline")
     ns.motion_primitive_constraints = imp(_PKG + ".constraints.motion_primitive_constraints")
     ns.objective_functions = imp(_PKG + ".motion_generator.optimization.objective_functions")
@@ -151,6 +154,31 @@ def load():
     except Exception:
         ns.construction_utils = None
     return ns
+
+
+def scalar_spline_parameter(ns):
+    """Context manager for quirk Q8.  scipy's minimize hands `ParameterizedSpline.find_closest_point_fast`'s objective
+    (parameterized_spline.py:304-322) a 1-element ARRAY u; `CatmullRomSpline.query_point_by_parameter`
+    (catmull_rom_spline.py:132-153) then builds the ragged list [u**3, u**2, u, 1] and hands it to np.dot, which raises since
+    numpy 1.24 (and gave a (3, 1) point before: a 3 x 3 broadcast against the joint position).  While this context is active
+    the spline receives u as the Python float it stands for, so the reference's own classes run and compute the distance
+    the code states.  The class attribute is wrapped and restored; the reference's source is not touched."""
+    import contextlib
+
+    @contextlib.contextmanager
+    def cm():
+        import numpy
+        cls = ns.catmull_rom_spline.CatmullRomSpline
+        orig = cls.query_point_by_parameter
+
+        def query_point_by_parameter(self, u):
+            return orig(self, float(numpy.ravel(u)[0]))
+        cls.query_point_by_parameter = query_point_by_parameter
+        try:
+            yield
+        finally:
+            cls.query_point_by_parameter = orig
+    return cm()
 
 
 def make_wrapper(ns, model_json):

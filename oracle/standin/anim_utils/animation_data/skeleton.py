@@ -114,6 +114,10 @@ class Skeleton(object):
             node_names = list(self.node_name_frame_map.keys())
         return [self.nodes[n].get_global_position(quat_frame) for n in node_names]
 
+    def get_cartesian_coordinates_from_quaternion(self, node_name, quaternion_frame):
+        # anim_utils Skeleton method of that name (call site: trajectory_constraint.py:106)
+        return self.nodes[node_name].get_global_position(quaternion_frame)
+
     def get_joint_weights(self):
         return list(self.joint_weight_map.values())
 

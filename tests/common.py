@@ -10,7 +10,7 @@ from morphablegraphs_b200 import synthetic as syn
 from morphablegraphs_b200 import (Skeleton, MotionStateGraphNode, MotionPrimitiveConstraints, CONSTRAINT_FACTORY)
 
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
-CASES = ["s_config1", "s_mixed", "s_mixed_tm", "s_nonlocal", "xs_mixed", "l_mixed", "s_rot", "s_rot_nonlocal"]
+CASES = ["s_config1", "s_mixed", "s_mixed_tm", "s_nonlocal", "xs_mixed", "l_mixed", "s_rot", "s_rot_nonlocal", "s_traj", "s_traj_nonlocal"]
 RTOL = 1e-4   # BASELINE.json north_star: 1e-4 relative in fp32
 
 

@@ -294,14 +294,14 @@ def test_errors_are_loud(big):
     from morphablegraphs_b200 import engine, MotionPrimitiveConstraints
     from morphablegraphs_b200.constraints import SpatialConstraintBase
 
-    class Traj(SpatialConstraintBase):
+    class Discrete(SpatialConstraintBase):           # DiscreteTrajectoryConstraint: outside the device path
         def __init__(self):
-            super(Traj, self).__init__(1.0, 1.0)
-            self.constraint_type = "trajectory"
+            super(Discrete, self).__init__(1.0, 1.0)
+            self.constraint_type = "discrete_trajectory"
     mpc = MotionPrimitiveConstraints()
     mpc.skeleton = big.skeleton
     mpc.is_local = True
-    mpc.constraints = [Traj()]
+    mpc.constraints = [Discrete()]
     with pytest.raises(engine.UnsupportedConstraintError):
         engine.DeviceConstraints(big.dm, mpc)
     with pytest.raises(engine.MgbError):
@@ -383,6 +383,46 @@ def test_large_rotation_and_trajectory_terms(large):
     counts = dm.component_counts(n, seed=6)
     fused = dc.sample_score(n, seed=6, counts=counts, k=1, return_cost=True, quality_scale=0.1)
     staged = dc.score(dm.sample(n, seed=6, counts=counts), k=1, return_cost=True, quality_scale=0.1)
+    assert rel_err(fused["cost"].cpu().numpy(), staged["cost"].cpu().numpy()).max() < RTOL
+
+
+def test_large_whole_motion_trajectory_constraints(large):
+    """f2 on the L model (tensor-core step kernel): TrajectoryConstraint on the root (closest point per frame of the 100-frame
+    motion vector) and a TrajectorySetConstraint on both hands, against the float64 oracle (scipy L-BFGS-B per frame)."""
+    import warnings
+    from oracle import np_oracle as O
+    from morphablegraphs_b200 import engine, synthetic as syn, MotionPrimitiveConstraints, CONSTRAINT_FACTORY
+    dm, F = large.dm, large.F
+    ma = O.ModelArrays(large.node)
+    held = dm.sample(2, seed=91).cpu().numpy().astype(np.float64)
+    fr = O.eval_frames(ma, O.back_project_coeffs(ma, held), list(np.linspace(0, F - 1, 7)))
+
+    def path(k, joint):
+        return O.fk_global(large.skeleton, fr[k:k + 1], joint)[1][0].tolist()
+    specs = [syn.spec("TrajectoryConstraint", {"joint_name": "Hips", "control_points": path(0, "Hips"), "min_arc_length": 1.0,
+                                               "n_canonical_frames": F}, 1.0, 0.9),
+             syn.spec("TrajectorySetConstraint", {"joint_names": ["LeftHand", "RightHand"], "joint_arc_lengths": [2.0, 0.0], "n_canonical_frames": F,
+                                                  "trajectories": [{"control_points": path(1, "LeftHand"), "range": [0.0, 30.0]},
+                                                                   {"control_points": path(1, "RightHand"), "range": [10.0, 1e9]}]}, 1.0, 1.1),
+             syn.spec("GlobalTransformConstraint", syn.position_constraint_desc("RightHand", [10.0, 120.0, 50.0], F - 1, F), 1.0, 1.0)]
+    mpc = MotionPrimitiveConstraints()
+    mpc.skeleton = large.skeleton
+    mpc.is_local = True
+    mpc.constraints = syn.build_constraints(CONSTRAINT_FACTORY, large.skeleton, specs)
+    dc = engine.DeviceConstraints(dm, mpc)
+    n = 300
+    S = dm.sample(n, seed=8)
+    S64 = S.cpu().numpy().astype(np.float64)
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        ref, ref_terms = O.candidate_costs(large.node, large.skeleton, mpc, S64, return_terms=True)
+    res = dc.score(S, k=1, return_cost=True, return_terms=True)
+    assert rel_err(res["terms"].cpu().numpy(), ref_terms).max() < RTOL
+    assert rel_err(res["cost"].cpu().numpy(), ref).max() < RTOL
+    _check_argmin(ref, int(res["best_idx"][0]), float(res["best_cost"][0]))
+    counts = dm.component_counts(n, seed=8)
+    fused = dc.sample_score(n, seed=8, counts=counts, k=1, return_cost=True, quality_scale=0.1)
+    staged = dc.score(dm.sample(n, seed=8, counts=counts), k=1, return_cost=True, quality_scale=0.1)
     assert rel_err(fused["cost"].cpu().numpy(), staged["cost"].cpu().numpy()).max() < RTOL
 
 
@@ -759,6 +799,21 @@ def test_residual_vectors_match_the_reference():
     v = obj(c.samples[3], (c.node, c.constraints, None, 1.0, 0.1, 1.0))
     assert rel_err(v, c.g["objective_q01"][3]).max() < RTOL
     assert abs(c.constraints.min_error - c.g["residual_vectors"][3].sum()) < RTOL * abs(c.g["residual_vectors"][3].sum())
+
+
+@pytest.mark.parametrize("name", ["s_traj", "s_traj_nonlocal"])
+def test_trajectory_residual_vectors_match_the_reference(name):
+    """f2: one residual per frame of the motion vector for TrajectoryConstraint (closest point of the path at a parameter >=
+    the previous frame's) and TrajectorySetConstraint (arc-length walk of several joints), against the reference's own
+    classes (tests/golden/s_traj*.npz); the L step kernel family is covered by the `case` tests through CASES."""
+    from morphablegraphs_b200 import engine
+    c = Case(name)
+    want = c.g["residual_vectors"]
+    dm = engine.DeviceModel(c.node, c.skeleton)
+    dc = engine.DeviceConstraints(dm, c.constraints, c.prev_frames)
+    r = dc.residuals(c.samples[:len(want)]).cpu().numpy()
+    assert r.shape == want.shape
+    assert rel_err(r, want).max() < RTOL
 
 
 def test_device_least_squares_reaches_the_reference_optimisers_error():

@@ -101,8 +101,9 @@ def test_oracle_scores_the_local_set_like_the_reference(local_case):
 # "accepts the reference's own objects": reference classes -> the same flat tables as the mirror classes
 # ---------------------------------------------------------------------------
 class _StubModel(object):
-    def __init__(self, skeleton):
+    def __init__(self, skeleton, n_frames=None):
         sk = engine.pack_skeleton(skeleton)
+        self.F = n_frames
         self.node_index = sk["index"]
         self.channel_node = {int(ch): i for i, ch in enumerate(sk["channel"]) if ch >= 0}
         self.skeleton = skeleton
@@ -134,7 +135,7 @@ def _flat_close(fa, fb, tol):
         assert np.allclose(_struct_values(pa[i]), _struct_values(pb[i]), rtol=0.0, atol=tol), i
 
 
-@pytest.mark.parametrize("name", ["s_mixed", "s_local", "l_cfg4", "s_rot"])
+@pytest.mark.parametrize("name", ["s_mixed", "s_local", "l_cfg4", "s_rot", "s_traj"])
 def test_reference_objects_flatten_like_the_mirror(name):
     from oracle import refload, make_golden
     if not refload.available():
@@ -157,10 +158,14 @@ def test_reference_objects_flatten_like_the_mirror(name):
     for k in ("parent", "type", "channel", "offset", "rotation"):
         assert np.array_equal(a[k], b[k]), k
     # constraint tables
-    fa = engine.flatten_constraints(_StubModel(ref_skel), ref_mpc)
-    fb = engine.flatten_constraints(_StubModel(c.skeleton), mine)
+    fa = engine.flatten_constraints(_StubModel(ref_skel, c.F), ref_mpc)
+    fb = engine.flatten_constraints(_StubModel(c.skeleton, c.F), mine)
     if name == "s_rot":
         _flat_close(fa, fb, 1e-14)
+    elif name == "s_traj":
+        # the trajectory tables are queried from the reference's ParameterizedSpline on one side and from the mirror's own
+        # Catmull-Rom restatement on the other
+        _flat_close(fa, fb, 1e-10)
     else:
         assert _flat_bytes(fa) == _flat_bytes(fb)
         # and therefore the same cache key content
@@ -194,6 +199,20 @@ def test_oracle_residual_vectors_match_the_reference():
     mpc2.constraints = [c.constraints.constraints[i] for i in keep]
     assert rel_err(O.residual_vectors(c.node, c.skeleton, mpc2, c.samples).sum(axis=1),
                    sum(c.constraints.constraints[i].weight_factor * terms[i] for i in keep)).max() < 1e-9
+
+
+@pytest.mark.parametrize("name", ["s_traj", "s_traj_nonlocal"])
+def test_oracle_trajectory_residuals_match_the_reference(name):
+    """f2: TrajectoryConstraint / TrajectorySetConstraint, one residual per frame of the motion vector, made by the reference's own
+    classes (quirk Q8: with the spline parameter handed over as a scalar, oracle/refload.py:scalar_spline_parameter)."""
+    import warnings
+    c = Case(name)
+    want = c.g["residual_vectors"]
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        r = O.residual_vectors(c.node, c.skeleton, c.constraints, c.samples[:len(want)], c.prev_frames)
+    assert r.shape == want.shape == (len(want), 2 * c.F + 1)
+    assert rel_err(r, want).max() < 1e-9
 
 
 # ---------------------------------------------------------------------------
