@@ -34,6 +34,7 @@ int sm_count_tree() {
 }
 
 constexpr int KM_WARPS = 4;
+constexpr int KM_SMALL_STAGES = 3;
 
 // CH = ceil(dim_acc / 32): columns handled per lane.  W (power of two, >= dim_acc when CH == 1, else 32)
 // is the width of a lane group; the 32 / W groups of a warp split the samples of a run between them.
@@ -194,6 +195,248 @@ __global__ void __launch_bounds__(KM_WARPS * 32) mgb_kmeans_level_kernel(
     if (inertia && lane == 0 && total_inertia != 0.f) atomicAdd(inertia, total_inertia);
 }
 
+// The same step for narrow rows (dim_acc <= DA <= 16, n_sub <= NS = 4: the latent space of the S primitive): lane = sample
+// for the E-step AND the accumulation.  The row, the NS centroids of the current node and the NS x DA running sums live in
+// registers; a sample adds its row to the sums of its label with predicated adds (no shuffles, no shared-memory traffic per
+// sample), and the 32 lanes' sums are folded through a padded shared-memory transpose only when the node changes.  About a
+// third of the instructions of the general kernel per sample.
+template <int NS, int DA, int DD>
+__global__ void __launch_bounds__(KM_WARPS * 32, 4) mgb_kmeans_level_small_kernel(
+    const float* __restrict__ x, long long n, int dim, int dim_acc, int ld, const int* __restrict__ node,
+    const float* __restrict__ cent, int n_sub, int* __restrict__ label, float* __restrict__ sums,
+    int* __restrict__ counts, float* __restrict__ node_inertia, float* __restrict__ inertia, long long tiles_per_warp,
+    const int* __restrict__ skip) {
+    extern __shared__ __align__(16) float sm_tiles[];
+    constexpr int ST = KM_SMALL_STAGES;          // tile buffers per warp: the rows of ST - 1 tiles are in flight while one is processed
+    const unsigned FULL = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5;
+    const int tile_floats = (32 * ld + 1 + 3) & ~3;  // 16-byte aligned tile buffers; + 1: an odd dim_acc reads one float past its row
+    float* const tile0 = sm_tiles + (size_t)warp * ST * tile_floats;
+    // DA = dim_acc rounded up to even (the spare column of an odd dim_acc carries the next row's first float and is dropped at the
+    // flush), DD = dim exactly (even): no column guards in the loop.  Per-warp scratch: flush transpose, then the NS
+    // centroids of the current node, NEGATED, zero for clusters beyond n_sub (read as float2 broadcasts: every offset below
+    // is an even number of floats, so they are 8-byte aligned), then the ring of node ids
+    static_assert(DA % 2 == 0 && DD % 2 == 0 && DD <= DA && NS % 2 == 0, "even sizes");
+    float* const scr = sm_tiles + (size_t)KM_WARPS * ST * tile_floats + (size_t)warp * (NS * DA * 33 + NS * DD + 5 * 32);
+    float* const cen = scr + NS * DA * 33;
+    int* const ids_s = reinterpret_cast<int*>(cen + NS * DD);      // [5][32] node ids of the tiles t .. t + 4
+    const long long gwarp = (long long)blockIdx.x * KM_WARPS + warp;
+    const long long first = gwarp * tiles_per_warp * 32;
+    long long last = first + tiles_per_warp * 32;
+    if (last > n) last = n;
+    const bool vec_ok = ((reinterpret_cast<uintptr_t>(x) & 15u) == 0) && ((32 * ld) % 4 == 0);   // every full tile starts 16-byte aligned
+
+    static_assert(DA % 2 == 0, "columns are handled in pairs (packed fp32x2 arithmetic)");
+    constexpr int DP = DA / 2;
+    float2 acc[NS][DP];
+    int cnt[NS];
+#pragma unroll
+    for (int k = 0; k < NS; ++k) {
+        cnt[k] = 0;
+#pragma unroll
+        for (int j = 0; j < DP; ++j) acc[k][j] = make_float2(0.f, 0.f);
+    }
+    float inertia_part = 0.f, total_inertia = 0.f;
+    int cur = -1;
+
+    auto flush = [&]() {           // warp-uniform call
+        if (cur < 0) return;
+#pragma unroll
+        for (int k = 0; k < NS; ++k)
+#pragma unroll
+            for (int j = 0; j < DP; ++j) {
+                scr[(k * DA + 2 * j) * 33 + lane] = acc[k][j].x;
+                scr[(k * DA + 2 * j + 1) * 33 + lane] = acc[k][j].y;
+                acc[k][j] = make_float2(0.f, 0.f);
+            }
+        __syncwarp();
+#pragma unroll
+        for (int v0 = 0; v0 < NS * DA; v0 += 32) {
+            const int v = v0 + lane;
+            if (v < NS * DA) {
+                const float* row = scr + v * 33;
+                float t0 = 0.f, t1 = 0.f, t2 = 0.f, t3 = 0.f;
+#pragma unroll
+                for (int i = 0; i < 32; i += 4) { t0 += row[i]; t1 += row[i + 1]; t2 += row[i + 2]; t3 += row[i + 3]; }
+                const float t = (t0 + t1) + (t2 + t3);
+                const int k = v / DA, j = v - k * DA;
+                if (k < n_sub && j < dim_acc && t != 0.f) atomicAdd(sums + ((size_t)cur * n_sub + k) * dim_acc + j, t);
+            }
+        }
+        __syncwarp();
+#pragma unroll
+        for (int k = 0; k < NS; ++k) {
+            if (lane == 0 && k < n_sub && cnt[k] != 0) atomicAdd(counts + (size_t)cur * n_sub + k, cnt[k]);
+            cnt[k] = 0;
+        }
+        float t = inertia_part;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(FULL, t, o);
+        if (lane == 0) {
+            if (node_inertia && t != 0.f) atomicAdd(node_inertia + cur, t);
+            total_inertia += t;
+        }
+        inertia_part = 0.f;
+    };
+    auto fetch = [&](long long t0, float* dst) {      // no commit: the caller closes the group
+        if (t0 < last) {
+            const int rows = (int)((last - t0 < 32) ? (last - t0) : 32);
+            const float* src = x + (size_t)t0 * ld;
+            if (rows == 32 && vec_ok) {
+                const int total4 = 8 * ld;
+                for (int e = lane; e < total4; e += 32) __pipeline_memcpy_async(dst + 4 * e, src + 4 * e, 16);
+            } else {
+                const int total = rows * ld;
+                for (int e = lane; e < total; e += 32) __pipeline_memcpy_async(dst + e, src + e, sizeof(float));
+            }
+        }
+    };
+    auto tile_skippable = [&](long long t0, int nd_lane) -> bool {
+        if (t0 >= last) return true;
+        return skip != nullptr && __all_sync(FULL, nd_lane < 0 || __ldg(skip + nd_lane) != 0);
+    };
+    // Node ids travel through the same asynchronous-copy groups as the rows, four tiles ahead of the tile being processed, into
+    // a ring of five slots: whether a tile's rows are fetched at all is decided from ids that have long arrived (a register
+    // prefetch of the ids stalled the warp on every tile: the copy of an in-flight load waits for it).
+    //   group of iteration i = rows of tile i + 2, ids of tile i + 4;  before it is issued, all groups but one are awaited,
+    //   which completes the rows of tile i and the ids of tile i + 2.
+    static_assert(ST == 3, "the id ring below assumes three row buffers");
+    for (int q = 0; q < 4; ++q) {
+        const long long tq = first + 32 * q;
+        ids_s[q * 32 + lane] = (tq + lane < last) ? (node ? __ldg(node + tq + lane) : 0) : -1;
+    }
+    __syncwarp();
+    bool skq[2];
+#pragma unroll
+    for (int q = 0; q < 2; ++q) {
+        skq[q] = tile_skippable(first + 32 * q, ids_s[q * 32 + lane]);
+        if (!skq[q]) fetch(first + 32 * q, tile0 + q * tile_floats);
+        __pipeline_commit();
+    }
+    int bi = 0, s5 = 0;                            // row buffer / id slot of the tile being processed
+    for (long long t0 = first; t0 < last; t0 += 32) {
+        const int rows = (int)((last - t0 < 32) ? (last - t0) : 32);
+        __pipeline_wait_prior(1);
+        __syncwarp();
+        bool sk2;
+        {
+            const long long tq = t0 + 64;
+            int bq = bi + 2, sq = s5 + 2, sa = s5 + 4;
+            if (bq >= 3) bq -= 3;
+            if (sq >= 5) sq -= 5;
+            if (sa >= 5) sa -= 5;
+            sk2 = tile_skippable(tq, (tq + lane < last) ? ids_s[sq * 32 + lane] : -1);
+            if (!sk2) fetch(tq, tile0 + bq * tile_floats);
+            const long long ta = t0 + 128;
+            if (ta + lane < last) {
+                if (node) __pipeline_memcpy_async(ids_s + sa * 32 + lane, node + ta + lane, sizeof(int));
+                else ids_s[sa * 32 + lane] = 0;
+            } else {
+                ids_s[sa * 32 + lane] = -1;
+            }
+            __pipeline_commit();
+        }
+        const float* tile = tile0 + bi * tile_floats;
+        const int nd = (lane < rows) ? ids_s[s5 * 32 + lane] : -1;
+        const bool skip_cur = skq[0];
+        skq[0] = skq[1];
+        skq[1] = sk2;
+        if (++bi == 3) bi = 0;
+        if (++s5 == 5) s5 = 0;
+        if (skip_cur) continue;
+        // lanes beyond the last row of a partial tile read its last row: they belong to no run and add it with factor 0
+        float2 xr[DP];
+        const bool have = lane < rows;
+        const float* xrow = tile + min(lane, rows - 1) * ld;
+#pragma unroll
+        for (int j = 0; j < DP; ++j) {
+            xr[j].x = xrow[2 * j];
+            xr[j].y = xrow[2 * j + 1];
+        }
+        const int prev = __shfl_up_sync(FULL, nd, 1);
+        unsigned heads = __ballot_sync(FULL, have && (lane == 0 || nd != prev));
+        while (heads) {
+            const int a = __ffs(heads) - 1;
+            heads &= heads - 1;
+            const int b = heads ? (__ffs(heads) - 1) : rows;
+            const int run_nd = __shfl_sync(FULL, nd, a);
+            if (run_nd != cur) {
+                flush();
+                cur = run_nd;
+                const float* cb = cent + (size_t)cur * n_sub * dim;
+                __syncwarp();
+                for (int v = lane; v < NS * DD; v += 32) cen[v] = (v < n_sub * DD) ? -__ldg(cb + v) : 0.f;
+                __syncwarp();
+            }
+            const bool in_run = lane >= a && lane < b;
+            // squared distances over the first DD columns, two columns per instruction (FADD2 / FFMA2: each half rounded like
+            // the scalar instruction)
+            float2 d2[NS];
+#pragma unroll
+            for (int k = 0; k < NS; ++k) d2[k] = make_float2(0.f, 0.f);
+#pragma unroll
+            for (int j = 0; j < DD / 2; ++j) {
+#pragma unroll
+                for (int k = 0; k < NS; ++k) {
+                    const float2 e = __fadd2_rn(xr[j], *reinterpret_cast<const float2*>(cen + k * DD + 2 * j));
+                    d2[k] = __ffma2_rn(e, e, d2[k]);
+                }
+            }
+            float d[NS];
+#pragma unroll
+            for (int k = 0; k < NS; ++k) d[k] = d2[k].x + d2[k].y;
+            float best = INFINITY;
+            int lb = 0;
+#pragma unroll
+            for (int k = 0; k < NS; ++k)
+                if (k < n_sub && d[k] < best) { best = d[k]; lb = k; }
+            if (in_run) {
+                label[t0 + lane] = lb;
+                inertia_part += best;
+            }
+            // the row joins the sums of its label: one FMA per (label, column) with a 0 / 1 factor (rows beyond the tile are zero)
+#pragma unroll
+            for (int k = 0; k < NS; ++k) {
+                const bool mine = in_run && lb == k;
+                cnt[k] += __popc(__ballot_sync(FULL, mine));
+                const float m = mine ? 1.f : 0.f;
+                const float2 mm = make_float2(m, m);
+#pragma unroll
+                for (int j = 0; j < DP; ++j) acc[k][j] = __ffma2_rn(mm, xr[j], acc[k][j]);
+            }
+        }
+        __syncwarp();
+    }
+    flush();
+    if (inertia && lane == 0 && total_inertia != 0.f) atomicAdd(inertia, total_inertia);
+}
+
+template <int NS, int DA, int DD>
+int launch_level_small(const float* d_x, int64_t n, int dim, int dim_acc, int ld, const int* d_node, const float* d_cent, int n_sub,
+                       int* d_label, float* d_sums, int* d_counts, float* d_node_inertia, float* d_inertia, cudaStream_t stream,
+                       const int* d_skip) {
+    auto kern = mgb_kmeans_level_small_kernel<NS, DA, DD>;
+    const size_t smem = ((size_t)KM_SMALL_STAGES * KM_WARPS * ((32 * ld + 1 + 3) & ~3) + (size_t)KM_WARPS * (NS * DA * 33 + NS * DD + 5 * 32)) * sizeof(float);
+    static bool configured[MGB_MAX_DEVICES] = {false};
+    if (int rc = mgb_opt_in_smem(kern, configured, 160 * 1024)) return rc;
+    const long long tiles = (n + 31) / 32;
+    int occ = 1;
+    MGB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, KM_WARPS * 32, smem));
+    if (occ < 1) occ = 1;
+    // one resident wave: every warp folds its register sums once per node it meets, so fewer, longer warps are cheaper
+    long long warps = (long long)sm_count_tree() * occ * KM_WARPS;
+    if (warps > tiles) warps = tiles;
+    const long long tpw = (tiles + warps - 1) / warps;
+    const long long used_warps = (tiles + tpw - 1) / tpw;
+    const long long grid = (used_warps + KM_WARPS - 1) / KM_WARPS;
+    kern<<<(unsigned)grid, KM_WARPS * 32, smem, stream>>>(d_x, n, dim, dim_acc, ld, d_node, d_cent, n_sub, d_label, d_sums, d_counts,
+                                                           d_node_inertia, d_inertia, tpw, d_skip);
+    mgb_count_launch();
+    MGB_CUDA(cudaGetLastError());
+    return MGB_OK;
+}
+
 // M-step finish + convergence test, one thread per node.  Empty clusters keep their centroid.
 __global__ void __launch_bounds__(128) mgb_kmeans_centroid_kernel(int n_nodes, int n_sub, int dim, int dim_acc,
                                                                  const float* __restrict__ sums, const int* __restrict__ counts,
@@ -264,7 +507,22 @@ int dispatch_level(const float* d_x, int64_t n, int dim, int dim_acc, int ld, co
                    const int* d_skip = nullptr) {
     const int ch = (dim_acc + 31) / 32;
     MGB_REQUIRE(n_sub >= 1 && n_sub <= 8, "n_sub must be in 1..8");
-    MGB_REQUIRE(ch <= 4, "at most 128 accumulated columns");
+    if (n_sub <= 4 && ld <= 64) {
+        // narrow rows (the latent space of the S primitive: 14 columns, clustered on the first 10): registers + packed fp32x2
+#define MGB_KM_SMALL(DA, DD)                                                                                                            \
+    if (((dim_acc + 1) & ~1) == DA && dim == DD)                                                                                        \
+        return launch_level_small<4, DA, DD>(d_x, n, dim, dim_acc, ld, d_node, d_cent, n_sub, d_label, d_sums, d_counts, d_node_inertia, \
+                                             d_inertia, stream, d_skip)
+        MGB_KM_SMALL(14, 10);
+        MGB_KM_SMALL(14, 14);
+        MGB_KM_SMALL(16, 16);
+        MGB_KM_SMALL(16, 10);
+        MGB_KM_SMALL(12, 12);
+        MGB_KM_SMALL(12, 10);
+        MGB_KM_SMALL(10, 10);
+        MGB_KM_SMALL(8, 8);
+#undef MGB_KM_SMALL
+    }
 #define MGB_KM_CASE(NS, CH)                                                                                              \
     return launch_level<NS, CH>(d_x, n, dim, dim_acc, ld, d_node, d_cent, n_sub, d_label, d_sums, d_counts, d_node_inertia, \
                                 d_inertia, stream, d_skip)
