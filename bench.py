@@ -58,7 +58,7 @@ SECONDARY = {"L4M": ["S1M", "L4M_stress"], "S1M": ["L4M"], "L4M_stress": []}
 # dram__bytes_read.sum + dram__bytes_write.sum of the step kernel, per launch, from the committed
 # `ncu --set full` captures (profiles/); captures ran 1M candidates, scaled to the workload's launch
 TRAFFIC = {
-    "L4M": {"bytes": 5999872.0, "source": "profiles/r02_p_ncu_L_cfg4_raw.csv: 6.0 MB read + 0 written per 4M-candidate launch (the packed operands come "
+    "L4M": {"bytes": 6031104.0, "source": "profiles/r02_x_ncu_L_cfg4_raw.csv: 6.0 MB read + 0 written per 4M-candidate launch (the packed operands come "
                                           "from HBM once and are re-read from L2: 92.6 GB of L2 -> SM traffic per launch; candidates are never stored)"},
     "S1M": {"bytes": 123904.0, "source": "profiles/r01_zb_ncu_k1k6_S_raw.csv: 88.6 KB read + 35.3 KB written per 1M-candidate launch "
                                           "(tables + arg-min partials; candidates are never stored)"},
@@ -66,7 +66,7 @@ TRAFFIC = {
                                                         "(packed operands re-read from L2/HBM per tile), x4 for the 4M launch"},
 }
 # sm__pipe_tensor_cycles_active (ncu, % of peak sustained active) of the tensor-core step kernel, from the committed captures
-TENSOR_PIPE_NCU = {"L4M": 71.7}      # profiles/r02_p_ncu_L_cfg4_raw.csv (38.7 at the start of round 2: profiles/r02_a_ncu_L_cfg4_raw.csv)
+TENSOR_PIPE_NCU = {"L4M": 70.2}      # profiles/r02_x_ncu_L_cfg4_raw.csv (71.7 in r02_p; 38.7 at the start of round 2: profiles/r02_a_ncu_L_cfg4_raw.csv)
 
 
 def config_of(workload, world):

@@ -765,12 +765,14 @@ def build_cluster_tree(data, n_sub, max_level, dim, use_kd_tree=True, seeds=None
     t._parts = [means_dev.double().cpu().numpy(), np.asarray(data, dtype=np.float64)]
     if dev.type == "cuda":
         t.device_table = torch.cat([means_dev.float(), X], dim=0).contiguous()
+    t0 = tick("assembly: points", t0)
     t.node_row = np.arange(n_nodes, dtype=np.int64)
     t.node_leaf = torch.cat(node_leaf).cpu().numpy()
     ep = torch.cat(edges_parent).cpu().numpy() if edges_parent else np.empty(0, dtype=np.int64)
     ec = torch.cat(edges_child).cpu().numpy() if edges_child else np.empty(0, dtype=np.int64)
     kp = owner.cpu().numpy()
     kc = roots.cpu().numpy()
+    t0 = tick("assembly: edges to host", t0)
     par = np.concatenate([ep, kp])
     chi = np.concatenate([ec, kc])
     iskd = np.concatenate([np.zeros(len(ep), dtype=bool), np.ones(len(kp), dtype=bool)])
@@ -778,8 +780,10 @@ def build_cluster_tree(data, n_sub, max_level, dim, use_kd_tree=True, seeds=None
     t.child_idx, t.child_is_kd = chi[o], iskd[o]
     t.child_ptr = np.zeros(n_nodes + 1, dtype=np.int64)
     t.child_ptr[1:] = np.cumsum(np.bincount(par, minlength=n_nodes))
+    t0 = tick("assembly: child lists", t0)
     t.kd_row = n_nodes + kd_pt.cpu().numpy()
     t.kd_left, t.kd_right, t.kd_inner = kd_l.cpu().numpy(), kd_r.cpu().numpy(), kd_in.cpu().numpy()
+    t0 = tick("assembly: kd arrays to host", t0)
     info["n_nodes"] = n_nodes
     info["n_kd_nodes"] = int(len(t.kd_row))
     if timing is not None:
