@@ -89,6 +89,7 @@ def parse_args():
     ap.add_argument("--cpu-seconds", type=float, default=10.0, help="budget of the headline cpu_baseline leg")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-staged", action="store_true", help="skip the staged-pipeline kernel rooflines")
+    ap.add_argument("--no-tree", action="store_true", help="skip the config-5 side measurement (`tree` key)")
     return ap.parse_args()
 
 
@@ -754,6 +755,16 @@ def main():
         others["C3"] = c3
     if others:
         out["workloads"] = others
+    if gpu.world == 1 and not args.only and not args.no_tree:
+        # BASELINE.json configs[4] (cluster-tree build and search over 1M latent samples of the S primitive): tools/tree_bench.py
+        try:
+            import importlib.util
+            spec = importlib.util.spec_from_file_location("mgb_tree_bench", os.path.join(os.path.dirname(os.path.abspath(__file__)), "tools", "tree_bench.py"))
+            tb = importlib.util.module_from_spec(spec)
+            spec.loader.exec_module(tb)
+            out["tree"] = tb.run(argparse.Namespace(m=1_000_000, levels=8, no_features=True))
+        except Exception as e:          # a side measurement must not cost the headline line
+            out["tree"] = {"error": "%s: %s" % (type(e).__name__, e)}
     emit(json.dumps(out))
     if gpu.world > 1:
         gpu.dist.destroy_process_group()

@@ -10,8 +10,8 @@ python tools/show_bench.py $out/${tag}_bench.json
 timeout 600 python bench.py --impl reference --steps 3 --warmup 1 > $out/${tag}_bench_ref.json 2> $out/${tag}_bench_ref.err; echo "bench ref rc=$?"; cut -c1-300 $out/${tag}_bench_ref.json
 if [ "$2" = "ncu" ]; then
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file $out/${tag}_launches.csv \
-  python bench.py --steps 2 --warmup 3 --no-cpu-baseline > $out/${tag}_ncu_list.log 2>&1; echo "ncu list rc=$?"
+  python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-tree > $out/${tag}_ncu_list.log 2>&1; echo "ncu list rc=$?"
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:mgb_score_tc -c 1 -f -o $out/${tag}_full_L \
-  python bench.py --steps 1 --warmup 3 --no-cpu-baseline --only --no-staged > $out/${tag}_ncu_full_L.log 2>&1; echo "ncu full L rc=$?"
+  python bench.py --steps 1 --warmup 3 --no-cpu-baseline --only --no-staged --no-tree > $out/${tag}_ncu_full_L.log 2>&1; echo "ncu full L rc=$?"
 fi
 ls $out | grep $tag

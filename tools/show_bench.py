@@ -29,3 +29,13 @@ for k, v in d.get("workloads", {}).items():
     else:
         print("%-11s value %.4g  %s" % (k, v["value"], {a: b for a, b in v.items() if a not in ("value", "description", "unit", "timing")}))
 print(d.get("clocks"))
+t = d.get("tree")
+if t:
+    if "error" in t:
+        print("tree        ERROR", t["error"])
+    else:
+        b = t["cluster_tree_build"]
+        print("tree        build %.4f s (%d launches, %d nodes)  K7 pass %s  search %s" % (
+            b["seconds"], b["launches"], b["n_nodes"],
+            {k: "%.1f us (in loop %.1f)" % (v["ms"] * 1e3, v.get("ms_per_pass_in_loop", 0) * 1e3) for k, v in t["K7_lloyd_iteration"].items()},
+            {k: round(v["seconds"] * 1e3, 3) for k, v in t["cluster_tree_search"].items() if isinstance(v, dict) and "seconds" in v}))

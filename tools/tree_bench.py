@@ -34,7 +34,11 @@ def main():
     ap.add_argument("--levels", type=int, default=8)
     ap.add_argument("--cpu-m", type=int, default=0, help="unused (the CPU build is timed by bench.py's cpu_baseline leg: tree_build_port)")
     ap.add_argument("--no-features", action="store_true")
-    a = ap.parse_args()
+    print(json.dumps(run(ap.parse_args())))
+
+
+def run(a):
+    """a: namespace with m, levels, no_features.  Returns the result dictionary (bench.py stores it under its `tree` key)."""
     node, skeleton, mpc, prev = bench.build_case("S1M")
     dm = engine.DeviceModel(node, skeleton, 0)
     dc = engine.DeviceConstraints(dm, mpc, prev)
@@ -117,7 +121,7 @@ def main():
         (v, s), t = wall(lambda: ftree.find_best_example_excluding_search_candidates(obj_spatial_error_sum, data_t, 5))
         (v, s), t = wall(lambda: ftree.find_best_example_excluding_search_candidates(obj_spatial_error_sum, data_t, 5))
         out["feature_tree_search"] = {"seconds": t, "value": v}
-    print(json.dumps(out))
+    return out
 
 
 if __name__ == "__main__":
