@@ -201,6 +201,39 @@ def test_oracle_residual_vectors_match_the_reference():
                    sum(c.constraints.constraints[i].weight_factor * terms[i] for i in keep)).max() < 1e-9
 
 
+def test_quirk_q8_reference_closest_point_needs_a_scalar_parameter():
+    """as written, ParameterizedSpline.find_closest_point_fast (parameterized_spline.py:303-322) hands the
+    Catmull-Rom spline scipy's 1-element array; numpy >= 1.24 refuses the ragged list built from it (catmull_rom_spline.py:141-165).
+    With the parameter handed over as a scalar (oracle/refload.py:scalar_spline_parameter) the reference's own class runs and finds
+    the closest point of the curve."""
+    import warnings
+    from oracle import refload
+    if not refload.available():
+        pytest.skip("reference modules not present (neither /root/reference nor oracle/_ref)")
+    ns = refload.load()
+    cps = [np.array(p) for p in ([0.0, 0.0, 0.0], [5.0, 2.0, 15.0], [12.0, 0.0, 30.0], [10.0, 3.0, 45.0], [0.0, 0.0, 60.0])]
+    import contextlib, io
+    with contextlib.redirect_stdout(io.StringIO()):
+        spline = ns.parameterized_spline.ParameterizedSpline(cps)
+    p = np.asarray(spline.query_point_by_parameter(0.4)) + np.array([0.3, -0.2, 0.1])
+    if tuple(int(x) for x in np.__version__.split(".")[:2]) >= (1, 24):
+        with pytest.raises(ValueError), warnings.catch_warnings():
+            warnings.simplefilter("ignore")
+            spline.find_closest_point_fast(p, 0.1)
+    with refload.scalar_spline_parameter(ns), warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        target, u = spline.find_closest_point_fast(p, 0.1)
+    assert abs(float(np.ravel(u)[0]) - 0.4) < 0.02 and np.linalg.norm(np.asarray(target) - p) < 0.4
+    # and the mirror's own Catmull-Rom restatement is the same curve
+    from morphablegraphs_b200.constraints import CatmullRomTrajectory
+    mine = CatmullRomTrajectory(cps)
+    assert abs(mine.full_arc_length - spline.full_arc_length) < 1e-9
+    for x in np.linspace(0.0, 1.0, 41):
+        assert np.abs(mine.query_point_by_parameter(x) - np.asarray(spline.query_point_by_parameter(x))).max() < 1e-9
+    for a_len in np.linspace(0.0, 1.1 * spline.full_arc_length, 37):
+        assert np.abs(mine.query_point_by_absolute_arc_length(a_len) - np.asarray(spline.query_point_by_absolute_arc_length(a_len))).max() < 1e-9
+
+
 @pytest.mark.parametrize("name", ["s_traj", "s_traj_nonlocal"])
 def test_oracle_trajectory_residuals_match_the_reference(name):
     """f2: TrajectoryConstraint / TrajectorySetConstraint, one residual per frame of the motion vector, made by the reference's own
