@@ -89,6 +89,123 @@ __global__ void __launch_bounds__(SAMPLE_BLOCK) mgb_sample_kernel(const float* _
 }
 
 // ---------------------------------------------------------------------------
+// K1 for large latent spaces (32 < D <= 128): one CTA = a tile of SG_ROWS candidates of ONE mixture component, drawn as a
+// register-tiled product  s[r][d] = mu[d] + sum_j L[d][j] z[r][j]  out of shared memory (z transposed, L transposed and
+// padded to a conflict-free stride).  The per-row loop above spends two loads and a dependent FMA per term (15 ms per 4M
+// candidates at D = 103); here a thread owns 8 rows x D/16 columns and every output is still accumulated by ONE thread in
+// ascending j starting from mu[d] - the terms above the diagonal multiply a stored zero - so the rows are bit for bit those
+// of the per-row loop (and of the reference-ordered oracle).
+// ---------------------------------------------------------------------------
+constexpr int SG_ROWS = 128;
+constexpr int SG_THREADS = 256;
+constexpr int SG_CMAX = 8;          // columns per thread: d = cg + 16 c, D <= 128
+
+struct SgTiles {
+    int first[MGB_MAX_GMM + 1];     // tiles before component g (tiles never straddle components)
+};
+
+template <int CN>
+__global__ void __launch_bounds__(SG_THREADS) mgb_sample_gemm_kernel(const float* __restrict__ means, const float* __restrict__ chol, int LS,
+                                                                    const __grid_constant__ MgbGmmPrefix pre, const __grid_constant__ SgTiles tl,
+                                                                    int G, int D, long long n, long long index_base, unsigned long long seed,
+                                                                    float* __restrict__ out) {
+    extern __shared__ __align__(128) float sg_sm[];
+    const int D4 = (D + 3) & ~3;                 // z columns drawn (4 per Philox call)
+    constexpr int ZS = SG_ROWS + 4;              // zt[j][row]
+    constexpr int LT = 16 * CN + 1;              // lt[j][d], odd stride: the transposing stores do not conflict
+    float* zt = sg_sm;                           // [D4][ZS]; later the finished rows [SG_ROWS][D]
+    float* lt = sg_sm + (size_t)D4 * ZS;         // [D4][LT]
+    const int tid = threadIdx.x;
+    int g = 0;
+    while (g + 1 < G && (int)blockIdx.x >= tl.first[g + 1]) ++g;
+    const long long lo = max(pre.v[g], index_base), hi = min(pre.v[g + 1], index_base + n);
+    const long long row0 = lo + (long long)((int)blockIdx.x - tl.first[g]) * SG_ROWS;      // global index of the tile's first row
+    const int rows = (int)min((long long)SG_ROWS, hi - row0);
+    const uint2 key = make_uint2((unsigned int)seed, (unsigned int)(seed >> 32));
+    // L_g transposed (zero above the diagonal and beyond D)
+    const float* Lg = chol + (size_t)g * D * LS;
+    for (int e = tid; e < D4 * 16 * CN; e += SG_THREADS) {
+        const int d = e / D4, j = e - d * D4;
+        lt[j * LT + d] = (d < D && j <= d) ? __ldg(Lg + (size_t)d * LS + j) : 0.f;
+    }
+    // normals of the tile, transposed
+    const int nb = D4 >> 2;
+    for (int e = tid; e < SG_ROWS * nb; e += SG_THREADS) {
+        const int r = e % SG_ROWS, b = e / SG_ROWS;
+        float q[4] = {0.f, 0.f, 0.f, 0.f};
+        if (r < rows) mgb_normal4((unsigned long long)(row0 + r), (unsigned int)b, key, q);
+#pragma unroll
+        for (int c = 0; c < 4; ++c) zt[(4 * b + c) * ZS + r] = q[c];
+    }
+    __syncthreads();
+    const int rg = tid >> 4, cg = tid & 15;
+    float acc[8][CN];
+#pragma unroll
+    for (int c = 0; c < CN; ++c) {
+        const int d = cg + 16 * c;
+        const float mu = d < D ? __ldg(means + (size_t)g * D + d) : 0.f;
+#pragma unroll
+        for (int r = 0; r < 8; ++r) acc[r][c] = mu;
+    }
+    // j in blocks of 16: L is lower triangular, so the columns d < 16 jb (c < jb) have nothing but zeros in block jb and are left
+    // out (57 % of the square at D = 103); a skipped term would have added 0 * z
+#pragma unroll
+    for (int jb = 0; jb < CN; ++jb) {
+        const int j1 = min(16 * jb + 16, D);
+        for (int j = 16 * jb; j < j1; ++j) {
+            const float4 za = *reinterpret_cast<const float4*>(zt + j * ZS + rg * 8);
+            const float4 zb = *reinterpret_cast<const float4*>(zt + j * ZS + rg * 8 + 4);
+            const float z[8] = {za.x, za.y, za.z, za.w, zb.x, zb.y, zb.z, zb.w};
+#pragma unroll
+            for (int c = jb; c < CN; ++c) {
+                const float l = lt[j * LT + cg + 16 * c];
+#pragma unroll
+                for (int r = 0; r < 8; ++r) acc[r][c] = fmaf(l, z[r], acc[r][c]);
+            }
+        }
+    }
+    __syncthreads();                             // every thread is done with zt: it becomes the output tile [rows][D]
+    float* tile = zt;
+#pragma unroll
+    for (int r = 0; r < 8; ++r)
+#pragma unroll
+        for (int c = 0; c < CN; ++c) {
+            const int d = cg + 16 * c;
+            if (d < D) tile[(size_t)(rg * 8 + r) * D + d] = acc[r][c];
+        }
+    float* dst = out + (size_t)(row0 - index_base) * D;
+    const unsigned int bytes = (unsigned int)((size_t)rows * D * sizeof(float));
+    const bool bulk = ((reinterpret_cast<uintptr_t>(dst) | bytes) & 15u) == 0;
+    if (bulk) mgb_fence_proxy_async();
+    __syncthreads();
+    if (bulk) {
+        if (tid == 0) {
+            mgb_tma_store_1d(dst, tile, bytes);
+            mgb_tma_store_wait_read<0>();
+        }
+    } else {
+        for (int e = tid; e < rows * D; e += SG_THREADS) dst[e] = tile[e];
+    }
+}
+
+template <int CN>
+static int launch_sample_gemm(const mgb_model* m, const MgbGmmPrefix& prefix, const SgTiles& tl, int total, int64_t n, int64_t index_base,
+                              uint64_t seed, float* d_s, cudaStream_t stream) {
+    auto kern = mgb_sample_gemm_kernel<CN>;
+    const int D4 = (m->D + 3) & ~3;
+    const size_t smem = ((size_t)D4 * (SG_ROWS + 4) + (size_t)D4 * (16 * CN + 1)) * sizeof(float);
+    MGB_REQUIRE((size_t)SG_ROWS * m->D <= (size_t)D4 * (SG_ROWS + 4), "internal: output tile larger than the z tile");
+    static bool configured[MGB_MAX_DEVICES] = {false};
+    if (int rc = mgb_opt_in_smem(kern, configured, 200 * 1024)) return rc;
+    MGB_REQUIRE(smem <= 200 * 1024, "latent dimension too large for the sampler");
+    kern<<<(unsigned)total, SG_THREADS, smem, stream>>>(m->d_means, m->d_chol, m->LS, prefix, tl, m->G, m->D, n, index_base,
+                                                        (unsigned long long)seed, d_s);
+    mgb_count_launch();
+    MGB_CUDA(cudaGetLastError());
+    return MGB_OK;
+}
+
+// ---------------------------------------------------------------------------
 // K2 (SIMT fp32): coeffs[n, M] = alpha[n, K] . E'[K, M] + mean'[M]
 // CTA = 256 threads = 256 consecutive columns x BP_ROWS candidates; alpha tile
 // transposed in shared memory so one 128-bit broadcast load feeds 4 FMAs;
@@ -376,6 +493,25 @@ extern "C" int mgb_sample(const mgb_model* m, int64_t n, int64_t index_base, con
                 (long long)index_base, (long long)(index_base + n));
     if (m->D <= 16) return launch_sample<16>(m, prefix, n, index_base, seed, d_s, stream);
     if (m->D <= 32) return launch_sample<32>(m, prefix, n, index_base, seed, d_s, stream);
+    if (m->D <= 16 * SG_CMAX && n >= 4 * SG_ROWS) {
+        // tiles of one component each
+        SgTiles tl;
+        int total = 0;
+        for (int g = 0; g < m->G; ++g) {
+            tl.first[g] = total;
+            const long long lo = std::max<long long>(prefix.v[g], index_base), hi = std::min<long long>(prefix.v[g + 1], index_base + n);
+            if (hi > lo) total += (int)((hi - lo + SG_ROWS - 1) / SG_ROWS);
+        }
+        for (int g = m->G; g <= MGB_MAX_GMM; ++g) tl.first[g] = total;
+        switch ((m->D + 15) / 16) {
+            case 3: return launch_sample_gemm<3>(m, prefix, tl, total, n, index_base, seed, d_s, stream);
+            case 4: return launch_sample_gemm<4>(m, prefix, tl, total, n, index_base, seed, d_s, stream);
+            case 5: return launch_sample_gemm<5>(m, prefix, tl, total, n, index_base, seed, d_s, stream);
+            case 6: return launch_sample_gemm<6>(m, prefix, tl, total, n, index_base, seed, d_s, stream);
+            case 7: return launch_sample_gemm<7>(m, prefix, tl, total, n, index_base, seed, d_s, stream);
+            default: return launch_sample_gemm<8>(m, prefix, tl, total, n, index_base, seed, d_s, stream);
+        }
+    }
     return launch_sample<0>(m, prefix, n, index_base, seed, d_s, stream);
 }
 

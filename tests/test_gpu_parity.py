@@ -386,6 +386,25 @@ def test_large_rotation_and_trajectory_terms(large):
     assert rel_err(fused["cost"].cpu().numpy(), staged["cost"].cpu().numpy()).max() < RTOL
 
 
+def test_large_sampler_tiled_equals_per_row(large):
+    """K1 at D = 103: the register-tiled sampler (tiles of 128 candidates of one component, n >= 512) returns bit for bit the rows
+    of the per-row sampler (which small calls still use), for a job of 40 003 candidates over 32 components, whole and as a
+    window that starts and ends inside components."""
+    import torch
+    dm = large.dm
+    total = 40_003
+    counts = dm.component_counts(total, seed=21)
+    whole = dm.sample(total, seed=21, counts=counts)
+    assert torch.isfinite(whole).all()
+    # per-row path: windows of 300 rows (< 4 tiles)
+    for base in (0, 299, 17_000, total - 300):
+        part = dm.sample(300, seed=21, counts=counts, index_base=base, n_total=total)
+        assert torch.equal(part, whole[base:base + 300]), base
+    # tiled path on a window
+    win = dm.sample(12_345, seed=21, counts=counts, index_base=7_777, n_total=total)
+    assert torch.equal(win, whole[7_777:7_777 + 12_345])
+
+
 def test_large_whole_motion_trajectory_constraints(large):
     """f2 on the L model (tensor-core step kernel): TrajectoryConstraint on the root (closest point per frame of the 100-frame
     motion vector) and a TrajectorySetConstraint on both hands, against the float64 oracle (scipy L-BFGS-B per frame)."""
