@@ -268,6 +268,7 @@ struct ScoreParams {
     long long* best_idx;
     MgbExchange xch;           // world > 1 (xch.peer_slots != NULL): the folding CTA exchanges this rank's best with its peers
     float* best_row;           // MODE_SAMPLE: [D] the winning latent vector, re-drawn by the CTA that folds the partials (or NULL)
+    const float* cost_base;    // [n] or NULL: added to every candidate's cost (the naturalness / magnitude part computed by another launch)
 };
 
 // launchers implemented in the kernel translation units

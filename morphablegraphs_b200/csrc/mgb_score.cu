@@ -271,6 +271,11 @@ __device__ __forceinline__ void score_body(const ScoreParams& p, const int cta, 
         float cost[CPT];
 #pragma unroll
         for (int c = 0; c < CPT; ++c) cost[c] = p.err_scale * total[c];
+        if (p.cost_base != nullptr) {
+#pragma unroll
+            for (int c = 0; c < CPT; ++c)
+                if (valid[c]) cost[c] += p.cost_base[idx[c]];
+        }
         if (p.quality_scale != 0.f) {
             // GMM log-density from the precision Cholesky factors; column quad jq of the
             // upper-triangular factor only needs rows k < 4 jq + 4
@@ -718,6 +723,18 @@ int mgb_launch_score(const mgb_model* m, const mgb_constraints* c, int mode, con
         // large latent spaces: sampling, contraction and GMM log-density on the tensor cores (mgb_tc.cu)
         rc = mgb_launch_score_tc(m, c, p, s_is_f64, quality_scale, mode == MODE_SAMPLE ? 1 : 0, stream);
     } else if (mode == MODE_FRAMES) {
+        if ((quality_scale != 0.f || magnitude_scale != 0.f) && d_cost && d_s && mgb_score_tc_usable(m, nullptr, quality_scale, 0)) {
+            // large latent space: the density (2 G D^2 flop per candidate) on the tensor cores by a launch of its own, into d_cost;
+            // the frames kernel then adds the constraint error to it (same index read and written by the same thread)
+            if (int r1 = mgb_launch_score(m, nullptr, MODE_S, d_s, 0, nullptr, nullptr, 0, n, index_base, 0.f, quality_scale, magnitude_scale, d_cost,
+                                          nullptr, 0, nullptr, nullptr, nullptr, 0, stream))
+                return r1;
+            p.quality_scale = 0.f;
+            p.magnitude_scale = 0.f;
+            p.gmm_in_smem = 0;
+            p.s = nullptr;             // the frames kernel no longer reads the latent vectors
+            p.cost_base = d_cost;
+        }
         rc = launch_variant<0, 1, MODE_FRAMES, float>(p, plan, stream);
     } else if (mode == MODE_SAMPLE) {
         rc = launch_shape<MODE_SAMPLE, float>(D, p, plan, stream);

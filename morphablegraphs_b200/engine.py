@@ -606,7 +606,8 @@ class DeviceConstraints(object):
         s = s.contiguous()
         n = int(s.shape[0])
         assert s.dim() == 2 and s.shape[1] == dm.D, "samples must be [n, %d]" % dm.D
-        need_cost = return_cost or k > 1
+        # frames mode at a large latent dimension: the density part is computed by a tensor-core launch INTO the cost array
+        need_cost = return_cost or k > 1 or (frames is not None and dm.D > 32 and (quality_scale != 0.0 or magnitude_scale != 0.0))
         cost = torch.empty((n,), dtype=torch.float32, device=dm.torch_device) if need_cost else None
         terms = torch.empty((self.n_terms, n), dtype=torch.float32, device=dm.torch_device) if return_terms else None
         best_cost = torch.empty((max(k, 1),), dtype=torch.float32, device=dm.torch_device)

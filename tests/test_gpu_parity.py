@@ -386,6 +386,23 @@ def test_large_rotation_and_trajectory_terms(large):
     assert rel_err(fused["cost"].cpu().numpy(), staged["cost"].cpu().numpy()).max() < RTOL
 
 
+def test_large_score_from_frames_with_naturalness(large):
+    """K5a at D = 103 with the naturalness and magnitude terms: the density comes from a tensor-core launch into the cost array,
+    the frames kernel adds the constraint error; equal to the fused scorer on the same candidates."""
+    dm, dc = large.dm, large.dc
+    S = dm.sample(3000, seed=4)
+    fr = dm.eval_frames(dm.backproject(S), dc.times)
+    for kw in ({"quality_scale": 0.1}, {"quality_scale": 0.1, "magnitude_scale": 2.0}, {}):
+        a = dc.score(S, k=1, return_cost=True, **kw)
+        b = dc.score(S, k=1, return_cost=True, frames=fr, **kw)
+        ca, cb = a["cost"].cpu().numpy(), b["cost"].cpu().numpy()
+        assert rel_err(cb, ca).max() < RTOL
+        ia, ib = int(a["best_idx"][0]), int(b["best_idx"][0])
+        assert ia == ib or abs(float(ca[ia]) - float(ca[ib])) < RTOL * max(1.0, abs(float(ca[ia])))
+        c = dc.score(S, k=1, frames=fr, **kw)                      # no cost array asked for: the engine supplies one
+        assert int(c["best_idx"][0]) == ib
+
+
 def test_large_sampler_tiled_equals_per_row(large):
     """K1 at D = 103: the register-tiled sampler (tiles of 128 candidates of one component, n >= 512) returns bit for bit the rows
     of the per-row sampler (which small calls still use), for a job of 40 003 candidates over 32 components, whole and as a

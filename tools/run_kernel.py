@@ -1,6 +1,6 @@
 #!/usr/bin/env python
 """Run ONE kernel of libmgb200.so a few times on cuda:0 (the target of ncu captures).
-usage: python tools/run_kernel.py <k1|k2tc|k2simt|k3|k4|k5a|k6|k1k6|k5b|k8|k9|k10|k11|multi> [--shape S|L] [--n N] [--reps R]"""
+usage: python tools/run_kernel.py <k1|k2tc|k2simt|k3|k4|k5a|k5c|k6|k1k6|k5b|k8|k9|k10|k11|multi> [--shape S|L] [--n N] [--reps R]"""
 import argparse
 import os
 import sys
@@ -45,6 +45,14 @@ def main():
     if a.kernel == "multi":
         jobs = [dict(dc=engine.DeviceConstraints(dm, mpc, prev), n=max(1, n // 4), seed=5 + j) for j in range(4)]
     seeds8 = dm.sample(8, seed=77)
+    if a.kernel == "k5c":
+        import ctypes as C
+        from morphablegraphs_b200 import _lib
+        lib = _lib.load()
+        cost = torch.rand(n, device="cuda")
+        tk_ws = torch.zeros(int(lib.mgb_score_workspace_bytes(n, 16)), dtype=torch.uint8, device="cuda")
+        tk_c = torch.empty(16, dtype=torch.float32, device="cuda")
+        tk_i = torch.empty(16, dtype=torch.int64, device="cuda")
     fns = {
         "k1": lambda: dm.sample(n, seed=7, counts=counts, out=S),
         "k2tc": lambda: dm.backproject(S, impl=2, out=coeffs),
@@ -61,6 +69,8 @@ def main():
         "k11": lambda: _lib.check(_lib.load().mgb_syrk_upper(C.c_void_p(X.data_ptr()), n, 1500, 1500, C.c_void_p(mean.data_ptr()),
                                                              C.c_void_p(up.data_ptr()), C.c_void_p(torch.cuda.current_stream().cuda_stream))),
         "multi": lambda: engine.sample_score_multi(jobs),
+        "k5c": lambda: _lib.check(lib.mgb_topk(C.c_void_p(cost.data_ptr()), n, 0, 16, C.c_void_p(tk_c.data_ptr()), C.c_void_p(tk_i.data_ptr()),
+                                               C.c_void_p(tk_ws.data_ptr()), tk_ws.numel(), C.c_void_p(torch.cuda.current_stream().cuda_stream))),
     }
     fn = fns[a.kernel]
     torch.cuda.synchronize()
