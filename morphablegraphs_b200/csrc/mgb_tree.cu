@@ -18,6 +18,7 @@
 #include <cuda_pipeline.h>
 #include <math.h>
 
+#include "mgb_device.cuh"
 #include "mgb_internal.cuh"
 
 namespace {
@@ -218,9 +219,15 @@ __global__ void __launch_bounds__(KM_WARPS * 32, 4) mgb_kmeans_level_small_kerne
     // centroids of the current node, NEGATED, zero for clusters beyond n_sub (read as float2 broadcasts: every offset below
     // is an even number of floats, so they are 8-byte aligned), then the ring of node ids
     static_assert(DA % 2 == 0 && DD % 2 == 0 && DD <= DA && NS % 2 == 0, "even sizes");
-    float* const scr = sm_tiles + (size_t)KM_WARPS * ST * tile_floats + (size_t)warp * (NS * DA * 33 + NS * DD + 5 * 32);
+    float* const scr = sm_tiles + (size_t)KM_WARPS * ST * tile_floats + (size_t)warp * (NS * DA * 33 + NS * DD + 5 * 32 + 2 * KM_SMALL_STAGES);
     float* const cen = scr + NS * DA * 33;
     int* const ids_s = reinterpret_cast<int*>(cen + NS * DD);      // [5][32] node ids of the tiles t .. t + 4
+    unsigned long long* const bars = reinterpret_cast<unsigned long long*>(ids_s + 5 * 32);   // one mbarrier per row buffer
+    if (lane == 0) {
+        for (int b = 0; b < ST; ++b) mgb_mbar_init(bars + b, 1);
+        mgb_fence_barrier_init();
+    }
+    __syncwarp();
     const long long gwarp = (long long)blockIdx.x * KM_WARPS + warp;
     const long long first = gwarp * tiles_per_warp * 32;
     long long last = first + tiles_per_warp * 32;
@@ -279,18 +286,24 @@ __global__ void __launch_bounds__(KM_WARPS * 32, 4) mgb_kmeans_level_small_kerne
         }
         inertia_part = 0.f;
     };
-    auto fetch = [&](long long t0, float* dst) {      // no commit: the caller closes the group
-        if (t0 < last) {
-            const int rows = (int)((last - t0 < 32) ? (last - t0) : 32);
-            const float* src = x + (size_t)t0 * ld;
-            if (rows == 32 && vec_ok) {
-                const int total4 = 8 * ld;
-                for (int e = lane; e < total4; e += 32) __pipeline_memcpy_async(dst + 4 * e, src + 4 * e, 16);
-            } else {
-                const int total = rows * ld;
-                for (int e = lane; e < total; e += 32) __pipeline_memcpy_async(dst + e, src + e, sizeof(float));
+    // rows of a tile -> buffer b.  A full, 16-byte aligned tile is ONE bulk copy issued by lane 0 and completes on the buffer's
+    // mbarrier (returns true); the last, partial tile goes through 4-byte asynchronous copies that complete with the caller's
+    // copy group (no commit here)
+    auto fetch = [&](long long t0, int b) -> bool {
+        float* dst = tile0 + b * tile_floats;
+        if (t0 >= last) return false;
+        const int rows = (int)((last - t0 < 32) ? (last - t0) : 32);
+        const float* src = x + (size_t)t0 * ld;
+        if (rows == 32 && vec_ok) {
+            if (lane == 0) {
+                mgb_fence_proxy_async();        // the buffer's previous rows were read through the generic proxy
+                mgb_tma_load_1d(dst, src, (unsigned int)(32 * ld * sizeof(float)), bars + b);
             }
+            return true;
         }
+        const int total = rows * ld;
+        for (int e = lane; e < total; e += 32) __pipeline_memcpy_async(dst + e, src + e, sizeof(float));
+        return false;
     };
     auto tile_skippable = [&](long long t0, int nd_lane) -> bool {
         if (t0 >= last) return true;
@@ -307,19 +320,20 @@ __global__ void __launch_bounds__(KM_WARPS * 32, 4) mgb_kmeans_level_small_kerne
         ids_s[q * 32 + lane] = (tq + lane < last) ? (node ? __ldg(node + tq + lane) : 0) : -1;
     }
     __syncwarp();
-    bool skq[2];
+    bool skq[2], blq[2];                           // tiles t, t + 1: skipped / fetched by a bulk copy
 #pragma unroll
     for (int q = 0; q < 2; ++q) {
         skq[q] = tile_skippable(first + 32 * q, ids_s[q * 32 + lane]);
-        if (!skq[q]) fetch(first + 32 * q, tile0 + q * tile_floats);
+        blq[q] = skq[q] ? false : fetch(first + 32 * q, q);
         __pipeline_commit();
     }
     int bi = 0, s5 = 0;                            // row buffer / id slot of the tile being processed
+    unsigned int ph = 0;                           // bit b: parity of the next completion of buffer b's mbarrier
     for (long long t0 = first; t0 < last; t0 += 32) {
         const int rows = (int)((last - t0 < 32) ? (last - t0) : 32);
         __pipeline_wait_prior(1);
         __syncwarp();
-        bool sk2;
+        bool sk2, bl2;
         {
             const long long tq = t0 + 64;
             int bq = bi + 2, sq = s5 + 2, sa = s5 + 4;
@@ -327,7 +341,7 @@ __global__ void __launch_bounds__(KM_WARPS * 32, 4) mgb_kmeans_level_small_kerne
             if (sq >= 5) sq -= 5;
             if (sa >= 5) sa -= 5;
             sk2 = tile_skippable(tq, (tq + lane < last) ? ids_s[sq * 32 + lane] : -1);
-            if (!sk2) fetch(tq, tile0 + bq * tile_floats);
+            bl2 = sk2 ? false : fetch(tq, bq);
             const long long ta = t0 + 128;
             if (ta + lane < last) {
                 if (node) __pipeline_memcpy_async(ids_s + sa * 32 + lane, node + ta + lane, sizeof(int));
@@ -339,9 +353,13 @@ __global__ void __launch_bounds__(KM_WARPS * 32, 4) mgb_kmeans_level_small_kerne
         }
         const float* tile = tile0 + bi * tile_floats;
         const int nd = (lane < rows) ? ids_s[s5 * 32 + lane] : -1;
-        const bool skip_cur = skq[0];
-        skq[0] = skq[1];
-        skq[1] = sk2;
+        const bool skip_cur = skq[0], bulk_cur = blq[0];
+        skq[0] = skq[1]; blq[0] = blq[1];
+        skq[1] = sk2; blq[1] = bl2;
+        if (bulk_cur) {
+            mgb_mbar_wait(bars + bi, (ph >> bi) & 1u);
+            ph ^= 1u << bi;
+        }
         if (++bi == 3) bi = 0;
         if (++s5 == 5) s5 = 0;
         if (skip_cur) continue;
@@ -417,7 +435,7 @@ int launch_level_small(const float* d_x, int64_t n, int dim, int dim_acc, int ld
                        int* d_label, float* d_sums, int* d_counts, float* d_node_inertia, float* d_inertia, cudaStream_t stream,
                        const int* d_skip) {
     auto kern = mgb_kmeans_level_small_kernel<NS, DA, DD>;
-    const size_t smem = ((size_t)KM_SMALL_STAGES * KM_WARPS * ((32 * ld + 1 + 3) & ~3) + (size_t)KM_WARPS * (NS * DA * 33 + NS * DD + 5 * 32)) * sizeof(float);
+    const size_t smem = ((size_t)KM_SMALL_STAGES * KM_WARPS * ((32 * ld + 1 + 3) & ~3) + (size_t)KM_WARPS * (NS * DA * 33 + NS * DD + 5 * 32 + 2 * KM_SMALL_STAGES)) * sizeof(float);
     static bool configured[MGB_MAX_DEVICES] = {false};
     if (int rc = mgb_opt_in_smem(kern, configured, 160 * 1024)) return rc;
     const long long tiles = (n + 31) / 32;
