@@ -395,6 +395,13 @@ int mgb_topk(const float* d_cost, int64_t n, int64_t index_base, int32_t k, floa
 int mgb_topk_noalloc(const float* d_cost, int64_t n, int64_t index_base, int32_t k, float* d_best_cost,
                      int64_t* d_best_idx, void* stream);
 
+/* k-means++ seeding step for every node of a level at once: d2[i] = min(d2[i], |x[i, :dim] - centers[node[i], :dim]|^2), or
+ * the squared distance itself when first != 0; d2 is float64.  centers[n_nodes, dim] = the centre chosen last in every node.
+ * Replaces the closest_dist_sq update inside the k-means++ initialisation of sklearn KMeans as the reference calls it
+ * (space_partitioning/clustering.py:74-80); the D^2 sampling on top of it (prefix sums, picks) stays index bookkeeping. */
+int mgb_min_sqdist(const float* d_x, int64_t n, int32_t dim, int32_t ld, const int32_t* d_node, const float* d_centers,
+                   double* d_d2, int32_t first, void* stream);
+
 /* K7: one Lloyd iteration (E-step + M-step sums) for every node of a cluster-tree level at once.
  * x[n, dim] (row stride ld) with the samples of one node stored contiguously (any order is
  * accepted; runs of equal node ids are what makes the accumulation cheap), node[n] = tree node of

@@ -18,6 +18,8 @@
 #include <cuda_pipeline.h>
 #include <math.h>
 
+#include <algorithm>
+
 #include "mgb_device.cuh"
 #include "mgb_internal.cuh"
 
@@ -562,6 +564,39 @@ int dispatch_level(const float* d_x, int64_t n, int dim, int dim_acc, int ld, co
 }
 
 }  // namespace
+
+// k-means++ seeding helper: d2[i] = min(d2[i], |x[i, :dim] - centers[node[i]]|^2) (or just the distance when first != 0), in
+// float64 like the seeding of sklearn's KMeans (cluster/_kmeans.py _kmeans_plusplus: closest_dist_sq).  One pass over the rows
+// of a level in place of six element-wise library kernels per chosen centre.
+namespace {
+__global__ void __launch_bounds__(256) mgb_min_sqdist_kernel(const float* __restrict__ x, long long n, int dim, int ld, const int* __restrict__ node,
+                                                            const float* __restrict__ centers, double* __restrict__ d2, int first) {
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        const float* xi = x + (size_t)i * ld;
+        const float* c = centers + (size_t)(node ? __ldg(node + i) : 0) * dim;
+        float acc = 0.f;
+        for (int j = 0; j < dim; ++j) {
+            const float e = __ldg(xi + j) - __ldg(c + j);
+            acc += e * e;                         // float32 terms summed in order, as the element-wise form did
+        }
+        const double v = (double)acc;
+        d2[i] = first ? v : fmin(d2[i], v);
+    }
+}
+}  // namespace
+
+extern "C" int mgb_min_sqdist(const float* d_x, int64_t n, int32_t dim, int32_t ld, const int32_t* d_node, const float* d_centers, double* d_d2,
+                              int32_t first, void* stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    MGB_REQUIRE(n >= 0 && dim > 0 && ld >= dim, "bad shape");
+    if (n == 0) return MGB_OK;
+    MGB_REQUIRE(d_x && d_centers && d_d2, "null argument");
+    const long long blocks = std::min<long long>((n + 255) / 256, (long long)sm_count_tree() * 16);
+    mgb_min_sqdist_kernel<<<(unsigned)blocks, 256, 0, stream>>>(d_x, n, dim, ld, d_node, d_centers, d_d2, first);
+    mgb_count_launch();
+    MGB_CUDA(cudaGetLastError());
+    return MGB_OK;
+}
 
 extern "C" int mgb_kmeans_assign_update(const float* d_x, int64_t n, int32_t dim, int32_t ld, const int32_t* d_node,
                                         const float* d_centroids, int32_t n_sub, int32_t* d_label, float* d_sums,

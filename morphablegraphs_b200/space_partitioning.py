@@ -23,6 +23,7 @@ Two things run on the GPU:
 The flat layout: cluster nodes and kd nodes are rows of integer arrays; `points[M, D]` holds every
 evaluable point, `node_row` / `kd_row` index into it.
 """
+import ctypes as C
 import heapq
 
 import numpy as np
@@ -578,7 +579,23 @@ def _kmeanspp_seeds(x, dim, starts, counts, n_sub, gen):
     u = torch.rand((n_nodes, n_sub), generator=gen, device=dev, dtype=torch.float64)
     first = starts + (u[:, 0] * counts).long().minimum(counts - 1)
     cent[:, 0] = x[first, :dim]
-    d2 = ((x[:, :dim] - cent[node, 0]) ** 2).sum(dim=1).double()
+    if dev.type == "cuda":
+        # the closest-distance update as ONE pass (mgb_min_sqdist) instead of six element-wise kernels per centre
+        node32 = node.to(torch.int32)
+        d2 = torch.empty(x.shape[0], dtype=torch.float64, device=dev)
+        xc = x if x.is_contiguous() else x.contiguous()
+
+        def update(j, first_pass):
+            cj = cent[:, j].contiguous()
+            with torch.cuda.device(dev):
+                engine._lib.check(engine._lib.load().mgb_min_sqdist(C.c_void_p(xc.data_ptr()), int(xc.shape[0]), int(dim), int(xc.shape[1]),
+                                                                   C.c_void_p(node32.data_ptr()), C.c_void_p(cj.data_ptr()), C.c_void_p(d2.data_ptr()),
+                                                                   1 if first_pass else 0, C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)))
+    else:
+        d2 = ((x[:, :dim] - cent[node, 0]) ** 2).sum(dim=1).double()
+        update = None
+    if update is not None:
+        update(0, True)
     for j in range(1, n_sub):
         cs = torch.cumsum(d2, dim=0)
         base = torch.where(starts > 0, cs[(starts - 1).clamp(min=0)], torch.zeros_like(cs[:1]).expand(n_nodes))
@@ -587,7 +604,11 @@ def _kmeanspp_seeds(x, dim, starts, counts, n_sub, gen):
         pick = torch.searchsorted(cs, target, right=True)
         pick = torch.maximum(torch.minimum(pick, starts + counts - 1), starts)
         cent[:, j] = x[pick, :dim]
-        d2 = torch.minimum(d2, ((x[:, :dim] - cent[node, j]) ** 2).sum(dim=1).double())
+        if j + 1 < n_sub:                  # the last centre's distances are never read
+            if update is not None:
+                update(j, False)
+            else:
+                d2 = torch.minimum(d2, ((x[:, :dim] - cent[node, j]) ** 2).sum(dim=1).double())
     return cent.contiguous()
 
 
@@ -702,27 +723,45 @@ def _device_of(device):
     return torch.device("cuda", torch.cuda.current_device())
 
 
+_SUB_TIMING = {}
+
+
 def _subdivide_level(Xl, dim, n_sub, starts, counts, depth, gids, seeds, gen, dim_acc):
     """One tree level: k-means of every live node, samples re-sorted by (node, label).
     Returns (perm, child_node [n_children] index of the parent within the level, child_counts,
     child_means [n_children, dim_acc], parent_mean [n_live, dim_acc], iterations)."""
     torch = engine._torch()
+    import os
+    import time
+    timing = _SUB_TIMING if os.environ.get("MGB_TREE_TIMING") else None
+
+    def tick(name, t0):
+        if timing is not None:
+            torch.cuda.synchronize() if Xl.device.type == "cuda" else None
+            timing[name] = timing.get(name, 0.0) + time.perf_counter() - t0
+        return time.perf_counter()
+
+    t0 = time.perf_counter()
     n_live = int(starts.shape[0])
     node64 = torch.repeat_interleave(torch.arange(n_live, device=Xl.device), counts)
     node = node64.to(torch.int32).contiguous()
     mean, tol, _ = _segment_stats(Xl, dim, node, n_live, dim_acc)
+    t0 = tick("  node ids + stats", t0)
     if seeds is not None:
         cent = seeds(depth, gids, starts, counts, Xl)
         cent = torch.as_tensor(cent, dtype=torch.float32, device=Xl.device).contiguous()
     else:
         cent = _kmeanspp_seeds(Xl, dim, starts, counts, n_sub, gen)
+    t0 = tick("  seeding", t0)
     r = _lloyd_level(Xl, dim, node, n_live, n_sub, cent, tol, dim_acc)
+    t0 = tick("  Lloyd", t0)
     key = node64 * n_sub + r["label"].long()
     perm = torch.argsort(key, stable=True)
     flat_counts = r["counts"].reshape(-1).long()
     ck = torch.nonzero(flat_counts > 0).reshape(-1)          # ascending = (node, label) order
     cc = flat_counts[ck]
     means = r["sums"].reshape(-1, dim_acc)[ck] / cc[:, None].to(torch.float32)
+    tick("  sort by (node, label) + child means", t0)
     return perm, ck // n_sub, cc, means, mean, r["iters"]
 
 
@@ -811,6 +850,8 @@ def build_cluster_tree(data, n_sub, max_level, dim, use_kd_tree=True, seeds=None
     kd_pt, kd_l, kd_r, kd_in, roots = _build_kd_forest(X, rows, seg_len, dim)
     t0 = tick("kd forest", t0)
     if timing is not None:
+        timing.update(_SUB_TIMING)
+        _SUB_TIMING.clear()
         info["timing"] = timing
     # ---- flat arrays on the host ------------------------------------------------------------
     t = FlatClusterTree()
