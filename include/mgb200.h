@@ -402,6 +402,15 @@ int mgb_topk_noalloc(const float* d_cost, int64_t n, int64_t index_base, int32_t
 int mgb_min_sqdist(const float* d_x, int64_t n, int32_t dim, int32_t ld, const int32_t* d_node, const float* d_centers,
                    double* d_d2, int32_t first, void* stream);
 
+/* k-means++ seeding, the pick, for every node of a level at once: node i owns rows [starts[i], starts[i] + counts[i]) of x;
+ * with prefix == NULL the row start + min(floor(u counts), counts - 1) is chosen (first centre), else the first row of the node
+ * whose GLOBAL inclusive prefix sum of the closest squared distances (prefix[n], float64) exceeds
+ * prefix[start - 1] + u * (mass of the node) (D^2 sampling, one trial per centre); u[i * u_stride] in [0, 1).  The chosen row's
+ * first dim columns go to centers[i * center_stride ...].  Same reference lines as mgb_min_sqdist. */
+int mgb_kmeanspp_pick(const float* d_x, int32_t dim, int32_t ld, const int64_t* d_starts, const int64_t* d_counts, int32_t n_nodes,
+                      const double* d_u, int32_t u_stride, const double* d_prefix, float* d_centers, int32_t center_stride,
+                      void* stream);
+
 /* K7: one Lloyd iteration (E-step + M-step sums) for every node of a cluster-tree level at once.
  * x[n, dim] (row stride ld) with the samples of one node stored contiguously (any order is
  * accepted; runs of equal node ids are what makes the accumulation cheap), node[n] = tree node of

@@ -140,6 +140,7 @@ SYMBOLS = {
     "mgb_topk_noalloc": (C.c_int, [_vp, _i64, _i64, _i32, _vp, _vp, _vp]),
     "mgb_kmeans_assign_update": (C.c_int, [_vp, _i64, _i32, _i32, _vp, _vp, _i32, _vp, _vp, _vp, _vp, _vp]),
     "mgb_min_sqdist": (C.c_int, [_vp, _i64, _i32, _i32, _vp, _vp, _vp, _i32, _vp]),
+    "mgb_kmeanspp_pick": (C.c_int, [_vp, _i32, _i32, _vp, _vp, _i32, _vp, _i32, _vp, _vp, _i32, _vp]),
     "mgb_kmeans_level": (C.c_int, [_vp, _i64, _i32, _i32, _i32, _vp, _i32, _i32, _vp, _vp, _i32, _i32, _vp, _vp, _vp, _vp, _vp,
                                    C.POINTER(C.c_int32), _vp]),
     "mgb_exchange_slot_bytes": (C.c_size_t, [_i32]),

@@ -598,6 +598,54 @@ extern "C" int mgb_min_sqdist(const float* d_x, int64_t n, int32_t dim, int32_t 
     return MGB_OK;
 }
 
+// k-means++ seeding, the pick: for every node (rows [start, start + count) of x) choose a row - uniformly when cs == NULL
+// (first centre: start + min(floor(u count), count - 1)), else by D^2 sampling over the GLOBAL inclusive prefix sums cs of the
+// closest squared distances: the first row of the node whose prefix sum exceeds base + u * (mass of the node) - and copy its
+// first dim columns to centers[node].  One thread per node (a binary search), all nodes of a level per launch.
+namespace {
+__global__ void __launch_bounds__(128) mgb_kmeanspp_pick_kernel(const float* __restrict__ x, int dim, int ld, const long long* __restrict__ starts,
+                                                               const long long* __restrict__ counts, int n_nodes, const double* __restrict__ u,
+                                                               int u_stride, const double* __restrict__ cs, float* __restrict__ centers,
+                                                               int c_stride) {
+    const int nd = blockIdx.x * blockDim.x + threadIdx.x;
+    if (nd >= n_nodes) return;
+    const long long start = starts[nd], count = counts[nd];
+    const double un = u[(size_t)nd * u_stride];
+    long long pick;
+    if (cs == nullptr) {
+        pick = start + min((long long)(un * (double)count), count - 1);
+    } else {
+        const double base = start > 0 ? cs[start - 1] : 0.0;
+        const double target = base + un * (cs[start + count - 1] - base);
+        long long lo = start, hi = start + count;          // first index in [start, start + count) with cs[i] > target
+        while (lo < hi) {
+            const long long mid = (lo + hi) >> 1;
+            if (cs[mid] > target) hi = mid;
+            else lo = mid + 1;
+        }
+        pick = min(lo, start + count - 1);
+    }
+    const float* row = x + (size_t)pick * ld;
+    float* c = centers + (size_t)nd * c_stride;
+    for (int j = 0; j < dim; ++j) c[j] = row[j];
+}
+}  // namespace
+
+extern "C" int mgb_kmeanspp_pick(const float* d_x, int32_t dim, int32_t ld, const int64_t* d_starts, const int64_t* d_counts, int32_t n_nodes,
+                                 const double* d_u, int32_t u_stride, const double* d_prefix, float* d_centers, int32_t center_stride,
+                                 void* stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    MGB_REQUIRE(n_nodes >= 0 && dim > 0 && ld >= dim && center_stride >= dim && u_stride >= 1, "bad shape");
+    if (n_nodes == 0) return MGB_OK;
+    MGB_REQUIRE(d_x && d_starts && d_counts && d_u && d_centers, "null argument");
+    mgb_kmeanspp_pick_kernel<<<(n_nodes + 127) / 128, 128, 0, stream>>>(d_x, dim, ld, reinterpret_cast<const long long*>(d_starts),
+                                                                        reinterpret_cast<const long long*>(d_counts), n_nodes, d_u, u_stride,
+                                                                        d_prefix, d_centers, center_stride);
+    mgb_count_launch();
+    MGB_CUDA(cudaGetLastError());
+    return MGB_OK;
+}
+
 extern "C" int mgb_kmeans_assign_update(const float* d_x, int64_t n, int32_t dim, int32_t ld, const int32_t* d_node,
                                         const float* d_centroids, int32_t n_sub, int32_t* d_label, float* d_sums,
                                         int32_t* d_counts, float* d_inertia, void* stream_) {

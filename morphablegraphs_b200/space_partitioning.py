@@ -577,25 +577,30 @@ def _kmeanspp_seeds(x, dim, starts, counts, n_sub, gen):
     node = torch.repeat_interleave(torch.arange(n_nodes, device=dev), counts)
     cent = torch.empty((n_nodes, n_sub, dim), dtype=torch.float32, device=dev)
     u = torch.rand((n_nodes, n_sub), generator=gen, device=dev, dtype=torch.float64)
+    if dev.type == "cuda":
+        # per centre: ONE pick kernel for all nodes (mgb_kmeanspp_pick), ONE closest-distance pass (mgb_min_sqdist) and the
+        # library prefix sum in between - instead of ~14 element-wise / index kernels
+        lib = engine._lib.load()
+        p = lambda t: C.c_void_p(t.data_ptr())
+        node32 = node.to(torch.int32)
+        xc = x if x.is_contiguous() else x.contiguous()
+        st, ct = starts.contiguous(), counts.contiguous()
+        d2 = torch.empty(xc.shape[0], dtype=torch.float64, device=dev)
+        cj = torch.empty((n_nodes, dim), dtype=torch.float32, device=dev)
+        with torch.cuda.device(dev):
+            stream = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+            for j in range(n_sub):
+                cs = torch.cumsum(d2, dim=0) if j > 0 else None
+                engine._lib.check(lib.mgb_kmeanspp_pick(p(xc), int(dim), int(xc.shape[1]), p(st), p(ct), int(n_nodes), C.c_void_p(u.data_ptr() + 8 * j),
+                                                        int(n_sub), p(cs) if cs is not None else C.c_void_p(0), p(cj), int(dim), stream))
+                cent[:, j] = cj
+                if j + 1 < n_sub:          # the last centre's distances are never read
+                    engine._lib.check(lib.mgb_min_sqdist(p(xc), int(xc.shape[0]), int(dim), int(xc.shape[1]), p(node32), p(cj), p(d2),
+                                                         1 if j == 0 else 0, stream))
+        return cent.contiguous()
     first = starts + (u[:, 0] * counts).long().minimum(counts - 1)
     cent[:, 0] = x[first, :dim]
-    if dev.type == "cuda":
-        # the closest-distance update as ONE pass (mgb_min_sqdist) instead of six element-wise kernels per centre
-        node32 = node.to(torch.int32)
-        d2 = torch.empty(x.shape[0], dtype=torch.float64, device=dev)
-        xc = x if x.is_contiguous() else x.contiguous()
-
-        def update(j, first_pass):
-            cj = cent[:, j].contiguous()
-            with torch.cuda.device(dev):
-                engine._lib.check(engine._lib.load().mgb_min_sqdist(C.c_void_p(xc.data_ptr()), int(xc.shape[0]), int(dim), int(xc.shape[1]),
-                                                                   C.c_void_p(node32.data_ptr()), C.c_void_p(cj.data_ptr()), C.c_void_p(d2.data_ptr()),
-                                                                   1 if first_pass else 0, C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)))
-    else:
-        d2 = ((x[:, :dim] - cent[node, 0]) ** 2).sum(dim=1).double()
-        update = None
-    if update is not None:
-        update(0, True)
+    d2 = ((x[:, :dim] - cent[node, 0]) ** 2).sum(dim=1).double()
     for j in range(1, n_sub):
         cs = torch.cumsum(d2, dim=0)
         base = torch.where(starts > 0, cs[(starts - 1).clamp(min=0)], torch.zeros_like(cs[:1]).expand(n_nodes))
@@ -604,11 +609,7 @@ def _kmeanspp_seeds(x, dim, starts, counts, n_sub, gen):
         pick = torch.searchsorted(cs, target, right=True)
         pick = torch.maximum(torch.minimum(pick, starts + counts - 1), starts)
         cent[:, j] = x[pick, :dim]
-        if j + 1 < n_sub:                  # the last centre's distances are never read
-            if update is not None:
-                update(j, False)
-            else:
-                d2 = torch.minimum(d2, ((x[:, :dim] - cent[node, j]) ** 2).sum(dim=1).double())
+        d2 = torch.minimum(d2, ((x[:, :dim] - cent[node, j]) ** 2).sum(dim=1).double())
     return cent.contiguous()
 
 

@@ -326,3 +326,39 @@ def test_syrk_tensor_core_covariance(n, d, pad):
     assert (np.abs(got[iu] - 1.0 - want[iu]) / scale).max() < 2e-5
     il = np.tril_indices(d, -1)
     assert (got[il] == 1.0).all()          # the lower triangle is not touched
+
+
+@pytest.mark.gpu
+def test_kmeanspp_seeding_kernels_follow_the_d2_rule():
+    """mgb_kmeanspp_pick + mgb_min_sqdist (k-means++ seeding of every node of a level at once): every centre is a row of its own
+    node, the first one is the uniform pick, and the later ones are the D^2 picks a float64 numpy restatement makes from the same
+    uniforms (prefix sums differ in the last bits between a parallel and a sequential scan: 99 % agreement required)."""
+    from morphablegraphs_b200 import space_partitioning as sp
+    rng = np.random.RandomState(5)
+    sizes = np.array([1, 2, 5, 700, 33, 4096, 64, 9000, 3], dtype=np.int64)
+    n, ld, dim, n_sub = int(sizes.sum()), 13, 10, 4
+    X = (rng.randn(n, ld) * 3.0).astype(np.float32)
+    starts = np.concatenate([[0], np.cumsum(sizes)[:-1]])
+    dev = torch.device("cuda", 0)
+    xd = torch.as_tensor(X, device=dev)
+    st, ct = torch.as_tensor(starts, device=dev), torch.as_tensor(sizes, device=dev)
+    agree = total = 0
+    for seed in range(20):
+        gen = torch.Generator(device=dev)
+        gen.manual_seed(seed)
+        cent = sp._kmeanspp_seeds(xd, dim, st, ct, n_sub, gen).cpu().numpy()
+        gen.manual_seed(seed)
+        u = torch.rand((len(sizes), n_sub), generator=gen, device=dev, dtype=torch.float64).cpu().numpy()
+        for i, (s0, c0) in enumerate(zip(starts, sizes)):
+            rows = X[s0:s0 + c0, :dim]
+            for j in range(n_sub):          # a row of the node
+                assert (np.abs(rows - cent[i, j][None]).max(axis=1) == 0).any(), (seed, i, j)
+            assert np.array_equal(cent[i, 0], rows[min(int(u[i, 0] * c0), c0 - 1)])
+            d2 = ((rows.astype(np.float64) - cent[i, 0].astype(np.float64)) ** 2).sum(axis=1)
+            for j in range(1, n_sub):
+                cs = np.cumsum(d2)
+                pick = min(int(np.searchsorted(cs, u[i, j] * cs[-1], side="right")), c0 - 1)
+                total += 1
+                agree += int(np.array_equal(cent[i, j], rows[pick]))
+                d2 = np.minimum(d2, ((rows.astype(np.float64) - cent[i, j].astype(np.float64)) ** 2).sum(axis=1))
+    assert agree >= 0.99 * total, (agree, total)
