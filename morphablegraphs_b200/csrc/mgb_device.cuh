@@ -93,6 +93,48 @@ __device__ __forceinline__ void mgb_sample_row_reg(const float4* __restrict__ L4
     }
 }
 
+// Two candidates of the same mixture component at once: every Cholesky row (and mean) is loaded ONCE for both; each candidate's
+// sums keep the order of mgb_sample_row_reg, so its row has the same bits.
+template <int NREG>
+__device__ __forceinline__ void mgb_sample_rows_reg2(const float4* __restrict__ L4, int LS, const float* __restrict__ mu, int D,
+                                                    unsigned long long gi0, unsigned long long gi1, uint2 key, float (&s0)[NREG],
+                                                    float (&s1)[NREG]) {
+    float z0[NREG], z1[NREG];
+#pragma unroll
+    for (int b = 0; b < NREG / 4; ++b) {
+        if (4 * b < D) {
+            float q[4];
+            mgb_normal4(gi0, (unsigned int)b, key, q);
+            z0[4 * b] = q[0]; z0[4 * b + 1] = q[1]; z0[4 * b + 2] = q[2]; z0[4 * b + 3] = q[3];
+            mgb_normal4(gi1, (unsigned int)b, key, q);
+            z1[4 * b] = q[0]; z1[4 * b + 1] = q[1]; z1[4 * b + 2] = q[2]; z1[4 * b + 3] = q[3];
+        } else {
+            z0[4 * b] = z0[4 * b + 1] = z0[4 * b + 2] = z0[4 * b + 3] = 0.f;
+            z1[4 * b] = z1[4 * b + 1] = z1[4 * b + 2] = z1[4 * b + 3] = 0.f;
+        }
+    }
+    const int LS4 = LS >> 2;
+#pragma unroll
+    for (int d = 0; d < NREG; ++d) {
+        float a0 = 0.f, a1 = 0.f;
+        if (d < D) {
+            a0 = a1 = mu[d];
+            const float4* Lr = L4 + d * LS4;
+#pragma unroll
+            for (int c = 0; c <= d / 4; ++c) {
+                const float4 l = Lr[c];
+                a0 = fmaf(l.x, z0[4 * c], a0);
+                a1 = fmaf(l.x, z1[4 * c], a1);
+                if (4 * c + 1 <= d) { a0 = fmaf(l.y, z0[4 * c + 1], a0); a1 = fmaf(l.y, z1[4 * c + 1], a1); }
+                if (4 * c + 2 <= d) { a0 = fmaf(l.z, z0[4 * c + 2], a0); a1 = fmaf(l.z, z1[4 * c + 2], a1); }
+                if (4 * c + 3 <= d) { a0 = fmaf(l.w, z0[4 * c + 3], a0); a1 = fmaf(l.w, z1[4 * c + 3], a1); }
+            }
+        }
+        s0[d] = a0;
+        s1[d] = a1;
+    }
+}
+
 // same with the row in memory (any D): z is written to row[], then s in place from the last row up
 __device__ __forceinline__ void mgb_sample_row_mem(const float* __restrict__ L, int LS, const float* __restrict__ mu, int D,
                                                    unsigned long long gi, uint2 key, float* row) {

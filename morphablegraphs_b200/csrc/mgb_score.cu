@@ -207,6 +207,8 @@ __device__ __forceinline__ void score_body(const ScoreParams& p, const int cta, 
         long long idx[CPT];
         bool valid[CPT];
         float s[CPT][NR];
+        int g_first = 0;                       // CPT == 2, sampling: component / global index of the thread's first candidate
+        unsigned long long gi_first = 0;
         const TIn* srow[CPT];
         const float* frow[CPT];
         float* myrow[CPT];
@@ -229,7 +231,23 @@ __device__ __forceinline__ void score_body(const ScoreParams& p, const int cta, 
                     // without a density or magnitude term only the K spatial entries of s are ever read: rows >= K of the
                     // Cholesky product (and the normals only they need) are dead - the entries that ARE computed keep their bits
                     const int d_need = (p.quality_scale == 0.f && p.magnitude_scale == 0.f) ? p.K : D;
-                    mgb_sample_row_reg<NR>(reinterpret_cast<const float4*>(chol + (size_t)g * D * p.LS), p.LS, mus + (size_t)g * D, d_need, gi, key, s[c]);
+                    if constexpr (CPT == 2) {
+                        // both candidates of the thread are drawn together when they share a component (all but the tiles that
+                        // straddle a component boundary): one load of every Cholesky row for the two
+                        if (c == 0) {
+                            g_first = g;
+                        } else if (g == g_first) {
+                            mgb_sample_rows_reg2<NR>(reinterpret_cast<const float4*>(chol + (size_t)g * D * p.LS), p.LS, mus + (size_t)g * D, d_need,
+                                                     gi_first, gi, key, s[0], s[1]);
+                        } else {
+                            mgb_sample_row_reg<NR>(reinterpret_cast<const float4*>(chol + (size_t)g_first * D * p.LS), p.LS, mus + (size_t)g_first * D,
+                                                   d_need, gi_first, key, s[0]);
+                            mgb_sample_row_reg<NR>(reinterpret_cast<const float4*>(chol + (size_t)g * D * p.LS), p.LS, mus + (size_t)g * D, d_need, gi, key, s[1]);
+                        }
+                        gi_first = gi;
+                    } else {
+                        mgb_sample_row_reg<NR>(reinterpret_cast<const float4*>(chol + (size_t)g * D * p.LS), p.LS, mus + (size_t)g * D, d_need, gi, key, s[c]);
+                    }
                 } else {
                     mgb_sample_row_mem(chol + (size_t)g * D * p.LS, p.LS, mus + (size_t)g * D, D, gi, key, myrow[c]);
                 }
