@@ -898,7 +898,10 @@ def build_feature_tree(features, data, n_sub, seeds=None, seed=0, device=None):
     data = np.asarray(data)
     N, Fd = features.shape
     D = data.shape[1]
-    X = torch.as_tensor(np.ascontiguousarray(np.concatenate([features, data], axis=1), dtype=np.float32), device=dev)
+    # [features | data] rows in float32 on the device, each part converted into and copied from the pinned staging buffer
+    X = torch.empty((N, Fd + D), dtype=torch.float32, device=dev)
+    X[:, :Fd] = _upload_f32(features, dev)
+    X[:, Fd:] = _upload_f32(data, dev)
     means, exact, first_sample = [None], [torch.full((1,), -1, dtype=torch.long, device=dev)], [torch.zeros(1, dtype=torch.long, device=dev)]
     edges_parent, edges_child = [], []
     n_nodes = 1
@@ -959,17 +962,18 @@ def build_feature_tree(features, data, n_sub, seeds=None, seed=0, device=None):
         gids, counts = cg[live], cc[live]
         starts = torch.cumsum(counts, 0) - counts
         depth += 1
-    pts = torch.cat(means).double().cpu().numpy()
-    ex = torch.cat(exact).cpu().numpy()
+    # child lists sorted by parent and prefix-summed on the device; everything comes back through the pinned staging buffer
+    e = torch.empty(0, dtype=torch.long, device=dev)
+    par = torch.cat(edges_parent) if edges_parent else e
+    chi = torch.cat(edges_child) if edges_child else e
+    o = torch.argsort(par, stable=True)
+    cptr = torch.zeros(n_nodes + 1, dtype=torch.long, device=dev)
+    cptr[1:] = torch.cumsum(torch.bincount(par, minlength=n_nodes), 0)
+    pts, ex, child_ptr, child_idx, first = _to_host(torch.cat(means).double(), torch.cat(exact), cptr, chi[o], torch.cat(first_sample))
     sel = ex >= 0
-    pts[sel] = np.asarray(data, dtype=np.float64)[ex[sel]]
-    par = torch.cat(edges_parent).cpu().numpy() if edges_parent else np.empty(0, dtype=np.int64)
-    chi = torch.cat(edges_child).cpu().numpy() if edges_child else np.empty(0, dtype=np.int64)
-    o = np.argsort(par, kind="stable")
-    child_ptr = np.zeros(n_nodes + 1, dtype=np.int64)
-    child_ptr[1:] = np.cumsum(np.bincount(par, minlength=n_nodes))
+    pts[sel] = np.asarray(data, dtype=np.float64)[ex[sel]]          # single-sample nodes carry the sample itself, in float64
     info["n_nodes"] = n_nodes
-    flat = (pts, np.arange(n_nodes, dtype=np.int64), child_ptr, chi[o], torch.cat(first_sample).cpu().numpy())
+    flat = (pts, np.arange(n_nodes, dtype=np.int64), child_ptr, child_idx, first)
     return flat, info
 
 
