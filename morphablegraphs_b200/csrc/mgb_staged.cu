@@ -338,7 +338,8 @@ __device__ __forceinline__ void quat_R(float w, float x, float y, float z, float
 struct FkStep {
     int node_type;   // MGB_NODE_*
     int channel;     // quaternion_frame_index or -1
-    int parent_slot; // slot (in the plan) of the parent, -1 for the root
+    int parent_slot; // depth of the node in the walk (the plan is in depth-first order): its parent's transform sits one level up;
+                     // -1 for the root
     int out_index;   // >= 0: write position to output column out_index
     float off[3];
     float rot[9];    // fixed rotation
@@ -346,6 +347,7 @@ struct FkStep {
 
 #define FK_BLOCK 128
 #define FK_MAX_PLAN 160
+#define FK_MAX_DEPTH 16
 __global__ void __launch_bounds__(FK_BLOCK) mgb_fk_kernel(const float* __restrict__ frames, int P, long long n_frames, const FkStep* __restrict__ plan,
                                                          int n_plan, int n_out, float* __restrict__ pos) {
     extern __shared__ __align__(16) float smf[];
@@ -376,8 +378,10 @@ __global__ void __launch_bounds__(FK_BLOCK) mgb_fk_kernel(const float* __restric
         __syncthreads();
         const float* f = sm_frames + threadIdx.x * SROW;
         float* o = sm_out + threadIdx.x * OROW;
-        // global transforms of the plan's nodes, kept in local memory (12 floats per node)
-        float Gm[FK_MAX_PLAN][12];
+        // global transforms of the nodes on the current root-to-node path, one slot per depth (the plan is a depth-first walk:
+        // a node's parent is the last node written one level up).  768 B of local memory instead of 12 floats per plan node
+        // (7.7 KB, which made every transform an L1 / L2 round trip)
+        float Gm[FK_MAX_DEPTH][12];
         for (int sidx = 0; sidx < n_plan; ++sidx) {
             const FkStep& st = sm_plan[sidx];
             float Rl[9], tl[3] = {st.off[0], st.off[1], st.off[2]};
@@ -394,7 +398,7 @@ __global__ void __launch_bounds__(FK_BLOCK) mgb_fk_kernel(const float* __restric
 #pragma unroll
                 for (int q = 0; q < 9; ++q) Rl[q] = st.rot[q];
             }
-            float* Gc = Gm[sidx];
+            float* Gc = Gm[st.parent_slot + 1];
             if (st.parent_slot < 0) {
                 if (has_rot) {
 #pragma unroll
@@ -609,28 +613,37 @@ extern "C" int mgb_fk(const mgb_model* m, const float* d_frames, int64_t n_frame
             nd = m->parent[nd];
         }
     }
+    // depth-first walk over the needed nodes (explicit stack); the kernel keeps one transform per depth
     std::vector<FkStep> plan;
-    std::vector<int> slot(m->n_nodes, -1);
-    for (int nd = 0; nd < m->n_nodes; ++nd) {
-        if (!need[nd]) continue;
-        // a node requested several times gets one step per extra output (cheap, rare)
+    int max_depth = 0;
+    std::vector<std::pair<int, int>> todo;     // (node, depth of its parent)
+    for (int nd = m->n_nodes - 1; nd >= 0; --nd)
+        if (need[nd] && m->parent[nd] < 0) todo.push_back({nd, -1});
+    while (!todo.empty()) {
+        const int nd = todo.back().first, pdepth = todo.back().second;
+        todo.pop_back();
+        // a node requested several times gets one step per extra output (cheap, rare): same depth, same parent
         for (size_t rep = 0; rep < (outs[nd].empty() ? 1 : outs[nd].size()); ++rep) {
             FkStep st;
             st.node_type = m->type[nd];
             st.channel = m->channel[nd];
-            st.parent_slot = m->parent[nd] >= 0 ? slot[m->parent[nd]] : -1;
+            st.parent_slot = pdepth;
             st.out_index = outs[nd].empty() ? -1 : outs[nd][rep];
             for (int q = 0; q < 3; ++q) st.off[q] = (float)m->offset[nd * 3 + q];
             for (int q = 0; q < 9; ++q) st.rot[q] = (float)m->fixed_rot[nd * 9 + q];
-            if (rep == 0) slot[nd] = (int)plan.size();
             plan.push_back(st);
         }
+        max_depth = std::max(max_depth, pdepth + 1);
+        const std::vector<int>& kids = m->children[nd];
+        for (int i = (int)kids.size() - 1; i >= 0; --i)
+            if (need[kids[i]]) todo.push_back({kids[i], pdepth + 1});
     }
     MGB_REQUIRE((int)plan.size() <= FK_MAX_PLAN, "FK plan of %d nodes exceeds %d", (int)plan.size(), FK_MAX_PLAN);
+    MGB_REQUIRE(max_depth < FK_MAX_DEPTH, "skeleton deeper than %d levels", FK_MAX_DEPTH);
     FkStep* d_plan = nullptr;
     MGB_CUDA(cudaMallocAsync((void**)&d_plan, sizeof(FkStep) * plan.size(), stream));
+    // pageable source: the runtime stages it before the call returns, so `plan` may go out of scope without a synchronisation
     MGB_CUDA(cudaMemcpyAsync(d_plan, plan.data(), sizeof(FkStep) * plan.size(), cudaMemcpyHostToDevice, stream));
-    MGB_CUDA(cudaStreamSynchronize(stream));
     int fkb = FK_BLOCK;
     size_t smem = 0;
     for (;; fkb >>= 1) {
