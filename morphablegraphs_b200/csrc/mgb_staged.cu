@@ -316,48 +316,34 @@ __global__ void __launch_bounds__(256) mgb_eval_frames_kernel(const float* __res
 }
 
 // ---------------------------------------------------------------------------
-// K4: forward kinematics of listed nodes.  Thread per frame; a tile of frames
-// is staged in shared memory (rows of P floats, odd stride), each thread walks
-// the parent chains from a per-call "plan" (node order with parents first).
+// K4: forward kinematics of listed nodes.  A tile of frames is staged in shared memory (rows of P floats, odd stride).
 // ---------------------------------------------------------------------------
+#define FK_BLOCK 128
 
-__device__ __forceinline__ void quat_R(float w, float x, float y, float z, float* R) {
-    float n = w * w + x * x + y * y + z * z;
-    if (n < MGB_QUAT_EPS) {
-        R[0] = 1.f; R[1] = 0.f; R[2] = 0.f; R[3] = 0.f; R[4] = 1.f; R[5] = 0.f; R[6] = 0.f; R[7] = 0.f; R[8] = 1.f;
-        return;
-    }
-    float s = __fdividef(2.0f, n);
-    float xs = x * s, ys = y * s, zs = z * s;
-    float wx = w * xs, wy = w * ys, wz = w * zs, xx = x * xs, xy = x * ys, xz = x * zs, yy = y * ys, yz = y * zs, zz = z * zs;
-    R[0] = 1.f - (yy + zz); R[1] = xy - wz; R[2] = xz + wy;
-    R[3] = xy + wz; R[4] = 1.f - (xx + zz); R[5] = yz - wx;
-    R[6] = xz - wy; R[7] = yz + wx; R[8] = 1.f - (xx + yy);
-}
-
-struct FkStep {
-    int node_type;   // MGB_NODE_*
-    int channel;     // quaternion_frame_index or -1
-    int parent_slot; // depth of the node in the walk (the plan is in depth-first order): its parent's transform sits one level up;
-                     // -1 for the root
-    int out_index;   // >= 0: write position to output column out_index
+// K4: the chain root -> joint of every requested joint is walked in quaternion form with the transform in registers (the helpers of
+// the fused kernels: same arithmetic as their forward kinematics).  Shared ancestors are recomputed per requested joint (about 1.5x
+// the arithmetic of a walk over the needed part of the tree with one 3 x 4 matrix per node), but nothing lives in local memory:
+// the matrix walk kept 7.7 KB per thread there and took 1.40 ms where this takes 0.98 ms (32768 x 50 frames, 10 joints).
+struct FkChainStep {
+    int kind;        // 0 root, 1 animated joint, 2 fixed rotation + offset, 3 offset only
+    int channel;
     float off[3];
-    float rot[9];    // fixed rotation
+    float q[4];
 };
 
-#define FK_BLOCK 128
-#define FK_MAX_PLAN 160
-#define FK_MAX_DEPTH 16
-__global__ void __launch_bounds__(FK_BLOCK) mgb_fk_kernel(const float* __restrict__ frames, int P, long long n_frames, const FkStep* __restrict__ plan,
-                                                         int n_plan, int n_out, float* __restrict__ pos) {
+__global__ void __launch_bounds__(FK_BLOCK) mgb_fk_chain_kernel(const float* __restrict__ frames, int P, long long n_frames,
+                                                            const FkChainStep* __restrict__ steps, const int* __restrict__ chain_first,
+                                                            int n_steps, int n_out, float* __restrict__ pos) {
     extern __shared__ __align__(16) float smf[];
-    const int FKB = blockDim.x;  // frames per tile (<= FKB, chosen by the launcher to fit shared memory)
+    const int FKB = blockDim.x;  // frames per tile = threads (chosen by the launcher to fit shared memory)
     const int SROW = P | 1;
-    float* sm_frames = smf;                                  // [FKB][SROW]
-    float* sm_out = smf + (size_t)FKB * SROW;           // [FKB][n_out*3 | 1]
     const int OROW = (n_out * 3) | 1;
-    __shared__ FkStep sm_plan[FK_MAX_PLAN];
-    for (int e = threadIdx.x; e < n_plan; e += FKB) sm_plan[e] = plan[e];
+    float* sm_frames = smf;                                  // [FKB][SROW]
+    float* sm_out = smf + (size_t)FKB * SROW;                // [FKB][OROW]
+    FkChainStep* sm_steps = reinterpret_cast<FkChainStep*>(sm_out + (size_t)FKB * OROW + 1);
+    int* sm_first = reinterpret_cast<int*>(sm_steps + n_steps);
+    for (int e = threadIdx.x; e < n_steps; e += FKB) sm_steps[e] = steps[e];
+    for (int e = threadIdx.x; e <= n_out; e += FKB) sm_first[e] = chain_first[e];
     const long long n_tiles = (n_frames + FKB - 1) / FKB;
     for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
         const long long base = tile * FKB;
@@ -376,59 +362,29 @@ __global__ void __launch_bounds__(FK_BLOCK) mgb_fk_kernel(const float* __restric
             }
         }
         __syncthreads();
-        const float* f = sm_frames + threadIdx.x * SROW;
-        float* o = sm_out + threadIdx.x * OROW;
-        // global transforms of the nodes on the current root-to-node path, one slot per depth (the plan is a depth-first walk:
-        // a node's parent is the last node written one level up).  768 B of local memory instead of 12 floats per plan node
-        // (7.7 KB, which made every transform an L1 / L2 round trip)
-        float Gm[FK_MAX_DEPTH][12];
-        for (int sidx = 0; sidx < n_plan; ++sidx) {
-            const FkStep& st = sm_plan[sidx];
-            float Rl[9], tl[3] = {st.off[0], st.off[1], st.off[2]};
-            bool has_rot = true;
-            if (st.node_type == MGB_NODE_ROOT) {
-                quat_R(f[3], f[4], f[5], f[6], Rl);
-                tl[0] += f[0]; tl[1] += f[1]; tl[2] += f[2];
-            } else if (st.node_type == MGB_NODE_END_SITE) {
-                has_rot = false;
-            } else if (st.channel >= 0) {
-                const float* q = f + 3 + 4 * st.channel;
-                quat_R(q[0], q[1], q[2], q[3], Rl);
-            } else {
-#pragma unroll
-                for (int q = 0; q < 9; ++q) Rl[q] = st.rot[q];
-            }
-            float* Gc = Gm[st.parent_slot + 1];
-            if (st.parent_slot < 0) {
-                if (has_rot) {
-#pragma unroll
-                    for (int q = 0; q < 9; ++q) Gc[q] = Rl[q];
+        for (int w = threadIdx.x; w < FKB * n_out; w += FKB) {
+            const int r = w / n_out, j = w - r * n_out;
+            const float* f = sm_frames + r * SROW;
+            MgbXf G;
+            mgb_xf_identity(G);
+            for (int si = sm_first[j]; si < sm_first[j + 1]; ++si) {
+                const FkChainStep& st = sm_steps[si];
+                if (st.kind == 0) {
+                    mgb_xf_set_rot(G, f[3], f[4], f[5], f[6]);
+                    G.tx = f[0] + st.off[0];
+                    G.ty = f[1] + st.off[1];
+                    G.tz = f[2] + st.off[2];
+                } else if (st.kind == 1) {
+                    const float* q = f + 3 + 4 * st.channel;
+                    mgb_xf_child(G, q[0], q[1], q[2], q[3], st.off[0], st.off[1], st.off[2]);
+                } else if (st.kind == 2) {
+                    mgb_xf_child(G, st.q[0], st.q[1], st.q[2], st.q[3], st.off[0], st.off[1], st.off[2]);
                 } else {
-#pragma unroll
-                    for (int q = 0; q < 9; ++q) Gc[q] = (q % 4 == 0) ? 1.f : 0.f;
-                }
-                Gc[9] = tl[0]; Gc[10] = tl[1]; Gc[11] = tl[2];
-            } else {
-                const float* Gp = Gm[st.parent_slot];
-#pragma unroll
-                for (int a = 0; a < 3; ++a)
-                    Gc[9 + a] = fmaf(Gp[a * 3], tl[0], fmaf(Gp[a * 3 + 1], tl[1], fmaf(Gp[a * 3 + 2], tl[2], Gp[9 + a])));
-                if (has_rot) {
-#pragma unroll
-                    for (int a = 0; a < 3; ++a)
-#pragma unroll
-                        for (int b = 0; b < 3; ++b)
-                            Gc[a * 3 + b] = fmaf(Gp[a * 3], Rl[b], fmaf(Gp[a * 3 + 1], Rl[3 + b], Gp[a * 3 + 2] * Rl[6 + b]));
-                } else {
-#pragma unroll
-                    for (int q = 0; q < 9; ++q) Gc[q] = Gp[q];
+                    mgb_xf_translate(G, st.off[0], st.off[1], st.off[2]);
                 }
             }
-            if (st.out_index >= 0) {
-                o[st.out_index * 3 + 0] = Gc[9];
-                o[st.out_index * 3 + 1] = Gc[10];
-                o[st.out_index * 3 + 2] = Gc[11];
-            }
+            float* o = sm_out + r * OROW + 3 * j;
+            o[0] = G.tx; o[1] = G.ty; o[2] = G.tz;
         }
         __syncthreads();
         {
@@ -601,64 +557,60 @@ extern "C" int mgb_fk(const mgb_model* m, const float* d_frames, int64_t n_frame
     MGB_REQUIRE(m && h_nodes && n_out > 0, "null argument");
     MGB_REQUIRE(n_frames == 0 || (d_frames && d_pos), "null device pointer");
     if (n_frames == 0) return MGB_OK;
-    // plan: every ancestor of a requested node, parents first (node order is topological)
-    std::vector<int> need(m->n_nodes, 0), out_of(m->n_nodes, -1);
-    std::vector<std::vector<int>> outs(m->n_nodes);
+    // one chain root -> node per requested output
+    std::vector<FkChainStep> steps;
+    std::vector<int> first(n_out + 1, 0);
     for (int j = 0; j < n_out; ++j) {
         int nd = h_nodes[j];
         MGB_REQUIRE(nd >= 0 && nd < m->n_nodes, "node index %d out of range", nd);
-        outs[nd].push_back(j);
-        while (nd >= 0 && !need[nd]) {
-            need[nd] = 1;
-            nd = m->parent[nd];
+        std::vector<int> chain;
+        for (; nd >= 0; nd = m->parent[nd]) chain.push_back(nd);
+        first[j] = (int)steps.size();
+        for (int i = (int)chain.size() - 1; i >= 0; --i) {
+            const int c = chain[i];
+            FkChainStep st;
+            st.channel = m->channel[c];
+            for (int q = 0; q < 3; ++q) st.off[q] = (float)m->offset[c * 3 + q];
+            bool ident = true;
+            for (int q = 0; q < 4; ++q) {
+                const double r = (m->type[c] == MGB_NODE_END_SITE) ? (q == 0 ? 1.0 : 0.0) : m->fixed_quat[(size_t)4 * c + q];
+                st.q[q] = (float)r;
+                if (fabs(fabs(r) - (q == 0 ? 1.0 : 0.0)) > 0.0) ident = false;
+            }
+            if (m->type[c] == MGB_NODE_ROOT) st.kind = 0;
+            else if (m->type[c] == MGB_NODE_JOINT && m->channel[c] >= 0) st.kind = 1;
+            else st.kind = ident ? 3 : 2;
+            steps.push_back(st);
         }
     }
-    // depth-first walk over the needed nodes (explicit stack); the kernel keeps one transform per depth
-    std::vector<FkStep> plan;
-    int max_depth = 0;
-    std::vector<std::pair<int, int>> todo;     // (node, depth of its parent)
-    for (int nd = m->n_nodes - 1; nd >= 0; --nd)
-        if (need[nd] && m->parent[nd] < 0) todo.push_back({nd, -1});
-    while (!todo.empty()) {
-        const int nd = todo.back().first, pdepth = todo.back().second;
-        todo.pop_back();
-        // a node requested several times gets one step per extra output (cheap, rare): same depth, same parent
-        for (size_t rep = 0; rep < (outs[nd].empty() ? 1 : outs[nd].size()); ++rep) {
-            FkStep st;
-            st.node_type = m->type[nd];
-            st.channel = m->channel[nd];
-            st.parent_slot = pdepth;
-            st.out_index = outs[nd].empty() ? -1 : outs[nd][rep];
-            for (int q = 0; q < 3; ++q) st.off[q] = (float)m->offset[nd * 3 + q];
-            for (int q = 0; q < 9; ++q) st.rot[q] = (float)m->fixed_rot[nd * 9 + q];
-            plan.push_back(st);
-        }
-        max_depth = std::max(max_depth, pdepth + 1);
-        const std::vector<int>& kids = m->children[nd];
-        for (int i = (int)kids.size() - 1; i >= 0; --i)
-            if (need[kids[i]]) todo.push_back({kids[i], pdepth + 1});
-    }
-    MGB_REQUIRE((int)plan.size() <= FK_MAX_PLAN, "FK plan of %d nodes exceeds %d", (int)plan.size(), FK_MAX_PLAN);
-    MGB_REQUIRE(max_depth < FK_MAX_DEPTH, "skeleton deeper than %d levels", FK_MAX_DEPTH);
-    FkStep* d_plan = nullptr;
-    MGB_CUDA(cudaMallocAsync((void**)&d_plan, sizeof(FkStep) * plan.size(), stream));
-    // pageable source: the runtime stages it before the call returns, so `plan` may go out of scope without a synchronisation
-    MGB_CUDA(cudaMemcpyAsync(d_plan, plan.data(), sizeof(FkStep) * plan.size(), cudaMemcpyHostToDevice, stream));
+    first[n_out] = (int)steps.size();
+    const size_t plan_bytes = sizeof(FkChainStep) * steps.size() + sizeof(int) * (n_out + 1);
+    MGB_REQUIRE(plan_bytes <= 48 * 1024, "FK plan of %d steps too large", (int)steps.size());
+    unsigned char* d_plan = nullptr;
+    MGB_CUDA(cudaMallocAsync((void**)&d_plan, plan_bytes, stream));
+    // pageable sources: the runtime stages them before the calls return, so the vectors may go out of scope without a synchronisation
+    MGB_CUDA(cudaMemcpyAsync(d_plan, steps.data(), sizeof(FkChainStep) * steps.size(), cudaMemcpyHostToDevice, stream));
+    MGB_CUDA(cudaMemcpyAsync(d_plan + sizeof(FkChainStep) * steps.size(), first.data(), sizeof(int) * (n_out + 1), cudaMemcpyHostToDevice, stream));
+    // tile of fkb frames and as many threads, each walking the n_out chains of a frame one after the other (measured: 0.98 ms per
+    // 32768 x 50 frames x 10 joints; one thread per (frame, joint) in 512-thread CTAs of 64 frames: 1.11 ms)
     int fkb = FK_BLOCK;
     size_t smem = 0;
     for (;; fkb >>= 1) {
-        smem = ((size_t)fkb * (m->P | 1) + (size_t)fkb * ((n_out * 3) | 1)) * sizeof(float);
+        smem = ((size_t)fkb * (m->P | 1) + (size_t)fkb * ((n_out * 3) | 1) + 2) * sizeof(float) + plan_bytes;
         if (smem <= 100 * 1024 || fkb == 32) break;
     }
     MGB_REQUIRE(smem <= 200 * 1024, "frame tile too large for shared memory");
+    const int threads = fkb;
     static bool configured[MGB_MAX_DEVICES] = {false};
-    if (int rc = mgb_opt_in_smem(mgb_fk_kernel, configured, 200 * 1024)) return rc;
+    if (int rc = mgb_opt_in_smem(mgb_fk_chain_kernel, configured, 200 * 1024)) return rc;
     int occ = 1;
-    MGB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, mgb_fk_kernel, fkb, smem));
+    MGB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, mgb_fk_chain_kernel, threads, smem));
     long long n_tiles = (n_frames + fkb - 1) / fkb;
     long long grid = (long long)sm_count() * (occ > 0 ? occ : 1);
     if (grid > n_tiles) grid = n_tiles;
-    mgb_fk_kernel<<<(unsigned)grid, fkb, smem, stream>>>(d_frames, m->P, n_frames, d_plan, (int)plan.size(), n_out, d_pos);
+    mgb_fk_chain_kernel<<<(unsigned)grid, threads, smem, stream>>>(d_frames, m->P, n_frames, reinterpret_cast<const FkChainStep*>(d_plan),
+                                                                    reinterpret_cast<const int*>(d_plan + sizeof(FkChainStep) * steps.size()),
+                                                                    (int)steps.size(), n_out, d_pos);
     mgb_count_launch();
     MGB_CUDA(cudaGetLastError());
     MGB_CUDA(cudaFreeAsync(d_plan, stream));
