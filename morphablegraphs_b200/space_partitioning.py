@@ -598,6 +598,8 @@ def _kmeanspp_seeds(x, dim, starts, counts, n_sub, gen):
                     engine._lib.check(lib.mgb_min_sqdist(p(xc), int(xc.shape[0]), int(dim), int(xc.shape[1]), p(node32), p(cj), p(d2),
                                                          1 if j == 0 else 0, stream))
         return cent.contiguous()
+    # CPU tensors: only the world-size-2 gloo tests of the sharded host logic get here (they stand the oracle in for K7; a build on
+    # a CPU device without that stand-in fails in mgb_kmeans_level, which needs the CUDA library) - the same picks in torch index ops
     first = starts + (u[:, 0] * counts).long().minimum(counts - 1)
     cent[:, 0] = x[first, :dim]
     d2 = ((x[:, :dim] - cent[node, 0]) ** 2).sum(dim=1).double()
