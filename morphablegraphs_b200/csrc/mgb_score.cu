@@ -931,8 +931,9 @@ extern "C" int mgb_topk(const float* d_cost, int64_t n, int64_t index_base, int3
         MGB_CUDA(cudaGetLastError());
         return MGB_OK;
     }
-    // k = 1, or arrays too large for one shared-memory chunk per CTA: k passes, each a grid arg-min over the entries
-    // "after" the previous pick
+    // k = 1, or arrays too large for one shared-memory chunk per CTA (n > 592 x 49 152 = 29 M): k passes, each a grid arg-min over
+    // the entries "after" the previous pick.  Known limit of this form: once the selectable entries are exhausted (fewer than k
+    // non-NaN costs) a later pass can pick an infinite-cost entry again; the one-pass form above has no such case.
     long long* part_idx = reinterpret_cast<long long*>(ws);
     float* part_cost = reinterpret_cast<float*>(ws + parts * sizeof(long long));
     long long n_tiles = (n + MGB_BLOCK - 1) / MGB_BLOCK;
