@@ -501,13 +501,15 @@ __global__ void __launch_bounds__(MGB_BLOCK) mgb_score_multi_kernel(const MultiP
 // ---------------------------------------------------------------------------
 __global__ void __launch_bounds__(MGB_BLOCK) mgb_topk_partial(const float* __restrict__ cost, long long n, long long index_base,
                                                              const float* __restrict__ prev_cost, const long long* __restrict__ prev_idx,
-                                                             int have_prev, float* part_cost, long long* part_idx) {
-    // candidates strictly "after" the previous pick in (cost, index) order
+                                                             int have_prev, float* part_cost, long long* part_idx,
+                                                             const int* __restrict__ exhausted) {
+    // candidates strictly "after" the previous pick in (cost, index) order; nothing once a pass has found no entry
     float pc = have_prev ? prev_cost[0] : -INFINITY;
     long long pi = have_prev ? prev_idx[0] : -1;
     float best_c = INFINITY;
     long long best_i = LLONG_MAX;
-    for (long long i = (long long)blockIdx.x * MGB_BLOCK + threadIdx.x; i < n; i += (long long)gridDim.x * MGB_BLOCK) {
+    const long long n_eff = (have_prev && *exhausted) ? 0 : n;
+    for (long long i = (long long)blockIdx.x * MGB_BLOCK + threadIdx.x; i < n_eff; i += (long long)gridDim.x * MGB_BLOCK) {
         float c = cost[i];
         long long gi = index_base + i;
         bool after = !have_prev || (c > pc) || (c == pc && gi > pi);
@@ -532,7 +534,7 @@ __global__ void __launch_bounds__(MGB_BLOCK) mgb_topk_partial(const float* __res
 }
 
 __global__ void mgb_topk_final(const float* part_cost, const long long* part_idx, int nparts, long long index_base,
-                               float* out_cost, long long* out_idx) {
+                               float* out_cost, long long* out_idx, int* exhausted) {
     float best_c = INFINITY;
     long long best_i = LLONG_MAX;
     for (int b = threadIdx.x; b < nparts; b += 32) {
@@ -545,7 +547,10 @@ __global__ void mgb_topk_final(const float* part_cost, const long long* part_idx
         if (better(oc, oi, best_c, best_i)) { best_c = oc; best_i = oi; }
     }
     if (threadIdx.x == 0) {
-        if (best_i == LLONG_MAX) best_i = index_base;
+        if (best_i == LLONG_MAX) {
+            best_i = index_base;
+            *exhausted = 1;      // fewer selectable entries than picks: the remaining slots are (inf, index_base)
+        }
         out_cost[0] = best_c;
         out_idx[0] = best_i;
     }
@@ -932,8 +937,10 @@ extern "C" int mgb_topk(const float* d_cost, int64_t n, int64_t index_base, int3
         return MGB_OK;
     }
     // k = 1, or arrays too large for one shared-memory chunk per CTA (n > 592 x 49 152 = 29 M): k passes, each a grid arg-min over
-    // the entries "after" the previous pick.  Known limit of this form: once the selectable entries are exhausted (fewer than k
-    // non-NaN costs) a later pass can pick an infinite-cost entry again; the one-pass form above has no such case.
+    // the entries "after" the previous pick; a pass that finds nothing raises a flag (in the pad behind the completion counter)
+    // and the later passes fill their slots with (inf, index_base)
+    int* d_exhausted = reinterpret_cast<int*>(ws + parts * (sizeof(long long) + sizeof(float)) + 128);
+    MGB_CUDA(cudaMemsetAsync(d_exhausted, 0, sizeof(int), stream));
     long long* part_idx = reinterpret_cast<long long*>(ws);
     float* part_cost = reinterpret_cast<float*>(ws + parts * sizeof(long long));
     long long n_tiles = (n + MGB_BLOCK - 1) / MGB_BLOCK;
@@ -942,9 +949,9 @@ extern "C" int mgb_topk(const float* d_cost, int64_t n, int64_t index_base, int3
     for (int j = 0; j < k; ++j) {
         mgb_topk_partial<<<grid, MGB_BLOCK, 0, stream>>>(d_cost, n, index_base, j ? d_best_cost + j - 1 : nullptr,
                                                         j ? reinterpret_cast<long long*>(d_best_idx) + j - 1 : nullptr, j ? 1 : 0,
-                                                        part_cost, part_idx);
+                                                        part_cost, part_idx, d_exhausted);
         mgb_topk_final<<<1, 32, 0, stream>>>(part_cost, part_idx, grid, index_base, d_best_cost + j,
-                                             reinterpret_cast<long long*>(d_best_idx) + j);
+                                             reinterpret_cast<long long*>(d_best_idx) + j, d_exhausted);
         mgb_count_launch(2);
     }
     MGB_CUDA(cudaGetLastError());

@@ -1043,3 +1043,40 @@ def test_topk_kernel_against_numpy(n):
         want_c[:len(order)] = cost[order]
         assert list(bi.cpu().numpy()) == list(want_i), (n, k)
         assert np.array_equal(bc.cpu().numpy(), want_c), (n, k)
+
+
+@pytest.mark.gpu
+def test_topk_k_pass_form_on_an_array_beyond_the_one_pass_limit():
+    """n > 592 x 49 152 costs: mgb_topk falls back to k grid arg-min passes.  Dense case against numpy, and the exhausted case
+    (one finite and one infinite entry among NaNs, k = 5): the slots beyond the two selectable entries are (inf, index_base)."""
+    import ctypes as C
+    import torch
+    from morphablegraphs_b200 import _lib
+    lib = _lib.load()
+    n, base, k = 29_200_000, 1000, 5
+    ws = torch.zeros(int(lib.mgb_score_workspace_bytes(n, k)), dtype=torch.uint8, device="cuda")
+    bc = torch.empty(k, dtype=torch.float32, device="cuda")
+    bi = torch.empty(k, dtype=torch.int64, device="cuda")
+
+    def run(d_cost):
+        rc = lib.mgb_topk(C.c_void_p(d_cost.data_ptr()), n, base, k, C.c_void_p(bc.data_ptr()), C.c_void_p(bi.data_ptr()),
+                          C.c_void_p(ws.data_ptr()), ws.numel(), C.c_void_p(torch.cuda.current_stream().cuda_stream))
+        assert rc == 0, lib.mgb_last_error().decode()
+        torch.cuda.synchronize()
+        return bc.cpu().numpy(), bi.cpu().numpy()
+
+    g = torch.Generator(device="cuda")
+    g.manual_seed(1)
+    cost = torch.randint(0, 1 << 20, (n,), generator=g, device="cuda").float()           # ties are likely among the smallest
+    got_c, got_i = run(cost)
+    h = cost.cpu().numpy()
+    kth = np.partition(h, k)[k]
+    cand = np.where(h <= kth)[0]
+    order = cand[np.lexsort((cand, h[cand]))][:k]
+    assert list(got_i) == list(order + base) and np.array_equal(got_c, h[order])
+    sparse = torch.full((n,), float("nan"), device="cuda")
+    sparse[17_000_123] = 3.5
+    sparse[28_999_999] = float("inf")
+    got_c, got_i = run(sparse)
+    assert list(got_i) == [base + 17_000_123, base + 28_999_999, base, base, base]
+    assert got_c[0] == 3.5 and np.all(np.isinf(got_c[1:]))
